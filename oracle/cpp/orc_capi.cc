@@ -1,0 +1,120 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_primitives.h).  ctypes-facing C entry points of the CPU oracle.
+#include "orc_extractor.h"
+#include "orc_matcher.h"
+#include <chrono>
+
+using namespace orc;
+
+extern "C" {
+
+// ---- primitives (checked one by one against cv2) ---------------------------------------------------------------
+void orc_resize_linear(const uint8_t* src, int sw, int sh, int sstride, uint8_t* dst, int dw, int dh, int dstride) {
+    resize_linear_8u(src, sw, sh, sstride, dst, dw, dh, dstride);
+}
+void orc_border101(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride, int b) {
+    make_border_101(src, w, h, sstride, dst, dstride, b);
+}
+void orc_gaussian7(const uint8_t* src, int w, int h, int sstride, uint8_t* dst, int dstride) {
+    gaussian7_8u(src, w, h, sstride, dst, dstride);
+}
+float orc_fast_atan2(float y, float x) { return fast_atan2_deg(y, x); }
+// returns the number of keypoints; writes up to cap (x,y,score) triples
+int orc_fast9_nms(const uint8_t* img, int w, int h, int stride, int th, int* xys, int cap) {
+    std::vector<FastPt> v;
+    fast9_nms(img, w, h, stride, th, v);
+    for (int i = 0; i < (int)v.size() && i < cap; ++i) { xys[3 * i] = v[i].x; xys[3 * i + 1] = v[i].y; xys[3 * i + 2] = v[i].score; }
+    return (int)v.size();
+}
+// std::sort with the reference's compareNodes ordering on (size, ULx) pairs; perm receives the resulting order
+// of the input indices.  Used to validate the device-side emulation of libstdc++'s introsort.
+void orc_sort_nodes(const int* size, const int* ulx, int n, int* perm) {
+    struct E { int s, x, i; };
+    std::vector<E> v(n);
+    for (int i = 0; i < n; ++i) v[i] = {size[i], ulx[i], i};
+    std::sort(v.begin(), v.end(), [](E& a, E& b) { return a.s != b.s ? a.s < b.s : a.x < b.x; });
+    for (int i = 0; i < n; ++i) perm[i] = v[i].i;
+}
+
+// ---- extractor ---------------------------------------------------------------------------------------------------
+void* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh) {
+    return new Extractor(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+}
+void orc_extractor_destroy(void* h) { delete (Extractor*)h; }
+
+void orc_extractor_tables(void* h, float* scale, float* inv, float* sigma2, float* invSigma2, int* perLevel, int* umax16) {
+    Extractor* e = (Extractor*)h;
+    for (int i = 0; i < e->nlevels; ++i) {
+        scale[i] = e->scale[i]; inv[i] = e->invScale[i]; sigma2[i] = e->sigma2[i]; invSigma2[i] = e->invSigma2[i];
+        perLevel[i] = e->featuresPerLevel[i];
+    }
+    for (int i = 0; i < 16; ++i) umax16[i] = e->umax[i];
+}
+
+// kps: n x 6 floats (x, y, size, angle, response, octave-as-float); desc: n x 32.  Returns monoIndex (or -1),
+// *n_out = number of keypoints (may exceed cap: then nothing is written).
+int orc_extract(void* h, const uint8_t* img, int w, int hh, int stride, int lap0, int lap1,
+                float* kps, uint8_t* desc, int cap, int* n_out) {
+    Extractor* e = (Extractor*)h;
+    std::vector<KeyPoint> k; std::vector<uint8_t> d;
+    int mono = e->extract(img, w, hh, stride, lap0, lap1, k, d);
+    *n_out = (int)k.size();
+    if (mono < 0 || (int)k.size() > cap) return mono;
+    for (size_t i = 0; i < k.size(); ++i) {
+        float* o = kps + 6 * i;
+        o[0] = k[i].x; o[1] = k[i].y; o[2] = k[i].size; o[3] = k[i].angle; o[4] = k[i].response; o[5] = (float)k[i].octave;
+    }
+    if (!d.empty()) std::memcpy(desc, d.data(), d.size());
+    return mono;
+}
+
+// timing helper for the CPU baseline: runs extract() `iters` times on the same frame set, returns seconds
+double orc_extract_timed(void* h, const uint8_t* imgs, int nimg, int w, int hh, int stride, int lap0, int lap1, int iters, long* total_kp) {
+    Extractor* e = (Extractor*)h;
+    std::vector<KeyPoint> k; std::vector<uint8_t> d;
+    long tot = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    for (int it = 0; it < iters; ++it) {
+        const uint8_t* img = imgs + (size_t)(it % nimg) * stride * hh;
+        e->extract(img, w, hh, stride, lap0, lap1, k, d);
+        tot += (long)k.size();
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    if (total_kp) *total_kp = tot;
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+void orc_level_size(void* h, int level, int* w, int* hh) {
+    Extractor* e = (Extractor*)h; *w = e->levels[level].w; *hh = e->levels[level].h;
+}
+// which: 0 = unpadded level (w x h), 1 = padded mvImagePyramid buffer ((w+38) x (h+38)), 2 = blurred level (w x h)
+int orc_level_pixels(void* h, int level, int which, uint8_t* out) {
+    Extractor* e = (Extractor*)h; const Extractor::Level& L = e->levels[level];
+    if (which == 1) { std::memcpy(out, L.padded.data(), L.padded.size()); return (int)L.padded.size(); }
+    if (which == 2) { if (L.blurred.empty()) return 0; std::memcpy(out, L.blurred.data(), L.blurred.size()); return (int)L.blurred.size(); }
+    for (int y = 0; y < L.h; ++y) std::memcpy(out + (size_t)y * L.w, L.roi() + (size_t)y * L.pstride, L.w);
+    return L.w * L.h;
+}
+// which: 0 = FAST candidates before culling (x,y relative to minBorder, response), 1 = kept keypoints of the level
+// (x,y level coords incl. border offset, response, angle).  out: n x 4 floats.  Returns n.
+int orc_level_points(void* h, int level, int which, float* out, int cap) {
+    Extractor* e = (Extractor*)h; const Extractor::Level& L = e->levels[level];
+    const std::vector<KeyPoint>& v = which ? L.kept : L.cand;
+    for (int i = 0; i < (int)v.size() && i < cap; ++i) {
+        out[4 * i] = v[i].x; out[4 * i + 1] = v[i].y; out[4 * i + 2] = v[i].response; out[4 * i + 3] = v[i].angle;
+    }
+    return (int)v.size();
+}
+long orc_sort_tie_count(void* h) { return ((Extractor*)h)->sortTieCount; }
+
+// standalone quadtree: keys n x 3 ints (x, y, response) relative to the min border; returns kept count, out n x 3
+int orc_distribute(int nfeatures_unused, const int* keys, int n, int minX, int maxX, int minY, int maxY, int N, int* out, int cap) {
+    (void)nfeatures_unused;
+    Extractor e(1000, 1.2f, 8, 20, 7);
+    std::vector<KeyPoint> v(n);
+    for (int i = 0; i < n; ++i) v[i] = KeyPoint{(float)keys[3 * i], (float)keys[3 * i + 1], 7.f, -1.f, (float)keys[3 * i + 2], 0};
+    std::vector<KeyPoint> r = e.distributeOctTree(v, minX, maxX, minY, maxY, N);
+    for (int i = 0; i < (int)r.size() && i < cap; ++i) { out[3 * i] = (int)r[i].x; out[3 * i + 1] = (int)r[i].y; out[3 * i + 2] = (int)r[i].response; }
+    return (int)r.size();
+}
+
+}  // extern "C"
