@@ -1,0 +1,77 @@
+"""Loader of libmam3slam_b200.so (CUDA kernels + C ABI, include/orbx.h + include/orbm.h).
+
+The library is built in-tree by `__graft_entry__.build()` / `make -C mam3slam_b200/csrc`.  There is no CPU fallback:
+if the library is missing, or no CUDA device is present when a compute entry point is called, this fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libmam3slam_b200.so")
+_LIB = None
+
+
+class OrbxConfig(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int),
+                ("ini_th_fast", C.c_int), ("min_th_fast", C.c_int), ("device", C.c_int), ("max_batch", C.c_int)]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(SO_PATH):
+        raise NativeError(f"{SO_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    L = C.CDLL(SO_PATH)
+    vp, i32, f32, u64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    ip = C.POINTER(C.c_int)
+    L.orbx_device_count.restype = i32
+    L.orbx_strerror.restype = C.c_char_p
+    L.orbx_strerror.argtypes = [i32]
+    L.orbx_last_error.restype = C.c_char_p
+    L.orbx_last_error.argtypes = [vp]
+    L.orbx_create.argtypes = [C.POINTER(OrbxConfig), C.POINTER(vp)]
+    L.orbx_destroy.argtypes = [vp]
+    L.orbx_destroy.restype = None
+    L.orbx_get_tables.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.orbx_max_keypoints.argtypes = [vp]
+    L.orbx_extract.argtypes = [vp, vp, i32, i32, i32, i32, i32, vp, vp, i32, ip, ip]
+    L.orbx_extract_batch.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, i32, vp, vp]
+    L.orbx_extract_device.argtypes = [vp, vp, u64, i32, i32, i32, i32, i32, i32, vp]
+    L.orbx_synchronize.argtypes = [vp]
+    L.orbx_results_device.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(vp), ip, ip]
+    L.orbx_fetch_results.argtypes = [vp, i32, vp, vp, i32, ip, ip]
+    L.orbx_level_size.argtypes = [vp, i32, ip, ip]
+    L.orbx_download_level.argtypes = [vp, i32, i32, i32, vp, i32]
+    L.orbx_download_blurred.argtypes = [vp, i32, i32, vp, i32]
+    L.orbx_download_candidates.argtypes = [vp, i32, i32, vp, i32, ip]
+    L.orbx_download_level_keypoints.argtypes = [vp, i32, i32, vp, i32, ip]
+    L.orbx_debug_sort_nodes.argtypes = [vp, vp, vp, i32, vp, i32]
+    L.orbx_debug_distribute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, ip]
+    L.orbx_launch_count.restype = C.c_longlong
+    L.orbx_launch_count.argtypes = [vp]
+    L.orbx_stream.restype = vp
+    L.orbx_stream.argtypes = [vp]
+    L.orbx_set_stage_timing.argtypes = [vp, i32]
+    L.orbx_stage_times.argtypes = [vp, vp]
+    for name in dir(L):
+        pass
+    _LIB = L
+    return L
+
+
+def check(status, handle=None, what=""):
+    if status == 0:
+        return
+    L = lib()
+    msg = L.orbx_strerror(status).decode()
+    if handle:
+        detail = L.orbx_last_error(handle).decode()
+        if detail:
+            msg += ": " + detail
+    raise NativeError(f"{what} failed ({status}): {msg}")

@@ -1,0 +1,679 @@
+// C ABI of the B200-native ORB extractor: handle management, geometry tables, launch sequence.
+// Host-side logic mirrors ORBextractor's constructor and operator() (src/ORBextractor.cc:409-469, 1086-1168).
+#include "orbx_kernels_desc.cuh"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <algorithm>
+
+using namespace orbx;
+
+namespace {
+
+const int kPatternTable[1024] = {
+#include "../../include/orb_pattern_31.inc"
+};
+
+struct Extractor {
+    orbx_config cfg;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    long long launches = 0;
+
+    // ctor tables (host)
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> perLevel;
+
+    // shape-dependent state
+    int W = 0, H = 0;
+    DevGeom geom;
+    DevGeom* dGeom = nullptr;
+    std::vector<FastCell> cells;
+    FastCell* dCells = nullptr;
+    ResizeTap* dTaps = nullptr;
+    BlurTiles blurTiles;
+    int blurTilesTotal = 0;
+    int fastTilePitch = 0, fastTileRows = 0;
+    size_t fastSmem = 0, treeSmem = 0;
+    int poolCap = 0, scanCap = 0;
+    int maxLevelW4 = 0;
+
+    std::vector<void*> allocs;       // everything cudaMalloc'ed for the current shape
+    uint8_t* dLvl0 = nullptr;        // B x plane(0): staging for host images
+    uint32_t* dCand = nullptr;
+    int* dCellCount = nullptr;
+    uint64_t *dQtA = nullptr, *dQtB = nullptr, *dLvlKp = nullptr;
+    int* dLvlCnt = nullptr;
+    orbx_keypoint* dOutKp = nullptr;
+    uint8_t* dOutDesc = nullptr;
+    int* dOutCnt = nullptr;
+    WorkItem* dWork = nullptr;
+    // pinned host staging
+    uint8_t* hImg = nullptr;
+    orbx_keypoint* hKp = nullptr;
+    uint8_t* hDesc = nullptr;
+    int* hCnt = nullptr;
+    int lastFrames = 0;
+    Level0 lastL0{};
+
+    bool timing = false;
+    cudaEvent_t ev[8] = {};
+    float stageMs[7] = {};
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            E->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return ORBX_ERR_CUDA;                                                                  \
+        }                                                                                          \
+    } while (0)
+
+int cvRoundF(float v) { return (int)lrintf(v); }
+
+void freeShape(Extractor* E) {
+    for (void* p : E->allocs) cudaFree(p);
+    E->allocs.clear();
+    if (E->hImg) cudaFreeHost(E->hImg);
+    if (E->hKp) cudaFreeHost(E->hKp);
+    if (E->hDesc) cudaFreeHost(E->hDesc);
+    if (E->hCnt) cudaFreeHost(E->hCnt);
+    E->hImg = nullptr; E->hKp = nullptr; E->hDesc = nullptr; E->hCnt = nullptr;
+    E->W = E->H = 0;
+}
+
+template <class T>
+int devAlloc(Extractor* E, T** p, size_t count) {
+    void* q = nullptr;
+    CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+    E->allocs.push_back(q);
+    *p = (T*)q;
+    return ORBX_OK;
+}
+
+// 11-bit bilinear taps of cv::resize; `rows` keeps the fraction at the ends (rows are clamped instead)
+void makeTaps(int ssize, int dsize, bool rows, std::vector<ResizeTap>& out) {
+    const double invScale = (double)dsize / ssize;
+    const double sc = 1.0 / invScale;
+    for (int d = 0; d < dsize; ++d) {
+        float f = (float)((d + 0.5) * sc - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (!rows) {
+            if (s < 0) { f = 0.f; s = 0; }
+            if (s >= ssize - 1) { f = 0.f; s = ssize - 1; }
+        }
+        ResizeTap t;
+        t.ofs = s;
+        t.c0 = (short)cvRoundF((1.f - f) * 2048.f);
+        t.c1 = (short)cvRoundF(f * 2048.f);
+        out.push_back(t);
+    }
+}
+
+// (Re)build every shape-dependent table and buffer.
+int configureShape(Extractor* E, int W, int H) {
+    if (E->W == W && E->H == H) return ORBX_OK;
+    freeShape(E);
+    const int L = E->cfg.nlevels, B = E->cfg.max_batch;
+    DevGeom& g = E->geom;
+    memset(&g, 0, sizeof(g));
+    g.nlevels = L; g.iniTh = E->cfg.ini_th_fast; g.minTh = E->cfg.min_th_fast;
+    E->cells.clear();
+    std::vector<ResizeTap> taps;
+    size_t qtOff = 0; int kpOff = 0, candOff = 0, maxCells = 0, maxCellW = 0, maxCellH = 0;
+    E->poolCap = 0;
+    int tileStart = 0;
+    for (int l = 0; l < L; ++l) {
+        LevelGeom& G = g.lv[l];
+        G.w = cvRoundF((float)W * E->invScale[l]);           // :1174-1175
+        G.h = cvRoundF((float)H * E->invScale[l]);
+        G.pitch = (G.w + 127) & ~127;
+        G.planeBytes = ((size_t)G.pitch * G.h + 255) & ~(size_t)255;
+        G.scale = E->scale[l];
+        G.sizeF = (float)(int)(31 * E->scale[l]);            // scaledPatchSize (:876)
+        G.quota = E->perLevel[l];
+        const int maxBX = G.w - kEdge + 3, maxBY = G.h - kEdge + 3;
+        const float width = (float)(maxBX - kMinBorder), height = (float)(maxBY - kMinBorder);
+        if (width < 35.f || height < 35.f) { E->err = "pyramid level smaller than one 35-px FAST cell"; return ORBX_ERR_UNSUPPORTED; }
+        G.nCols = (int)(width / 35.f); G.nRows = (int)(height / 35.f);
+        G.wCell = (int)ceilf(width / G.nCols); G.hCell = (int)ceilf(height / G.nRows);
+        G.treeW = maxBX - kMinBorder; G.treeH = maxBY - kMinBorder;
+        G.nIni = (int)roundf((float)G.treeW / (float)G.treeH);   // :559
+        if (G.nIni < 1) { E->err = "image too tall for the quadtree root layout (nIni = 0)"; return ORBX_ERR_UNSUPPORTED; }
+        G.hX = (float)G.treeW / G.nIni;
+        if (G.w > 65535 || G.h > 65535) { E->err = "level larger than 65535"; return ORBX_ERR_UNSUPPORTED; }
+        G.cellBegin = (int)E->cells.size();
+        G.candCap = 0;
+        for (int i = 0; i < G.nRows; ++i) {
+            const float iniY = (float)(kMinBorder + i * G.hCell);
+            float maxY = iniY + G.hCell + 6;
+            if (iniY >= maxBY - 3) continue;
+            if (maxY > maxBY) maxY = (float)maxBY;
+            for (int j = 0; j < G.nCols; ++j) {
+                const float iniX = (float)(kMinBorder + j * G.wCell);
+                float maxX = iniX + G.wCell + 6;
+                if (iniX >= maxBX - 6) continue;
+                if (maxX > maxBX) maxX = (float)maxBX;
+                FastCell c;
+                c.level = (short)l;
+                c.x0 = (short)((int)iniX + 3); c.y0 = (short)((int)iniY + 3);
+                c.w = (short)((int)maxX - (int)iniX - 6); c.h = (short)((int)maxY - (int)iniY - 6);
+                if (c.w <= 0 || c.h <= 0) continue;           // cv::FAST tests nothing in a < 7 px wide window
+                c.relX = (short)(j * G.wCell + 3); c.relY = (short)(i * G.hCell + 3);
+                c.pad = 0;
+                c.cap = ((c.w + 1) / 2) * ((c.h + 1) / 2);    // 3x3 strict maxima cannot be denser
+                c.outOffset = candOff;
+                candOff += c.cap; G.candCap += c.cap;
+                if (c.w > 255 || c.h > 255 || c.w * c.h > 32 * kFastThreads) { E->err = "FAST cell too large"; return ORBX_ERR_UNSUPPORTED; }
+                maxCellW = std::max<int>(maxCellW, c.w); maxCellH = std::max<int>(maxCellH, c.h);
+                E->cells.push_back(c);
+            }
+        }
+        G.cellEnd = (int)E->cells.size();
+        maxCells = std::max(maxCells, G.cellEnd - G.cellBegin);
+        G.poolCap = std::max(G.quota + 3, 4 * G.nIni) + 5;
+        E->poolCap = std::max(E->poolCap, G.poolCap);
+        G.kpCap = G.poolCap; G.kpOffset = kpOff; kpOff += G.kpCap;
+        G.qtOffset = qtOff; qtOff += (size_t)G.candCap + 32;
+        if (l > 0) {
+            const LevelGeom& P = g.lv[l - 1];
+            G.areaFast = (P.w == 2 * G.w && P.h == 2 * G.h) ? 1 : 0;
+            G.tabX = (int)taps.size(); makeTaps(P.w, G.w, false, taps);
+            G.tabY = (int)taps.size(); makeTaps(P.h, G.h, true, taps);
+        }
+        E->blurTiles.start[l] = tileStart;
+        E->blurTiles.tilesX[l] = (G.w + kBlurTW - 1) / kBlurTW;
+        tileStart += E->blurTiles.tilesX[l] * ((G.h + kBlurTH - 1) / kBlurTH);
+    }
+    E->blurTiles.start[L] = tileStart;
+    E->blurTilesTotal = tileStart;
+    g.nCells = (int)E->cells.size();
+    g.candCapFrame = candOff; g.qtCapFrame = qtOff; g.kpCapFrame = kpOff; g.outCap = kpOff;
+    if (E->poolCap > 60000) { E->err = "nfeatures too large"; return ORBX_ERR_UNSUPPORTED; }
+    E->scanCap = std::max(std::max(E->poolCap, maxCells), 64) + 8;
+    E->treeSmem = tree_smem_layout(E->poolCap, E->scanCap, nullptr, nullptr);
+    E->fastTilePitch = (maxCellW + 6 + 3 + 3) & ~3;
+    E->fastTileRows = maxCellH + 6;
+    E->fastSmem = (size_t)E->fastTileRows * E->fastTilePitch + (size_t)(maxCellH + 2) * (maxCellW + 2) + 16;
+    if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
+    CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
+    CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+
+    // device buffers
+    for (int l = 0; l < L; ++l) {
+        int rc;
+        if (l > 0) { if ((rc = devAlloc(E, &g.lvl[l], g.lv[l].planeBytes * B + 256))) return rc; }
+        if ((rc = devAlloc(E, &g.blur[l], g.lv[l].planeBytes * B + 256))) return rc;
+    }
+    int rc;
+    if ((rc = devAlloc(E, &E->dLvl0, g.lv[0].planeBytes * B + 256))) return rc;
+    g.lvl[0] = E->dLvl0;
+    if ((rc = devAlloc(E, &E->dCand, (size_t)g.candCapFrame * B))) return rc;
+    if ((rc = devAlloc(E, &E->dCellCount, (size_t)g.nCells * B))) return rc;
+    if ((rc = devAlloc(E, &E->dQtA, g.qtCapFrame * B))) return rc;
+    if ((rc = devAlloc(E, &E->dQtB, g.qtCapFrame * B))) return rc;
+    if ((rc = devAlloc(E, &E->dLvlKp, (size_t)g.kpCapFrame * B))) return rc;
+    if ((rc = devAlloc(E, &E->dLvlCnt, (size_t)L * B))) return rc;
+    if ((rc = devAlloc(E, &E->dOutKp, (size_t)g.outCap * B))) return rc;
+    if ((rc = devAlloc(E, &E->dOutDesc, (size_t)g.outCap * B * 32))) return rc;
+    if ((rc = devAlloc(E, &E->dOutCnt, (size_t)2 * B))) return rc;
+    if ((rc = devAlloc(E, &E->dWork, (size_t)g.outCap * B))) return rc;
+    if ((rc = devAlloc(E, &E->dGeom, 1))) return rc;
+    if ((rc = devAlloc(E, &E->dCells, E->cells.size()))) return rc;
+    if ((rc = devAlloc(E, &E->dTaps, taps.size()))) return rc;
+    CK(cudaMemcpy(E->dGeom, &g, sizeof(g), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(E->dCells, E->cells.data(), E->cells.size() * sizeof(FastCell), cudaMemcpyHostToDevice));
+    if (!taps.empty()) CK(cudaMemcpy(E->dTaps, taps.data(), taps.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
+    CK(cudaMallocHost((void**)&E->hImg, g.lv[0].planeBytes * B));
+    CK(cudaMallocHost((void**)&E->hKp, (size_t)g.outCap * B * sizeof(orbx_keypoint)));
+    CK(cudaMallocHost((void**)&E->hDesc, (size_t)g.outCap * B * 32));
+    CK(cudaMallocHost((void**)&E->hCnt, (size_t)2 * B * sizeof(int)));
+    E->W = W; E->H = H;
+    E->lastFrames = 0;
+    return ORBX_OK;
+}
+
+// The launch sequence of one pass over `n` frames whose level 0 lives at l0.
+int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st) {
+    const DevGeom& g = E->geom;
+    const int L = g.nlevels;
+    const bool tm = E->timing;
+    int evi = 0;
+    auto mark = [&]() { if (tm) cudaEventRecord(E->ev[evi++], st); };
+    mark();
+    for (int l = 1; l < L; ++l) {
+        dim3 grid((g.lv[l].w + 127) / 128, (g.lv[l].h + 7) / 8, n), block(32, 8);
+        k_pyr_level<<<grid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps);
+        ++E->launches;
+    }
+    mark();
+    k_fast_cells<<<dim3(g.nCells, n), kFastThreads, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount,
+                                                                        E->fastTilePitch, E->fastTileRows);
+    ++E->launches;
+    mark();
+    k_octree<<<dim3(L, n), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,
+                                                            E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap);
+    ++E->launches;
+    mark();
+    k_blur7<<<dim3(E->blurTilesTotal, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles);
+    ++E->launches;
+    mark();
+    k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork);
+    ++E->launches;
+    mark();
+    k_orient_brief<<<dim3((g.outCap + kDescWarps - 1) / kDescWarps, n), kDescWarps * 32, 0, st>>>(
+        E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc);
+    ++E->launches;
+    mark();
+    CK(cudaGetLastError());
+    E->lastFrames = n;
+    E->lastL0 = l0;
+    return ORBX_OK;
+}
+
+}  // namespace
+
+struct orbx_extractor : Extractor {};
+#define E_FROM(h) Extractor* E = static_cast<Extractor*>(h)
+
+extern "C" {
+
+int orbx_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+const char* orbx_strerror(int s) {
+    switch (s) {
+        case ORBX_OK: return "ok";
+        case ORBX_ERR_INVALID: return "invalid argument";
+        case ORBX_ERR_CUDA: return "CUDA error";
+        case ORBX_ERR_CAPACITY: return "output buffer too small";
+        case ORBX_ERR_UNSUPPORTED: return "unsupported configuration";
+        case ORBX_ERR_NO_DEVICE: return "no CUDA device (no CPU fallback exists)";
+    }
+    return "unknown";
+}
+
+const char* orbx_last_error(orbx_handle h) { return h ? h->err.c_str() : ""; }
+
+int orbx_create(const orbx_config* cfg, orbx_handle* out) {
+    if (!cfg || !out || cfg->nfeatures <= 0 || cfg->nlevels <= 0 || cfg->nlevels > kMaxLevels || cfg->scale_factor < 1.f ||
+        cfg->max_batch < 1)
+        return ORBX_ERR_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return ORBX_ERR_NO_DEVICE;
+    if (cfg->device < 0 || cfg->device >= ndev) return ORBX_ERR_INVALID;
+    orbx_extractor* E = new orbx_extractor();
+    E->cfg = *cfg;
+    E->device = cfg->device;
+    const int L = cfg->nlevels;
+    // scale tables and per-level quotas with the constructor's float arithmetic (:414-445)
+    const double sf = (double)cfg->scale_factor;
+    E->scale.assign(L, 1.f); E->sigma2.assign(L, 1.f); E->invScale.resize(L); E->invSigma2.resize(L);
+    for (int i = 1; i < L; ++i) {
+        E->scale[i] = (float)(E->scale[i - 1] * sf);
+        E->sigma2[i] = E->scale[i] * E->scale[i];
+    }
+    for (int i = 0; i < L; ++i) { E->invScale[i] = 1.0f / E->scale[i]; E->invSigma2[i] = 1.0f / E->sigma2[i]; }
+    E->perLevel.resize(L);
+    const float factor = (float)(1.0f / sf);
+    float want = cfg->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l < L - 1; ++l) { E->perLevel[l] = cvRoundF(want); sum += E->perLevel[l]; want *= factor; }
+    E->perLevel[L - 1] = std::max(cfg->nfeatures - sum, 0);
+
+    auto fail = [&](cudaError_t e) { fprintf(stderr, "orbx_create: %s\n", cudaGetErrorString(e)); delete E; return ORBX_ERR_CUDA; };
+    cudaError_t e;
+    if ((e = cudaSetDevice(E->device)) != cudaSuccess) return fail(e);
+    if ((e = cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
+    for (auto& ev : E->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e);
+    // algorithm constants: circular-patch half-widths (:453-468) and the BRIEF pattern
+    int umax[16];
+    const int vmax = (int)floorf(kHalfPatch * sqrtf(2.f) / 2 + 1), vmin = (int)ceilf(kHalfPatch * sqrtf(2.f) / 2);
+    for (int v = 0; v <= vmax; ++v) umax[v] = (int)lrint(sqrt((double)kHalfPatch * kHalfPatch - v * v));
+    for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (umax[v0] == umax[v0 + 1]) ++v0;
+        umax[v] = v0; ++v0;
+    }
+    char4 pat[256];
+    for (int i = 0; i < 256; ++i)
+        pat[i] = make_char4((char)kPatternTable[4 * i], (char)kPatternTable[4 * i + 1], (char)kPatternTable[4 * i + 2], (char)kPatternTable[4 * i + 3]);
+    if ((e = cudaMemcpyToSymbol(c_umax, umax, sizeof(umax))) != cudaSuccess) return fail(e);
+    if ((e = cudaMemcpyToSymbol(c_pattern, pat, sizeof(pat))) != cudaSuccess) return fail(e);
+    *out = E;
+    return ORBX_OK;
+}
+
+void orbx_destroy(orbx_handle h) {
+    if (!h) return;
+    E_FROM(h);
+    cudaSetDevice(E->device);
+    cudaStreamSynchronize(E->stream);
+    freeShape(E);
+    for (auto& ev : E->ev) if (ev) cudaEventDestroy(ev);
+    if (E->stream) cudaStreamDestroy(E->stream);
+    delete h;
+}
+
+int orbx_get_tables(orbx_handle h, float* scale, float* inv, float* sigma2, float* invSigma2, int* perLevel) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    for (int i = 0; i < E->cfg.nlevels; ++i) {
+        if (scale) scale[i] = E->scale[i];
+        if (inv) inv[i] = E->invScale[i];
+        if (sigma2) sigma2[i] = E->sigma2[i];
+        if (invSigma2) invSigma2[i] = E->invSigma2[i];
+        if (perLevel) perLevel[i] = E->perLevel[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_max_keypoints(orbx_handle h) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (E->W) return E->geom.outCap;
+    int s = 0;
+    for (int q : E->perLevel) s += q + 24;     // shape-independent bound; the exact bound needs nIni per level
+    return s;
+}
+
+}  // extern "C"
+
+// ---- extraction entry points -------------------------------------------------------------------------------------
+namespace {
+
+int collectStageTimes(Extractor* E) {
+    if (!E->timing) return ORBX_OK;
+    float tot = 0;
+    for (int i = 0; i < 6; ++i) {
+        CK(cudaEventElapsedTime(&E->stageMs[i], E->ev[i], E->ev[i + 1]));
+        tot += E->stageMs[i];
+    }
+    E->stageMs[6] = tot;
+    return ORBX_OK;
+}
+
+// copy the results of frames [0,n) of the last pass to the pinned staging area and wait
+int stageResults(Extractor* E, int n, cudaStream_t st) {
+    const DevGeom& g = E->geom;
+    CK(cudaMemcpyAsync(E->hCnt, E->dOutCnt, (size_t)2 * n * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(E->hKp, E->dOutKp, (size_t)n * g.outCap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(E->hDesc, E->dOutDesc, (size_t)n * g.outCap * 32, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return collectStageTimes(E);
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int width, int height, int stride,
+                       int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_out) {
+    if (!h || !imgs || nimg <= 0 || !n_out || !mono_out) return ORBX_ERR_INVALID;
+    if (width <= 0 || height <= 0) return ORBX_ERR_INVALID;    // the reference returns -1 for an empty image (:1090)
+    if (stride < width) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    CK(cudaSetDevice(E->device));
+    int rc = configureShape(E, width, height);
+    if (rc) return rc;
+    const DevGeom& g = E->geom;
+    const int B = E->cfg.max_batch;
+    const int p0 = g.lv[0].pitch;
+    const size_t plane = g.lv[0].planeBytes;
+    int status = ORBX_OK;
+    for (int base = 0; base < nimg; base += B) {
+        const int n = std::min(B, nimg - base);
+        for (int f = 0; f < n; ++f) {
+            const uint8_t* src = imgs[base + f];
+            if (!src) return ORBX_ERR_INVALID;
+            uint8_t* dst = E->hImg + (size_t)f * plane;
+            if (stride == p0) memcpy(dst, src, (size_t)p0 * (height - 1) + width);
+            else for (int y = 0; y < height; ++y) memcpy(dst + (size_t)y * p0, src + (size_t)y * stride, width);
+        }
+        CK(cudaMemcpyAsync(E->dLvl0, E->hImg, plane * n, cudaMemcpyHostToDevice, E->stream));
+        Level0 l0{E->dLvl0, plane, p0};
+        if ((rc = runPass(E, l0, n, lap0, lap1, E->stream))) return rc;
+        if ((rc = stageResults(E, n, E->stream))) return rc;
+        for (int f = 0; f < n; ++f) {
+            const int cnt = E->hCnt[2 * f];
+            n_out[base + f] = cnt;
+            mono_out[base + f] = E->hCnt[2 * f + 1];
+            if (cnt > cap) { status = ORBX_ERR_CAPACITY; continue; }
+            if (kps) memcpy(kps + (size_t)(base + f) * cap, E->hKp + (size_t)f * g.outCap, (size_t)cnt * sizeof(orbx_keypoint));
+            if (desc) memcpy(desc + (size_t)(base + f) * cap * 32, E->hDesc + (size_t)f * g.outCap * 32, (size_t)cnt * 32);
+        }
+    }
+    return status;
+}
+
+int orbx_extract(orbx_handle h, const uint8_t* img, int width, int height, int stride, int lap0, int lap1,
+                 orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_out) {
+    if (!img) return ORBX_ERR_INVALID;
+    const uint8_t* one[1] = {img};
+    return orbx_extract_batch(h, one, 1, width, height, stride, lap0, lap1, kps, desc, cap, n_out, mono_out);
+}
+
+int orbx_extract_device(orbx_handle h, const uint8_t* d_imgs, size_t image_bytes, int nimg, int width, int height,
+                        int stride, int lap0, int lap1, void* stream) {
+    if (!h || !d_imgs || nimg <= 0 || width <= 0 || height <= 0 || stride < width) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (nimg > E->cfg.max_batch) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    int rc = configureShape(E, width, height);
+    if (rc) return rc;
+    Level0 l0{d_imgs, image_bytes, stride};
+    return runPass(E, l0, nimg, lap0, lap1, stream ? (cudaStream_t)stream : E->stream);
+}
+
+int orbx_synchronize(orbx_handle h) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    CK(cudaSetDevice(E->device));
+    CK(cudaStreamSynchronize(E->stream));
+    return collectStageTimes(E);
+}
+
+int orbx_results_device(orbx_handle h, int frame, const orbx_keypoint** d_kps, const uint32_t** d_desc, int* n_out, int* mono_out) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (frame < 0 || frame >= E->lastFrames) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    int cnt[2];
+    CK(cudaMemcpyAsync(cnt, E->dOutCnt + 2 * frame, sizeof(cnt), cudaMemcpyDeviceToHost, E->stream));
+    CK(cudaStreamSynchronize(E->stream));
+    if (d_kps) *d_kps = E->dOutKp + (size_t)frame * E->geom.outCap;
+    if (d_desc) *d_desc = reinterpret_cast<const uint32_t*>(E->dOutDesc + (size_t)frame * E->geom.outCap * 32);
+    if (n_out) *n_out = cnt[0];
+    if (mono_out) *mono_out = cnt[1];
+    return ORBX_OK;
+}
+
+int orbx_fetch_results(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_out) {
+    const orbx_keypoint* dk; const uint32_t* dd; int n, mono;
+    int rc = orbx_results_device(h, frame, &dk, &dd, &n, &mono);
+    if (rc) return rc;
+    E_FROM(h);
+    if (n_out) *n_out = n;
+    if (mono_out) *mono_out = mono;
+    if (n > cap) return ORBX_ERR_CAPACITY;
+    if (kps && n) CK(cudaMemcpy(kps, dk, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
+    if (desc && n) CK(cudaMemcpy(desc, dd, (size_t)n * 32, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+int orbx_level_size(orbx_handle h, int level, int* width, int* height) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (!E->W || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
+    if (width) *width = E->geom.lv[level].w;
+    if (height) *height = E->geom.lv[level].h;
+    return ORBX_OK;
+}
+
+static int downloadPlane(Extractor* E, const uint8_t* dsrc, int pitch, int w, int hgt, int padded, uint8_t* dst, int dst_stride) {
+    std::vector<uint8_t> tmp((size_t)w * hgt);
+    CK(cudaStreamSynchronize(E->stream));
+    CK(cudaMemcpy2D(tmp.data(), w, dsrc, pitch, w, hgt, cudaMemcpyDeviceToHost));
+    if (!padded) {
+        for (int y = 0; y < hgt; ++y) memcpy(dst + (size_t)y * dst_stride, &tmp[(size_t)y * w], w);
+        return ORBX_OK;
+    }
+    // mvImagePyramid's backing buffer: 19-px BORDER_REFLECT_101 ring synthesised from the level itself (:1185,1190).
+    // Nothing on the mono hot path reads the ring (FAST, IC_Angle and BRIEF stay >= 1 px inside the level), so the
+    // device never stores it; it is produced here for callers that read the padded pyramid (stereo matching).
+    auto refl = [](int p, int n) { if (n == 1) return 0; while (p < 0 || p >= n) p = p < 0 ? -p : 2 * (n - 1) - p; return p; };
+    for (int y = -kEdge; y < hgt + kEdge; ++y) {
+        const uint8_t* S = &tmp[(size_t)refl(y, hgt) * w];
+        uint8_t* D = dst + (size_t)(y + kEdge) * dst_stride;
+        for (int x = -kEdge; x < w + kEdge; ++x) D[x + kEdge] = S[refl(x, w)];
+    }
+    return ORBX_OK;
+}
+
+int orbx_download_level(orbx_handle h, int frame, int level, int padded, uint8_t* dst, int dst_stride) {
+    if (!h || !dst) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    const LevelGeom& G = E->geom.lv[level];
+    const uint8_t* src; int pitch;
+    if (level == 0) { src = E->lastL0.base + (size_t)frame * E->lastL0.frameBytes; pitch = E->lastL0.pitch; }
+    else { src = E->geom.lvl[level] + (size_t)frame * G.planeBytes; pitch = G.pitch; }
+    return downloadPlane(E, src, pitch, G.w, G.h, padded, dst, dst_stride);
+}
+
+int orbx_download_blurred(orbx_handle h, int frame, int level, uint8_t* dst, int dst_stride) {
+    if (!h || !dst) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    const LevelGeom& G = E->geom.lv[level];
+    return downloadPlane(E, E->geom.blur[level] + (size_t)frame * G.planeBytes, G.pitch, G.w, G.h, 0, dst, dst_stride);
+}
+
+int orbx_download_candidates(orbx_handle h, int frame, int level, int* out, int cap, int* n_out) {
+    if (!h || !n_out) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    CK(cudaStreamSynchronize(E->stream));
+    const DevGeom& g = E->geom;
+    const LevelGeom& G = g.lv[level];
+    std::vector<int> counts(g.nCells);
+    std::vector<uint32_t> cand(g.candCapFrame);
+    CK(cudaMemcpy(counts.data(), E->dCellCount + (size_t)frame * g.nCells, counts.size() * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(cand.data(), E->dCand + (size_t)frame * g.candCapFrame, cand.size() * 4, cudaMemcpyDeviceToHost));
+    int n = 0;
+    for (int c = G.cellBegin; c < G.cellEnd; ++c) {
+        const FastCell& fc = E->cells[c];
+        for (int k = 0; k < counts[c]; ++k, ++n) {
+            if (n >= cap || !out) continue;
+            const uint32_t e = cand[fc.outOffset + k];
+            out[3 * n] = (int)(e & 255u) + fc.relX; out[3 * n + 1] = (int)((e >> 8) & 255u) + fc.relY; out[3 * n + 2] = (int)(e >> 16);
+        }
+    }
+    *n_out = n;
+    return n > cap ? ORBX_ERR_CAPACITY : ORBX_OK;
+}
+
+int orbx_download_level_keypoints(orbx_handle h, int frame, int level, int* out, int cap, int* n_out) {
+    if (!h || !n_out) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
+    CK(cudaSetDevice(E->device));
+    CK(cudaStreamSynchronize(E->stream));
+    const DevGeom& g = E->geom;
+    const LevelGeom& G = g.lv[level];
+    int n = 0;
+    CK(cudaMemcpy(&n, E->dLvlCnt + frame * g.nlevels + level, 4, cudaMemcpyDeviceToHost));
+    *n_out = n;
+    if (n > cap) return ORBX_ERR_CAPACITY;
+    std::vector<uint64_t> keys(n);
+    if (n) CK(cudaMemcpy(keys.data(), E->dLvlKp + (size_t)frame * g.kpCapFrame + G.kpOffset, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && out; ++i) {
+        out[3 * i] = (int)(keys[i] & 0xffff); out[3 * i + 1] = (int)((keys[i] >> 16) & 0xffff); out[3 * i + 2] = (int)((keys[i] >> 32) & 0xff);
+    }
+    return ORBX_OK;
+}
+
+int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n, int* perm, int mode) {
+    if (!h || n < 0) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    CK(cudaSetDevice(E->device));
+    std::vector<ise::Elem> e(std::max(n, 1));
+    for (int i = 0; i < n; ++i) { e[i].key = ((uint64_t)(uint32_t)size[i] << 32) | (uint32_t)ul_x[i]; e[i].id = i; e[i].pad = 0; }
+    ise::Elem* d = nullptr;
+    CK(cudaMalloc((void**)&d, e.size() * sizeof(ise::Elem)));
+    cudaError_t er = cudaMemcpy(d, e.data(), e.size() * sizeof(ise::Elem), cudaMemcpyHostToDevice);
+    if (er == cudaSuccess) { k_debug_sort<<<1, 32, 0, E->stream>>>(d, n, mode); ++E->launches; er = cudaStreamSynchronize(E->stream); }
+    if (er == cudaSuccess) er = cudaMemcpy(e.data(), d, e.size() * sizeof(ise::Elem), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    CK(er);
+    for (int i = 0; i < n; ++i) perm[i] = e[i].id;
+    return ORBX_OK;
+}
+
+int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,
+                          int n_features, int* out, int cap, int* n_out) {
+    if (!h || n < 0 || !n_out || max_x <= min_x || max_y <= min_y || n_features < 1) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    CK(cudaSetDevice(E->device));
+    const int treeW = max_x - min_x, treeH = max_y - min_y;
+    const int nIni = (int)roundf((float)treeW / (float)treeH);
+    if (nIni < 1) return ORBX_ERR_UNSUPPORTED;
+    const float hX = (float)treeW / nIni;
+    const int P = std::max(n_features + 3, 4 * nIni) + 5;
+    const int scanCap = std::max(P, 64) + 8;
+    const size_t smem = tree_smem_layout(P, scanCap, nullptr, nullptr);
+    if (smem > 200 * 1024) return ORBX_ERR_UNSUPPORTED;
+    CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    std::vector<uint64_t> k(std::max(n, 1));
+    for (int i = 0; i < n; ++i)
+        k[i] = (uint64_t)(uint32_t)keys[3 * i] | ((uint64_t)(uint32_t)keys[3 * i + 1] << 16) | ((uint64_t)(uint32_t)keys[3 * i + 2] << 32);
+    uint64_t *dA = nullptr, *dB = nullptr, *dOut = nullptr; int* dCnt = nullptr;
+    cudaError_t er = cudaMalloc((void**)&dA, k.size() * 8);
+    if (er == cudaSuccess) er = cudaMalloc((void**)&dB, k.size() * 8);
+    if (er == cudaSuccess) er = cudaMalloc((void**)&dOut, (size_t)P * 8);
+    if (er == cudaSuccess) er = cudaMalloc((void**)&dCnt, 4);
+    if (er == cudaSuccess) er = cudaMemcpy(dA, k.data(), k.size() * 8, cudaMemcpyHostToDevice);
+    int cnt = 0;
+    std::vector<uint64_t> res(P);
+    if (er == cudaSuccess) {
+        k_debug_distribute<<<1, kTreeThreads, smem, E->stream>>>(dA, dB, n, n_features, nIni, hX, treeH, dOut, dCnt, P, scanCap);
+        ++E->launches;
+        er = cudaStreamSynchronize(E->stream);
+    }
+    if (er == cudaSuccess) er = cudaMemcpy(&cnt, dCnt, 4, cudaMemcpyDeviceToHost);
+    if (er == cudaSuccess) er = cudaMemcpy(res.data(), dOut, (size_t)P * 8, cudaMemcpyDeviceToHost);
+    cudaFree(dA); cudaFree(dB); cudaFree(dOut); cudaFree(dCnt);
+    CK(er);
+    *n_out = cnt;
+    if (cnt > cap) return ORBX_ERR_CAPACITY;
+    for (int i = 0; i < cnt && out; ++i) {
+        out[3 * i] = (int)(res[i] & 0xffff); out[3 * i + 1] = (int)((res[i] >> 16) & 0xffff); out[3 * i + 2] = (int)((res[i] >> 32) & 0xff);
+    }
+    return ORBX_OK;
+}
+
+long long orbx_launch_count(orbx_handle h) { return h ? static_cast<Extractor*>(h)->launches : 0; }
+void* orbx_stream(orbx_handle h) { return h ? (void*)static_cast<Extractor*>(h)->stream : nullptr; }
+
+int orbx_set_stage_timing(orbx_handle h, int enable) {
+    if (!h) return ORBX_ERR_INVALID;
+    static_cast<Extractor*>(h)->timing = enable != 0;
+    return ORBX_OK;
+}
+int orbx_stage_times(orbx_handle h, float* ms7) {
+    if (!h || !ms7) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    for (int i = 0; i < 7; ++i) ms7[i] = E->stageMs[i];
+    return ORBX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,244 @@
+// Quadtree driver (E3/E4), output assembly (E8), orientation (E5) and rotated BRIEF (E7).
+// Reference: src/ORBextractor.cc:874-895 (post-octree fix-up), :76-103 (IC_Angle), :106-146 (computeOrbDescriptor),
+// :1086-1168 (operator() assembly, lapping order).
+#pragma once
+#include "orbx_kernels_image.cuh"
+#include "orbx_kernels_tree.cuh"
+
+namespace orbx {
+
+__constant__ int c_umax[16];          // circular patch half-widths (src/ORBextractor.cc:453-468)
+__constant__ char4 c_pattern[256];    // rBRIEF tests (x0,y0,x1,y1), include/orb_pattern_31.inc
+
+__host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+// shared-memory carve-up of the tree state; the host uses the same function to size the launch
+__host__ __device__ inline size_t tree_smem_layout(int P, int scanCap, TreeSmem* S, uint8_t* base) {
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += align16(bytes); return at; };
+    size_t r0 = take((size_t)P * 8), r1 = take((size_t)P * 8);
+    size_t b0 = take((size_t)P * 4), b1 = take((size_t)P * 4);
+    size_t c0 = take((size_t)P * 4), c1 = take((size_t)P * 4);
+    size_t pe = take((size_t)P * 16), cc = take((size_t)P * 16);
+    size_t sa = take((size_t)scanCap * 4), sb = take((size_t)scanCap * 4);
+    size_t pr = take((size_t)P * 2), dv = take((size_t)P);
+    if (S) {
+        S->rect[0] = (ushort4*)(base + r0); S->rect[1] = (ushort4*)(base + r1);
+        S->beg[0] = (uint32_t*)(base + b0); S->beg[1] = (uint32_t*)(base + b1);
+        S->cnt[0] = (uint32_t*)(base + c0); S->cnt[1] = (uint32_t*)(base + c1);
+        S->pend = (ise::Elem*)(base + pe); S->cc = (uint4*)(base + cc);
+        S->scanA = (int*)(base + sa); S->scanB = (int*)(base + sb);
+        S->proc = (uint16_t*)(base + pr); S->dv = base + dv;
+    }
+    return o;
+}
+
+// One CTA per (level, frame): gather the level's FAST candidates in the reference's order (cells row-major,
+// raster inside a cell), cull with the quadtree, leave the kept keys in list order.
+__global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
+                                                         const uint32_t* __restrict__ cand, const int* __restrict__ cellCount,
+                                                         uint64_t* qtA, uint64_t* qtB, uint64_t* lvlKp, int* lvlCnt,
+                                                         int P, int scanCap) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ int sW[33];
+    TreeSmem S;
+    tree_smem_layout(P, scanCap, &S, smem);
+    const int l = blockIdx.x, frame = blockIdx.y;
+    const LevelGeom& L = g->lv[l];
+    const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    const int cb = L.cellBegin, nc = L.cellEnd - L.cellBegin;
+    const int* cc = cellCount + (size_t)frame * g->nCells + cb;
+    for (int i = tid; i < nc; i += kTreeThreads) S.scanA[i] = cc[i];
+    __syncthreads();
+    const int n = block_exscan(S.scanA, nc, sW);
+    uint64_t* bufA = qtA + (size_t)frame * g->qtCapFrame + L.qtOffset;
+    uint64_t* bufB = qtB + (size_t)frame * g->qtCapFrame + L.qtOffset;
+    const uint32_t* cf = cand + (size_t)frame * g->candCapFrame;
+    for (int c = wid; c < nc; c += kTreeWarps) {
+        const FastCell cell = cells[cb + c];
+        const int cnt = cc[c], off = S.scanA[c];
+        for (int k = lane; k < cnt; k += 32) {
+            const uint32_t e = cf[cell.outOffset + k];
+            const uint32_t x = (e & 255u) + cell.relX, y = ((e >> 8) & 255u) + cell.relY, sc = e >> 16;
+            bufA[off + k] = (uint64_t)x | ((uint64_t)y << 16) | ((uint64_t)sc << 32);
+        }
+    }
+    __syncthreads();
+    uint64_t* const buf[2] = {bufA, bufB};
+    distribute_tree(buf, n, L.quota, L.nIni, L.hX, L.treeH, S,
+                    lvlKp + (size_t)frame * g->kpCapFrame + L.kpOffset, lvlCnt + frame * g->nlevels + l);
+}
+
+// standalone tree for tests: keys (x | y<<16 | score<<32) already in bufA
+__global__ void __launch_bounds__(kTreeThreads) k_debug_distribute(uint64_t* bufA, uint64_t* bufB, int n, int N, int nIni,
+                                                                   float hX, int treeH, uint64_t* out, int* outCount,
+                                                                   int P, int scanCap) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    TreeSmem S;
+    tree_smem_layout(P, scanCap, &S, smem);
+    uint64_t* const buf[2] = {bufA, bufB};
+    distribute_tree(buf, n, N, nIni, hX, treeH, S, out, outCount);
+}
+
+__global__ void k_debug_sort(ise::Elem* e, int n, int mode) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        if (mode == 1) ise::heap_sort(e, 0, n);
+        else ise::sort(e, n);
+    }
+}
+
+struct WorkItem { short level; short pad; int x, y; int dst; };   // keypoint in level coordinates + output slot
+
+// E4 + E8: one CTA per frame.  Walk the kept lists level by level (the reference's order), add the border offset,
+// scale to level-0 coordinates, and place every keypoint where operator() would (:1143-1164): points inside
+// [lap0, lap1] fill the output from the BACK in reverse, the others from the front; monoIndex = number at the front.
+constexpr int kFinalThreads = 256;
+__global__ void __launch_bounds__(kFinalThreads) k_finalize(const DevGeom* __restrict__ g, const uint64_t* __restrict__ lvlKp,
+                                                            const int* __restrict__ lvlCnt, int lap0, int lap1,
+                                                            orbx_keypoint* outKp, int* outCnt, WorkItem* work) {
+    __shared__ int sOff[kMaxLevels + 1];
+    __shared__ int sWarp[kFinalThreads / 32 + 1];
+    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int L = g->nlevels;
+    if (tid == 0) {
+        int o = 0;
+        for (int l = 0; l < L; ++l) { sOff[l] = o; o += lvlCnt[frame * L + l]; }
+        sOff[L] = o;
+    }
+    __syncthreads();
+    const int n = min(sOff[L], g->outCap);
+    const int per = (n + kFinalThreads - 1) / kFinalThreads;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    const float fl0 = (float)lap0, fl1 = (float)lap1;
+    const uint64_t* kf = lvlKp + (size_t)frame * g->kpCapFrame;
+    // pass 1: count lapping keypoints in my chunk
+    int myLap = 0;
+    int l = 0;
+    for (int o = b; o < e; ++o) {
+        while (o >= sOff[l + 1]) ++l;
+        const uint64_t key = kf[g->lv[l].kpOffset + (o - sOff[l])];
+        float x = (float)((int)(key & 0xffff) + kMinBorder);
+        if (l != 0) x = __fmul_rn(x, g->lv[l].scale);
+        myLap += (x >= fl0 && x <= fl1) ? 1 : 0;
+    }
+    int incl = myLap;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
+    if (lane == 31) sWarp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int v = lane < kFinalThreads / 32 ? sWarp[lane] : 0, iv = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { int t = __shfl_up_sync(0xffffffffu, iv, s); if (lane >= s) iv += t; }
+        if (lane < kFinalThreads / 32) sWarp[lane] = iv - v;
+        if (lane == 31) sWarp[kFinalThreads / 32] = iv;
+    }
+    __syncthreads();
+    int lapBefore = sWarp[wid] + incl - myLap;
+    const int lapTotal = sWarp[kFinalThreads / 32];
+    orbx_keypoint* ok = outKp + (size_t)frame * g->outCap;
+    WorkItem* wk = work + (size_t)frame * g->outCap;
+    l = 0;
+    for (int o = b; o < e; ++o) {
+        while (o >= sOff[l + 1]) ++l;
+        const LevelGeom& G = g->lv[l];
+        const uint64_t key = kf[G.kpOffset + (o - sOff[l])];
+        const int xi = (int)(key & 0xffff) + kMinBorder, yi = (int)((key >> 16) & 0xffff) + kMinBorder;
+        float x = (float)xi, y = (float)yi;
+        if (l != 0) { x = __fmul_rn(x, G.scale); y = __fmul_rn(y, G.scale); }
+        const bool lap = (x >= fl0 && x <= fl1);
+        const int dst = lap ? (n - 1 - lapBefore) : (o - lapBefore);
+        lapBefore += lap ? 1 : 0;
+        orbx_keypoint k;
+        k.x = x; k.y = y; k.size = G.sizeF; k.angle = -1.f; k.response = (float)(int)((key >> 32) & 0xff);
+        k.octave = l; k.class_id = -1;
+        ok[dst] = k;
+        WorkItem w; w.level = (short)l; w.pad = 0; w.x = xi; w.y = yi; w.dst = dst;
+        wk[o] = w;
+    }
+    if (tid == 0) { outCnt[2 * frame] = n; outCnt[2 * frame + 1] = n - lapTotal; }
+}
+
+// cv::fastAtan2 scalar path, evaluated without FMA contraction so that it matches a plain float CPU build.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    constexpr float p1 = 0.9997878412794807f * (float)(180 / 3.14159265358979323846);
+    constexpr float p3 = -0.3258083974640975f * (float)(180 / 3.14159265358979323846);
+    constexpr float p5 = 0.1555786518463281f * (float)(180 / 3.14159265358979323846);
+    constexpr float p7 = -0.04432655554792128f * (float)(180 / 3.14159265358979323846);
+    constexpr float eps = (float)2.2204460492503131e-16;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        const float c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        const float c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// E5 + E7: one warp per keypoint.  Orientation: lanes = columns u=-15..15 of the radius-15 disc on the UNBLURRED
+// level, int32 moments, shuffle reduction.  Descriptor: lane i produces byte i (8 of the 256 tests) on the BLURRED
+// level; pattern points rotated in float with separately rounded products (no FMA), cvRound = round-half-even.
+constexpr int kDescWarps = 8;
+__global__ void __launch_bounds__(kDescWarps * 32) k_orient_brief(const DevGeom* __restrict__ g, Level0 l0,
+                                                                  const WorkItem* __restrict__ work,
+                                                                  const int* __restrict__ outCnt, orbx_keypoint* outKp,
+                                                                  uint8_t* outDesc) {
+    const int frame = blockIdx.y;
+    const int o = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (o >= outCnt[2 * frame]) return;
+    const WorkItem w = work[(size_t)frame * g->outCap + o];
+    int pitch;
+    const uint8_t* img = level_ptr(g, l0, w.level, frame, &pitch);
+    const uint8_t* ctr = img + (size_t)w.y * pitch + w.x;
+    int m10 = 0, m01 = 0;
+    const int u = lane - kHalfPatch;
+    if (lane < 31) {
+        const int au = abs(u);
+#pragma unroll 1
+        for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+            if (au <= c_umax[abs(v)]) {
+                const int val = ctr[v * pitch + u];
+                m10 += u * val;
+                m01 += v * val;
+            }
+        }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, s);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    orbx_keypoint* kp = outKp + (size_t)frame * g->outCap + w.dst;
+    if (lane == 0) kp->angle = angle;
+
+    constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
+    const float rad = __fmul_rn(angle, factorPI);
+    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+    const LevelGeom& G = g->lv[w.level];
+    const uint8_t* bc = g->blur[w.level] + (size_t)frame * G.planeBytes + (size_t)w.y * G.pitch + w.x;
+    const int bp = G.pitch;
+    int byte = 0;
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+        const char4 t = c_pattern[lane * 8 + bit];
+        const float x0 = (float)t.x, y0 = (float)t.y, x1 = (float)t.z, y1 = (float)t.w;
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int v0 = bc[r0 * bp + c0], v1 = bc[r1 * bp + c1];
+        byte |= (v0 < v1 ? 1 : 0) << bit;
+    }
+    outDesc[((size_t)frame * g->outCap + w.dst) * 32 + lane] = (uint8_t)byte;
+}
+
+}  // namespace orbx

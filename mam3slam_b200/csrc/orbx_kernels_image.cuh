@@ -1,0 +1,282 @@
+// Image-plane kernels of the extractor: pyramid level (E1), per-cell FAST (E2), 7x7 Gaussian (E6).
+// Reference behaviour: src/ORBextractor.cc:1170-1195 (ComputePyramid), :781-872 (FAST grid), :1131-1133 (blur);
+// pixel arithmetic = OpenCV 4.x 8-bit paths, restated independently in oracle/cpp.
+#pragma once
+#include "orbx_internal.h"
+
+namespace orbx {
+
+struct Level0 {                    // where level 0 (the input image) lives for this pass
+    const uint8_t* base;
+    size_t frameBytes;
+    int pitch;
+};
+
+__device__ __forceinline__ const uint8_t* level_ptr(const DevGeom* g, const Level0& l0, int l, int frame, int* pitch) {
+    if (l == 0) { *pitch = l0.pitch; return l0.base + (size_t)frame * l0.frameBytes; }
+    *pitch = g->lv[l].pitch;
+    return g->lvl[l] + (size_t)frame * g->lv[l].planeBytes;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// E1: one pyramid level from the previous one.  cv::resize INTER_LINEAR on 8U: 11-bit fixed-point taps, horizontal
+// pass in int32, vertical pass ((b0*(r0>>4))>>16 + (b1*(r1>>4))>>16 + 2)>>2.  Each thread produces 4 adjacent
+// pixels of one row and stores them as one 32-bit word (rows are 128-B aligned).  HBM-bound: reads ~1.44 source
+// bytes and writes 1 byte per output pixel; taps come from a table built once per shape on the host.
+// grid (ceil(w/128), ceil(h/8), B), block (32, 8).
+__global__ void __launch_bounds__(256) k_pyr_level(const DevGeom* __restrict__ g, Level0 l0, int l,
+                                                   const ResizeTap* __restrict__ taps) {
+    const LevelGeom& D = g->lv[l];
+    const LevelGeom& S = g->lv[l - 1];
+    const int frame = blockIdx.z;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (y >= D.h || x4 >= D.w) return;
+    int sp;
+    const uint8_t* src = level_ptr(g, l0, l - 1, frame, &sp);
+    uint8_t* dst = g->lvl[l] + (size_t)frame * D.planeBytes + (size_t)y * D.pitch;
+    uint32_t packed = 0;
+    if (D.areaFast) {
+        const uint8_t* r0 = src + (size_t)(2 * y) * sp;
+        const uint8_t* r1 = r0 + sp;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int x = x4 + k;
+            if (x < D.w) {
+                int v = (r0[2 * x] + r0[2 * x + 1] + r1[2 * x] + r1[2 * x + 1] + 2) >> 2;
+                packed |= (uint32_t)v << (8 * k);
+            }
+        }
+    } else {
+        const ResizeTap ty = taps[D.tabY + y];
+        const int s0 = min(max(ty.ofs, 0), S.h - 1), s1 = min(max(ty.ofs + 1, 0), S.h - 1);
+        const uint8_t* r0 = src + (size_t)s0 * sp;
+        const uint8_t* r1 = src + (size_t)s1 * sp;
+        const int b0 = ty.c0, b1 = ty.c1;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            int x = x4 + k;
+            if (x < D.w) {
+                const ResizeTap tx = taps[D.tabX + x];
+                const int a = tx.ofs, a1 = min(tx.ofs + 1, S.w - 1);
+                const int h0 = r0[a] * tx.c0 + r0[a1] * tx.c1;
+                const int h1 = r1[a] * tx.c0 + r1[a1] * tx.c1;
+                const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                packed |= (uint32_t)v << (8 * k);
+            }
+        }
+    }
+    if (x4 + 3 < D.w) {
+        *reinterpret_cast<uint32_t*>(dst + x4) = packed;
+    } else {
+        for (int k = 0; k < 4 && x4 + k < D.w; ++k) dst[x4 + k] = (uint8_t)(packed >> (8 * k));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// E2: FAST-9/16 strength of one pixel: s = max over the 16 cyclic 9-arcs of max(min(v - ring), min(ring - v)).
+// cv::FAST declares a corner at threshold t iff s > t and reports response s-1.
+// Sliding 9-window minima by doubling (2,4,8,+1) on both d = v-ring and e = ring-v.
+// NOTE (toolchain): the obvious form max(lo9, -hi9) (min and max over the same d) MISCOMPILES with nvcc 12.9 for
+// sm_100a: ptxas fuses the negation into VIMNMX3 and the result is max(d) (measured on B200: 69 instead of 0 for
+// v=123, ring={78,128,101,87,114,99,101,115,95,111,129,76,83,87,54,83}; tools/t_fs.cu).  Using only min/max of
+// non-negated operands avoids the pattern; tests/test_extractor_gpu.py pins the vector.
+__device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
+    int d[16], e[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { d[k] = v - r[k]; e[k] = r[k] - v; }
+    int d2[16], e2[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { d2[k] = min(d[k], d[(k + 1) & 15]); e2[k] = min(e[k], e[(k + 1) & 15]); }
+    int d4[16], e4[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { d4[k] = min(d2[k], d2[(k + 2) & 15]); e4[k] = min(e2[k], e2[(k + 2) & 15]); }
+    int best = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int d9 = min(min(d4[k], d4[(k + 4) & 15]), d[(k + 8) & 15]);
+        const int e9 = min(min(e4[k], e4[(k + 4) & 15]), e[(k + 8) & 15]);
+        best = max(best, max(d9, e9));
+    }
+    return best;
+}
+
+// One CTA per reference FAST cell.  The cell's pixels (+3 ring halo) are staged in shared memory with aligned
+// 32-bit loads, every tested pixel's strength is computed once at minThFAST, then the reference's per-cell logic
+// runs on the shared score tile: NMS at iniThFAST; if that leaves the cell empty, NMS at minThFAST
+// (src/ORBextractor.cc:826-846).  Neighbours outside the cell's tested interior count as 0, exactly like a
+// cv::FAST call on the sub-image.  Survivors are compacted in raster order into the cell's fixed slot range.
+// grid (nCells, B), block 256.  dynamic smem: tile + score tile.
+constexpr int kFastThreads = 256;
+
+__global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
+                                                             const FastCell* __restrict__ cells,
+                                                             uint32_t* __restrict__ cand, int* __restrict__ cellCount,
+                                                             int tilePitchMax, int tileRowsMax) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const FastCell c = cells[blockIdx.x];
+    const int frame = blockIdx.y;
+    const int tid = threadIdx.x;
+    int pitch;
+    const uint8_t* img = level_ptr(g, l0, c.level, frame, &pitch);
+    const int w = c.w, h = c.h;
+    const int tw = w + 6, th = h + 6;
+    uint8_t* tile = smem;                                  // th rows x tp
+    const int gx0 = c.x0 - 3, gy0 = c.y0 - 3;
+    const uint8_t* origin = img + (size_t)gy0 * pitch + gx0;
+    const int a = (int)((uintptr_t)origin & 3);            // leading bytes so that rows start word-aligned
+    const bool aligned = (pitch & 3) == 0;
+    const int tp = tilePitchMax;                            // multiple of 4
+    uint8_t* score = smem + (size_t)tileRowsMax * tp;      // (h+2) x (w+2), apron = 0
+    const int sp = w + 2;
+
+    if (aligned) {
+        const int wordsPerRow = (tw + a + 3) >> 2;
+        const uint8_t* base = origin - a;
+        for (int i = tid; i < wordsPerRow * th; i += kFastThreads) {
+            int ry = i / wordsPerRow, rw = i - ry * wordsPerRow;
+            uint32_t v = *reinterpret_cast<const uint32_t*>(base + (size_t)ry * pitch + 4 * rw);
+            *reinterpret_cast<uint32_t*>(tile + ry * tp + 4 * rw) = v;
+        }
+    } else {
+        for (int i = tid; i < tw * th; i += kFastThreads) {
+            int ry = i / tw, rx = i - ry * tw;
+            tile[ry * tp + rx + a] = origin[(size_t)ry * pitch + rx];
+        }
+    }
+    for (int i = tid; i < (h + 2) * sp; i += kFastThreads) score[i] = 0;
+    __syncthreads();
+
+    const int minTh = g->minTh, iniTh = g->iniTh;
+    const int npx = w * h;
+    for (int p = tid; p < npx; p += kFastThreads) {
+        const int py = p / w, px = p - py * w;
+        const uint8_t* ctr = tile + (py + 3) * tp + px + 3 + a;
+        const int v = ctr[0];
+        // compass pre-test: every 9-arc contains at least two of ring points 0,4,8,12
+        const int r0 = ctr[3 * tp], r4 = ctr[3], r8 = ctr[-3 * tp], r12 = ctr[-3];
+        const int hi = (r0 > v + minTh) + (r4 > v + minTh) + (r8 > v + minTh) + (r12 > v + minTh);
+        const int lo = (r0 < v - minTh) + (r4 < v - minTh) + (r8 < v - minTh) + (r12 < v - minTh);
+        if (hi < 2 && lo < 2) continue;
+        int r[16];
+        r[0] = r0;               r[1] = ctr[3 * tp + 1];   r[2] = ctr[2 * tp + 2];   r[3] = ctr[tp + 3];
+        r[4] = r4;               r[5] = ctr[-tp + 3];      r[6] = ctr[-2 * tp + 2];  r[7] = ctr[-3 * tp + 1];
+        r[8] = r8;               r[9] = ctr[-3 * tp - 1];  r[10] = ctr[-2 * tp - 2]; r[11] = ctr[-tp - 3];
+        r[12] = r12;             r[13] = ctr[tp - 3];      r[14] = ctr[2 * tp - 2];  r[15] = ctr[3 * tp - 1];
+        const int s = fast_strength(v, r);
+        if (s > minTh) score[(py + 1) * sp + px + 1] = (uint8_t)s;
+    }
+    __syncthreads();
+
+    // NMS at both thresholds over a contiguous raster chunk per thread (<= 32 pixels)
+    const int per = (npx + kFastThreads - 1) / kFastThreads;
+    const int pb = tid * per, pe = min(pb + per, npx);
+    uint32_t keepIni = 0, keepMin = 0;
+    for (int p = pb; p < pe; ++p) {
+        const int py = p / w, px = p - py * w;
+        const uint8_t* sc = score + (py + 1) * sp + px + 1;
+        const int s = sc[0];
+        if (s == 0) continue;
+        int nbMin = 0, nbIni = 0;     // max neighbour stored score at each threshold
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+                if (dx == 0 && dy == 0) continue;
+                const int q = sc[dy * sp + dx];
+                nbMin = max(nbMin, q);
+                nbIni = max(nbIni, q > iniTh ? q : 0);
+            }
+        // stored scores are strength-1 on both sides of the comparison; strength 0 means "not a corner" (score 0)
+        const int mine = s - 1;
+        if (mine > max(nbMin - 1, 0)) keepMin |= 1u << (p - pb);
+        if (s > iniTh && mine > max(nbIni - 1, 0)) keepIni |= 1u << (p - pb);
+    }
+    __shared__ int warpSum[kFastThreads / 32];
+    __shared__ int total;
+    const int lane = tid & 31, wid = tid >> 5;
+    const int anyIni = __syncthreads_or(keepIni != 0);
+    const uint32_t keep = anyIni ? keepIni : keepMin;
+    const int cnt = __popc(keep);
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) warpSum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int v = lane < kFastThreads / 32 ? warpSum[lane] : 0;
+        int iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
+        if (lane < kFastThreads / 32) warpSum[lane] = iv - v;
+        if (lane == 31) total = iv;
+    }
+    __syncthreads();
+    int rank = warpSum[wid] + incl - cnt;
+    uint32_t* out = cand + (size_t)frame * g->candCapFrame + c.outOffset;
+    uint32_t m = keep;
+    while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1;
+        const int p = pb + b;
+        const int py = p / w, px = p - py * w;
+        const int s = score[(py + 1) * sp + px + 1];
+        out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
+    }
+    if (tid == 0) cellCount[(size_t)frame * g->nCells + blockIdx.x] = total;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// E6: cv::GaussianBlur 7x7 sigma 2 on 8U = separable fixed-point kernel [18,34,48,56,48,34,18]/256, no intermediate
+// rounding, (sum + 2^15) >> 16, BORDER_REFLECT_101 at the edge of the (unpadded) level.  One CTA blurs a 64x32
+// tile: load 70x38 u8 -> horizontal pass to 64x38 u16 -> vertical pass -> u8.  grid (tiles over all levels, B).
+constexpr int kBlurTW = 64, kBlurTH = 32;
+
+__device__ __forceinline__ int reflect101_dev(int p, int n) {
+    if (n == 1) return 0;
+    while (p < 0 || p >= n) p = p < 0 ? -p : 2 * (n - 1) - p;
+    return p;
+}
+
+struct BlurTiles { int start[kMaxLevels + 1]; int tilesX[kMaxLevels]; };
+
+__global__ void __launch_bounds__(256) k_blur7(const DevGeom* __restrict__ g, Level0 l0, BlurTiles bt) {
+    __shared__ uint8_t in[(kBlurTH + 6) * (kBlurTW + 8)];
+    __shared__ uint16_t hb[(kBlurTH + 6) * kBlurTW];
+    const int frame = blockIdx.y;
+    int l = 0;
+    while (l + 1 < g->nlevels && (int)blockIdx.x >= bt.start[l + 1]) ++l;
+    const int t = blockIdx.x - bt.start[l];
+    const int tx = t % bt.tilesX[l], ty = t / bt.tilesX[l];
+    const LevelGeom& L = g->lv[l];
+    int pitch;
+    const uint8_t* src = level_ptr(g, l0, l, frame, &pitch);
+    const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
+    const int tid = threadIdx.x;
+    constexpr int IP = kBlurTW + 8;
+    for (int i = tid; i < (kBlurTH + 6) * (kBlurTW + 6); i += 256) {
+        const int ry = i / (kBlurTW + 6), rx = i - ry * (kBlurTW + 6);
+        const int sy = reflect101_dev(min(y0 + ry - 3, L.h + 2), L.h);
+        const int sx = reflect101_dev(min(x0 + rx - 3, L.w + 2), L.w);
+        in[ry * IP + rx] = src[(size_t)sy * pitch + sx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (kBlurTH + 6) * kBlurTW; i += 256) {
+        const int ry = i / kBlurTW, rx = i - ry * kBlurTW;
+        const uint8_t* p = in + ry * IP + rx;
+        hb[i] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
+    }
+    __syncthreads();
+    uint8_t* dst = g->blur[l] + (size_t)frame * L.planeBytes;
+    for (int i = tid; i < kBlurTH * kBlurTW; i += 256) {
+        const int ry = i / kBlurTW, rx = i - ry * kBlurTW;
+        const int x = x0 + rx, y = y0 + ry;
+        if (x >= L.w || y >= L.h) continue;
+        const uint16_t* p = hb + ry * kBlurTW + rx;
+        const uint32_t acc = 18u * (p[0] + p[6 * kBlurTW]) + 34u * (p[kBlurTW] + p[5 * kBlurTW]) +
+                             48u * (p[2 * kBlurTW] + p[4 * kBlurTW]) + 56u * p[3 * kBlurTW];
+        dst[(size_t)y * L.pitch + x] = (uint8_t)((acc + 32768u) >> 16);
+    }
+}
+
+}  // namespace orbx

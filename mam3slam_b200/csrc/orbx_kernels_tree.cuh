@@ -1,0 +1,377 @@
+// E3: DistributeOctTree on device (src/ORBextractor.cc:555-779; DivideNode :480-536; compareNodes :538-553).
+//
+// The reference walks a std::list of nodes that own std::vector<KeyPoint> copies.  Here one CTA owns one
+// (frame, level) and keeps:
+//   * the keys as 64-bit words (x | y<<16 | score<<32) in two ping-pong HBM/L2 buffers; a node owns a contiguous
+//     segment [beg, beg+cnt) of one of them, and splitting a node is a STABLE 4-way partition of that segment into
+//     the other buffer (stable = the reference's push_back order inside every child);
+//   * the list as an ARRAY in shared memory that is rebuilt after every pass: a pass of the reference only ever
+//     pushes children to the list front and erases the split parents, so the new list is
+//         [children of the nodes split in this pass, last split first, each as n4,n3,n2,n1] ++ [unsplit nodes in old order],
+//     which is computed with prefix sums instead of pointer surgery;
+//   * the "split the largest first" phase (:689-753) with an exact emulation of libstdc++ std::sort
+//     (introsort_emul.h), because compareNodes ties are resolved by the sort's element movement.
+// Every partition is speculative-safe: children are written to the other buffer, so a node that ends up not being
+// split (the >= N early exit) still owns intact data.
+#pragma once
+#include "orbx_internal.h"
+#include "introsort_emul.h"
+
+namespace orbx {
+
+constexpr int kTreeThreads = 512;
+constexpr int kTreeWarps = kTreeThreads / 32;
+constexpr int kCtaPartitionMin = 1024;   // nodes with at least this many keys are partitioned by the whole CTA
+
+struct TreeSmem {                   // carved out of dynamic shared memory, sized by poolCap P and scanCap
+    ushort4* rect[2];               // x0,y0,x1,y1
+    uint32_t* beg[2];               // segment start | buffer flag << 31
+    uint32_t* cnt[2];
+    ise::Elem* pend;                // pending (splittable) nodes of the current list: key=(cnt<<32)|x0, id=list index
+    uint4* cc;                      // child key counts of a node being split, indexed by list position
+    int* scanA;                     // generic scan array (>= max(P, cells per level)+1)
+    int* scanB;
+    uint16_t* proc;                 // processing order (list positions)
+    uint8_t* dv;                    // node was split in this pass
+};
+
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+    return v;
+}
+
+// In-place exclusive scan of a[0..n) by the whole CTA; returns the total.  Ends with a barrier.
+__device__ int block_exscan(int* a, int n, int* sWarp /* >= 33 ints */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int per = (n + kTreeThreads - 1) / kTreeThreads;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    int sum = 0;
+    for (int i = b; i < e; ++i) sum += a[i];
+    const int incl = warp_incl_scan(sum, lane);
+    if (lane == 31) sWarp[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int v = lane < kTreeWarps ? sWarp[lane] : 0;
+        int iv = warp_incl_scan(v, lane);
+        sWarp[lane] = iv - v;
+        if (lane == 31) sWarp[32] = iv;
+    }
+    __syncthreads();
+    int run = sWarp[wid] + incl - sum;
+    for (int i = b; i < e; ++i) { int t = a[i]; a[i] = run; run += t; }
+    const int total = sWarp[32];
+    __syncthreads();
+    return total;
+}
+
+// class of a key for DivideNode: n1=0 (x<mx,y<my), n2=1 (x>=mx,y<my), n3=2 (x<mx,y>=my), n4=3
+struct QuadClass {
+    int mx, my;
+    __device__ __forceinline__ int operator()(uint64_t k) const {
+        const int x = (int)(k & 0xffff), y = (int)((k >> 16) & 0xffff);
+        return (x < mx ? 0 : 1) + (y < my ? 0 : 2);
+    }
+};
+// class of a key for the root assignment vpIniNodes[kp.pt.x/hX] (:585), restricted to roots [base, base+4)
+struct RootClass {
+    float hX; int base;
+    __device__ __forceinline__ int operator()(uint64_t k) const {
+        const float x = (float)(int)(k & 0xffff);
+        return (int)__fdiv_rn(x, hX) - base;        // outside 0..3 = not in this group
+    }
+};
+
+// Stable 4-way partition of src[beg, beg+cnt) into dst starting at outBase, by one warp.  Returns class counts.
+template <class F>
+__device__ __forceinline__ uint4 warp_partition4(const uint64_t* src, uint64_t* dst, int beg, int cnt, int outBase, F cls) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1;
+    int n0 = 0, n1 = 0, n2 = 0, n3 = 0;
+    uint64_t keep = 0; int keepQ = -1;
+    for (int base = 0; base < cnt; base += 32) {
+        const int i = base + lane;
+        int q = -1; uint64_t k = 0;
+        if (i < cnt) { k = src[beg + i]; q = cls(k); }
+        n0 += __popc(__ballot_sync(0xffffffffu, q == 0));
+        n1 += __popc(__ballot_sync(0xffffffffu, q == 1));
+        n2 += __popc(__ballot_sync(0xffffffffu, q == 2));
+        n3 += __popc(__ballot_sync(0xffffffffu, q == 3));
+        keep = k; keepQ = q;
+    }
+    int o0 = outBase, o1 = o0 + n0, o2 = o1 + n1, o3 = o2 + n2;
+    for (int base = 0; base < cnt; base += 32) {
+        const int i = base + lane;
+        int q; uint64_t k;
+        if (cnt <= 32) { q = keepQ; k = keep; }
+        else { q = -1; k = 0; if (i < cnt) { k = src[beg + i]; q = cls(k); } }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, q == 0), b1 = __ballot_sync(0xffffffffu, q == 1);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, q == 2), b3 = __ballot_sync(0xffffffffu, q == 3);
+        if (q == 0) dst[o0 + __popc(b0 & lt)] = k;
+        else if (q == 1) dst[o1 + __popc(b1 & lt)] = k;
+        else if (q == 2) dst[o2 + __popc(b2 & lt)] = k;
+        else if (q == 3) dst[o3 + __popc(b3 & lt)] = k;
+        o0 += __popc(b0); o1 += __popc(b1); o2 += __popc(b2); o3 += __popc(b3);
+    }
+    return make_uint4(n0, n1, n2, n3);
+}
+
+// Same, by the whole CTA (warps own contiguous chunks).  All threads must call it; ends with a barrier.
+template <class F>
+__device__ uint4 cta_partition4(const uint64_t* src, uint64_t* dst, int beg, int cnt, int outBase, F cls,
+                                int (*sCnt)[4] /* [kTreeWarps+1][4] */) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t lt = (1u << lane) - 1;
+    int chunk = (cnt + kTreeWarps - 1) / kTreeWarps;
+    chunk = (chunk + 31) & ~31;
+    const int cb = min(wid * chunk, cnt), ce = min(cb + chunk, cnt);
+    int n0 = 0, n1 = 0, n2 = 0, n3 = 0;
+    for (int base = cb; base < ce; base += 32) {
+        const int i = base + lane;
+        int q = -1;
+        if (i < ce) q = cls(src[beg + i]);
+        n0 += __popc(__ballot_sync(0xffffffffu, q == 0));
+        n1 += __popc(__ballot_sync(0xffffffffu, q == 1));
+        n2 += __popc(__ballot_sync(0xffffffffu, q == 2));
+        n3 += __popc(__ballot_sync(0xffffffffu, q == 3));
+    }
+    if (lane == 0) { sCnt[wid][0] = n0; sCnt[wid][1] = n1; sCnt[wid][2] = n2; sCnt[wid][3] = n3; }
+    __syncthreads();
+    int t0 = 0, t1 = 0, t2 = 0, t3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0;
+    for (int w = 0; w < kTreeWarps; ++w) {
+        if (w == wid) { p0 = t0; p1 = t1; p2 = t2; p3 = t3; }
+        t0 += sCnt[w][0]; t1 += sCnt[w][1]; t2 += sCnt[w][2]; t3 += sCnt[w][3];
+    }
+    int o0 = outBase + p0, o1 = outBase + t0 + p1, o2 = outBase + t0 + t1 + p2, o3 = outBase + t0 + t1 + t2 + p3;
+    for (int base = cb; base < ce; base += 32) {
+        const int i = base + lane;
+        int q = -1; uint64_t k = 0;
+        if (i < ce) { k = src[beg + i]; q = cls(k); }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, q == 0), b1 = __ballot_sync(0xffffffffu, q == 1);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, q == 2), b3 = __ballot_sync(0xffffffffu, q == 3);
+        if (q == 0) dst[o0 + __popc(b0 & lt)] = k;
+        else if (q == 1) dst[o1 + __popc(b1 & lt)] = k;
+        else if (q == 2) dst[o2 + __popc(b2 & lt)] = k;
+        else if (q == 3) dst[o3 + __popc(b3 & lt)] = k;
+        o0 += __popc(b0); o1 += __popc(b1); o2 += __popc(b2); o3 += __popc(b3);
+    }
+    __syncthreads();
+    return make_uint4(t0, t1, t2, t3);
+}
+
+__device__ __forceinline__ int nonempty4(uint4 c) { return (c.x > 0) + (c.y > 0) + (c.z > 0) + (c.w > 0); }
+__device__ __forceinline__ int splittable4(uint4 c) { return (c.x > 1) + (c.y > 1) + (c.z > 1) + (c.w > 1); }
+
+// Split points of DivideNode: halfX = ceil(float(UR.x-UL.x)/2) (:482-483)
+__device__ __forceinline__ QuadClass split_of(ushort4 r) {
+    QuadClass q;
+    q.mx = r.x + (((int)r.z - (int)r.x + 1) >> 1);
+    q.my = r.y + (((int)r.w - (int)r.y + 1) >> 1);
+    return q;
+}
+
+// Partition every node listed in proc[0..T) (list positions of pool `cur`) into its four children.
+// Big nodes by the whole CTA, the rest one warp each.  warpBegin lets warp 0 be busy elsewhere (sorting).
+__device__ void split_nodes(TreeSmem& S, int cur, int T, uint64_t* const (&buf)[2], int (*sCnt)[4], int firstWarp) {
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (wid >= firstWarp) {
+        for (int t = wid - firstWarp; t < T; t += kTreeWarps - firstWarp) {
+            const int node = S.proc[t];
+            const int cnt = (int)S.cnt[cur][node];
+            if (cnt >= kCtaPartitionMin) continue;
+            const uint32_t bf = S.beg[cur][node];
+            const int beg = (int)(bf & 0x7fffffffu), flag = (int)(bf >> 31);
+            const uint4 c = warp_partition4(buf[flag], buf[flag ^ 1], beg, cnt, beg, split_of(S.rect[cur][node]));
+            if (lane == 0) S.cc[node] = c;
+        }
+    }
+}
+__device__ void split_big_nodes(TreeSmem& S, int cur, int T, uint64_t* const (&buf)[2], int (*sCnt)[4]) {
+    for (int t = 0; t < T; ++t) {
+        const int node = S.proc[t];
+        const int cnt = (int)S.cnt[cur][node];
+        if (cnt < kCtaPartitionMin) continue;        // uniform across the CTA
+        const uint32_t bf = S.beg[cur][node];
+        const int beg = (int)(bf & 0x7fffffffu), flag = (int)(bf >> 31);
+        const uint4 c = cta_partition4(buf[flag], buf[flag ^ 1], beg, cnt, beg, split_of(S.rect[cur][node]), sCnt);
+        if (threadIdx.x == 0) S.cc[node] = c;
+    }
+}
+
+// Rebuild the list after the nodes proc[0..T) (in processing order) were split.  Returns new size; *mOut = number
+// of splittable children (the new pending list, in the reference's push_back order).
+__device__ int apply_splits(TreeSmem& S, int cur, int listSize, int T, int* sWarp, int* mOut) {
+    const int tid = threadIdx.x;
+    const int nxt = cur ^ 1;
+    for (int i = tid; i < listSize; i += kTreeThreads) S.dv[i] = 0;
+    __syncthreads();
+    for (int t = tid; t < T; t += kTreeThreads) {
+        const int node = S.proc[t];
+        S.dv[node] = 1;
+        const uint4 c = S.cc[node];
+        S.scanA[t] = nonempty4(c);
+        S.scanB[t] = splittable4(c);
+    }
+    __syncthreads();
+    const int neTot = block_exscan(S.scanA, T, sWarp);
+    const int exTot = block_exscan(S.scanB, T, sWarp);
+    for (int t = tid; t < T; t += kTreeThreads) {
+        const int node = S.proc[t];
+        const ushort4 r = S.rect[cur][node];
+        const QuadClass sp = split_of(r);
+        const uint32_t bf = S.beg[cur][node];
+        uint32_t b = bf & 0x7fffffffu;
+        const uint32_t childFlag = ((bf >> 31) ^ 1u) << 31;
+        const uint4 c = S.cc[node];
+        const uint32_t cn[4] = {c.x, c.y, c.z, c.w};
+        const ushort4 cr[4] = {make_ushort4(r.x, r.y, sp.mx, sp.my), make_ushort4(sp.mx, r.y, r.z, sp.my),
+                               make_ushort4(r.x, sp.my, sp.mx, r.w), make_ushort4(sp.mx, sp.my, r.z, r.w)};
+        int rl = 0, el = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if (cn[q] > 0) {
+                const int idx = neTot - 1 - (S.scanA[t] + rl);
+                S.rect[nxt][idx] = cr[q];
+                S.beg[nxt][idx] = b | childFlag;
+                S.cnt[nxt][idx] = cn[q];
+                if (cn[q] > 1) {
+                    ise::Elem e;
+                    e.key = ((uint64_t)cn[q] << 32) | (uint32_t)cr[q].x;
+                    e.id = idx; e.pad = 0;
+                    S.pend[S.scanB[t] + el] = e;
+                    ++el;
+                }
+                ++rl;
+            }
+            b += cn[q];
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < listSize; i += kTreeThreads) S.scanA[i] = S.dv[i] ? 0 : 1;
+    __syncthreads();
+    block_exscan(S.scanA, listSize, sWarp);
+    for (int i = tid; i < listSize; i += kTreeThreads) {
+        if (S.dv[i]) continue;
+        const int idx = neTot + S.scanA[i];
+        S.rect[nxt][idx] = S.rect[cur][i];
+        S.beg[nxt][idx] = S.beg[cur][i];
+        S.cnt[nxt][idx] = S.cnt[cur][i];
+    }
+    __syncthreads();
+    *mOut = exTot;
+    return neTot + listSize - T;
+}
+
+// The whole DistributeOctTree for one level.  Keys are in buf[0][0..n) in the reference's vToDistributeKeys order.
+// Writes the kept keys (one per final node, list order) to out[0..*outCount).
+__device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIni, float hX, int treeH,
+                                TreeSmem& S, uint64_t* out, int* outCount) {
+    __shared__ int sWarp[33];
+    __shared__ int sCnt[kTreeWarps + 1][4];
+    __shared__ int sT;
+    const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
+    if (n == 0) { if (tid == 0) *outCount = 0; return; }
+
+    // roots: stable grouping of the keys by (int)(x / hX) into buf[1]
+    int outBase = 0;
+    for (int gb = 0; gb < nIni; gb += 4) {
+        RootClass rc; rc.hX = hX; rc.base = gb;
+        const uint4 c = cta_partition4(buf[0], buf[1], 0, n, outBase, rc, sCnt);
+        if (tid == 0) { S.scanB[gb] = c.x; S.scanB[gb + 1] = c.y; S.scanB[gb + 2] = c.z; S.scanB[gb + 3] = c.w; }
+        outBase += c.x + c.y + c.z + c.w;
+    }
+    __syncthreads();
+    int cur = 0;
+    if (tid == 0) {
+        int sz = 0, b = 0;
+        for (int i = 0; i < nIni; ++i) {
+            const int c = S.scanB[i];
+            if (c > 0) {
+                S.rect[0][sz] = make_ushort4((unsigned short)(int)__fmul_rn(hX, (float)i), 0,
+                                             (unsigned short)(int)__fmul_rn(hX, (float)(i + 1)), (unsigned short)treeH);
+                S.beg[0][sz] = (uint32_t)b | 0x80000000u;
+                S.cnt[0][sz] = c;
+                ++sz;
+            }
+            b += c;
+        }
+        sT = sz;
+    }
+    __syncthreads();
+    int listSize = sT;
+
+    bool finish = false;
+    while (!finish) {
+        const int prevSize = listSize;
+        // all splittable nodes in list order
+        for (int i = tid; i < listSize; i += kTreeThreads) S.scanA[i] = S.cnt[cur][i] > 1 ? 1 : 0;
+        __syncthreads();
+        const int T = block_exscan(S.scanA, listSize, sWarp);
+        for (int i = tid; i < listSize; i += kTreeThreads)
+            if (S.cnt[cur][i] > 1) S.proc[S.scanA[i]] = (uint16_t)i;
+        __syncthreads();
+        split_big_nodes(S, cur, T, buf, sCnt);
+        split_nodes(S, cur, T, buf, sCnt, 0);
+        __syncthreads();
+        int m;
+        listSize = apply_splits(S, cur, listSize, T, sWarp, &m);
+        cur ^= 1;
+        if (listSize >= N || listSize == prevSize) {
+            finish = true;
+        } else if (listSize + 3 * m > N) {
+            while (!finish) {
+                const int prev2 = listSize;
+                for (int e = tid; e < m; e += kTreeThreads) S.proc[e] = (uint16_t)S.pend[e].id;
+                __syncthreads();
+                // std::sort emulation by one thread while the other warps pre-split every pending node
+                if (tid == 0) ise::sort(S.pend, m);
+                split_nodes(S, cur, m, buf, sCnt, 1);
+                __syncthreads();
+                split_big_nodes(S, cur, m, buf, sCnt);
+                // processing order = sorted order from the back; stop as soon as the list reaches N
+                for (int t = tid; t < m; t += kTreeThreads) {
+                    const int node = S.pend[m - 1 - t].id;
+                    S.proc[t] = (uint16_t)node;
+                    S.scanA[t] = nonempty4(S.cc[node]) - 1;
+                }
+                if (tid == 0) sT = m;
+                __syncthreads();
+                block_exscan(S.scanA, m, sWarp);
+                for (int t = tid; t < m; t += kTreeThreads) {
+                    const int v = nonempty4(S.cc[S.proc[t]]) - 1;
+                    if (listSize + S.scanA[t] + v >= N) atomicMin(&sT, t + 1);
+                }
+                __syncthreads();
+                const int T2 = sT;
+                __syncthreads();
+                listSize = apply_splits(S, cur, listSize, T2, sWarp, &m);
+                cur ^= 1;
+                if (listSize >= N || listSize == prev2) finish = true;
+            }
+        }
+    }
+
+    // keep the best response of every node; first maximum wins (:757-776)
+    for (int i = wid; i < listSize; i += kTreeWarps) {
+        const uint32_t bf = S.beg[cur][i];
+        const uint64_t* seg = buf[bf >> 31] + (bf & 0x7fffffffu);
+        const int cnt = (int)S.cnt[cur][i];
+        // order by (score desc, position asc): maximise score<<32 | ~pos
+        uint64_t best = 0; uint64_t bestKey = 0;      // every real candidate has ord > 0
+        for (int k = lane; k < cnt; k += 32) {
+            const uint64_t key = seg[k];
+            const uint64_t ord = ((key >> 32) << 32) | (uint32_t)(0x7fffffff - k);
+            if (ord > best) { best = ord; bestKey = key; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint64_t ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const uint64_t ok = __shfl_xor_sync(0xffffffffu, bestKey, o);
+            if (ob > best) { best = ob; bestKey = ok; }
+        }
+        if (lane == 0) out[i] = bestKey;
+    }
+    if (tid == 0) *outCount = listSize;
+}
+
+}  // namespace orbx
