@@ -1,0 +1,302 @@
+#!/usr/bin/env python3
+"""bench.py — ORB front-end throughput on B200 (BASELINE.json metric: ORB extract frames/s at 752x480 / 1000 kp,
+plus Hamming matches/s).
+
+One "step" = one pass of the hot path over one batch of synthetic EuRoC-shaped frames (config[1] of BASELINE.json:
+per-frame ORB extraction + SearchByProjection matching against the previous frame).
+  value  : frames/s with the input frames already resident in HBM (device pipeline only)
+  e2e    : frames/s through the C-ABI call with HOST buffers (pinned H2D of the frames + D2H of keypoints/descriptors
+           inside the timed region)
+  roofline / cpu_baseline / clocks / gpu_launches : see DESIGN.md "Measurement".
+N > 1 (torchrun): one agent stream per GPU, no data-path collective -> weak scaling.
+`--impl reference` times the CPU restatement of the reference path (oracle/, all host threads) on the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, NFEAT, NLEVELS, SCALE, INI_TH, MIN_TH = 752, 480, 1000, 8, 1.2, 20, 7
+ALG_BYTES_PER_FRAME = 1_933_774          # input + 2 x derived levels + 60 B per keypoint
+METRIC = "ORB extract frames/s (752x480, 1000 kp) + Hamming matches/s, 1-8 B200"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_frames(seed, n):
+    from mam3slam_b200 import synth
+    return synth.stream(W, H, seed, n)
+
+
+def cpu_reference_run(frames, iters, threads):
+    """Times the CPU restatement (oracle/) of ORBextractor::operator() on `iters` frames split over `threads`."""
+    import oracle
+    exs = [oracle.Extractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH) for _ in range(threads)]
+    per = [iters // threads + (1 if t < iters % threads else 0) for t in range(threads)]
+    for ex in exs:
+        ex.timed(frames[:1], 1)                     # warm the allocator / caches
+    res = [None] * threads
+
+    def work(t):
+        res[t] = exs[t].timed(frames, per[t]) if per[t] else (0.0, 0)
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    t0 = time.perf_counter()
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    wall = time.perf_counter() - t0
+    return wall, sum(per)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    frames = make_frames(0, 8)
+    per_step = max(threads * 2, 8)
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_run(frames, threads, threads)
+    tot_t, tot_f = 0.0, 0
+    for _ in range(args.steps):
+        t, f = cpu_reference_run(frames, per_step, threads)
+        tot_t += t
+        tot_f += f
+    fps = tot_f / tot_t
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "EuRoC-shaped 752x480 mono stream, 1000 kp, 8 levels @1.2, FAST 20/7: "
+                                   "ORBextractor::operator() per frame", "frames_per_step": per_step},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
+                             "sample": f"{per_step} frames per step x {args.steps} steps, {threads} threads, "
+                                       "oracle/cpp restatement (reference needs OpenCV C++/Eigen: not buildable here)"},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from mam3slam_b200 import ORBextractor
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    B = args.batch
+    nsets = args.sets                      # distinct input batches: nsets*B*361 KB > L2 (126 MB)
+    frames = make_frames(rank, min(64, B))                 # agent `rank`'s stream
+    reps = (B * nsets + len(frames) - 1) // len(frames)
+    host = np.concatenate([frames] * reps)[:B * nsets]
+    # make the batches distinct so no step re-reads cached input: roll each copy by a few pixels
+    for i in range(len(frames), len(host)):
+        host[i] = np.roll(host[i], (i // len(frames)) * 3, axis=1)
+    dev = torch.from_numpy(host).cuda()
+    img_bytes = W * H
+    ex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
+    tstream = torch.cuda.Stream()          # a real (non-NULL) stream: CUDA events below are recorded on it
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+
+    def step_device(i):
+        s = i % nsets
+        ex.extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident input ----
+    for i in range(args.warmup):
+        step_device(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ex.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step_device(args.warmup + i)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ex.launch_count() - l0
+    nkp = sum(ex.fetch(f)[1].shape[0] for f in range(min(B, 4))) / min(B, 4)
+
+    # ---- per-kernel durations (CUDA events on the launching stream, same work as the timed region) ----
+    ex.set_stage_timing(True)
+    acc = {}
+    nrep = min(args.steps, 5)
+    for i in range(nrep):
+        step_device(i)
+        torch.cuda.synchronize()
+        ex.synchronize()
+        for k, v in ex.stage_times().items():
+            acc[k] = acc.get(k, 0.0) + v / nrep
+    ex.set_stage_timing(False)
+
+    # ---- e2e: host buffers through the C-ABI call ----
+    host_batches = [host[s * B:(s + 1) * B] for s in range(nsets)]
+    for i in range(min(args.warmup, 3)):
+        ex.extract_batch(host_batches[i % nsets])
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ex.extract_batch(host_batches[i % nsets])
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+
+    tms = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = tms.tolist()
+    total_frames = B * args.steps * world
+    if rank == 0:
+        pk, pk_kind = peaks()
+        fps = total_frames / (ms * 1e-3)
+        stage_bytes = stage_algorithmic_bytes(nkp)
+        dom = max((k for k in acc if k != "total"), key=lambda k: acc[k])
+        ach = stage_bytes[dom] * B / (acc[dom] * 1e-3) / 1e9
+        cap = ex._cap()
+        line = {
+            "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "EuRoC-shaped 752x480 mono stream per GPU (one agent per GPU), 1000 kp, 8 levels "
+                                   "@1.2, FAST 20/7: ORBextractor::operator() per frame",
+                       "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
+                       "l2_policy": f"{nsets} distinct input batches rotated ({nsets * B * img_bytes / 1e6:.0f} MB > "
+                                    "126 MB L2); all intermediates rewritten every step"},
+            "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": int(B * 768 * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8))},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                         "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                         "stage_ms_per_step": acc,
+                         "pipeline_alg_gbs": ALG_BYTES_PER_FRAME * fps / 1e9 / world,
+                         "pipeline_frac": ALG_BYTES_PER_FRAME * fps / 1e9 / world / pk["hbm_gbs"]},
+        }
+        if world == 1 and not args.no_cpu:
+            cf = make_frames(0, 8)
+            wall, n = cpu_reference_run(cf, args.cpu_frames, 1)
+            line["cpu_baseline"] = {"value": n / wall, "unit": "frames/s", "cores": 1, "kind": "port",
+                                    "sample": f"{n} frames of the same stream, 1 thread, oracle/cpp restatement"}
+        print(json.dumps(line))
+    ex.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def stage_algorithmic_bytes(nkp):
+    """Algorithmic bytes per FRAME of each kernel (DESIGN.md 'Kernels'): pixels of the 8 EuRoC levels etc."""
+    lv = [752 * 480, 627 * 400, 522 * 333, 435 * 278, 363 * 231, 302 * 193, 252 * 161, 210 * 134]
+    allpx, derived = sum(lv), sum(lv[1:])
+    ncand = 26000                               # typical FAST candidates per synthetic frame (4 B each)
+    return {
+        "pyramid": sum(lv[:-1]) + derived,      # read every source level once, write every derived level once
+        "fast": allpx + 4 * ncand,              # read every level once, write packed candidates
+        "octree": 4 * ncand + 8 * ncand + 8 * nkp,   # read candidates, write 64-bit keys once, write kept keys
+        "blur": 2 * allpx,                      # read + write every level
+        "finalize": 8 * nkp + 28 * nkp + 16 * nkp,
+        "orient_brief": nkp * (749 + 512 + 32 + 4),  # patch reads + 512 blurred samples + descriptor
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="frames in flight per GPU per step")
+    ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
+    ap.add_argument("--cpu-frames", type=int, default=300, help="frames timed for cpu_baseline")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
