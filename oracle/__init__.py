@@ -57,6 +57,8 @@ def lib():
         L.orc_distribute.restype = C.c_int
         L.orc_distribute.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      C.c_void_p, C.c_int]
+        L.orc_ic_angles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_brief.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -113,6 +115,24 @@ def distribute(keys, minX, maxX, minY, maxY, N):
     out = np.empty((max(4 * N + 64, 64), 3), np.int32)
     n = lib().orc_distribute(0, _p(keys), len(keys), minX, maxX, minY, maxY, N, _p(out), len(out))
     return out[:n].copy()
+
+
+def ic_angles(img, xy):
+    """IC_Angle (degrees) at integer positions xy[n,2] of a plain image."""
+    img = np.ascontiguousarray(img, np.uint8)
+    xy = np.ascontiguousarray(xy, np.int32).reshape(-1, 2)
+    out = np.empty(len(xy), np.float32)
+    lib().orc_ic_angles(_p(img), img.shape[1], img.shape[0], img.shape[1], _p(xy), len(xy), _p(out))
+    return out
+
+
+def brief(blurred, kps):
+    """256-bit rotated-BRIEF rows for kps[n,3] = (x, y, angle_deg) on an already blurred plain image."""
+    blurred = np.ascontiguousarray(blurred, np.uint8)
+    kps = np.ascontiguousarray(kps, np.float32).reshape(-1, 3)
+    out = np.empty((len(kps), 32), np.uint8)
+    lib().orc_brief(_p(blurred), blurred.shape[1], blurred.shape[0], blurred.shape[1], _p(kps), len(kps), _p(out))
+    return out
 
 
 # ---- extractor ------------------------------------------------------------------------------------------------

@@ -104,6 +104,21 @@ int orc_level_points(void* h, int level, int which, float* out, int cap) {
     }
     return (int)v.size();
 }
+// IC_Angle (src/ORBextractor.cc:76-103) at n integer positions of a plain image (positions must be >= 15 px inside)
+void orc_ic_angles(const uint8_t* img, int w, int h, int stride, const int* xy, int n, float* out) {
+    Extractor e(1000, 1.2f, 8, 20, 7);
+    for (int i = 0; i < n; ++i) out[i] = e.icAngleAt(img + (size_t)xy[2 * i + 1] * stride + xy[2 * i], stride);
+    (void)w; (void)h;
+}
+// computeOrbDescriptor (src/ORBextractor.cc:106-146) on an already blurred plain image; kps n x 3 floats (x,y,angle)
+void orc_brief(const uint8_t* blurred, int w, int h, int stride, const float* kps, int n, uint8_t* out) {
+    Extractor e(1000, 1.2f, 8, 20, 7);
+    for (int i = 0; i < n; ++i) {
+        KeyPoint k{kps[3 * i], kps[3 * i + 1], 31.f, kps[3 * i + 2], 0.f, 0};
+        e.orbDescriptor(k, blurred, stride, out + 32 * (size_t)i);
+    }
+    (void)w; (void)h;
+}
 long orc_sort_tie_count(void* h) { return ((Extractor*)h)->sortTieCount; }
 
 // standalone quadtree: keys n x 3 ints (x, y, response) relative to the min border; returns kept count, out n x 3

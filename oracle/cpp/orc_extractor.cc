@@ -175,9 +175,10 @@ std::vector<KeyPoint> Extractor::distributeOctTree(const std::vector<KeyPoint>& 
 
 // ---- IC_Angle: src/ORBextractor.cc:76-103 --------------------------------------------------------------------
 float Extractor::icAngle(const Level& L, float px, float py) const {
+    return icAngleAt(L.roi() + (size_t)cv_round(py) * L.pstride + cv_round(px), L.pstride);
+}
+float Extractor::icAngleAt(const uint8_t* c, int step) const {
     int m01 = 0, m10 = 0;
-    const int step = L.pstride;
-    const uint8_t* c = L.roi() + (size_t)cv_round(py) * step + cv_round(px);
     for (int u = -kHalfPatch; u <= kHalfPatch; ++u) m10 += u * c[u];
     for (int v = 1; v <= kHalfPatch; ++v) {
         int vs = 0, d = umax[v];

@@ -49,6 +49,7 @@ public:
     void computeKeyPointsOctTree();
     std::vector<KeyPoint> distributeOctTree(const std::vector<KeyPoint>& keys, int minX, int maxX, int minY, int maxY, int N);
     float icAngle(const Level& L, float px, float py) const;
+    float icAngleAt(const uint8_t* center, int step) const;
     void orbDescriptor(const KeyPoint& kp, const uint8_t* img, int step, uint8_t* out) const;
 };
 
