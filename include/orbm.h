@@ -1,0 +1,156 @@
+/* orbm.h — C ABI of the B200-native ORB Hamming matcher (libmam3slam_b200.so).
+ *
+ * Drop-in boundary for MAM3SLAM's ORBmatcher (include/ORBmatcher.h:36-103, src/ORBmatcher.cc).  The reference has no
+ * FFI layer: the boundary is the C++ class, whose methods take Frame / KeyFrame / MapPoint pointer graphs.  The C++
+ * adapter (mam3slam_b200/cpp/ORBmatcher.h) flattens those graphs into the plain arrays below — every
+ * MapPoint-dependent predicate (isBad, Observations()>0, mbTrackInView, in-image projection ...) becomes a per-element
+ * flag or number computed on the host exactly where the reference computes it — and calls these entry points; all
+ * Hamming work (candidate gather through the 64x48 frame grid or the BoW node lists, DescriptorDistance, best /
+ * second-best selection in the reference's scan order, TH_LOW / TH_HIGH / NN-ratio acceptance, once-only slot
+ * occupancy, rotation-histogram filtering) runs in CUDA kernels.  Results are bit-exact with the reference's loops.
+ *
+ * Conventions: opaque handles, int status (0 = ORBM_OK, negative = error), no C++/OpenCV types, caller-owned HOST
+ * buffers unless stated, one CUDA stream per handle, one thread per handle at a time.  No CPU fallback.
+ * Keypoints use cv::KeyPoint's 28-byte layout (orbx_keypoint) so std::vector<cv::KeyPoint>::data() can be passed as is.
+ */
+#ifndef ORBM_H_
+#define ORBM_H_
+#include <stdint.h>
+#include <stddef.h>
+#include "orbx.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBM_OK 0
+#define ORBM_ERR_INVALID (-1)
+#define ORBM_ERR_CUDA (-2)
+#define ORBM_ERR_CAPACITY (-3)
+#define ORBM_ERR_UNSUPPORTED (-4)
+#define ORBM_ERR_NO_DEVICE (-5)
+
+#define ORBM_TH_HIGH 100      /* ORBmatcher::TH_HIGH  (src/ORBmatcher.cc:35) */
+#define ORBM_TH_LOW 50        /* ORBmatcher::TH_LOW   (:36) */
+#define ORBM_HISTO_LENGTH 30  /* ORBmatcher::HISTO_LENGTH (:37) */
+
+typedef struct orbm_matcher* orbm_handle;
+typedef struct orbm_frame_s* orbm_frame;
+
+const char* orbm_strerror(int status);
+const char* orbm_last_error(orbm_handle h);
+int orbm_create(int device, orbm_handle* out);
+void orbm_destroy(orbm_handle h);
+long long orbm_launch_count(orbm_handle h);
+void* orbm_stream(orbm_handle h);
+
+/* replaces ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:2058-2074): host-side, same SWAR arithmetic */
+int orbm_distance(const uint8_t* a, const uint8_t* b);
+
+/* ---- frames: device mirror of what the searches read from a Frame / KeyFrame ----
+ * n undistorted keypoints (mvKeysUn), n x 32 descriptor bytes (mDescriptors), image bounds (mnMinX.. mnMaxY).  The 64x48
+ * grid of Frame::AssignFeaturesToGrid (src/Frame.cc:385-416; PosInGrid :725-735) is built on the device.
+ * on_device != 0: kps / desc are DEVICE pointers (e.g. from orbx_results_device), nothing crosses PCIe. */
+typedef struct orbm_frame_view {
+    int n;
+    const orbx_keypoint* kps;
+    const uint8_t* desc;
+    float min_x, min_y, max_x, max_y;
+    int on_device;
+} orbm_frame_view;
+int orbm_frame_create(orbm_handle h, const orbm_frame_view* view, orbm_frame* out);
+int orbm_frame_update(orbm_handle h, orbm_frame f, const orbm_frame_view* view);   /* reuse the slot for a new frame */
+void orbm_frame_destroy(orbm_handle h, orbm_frame f);
+/* the grid as CSR (cell = ix*48+iy, off has 64*48+1 ints, idx has n ints): parity tap for AssignFeaturesToGrid */
+int orbm_frame_grid(orbm_handle h, orbm_frame f, int* off, int* idx);
+/* replaces Frame::GetFeaturesInArea (src/Frame.cc:657-723) and KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:704-748,
+ * min_level = max_level = -1): indices in the reference's order.  Parity tap; the searches gather on the device. */
+int orbm_features_in_area(orbm_handle h, orbm_frame f, float x, float y, float r, int min_level, int max_level,
+                          int* out, int cap, int* n_out);
+
+/* ---- projection-guided searches (queries = map points already projected by the caller) ----
+ * Common arguments: nq queries; valid[q] = the query survives the reference's pre-checks; qdesc = nq x 32 bytes
+ * (MapPoint::GetDescriptor); scale_factors = mvScaleFactors (nlevels floats); kp_match[n] (out) = index of the query
+ * assigned to keypoint i or -1 (the reference writes F.mvpMapPoints[i] = pMP); *nmatches = the reference's return
+ * value.  occupied[n] (in/out) = slot already holds a map point that blocks matching; accepted matches occupy their
+ * slot for later queries (sequential semantics of the reference loop). */
+
+/* replaces SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints) (src/ORBmatcher.cc:43-213),
+ * mono branch.  level = mnTrackScaleLevel, view_cos = mTrackViewCos (RadiusByViewingCos :215-221). */
+int orbm_search_local_map(orbm_handle h, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels,
+                          int nq, const uint8_t* valid, const float* proj_x, const float* proj_y, const int* level,
+                          const float* view_cos, const uint8_t* qdesc, float th, float nnratio, int* kp_match,
+                          int* nmatches);
+/* replaces SearchByProjection(Frame& Cur, const Frame& Last, th, bMono=true) (:1676-1887) and
+ * SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:1889-2010): octave = last octave / predicted
+ * level, qangle = angle of the source keypoint, th_dist = TH_HIGH or ORBdist. */
+int orbm_search_frame(orbm_handle h, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
+                      const uint8_t* valid, const float* u, const float* v, const int* octave, const float* qangle,
+                      const uint8_t* qdesc, float th, int th_dist, int check_orientation, int* kp_match,
+                      int* nmatches);
+/* replaces SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) (:427-532) and its pointKFs
+ * overload (:534-646): matched[n] in/out = vpMatched[i] != NULL. */
+int orbm_search_sim3(orbm_handle h, orbm_frame kf, uint8_t* matched, const float* scale_factors, int nlevels, int nq,
+                     const uint8_t* valid, const float* u, const float* v, const int* level, const uint8_t* qdesc,
+                     int th, float ratio_hamming, int* kp_match, int* nmatches);
+/* replaces SearchForInitialization (:648-763): prev_matched = n1 x 2 floats in/out (vbPrevMatched), matches12[n1]. */
+int orbm_search_initialization(orbm_handle h, orbm_frame f1, orbm_frame f2, float* prev_matched, int window_size,
+                               float nnratio, int check_orientation, int* matches12, int* nmatches);
+/* candidate part of Fuse(KeyFrame*, vector<MapPoint*>, th) (:1148-1338, chi2_gate = 1, needs inv_sigma2 =
+ * mvInvLevelSigma2) and Fuse(KeyFrame*, Sim3, points, th, replace) (:1340-1455, chi2_gate = 0): best keypoint and
+ * distance per map point; the map mutations (Replace / AddObservation) stay on the host, applied in order. */
+int orbm_fuse_candidates(orbm_handle h, orbm_frame kf, const float* scale_factors, const float* inv_sigma2, int nlevels,
+                         int nq, const uint8_t* valid, const float* u, const float* v, const int* level,
+                         const uint8_t* qdesc, float th, int chi2_gate, int* best_idx, int* best_dist);
+
+/* ---- BoW-guided searches: DBoW2::FeatureVector (std::map<NodeId, vector<unsigned>>) flattened to CSR ---- */
+typedef struct orbm_featvec {
+    int n_nodes;
+    const int* node;     /* ascending node ids */
+    const int* off;      /* n_nodes + 1 */
+    const int* idx;      /* feature indices, insertion order */
+} orbm_featvec;
+/* replaces SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (:223-425), mono.  elig1[i] = KF keypoint i holds a good
+ * map point.  match_f[nF] = KF keypoint matched to frame keypoint j, or -1. */
+int orbm_search_bow_kf_frame(orbm_handle h, orbm_frame kf, const orbm_featvec* fv_kf, const uint8_t* elig1,
+                             orbm_frame f, const orbm_featvec* fv_f, float nnratio, int check_orientation,
+                             int* match_f, int* nmatches);
+/* replaces SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (:765-905): matches12[n1] = keypoint of KF2 or -1 */
+int orbm_search_bow_kf_kf(orbm_handle h, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* elig1, orbm_frame kf2,
+                          const orbm_featvec* fv2, const uint8_t* elig2, float nnratio, int check_orientation,
+                          int* matches12, int* nmatches);
+/* replaces SearchForTriangulation (:907-1146), mono + Pinhole: free1/free2 = keypoint has no map point; ep = epipole
+ * of KF1 in KF2 (2 floats); F12 = 9 floats row-major, computed by the caller as Pinhole::epipolarConstrain does
+ * (src/CameraModels/Pinhole.cpp:107-112); sigma2 = KF2's mvLevelSigma2; coarse = bCoarse. */
+int orbm_search_triangulation(orbm_handle h, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* free1,
+                              orbm_frame kf2, const orbm_featvec* fv2, const uint8_t* free2, const float* ep,
+                              const float* scale_factors2, const float* F12, const float* sigma2, int nlevels,
+                              int coarse, int check_orientation, int* matches12, int* nmatches);
+
+/* ---- brute-force k-NN Hamming search (BASELINE config 5: cross-map search at scale) ----
+ * For each of nq queries the k smallest distances over ndb rows, ties to the lowest row (a strict '<' scan).
+ * The database is uploaded once and stays in HBM; row_offset is added to every returned index (global row ids of a
+ * shard).  dist: nq x k uint16, idx: nq x k int32 (HOST buffers). */
+typedef struct orbm_db_s* orbm_db;
+int orbm_db_create(orbm_handle h, const uint8_t* rows, long long ndb, int rows_on_device, long long row_offset,
+                   orbm_db* out);
+void orbm_db_destroy(orbm_handle h, orbm_db db);
+int orbm_knn(orbm_handle h, orbm_db db, const uint8_t* q, int nq, int k, uint16_t* dist, int32_t* idx);
+/* device-resident variant: d_q, d_dist, d_idx are device pointers; asynchronous on `stream` (NULL = handle stream) */
+int orbm_knn_device(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx,
+                    void* stream);
+/* merge of per-shard top-k lists (nshards x nq x k, e.g. after an all-gather): same tie rule on global row ids */
+int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq, int k, uint16_t* out_dist,
+                   int32_t* out_idx);
+
+/* replaces the selection in MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:366-396) for a batch of map
+ * points: descriptors of point p are rows [off[p], off[p+1]); best[p] = row (relative) with the least median distance */
+int orbm_distinctive_descriptors(orbm_handle h, const uint8_t* desc, const int* off, int npoints, int* best);
+
+/* Hamming evaluations performed by the last search call (for matches/s reporting) */
+long long orbm_last_evaluations(orbm_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBM_H_ */

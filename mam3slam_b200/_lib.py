@@ -59,10 +59,71 @@ def lib():
     L.orbx_stream.argtypes = [vp]
     L.orbx_set_stage_timing.argtypes = [vp, i32]
     L.orbx_stage_times.argtypes = [vp, vp]
-    for name in dir(L):
-        pass
+    _bind_matcher(L)
     _LIB = L
     return L
+
+
+class OrbmFrameView(C.Structure):
+    _fields_ = [("n", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p), ("min_x", C.c_float), ("min_y", C.c_float),
+                ("max_x", C.c_float), ("max_y", C.c_float), ("on_device", C.c_int)]
+
+
+class OrbmFeatVec(C.Structure):
+    _fields_ = [("n_nodes", C.c_int), ("node", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p)]
+
+
+def _bind_matcher(L):
+    vp, i32, f32, ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
+    ip = C.POINTER(C.c_int)
+    fvp, fwp = C.POINTER(OrbmFeatVec), C.POINTER(OrbmFrameView)
+    L.orbm_strerror.restype = C.c_char_p
+    L.orbm_strerror.argtypes = [i32]
+    L.orbm_last_error.restype = C.c_char_p
+    L.orbm_last_error.argtypes = [vp]
+    L.orbm_create.argtypes = [i32, C.POINTER(vp)]
+    L.orbm_destroy.argtypes = [vp]
+    L.orbm_destroy.restype = None
+    L.orbm_launch_count.restype = ll
+    L.orbm_launch_count.argtypes = [vp]
+    L.orbm_stream.restype = vp
+    L.orbm_stream.argtypes = [vp]
+    L.orbm_last_evaluations.restype = ll
+    L.orbm_last_evaluations.argtypes = [vp]
+    L.orbm_distance.argtypes = [vp, vp]
+    L.orbm_frame_create.argtypes = [vp, fwp, C.POINTER(vp)]
+    L.orbm_frame_update.argtypes = [vp, vp, fwp]
+    L.orbm_frame_destroy.argtypes = [vp, vp]
+    L.orbm_frame_destroy.restype = None
+    L.orbm_frame_grid.argtypes = [vp, vp, vp, vp]
+    L.orbm_features_in_area.argtypes = [vp, vp, f32, f32, f32, i32, i32, vp, i32, ip]
+    L.orbm_search_local_map.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, f32, vp, ip]
+    L.orbm_search_frame.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, i32, i32, vp, ip]
+    L.orbm_search_sim3.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, i32, f32, vp, ip]
+    L.orbm_search_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, vp, ip]
+    L.orbm_fuse_candidates.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, f32, i32, vp, vp]
+    L.orbm_search_bow_kf_frame.argtypes = [vp, vp, fvp, vp, vp, fvp, f32, i32, vp, ip]
+    L.orbm_search_bow_kf_kf.argtypes = [vp, vp, fvp, vp, vp, fvp, vp, f32, i32, vp, ip]
+    L.orbm_search_triangulation.argtypes = [vp, vp, fvp, vp, vp, fvp, vp, vp, vp, vp, vp, i32, i32, i32, vp, ip]
+    L.orbm_db_create.argtypes = [vp, vp, ll, i32, ll, C.POINTER(vp)]
+    L.orbm_db_destroy.argtypes = [vp, vp]
+    L.orbm_db_destroy.restype = None
+    L.orbm_knn.argtypes = [vp, vp, vp, i32, i32, vp, vp]
+    L.orbm_knn_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
+    L.orbm_knn_merge.argtypes = [vp, vp, i32, i32, i32, vp, vp]
+    L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp]
+
+
+def check_m(status, handle=None, what=""):
+    if status == 0:
+        return
+    L = lib()
+    msg = L.orbm_strerror(status).decode()
+    if handle:
+        detail = L.orbm_last_error(handle).decode()
+        if detail:
+            msg += ": " + detail
+    raise NativeError(f"{what} failed ({status}): {msg}")
 
 
 def check(status, handle=None, what=""):

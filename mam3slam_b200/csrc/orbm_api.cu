@@ -1,0 +1,797 @@
+// C ABI of the B200-native ORB matcher (include/orbm.h): handle / frame management, query marshalling, launches.
+// Host-side logic mirrors what each ORBmatcher method does before and after its Hamming loop (src/ORBmatcher.cc).
+#include "orbm_kernels.cuh"
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace orbm;
+
+struct orbm_frame_s {
+    int n = 0, cap = 0;
+    bool ownsInput = false;            // kpsDev / descDev were allocated here (host upload) rather than borrowed
+    orbx_keypoint* kpsDev = nullptr;
+    uint32_t* descDev = nullptr;
+    float4* kp4 = nullptr;
+    int* cellOf = nullptr;
+    int* cellOff = nullptr;
+    int* cellIdx = nullptr;
+    float minX = 0, minY = 0, maxX = 0, maxY = 0, invW = 0, invH = 0;
+    std::vector<orbx_keypoint> kpsHost;   // kept for the host-side marshalling of BoW / initialization searches
+    bool haveHost = false;
+};
+
+struct orbm_db_s {
+    uint32_t* rows = nullptr;
+    bool owns = false;
+    long long n = 0, rowOffset = 0;
+};
+
+struct orbm_matcher {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    long long launches = 0;
+    long long lastEvals = 0;
+    int smCount = 148;
+    // growable device scratch for queries / results
+    void* scratch = nullptr; size_t scratchBytes = 0;
+    void* pinned = nullptr; size_t pinnedBytes = 0;
+    unsigned long long* dEvals = nullptr;
+    unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
+};
+
+namespace {
+
+#define CKM(call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            M->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return ORBM_ERR_CUDA;                                                                  \
+        }                                                                                          \
+    } while (0)
+
+int ensureScratch(orbm_matcher* M, size_t bytes) {
+    if (bytes <= M->scratchBytes) return ORBM_OK;
+    if (M->scratch) cudaFree(M->scratch);
+    if (M->pinned) cudaFreeHost(M->pinned);
+    M->scratch = nullptr; M->pinned = nullptr; M->scratchBytes = M->pinnedBytes = 0;
+    const size_t want = std::max<size_t>(bytes * 2, 1 << 20);
+    CKM(cudaMalloc(&M->scratch, want));
+    CKM(cudaMallocHost(&M->pinned, want));
+    M->scratchBytes = M->pinnedBytes = want;
+    return ORBM_OK;
+}
+
+// bump allocator over the pinned staging buffer and its device twin (same offsets)
+struct Stage {
+    orbm_matcher* M; size_t off = 0;
+    explicit Stage(orbm_matcher* m) : M(m) {}
+    template <class T> size_t take(size_t count) { off = (off + 255) & ~(size_t)255; size_t at = off; off += count * sizeof(T); return at; }
+    template <class T> T* host(size_t at) { return reinterpret_cast<T*>((uint8_t*)M->pinned + at); }
+    template <class T> T* dev(size_t at) { return reinterpret_cast<T*>((uint8_t*)M->scratch + at); }
+};
+
+void freeFrameBuffers(orbm_frame_s* f) {
+    if (f->ownsInput) { cudaFree(f->kpsDev); cudaFree(f->descDev); }
+    cudaFree(f->kp4); cudaFree(f->cellOf); cudaFree(f->cellOff); cudaFree(f->cellIdx);
+    f->kpsDev = nullptr; f->descDev = nullptr; f->kp4 = nullptr; f->cellOf = f->cellOff = f->cellIdx = nullptr;
+    f->cap = 0; f->ownsInput = false;
+}
+
+int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
+    if (!v || v->n < 0 || (v->n > 0 && (!v->kps || !v->desc)) || !(v->max_x > v->min_x) || !(v->max_y > v->min_y)) return ORBM_ERR_INVALID;
+    if (v->n >= (1 << 19)) { M->err = "more than 2^19 keypoints per frame"; return ORBM_ERR_UNSUPPORTED; }
+    CKM(cudaSetDevice(M->device));
+    const int n = v->n;
+    const bool needOwn = !v->on_device;
+    if (n > f->cap || needOwn != f->ownsInput || !f->cellOff) {
+        freeFrameBuffers(f);
+        const int cap = std::max(n, 1024);
+        if (needOwn) {
+            CKM(cudaMalloc((void**)&f->kpsDev, (size_t)cap * sizeof(orbx_keypoint)));
+            CKM(cudaMalloc((void**)&f->descDev, (size_t)cap * 32));
+        }
+        CKM(cudaMalloc((void**)&f->kp4, (size_t)cap * sizeof(float4)));
+        CKM(cudaMalloc((void**)&f->cellOf, (size_t)cap * sizeof(int)));
+        CKM(cudaMalloc((void**)&f->cellOff, (size_t)(kGridCells + 1) * sizeof(int)));
+        CKM(cudaMalloc((void**)&f->cellIdx, (size_t)cap * sizeof(int)));
+        f->cap = cap; f->ownsInput = needOwn;
+    }
+    f->n = n;
+    f->minX = v->min_x; f->minY = v->min_y; f->maxX = v->max_x; f->maxY = v->max_y;
+    // mfGridElementWidthInv / HeightInv (src/Frame.cc:251-252)
+    f->invW = static_cast<float>(kGridCols) / static_cast<float>(f->maxX - f->minX);
+    f->invH = static_cast<float>(kGridRows) / static_cast<float>(f->maxY - f->minY);
+    if (needOwn) {
+        if (n) {
+            CKM(cudaMemcpyAsync(f->kpsDev, v->kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, M->stream));
+            CKM(cudaMemcpyAsync(f->descDev, v->desc, (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
+        }
+        f->kpsHost.assign(v->kps, v->kps + n);
+        f->haveHost = true;
+    } else {
+        f->kpsDev = const_cast<orbx_keypoint*>(v->kps);
+        f->descDev = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(v->desc));
+        f->haveHost = false;
+    }
+    if (n) {
+        k_grid_prepare<<<(n + 255) / 256, 256, 0, M->stream>>>(n, f->kpsDev, f->kp4, f->cellOf, f->minX, f->minY, f->invW, f->invH);
+        ++M->launches;
+    }
+    k_grid_build<<<1, kGridThreads, 0, M->stream>>>(n, f->cellOf, f->cellOff, f->cellIdx);
+    ++M->launches;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+int ensureHostKps(orbm_matcher* M, orbm_frame_s* f) {
+    if (f->haveHost) return ORBM_OK;
+    f->kpsHost.resize(f->n);
+    if (f->n) {
+        CKM(cudaMemcpyAsync(f->kpsHost.data(), f->kpsDev, (size_t)f->n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, M->stream));
+        CKM(cudaStreamSynchronize(M->stream));
+    }
+    f->haveHost = true;
+    return ORBM_OK;
+}
+
+FrameDev devView(const orbm_frame_s* f) {
+    FrameDev d;
+    d.n = f->n; d.kp4 = f->kp4; d.desc = f->descDev; d.cellOff = f->cellOff; d.cellIdx = f->cellIdx;
+    d.minX = f->minX; d.minY = f->minY; d.invW = f->invW; d.invH = f->invH;
+    return d;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* orbm_strerror(int s) {
+    switch (s) {
+        case ORBM_OK: return "ok";
+        case ORBM_ERR_INVALID: return "invalid argument";
+        case ORBM_ERR_CUDA: return "CUDA error";
+        case ORBM_ERR_CAPACITY: return "output buffer too small";
+        case ORBM_ERR_UNSUPPORTED: return "unsupported configuration";
+        case ORBM_ERR_NO_DEVICE: return "no CUDA device (no CPU fallback exists)";
+    }
+    return "unknown";
+}
+const char* orbm_last_error(orbm_handle h) { return h ? h->err.c_str() : ""; }
+
+int orbm_create(int device, orbm_handle* out) {
+    if (!out) return ORBM_ERR_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return ORBM_ERR_NO_DEVICE;
+    if (device < 0 || device >= ndev) return ORBM_ERR_INVALID;
+    orbm_matcher* M = new orbm_matcher();
+    M->device = device;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&M->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMalloc((void**)&M->dEvals, 8) != cudaSuccess) {
+        fprintf(stderr, "orbm_create: %s\n", cudaGetErrorString(cudaGetLastError()));
+        delete M;
+        return ORBM_ERR_CUDA;
+    }
+    cudaDeviceGetAttribute(&M->smCount, cudaDevAttrMultiProcessorCount, device);
+    cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    *out = M;
+    return ORBM_OK;
+}
+
+void orbm_destroy(orbm_handle M) {
+    if (!M) return;
+    cudaSetDevice(M->device);
+    cudaStreamSynchronize(M->stream);
+    if (M->scratch) cudaFree(M->scratch);
+    if (M->pinned) cudaFreeHost(M->pinned);
+    if (M->dEvals) cudaFree(M->dEvals);
+    if (M->knnPart) cudaFree(M->knnPart);
+    cudaStreamDestroy(M->stream);
+    delete M;
+}
+
+long long orbm_launch_count(orbm_handle h) { return h ? h->launches : 0; }
+void* orbm_stream(orbm_handle h) { return h ? (void*)h->stream : nullptr; }
+long long orbm_last_evaluations(orbm_handle h) { return h ? h->lastEvals : 0; }
+
+// DescriptorDistance (src/ORBmatcher.cc:2058-2074), host side
+int orbm_distance(const uint8_t* a, const uint8_t* b) {
+    uint32_t pa[8], pb[8];
+    memcpy(pa, a, 32); memcpy(pb, b, 32);
+    int dist = 0;
+    for (int i = 0; i < 8; ++i) {
+        uint32_t v = pa[i] ^ pb[i];
+        v = v - ((v >> 1) & 0x55555555u);
+        v = (v & 0x33333333u) + ((v >> 2) & 0x33333333u);
+        dist += (int)((((v + (v >> 4)) & 0xF0F0F0Fu) * 0x1010101u) >> 24);
+    }
+    return dist;
+}
+
+int orbm_frame_create(orbm_handle M, const orbm_frame_view* view, orbm_frame* out) {
+    if (!M || !out) return ORBM_ERR_INVALID;
+    orbm_frame_s* f = new orbm_frame_s();
+    int rc = setFrame(M, f, view);
+    if (rc) { freeFrameBuffers(f); delete f; return rc; }
+    *out = f;
+    return ORBM_OK;
+}
+int orbm_frame_update(orbm_handle M, orbm_frame f, const orbm_frame_view* view) {
+    if (!M || !f) return ORBM_ERR_INVALID;
+    return setFrame(M, f, view);
+}
+void orbm_frame_destroy(orbm_handle M, orbm_frame f) {
+    if (!M || !f) return;
+    cudaSetDevice(M->device);
+    cudaStreamSynchronize(M->stream);
+    freeFrameBuffers(f);
+    delete f;
+}
+
+int orbm_frame_grid(orbm_handle M, orbm_frame f, int* off, int* idx) {
+    if (!M || !f || !off || !idx) return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    CKM(cudaMemcpyAsync(off, f->cellOff, (size_t)(kGridCells + 1) * sizeof(int), cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    if (off[kGridCells]) CKM(cudaMemcpy(idx, f->cellIdx, (size_t)off[kGridCells] * sizeof(int), cudaMemcpyDeviceToHost));
+    return ORBM_OK;
+}
+
+}  // extern "C"
+
+// ---- generic search driver -------------------------------------------------------------------------------------------
+namespace {
+
+// parity tap kernel: the candidate list of one window query, in the reference's order
+__global__ void k_area_list(SearchParams P, int* out, int cap, int* nOut) {
+    const int lane = threadIdx.x & 31;
+    uint32_t qd[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long ne = 0;
+    int count = 0;
+    walk_candidates(P, 0, qd, ne, [&](bool ok, uint32_t entry) {
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) { const int pos = count + __popc(m & ((1u << lane) - 1)); if (pos < cap) out[pos] = (int)(entry & 0x7ffff); }
+        count += __popc(m);
+    });
+    if (lane == 0) *nOut = count;
+}
+
+struct SearchIO {
+    int nq = 0;
+    std::vector<float4> qwin;
+    std::vector<int2> qlev, qrun;
+    std::vector<float> qangle;
+    const uint8_t* qdescSrc = nullptr;      // rows gathered through qsrc
+    std::vector<int> qsrc;                  // original query index of each compacted query
+    const int* bowIdx = nullptr; int nBow = 0;
+    const uint8_t* elig = nullptr;
+    uint8_t* occ = nullptr;                 // in/out, n bytes
+    std::vector<int> result, dist;
+};
+
+// uploads the compacted queries, runs k_search (+ k_rot_filter), downloads per-query results
+int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& io) {
+    CKM(cudaSetDevice(M->device));
+    const int nq = io.nq, n = T->n;
+    io.result.assign(nq, -1); io.dist.assign(nq, 256);
+    M->lastEvals = 0;
+    if (nq == 0) return ORBM_OK;
+    Stage S(M);
+    const size_t oWin = S.take<float4>(nq), oLev = S.take<int2>(nq), oRun = S.take<int2>(nq), oDesc = S.take<uint32_t>((size_t)nq * 8);
+    const size_t oAng = S.take<float>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oElig = S.take<uint8_t>(std::max(n, 1));
+    const size_t oOcc = S.take<uint8_t>(std::max(n, 1));
+    const size_t inEnd = S.off;
+    const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(1);
+    const size_t outEnd = S.off;
+    int rc = ensureScratch(M, outEnd);
+    if (rc) return rc;
+    if (!io.qwin.empty()) memcpy(S.host<float4>(oWin), io.qwin.data(), (size_t)nq * sizeof(float4));
+    if (!io.qlev.empty()) memcpy(S.host<int2>(oLev), io.qlev.data(), (size_t)nq * sizeof(int2));
+    if (!io.qrun.empty()) memcpy(S.host<int2>(oRun), io.qrun.data(), (size_t)nq * sizeof(int2));
+    if (!io.qangle.empty()) memcpy(S.host<float>(oAng), io.qangle.data(), (size_t)nq * sizeof(float));
+    uint8_t* hd = S.host<uint8_t>(oDesc);
+    for (int q = 0; q < nq; ++q) memcpy(hd + 32 * (size_t)q, io.qdescSrc + 32 * (size_t)io.qsrc[q], 32);
+    if (io.nBow) memcpy(S.host<int>(oBow), io.bowIdx, (size_t)io.nBow * sizeof(int));
+    if (io.elig && n) memcpy(S.host<uint8_t>(oElig), io.elig, n);
+    if (io.occ && n) memcpy(S.host<uint8_t>(oOcc), io.occ, n);
+    *S.host<unsigned long long>(oEv) = 0;
+    CKM(cudaMemcpyAsync(M->scratch, M->pinned, inEnd, cudaMemcpyHostToDevice, M->stream));
+    CKM(cudaMemsetAsync(S.dev<unsigned long long>(oEv), 0, 8, M->stream));
+    P.tgt = devView(T);
+    P.nq = nq;
+    P.qwin = S.dev<float4>(oWin); P.qlev = S.dev<int2>(oLev); P.qrun = S.dev<int2>(oRun);
+    P.qdesc = S.dev<uint32_t>(oDesc); P.qangle = S.dev<float>(oAng); P.bowIdx = S.dev<int>(oBow);
+    P.elig = io.elig ? S.dev<uint8_t>(oElig) : nullptr;
+    P.occ = io.occ ? S.dev<uint8_t>(oOcc) : nullptr;
+    P.qResult = S.dev<int>(oRes); P.qDist = S.dev<int>(oDist); P.qBin = S.dev<int>(oBin);
+    P.evals = S.dev<unsigned long long>(oEv);
+    size_t smem = (size_t)kSearchWarps * kSlab * 4;
+    if (P.state == 1) smem += ((size_t)n + 15) & ~(size_t)15;
+    if (P.state == 2) smem += (((size_t)n * 2 + 15) & ~(size_t)15) + (size_t)n * 4;
+    if (smem > 200 * 1024) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
+    const int grid = P.state != 0 ? 1 : std::max(1, std::min((nq + kSearchWarps - 1) / kSearchWarps, M->smCount * 2));
+    k_search<<<grid, kSearchThreads, smem, M->stream>>>(P);
+    ++M->launches;
+    if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oRes, (uint8_t*)M->scratch + oRes, outEnd - oRes, cudaMemcpyDeviceToHost, M->stream));
+    if (io.occ && n) CKM(cudaMemcpyAsync(S.host<uint8_t>(oOcc), S.dev<uint8_t>(oOcc), n, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    memcpy(io.result.data(), S.host<int>(oRes), (size_t)nq * sizeof(int));
+    memcpy(io.dist.data(), S.host<int>(oDist), (size_t)nq * sizeof(int));
+    if (io.occ && n && P.state == 1) memcpy(io.occ, S.host<uint8_t>(oOcc), n);
+    M->lastEvals = (long long)*S.host<unsigned long long>(oEv);
+    return ORBM_OK;
+}
+
+SearchParams baseParams() {
+    SearchParams P;
+    memset(&P, 0, sizeof(P));
+    P.none2 = 256;
+    return P;
+}
+
+// level bounds of Frame::GetFeaturesInArea (src/Frame.cc:689-707): bCheckLevels = minLevel > 0 || maxLevel >= 0
+int2 levelBounds(int minLevel, int maxLevel) {
+    const bool check = (minLevel > 0) || (maxLevel >= 0);
+    if (!check) return make_int2(INT_MIN, INT_MAX);
+    return make_int2(minLevel, maxLevel >= 0 ? maxLevel : INT_MAX);
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbm_features_in_area(orbm_handle M, orbm_frame f, float x, float y, float r, int min_level, int max_level, int* out,
+                          int cap, int* n_out) {
+    if (!M || !f || !n_out || cap < 0) return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    Stage S(M);
+    const size_t oWin = S.take<float4>(1), oLev = S.take<int2>(1), oOut = S.take<int>(std::max(cap, 1)), oN = S.take<int>(1);
+    int rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    *S.host<float4>(oWin) = make_float4(x, y, r, 0);
+    *S.host<int2>(oLev) = levelBounds(min_level, max_level);
+    CKM(cudaMemcpyAsync(M->scratch, M->pinned, oOut, cudaMemcpyHostToDevice, M->stream));
+    SearchParams P = baseParams();
+    P.tgt = devView(f); P.nq = 1; P.source = 0;
+    P.qwin = S.dev<float4>(oWin); P.qlev = S.dev<int2>(oLev);
+    // the walk also evaluates a distance per candidate: give it a valid descriptor row to read (the frame's first)
+    if (f->n == 0) { *n_out = 0; return ORBM_OK; }
+    k_area_list<<<1, 32, 0, M->stream>>>(P, S.dev<int>(oOut), cap, S.dev<int>(oN));
+    ++M->launches;
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOut, (uint8_t*)M->scratch + oOut, S.off - oOut, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    const int n = *S.host<int>(oN);
+    *n_out = n;
+    if (out) memcpy(out, S.host<int>(oOut), (size_t)std::min(n, cap) * sizeof(int));
+    return n > cap ? ORBM_ERR_CAPACITY : ORBM_OK;
+}
+
+// M1: src/ORBmatcher.cc:43-213 (mono branch)
+int orbm_search_local_map(orbm_handle M, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
+                          const uint8_t* valid, const float* proj_x, const float* proj_y, const int* level,
+                          const float* view_cos, const uint8_t* qdesc, float th, float nnratio, int* kp_match, int* nmatches) {
+    if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
+    const bool bFactor = th != 1.0;
+    SearchIO io;
+    for (int q = 0; q < nq; ++q) {
+        if (!valid[q]) continue;
+        const int l = level[q];
+        if (l < 0 || l >= nlevels) return ORBM_ERR_INVALID;
+        float r = (view_cos[q] > 0.998) ? 2.5f : 4.0f;           // RadiusByViewingCos (:215-221)
+        if (bFactor) r *= th;
+        io.qwin.push_back(make_float4(proj_x[q], proj_y[q], r * scale_factors[l], 0));
+        io.qlev.push_back(levelBounds(l - 1, l));
+        io.qsrc.push_back(q);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied;
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 1; P.rule = RULE_LOCAL_MAP; P.nnratio = nnratio;
+    int rc = runSearch(M, f, P, io);
+    if (rc) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { kp_match[io.result[q]] = io.qsrc[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// M2 / M3: src/ORBmatcher.cc:1676-1887 (mono), :1889-2010
+int orbm_search_frame(orbm_handle M, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
+                      const uint8_t* valid, const float* u, const float* v, const int* octave, const float* qangle,
+                      const uint8_t* qdesc, float th, int th_dist, int check_orientation, int* kp_match, int* nmatches) {
+    if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
+    SearchIO io;
+    for (int q = 0; q < nq; ++q) {
+        if (!valid[q]) continue;
+        const int o = octave[q];
+        if (o < 0 || o >= nlevels) return ORBM_ERR_INVALID;
+        const float radius = th * scale_factors[o];
+        io.qwin.push_back(make_float4(u[q], v[q], radius, 0));
+        io.qlev.push_back(levelBounds(o - 1, o + 1));
+        io.qangle.push_back(qangle ? qangle[q] : 0.f);
+        io.qsrc.push_back(q);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied;
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 1; P.rule = RULE_BEST_LE; P.thF = (float)th_dist; P.checkOri = check_orientation && qangle;
+    int rc = runSearch(M, f, P, io);
+    if (rc) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { kp_match[io.result[q]] = io.qsrc[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// M7: src/ORBmatcher.cc:427-532, :534-646
+int orbm_search_sim3(orbm_handle M, orbm_frame kf, uint8_t* matched, const float* scale_factors, int nlevels, int nq,
+                     const uint8_t* valid, const float* u, const float* v, const int* level, const uint8_t* qdesc, int th,
+                     float ratio_hamming, int* kp_match, int* nmatches) {
+    if (!M || !kf || !matched || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
+    SearchIO io;
+    for (int q = 0; q < nq; ++q) {
+        if (!valid[q]) continue;
+        const int l = level[q];
+        if (l < 0 || l >= nlevels) return ORBM_ERR_INVALID;
+        const float radius = th * scale_factors[l];
+        io.qwin.push_back(make_float4(u[q], v[q], radius, 0));
+        io.qlev.push_back(make_int2(l - 1, l));                   // the loop's own level test (:505)
+        io.qsrc.push_back(q);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = matched;
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 1; P.rule = RULE_BEST_LE; P.thF = ORBM_TH_LOW * ratio_hamming;
+    int rc = runSearch(M, kf, P, io);
+    if (rc) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { kp_match[io.result[q]] = io.qsrc[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// M9 (candidate part): src/ORBmatcher.cc:1233-1291, :1400-1437
+int orbm_fuse_candidates(orbm_handle M, orbm_frame kf, const float* scale_factors, const float* inv_sigma2, int nlevels, int nq,
+                         const uint8_t* valid, const float* u, const float* v, const int* level, const uint8_t* qdesc, float th,
+                         int chi2_gate, int* best_idx, int* best_dist) {
+    if (!M || !kf || !scale_factors || nq < 0 || !best_idx || !best_dist || (chi2_gate && !inv_sigma2)) return ORBM_ERR_INVALID;
+    SearchIO io;
+    for (int q = 0; q < nq; ++q) {
+        best_idx[q] = -1; best_dist[q] = 256;
+        if (!valid[q]) continue;
+        const int l = level[q];
+        if (l < 0 || l >= nlevels) return ORBM_ERR_INVALID;
+        io.qwin.push_back(make_float4(u[q], v[q], th * scale_factors[l], 0));
+        io.qlev.push_back(make_int2(l - 1, l));
+        io.qsrc.push_back(q);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc;
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 0; P.rule = RULE_NONE; P.chi2 = chi2_gate;
+    // the chi2 table rides in the (otherwise unused) elig slot of the staging area: upload it separately
+    float* dSig = nullptr;
+    if (chi2_gate) {
+        CKM(cudaSetDevice(M->device));
+        CKM(cudaMalloc((void**)&dSig, (size_t)nlevels * sizeof(float)));
+        cudaError_t e = cudaMemcpyAsync(dSig, inv_sigma2, (size_t)nlevels * sizeof(float), cudaMemcpyHostToDevice, M->stream);
+        if (e != cudaSuccess) { cudaFree(dSig); CKM(e); }
+        P.invSigma2 = dSig;
+    }
+    int rc = runSearch(M, kf, P, io);
+    if (dSig) cudaFree(dSig);
+    if (rc) return rc;
+    for (int q = 0; q < io.nq; ++q) { best_idx[io.qsrc[q]] = io.result[q]; best_dist[io.qsrc[q]] = io.dist[q]; }
+    return ORBM_OK;
+}
+
+// M5: src/ORBmatcher.cc:648-763
+int orbm_search_initialization(orbm_handle M, orbm_frame f1, orbm_frame f2, float* prev_matched, int window_size, float nnratio,
+                               int check_orientation, int* matches12, int* nmatches) {
+    if (!M || !f1 || !f2 || !prev_matched || !matches12 || !nmatches) return ORBM_ERR_INVALID;
+    int rc = ensureHostKps(M, f1);
+    if (rc) return rc;
+    if ((rc = ensureHostKps(M, f2))) return rc;
+    const int n1 = f1->n;
+    // query descriptors = F1's rows: fetch them to the host once (F1 may be device-resident)
+    std::vector<uint8_t> d1((size_t)std::max(n1, 1) * 32);
+    if (n1) {
+        CKM(cudaSetDevice(M->device));
+        CKM(cudaMemcpyAsync(d1.data(), f1->descDev, (size_t)n1 * 32, cudaMemcpyDeviceToHost, M->stream));
+        CKM(cudaStreamSynchronize(M->stream));
+    }
+    SearchIO io;
+    for (int i1 = 0; i1 < n1; ++i1) {
+        matches12[i1] = -1;
+        const int level1 = f1->kpsHost[i1].octave;
+        if (level1 > 0) continue;
+        io.qwin.push_back(make_float4(prev_matched[2 * i1], prev_matched[2 * i1 + 1], (float)window_size, 0));
+        io.qlev.push_back(levelBounds(level1, level1));
+        io.qangle.push_back(f1->kpsHost[i1].angle);
+        io.qsrc.push_back(i1);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = d1.data();
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 2; P.rule = RULE_INIT; P.thI = ORBM_TH_LOW; P.nnratio = nnratio; P.none2 = INT_MAX;
+    P.checkOri = check_orientation;
+    if ((rc = runSearch(M, f2, P, io))) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q)
+        if (io.result[q] >= 0) {
+            const int i1 = io.qsrc[q];
+            matches12[i1] = io.result[q];
+            prev_matched[2 * i1] = f2->kpsHost[io.result[q]].x;       // "update prev matched" (:758-760)
+            prev_matched[2 * i1 + 1] = f2->kpsHost[io.result[q]].y;
+            ++nm;
+        }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+}  // extern "C"
+
+// ---- BoW-guided searches ---------------------------------------------------------------------------------------------
+namespace {
+
+bool validFeatVec(const orbm_featvec* fv, int n) {
+    if (!fv || fv->n_nodes < 0) return false;
+    if (fv->n_nodes == 0) return true;
+    if (!fv->node || !fv->off || !fv->idx) return false;
+    for (int i = 1; i < fv->n_nodes; ++i) if (fv->node[i] <= fv->node[i - 1]) return false;
+    for (int i = 0; i < fv->n_nodes; ++i) if (fv->off[i + 1] < fv->off[i]) return false;
+    for (int i = fv->off[0]; i < fv->off[fv->n_nodes]; ++i) if (fv->idx[i] < 0 || fv->idx[i] >= n) return false;
+    return true;
+}
+
+// The merge-join of two DBoW2::FeatureVector maps (e.g. src/ORBmatcher.cc:241-392): for every shared node, every
+// eligible feature of side 1 becomes a query (in node order, then list order) whose candidates are the node's run of
+// side 2.
+void joinQueries(const orbm_featvec* a, const orbm_featvec* b, const uint8_t* elig1, SearchIO& io) {
+    int ia = 0, ib = 0;
+    while (ia < a->n_nodes && ib < b->n_nodes) {
+        if (a->node[ia] == b->node[ib]) {
+            for (int p = a->off[ia]; p < a->off[ia + 1]; ++p) {
+                const int i1 = a->idx[p];
+                if (elig1 && !elig1[i1]) continue;
+                io.qrun.push_back(make_int2(b->off[ib] - b->off[0], b->off[ib + 1] - b->off[0]));
+                io.qsrc.push_back(i1);
+            }
+            ++ia; ++ib;
+        } else if (a->node[ia] < b->node[ib]) {
+            ia = (int)(std::lower_bound(a->node, a->node + a->n_nodes, b->node[ib]) - a->node);
+        } else {
+            ib = (int)(std::lower_bound(b->node, b->node + b->n_nodes, a->node[ia]) - b->node);
+        }
+    }
+    io.nq = (int)io.qsrc.size();
+    io.bowIdx = b->n_nodes ? b->idx + b->off[0] : nullptr;
+    io.nBow = b->n_nodes ? b->off[b->n_nodes] - b->off[0] : 0;
+}
+
+int fetchDescHost(orbm_matcher* M, orbm_frame_s* f, std::vector<uint8_t>& out) {
+    out.resize((size_t)std::max(f->n, 1) * 32);
+    if (f->n) {
+        CKM(cudaSetDevice(M->device));
+        CKM(cudaMemcpyAsync(out.data(), f->descDev, (size_t)f->n * 32, cudaMemcpyDeviceToHost, M->stream));
+        CKM(cudaStreamSynchronize(M->stream));
+    }
+    return ORBM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+// M4a: src/ORBmatcher.cc:223-425
+int orbm_search_bow_kf_frame(orbm_handle M, orbm_frame kf, const orbm_featvec* fv_kf, const uint8_t* elig1, orbm_frame f,
+                             const orbm_featvec* fv_f, float nnratio, int check_orientation, int* match_f, int* nmatches) {
+    if (!M || !kf || !f || !elig1 || !match_f || !nmatches || !validFeatVec(fv_kf, kf->n) || !validFeatVec(fv_f, f->n)) return ORBM_ERR_INVALID;
+    int rc = ensureHostKps(M, kf);
+    if (rc) return rc;
+    std::vector<uint8_t> d1;
+    if ((rc = fetchDescHost(M, kf, d1))) return rc;
+    for (int j = 0; j < f->n; ++j) match_f[j] = -1;
+    SearchIO io;
+    joinQueries(fv_kf, fv_f, elig1, io);
+    for (int q = 0; q < io.nq; ++q) io.qangle.push_back(kf->kpsHost[io.qsrc[q]].angle);
+    io.qdescSrc = d1.data();
+    std::vector<uint8_t> occ((size_t)std::max(f->n, 1), 0);        // vpMapPointMatches starts all NULL (:227)
+    io.occ = occ.data();
+    SearchParams P = baseParams();
+    P.source = 1; P.state = 1; P.rule = RULE_RATIO_LE; P.thI = ORBM_TH_LOW; P.nnratio = nnratio; P.checkOri = check_orientation;
+    if ((rc = runSearch(M, f, P, io))) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { match_f[io.result[q]] = io.qsrc[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// M4b: src/ORBmatcher.cc:765-905
+int orbm_search_bow_kf_kf(orbm_handle M, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* elig1, orbm_frame kf2,
+                          const orbm_featvec* fv2, const uint8_t* elig2, float nnratio, int check_orientation, int* matches12,
+                          int* nmatches) {
+    if (!M || !kf1 || !kf2 || !elig1 || !elig2 || !matches12 || !nmatches || !validFeatVec(fv1, kf1->n) || !validFeatVec(fv2, kf2->n))
+        return ORBM_ERR_INVALID;
+    int rc = ensureHostKps(M, kf1);
+    if (rc) return rc;
+    std::vector<uint8_t> d1;
+    if ((rc = fetchDescHost(M, kf1, d1))) return rc;
+    for (int i = 0; i < kf1->n; ++i) matches12[i] = -1;
+    SearchIO io;
+    joinQueries(fv1, fv2, elig1, io);
+    for (int q = 0; q < io.nq; ++q) io.qangle.push_back(kf1->kpsHost[io.qsrc[q]].angle);
+    io.qdescSrc = d1.data();
+    io.elig = elig2;
+    std::vector<uint8_t> occ((size_t)std::max(kf2->n, 1), 0);      // vbMatched2 (:778)
+    io.occ = occ.data();
+    SearchParams P = baseParams();
+    P.source = 1; P.state = 1; P.rule = RULE_RATIO_LT; P.thI = ORBM_TH_LOW; P.nnratio = nnratio; P.checkOri = check_orientation;
+    if ((rc = runSearch(M, kf2, P, io))) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { matches12[io.qsrc[q]] = io.result[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// M6: src/ORBmatcher.cc:907-1146 (mono, Pinhole)
+int orbm_search_triangulation(orbm_handle M, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* free1, orbm_frame kf2,
+                              const orbm_featvec* fv2, const uint8_t* free2, const float* ep, const float* scale_factors2,
+                              const float* F12, const float* sigma2, int nlevels, int coarse, int check_orientation,
+                              int* matches12, int* nmatches) {
+    if (!M || !kf1 || !kf2 || !free1 || !free2 || !ep || !scale_factors2 || !matches12 || !nmatches || nlevels < 1 ||
+        (!coarse && (!F12 || !sigma2)) || !validFeatVec(fv1, kf1->n) || !validFeatVec(fv2, kf2->n))
+        return ORBM_ERR_INVALID;
+    int rc = ensureHostKps(M, kf1);
+    if (rc) return rc;
+    std::vector<uint8_t> d1;
+    if ((rc = fetchDescHost(M, kf1, d1))) return rc;
+    for (int i = 0; i < kf1->n; ++i) matches12[i] = -1;
+    SearchIO io;
+    joinQueries(fv1, fv2, free1, io);
+    for (int q = 0; q < io.nq; ++q) {
+        const orbx_keypoint& k = kf1->kpsHost[io.qsrc[q]];
+        io.qwin.push_back(make_float4(k.x, k.y, 0, 0));
+        io.qangle.push_back(k.angle);
+    }
+    io.qdescSrc = d1.data();
+    io.elig = free2;
+    SearchParams P = baseParams();
+    P.source = 1; P.state = 0; P.rule = RULE_LAST_MIN; P.tri = 1; P.coarse = coarse; P.checkOri = check_orientation;
+    P.ep0 = ep[0]; P.ep1 = ep[1];
+    if (F12) memcpy(P.F, F12, sizeof(P.F));
+    CKM(cudaSetDevice(M->device));
+    float* dTab = nullptr;
+    CKM(cudaMalloc((void**)&dTab, (size_t)2 * nlevels * sizeof(float)));
+    std::vector<float> tab(2 * (size_t)nlevels, 0.f);
+    for (int l = 0; l < nlevels; ++l) { tab[l] = scale_factors2[l]; tab[nlevels + l] = sigma2 ? sigma2[l] : 0.f; }
+    cudaError_t e = cudaMemcpyAsync(dTab, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, M->stream);
+    if (e != cudaSuccess) { cudaFree(dTab); CKM(e); }
+    P.scale2 = dTab; P.sigma2 = dTab + nlevels;
+    rc = runSearch(M, kf2, P, io);
+    cudaFree(dTab);
+    if (rc) return rc;
+    int nm = 0;
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { matches12[io.qsrc[q]] = io.result[q]; ++nm; }
+    *nmatches = nm;
+    return ORBM_OK;
+}
+
+// ---- brute-force k-NN ----------------------------------------------------------------------------------------------------
+int orbm_db_create(orbm_handle M, const uint8_t* rows, long long ndb, int rows_on_device, long long row_offset, orbm_db* out) {
+    if (!M || !out || ndb < 0 || (ndb > 0 && !rows)) return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    orbm_db_s* db = new orbm_db_s();
+    db->n = ndb; db->rowOffset = row_offset;
+    if (rows_on_device) {
+        db->rows = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(rows)); db->owns = false;
+    } else {
+        cudaError_t e = cudaMalloc((void**)&db->rows, (size_t)std::max<long long>(ndb, 1) * 32);
+        if (e == cudaSuccess && ndb) e = cudaMemcpy(db->rows, rows, (size_t)ndb * 32, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { if (db->rows) cudaFree(db->rows); delete db; CKM(e); }
+        db->owns = true;
+    }
+    *out = db;
+    return ORBM_OK;
+}
+void orbm_db_destroy(orbm_handle M, orbm_db db) {
+    if (!M || !db) return;
+    cudaSetDevice(M->device);
+    cudaStreamSynchronize(M->stream);
+    if (db->owns) cudaFree(db->rows);
+    delete db;
+}
+
+int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
+    if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
+    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    const int qblocks = (nq + kKnnThreads - 1) / kKnnThreads;
+    // chunks: about 4 resident CTAs per SM over all query blocks, each a multiple of the tile, at most 2^23 rows
+    long long target = std::max<long long>(1, ((long long)M->smCount * 4 + qblocks - 1) / qblocks);
+    long long rowsPerChunk = (db->n + target - 1) / std::max<long long>(target, 1);
+    rowsPerChunk = std::max<long long>(kKnnTileRows, (rowsPerChunk + kKnnTileRows - 1) / kKnnTileRows * kKnnTileRows);
+    rowsPerChunk = std::min<long long>(rowsPerChunk, 1LL << 22);
+    const int nchunks = (int)std::max<long long>(1, (db->n + rowsPerChunk - 1) / rowsPerChunk);
+    const size_t need = (size_t)nchunks * nq * k * sizeof(unsigned long long);
+    if (need > M->knnPartBytes) {
+        if (M->knnPart) cudaFree(M->knnPart);
+        M->knnPart = nullptr; M->knnPartBytes = 0;
+        CKM(cudaMalloc((void**)&M->knnPart, need));
+        M->knnPartBytes = need;
+    }
+    k_knn<<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n, db->rowOffset,
+                                                          (int)rowsPerChunk, k, M->knnPart);
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx);
+    M->launches += 2;
+    M->lastEvals = (long long)nq * db->n;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+int orbm_knn(orbm_handle M, orbm_db db, const uint8_t* q, int nq, int k, uint16_t* dist, int32_t* idx) {
+    if (!M || !db || !q || nq <= 0 || k < 1 || k > kKnnMaxK || !dist || !idx) return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    Stage S(M);
+    const size_t oQ = S.take<uint8_t>((size_t)nq * 32), oD = S.take<uint16_t>((size_t)nq * k), oI = S.take<int32_t>((size_t)nq * k);
+    int rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    memcpy(S.host<uint8_t>(oQ), q, (size_t)nq * 32);
+    CKM(cudaMemcpyAsync(S.dev<uint8_t>(oQ), S.host<uint8_t>(oQ), (size_t)nq * 32, cudaMemcpyHostToDevice, M->stream));
+    if ((rc = orbm_knn_device(M, db, S.dev<uint8_t>(oQ), nq, k, S.dev<uint16_t>(oD), S.dev<int32_t>(oI), nullptr))) return rc;
+    CKM(cudaMemcpyAsync(S.host<uint8_t>(oD), S.dev<uint8_t>(oD), S.off - oD, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    memcpy(dist, S.host<uint16_t>(oD), (size_t)nq * k * sizeof(uint16_t));
+    memcpy(idx, S.host<int32_t>(oI), (size_t)nq * k * sizeof(int32_t));
+    return ORBM_OK;
+}
+
+// k smallest (dist, global row) per query over nshards sorted lists (host side: 2000 x 8 x k entries at most)
+int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq, int k, uint16_t* out_dist, int32_t* out_idx) {
+    if (!dist || !idx || nshards < 1 || nq < 0 || k < 1 || !out_dist || !out_idx) return ORBM_ERR_INVALID;
+    std::vector<unsigned long long> keys((size_t)nshards * k);
+    for (int q = 0; q < nq; ++q) {
+        size_t m = 0;
+        for (int s = 0; s < nshards; ++s)
+            for (int t = 0; t < k; ++t) {
+                const size_t at = ((size_t)s * nq + q) * k + t;
+                if (idx[at] < 0) continue;
+                keys[m++] = ((unsigned long long)dist[at] << 32) | (uint32_t)idx[at];
+            }
+        std::sort(keys.begin(), keys.begin() + m);
+        for (int t = 0; t < k; ++t) {
+            if ((size_t)t < m) { out_dist[(size_t)q * k + t] = (uint16_t)(keys[t] >> 32); out_idx[(size_t)q * k + t] = (int32_t)(keys[t] & 0xffffffffu); }
+            else { out_dist[(size_t)q * k + t] = 65535; out_idx[(size_t)q * k + t] = -1; }
+        }
+    }
+    return ORBM_OK;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors selection (src/MapPoint.cc:366-396), batched over map points
+int orbm_distinctive_descriptors(orbm_handle M, const uint8_t* desc, const int* off, int npoints, int* best) {
+    if (!M || !off || npoints < 0 || !best || (npoints > 0 && off[npoints] > 0 && !desc)) return ORBM_ERR_INVALID;
+    if (npoints == 0) return ORBM_OK;
+    CKM(cudaSetDevice(M->device));
+    const int rows = off[npoints];
+    Stage S(M);
+    const size_t oD = S.take<uint8_t>((size_t)std::max(rows, 1) * 32), oO = S.take<int>(npoints + 1), oB = S.take<int>(npoints);
+    int rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    if (rows) memcpy(S.host<uint8_t>(oD), desc, (size_t)rows * 32);
+    memcpy(S.host<int>(oO), off, (size_t)(npoints + 1) * sizeof(int));
+    CKM(cudaMemcpyAsync(M->scratch, M->pinned, oB, cudaMemcpyHostToDevice, M->stream));
+    k_distinctive<<<(npoints + 7) / 8, 256, 0, M->stream>>>(S.dev<uint32_t>(oD), S.dev<int>(oO), npoints, S.dev<int>(oB));
+    ++M->launches;
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync(S.host<int>(oB), S.dev<int>(oB), (size_t)npoints * sizeof(int), cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    memcpy(best, S.host<int>(oB), (size_t)npoints * sizeof(int));
+    return ORBM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,581 @@
+// Hamming-matching kernels of the B200-native ORBmatcher (include/orbm.h).
+//
+// k_grid_*        Frame::AssignFeaturesToGrid (src/Frame.cc:385-416) as a stable counting sort -> CSR grid.
+// k_search        every guided search of src/ORBmatcher.cc (M1-M7, M9 of SURVEY.md 8a) behind one engine:
+//                   candidate source   : 64x48 frame grid window (Frame/KeyFrame::GetFeaturesInArea order) | BoW node run
+//                   per-candidate test : level range, square window, chi2 gate, eligibility, epipolar predicate
+//                   distance           : 256-bit Hamming, 8 x (xor, popc) on the integer pipe
+//                   reduction          : first minimum (+ second best and their levels) | last minimum
+//                   acceptance         : TH_HIGH / TH_LOW / ORBdist, NN-ratio variants of the reference
+//                   state              : once-only slot occupancy | "steal if strictly better" (SearchForInitialization)
+//                 The reference loops are SEQUENTIAL over queries (an accepted match occupies its keypoint for all later
+//                 queries).  Here every warp gathers candidates and computes distances for its own query in parallel
+//                 (the expensive part), parks them in a shared-memory slab, and then the queries are RESOLVED in query
+//                 order by passing a token through shared memory: the resolve step only reads the slab, tests the
+//                 occupancy bytes and does two warp reductions.  Searches without inter-query state (triangulation,
+//                 fuse) skip the token and spread over many CTAs.
+// k_rot_filter    rotation histogram + ComputeThreeMaxima (src/ORBmatcher.cc:2012-2053) epilogue.
+// k_knn / k_knn_merge   brute-force k-NN (BASELINE config 5): thread = query, database rows broadcast from shared memory
+//                 tiles filled with TMA bulk copies; 256-bit popcount through a carry-save adder tree (4 POPC instead of
+//                 8: POPC issues at 16/clk/SM on B200, LOP3 at 128/clk/SM — tools/microbench.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/orbm.h"
+
+namespace orbm {
+
+constexpr int kGridCols = 64, kGridRows = 48, kGridCells = kGridCols * kGridRows;
+
+struct FrameDev {
+    int n;
+    const float4* kp4;        // x, y, angle, octave (int bits)
+    const uint32_t* desc;     // n x 8
+    const int* cellOff;       // kGridCells + 1
+    const int* cellIdx;       // n
+    float minX, minY, invW, invH;
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// grid build: cell of every keypoint (PosInGrid uses round(), half away from zero), then a stable counting sort
+__global__ void k_grid_prepare(int n, const orbx_keypoint* __restrict__ kps, float4* __restrict__ kp4, int* __restrict__ cellOf,
+                               float minX, float minY, float invW, float invH) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const orbx_keypoint k = kps[i];
+    kp4[i] = make_float4(k.x, k.y, k.angle, __int_as_float(k.octave));
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(k.x, minX), invW));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(k.y, minY), invH));
+    cellOf[i] = (px < 0 || px >= kGridCols || py < 0 || py >= kGridRows) ? -1 : px * kGridRows + py;
+}
+
+// one CTA: histogram, exclusive scan over the 3072 cells, then a STABLE scatter (ascending keypoint index inside a cell,
+// the reference's push_back order).  n is a few thousand; the per-cell order is produced by letting each thread own a
+// contiguous range of cells and scan the keypoints of those cells in index order via a per-cell linked pass.
+constexpr int kGridThreads = 1024;
+__global__ void __launch_bounds__(kGridThreads) k_grid_build(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
+                                                             int* __restrict__ cellIdx) {
+    __shared__ int cnt[kGridCells];
+    __shared__ int warpSum[32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int c = tid; c < kGridCells; c += kGridThreads) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kGridThreads) { const int c = cellOf[i]; if (c >= 0) atomicAdd(&cnt[c], 1); }
+    __syncthreads();
+    // exclusive scan of cnt[0..3072): 3 cells per thread
+    constexpr int per = kGridCells / kGridThreads;
+    int v[per], s = 0;
+#pragma unroll
+    for (int k = 0; k < per; ++k) { v[k] = cnt[tid * per + k]; s += v[k]; }
+    int incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) warpSum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int w = warpSum[lane], iw = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, iw, o); if (lane >= o) iw += t; }
+        warpSum[lane] = iw - w;
+    }
+    __syncthreads();
+    int run = warpSum[wid] + incl - s;
+#pragma unroll
+    for (int k = 0; k < per; ++k) { cnt[tid * per + k] = run; cellOff[tid * per + k] = run; run += v[k]; }
+    if (tid == kGridThreads - 1) cellOff[kGridCells] = run;
+    __syncthreads();
+    // stable scatter: warp w walks keypoints in index order in chunks of 32; within a chunk, a keypoint's rank inside its
+    // cell = number of lower lanes with the same cell (match_any); chunks are processed in order by ONE warp per pass
+    // over the array — n is small, so a single warp does the ordered pass while the others idle.
+    if (wid == 0) {
+        for (int base = 0; base < n; base += 32) {
+            const int i = base + lane;
+            const int c = i < n ? cellOf[i] : -1;
+            const unsigned peers = __match_any_sync(0xffffffffu, c);
+            if (c >= 0) {
+                const int rank = __popc(peers & ((1u << lane) - 1));
+                const int leader = __ffs(peers) - 1;
+                int basePos = 0;
+                if (lane == leader) { basePos = cnt[c]; cnt[c] = basePos + __popc(peers); }
+                basePos = __shfl_sync(peers, basePos, leader);
+                cellIdx[basePos + rank] = i;
+            }
+            __syncwarp();
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+enum Rule : int {
+    RULE_LOCAL_MAP = 0,   // M1: best <= TH_HIGH, reject iff bestLevel == bestLevel2 && best > nnratio * best2
+    RULE_BEST_LE = 1,     // M2/M3/M7: (float)best <= thF
+    RULE_RATIO_LE = 2,    // M4a: best <= thI && (float)best < nnratio * (float)best2
+    RULE_RATIO_LT = 3,    // M4b: best <  thI && (float)best < nnratio * (float)best2
+    RULE_INIT = 4,        // M5: best <= thI && best < (float)best2 * nnratio
+    RULE_LAST_MIN = 5,    // M6: any surviving candidate; the LAST minimum wins
+    RULE_NONE = 6         // M9: report best index / distance, no acceptance
+};
+
+struct SearchParams {
+    FrameDev tgt;
+    int nq;
+    int source;                  // 0 = grid window, 1 = BoW run
+    const float4* qwin;          // window: u, v, r, -          (M6: kp1.x, kp1.y, -, -)
+    const int2* qlev;            // window: lo, hi octave bounds (inclusive)
+    const int2* qrun;            // BoW: [begin, end) into bowIdx
+    const int* bowIdx;
+    const uint32_t* qdesc;       // nq x 8
+    const float* qangle;
+    const uint8_t* elig;         // target-side eligibility (may be NULL)
+    uint8_t* occ;                // target-side occupancy bytes, in/out (NULL when state == 0)
+    int state;                   // 0 = none, 1 = occupancy (claim on accept), 2 = steal-if-better (M5)
+    int rule;
+    float thF; int thI; float nnratio; int none2;
+    int checkOri;
+    int chi2; const float* invSigma2;
+    int tri; int coarse; float ep0, ep1; float F[9]; const float* scale2; const float* sigma2;
+    int* qResult;                // accepted target index or -1
+    int* qDist;                  // best distance
+    int* qBin;                   // rotation bin of the accept event or -1
+    unsigned long long* evals;
+};
+
+constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 384;
+
+__device__ __forceinline__ int hamming8(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
+    return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
+           __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y) + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+}
+
+// entry packing: dist (9 bits) << 23 | octave (4 bits) << 19 | idx (19 bits)
+__device__ __forceinline__ uint32_t pack_entry(int dist, int oct, int idx) { return ((uint32_t)dist << 23) | ((uint32_t)(oct & 15) << 19) | (uint32_t)idx; }
+
+// Walks the candidates of query q in the reference's order; calls consume(active, entry) warp-synchronously for every
+// chunk of 32 candidate slots (active = this lane holds a candidate that passed all per-candidate tests).
+template <class Consume>
+__device__ __forceinline__ void walk_candidates(const SearchParams& P, int q, const uint32_t (&qd)[8], unsigned long long& nEval,
+                                                Consume&& consume) {
+    const int lane = threadIdx.x & 31;
+    const FrameDev& T = P.tgt;
+    const uint4* drows = reinterpret_cast<const uint4*>(T.desc);
+    if (P.source == 0) {
+        const float4 w = P.qwin[q];
+        const int2 lv = P.qlev[q];
+        const float x = w.x, y = w.y, r = w.z;
+        // Frame::GetFeaturesInArea (src/Frame.cc:665-687): cell range, early outs
+        const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, T.minX), r), T.invW)));
+        if (minCX >= kGridCols) return;
+        const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, T.minX), r), T.invW)));
+        if (maxCX < 0) return;
+        const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, T.minY), r), T.invH)));
+        if (minCY >= kGridRows) return;
+        const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, T.minY), r), T.invH)));
+        if (maxCY < 0) return;
+        for (int ix = minCX; ix <= maxCX; ++ix) {
+            if (minCY > maxCY) break;
+            const int rb = T.cellOff[ix * kGridRows + minCY], re = T.cellOff[ix * kGridRows + maxCY + 1];
+            for (int base = rb; base < re; base += 32) {
+                const int e = base + lane;
+                bool ok = false; uint32_t entry = 0;
+                if (e < re) {
+                    const int idx = T.cellIdx[e];
+                    const float4 k = T.kp4[idx];
+                    const int oct = __float_as_int(k.w);
+                    ok = oct >= lv.x && oct <= lv.y && fabsf(__fsub_rn(k.x, x)) < r && fabsf(__fsub_rn(k.y, y)) < r;
+                    if (ok && P.chi2) {
+                        const float ex = __fsub_rn(x, k.x), ey = __fsub_rn(y, k.y);
+                        const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                        ok = !((double)__fmul_rn(e2, P.invSigma2[oct]) > 5.99);
+                    }
+                    if (ok && P.elig) ok = P.elig[idx] != 0;
+                    if (ok) {
+                        const int d = hamming8(qd, drows[2 * idx], drows[2 * idx + 1]);
+                        ++nEval;
+                        entry = pack_entry(d, oct, idx);
+                    }
+                }
+                consume(ok, entry);
+            }
+        }
+    } else {
+        const int2 run = P.qrun[q];
+        const float4 w = P.tri ? P.qwin[q] : make_float4(0, 0, 0, 0);
+        float la = 0, lb = 0, lc = 0;
+        if (P.tri && !P.coarse) {   // epipolar line l = x1' F12 (src/CameraModels/Pinhole.cpp:115-117), no FMA contraction
+            la = __fadd_rn(__fadd_rn(__fmul_rn(w.x, P.F[0]), __fmul_rn(w.y, P.F[3])), P.F[6]);
+            lb = __fadd_rn(__fadd_rn(__fmul_rn(w.x, P.F[1]), __fmul_rn(w.y, P.F[4])), P.F[7]);
+            lc = __fadd_rn(__fadd_rn(__fmul_rn(w.x, P.F[2]), __fmul_rn(w.y, P.F[5])), P.F[8]);
+        }
+        for (int base = run.x; base < run.y; base += 32) {
+            const int e = base + lane;
+            bool ok = false; uint32_t entry = 0;
+            if (e < run.y) {
+                const int idx = P.bowIdx[e];
+                ok = !P.elig || P.elig[idx] != 0;
+                if (ok) {
+                    const int d = hamming8(qd, drows[2 * idx], drows[2 * idx + 1]);
+                    ++nEval;
+                    const float4 k = T.kp4[idx];
+                    const int oct = __float_as_int(k.w);
+                    if (P.tri) {
+                        // SearchForTriangulation (:1017-1034, :1072): dist <= TH_LOW, epipole distance, epipolar constraint.
+                        // (the running "dist > bestDist" test is applied by the LAST_MIN reduction)
+                        ok = d <= ORBM_TH_LOW;
+                        if (ok) {
+                            const float dx = __fsub_rn(P.ep0, k.x), dy = __fsub_rn(P.ep1, k.y);
+                            ok = !(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, P.scale2[oct]));
+                        }
+                        if (ok && !P.coarse) {
+                            const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, k.x), __fmul_rn(lb, k.y)), lc);
+                            const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+                            if (den == 0.f) ok = false;
+                            else ok = (double)__fdiv_rn(__fmul_rn(num, num), den) < 3.84 * (double)P.sigma2[oct];
+                        }
+                    }
+                    entry = pack_entry(d, oct, idx);
+                }
+            }
+            consume(ok, entry);
+        }
+    }
+}
+
+struct Best { uint32_t k1, k2; uint32_t e1, e2; };   // lane-private best / second-best keys (dist<<20|pos) and entries
+
+// state tests of one candidate at resolve time
+__device__ __forceinline__ bool blocked(const SearchParams& P, const uint8_t* occS, const uint16_t* mdS, uint32_t entry) {
+    const int idx = entry & 0x7ffff;
+    if (P.state == 1) return occS[idx] != 0;
+    if (P.state == 2) return mdS[idx] <= (entry >> 23);           // vMatchedDistance[i2] <= dist (:687)
+    return false;
+}
+
+__device__ __forceinline__ void best_update(Best& b, uint32_t key, uint32_t entry) {
+    if (key < b.k1) { b.k2 = b.k1; b.e2 = b.e1; b.k1 = key; b.e1 = entry; }
+    else if (key < b.k2) { b.k2 = key; b.e2 = entry; }
+}
+
+// One CTA per search (state != 0) or per slice of queries (state == 0).
+// dynamic smem: occupancy bytes [n] (state 1) | matched distance u16 [n] + match21 int [n] (state 2); slabs.
+__global__ void __launch_bounds__(kSearchThreads) k_search(const SearchParams P) {
+    extern __shared__ __align__(16) uint8_t dyn[];
+    __shared__ volatile int token;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int n = P.tgt.n;
+    uint32_t* slab = reinterpret_cast<uint32_t*>(dyn) + (size_t)wid * kSlab;
+    uint8_t* stateBase = dyn + (size_t)kSearchWarps * kSlab * 4;
+    uint8_t* occS = stateBase;                                        // state 1
+    uint16_t* mdS = reinterpret_cast<uint16_t*>(stateBase);           // state 2
+    int* m21S = reinterpret_cast<int*>(stateBase + (((size_t)n * 2 + 15) & ~(size_t)15));
+    if (P.state == 1) for (int i = tid; i < n; i += kSearchThreads) occS[i] = P.occ[i];
+    if (P.state == 2) for (int i = tid; i < n; i += kSearchThreads) { mdS[i] = 0xffff; m21S[i] = -1; }
+    if (tid == 0) token = 0;
+    __syncthreads();
+
+    const int qStride = (P.state != 0) ? kSearchWarps : kSearchWarps * gridDim.x;
+    const int qFirst = (P.state != 0) ? wid : blockIdx.x * kSearchWarps + wid;
+    unsigned long long nEval = 0;
+    const bool lastMin = P.rule == RULE_LAST_MIN;
+
+    for (int q = qFirst; q < P.nq; q += qStride) {
+        uint32_t qd[8];
+        {
+            const uint4 a = reinterpret_cast<const uint4*>(P.qdesc)[2 * q], b = reinterpret_cast<const uint4*>(P.qdesc)[2 * q + 1];
+            qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
+        }
+        // ---- phase A: gather + distances into the slab (order preserved by ballot compaction) ----
+        int count = 0;
+        walk_candidates(P, q, qd, nEval, [&](bool ok, uint32_t entry) {
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const int pos = count + __popc(m & ((1u << lane) - 1));
+                if (pos < kSlab) slab[pos] = entry;
+            }
+            count += __popc(m);
+        });
+        __syncwarp();
+        // ---- phase B: resolve in query order ----
+        if (P.state != 0) {
+            if (lane == 0) while (token != q) { }
+            __syncwarp();
+            __threadfence_block();
+        }
+        Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = 0;
+        if (count <= kSlab) {
+            for (int p = lane; p < count; p += 32) {
+                const uint32_t e = slab[p];
+                if (blocked(P, occS, mdS, e)) continue;
+                const uint32_t key = ((e >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
+                best_update(b, key, e);
+            }
+        } else {
+            // rare: more candidates than the slab holds -> redo the walk while holding the token
+            int pos0 = 0;
+            unsigned long long dummy = 0;
+            walk_candidates(P, q, qd, dummy, [&](bool ok, uint32_t entry) {
+                const unsigned m = __ballot_sync(0xffffffffu, ok);
+                if (ok && !blocked(P, occS, mdS, entry)) {
+                    const int p = pos0 + __popc(m & ((1u << lane) - 1));
+                    const uint32_t key = ((entry >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
+                    best_update(b, key, entry);
+                }
+                pos0 += __popc(m);
+            });
+        }
+        // warp merge: best = min k1; second = min over {k2 of the winner lane, k1 of the others}
+        const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
+        const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);
+        const uint32_t cand2 = win ? b.k2 : b.k1;
+        const uint32_t m2 = __reduce_min_sync(0xffffffffu, cand2);
+        const unsigned wmask = __ballot_sync(0xffffffffu, win);
+        const int wl = wmask ? __ffs(wmask) - 1 : 0;
+        const uint32_t e1 = __shfl_sync(0xffffffffu, b.e1, wl);
+        const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
+        const int sl = smask ? __ffs(smask) - 1 : 0;
+        const uint32_t e2src = (cand2 == b.k1 && !win) ? b.e1 : b.e2;
+        const uint32_t e2 = __shfl_sync(0xffffffffu, e2src, sl);
+
+        if (lane == 0) {
+            const bool has1 = m1 != 0xffffffffu, has2 = m2 != 0xffffffffu;
+            const int bestDist = has1 ? (int)(e1 >> 23) : 256;
+            const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
+            const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
+            const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
+            const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
+            bool accept = false;
+            switch (P.rule) {
+                case RULE_LOCAL_MAP:
+                    accept = has1 && bestDist <= ORBM_TH_HIGH &&
+                             !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
+                    break;
+                case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
+                case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+                case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+                case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
+                case RULE_LAST_MIN: accept = has1; break;
+                default: accept = false; break;
+            }
+            int bin = -1;
+            if (accept) {
+                if (P.state == 1) occS[bestIdx] = 1;
+                if (P.state == 2) {
+                    const int prev = m21S[bestIdx];
+                    if (prev >= 0) P.qResult[prev] = -1;          // the earlier, worse match loses the keypoint (:706-710)
+                    m21S[bestIdx] = q;
+                    mdS[bestIdx] = (uint16_t)bestDist;
+                }
+                if (P.checkOri) {
+                    float rot = __fsub_rn(P.qangle[q], P.tgt.kp4[bestIdx].z);
+                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                    bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
+                    if (bin == ORBM_HISTO_LENGTH) bin = 0;
+                }
+            }
+            P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
+            P.qDist[q] = bestDist;
+            P.qBin[q] = bin;
+            if (P.state != 0) { __threadfence_block(); token = q + 1; }
+        }
+        __syncwarp();
+    }
+    // evaluation count (reporting only)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nEval += __shfl_xor_sync(0xffffffffu, nEval, o);
+    if (lane == 0 && nEval) atomicAdd(P.evals, nEval);
+    if (P.state == 1) {
+        __syncthreads();
+        for (int i = tid; i < n; i += kSearchThreads) P.occ[i] = occS[i];
+    }
+}
+
+// rotation-consistency epilogue (e.g. src/ORBmatcher.cc:1862-1884): histogram of accept events, three maxima, drop the rest
+__global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
+    __shared__ int hist[ORBM_HISTO_LENGTH];
+    __shared__ int keep[3];
+    const int tid = threadIdx.x;
+    if (tid < ORBM_HISTO_LENGTH) hist[tid] = 0;
+    __syncthreads();
+    for (int q = tid; q < nq; q += 256) { const int b = qBin[q]; if (b >= 0) atomicAdd(&hist[b], 1); }
+    __syncthreads();
+    if (tid == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+        keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+    }
+    __syncthreads();
+    for (int q = tid; q < nq; q += 256) {
+        const int b = qBin[q];
+        if (b >= 0 && b != keep[0] && b != keep[1] && b != keep[2]) qResult[q] = -1;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// brute-force k-NN.  grid (query blocks, db chunks); block kKnnThreads; thread = query.
+constexpr int kKnnThreads = 256, kKnnTileRows = 128, kKnnMaxK = 16;
+
+// 256-bit Hamming distance with a carry-save adder tree: 8 xor words -> ones/twos/fours/eights -> 4 popc
+__device__ __forceinline__ void csa(uint32_t& h, uint32_t& l, uint32_t a, uint32_t b, uint32_t c) {
+    l = a ^ b ^ c;                      // LOP3 0x96
+    h = (a & b) | (c & (a | b));        // LOP3 0xe8 (majority)
+}
+__device__ __forceinline__ int hamming_csa(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
+    const uint32_t x0 = q[0] ^ a.x, x1 = q[1] ^ a.y, x2 = q[2] ^ a.z, x3 = q[3] ^ a.w;
+    const uint32_t x4 = q[4] ^ b.x, x5 = q[5] ^ b.y, x6 = q[6] ^ b.z, x7 = q[7] ^ b.w;
+    uint32_t t0, o0, t1, o1, t2, o2, f0, tw, f1, tw2, ei, fo;
+    csa(t0, o0, x0, x1, x2);
+    csa(t1, o1, x3, x4, x5);
+    csa(t2, o2, o0, o1, x6);            // ones so far: o2 (+ x7)
+    const uint32_t ones = o2 ^ x7, c7 = o2 & x7;     // half adder
+    csa(f0, tw, t0, t1, t2);
+    tw2 = tw ^ c7; f1 = tw & c7;        // half adder on the twos
+    ei = f0 & f1; fo = f0 ^ f1;         // fours: f0 + f1 -> fo (4s) + ei (8s)
+    return __popc(ones) + 2 * __popc(tw2) + 4 * __popc(fo) + 8 * __popc(ei);
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// dist/idx partial lists: part[(chunk * nq + q) * k + t] = key (dist << 32 | global row)
+__global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict__ qdesc, int nq, const uint32_t* __restrict__ db,
+                                                     long long ndb, long long rowOffset, int rowsPerChunk, int k,
+                                                     unsigned long long* __restrict__ part) {
+    __shared__ __align__(128) uint4 tile[2][kKnnTileRows * 2];
+    __shared__ __align__(8) unsigned long long mbar[2];
+    const int tid = threadIdx.x;
+    const int q = blockIdx.x * kKnnThreads + tid;
+    const long long r0 = (long long)blockIdx.y * rowsPerChunk;
+    const long long r1 = min(ndb, r0 + rowsPerChunk);
+    const int nrows = (int)max(0LL, r1 - r0);
+    uint32_t qd[8];
+    {
+        const int qq = min(q, nq - 1);
+        const uint4 a = reinterpret_cast<const uint4*>(qdesc)[2 * qq], b = reinterpret_cast<const uint4*>(qdesc)[2 * qq + 1];
+        qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
+    }
+    uint32_t best[kKnnMaxK];     // keys dist << 23 | chunk-local row, ascending
+#pragma unroll
+    for (int t = 0; t < kKnnMaxK; ++t) best[t] = 0xffffffffu;
+    uint32_t worst = 0xffffffffu;
+
+    const int ntiles = (nrows + kKnnTileRows - 1) / kKnnTileRows;
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar[s])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int t) {     // one elected thread: TMA bulk copy of a tile of rows into stage t & 1
+        const int s = t & 1;
+        const int rows = min(kKnnTileRows, nrows - t * kKnnTileRows);
+        const uint32_t bytes = (uint32_t)rows * 32u;
+        const uint32_t bar = smem_u32(&mbar[s]);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(&tile[s][0])), "l"(db + (size_t)(r0 + (long long)t * kKnnTileRows) * 8), "r"(bytes), "r"(bar)
+                     : "memory");
+    };
+    if (tid == 0 && ntiles > 0) issue(0);
+    for (int t = 0; t < ntiles; ++t) {
+        const int s = t & 1;
+        if (tid == 0 && t + 1 < ntiles) issue(t + 1);
+        {   // wait for stage s (phase parity = (t >> 1) & 1)
+            const uint32_t bar = smem_u32(&mbar[s]);
+            const uint32_t parity = (t >> 1) & 1;
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        }
+        const int rows = min(kKnnTileRows, nrows - t * kKnnTileRows);
+        const uint32_t rowBase = (uint32_t)(t * kKnnTileRows);
+#pragma unroll 4
+        for (int r = 0; r < rows; ++r) {
+            const int d = hamming_csa(qd, tile[s][2 * r], tile[s][2 * r + 1]);
+            const uint32_t key = ((uint32_t)d << 23) | (rowBase + (uint32_t)r);
+            if (key < worst) {
+                // sorted insertion into the k best (k <= kKnnMaxK): bubble the new key through, drop the largest
+                uint32_t carry = key;
+#pragma unroll
+                for (int u = 0; u < kKnnMaxK; ++u) {
+                    if (u < k) { const uint32_t lo = min(best[u], carry), hi = max(best[u], carry); best[u] = lo; carry = hi; worst = lo; }
+                }
+            }
+        }
+        __syncthreads();      // everyone is done with stage s before it is refilled (issue(t+2) happens next iteration)
+    }
+    if (q < nq) {
+        unsigned long long* out = part + ((size_t)blockIdx.y * nq + q) * k;
+#pragma unroll
+        for (int u = 0; u < kKnnMaxK; ++u) {
+            if (u < k) {
+                const uint32_t key = best[u];
+                out[u] = key == 0xffffffffu ? 0xffffffffffffffffull
+                                            : (((unsigned long long)(key >> 23)) << 32) | (unsigned long long)(rowOffset + r0 + (key & 0x7fffffu));
+            }
+        }
+    }
+}
+
+// merge the per-chunk lists of one query: k smallest (dist, row) keys.  One warp per query.
+__global__ void __launch_bounds__(256) k_knn_merge(const unsigned long long* __restrict__ part, int nchunks, int nq, int k,
+                                                   uint16_t* __restrict__ dist, int32_t* __restrict__ idx) {
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const int total = nchunks * k;
+    unsigned long long prev = 0; bool first = true;
+    for (int t = 0; t < k; ++t) {
+        // smallest key strictly greater than the previous pick (keys are unique: distinct rows)
+        unsigned long long m = 0xffffffffffffffffull;
+        for (int e = lane; e < total; e += 32) {
+            const int c = e / k, u = e - c * k;
+            const unsigned long long key = part[((size_t)c * nq + q) * k + u];
+            if ((first || key > prev) && key < m) m = key;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(0xffffffffu, m, o); m = x < m ? x : m; }
+        if (lane == 0) {
+            if (m == 0xffffffffffffffffull) { dist[(size_t)q * k + t] = 65535; idx[(size_t)q * k + t] = -1; }
+            else { dist[(size_t)q * k + t] = (uint16_t)(m >> 32); idx[(size_t)q * k + t] = (int32_t)(m & 0xffffffffull); }
+        }
+        prev = m; first = false;
+        if (m == 0xffffffffffffffffull) { for (int u = t + 1; u < k && lane == 0; ++u) { dist[(size_t)q * k + u] = 65535; idx[(size_t)q * k + u] = -1; } break; }
+    }
+}
+
+// MapPoint::ComputeDistinctiveDescriptors selection (src/MapPoint.cc:366-396): one warp per map point (N <= 32 rows
+// handled lane = row; larger N loops).  median = sorted row distances [0.5*(N-1)] (self distance 0 included).
+__global__ void __launch_bounds__(256) k_distinctive(const uint32_t* __restrict__ desc, const int* __restrict__ off, int npoints,
+                                                     int* __restrict__ best) {
+    const int p = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (p >= npoints) return;
+    const int b = off[p], N = off[p + 1] - b;
+    if (N <= 0) { if (lane == 0) best[p] = -1; return; }
+    const int mpos = (int)(0.5 * (N - 1));
+    const uint4* rows = reinterpret_cast<const uint4*>(desc);
+    unsigned bestKey = 0xffffffffu;       // median << 16 | row
+    for (int i = lane; i < N; i += 32) {
+        uint32_t qd[8];
+        const uint4 a = rows[2 * (b + i)], c = rows[2 * (b + i) + 1];
+        qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = c.x; qd[5] = c.y; qd[6] = c.z; qd[7] = c.w;
+        // the median = value v with  #(d < v) <= mpos < #(d <= v): count-based selection over the 257 possible values
+        int lo = 0, hi = 256;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int le = 0;
+            for (int j = 0; j < N; ++j) le += hamming8(qd, rows[2 * (b + j)], rows[2 * (b + j) + 1]) <= mid;
+            if (le > mpos) hi = mid; else lo = mid + 1;
+        }
+        const unsigned key = ((unsigned)lo << 16) | (unsigned)i;
+        bestKey = min(bestKey, key);
+    }
+    bestKey = __reduce_min_sync(0xffffffffu, bestKey);
+    if (lane == 0) best[p] = (int)(bestKey & 0xffff);
+}
+
+}  // namespace orbm

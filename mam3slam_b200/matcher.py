@@ -1,0 +1,286 @@
+"""Host-side mirror of the reference's ORBmatcher (include/ORBmatcher.h:36-103) over the C ABI (include/orbm.h).
+
+The reference's methods take Frame / KeyFrame / MapPoint pointer graphs; here a `MatchFrame` is the device mirror of
+what the searches read from a Frame or KeyFrame (mvKeysUn, mDescriptors, image bounds, the 64x48 grid) and every
+MapPoint-dependent predicate arrives as a per-element array, exactly as the C++ adapter passes it.  Method names follow
+the reference; all Hamming work runs in the CUDA library (no CPU fallback).
+"""
+import ctypes as C
+import numpy as np
+
+from ._lib import lib, check_m, OrbmFrameView, OrbmFeatVec
+from .extractor import KEYPOINT_DTYPE
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _c(a, dt):
+    return np.ascontiguousarray(a, dt)
+
+
+class MatchFrame:
+    """Device mirror of a Frame / KeyFrame for the searches (orbm_frame)."""
+
+    def __init__(self, matcher, kps, desc, bounds, on_device=False, n=None):
+        self._m = matcher
+        self._L = matcher._L
+        self._f = C.c_void_p()
+        self._keep = None
+        view = self._view(kps, desc, bounds, on_device, n)
+        check_m(self._L.orbm_frame_create(matcher._h, C.byref(view), C.byref(self._f)), matcher._h, "orbm_frame_create")
+
+    def _view(self, kps, desc, bounds, on_device, n):
+        b = [float(x) for x in bounds]
+        if on_device:
+            self.n = int(n)
+            return OrbmFrameView(self.n, C.c_void_p(kps), C.c_void_p(desc), b[0], b[1], b[2], b[3], 1)
+        kps = np.ascontiguousarray(kps)
+        assert kps.dtype.itemsize == 28, "cv::KeyPoint layout expected"
+        desc = _c(desc, np.uint8)
+        self.n = len(kps)
+        self._keep = (kps, desc)
+        return OrbmFrameView(self.n, kps.ctypes.data, desc.ctypes.data, b[0], b[1], b[2], b[3], 0)
+
+    def update(self, kps, desc, bounds, on_device=False, n=None):
+        view = self._view(kps, desc, bounds, on_device, n)
+        check_m(self._L.orbm_frame_update(self._m._h, self._f, C.byref(view)), self._m._h, "orbm_frame_update")
+
+    def grid(self):
+        """(off[64*48+1], idx[...]) — Frame::AssignFeaturesToGrid as CSR, cell = ix*48+iy."""
+        off = np.empty(64 * 48 + 1, np.int32)
+        idx = np.empty(max(self.n, 1), np.int32)
+        check_m(self._L.orbm_frame_grid(self._m._h, self._f, _p(off), _p(idx)), self._m._h, "orbm_frame_grid")
+        return off, idx[:off[-1]].copy()
+
+    def GetFeaturesInArea(self, x, y, r, minLevel=-1, maxLevel=-1):
+        out = np.empty(max(self.n, 1), np.int32)
+        n = C.c_int(0)
+        check_m(self._L.orbm_features_in_area(self._m._h, self._f, float(x), float(y), float(r), int(minLevel), int(maxLevel),
+                                              _p(out), len(out), C.byref(n)), self._m._h, "orbm_features_in_area")
+        return out[:n.value].copy()
+
+    def close(self):
+        if getattr(self, "_f", None) and self._m._h:
+            self._L.orbm_frame_destroy(self._m._h, self._f)
+            self._f = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _fv(fv, keep):
+    node, off, idx = (_c(a, np.int32) for a in fv)
+    keep.extend([node, off, idx])
+    return OrbmFeatVec(len(node), node.ctypes.data, off.ctypes.data, idx.ctypes.data)
+
+
+class KnnDatabase:
+    """Descriptor rows resident in HBM for brute-force k-NN (orbm_db); row_offset = global id of the first row."""
+
+    def __init__(self, matcher, rows, row_offset=0, device_ptr=None, n=None):
+        self._m = matcher
+        self._db = C.c_void_p()
+        if device_ptr is not None:
+            self.n = int(n)
+            check_m(matcher._L.orbm_db_create(matcher._h, C.c_void_p(device_ptr), self.n, 1, int(row_offset), C.byref(self._db)),
+                    matcher._h, "orbm_db_create")
+        else:
+            rows = _c(rows, np.uint8)
+            self.n = len(rows)
+            check_m(matcher._L.orbm_db_create(matcher._h, _p(rows), self.n, 0, int(row_offset), C.byref(self._db)),
+                    matcher._h, "orbm_db_create")
+
+    def close(self):
+        if getattr(self, "_db", None) and self._m._h:
+            self._m._L.orbm_db_destroy(self._m._h, self._db)
+            self._db = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class ORBmatcher:
+    TH_HIGH = 100
+    TH_LOW = 50
+    HISTO_LENGTH = 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self._L = lib()
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self._h = C.c_void_p()
+        check_m(self._L.orbm_create(int(device), C.byref(self._h)), None, "orbm_create")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.orbm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def launch_count(self):
+        return int(self._L.orbm_launch_count(self._h))
+
+    def last_evaluations(self):
+        return int(self._L.orbm_last_evaluations(self._h))
+
+    def stream(self):
+        return self._L.orbm_stream(self._h)
+
+    # ---- M0 ----
+    @staticmethod
+    def DescriptorDistance(a, b):
+        a, b = _c(a, np.uint8), _c(b, np.uint8)
+        return int(lib().orbm_distance(_p(a), _p(b)))
+
+    def frame(self, kps, desc, bounds, on_device=False, n=None):
+        return MatchFrame(self, kps, desc, bounds, on_device, n)
+
+    # ---- M1: SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) ----
+    def SearchByProjection_LocalMap(self, F, occupied, scale_factors, valid, proj_x, proj_y, level, view_cos, qdesc, th=1.0):
+        occ = _c(occupied, np.uint8).copy()
+        sf = _c(scale_factors, np.float32)
+        valid, px, py = _c(valid, np.uint8), _c(proj_x, np.float32), _c(proj_y, np.float32)
+        level, vc, qd = _c(level, np.int32), _c(view_cos, np.float32), _c(qdesc, np.uint8)
+        km = np.full(F.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_local_map(self._h, F._f, _p(occ), _p(sf), len(sf), len(valid), _p(valid), _p(px), _p(py),
+                                              _p(level), _p(vc), _p(qd), float(th), self.mfNNratio, _p(km), C.byref(nm)),
+                self._h, "orbm_search_local_map")
+        return nm.value, km, occ
+
+    # ---- M2 / M3: SearchByProjection(Frame& Cur, Frame& Last, th, bMono) / (Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) ----
+    def SearchByProjection_Frame(self, F, occupied, scale_factors, valid, u, v, octave, qangle, qdesc, th, ORBdist=100):
+        occ = _c(occupied, np.uint8).copy()
+        sf = _c(scale_factors, np.float32)
+        valid, u, v = _c(valid, np.uint8), _c(u, np.float32), _c(v, np.float32)
+        octave, qa, qd = _c(octave, np.int32), _c(qangle, np.float32), _c(qdesc, np.uint8)
+        km = np.full(F.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_frame(self._h, F._f, _p(occ), _p(sf), len(sf), len(valid), _p(valid), _p(u), _p(v), _p(octave),
+                                          _p(qa), _p(qd), float(th), int(ORBdist), int(self.mbCheckOrientation), _p(km),
+                                          C.byref(nm)), self._h, "orbm_search_frame")
+        return nm.value, km
+
+    # ---- M7: SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) ----
+    def SearchByProjection_Sim3(self, KF, matched, scale_factors, valid, u, v, level, qdesc, th, ratioHamming=1.0):
+        m = _c(matched, np.uint8).copy()
+        sf = _c(scale_factors, np.float32)
+        valid, u, v = _c(valid, np.uint8), _c(u, np.float32), _c(v, np.float32)
+        level, qd = _c(level, np.int32), _c(qdesc, np.uint8)
+        km = np.full(KF.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_sim3(self._h, KF._f, _p(m), _p(sf), len(sf), len(valid), _p(valid), _p(u), _p(v), _p(level),
+                                         _p(qd), int(th), float(ratioHamming), _p(km), C.byref(nm)), self._h, "orbm_search_sim3")
+        return nm.value, km
+
+    # ---- M5: SearchForInitialization ----
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        pm = _c(vbPrevMatched, np.float32).copy()
+        m12 = np.full(F1.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_initialization(self._h, F1._f, F2._f, _p(pm), int(windowSize), self.mfNNratio,
+                                                   int(self.mbCheckOrientation), _p(m12), C.byref(nm)), self._h,
+                "orbm_search_initialization")
+        return nm.value, m12, pm
+
+    # ---- M4: SearchByBoW ----
+    def SearchByBoW_KF_Frame(self, KF, fvKF, elig1, F, fvF):
+        keep = []
+        a, b = _fv(fvKF, keep), _fv(fvF, keep)
+        e1 = _c(elig1, np.uint8)
+        out = np.full(F.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_bow_kf_frame(self._h, KF._f, C.byref(a), _p(e1), F._f, C.byref(b), self.mfNNratio,
+                                                 int(self.mbCheckOrientation), _p(out), C.byref(nm)), self._h,
+                "orbm_search_bow_kf_frame")
+        return nm.value, out
+
+    def SearchByBoW_KF_KF(self, KF1, fv1, elig1, KF2, fv2, elig2):
+        keep = []
+        a, b = _fv(fv1, keep), _fv(fv2, keep)
+        e1, e2 = _c(elig1, np.uint8), _c(elig2, np.uint8)
+        out = np.full(KF1.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_bow_kf_kf(self._h, KF1._f, C.byref(a), _p(e1), KF2._f, C.byref(b), _p(e2), self.mfNNratio,
+                                              int(self.mbCheckOrientation), _p(out), C.byref(nm)), self._h,
+                "orbm_search_bow_kf_kf")
+        return nm.value, out
+
+    # ---- M6: SearchForTriangulation ----
+    def SearchForTriangulation(self, KF1, fv1, free1, KF2, fv2, free2, ep, scale_factors2, F12, sigma2, bCoarse=False):
+        keep = []
+        a, b = _fv(fv1, keep), _fv(fv2, keep)
+        f1, f2 = _c(free1, np.uint8), _c(free2, np.uint8)
+        ep, sf = _c(ep, np.float32), _c(scale_factors2, np.float32)
+        F, s2 = _c(F12, np.float32).reshape(9), _c(sigma2, np.float32)
+        out = np.full(KF1.n, -1, np.int32)
+        nm = C.c_int(0)
+        check_m(self._L.orbm_search_triangulation(self._h, KF1._f, C.byref(a), _p(f1), KF2._f, C.byref(b), _p(f2), _p(ep), _p(sf),
+                                                  _p(F), _p(s2), len(sf), int(bCoarse), int(self.mbCheckOrientation), _p(out),
+                                                  C.byref(nm)), self._h, "orbm_search_triangulation")
+        return nm.value, out
+
+    # ---- M9: candidate part of Fuse ----
+    def Fuse_candidates(self, KF, scale_factors, inv_sigma2, valid, u, v, level, qdesc, th, chi2_gate=True):
+        sf, is2 = _c(scale_factors, np.float32), _c(inv_sigma2, np.float32)
+        valid, u, v = _c(valid, np.uint8), _c(u, np.float32), _c(v, np.float32)
+        level, qd = _c(level, np.int32), _c(qdesc, np.uint8)
+        bi = np.empty(len(valid), np.int32)
+        bd = np.empty(len(valid), np.int32)
+        check_m(self._L.orbm_fuse_candidates(self._h, KF._f, _p(sf), _p(is2), len(sf), len(valid), _p(valid), _p(u), _p(v),
+                                             _p(level), _p(qd), float(th), int(chi2_gate), _p(bi), _p(bd)), self._h,
+                "orbm_fuse_candidates")
+        return bi, bd
+
+    # ---- M11: brute-force k-NN ----
+    def database(self, rows, row_offset=0):
+        return KnnDatabase(self, rows, row_offset)
+
+    def knn(self, q, db, k):
+        """(dist[nq,k] uint16, idx[nq,k] int32); `db` = KnnDatabase or an array of rows (uploaded for this call)."""
+        own = None
+        if not isinstance(db, KnnDatabase):
+            own = db = KnnDatabase(self, db)
+        q = _c(q, np.uint8)
+        dist = np.empty((len(q), k), np.uint16)
+        idx = np.empty((len(q), k), np.int32)
+        check_m(self._L.orbm_knn(self._h, db._db, _p(q), len(q), int(k), _p(dist), _p(idx)), self._h, "orbm_knn")
+        if own is not None:
+            own.close()
+        return dist, idx
+
+    def knn_device(self, db, d_q, nq, k, d_dist, d_idx, stream=None):
+        check_m(self._L.orbm_knn_device(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist), C.c_void_p(d_idx),
+                                        C.c_void_p(stream or 0)), self._h, "orbm_knn_device")
+
+    @staticmethod
+    def knn_merge(dist, idx):
+        """dist/idx: [nshards, nq, k] per-shard lists with global row ids -> merged [nq, k]."""
+        dist, idx = _c(dist, np.uint16), _c(idx, np.int32)
+        s, nq, k = dist.shape
+        od = np.empty((nq, k), np.uint16)
+        oi = np.empty((nq, k), np.int32)
+        st = lib().orbm_knn_merge(_p(dist), _p(idx), s, nq, k, _p(od), _p(oi))
+        check_m(st, None, "orbm_knn_merge")
+        return od, oi
+
+    # ---- 8(f): MapPoint::ComputeDistinctiveDescriptors selection ----
+    def ComputeDistinctiveDescriptors(self, desc, off):
+        desc, off = _c(desc, np.uint8), _c(off, np.int32)
+        best = np.empty(len(off) - 1, np.int32)
+        check_m(self._L.orbm_distinctive_descriptors(self._h, _p(desc), _p(off), len(off) - 1, _p(best)), self._h,
+                "orbm_distinctive_descriptors")
+        return best

@@ -133,3 +133,94 @@ int orc_distribute(int nfeatures_unused, const int* keys, int n, int minX, int m
 }
 
 }  // extern "C"
+
+// ---- matcher ---------------------------------------------------------------------------------------------------------
+namespace {
+FrameView makeView(int n, const void* kps, const uint8_t* desc, const float* bounds) {
+    FrameView f;
+    f.build(n, (const KP*)kps, desc, bounds[0], bounds[1], bounds[2], bounds[3]);
+    return f;
+}
+}  // namespace
+
+extern "C" {
+
+int orc_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptor_distance(a, b); }
+
+// grid as CSR (cell = ix*48+iy): off has 64*48+1 entries
+void orc_grid_build(int n, const void* kps, const float* bounds, int* off, int* idx) {
+    FrameView f = makeView(n, kps, nullptr, bounds);
+    int o = 0;
+    for (int c = 0; c < GRID_COLS * GRID_ROWS; ++c) { off[c] = o; for (int i : f.grid[c]) idx[o++] = i; }
+    off[GRID_COLS * GRID_ROWS] = o;
+}
+int orc_features_in_area(int n, const void* kps, const float* bounds, float x, float y, float r, int minLevel, int maxLevel, int* out) {
+    FrameView f = makeView(n, kps, nullptr, bounds);
+    std::vector<int> v;
+    f.features_in_area(x, y, r, minLevel, maxLevel, v);
+    for (size_t i = 0; i < v.size(); ++i) out[i] = v[i];
+    return (int)v.size();
+}
+void orc_three_maxima(const int* sizes, int L, int* ind) { ind[0] = ind[1] = ind[2] = -1; three_maxima(sizes, L, ind[0], ind[1], ind[2]); }
+int orc_rot_bin(float a1, float a2) { return rot_bin(a1, a2); }
+
+int orc_search_local_map(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* occupied,
+                         const float* scaleFactors, int nq, const uint8_t* valid, const float* projX, const float* projY,
+                         const int* level, const float* viewCos, const uint8_t* qdesc, float th, float nnratio, int* kpMatch) {
+    FrameView f = makeView(n, kps, desc, bounds);
+    return search_local_map(f, occupied, scaleFactors, nq, valid, projX, projY, level, viewCos, qdesc, th, nnratio, kpMatch);
+}
+int orc_search_frame(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* occupied,
+                     const float* scaleFactors, int nq, const uint8_t* valid, const float* u, const float* v,
+                     const int* octave, const float* qangle, const uint8_t* qdesc, float th, int thDist, int checkOri, int* kpMatch) {
+    FrameView f = makeView(n, kps, desc, bounds);
+    return search_frame(f, occupied, scaleFactors, nq, valid, u, v, octave, qangle, qdesc, th, thDist, checkOri != 0, kpMatch);
+}
+int orc_search_sim3(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* matched,
+                    const float* scaleFactors, int nq, const uint8_t* valid, const float* u, const float* v,
+                    const int* level, const uint8_t* qdesc, int th, float ratioHamming, int* kpMatch) {
+    FrameView f = makeView(n, kps, desc, bounds);
+    return search_sim3(f, matched, scaleFactors, nq, valid, u, v, level, qdesc, th, ratioHamming, kpMatch);
+}
+int orc_search_initialization(int n1, const void* kps1, const uint8_t* desc1, int n2, const void* kps2, const uint8_t* desc2,
+                              const float* bounds, float* prevMatched, int windowSize, float nnratio, int checkOri, int* matches12) {
+    FrameView f1 = makeView(n1, kps1, desc1, bounds), f2 = makeView(n2, kps2, desc2, bounds);
+    return search_initialization(f1, f2, prevMatched, windowSize, nnratio, checkOri != 0, matches12);
+}
+int orc_search_bow_kf_frame(int n1, const void* kps1, const uint8_t* desc1, int nn1, const int* node1, const int* off1, const int* idx1,
+                            const uint8_t* elig1, int n2, const void* kps2, const uint8_t* desc2, int nn2, const int* node2,
+                            const int* off2, const int* idx2, float nnratio, int checkOri, int* matchF) {
+    const float b[4] = {0, 0, 1, 1};
+    FrameView f1 = makeView(n1, kps1, desc1, b), f2 = makeView(n2, kps2, desc2, b);
+    FeatVec a{nn1, node1, off1, idx1}, c{nn2, node2, off2, idx2};
+    return search_bow_kf_frame(f1, a, elig1, f2, c, nnratio, checkOri != 0, matchF);
+}
+int orc_search_bow_kf_kf(int n1, const void* kps1, const uint8_t* desc1, int nn1, const int* node1, const int* off1, const int* idx1,
+                         const uint8_t* elig1, int n2, const void* kps2, const uint8_t* desc2, int nn2, const int* node2,
+                         const int* off2, const int* idx2, const uint8_t* elig2, float nnratio, int checkOri, int* matches12) {
+    const float b[4] = {0, 0, 1, 1};
+    FrameView f1 = makeView(n1, kps1, desc1, b), f2 = makeView(n2, kps2, desc2, b);
+    FeatVec a{nn1, node1, off1, idx1}, c{nn2, node2, off2, idx2};
+    return search_bow_kf_kf(f1, a, elig1, f2, c, elig2, nnratio, checkOri != 0, matches12);
+}
+int orc_search_triangulation(int n1, const void* kps1, const uint8_t* desc1, int nn1, const int* node1, const int* off1, const int* idx1,
+                             const uint8_t* free1, int n2, const void* kps2, const uint8_t* desc2, int nn2, const int* node2,
+                             const int* off2, const int* idx2, const uint8_t* free2, const float* ep, const float* scaleFactors2,
+                             const float* F12, const float* sigma2, int coarse, int checkOri, int* matches12) {
+    const float b[4] = {0, 0, 1, 1};
+    FrameView f1 = makeView(n1, kps1, desc1, b), f2 = makeView(n2, kps2, desc2, b);
+    FeatVec a{nn1, node1, off1, idx1}, c{nn2, node2, off2, idx2};
+    return search_triangulation(f1, a, free1, f2, c, free2, ep, scaleFactors2, F12, sigma2, coarse != 0, checkOri != 0, matches12);
+}
+void orc_fuse_candidates(int n, const void* kps, const uint8_t* desc, const float* bounds, const float* scaleFactors,
+                         const float* invSigma2, int nq, const uint8_t* valid, const float* u, const float* v, const int* level,
+                         const uint8_t* qdesc, float th, int chi2Gate, int* bestIdx, int* bestDist) {
+    FrameView f = makeView(n, kps, desc, bounds);
+    fuse_candidates(f, scaleFactors, invSigma2, nq, valid, u, v, level, qdesc, th, chi2Gate != 0, bestIdx, bestDist);
+}
+void orc_knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads) {
+    knn(q, nq, db, ndb, k, dist, idx, threads);
+}
+int orc_distinctive_descriptor(const uint8_t* desc, int n) { return distinctive_descriptor(desc, n); }
+
+}  // extern "C"

@@ -1,5 +1,101 @@
-// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_primitives.h).  CPU restatement of the reference's ORBmatcher
-// searches over plain arrays (src/ORBmatcher.cc).  Filled in by orc_matcher.cc.
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_primitives.h).  CPU restatement of the reference's ORBmatcher searches
+// (src/ORBmatcher.cc) and of the candidate-gather helpers they call (src/Frame.cc:385-416,657-735,
+// src/KeyFrame.cc:704-748) over PLAIN ARRAYS: the reference works on a pointer graph (Frame / KeyFrame / MapPoint);
+// here every MapPoint-dependent predicate (isBad, Observations()>0, mbTrackInView, projection into the image...)
+// arrives as a precomputed per-element flag or number, exactly what the C++ adapter of the product passes to the
+// C ABI (include/orbm.h).  Each function keeps the loop structure, scan order, comparison operators and float
+// expressions of the function it restates, so it can be checked against the reference line by line.
+//
+// Parity: UNPINNED by the reference (no tests / golden vectors for this path).  DescriptorDistance
+// is pinned against numpy popcount; the search functions are pinned only by being literal restatements.
 #pragma once
 #include <cstdint>
 #include <vector>
+
+namespace orc {
+
+struct KP {              // binary layout of cv::KeyPoint
+    float x, y, size, angle, response;
+    int octave, class_id;
+};
+
+constexpr int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:35-37
+constexpr int GRID_COLS = 64, GRID_ROWS = 48;                      // include/Frame.h:44-45
+
+// DescriptorDistance (src/ORBmatcher.cc:2058-2074): SWAR popcount over 8 x 32 bits
+int descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+// A Frame / KeyFrame as the searches see it: undistorted keypoints, descriptors, image bounds and the 64x48 grid.
+struct FrameView {
+    int n = 0;
+    const KP* kps = nullptr;
+    const uint8_t* desc = nullptr;           // n x 32
+    float minX = 0, minY = 0, maxX = 0, maxY = 0;
+    float invW = 0, invH = 0;                // mfGridElementWidthInv / HeightInv
+    std::vector<std::vector<int>> grid;      // [ix*GRID_ROWS+iy] -> keypoint indices in insertion order
+
+    void build(int n_, const KP* k, const uint8_t* d, float minX_, float minY_, float maxX_, float maxY_);
+    // Frame::GetFeaturesInArea (src/Frame.cc:657-723); KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:704-748) is the
+    // same walk with minLevel = maxLevel = -1
+    void features_in_area(float x, float y, float r, int minLevel, int maxLevel, std::vector<int>& out) const;
+};
+
+// ComputeThreeMaxima (src/ORBmatcher.cc:2012-2053) on bin sizes
+void three_maxima(const int* sizes, int L, int& ind1, int& ind2, int& ind3);
+// rotation-histogram bin of a match (e.g. src/ORBmatcher.cc:1784-1791)
+int rot_bin(float angle1, float angle2);
+
+// M1  SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) (src/ORBmatcher.cc:43-213), mono branch.
+//     valid[q] = mbTrackInView && !far && !isBad;  occupied[i] = mvpMapPoints[i] && Observations()>0 (in/out: a new
+//     assignment occupies the slot, see DESIGN.md "matcher assumptions").  kpMatch[i] = query assigned to keypoint i.
+int search_local_map(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
+                     const float* projX, const float* projY, const int* level, const float* viewCos,
+                     const uint8_t* qdesc, float th, float nnratio, int* kpMatch);
+
+// M2 / M3  SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) (:1676-1887, mono) and
+//     SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:1889-2010): window th*scale[octave],
+//     levels [octave-1, octave+1], accept best <= thDist, claim, rotation histogram.
+int search_frame(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
+                 const float* u, const float* v, const int* octave, const float* qangle, const uint8_t* qdesc,
+                 float th, int thDist, bool checkOri, int* kpMatch);
+
+// M7  SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) (:427-532 and :534-646)
+int search_sim3(const FrameView& KF, uint8_t* matched, const float* scaleFactors, int nq, const uint8_t* valid,
+                const float* u, const float* v, const int* level, const uint8_t* qdesc, int th, float ratioHamming,
+                int* kpMatch);
+
+// M5  SearchForInitialization (:648-763).  prevMatched: n1 x 2 floats, updated like vbPrevMatched.
+int search_initialization(const FrameView& F1, const FrameView& F2, float* prevMatched, int windowSize, float nnratio,
+                          bool checkOri, int* matches12);
+
+// DBoW2::FeatureVector as CSR: sorted node ids, offsets (nn+1), feature indices
+struct FeatVec { int nn; const int* node; const int* off; const int* idx; };
+
+// M4a SearchByBoW(KeyFrame*, Frame&, matches) (:223-425), mono.  elig1[i] = KF keypoint i has a good MapPoint.
+//     matchF[j] = KF keypoint matched to frame keypoint j (vpMapPointMatches), -1 = NULL.
+int search_bow_kf_frame(const FrameView& KF, const FeatVec& fvKF, const uint8_t* elig1, const FrameView& F,
+                        const FeatVec& fvF, float nnratio, bool checkOri, int* matchF);
+// M4b SearchByBoW(KeyFrame*, KeyFrame*, matches12) (:765-905).  matches12[i1] = i2.
+int search_bow_kf_kf(const FrameView& K1, const FeatVec& fv1, const uint8_t* elig1, const FrameView& K2,
+                     const FeatVec& fv2, const uint8_t* elig2, float nnratio, bool checkOri, int* matches12);
+
+// M6  SearchForTriangulation (:907-1146), mono / Pinhole.  free1/free2 = keypoint has no MapPoint; ep = epipole in
+//     image 2; F12 row-major as Pinhole::epipolarConstrain computes it (src/CameraModels/Pinhole.cpp:107-129);
+//     sigma2 = mvLevelSigma2 of KF2.
+int search_triangulation(const FrameView& K1, const FeatVec& fv1, const uint8_t* free1, const FrameView& K2,
+                         const FeatVec& fv2, const uint8_t* free2, const float* ep, const float* scaleFactors2,
+                         const float* F12, const float* sigma2, bool coarse, bool checkOri, int* matches12);
+
+// M9  candidate part of Fuse (:1148-1338 mono, :1340-1455): per map point the best keypoint in the window.
+void fuse_candidates(const FrameView& KF, const float* scaleFactors, const float* invSigma2, int nq,
+                     const uint8_t* valid, const float* u, const float* v, const int* level, const uint8_t* qdesc,
+                     float th, bool chi2Gate, int* bestIdx, int* bestDist);
+
+// M11 brute-force k-NN (config 5): per query the k smallest distances, ties -> lowest row
+void knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads);
+
+// 8(f) rank 2: MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:329-396): index of the descriptor with the
+// least median distance to the others
+int distinctive_descriptor(const uint8_t* desc, int n);
+
+}  // namespace orc

@@ -1,0 +1,267 @@
+"""GPU parity of every matcher entry point (through the C ABI) against the CPU oracle's literal restatements of the
+reference functions (oracle/cpp/orc_matcher.cc).  Bar: matches, assigned indices and distances bit-exact."""
+import numpy as np
+import pytest
+
+from mam3slam_b200 import ORBmatcher
+from oracle import matcher as om
+from tests import matcher_scenarios as sc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def M():
+    m = ORBmatcher(0.9, True)
+    yield m
+    m.close()
+
+
+@pytest.fixture(scope="module", params=[(752, 480, 1000, 0), (1241, 376, 2000, 1)], ids=["euroc", "kitti"])
+def pair(request):
+    return sc.frame_pair(*request.param)
+
+
+def _jitter(a, seed, amp):
+    rng = np.random.default_rng(seed)
+    return (a + rng.uniform(-amp, amp, len(a))).astype(np.float32)
+
+
+def test_grid_and_area_queries(M, pair):
+    (k1, d1), _, bounds, _ = pair
+    F = M.frame(k1, d1, bounds)
+    off, idx = F.grid()
+    ooff, oidx = om.grid_build(k1, bounds)
+    assert np.array_equal(off, ooff) and np.array_equal(idx, oidx)
+    rng = np.random.default_rng(5)
+    for _ in range(40):
+        x, y, r = float(rng.uniform(-30, bounds[2] + 30)), float(rng.uniform(-30, bounds[3] + 30)), float(rng.uniform(0.5, 150))
+        lo, hi = int(rng.integers(-1, 8)), int(rng.integers(-1, 8))
+        assert np.array_equal(F.GetFeaturesInArea(x, y, r, lo, hi), om.features_in_area(k1, bounds, x, y, r, lo, hi))
+    F.close()
+
+
+@pytest.mark.parametrize("th", [15.0, 30.0, 3.0])
+@pytest.mark.parametrize("ori", [True, False])
+def test_search_by_projection_frame(M, pair, th, ori):
+    """M2 (TrackWithMotionModel) and M3 (relocalisation, ORBdist 64)."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    n1 = len(k1)
+    rng = np.random.default_rng(int(th))
+    valid = (rng.random(n1) < 0.8).astype(np.uint8)
+    occ = (rng.random(len(k2)) < 0.1).astype(np.uint8)
+    u, v = _jitter(k1["x"], 1, 6), _jitter(k1["y"], 2, 6)
+    F = M.frame(k2, d2, bounds)
+    M.mbCheckOrientation = ori
+    for orbdist in (100, 64):
+        nm, km = M.SearchByProjection_Frame(F, occ, tabs["scale"], valid, u, v, k1["octave"], k1["angle"], d1, th, orbdist)
+        onm, okm = om.search_frame(k2, d2, bounds, occ, tabs["scale"], valid, u, v, k1["octave"], k1["angle"], d1, th, orbdist, ori)
+        assert nm == onm and np.array_equal(km, okm)
+    assert onm > 20
+    M.mbCheckOrientation = True
+    F.close()
+
+
+@pytest.mark.parametrize("th,ratio", [(1.0, 0.8), (5.0, 0.8), (15.0, 0.6)])
+def test_search_by_projection_local_map(M, pair, th, ratio):
+    """M1 (SearchLocalPoints): best / second best with levels, same-level NN-ratio rule."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    n1 = len(k1)
+    rng = np.random.default_rng(7)
+    # "map points" = frame-1 keypoints plus duplicates with a few flipped bits, so that second-best tests have work
+    rep = np.concatenate([np.arange(n1), rng.integers(0, n1, n1 // 2)])
+    qd = d1[rep].copy()
+    flip = rng.integers(0, 256, len(rep))
+    qd[np.arange(len(rep)), flip >> 3] ^= (1 << (flip & 7)).astype(np.uint8)
+    px, py = _jitter(k1["x"][rep], 3, 3), _jitter(k1["y"][rep], 4, 3)
+    level = np.clip(k1["octave"][rep] + rng.integers(0, 2, len(rep)), 0, 7).astype(np.int32)
+    vc = rng.uniform(0.99, 1.0, len(rep)).astype(np.float32)
+    valid = (rng.random(len(rep)) < 0.9).astype(np.uint8)
+    occ = (rng.random(len(k2)) < 0.05).astype(np.uint8)
+    F = M.frame(k2, d2, bounds)
+    M.mfNNratio = ratio
+    nm, km, occ_after = M.SearchByProjection_LocalMap(F, occ, tabs["scale"], valid, px, py, level, vc, qd, th)
+    onm, okm, oocc = om.search_local_map(k2, d2, bounds, occ, tabs["scale"], valid, px, py, level, vc, qd, th, ratio)
+    assert nm == onm and np.array_equal(km, okm) and np.array_equal(occ_after, oocc)
+    assert onm > 20
+    M.mfNNratio = 0.9
+    F.close()
+
+
+@pytest.mark.parametrize("th,ratio", [(8, 1.5), (5, 1.0)])
+def test_search_by_projection_sim3(M, pair, th, ratio):
+    """M7 (place recognition / merge)."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    n1 = len(k1)
+    rng = np.random.default_rng(11)
+    u, v = _jitter(k1["x"], 5, 4), _jitter(k1["y"], 6, 4)
+    level = np.clip(k1["octave"] + rng.integers(0, 2, n1), 0, 7).astype(np.int32)
+    valid = (rng.random(n1) < 0.85).astype(np.uint8)
+    matched = (rng.random(len(k2)) < 0.2).astype(np.uint8)
+    KF = M.frame(k2, d2, bounds)
+    nm, km = M.SearchByProjection_Sim3(KF, matched, tabs["scale"], valid, u, v, level, d1, th, ratio)
+    onm, okm = om.search_sim3(k2, d2, bounds, matched, tabs["scale"], valid, u, v, level, d1, th, ratio)
+    assert nm == onm and np.array_equal(km, okm) and onm > 20
+    KF.close()
+
+
+@pytest.mark.parametrize("window", [100, 10])
+def test_search_for_initialization(M, window):
+    """M5 on the 5x init extractor (src/Tracking.cc:606): stealing of worse earlier matches."""
+    (k1, d1), (k2, d2), bounds, _ = sc.frame_pair(752, 480, 5000, 2)
+    F1, F2 = M.frame(k1, d1, bounds), M.frame(k2, d2, bounds)
+    prev = np.stack([k1["x"], k1["y"]], 1)
+    for ori in (True, False):
+        M.mbCheckOrientation = ori
+        nm, m12, pm = M.SearchForInitialization(F1, F2, prev, window)
+        onm, om12, opm = om.search_initialization(k1, d1, k2, d2, bounds, prev, window, M.mfNNratio, ori)
+        assert nm == onm and np.array_equal(m12, om12) and np.array_equal(pm, opm)
+    assert onm > 50
+    M.mbCheckOrientation = True
+    F1.close(); F2.close()
+
+
+@pytest.mark.parametrize("ratio", [0.7, 0.9])
+def test_search_by_bow(M, pair, ratio):
+    """M4a (KeyFrame -> Frame, <= TH_LOW) and M4b (KeyFrame -> KeyFrame, < TH_LOW)."""
+    (k1, d1), (k2, d2), bounds, _ = pair
+    rng = np.random.default_rng(13)
+    fv1, fv2 = sc.feat_vec(d1), sc.feat_vec(d2)
+    e1 = (rng.random(len(k1)) < 0.7).astype(np.uint8)
+    e2 = (rng.random(len(k2)) < 0.7).astype(np.uint8)
+    K1, K2 = M.frame(k1, d1, bounds), M.frame(k2, d2, bounds)
+    M.mfNNratio = ratio
+    for ori in (True, False):
+        M.mbCheckOrientation = ori
+        nm, mf = M.SearchByBoW_KF_Frame(K1, fv1, e1, K2, fv2)
+        onm, omf = om.search_bow_kf_frame(k1, d1, fv1, e1, k2, d2, fv2, ratio, ori)
+        assert nm == onm and np.array_equal(mf, omf)
+        nm2, m12 = M.SearchByBoW_KF_KF(K1, fv1, e1, K2, fv2, e2)
+        onm2, om12 = om.search_bow_kf_kf(k1, d1, fv1, e1, k2, d2, fv2, e2, ratio, ori)
+        assert nm2 == onm2 and np.array_equal(m12, om12)
+    assert onm > 10 and onm2 > 5
+    M.mfNNratio, M.mbCheckOrientation = 0.9, True
+    K1.close(); K2.close()
+
+
+@pytest.mark.parametrize("coarse", [False, True])
+def test_search_for_triangulation(M, pair, coarse):
+    """M6: last minimum wins, epipole rejection, Pinhole epipolar constraint with the caller's F12."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    rng = np.random.default_rng(17)
+    fv1, fv2 = sc.feat_vec(d1, 5), sc.feat_vec(d2, 5)
+    free1 = (rng.random(len(k1)) < 0.6).astype(np.uint8)
+    free2 = (rng.random(len(k2)) < 0.6).astype(np.uint8)
+    # a sideways-translation pair: F12 = [t]x for t = (1, 0.02, 0) in pixel units -> near-horizontal epipolar lines
+    t = np.array([1.0, 0.02, 0.0])
+    F12 = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]], np.float32)
+    ep = np.array([bounds[2] * 0.8, bounds[3] * 0.5], np.float32)
+    K1, K2 = M.frame(k1, d1, bounds), M.frame(k2, d2, bounds)
+    for ori in (False, True):
+        M.mbCheckOrientation = ori
+        nm, m12 = M.SearchForTriangulation(K1, fv1, free1, K2, fv2, free2, ep, tabs["scale"], F12, tabs["sigma2"] * 9, coarse)
+        onm, om12 = om.search_triangulation(k1, d1, fv1, free1, k2, d2, fv2, free2, ep, tabs["scale"], F12, tabs["sigma2"] * 9,
+                                            coarse, ori)
+        assert nm == onm and np.array_equal(m12, om12)
+    assert onm > 10
+    M.mbCheckOrientation = True
+    K1.close(); K2.close()
+
+
+def test_fuse_candidates(M, pair):
+    """M9: best keypoint per map point with the level window and the chi2 reprojection gate."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    n1 = len(k1)
+    rng = np.random.default_rng(19)
+    u, v = _jitter(k1["x"], 7, 3), _jitter(k1["y"], 8, 3)
+    level = np.clip(k1["octave"] + rng.integers(0, 2, n1), 0, 7).astype(np.int32)
+    valid = (rng.random(n1) < 0.9).astype(np.uint8)
+    KF = M.frame(k2, d2, bounds)
+    for gate, th in ((True, 3.0), (False, 4.0)):
+        bi, bd = M.Fuse_candidates(KF, tabs["scale"], tabs["inv_sigma2"], valid, u, v, level, d1, th, gate)
+        obi, obd = om.fuse_candidates(k2, d2, bounds, tabs["scale"], tabs["inv_sigma2"], valid, u, v, level, d1, th, gate)
+        assert np.array_equal(bi, obi) and np.array_equal(bd, obd)
+        assert (obi >= 0).sum() > 20
+    KF.close()
+
+
+def test_empty_and_degenerate_inputs(M, pair):
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    F = M.frame(k2, d2, bounds)
+    z = np.zeros(0, np.float32)
+    nm, km = M.SearchByProjection_Frame(F, np.zeros(len(k2), np.uint8), tabs["scale"], np.zeros(0, np.uint8), z, z,
+                                        np.zeros(0, np.int32), z, np.zeros((0, 32), np.uint8), 15.0)
+    assert nm == 0 and (km == -1).all()
+    # every slot occupied -> nothing can match; queries far outside the image -> no candidates
+    n1 = len(k1)
+    nm, km = M.SearchByProjection_Frame(F, np.ones(len(k2), np.uint8), tabs["scale"], np.ones(n1, np.uint8), k1["x"], k1["y"],
+                                        k1["octave"], k1["angle"], d1, 15.0)
+    assert nm == 0
+    nm, km = M.SearchByProjection_Frame(F, np.zeros(len(k2), np.uint8), tabs["scale"], np.ones(n1, np.uint8), k1["x"] + 5000,
+                                        k1["y"], k1["octave"], k1["angle"], d1, 15.0)
+    assert nm == 0
+    E = M.frame(k2[:0], d2[:0], bounds)
+    nm, km = M.SearchByProjection_Frame(E, np.zeros(0, np.uint8), tabs["scale"], np.ones(n1, np.uint8), k1["x"], k1["y"],
+                                        k1["octave"], k1["angle"], d1, 15.0)
+    assert nm == 0 and len(km) == 0
+    E.close(); F.close()
+
+
+def test_slab_overflow_path(M):
+    """More candidates in one window than the shared-memory slab holds: the streaming resolve must give the same answer."""
+    (k1, d1), (k2, d2), bounds, tabs = sc.frame_pair(752, 480, 5000, 2)
+    n1 = 200
+    F = M.frame(k2, d2, bounds)
+    valid = np.ones(n1, np.uint8)
+    occ = np.zeros(len(k2), np.uint8)
+    big_scale = np.full(8, 40.0, np.float32)          # radius 600 px: thousands of candidates per query
+    nm, km = M.SearchByProjection_Frame(F, occ, big_scale, valid, k1["x"][:n1], k1["y"][:n1], k1["octave"][:n1],
+                                        k1["angle"][:n1], d1[:n1], 15.0)
+    onm, okm = om.search_frame(k2, d2, bounds, occ, big_scale, valid, k1["x"][:n1], k1["y"][:n1], k1["octave"][:n1],
+                               k1["angle"][:n1], d1[:n1], 15.0, 100, True)
+    assert nm == onm and np.array_equal(km, okm)
+    F.close()
+
+
+@pytest.mark.parametrize("ndb,nq,k", [(50_000, 300, 2), (50_000, 300, 8), (1000, 17, 1), (129, 5, 16), (7, 3, 4)])
+def test_knn_vs_oracle(M, ndb, nq, k):
+    q, db = sc.knn_data(ndb, nq, planted=ndb >= 1000)
+    d, i = M.knn(q, db, k)
+    od, oi = om.knn(q, db, k, threads=8)
+    assert np.array_equal(d, od) and np.array_equal(i, oi)
+
+
+def test_knn_full_size_properties(M):
+    """BASELINE config 5 at full size (1 M x 2000): checked through properties the oracle need not recompute —
+    planted neighbours found at their known distance, lists sorted by (dist, row), sharded search + merge == unsharded."""
+    q, db = sc.knn_data(1_000_000, 2000)
+    D = M.database(db)
+    d, i = M.knn(q, D, 8)
+    assert (d[:, 0] <= 40).all()
+    key = d.astype(np.int64) * (1 << 32) + i
+    assert (np.diff(key, axis=1) > 0).all()
+    true_d = np.unpackbits(q[:, None, :] ^ db[i], axis=2).sum(2)
+    assert np.array_equal(true_d, d)
+    parts = []
+    for s in range(4):
+        Ds = M.database(db[s * 250_000:(s + 1) * 250_000], row_offset=s * 250_000)
+        parts.append(M.knn(q, Ds, 8))
+        Ds.close()
+    md, mi = M.knn_merge(np.stack([p[0] for p in parts]), np.stack([p[1] for p in parts]))
+    assert np.array_equal(md, d) and np.array_equal(mi, i)
+    # a 20k-row prefix against the oracle
+    Dp = M.database(db[:20_000])
+    dp, ip = M.knn(q[:200], Dp, 8)
+    od, oi = om.knn(q[:200], db[:20_000], 8, threads=8)
+    assert np.array_equal(dp, od) and np.array_equal(ip, oi)
+    Dp.close(); D.close()
+
+
+def test_distinctive_descriptors(M):
+    rng = np.random.default_rng(23)
+    sizes = [1, 2, 3, 5, 8, 13, 21, 34, 40]
+    desc = rng.integers(0, 256, (sum(sizes), 32), dtype=np.uint8)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    best = M.ComputeDistinctiveDescriptors(desc, off)
+    want = [om.distinctive_descriptor(desc[off[p]:off[p + 1]]) for p in range(len(sizes))]
+    assert best.tolist() == want
