@@ -86,3 +86,44 @@ def test_sort_emulation_adversarial(oracle_mod, emul):
                  np.arange(n) % 2, (np.arange(n) * 7919) % 13):
         ulx = np.zeros(n, np.int32)
         assert np.array_equal(_emul_sort(emul, size, ulx), oracle_mod.sort_nodes(size, ulx))
+
+
+def _build_adapter_demo(tmpdir):
+    exe = os.path.join(str(tmpdir), "adapter_demo")
+    libdir = os.path.join(ROOT, "mam3slam_b200")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", "-o", exe,
+                           os.path.join(ROOT, "tests", "native", "adapter_demo.cc"), "-L" + libdir, "-lmam3slam_b200",
+                           "-Wl,-rpath," + libdir])
+    return exe
+
+
+def test_cpp_adapters_compile_and_link(native, tmp_path):
+    """mam3slam_b200/cpp/ORBextractor.h / ORBmatcher.h (the reference's class surface) build as C++14 against the cv:: shim
+    and link against the C-ABI library; without a GPU the constructor must throw (no CPU fallback)."""
+    exe = _build_adapter_demo(tmp_path)
+    import torch
+    if not torch.cuda.is_available():
+        img = tmp_path / "im.raw"
+        img.write_bytes(bytes(64 * 64))
+        r = subprocess.run([exe, str(img), "64", "64"], capture_output=True, text=True)
+        assert r.returncode != 0 and "no CUDA device" in (r.stderr + r.stdout)
+
+
+@pytest.mark.gpu
+def test_cpp_adapter_matches_python_mirror(native, tmp_path):
+    from mam3slam_b200 import ORBextractor, synth
+    exe = _build_adapter_demo(tmp_path)
+    im = synth.frame(752, 480, 0)
+    p = tmp_path / "im.raw"
+    p.write_bytes(im.tobytes())
+    out = subprocess.run([exe, str(p), "752", "480"], capture_output=True, text=True, check=True).stdout.split()
+    ex = ORBextractor(1000, 1.2, 8, 20, 7)
+    mono, kps, desc = ex(im)
+    cs = 0
+    for k, d in zip(kps, desc):
+        cs = (cs * 1315423911 + int(k["x"]) * 31 + int(k["y"]) * 7 + int(k["octave"])) % (1 << 64)
+        for b in d:
+            cs = (cs * 131 + int(b)) % (1 << 64)
+    assert int(out[0]) == mono and int(out[1]) == len(kps) and int(out[2]) == cs
+    assert int(out[3]) == int(np.unpackbits(desc[0] ^ desc[1]).sum()) and int(out[4]) == 210
+    ex.close()
