@@ -91,18 +91,38 @@ def make_frames(seed, n):
     return synth.stream(W, H, seed, n)
 
 
+TH_TRACK = 15.0                          # TrackWithMotionModel's first window (src/Tracking.cc:2789-2812)
+BOUNDS = (0.0, 0.0, float(W), float(H))
+WORKLOAD = ("single-agent EuRoC-shaped 752x480 synthetic mono stream per GPU, 1000 kp, 8 levels @1.2, FAST 20/7: per frame "
+            "ORBextractor::operator() + SearchByProjection(Cur, Last, th=15, mono)")
+POPC_PEAK = 4.635e12                     # measured on this pool's B200 (profiles/int_peaks_b200.txt): 16.5 popc/clk/SM
+
+
 def cpu_reference_run(frames, iters, threads):
-    """Times the CPU restatement (oracle/) of ORBextractor::operator() on `iters` frames split over `threads`."""
+    """Times the CPU restatement (oracle/) of the hot path — ORBextractor::operator() on every frame followed by
+    SearchByProjection(Cur, Last) against the previous frame — on `iters` frames split over `threads` host threads
+    (one independent agent stream per thread, like the reference's one Tracking thread per agent)."""
     import oracle
+    from oracle import matcher as om
+    from tests.matcher_scenarios import to_kp
     exs = [oracle.Extractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH) for _ in range(threads)]
+    sf = exs[0].tables()["scale"]
     per = [iters // threads + (1 if t < iters % threads else 0) for t in range(threads)]
-    for ex in exs:
-        ex.timed(frames[:1], 1)                     # warm the allocator / caches
-    res = [None] * threads
+    evals = [0] * threads
 
     def work(t):
-        res[t] = exs[t].timed(frames, per[t]) if per[t] else (0.0, 0)
+        last = None
+        for i in range(per[t]):
+            _, k, d = exs[t](frames[i % len(frames)])
+            k = to_kp(k)
+            if last is not None:
+                k1, d1 = last
+                om.search_frame(k, d, BOUNDS, np.zeros(len(k), np.uint8), sf, np.ones(len(k1), np.uint8), k1["x"], k1["y"],
+                                k1["octave"], k1["angle"], d1, TH_TRACK, 100, True)
+            last = (k, d)
 
+    for ex in exs[:1]:
+        ex(frames[0])                                # warm the allocator / caches
     th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
     t0 = time.perf_counter()
     for x in th:
@@ -114,7 +134,8 @@ def cpu_reference_run(frames, iters, threads):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on this box's host cores."""
+    """--impl reference: the reference's CPU implementation of the path on this box's host cores (oracle port: the
+    reference itself needs OpenCV C++ / Eigen, which are not installed)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -132,19 +153,78 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "EuRoC-shaped 752x480 mono stream, 1000 kp, 8 levels @1.2, FAST 20/7: "
-                                   "ORBextractor::operator() per frame", "frames_per_step": per_step},
+            "config": {"workload": WORKLOAD, "frames_per_step": per_step},
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
-                             "sample": f"{per_step} frames per step x {args.steps} steps, {threads} threads, "
-                                       "oracle/cpp restatement (reference needs OpenCV C++/Eigen: not buildable here)"},
+                             "sample": f"{per_step} frames per step x {args.steps} steps, {threads} threads (one agent stream "
+                                       "each), oracle/cpp restatement of ORBextractor + SearchByProjection (reference needs "
+                                       "OpenCV C++/Eigen: not buildable here)"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+def knn_bench(args, torch, dist, rank, world, local):
+    """BASELINE config 5: 1 M x 2000 brute-force k-NN (k = 2), database rows sharded over the ranks, per-rank top-k lists
+    all-gathered (NCCL) and merged with the (dist, global row) rule.  Returns a dict for the JSON line."""
+    from mam3slam_b200 import ORBmatcher
+    from mam3slam_b200.matcher import KnnDatabase
+    NDB, NQ, K = 1_000_000, 2000, 2
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    db = torch.randint(0, 256, (NDB, 32), dtype=torch.uint8, device="cuda", generator=g)
+    q = db[torch.randint(0, NDB, (NQ,), device="cuda", generator=g)].clone()
+    q[:, 0] ^= 1
+    lo, hi = NDB * rank // world, NDB * (rank + 1) // world
+    shard = db[lo:hi].contiguous()
+    m = ORBmatcher(0.6, True, device=local)
+    D = KnnDatabase(m, None, row_offset=lo, device_ptr=shard.data_ptr(), n=hi - lo)
+    dd = torch.empty((NQ, K), dtype=torch.int16, device="cuda")
+    di = torch.empty((NQ, K), dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    gath_d = [torch.empty_like(dd) for _ in range(world)]
+    gath_i = [torch.empty_like(di) for _ in range(world)]
+
+    def step():
+        m.knn_device(D, q.data_ptr(), NQ, K, dd.data_ptr(), di.data_ptr(), st)
+        if world > 1:
+            dist.all_gather(gath_d, dd)
+            dist.all_gather(gath_i, di)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 10
+    e0.record()
+    for _ in range(iters):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    # correctness of the merged result on rank 0: the planted neighbour (distance 1) is found for every query
+    if world > 1:
+        md, mi = ORBmatcher.knn_merge(torch.stack(gath_d).cpu().numpy().view(np.uint16), torch.stack(gath_i).cpu().numpy())
+    else:
+        md, mi = dd.cpu().numpy().view(np.uint16), di.cpu().numpy()
+    ok = bool((md[:, 0] <= 1).all())
+    evals = float(NDB) * NQ
+    out = {"workload": f"brute-force k-NN {NDB} x {NQ}, k={K}, db rows sharded over {world} GPU(s), all-gather + merge",
+           "ms": ms, "evaluations_per_s": evals / (ms * 1e-3), "planted_neighbours_found": ok,
+           "roofline_int": {"bound": "popc", "achieved_popc_equiv_per_s": 8 * evals / (ms * 1e-3), "peak_popc_per_s": POPC_PEAK * world,
+                            "frac": 8 * evals / (ms * 1e-3) / (POPC_PEAK * world),
+                            "note": "8 popc per 256-bit evaluation by definition; the kernel issues 4 (carry-save adder tree), so "
+                                    "frac may exceed 1"}}
+    D.close(); m.close()
+    return out
 
 
 def run_gpu(args):
     import torch
     import torch.distributed as dist
-    from mam3slam_b200 import ORBextractor
+    from mam3slam_b200 import ORBextractor, ORBmatcher, KEYPOINT_DTYPE
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -160,20 +240,31 @@ def run_gpu(args):
     nsets = args.sets                      # distinct input batches: nsets*B*361 KB > L2 (126 MB)
     frames = make_frames(rank, min(64, B))                 # agent `rank`'s stream
     reps = (B * nsets + len(frames) - 1) // len(frames)
-    host = np.concatenate([frames] * reps)[:B * nsets]
+    # page-locked host frames: the e2e leg copies from pinned memory as the contract asks
+    host_t = torch.empty((B * nsets, H, W), dtype=torch.uint8).pin_memory()
+    host = host_t.numpy()
+    host[:] = np.concatenate([frames] * reps)[:B * nsets]
     # make the batches distinct so no step re-reads cached input: roll each copy by a few pixels
     for i in range(len(frames), len(host)):
         host[i] = np.roll(host[i], (i // len(frames)) * 3, axis=1)
     dev = torch.from_numpy(host).cuda()
     img_bytes = W * H
     ex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
+    mt = ORBmatcher(0.9, True, device=local)
+    sf = ex.GetScaleFactors()
     tstream = torch.cuda.Stream()          # a real (non-NULL) stream: CUDA events below are recorded on it
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
+    ex.extract_device(dev.data_ptr(), img_bytes, B, W, H, W, (0, 1000), stream)   # allocates the shape-dependent buffers
+    torch.cuda.synchronize()
+    dk, dd, dc, stride = ex.results_batch_device()
+    kpm = torch.empty((B, stride), dtype=torch.int32, device="cuda")
+    nmt = torch.empty(B, dtype=torch.int32, device="cuda")
 
     def step_device(i):
         s = i % nsets
         ex.extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), stream)
+        mt.track_batch_device(B, dk, dd, dc, stride, BOUNDS, sf, TH_TRACK, kpm.data_ptr(), nmt.data_ptr(), stream=stream)
 
     def barrier():
         torch.cuda.synchronize()
@@ -188,7 +279,7 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    l0 = ex.launch_count()
+    l0 = ex.launch_count() + mt.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
@@ -196,29 +287,52 @@ def run_gpu(args):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    launches = ex.launch_count() - l0
-    nkp = sum(ex.fetch(f)[1].shape[0] for f in range(min(B, 4))) / min(B, 4)
+    launches = ex.launch_count() + mt.launch_count() - l0
+    nkp = float(np.mean([ex.fetch(f)[1].shape[0] for f in range(min(B, 4))]))
+    track_evals = mt.track_evaluations()
+    nmatch = float(nmt[1:].float().mean().item())
 
     # ---- per-kernel durations (CUDA events on the launching stream, same work as the timed region) ----
     ex.set_stage_timing(True)
     acc = {}
     nrep = min(args.steps, 5)
+    t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for i in range(nrep):
-        step_device(i)
+        s = i % nsets
+        ex.extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), stream)
+        t0e.record()
+        mt.track_batch_device(B, dk, dd, dc, stride, BOUNDS, sf, TH_TRACK, kpm.data_ptr(), nmt.data_ptr(), stream=stream)
+        t1e.record()
         torch.cuda.synchronize()
         ex.synchronize()
         for k, v in ex.stage_times().items():
             acc[k] = acc.get(k, 0.0) + v / nrep
+        acc["track"] = acc.get("track", 0.0) + t0e.elapsed_time(t1e) / nrep
+    acc["total"] = acc["total"] + acc["track"]
     ex.set_stage_timing(False)
 
-    # ---- e2e: host buffers through the C-ABI call ----
+    # ---- e2e: page-locked host buffers through the C-ABI calls (H2D of frames, D2H of keypoints / descriptors / matches) ----
+    cap = stride
+    kps_h = torch.empty((B, cap * KEYPOINT_DTYPE.itemsize), dtype=torch.uint8).pin_memory().numpy().view(KEYPOINT_DTYPE).reshape(B, cap)
+    desc_h = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory().numpy()
+    n_h, mono_h = np.zeros(B, np.int32), np.zeros(B, np.int32)
+    kpm_h = torch.empty((B, stride), dtype=torch.int32).pin_memory()
+    nm_h = torch.empty(B, dtype=torch.int32).pin_memory()
     host_batches = [host[s * B:(s + 1) * B] for s in range(nsets)]
+
+    def step_e2e(i):
+        ex.extract_batch_into(host_batches[i % nsets], kps_h, desc_h, n_h, mono_h)
+        mt.track_batch_device(B, dk, dd, dc, stride, BOUNDS, sf, TH_TRACK, kpm.data_ptr(), nmt.data_ptr(), stream=stream)
+        kpm_h.copy_(kpm, non_blocking=True)
+        nm_h.copy_(nmt, non_blocking=True)
+        tstream.synchronize()
+
     for i in range(min(args.warmup, 3)):
-        ex.extract_batch(host_batches[i % nsets])
+        step_e2e(i)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        ex.extract_batch(host_batches[i % nsets])
+        step_e2e(i)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
@@ -228,44 +342,46 @@ def run_gpu(args):
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms, e2e_ms = tms.tolist()
     total_frames = B * args.steps * world
+    hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     if rank == 0:
         pk, pk_kind = peaks()
         fps = total_frames / (ms * 1e-3)
-        stage_bytes = stage_algorithmic_bytes(nkp)
+        stage_bytes = stage_algorithmic_bytes(nkp, track_evals / max(B - 1, 1))
         dom = max((k for k in acc if k != "total"), key=lambda k: acc[k])
         ach = stage_bytes[dom] * B / (acc[dom] * 1e-3) / 1e9
-        cap = ex._cap()
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "EuRoC-shaped 752x480 mono stream per GPU (one agent per GPU), 1000 kp, 8 levels "
-                                   "@1.2, FAST 20/7: ORBextractor::operator() per frame",
-                       "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
+            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
+                       "matches_per_frame": nmatch, "hamming_evaluations_per_frame": track_evals / max(B - 1, 1),
                        "l2_policy": f"{nsets} distinct input batches rotated ({nsets * B * img_bytes / 1e6:.0f} MB > "
                                     "126 MB L2); all intermediates rewritten every step"},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
-                    "h2d_bytes_per_step": int(B * 768 * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8))},
+                    "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8 + stride * 4 + 4))},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
                          "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
                          "stage_ms_per_step": acc,
+                         "note": "integer/issue-bound path: see DESIGN.md 4; pipeline_* = 1.93 MB algorithmic bytes per frame",
                          "pipeline_alg_gbs": ALG_BYTES_PER_FRAME * fps / 1e9 / world,
                          "pipeline_frac": ALG_BYTES_PER_FRAME * fps / 1e9 / world / pk["hbm_gbs"]},
+            "hamming": {"track_evaluations_per_s": track_evals * world / (acc["track"] * 1e-3), "knn": hamming},
         }
         if world == 1 and not args.no_cpu:
             cf = make_frames(0, 8)
             wall, n = cpu_reference_run(cf, args.cpu_frames, 1)
             line["cpu_baseline"] = {"value": n / wall, "unit": "frames/s", "cores": 1, "kind": "port",
-                                    "sample": f"{n} frames of the same stream, 1 thread, oracle/cpp restatement"}
+                                    "sample": f"{n} frames of the same stream (extraction + SearchByProjection), 1 thread, "
+                                              "oracle/cpp restatement"}
         print(json.dumps(line))
-    ex.close()
+    ex.close(); mt.close()
     if world > 1:
         dist.destroy_process_group()
 
 
-def stage_algorithmic_bytes(nkp):
+def stage_algorithmic_bytes(nkp, evals_per_frame=20000.0):
     """Algorithmic bytes per FRAME of each kernel (DESIGN.md 'Kernels'): pixels of the 8 EuRoC levels etc."""
     lv = [752 * 480, 627 * 400, 522 * 333, 435 * 278, 363 * 231, 302 * 193, 252 * 161, 210 * 134]
     allpx, derived = sum(lv), sum(lv[1:])
@@ -277,6 +393,7 @@ def stage_algorithmic_bytes(nkp):
         "blur": 2 * allpx,                      # read + write every level
         "finalize": 8 * nkp + 28 * nkp + 16 * nkp,
         "orient_brief": nkp * (749 + 512 + 32 + 4),  # patch reads + 512 blurred samples + descriptor
+        "track": 52 * nkp + 48 * evals_per_frame + 4 * nkp,   # grid build + (32-B row + 16-B kp4) per evaluation + matches
     }
 
 
@@ -288,8 +405,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="frames in flight per GPU per step")
     ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
-    ap.add_argument("--cpu-frames", type=int, default=300, help="frames timed for cpu_baseline")
+    ap.add_argument("--cpu-frames", type=int, default=400, help="frames timed for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -103,6 +103,17 @@ int orbm_fuse_candidates(orbm_handle h, orbm_frame kf, const float* scale_factor
                          int nq, const uint8_t* valid, const float* u, const float* v, const int* level,
                          const uint8_t* qdesc, float th, int chi2_gate, int* best_idx, int* best_dist);
 
+/* Device-resident tracking step (BASELINE config[1]: per-frame extraction + SearchByProjection on one GPU): for every
+ * frame i >= 1 of a batch of extractor results that never left HBM (d_kps / d_desc / d_counts = the arrays behind
+ * orbx_results_device: frame f at d_kps + f*frame_stride, its keypoint count at d_counts[f*count_stride]) runs
+ * SearchByProjection(Cur = frame i, Last = frame i-1, th, bMono = true) (src/ORBmatcher.cc:1676-1887) with every keypoint
+ * of the last frame standing for a map point projected at its own position.  The frame grids are built on the device.
+ * d_kp_match: nframes x frame_stride ints (row i = the reference's CurrentFrame.mvpMapPoints as indices into frame i-1,
+ * -1 = none; row 0 all -1), d_nmatches: nframes ints.  Asynchronous on `stream` (NULL = the handle's stream). */
+int orbm_track_batch_device(orbm_handle h, int nframes, const orbx_keypoint* d_kps, const uint8_t* d_desc, const int* d_counts,
+                            int frame_stride, int count_stride, const float* bounds4, const float* scale_factors, int nlevels,
+                            float th, int th_dist, int check_orientation, int* d_kp_match, int* d_nmatches, void* stream);
+
 /* ---- BoW-guided searches: DBoW2::FeatureVector (std::map<NodeId, vector<unsigned>>) flattened to CSR ---- */
 typedef struct orbm_featvec {
     int n_nodes;
@@ -147,7 +158,9 @@ int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq
  * points: descriptors of point p are rows [off[p], off[p+1]); best[p] = row (relative) with the least median distance */
 int orbm_distinctive_descriptors(orbm_handle h, const uint8_t* desc, const int* off, int npoints, int* best);
 
-/* Hamming evaluations performed by the last search call (for matches/s reporting) */
+/* Hamming evaluations performed by the last search call (for matches/s reporting); the track variant waits for the
+ * device and reads the counter of the last orbm_track_batch_device */
+long long orbm_track_evaluations(orbm_handle h);
 long long orbm_last_evaluations(orbm_handle h);
 
 #ifdef __cplusplus

@@ -88,6 +88,10 @@ int orbx_synchronize(orbx_handle h);
 /* per-frame results of the last pass: device pointers (valid until the next pass), counts read back */
 int orbx_results_device(orbx_handle h, int frame, const orbx_keypoint** d_kps, const uint32_t** d_desc,
                         int* n_out, int* mono_index_out);
+/* the batch arrays themselves (device): frame f's keypoints at *d_kps + f*(*frame_stride), descriptor rows at *d_desc +
+ * f*(*frame_stride)*32, its {n, monoIndex} at (*d_counts)[2f .. 2f+1].  Feed these to orbm_track_batch_device. */
+int orbx_results_batch_device(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc, const int** d_counts,
+                              int* frame_stride);
 int orbx_fetch_results(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
                        int* mono_index_out);
 

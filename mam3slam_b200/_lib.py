@@ -45,6 +45,7 @@ def lib():
     L.orbx_extract_device.argtypes = [vp, vp, u64, i32, i32, i32, i32, i32, i32, vp]
     L.orbx_synchronize.argtypes = [vp]
     L.orbx_results_device.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(vp), ip, ip]
+    L.orbx_results_batch_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), ip]
     L.orbx_fetch_results.argtypes = [vp, i32, vp, vp, i32, ip, ip]
     L.orbx_level_size.argtypes = [vp, i32, ip, ip]
     L.orbx_download_level.argtypes = [vp, i32, i32, i32, vp, i32]
@@ -112,6 +113,9 @@ def _bind_matcher(L):
     L.orbm_knn_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
     L.orbm_knn_merge.argtypes = [vp, vp, i32, i32, i32, vp, vp]
     L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp]
+    L.orbm_track_batch_device.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, i32, f32, i32, i32, vp, vp, vp]
+    L.orbm_track_evaluations.restype = ll
+    L.orbm_track_evaluations.argtypes = [vp]
 
 
 def check_m(status, handle=None, what=""):

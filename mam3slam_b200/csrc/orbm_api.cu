@@ -43,6 +43,7 @@ struct orbm_matcher {
     void* pinned = nullptr; size_t pinnedBytes = 0;
     unsigned long long* dEvals = nullptr;
     unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
+    void* trackBuf = nullptr; size_t trackBytes = 0;
 };
 
 namespace {
@@ -192,6 +193,7 @@ void orbm_destroy(orbm_handle M) {
     if (M->pinned) cudaFreeHost(M->pinned);
     if (M->dEvals) cudaFree(M->dEvals);
     if (M->knnPart) cudaFree(M->knnPart);
+    if (M->trackBuf) cudaFree(M->trackBuf);
     cudaStreamDestroy(M->stream);
     delete M;
 }
@@ -254,7 +256,7 @@ __global__ void k_area_list(SearchParams P, int* out, int cap, int* nOut) {
     uint32_t qd[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned long long ne = 0;
     int count = 0;
-    walk_candidates(P, 0, qd, ne, [&](bool ok, uint32_t entry) {
+    walk_candidates(P, P.tgt, 0, qd, ne, [&](bool ok, uint32_t entry) {
         const unsigned m = __ballot_sync(0xffffffffu, ok);
         if (ok) { const int pos = count + __popc(m & ((1u << lane) - 1)); if (pos < cap) out[pos] = (int)(entry & 0x7ffff); }
         count += __popc(m);
@@ -311,10 +313,10 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     P.occ = io.occ ? S.dev<uint8_t>(oOcc) : nullptr;
     P.qResult = S.dev<int>(oRes); P.qDist = S.dev<int>(oDist); P.qBin = S.dev<int>(oBin);
     P.evals = S.dev<unsigned long long>(oEv);
-    size_t smem = (size_t)kSearchWarps * kSlab * 4;
-    if (P.state == 1) smem += ((size_t)n + 15) & ~(size_t)15;
-    if (P.state == 2) smem += (((size_t)n * 2 + 15) & ~(size_t)15) + (size_t)n * 4;
-    if (smem > 200 * 1024) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
+    // stateful searches run on one CTA: stage the target frame on chip; stateless ones spread over many CTAs instead
+    P.stageTgt = (P.state != 0 && search_smem_bytes(n, P.state, true) <= kSearchSmemMax && nq >= 64) ? 1 : 0;
+    const size_t smem = search_smem_bytes(n, P.state, P.stageTgt != 0);
+    if (smem > kSearchSmemMax) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
     const int grid = P.state != 0 ? 1 : std::max(1, std::min((nq + kSearchWarps - 1) / kSearchWarps, M->smCount * 2));
     k_search<<<grid, kSearchThreads, smem, M->stream>>>(P);
     ++M->launches;
@@ -795,3 +797,70 @@ int orbm_distinctive_descriptors(orbm_handle M, const uint8_t* desc, const int* 
 }
 
 }  // extern "C"
+
+// ---- device-resident tracking step -----------------------------------------------------------------------------------
+extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_keypoint* d_kps, const uint8_t* d_desc,
+                                       const int* d_counts, int frame_stride, int count_stride, const float* bounds4,
+                                       const float* scale_factors, int nlevels, float th, int th_dist, int check_orientation,
+                                       int* d_kp_match, int* d_nmatches, void* stream) {
+    if (!M || nframes < 1 || !d_kps || !d_desc || !d_counts || frame_stride < 1 || count_stride < 1 || !bounds4 || !scale_factors ||
+        nlevels < 1 || nlevels > 16 || !d_kp_match || !d_nmatches || !(bounds4[2] > bounds4[0]) || !(bounds4[3] > bounds4[1]))
+        return ORBM_ERR_INVALID;
+    if (frame_stride >= (1 << 19)) return ORBM_ERR_UNSUPPORTED;
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    const size_t NS = (size_t)nframes * frame_stride;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { off = (off + 255) & ~(size_t)255; size_t at = off; off += bytes; return at; };
+    const size_t oKp4 = take(NS * 16), oCellOf = take(NS * 4), oCellIdx = take(NS * 4), oCellOff = take((size_t)nframes * (kGridCells + 1) * 4);
+    const size_t oWin = take(NS * 16), oLev = take(NS * 8), oAng = take(NS * 4), oOcc = take(NS);
+    const size_t oRes = take(NS * 4), oDist = take(NS * 4), oBin = take(NS * 4);
+    if (off > M->trackBytes) {
+        if (M->trackBuf) { CKM(cudaStreamSynchronize(st)); cudaFree(M->trackBuf); }
+        M->trackBuf = nullptr; M->trackBytes = 0;
+        CKM(cudaMalloc(&M->trackBuf, off));
+        M->trackBytes = off;
+    }
+    uint8_t* b = (uint8_t*)M->trackBuf;
+    TrackBatch T;
+    memset(&T, 0, sizeof(T));
+    T.nframes = nframes; T.stride = frame_stride; T.countStride = count_stride;
+    T.kps = d_kps; T.desc = reinterpret_cast<const uint32_t*>(d_desc); T.counts = d_counts;
+    T.minX = bounds4[0]; T.minY = bounds4[1];
+    T.invW = static_cast<float>(kGridCols) / static_cast<float>(bounds4[2] - bounds4[0]);
+    T.invH = static_cast<float>(kGridRows) / static_cast<float>(bounds4[3] - bounds4[1]);
+    T.th = th; T.thF = (float)th_dist; T.checkOri = check_orientation;
+    for (int l = 0; l < 16; ++l) T.scale[l] = l < nlevels ? scale_factors[l] : scale_factors[nlevels - 1];
+    T.kp4 = (float4*)(b + oKp4); T.cellOf = (int*)(b + oCellOf); T.cellIdx = (int*)(b + oCellIdx); T.cellOff = (int*)(b + oCellOff);
+    T.qwin = (float4*)(b + oWin); T.qlev = (int2*)(b + oLev); T.qangle = (float*)(b + oAng); T.occ = b + oOcc;
+    T.qResult = (int*)(b + oRes); T.qDist = (int*)(b + oDist); T.qBin = (int*)(b + oBin);
+    T.kpMatch = d_kp_match; T.nMatches = d_nmatches; T.evals = M->dEvals;
+    T.stageTgt = search_smem_bytes(frame_stride, 1, true) <= kSearchSmemMax ? 1 : 0;
+    const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0);
+    if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(k_track_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+    CKM(cudaMemsetAsync(M->dEvals, 0, 8, st));
+    k_track_prepare<<<dim3((frame_stride + 255) / 256, nframes), 256, 0, st>>>(T);
+    k_track_grid<<<nframes, kGridThreads, 0, st>>>(T);
+    M->launches += 2;
+    if (nframes > 1) {
+        k_track_search<<<nframes - 1, kSearchThreads, smem, st>>>(T);
+        k_track_finish<<<nframes - 1, 256, 0, st>>>(T);
+        M->launches += 2;
+    } else {
+        CKM(cudaMemsetAsync(d_nmatches, 0, sizeof(int), st));
+    }
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+// evaluations of the last asynchronous tracking step (synchronises the handle's device)
+extern "C" long long orbm_track_evaluations(orbm_handle M) {
+    if (!M) return 0;
+    unsigned long long v = 0;
+    cudaSetDevice(M->device);
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    if (cudaMemcpy(&v, M->dEvals, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (long long)v;
+}

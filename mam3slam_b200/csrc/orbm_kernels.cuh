@@ -53,8 +53,8 @@ __global__ void k_grid_prepare(int n, const orbx_keypoint* __restrict__ kps, flo
 // the reference's push_back order).  n is a few thousand; the per-cell order is produced by letting each thread own a
 // contiguous range of cells and scan the keypoints of those cells in index order via a per-cell linked pass.
 constexpr int kGridThreads = 1024;
-__global__ void __launch_bounds__(kGridThreads) k_grid_build(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
-                                                             int* __restrict__ cellIdx) {
+__device__ __forceinline__ void grid_build_cta(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
+                                               int* __restrict__ cellIdx) {
     __shared__ int cnt[kGridCells];
     __shared__ int warpSum[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -105,6 +105,11 @@ __global__ void __launch_bounds__(kGridThreads) k_grid_build(int n, const int* _
     }
 }
 
+__global__ void __launch_bounds__(kGridThreads) k_grid_build(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
+                                                             int* __restrict__ cellIdx) {
+    grid_build_cta(n, cellOf, cellOff, cellIdx);
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 enum Rule : int {
     RULE_LOCAL_MAP = 0,   // M1: best <= TH_HIGH, reject iff bestLevel == bestLevel2 && best > nnratio * best2
@@ -129,6 +134,7 @@ struct SearchParams {
     const uint8_t* elig;         // target-side eligibility (may be NULL)
     uint8_t* occ;                // target-side occupancy bytes, in/out (NULL when state == 0)
     int state;                   // 0 = none, 1 = occupancy (claim on accept), 2 = steal-if-better (M5)
+    int stageTgt;                // 1 = the launch has room to stage the target frame (grid, kp4, descriptors) in shared memory
     int rule;
     float thF; int thI; float nnratio; int none2;
     int checkOri;
@@ -140,7 +146,17 @@ struct SearchParams {
     unsigned long long* evals;
 };
 
-constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 384;
+constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 384, kSlots = 32;
+
+// dynamic shared memory of a search CTA: slabs + match state (+ the staged target frame); host and device agree on this
+__host__ __device__ inline size_t search_smem_bytes(int n, int state, bool stage) {
+    size_t b = (size_t)kSlots * kSlab * 4;
+    if (state == 1) b += ((size_t)n + 15) & ~(size_t)15;
+    if (state == 2) b += (((size_t)n * 2 + 15) & ~(size_t)15) + (((size_t)n * 4 + 15) & ~(size_t)15);
+    if (stage) b = ((b + 15) & ~(size_t)15) + (size_t)n * 32 + (size_t)n * 16 + (size_t)(kGridCells + 1) * 4 + (size_t)n * 4 + 16;
+    return b;
+}
+constexpr size_t kSearchSmemMax = 200 * 1024;
 
 __device__ __forceinline__ int hamming8(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
     return __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z) + __popc(q[3] ^ a.w) +
@@ -153,10 +169,9 @@ __device__ __forceinline__ uint32_t pack_entry(int dist, int oct, int idx) { ret
 // Walks the candidates of query q in the reference's order; calls consume(active, entry) warp-synchronously for every
 // chunk of 32 candidate slots (active = this lane holds a candidate that passed all per-candidate tests).
 template <class Consume>
-__device__ __forceinline__ void walk_candidates(const SearchParams& P, int q, const uint32_t (&qd)[8], unsigned long long& nEval,
+__device__ __forceinline__ void walk_candidates(const SearchParams& P, const FrameDev& T, int q, const uint32_t (&qd)[8], unsigned long long& nEval,
                                                 Consume&& consume) {
     const int lane = threadIdx.x & 31;
-    const FrameDev& T = P.tgt;
     const uint4* drows = reinterpret_cast<const uint4*>(T.desc);
     if (P.source == 0) {
         const float4 w = P.qwin[q];
@@ -255,128 +270,185 @@ __device__ __forceinline__ void best_update(Best& b, uint32_t key, uint32_t entr
     else if (key < b.k2) { b.k2 = key; b.e2 = entry; }
 }
 
+// Resolve one query: best (and second best) among its candidates that are not blocked by the match state, acceptance by
+// the reference's rule, state update, result write.  Executed by one full warp.  `slab` holds the first min(count, kSlab)
+// candidates in scan order; more than kSlab candidates (rare) are re-walked here.
+__device__ __forceinline__ void resolve_query(const SearchParams& P, const FrameDev& T, int q, const uint32_t* slab, int count,
+                                              float qa, uint8_t* occS, uint16_t* mdS, int* m21S) {
+    const int lane = threadIdx.x & 31;
+    const bool lastMin = P.rule == RULE_LAST_MIN;
+    const bool needSecond = P.rule == RULE_LOCAL_MAP || P.rule == RULE_RATIO_LE || P.rule == RULE_RATIO_LT || P.rule == RULE_INIT;
+    Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = 0;
+    if (count <= kSlab) {
+        for (int p = lane; p < count; p += 32) {
+            const uint32_t e = slab[p];
+            if (blocked(P, occS, mdS, e)) continue;
+            const uint32_t key = ((e >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
+            best_update(b, key, e);
+        }
+    } else {
+        uint32_t qd[8];
+        const uint4 a = reinterpret_cast<const uint4*>(P.qdesc)[2 * q], c = reinterpret_cast<const uint4*>(P.qdesc)[2 * q + 1];
+        qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = c.x; qd[5] = c.y; qd[6] = c.z; qd[7] = c.w;
+        int pos0 = 0;
+        unsigned long long dummy = 0;
+        walk_candidates(P, T, q, qd, dummy, [&](bool ok, uint32_t entry) {
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            if (ok && !blocked(P, occS, mdS, entry)) {
+                const int p = pos0 + __popc(m & ((1u << lane) - 1));
+                const uint32_t key = ((entry >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
+                best_update(b, key, entry);
+            }
+            pos0 += __popc(m);
+        });
+    }
+    // warp merge: best = min k1; second = min over {k2 of the winner lane, k1 of the others}
+    const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
+    const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);
+    const unsigned wmask = __ballot_sync(0xffffffffu, win);
+    const int wl = wmask ? __ffs(wmask) - 1 : 0;
+    const uint32_t e1 = __shfl_sync(0xffffffffu, b.e1, wl);
+    uint32_t m2 = 0xffffffffu, e2 = 0;
+    if (needSecond) {
+        const uint32_t cand2 = win ? b.k2 : b.k1;
+        m2 = __reduce_min_sync(0xffffffffu, cand2);
+        const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
+        const int sl = smask ? __ffs(smask) - 1 : 0;
+        e2 = __shfl_sync(0xffffffffu, win ? b.e2 : b.e1, sl);
+    }
+    if (lane == 0) {
+        const bool has1 = m1 != 0xffffffffu, has2 = m2 != 0xffffffffu;
+        const int bestDist = has1 ? (int)(e1 >> 23) : 256;
+        const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
+        const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
+        const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
+        const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
+        bool accept = false;
+        switch (P.rule) {
+            case RULE_LOCAL_MAP:
+                accept = has1 && bestDist <= ORBM_TH_HIGH &&
+                         !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
+                break;
+            case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
+            case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+            case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+            case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
+            case RULE_LAST_MIN: accept = has1; break;
+            default: accept = false; break;
+        }
+        int bin = -1;
+        if (accept) {
+            if (P.state == 1) occS[bestIdx] = 1;
+            if (P.state == 2) {
+                const int prev = m21S[bestIdx];
+                if (prev >= 0) P.qResult[prev] = -1;          // the earlier, worse match loses the keypoint (:706-710)
+                m21S[bestIdx] = q;
+                mdS[bestIdx] = (uint16_t)bestDist;
+            }
+            if (P.checkOri) {
+                float rot = __fsub_rn(qa, T.kp4[bestIdx].z);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
+                if (bin == ORBM_HISTO_LENGTH) bin = 0;
+            }
+        }
+        P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
+        P.qDist[q] = bestDist;
+        P.qBin[q] = bin;
+    }
+    __syncwarp();
+}
+
+// gather + distances of query q into a slab (scan order preserved by ballot compaction); returns the candidate count
+__device__ __forceinline__ int gather_query(const SearchParams& P, const FrameDev& T, int q, uint32_t* slab, unsigned long long& nEval) {
+    const int lane = threadIdx.x & 31;
+    uint32_t qd[8];
+    const uint4 a = reinterpret_cast<const uint4*>(P.qdesc)[2 * q], b = reinterpret_cast<const uint4*>(P.qdesc)[2 * q + 1];
+    qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
+    int count = 0;
+    walk_candidates(P, T, q, qd, nEval, [&](bool ok, uint32_t entry) {
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            const int pos = count + __popc(m & ((1u << lane) - 1));
+            if (pos < kSlab) slab[pos] = entry;
+        }
+        count += __popc(m);
+    });
+    __syncwarp();
+    return count;
+}
+
 // One CTA per search (state != 0) or per slice of queries (state == 0).
-// dynamic smem: occupancy bytes [n] (state 1) | matched distance u16 [n] + match21 int [n] (state 2); slabs.
-__global__ void __launch_bounds__(kSearchThreads) k_search(const SearchParams P) {
-    extern __shared__ __align__(16) uint8_t dyn[];
-    __shared__ volatile int token;
+// dynamic smem: kSlots slabs | match state (occupancy bytes [n], or matched distance u16 [n] + match21 int [n]) | staged frame.
+// Stateful searches: warp 0 is the RESOLVER — it walks the queries in the reference's order and is the only warp that reads
+// or writes the match state; warps 1..15 are PRODUCERS that gather candidates / distances for later queries into a ring of
+// slabs (ready[slot] = q+1 publishes a slab, `done` frees it).  The sequential part of the reference loop thus costs two
+// shared-memory round trips and one redux per query, and no warp spins on the critical path.
+__device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, int ctaIdx, int nCtas) {
+    __shared__ volatile int ready[kSlots];
+    __shared__ volatile int done;
+    __shared__ int slotCount[kSlots];
+    __shared__ float slotAngle[kSlots];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = P.tgt.n;
-    uint32_t* slab = reinterpret_cast<uint32_t*>(dyn) + (size_t)wid * kSlab;
-    uint8_t* stateBase = dyn + (size_t)kSearchWarps * kSlab * 4;
+    uint32_t* slabs = reinterpret_cast<uint32_t*>(dyn);
+    uint8_t* stateBase = dyn + (size_t)kSlots * kSlab * 4;
     uint8_t* occS = stateBase;                                        // state 1
     uint16_t* mdS = reinterpret_cast<uint16_t*>(stateBase);           // state 2
     int* m21S = reinterpret_cast<int*>(stateBase + (((size_t)n * 2 + 15) & ~(size_t)15));
+    // The candidate walk is a chain of dependent loads (cell offsets -> keypoint index -> keypoint -> descriptor row).  When the
+    // target frame fits (a few thousand keypoints), stage all four arrays in shared memory once per CTA so that the chain
+    // runs at shared-memory latency instead of L2 latency.
+    FrameDev T = P.tgt;
+    if (P.stageTgt) {
+        const size_t so = search_smem_bytes(n, P.state, false);
+        uint4* sDesc = reinterpret_cast<uint4*>(dyn + ((so + 15) & ~(size_t)15));
+        float4* sKp4 = reinterpret_cast<float4*>(sDesc + 2 * (size_t)n);
+        int* sOff = reinterpret_cast<int*>(sKp4 + n);
+        int* sIdx = sOff + kGridCells + 1;
+        const uint4* gDesc = reinterpret_cast<const uint4*>(P.tgt.desc);
+        for (int i = tid; i < 2 * n; i += kSearchThreads) sDesc[i] = gDesc[i];
+        for (int i = tid; i < n; i += kSearchThreads) { sKp4[i] = P.tgt.kp4[i]; sIdx[i] = P.tgt.cellIdx[i]; }
+        for (int i = tid; i <= kGridCells; i += kSearchThreads) sOff[i] = P.tgt.cellOff[i];
+        T.desc = reinterpret_cast<const uint32_t*>(sDesc); T.kp4 = sKp4; T.cellOff = sOff; T.cellIdx = sIdx;
+    }
     if (P.state == 1) for (int i = tid; i < n; i += kSearchThreads) occS[i] = P.occ[i];
     if (P.state == 2) for (int i = tid; i < n; i += kSearchThreads) { mdS[i] = 0xffff; m21S[i] = -1; }
-    if (tid == 0) token = 0;
+    if (tid < kSlots) ready[tid] = 0;
+    if (tid == 0) done = 0;
     __syncthreads();
 
-    const int qStride = (P.state != 0) ? kSearchWarps : kSearchWarps * gridDim.x;
-    const int qFirst = (P.state != 0) ? wid : blockIdx.x * kSearchWarps + wid;
     unsigned long long nEval = 0;
-    const bool lastMin = P.rule == RULE_LAST_MIN;
-
-    for (int q = qFirst; q < P.nq; q += qStride) {
-        uint32_t qd[8];
-        {
-            const uint4 a = reinterpret_cast<const uint4*>(P.qdesc)[2 * q], b = reinterpret_cast<const uint4*>(P.qdesc)[2 * q + 1];
-            qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
+    if (P.state == 0) {
+        // independent queries: every warp gathers and resolves its own
+        uint32_t* slab = slabs + (size_t)wid * kSlab;
+        for (int q = ctaIdx * kSearchWarps + wid; q < P.nq; q += kSearchWarps * nCtas) {
+            const int count = gather_query(P, T, q, slab, nEval);
+            resolve_query(P, T, q, slab, count, P.checkOri ? P.qangle[q] : 0.f, occS, mdS, m21S);
         }
-        // ---- phase A: gather + distances into the slab (order preserved by ballot compaction) ----
-        int count = 0;
-        walk_candidates(P, q, qd, nEval, [&](bool ok, uint32_t entry) {
-            const unsigned m = __ballot_sync(0xffffffffu, ok);
-            if (ok) {
-                const int pos = count + __popc(m & ((1u << lane) - 1));
-                if (pos < kSlab) slab[pos] = entry;
-            }
-            count += __popc(m);
-        });
-        __syncwarp();
-        // ---- phase B: resolve in query order ----
-        if (P.state != 0) {
-            if (lane == 0) while (token != q) { }
+    } else if (wid == 0) {
+        for (int q = 0; q < P.nq; ++q) {
+            const int slot = q % kSlots;
+            if (lane == 0) while (ready[slot] != q + 1) { }
             __syncwarp();
             __threadfence_block();
+            resolve_query(P, T, q, slabs + (size_t)slot * kSlab, slotCount[slot], slotAngle[slot], occS, mdS, m21S);
+            if (lane == 0) { __threadfence_block(); done = q + 1; }
         }
-        Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = 0;
-        if (count <= kSlab) {
-            for (int p = lane; p < count; p += 32) {
-                const uint32_t e = slab[p];
-                if (blocked(P, occS, mdS, e)) continue;
-                const uint32_t key = ((e >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
-                best_update(b, key, e);
+    } else {
+        for (int q = wid - 1; q < P.nq; q += kSearchWarps - 1) {
+            const int slot = q % kSlots;
+            if (lane == 0) while (q - done >= kSlots) { __nanosleep(64); }
+            __syncwarp();
+            const int count = gather_query(P, T, q, slabs + (size_t)slot * kSlab, nEval);
+            if (lane == 0) {
+                slotCount[slot] = count;
+                slotAngle[slot] = P.checkOri ? P.qangle[q] : 0.f;
+                __threadfence_block();
+                ready[slot] = q + 1;
             }
-        } else {
-            // rare: more candidates than the slab holds -> redo the walk while holding the token
-            int pos0 = 0;
-            unsigned long long dummy = 0;
-            walk_candidates(P, q, qd, dummy, [&](bool ok, uint32_t entry) {
-                const unsigned m = __ballot_sync(0xffffffffu, ok);
-                if (ok && !blocked(P, occS, mdS, entry)) {
-                    const int p = pos0 + __popc(m & ((1u << lane) - 1));
-                    const uint32_t key = ((entry >> 23) << 20) | (uint32_t)(lastMin ? (0xfffff - p) : p);
-                    best_update(b, key, entry);
-                }
-                pos0 += __popc(m);
-            });
+            __syncwarp();
         }
-        // warp merge: best = min k1; second = min over {k2 of the winner lane, k1 of the others}
-        const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
-        const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);
-        const uint32_t cand2 = win ? b.k2 : b.k1;
-        const uint32_t m2 = __reduce_min_sync(0xffffffffu, cand2);
-        const unsigned wmask = __ballot_sync(0xffffffffu, win);
-        const int wl = wmask ? __ffs(wmask) - 1 : 0;
-        const uint32_t e1 = __shfl_sync(0xffffffffu, b.e1, wl);
-        const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
-        const int sl = smask ? __ffs(smask) - 1 : 0;
-        const uint32_t e2src = (cand2 == b.k1 && !win) ? b.e1 : b.e2;
-        const uint32_t e2 = __shfl_sync(0xffffffffu, e2src, sl);
-
-        if (lane == 0) {
-            const bool has1 = m1 != 0xffffffffu, has2 = m2 != 0xffffffffu;
-            const int bestDist = has1 ? (int)(e1 >> 23) : 256;
-            const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
-            const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
-            const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
-            const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
-            bool accept = false;
-            switch (P.rule) {
-                case RULE_LOCAL_MAP:
-                    accept = has1 && bestDist <= ORBM_TH_HIGH &&
-                             !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
-                    break;
-                case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
-                case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-                case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-                case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
-                case RULE_LAST_MIN: accept = has1; break;
-                default: accept = false; break;
-            }
-            int bin = -1;
-            if (accept) {
-                if (P.state == 1) occS[bestIdx] = 1;
-                if (P.state == 2) {
-                    const int prev = m21S[bestIdx];
-                    if (prev >= 0) P.qResult[prev] = -1;          // the earlier, worse match loses the keypoint (:706-710)
-                    m21S[bestIdx] = q;
-                    mdS[bestIdx] = (uint16_t)bestDist;
-                }
-                if (P.checkOri) {
-                    float rot = __fsub_rn(P.qangle[q], P.tgt.kp4[bestIdx].z);
-                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                    bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
-                    if (bin == ORBM_HISTO_LENGTH) bin = 0;
-                }
-            }
-            P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
-            P.qDist[q] = bestDist;
-            P.qBin[q] = bin;
-            if (P.state != 0) { __threadfence_block(); token = q + 1; }
-        }
-        __syncwarp();
     }
     // evaluation count (reporting only)
 #pragma unroll
@@ -388,14 +460,20 @@ __global__ void __launch_bounds__(kSearchThreads) k_search(const SearchParams P)
     }
 }
 
+
+__global__ void __launch_bounds__(kSearchThreads) k_search(const SearchParams P) {
+    extern __shared__ __align__(16) uint8_t dyn[];
+    search_cta(P, dyn, blockIdx.x, gridDim.x);
+}
+
 // rotation-consistency epilogue (e.g. src/ORBmatcher.cc:1862-1884): histogram of accept events, three maxima, drop the rest
-__global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
+__device__ __forceinline__ void rot_filter_cta(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
     __shared__ int hist[ORBM_HISTO_LENGTH];
     __shared__ int keep[3];
     const int tid = threadIdx.x;
     if (tid < ORBM_HISTO_LENGTH) hist[tid] = 0;
     __syncthreads();
-    for (int q = tid; q < nq; q += 256) { const int b = qBin[q]; if (b >= 0) atomicAdd(&hist[b], 1); }
+    for (int q = tid; q < nq; q += blockDim.x) { const int b = qBin[q]; if (b >= 0) atomicAdd(&hist[b], 1); }
     __syncthreads();
     if (tid == 0) {
         int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
@@ -410,10 +488,102 @@ __global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restric
         keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
     }
     __syncthreads();
-    for (int q = tid; q < nq; q += 256) {
+    for (int q = tid; q < nq; q += blockDim.x) {
         const int b = qBin[q];
         if (b >= 0 && b != keep[0] && b != keep[1] && b != keep[2]) qResult[q] = -1;
     }
+}
+__global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
+    rot_filter_cta(nq, qBin, qResult);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Device-resident tracking step (BASELINE config[1]): SearchByProjection(Cur = frame i, Last = frame i-1, th, bMono)
+// (src/ORBmatcher.cc:1676-1887) for every consecutive pair of a batch of extractor results that never left HBM.
+// Every keypoint of the last frame stands for a map point projected at its own position (identity motion prior).
+struct TrackBatch {
+    int nframes, stride, countStride;
+    const orbx_keypoint* kps; const uint32_t* desc; const int* counts;     // extractor outputs (outKp / outDesc / outCnt)
+    float minX, minY, invW, invH;
+    float th, thF; int checkOri; int stageTgt;
+    float scale[16];
+    // per-frame work buffers, [nframes x stride] unless noted
+    float4* kp4; int* cellOf; int* cellIdx; int* cellOff /* nframes x (kGridCells+1) */;
+    float4* qwin; int2* qlev; float* qangle; uint8_t* occ;
+    int* qResult; int* qDist; int* qBin;
+    int* kpMatch; int* nMatches /* nframes */;
+    unsigned long long* evals;
+};
+
+__global__ void k_track_prepare(const TrackBatch T) {
+    const int f = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T.stride) return;
+    const size_t at = (size_t)f * T.stride + i;
+    T.kpMatch[at] = -1; T.occ[at] = 0; T.qBin[at] = -1; T.qResult[at] = -1;
+    const int n = min(T.counts[f * T.countStride], T.stride);
+    if (i >= n) return;
+    const orbx_keypoint k = T.kps[at];
+    T.kp4[at] = make_float4(k.x, k.y, k.angle, __int_as_float(k.octave));
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(k.x, T.minX), T.invW));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(k.y, T.minY), T.invH));
+    T.cellOf[at] = (px < 0 || px >= kGridCols || py < 0 || py >= kGridRows) ? -1 : px * kGridRows + py;
+    // the keypoint as a query into the NEXT frame: window th * scale[octave], levels [octave-1, octave+1] (:1731-1741)
+    const int o = k.octave;
+    T.qwin[at] = make_float4(k.x, k.y, __fmul_rn(T.th, T.scale[o & 15]), 0.f);
+    T.qlev[at] = make_int2(o - 1, o + 1);            // bCheckLevels is true: maxLevel = o+1 >= 0
+    T.qangle[at] = k.angle;
+}
+
+__global__ void __launch_bounds__(kGridThreads) k_track_grid(const TrackBatch T) {
+    const int f = blockIdx.x;
+    const int n = min(T.counts[f * T.countStride], T.stride);
+    grid_build_cta(n, T.cellOf + (size_t)f * T.stride, T.cellOff + (size_t)f * (kGridCells + 1), T.cellIdx + (size_t)f * T.stride);
+}
+
+__global__ void __launch_bounds__(kSearchThreads) k_track_search(const TrackBatch T) {
+    extern __shared__ __align__(16) uint8_t dyn[];
+    const int cur = blockIdx.x + 1, last = blockIdx.x;
+    SearchParams P;
+    P.tgt.n = min(T.counts[cur * T.countStride], T.stride);
+    P.tgt.kp4 = T.kp4 + (size_t)cur * T.stride;
+    P.tgt.desc = T.desc + (size_t)cur * T.stride * 8;
+    P.tgt.cellOff = T.cellOff + (size_t)cur * (kGridCells + 1);
+    P.tgt.cellIdx = T.cellIdx + (size_t)cur * T.stride;
+    P.tgt.minX = T.minX; P.tgt.minY = T.minY; P.tgt.invW = T.invW; P.tgt.invH = T.invH;
+    P.nq = min(T.counts[last * T.countStride], T.stride);
+    P.source = 0;
+    P.qwin = T.qwin + (size_t)last * T.stride; P.qlev = T.qlev + (size_t)last * T.stride;
+    P.qrun = nullptr; P.bowIdx = nullptr;
+    P.qdesc = T.desc + (size_t)last * T.stride * 8;
+    P.qangle = T.qangle + (size_t)last * T.stride;
+    P.elig = nullptr;
+    P.occ = T.occ + (size_t)cur * T.stride;
+    P.stageTgt = T.stageTgt;
+    P.state = 1; P.rule = RULE_BEST_LE; P.thF = T.thF; P.thI = 0; P.nnratio = 0.f; P.none2 = 256;
+    P.checkOri = T.checkOri; P.chi2 = 0; P.invSigma2 = nullptr;
+    P.tri = 0; P.coarse = 0; P.ep0 = P.ep1 = 0.f; P.scale2 = nullptr; P.sigma2 = nullptr;
+    P.qResult = T.qResult + (size_t)cur * T.stride; P.qDist = T.qDist + (size_t)cur * T.stride; P.qBin = T.qBin + (size_t)cur * T.stride;
+    P.evals = T.evals;
+    search_cta(P, dyn, 0, 1);
+}
+
+// rotation filter + scatter into the reference's output (CurrentFrame.mvpMapPoints[i2] = pMP  ->  kpMatch[i2] = query)
+__global__ void __launch_bounds__(256) k_track_finish(const TrackBatch T) {
+    __shared__ int cnt;
+    const int cur = blockIdx.x + 1, last = blockIdx.x;
+    const int nq = min(T.counts[last * T.countStride], T.stride);
+    int* qRes = T.qResult + (size_t)cur * T.stride;
+    if (threadIdx.x == 0) cnt = 0;
+    if (T.checkOri) rot_filter_cta(nq, T.qBin + (size_t)cur * T.stride, qRes);
+    __syncthreads();
+    int mine = 0;
+    for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+        const int r = qRes[q];
+        if (r >= 0) { T.kpMatch[(size_t)cur * T.stride + r] = q; ++mine; }
+    }
+    if (mine) atomicAdd(&cnt, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) { T.nMatches[cur] = cnt; if (cur == 1) T.nMatches[0] = 0; }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

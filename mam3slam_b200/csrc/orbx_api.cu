@@ -17,7 +17,8 @@ const int kPatternTable[1024] = {
 struct Extractor {
     orbx_config cfg;
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;
+    int chunk = 0;                   // frames per pipelined sub-batch of the host path (0 = auto)
     std::string err;
     long long launches = 0;
 
@@ -195,9 +196,9 @@ int configureShape(Extractor* E, int W, int H) {
     if (E->poolCap > 60000) { E->err = "nfeatures too large"; return ORBX_ERR_UNSUPPORTED; }
     E->scanCap = std::max(std::max(E->poolCap, maxCells), 64) + 8;
     E->treeSmem = tree_smem_layout(E->poolCap, E->scanCap, nullptr, nullptr);
-    E->fastTilePitch = (maxCellW + 6 + 3 + 3) & ~3;
+    E->fastTilePitch = (((maxCellW + 6 + 3 + 3) >> 2) + 1) * 2 + 1;      // words per row of each u16x2 pair copy (odd: spreads banks)
     E->fastTileRows = maxCellH + 6;
-    E->fastSmem = (size_t)E->fastTileRows * E->fastTilePitch + (size_t)(maxCellH + 2) * (maxCellW + 2) + 16;
+    E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (size_t)(maxCellH + 2) * (maxCellW + 2) + 16;
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
     CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -237,41 +238,43 @@ int configureShape(Extractor* E, int W, int H) {
     return ORBX_OK;
 }
 
-// The launch sequence of one pass over `n` frames whose level 0 lives at l0.
-int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st) {
+// The launch sequence of one pass over frames [fb, fb+n) of the handle's buffers; level 0 of frame fb+i lives at
+// l0.base + i*l0.frameBytes.
+int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb = 0) {
     const DevGeom& g = E->geom;
     const int L = g.nlevels;
-    const bool tm = E->timing;
+    const bool tm = E->timing && fb == 0;
     int evi = 0;
     auto mark = [&]() { if (tm) cudaEventRecord(E->ev[evi++], st); };
+    l0.base -= (size_t)fb * l0.frameBytes;          // kernels index level 0 by the global frame slot fb+i
     mark();
     for (int l = 1; l < L; ++l) {
         dim3 grid((g.lv[l].w + 127) / 128, (g.lv[l].h + 7) / 8, n), block(32, 8);
-        k_pyr_level<<<grid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps);
+        k_pyr_level<<<grid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);
         ++E->launches;
     }
     mark();
     k_fast_cells<<<dim3(g.nCells, n), kFastThreads, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount,
-                                                                        E->fastTilePitch, E->fastTileRows);
+                                                                        E->fastTilePitch, E->fastTileRows, fb);
     ++E->launches;
     mark();
     k_octree<<<dim3(L, n), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,
-                                                            E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap);
+                                                            E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb);
     ++E->launches;
     mark();
-    k_blur7<<<dim3(E->blurTilesTotal, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles);
+    k_blur7<<<dim3(E->blurTilesTotal, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
     ++E->launches;
     mark();
-    k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork);
+    k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork, fb);
     ++E->launches;
     mark();
     k_orient_brief<<<dim3((g.outCap + kDescWarps - 1) / kDescWarps, n), kDescWarps * 32, 0, st>>>(
-        E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc);
+        E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
     ++E->launches;
     mark();
     CK(cudaGetLastError());
-    E->lastFrames = n;
-    E->lastL0 = l0;
+    if (fb == 0) { E->lastFrames = n; E->lastL0 = l0; }
+    else E->lastFrames = std::max(E->lastFrames, fb + n);
     return ORBX_OK;
 }
 
@@ -332,6 +335,8 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     cudaError_t e;
     if ((e = cudaSetDevice(E->device)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
+    if ((e = cudaStreamCreateWithFlags(&E->stream2, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
+    if (const char* c = getenv("ORBX_CHUNK")) E->chunk = atoi(c);
     for (auto& ev : E->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e);
     // algorithm constants: circular-patch half-widths (:453-468) and the BRIEF pattern
     int umax[16];
@@ -355,9 +360,11 @@ void orbx_destroy(orbx_handle h) {
     E_FROM(h);
     cudaSetDevice(E->device);
     cudaStreamSynchronize(E->stream);
+    cudaStreamSynchronize(E->stream2);
     freeShape(E);
     for (auto& ev : E->ev) if (ev) cudaEventDestroy(ev);
     if (E->stream) cudaStreamDestroy(E->stream);
+    if (E->stream2) cudaStreamDestroy(E->stream2);
     delete h;
 }
 
@@ -413,6 +420,16 @@ int stageResults(Extractor* E, int n, cudaStream_t st) {
 
 extern "C" {
 
+// true iff p points into page-locked host memory (cudaMallocHost / cudaHostRegister): copies from/to it are truly async
+static bool isPinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+// Host path.  A batch is cut into sub-batches that alternate between the handle's two streams, so that the H2D copy of
+// one sub-batch overlaps the kernels of the previous one and its D2H the kernels of the next.  Page-locked caller buffers
+// are used in place (no staging copy); pageable ones go through the pinned staging area.
 int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int width, int height, int stride,
                        int lap0, int lap1, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_out) {
     if (!h || !imgs || nimg <= 0 || !n_out || !mono_out) return ORBX_ERR_INVALID;
@@ -426,27 +443,80 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int 
     const int B = E->cfg.max_batch;
     const int p0 = g.lv[0].pitch;
     const size_t plane = g.lv[0].planeBytes;
+    int C = E->chunk > 0 ? E->chunk : (B >= 32 ? B / 4 : (B >= 8 ? B / 2 : B));
+    C = std::max(1, std::min(C, B));
+    const bool inPinned = isPinned(imgs[0]) && isPinned(imgs[nimg - 1]);
+    const bool kpPinned = kps && isPinned(kps) && isPinned(kps + (size_t)nimg * cap - 1);
+    const bool dsPinned = desc && isPinned(desc) && isPinned(desc + (size_t)nimg * cap * 32 - 1);
+    const int rowsOut = std::min(cap, g.outCap);
+    cudaStream_t streams[2] = {E->stream, E->stream2};
     int status = ORBX_OK;
     for (int base = 0; base < nimg; base += B) {
         const int n = std::min(B, nimg - base);
-        for (int f = 0; f < n; ++f) {
-            const uint8_t* src = imgs[base + f];
-            if (!src) return ORBX_ERR_INVALID;
-            uint8_t* dst = E->hImg + (size_t)f * plane;
-            if (stride == p0) memcpy(dst, src, (size_t)p0 * (height - 1) + width);
-            else for (int y = 0; y < height; ++y) memcpy(dst + (size_t)y * p0, src + (size_t)y * stride, width);
+        for (int c0 = 0, ci = 0; c0 < n; c0 += C, ++ci) {
+            const int nc = std::min(C, n - c0);
+            cudaStream_t st = streams[ci & 1];
+            // Rows are copied with the caller's stride (one linear DMA per frame, or per sub-batch when the frames are
+            // contiguous) and the kernels read level 0 with that pitch: a pitched 2-D copy of 752-byte rows runs far below
+            // PCIe speed.  Strides that do not fit the slot fall back to re-pitching.
+            const size_t frameLin = (size_t)stride * (height - 1) + width;
+            const bool linear = (size_t)stride * height <= plane;
+            bool contiguous = linear;
+            for (int f = 0; f < nc; ++f) {
+                if (!imgs[base + c0 + f]) return ORBX_ERR_INVALID;
+                if (f && imgs[base + c0 + f] != imgs[base + c0 + f - 1] + (size_t)stride * height) contiguous = false;
+            }
+            const size_t slot = linear ? (size_t)stride * height : plane;         // distance between frames on the device
+            const int pitch0 = linear ? stride : p0;
+            uint8_t* dchunk = E->dLvl0 + (size_t)c0 * slot;
+            if (inPinned) {
+                if (contiguous) {
+                    CK(cudaMemcpyAsync(dchunk, imgs[base + c0], slot * (nc - 1) + frameLin, cudaMemcpyHostToDevice, st));
+                } else {
+                    for (int f = 0; f < nc; ++f) {
+                        if (linear) CK(cudaMemcpyAsync(dchunk + (size_t)f * slot, imgs[base + c0 + f], frameLin, cudaMemcpyHostToDevice, st));
+                        else CK(cudaMemcpy2DAsync(dchunk + (size_t)f * slot, p0, imgs[base + c0 + f], stride, width, height, cudaMemcpyHostToDevice, st));
+                    }
+                }
+            } else {
+                uint8_t* hchunk = E->hImg + (size_t)c0 * slot;
+                for (int f = 0; f < nc; ++f) {
+                    const uint8_t* src = imgs[base + c0 + f];
+                    uint8_t* hdst = hchunk + (size_t)f * slot;
+                    if (linear) memcpy(hdst, src, frameLin);
+                    else for (int y = 0; y < height; ++y) memcpy(hdst + (size_t)y * p0, src + (size_t)y * stride, width);
+                }
+                CK(cudaMemcpyAsync(dchunk, hchunk, slot * (nc - 1) + (linear ? frameLin : plane), cudaMemcpyHostToDevice, st));
+            }
+            Level0 l0{dchunk, slot, pitch0};
+            if ((rc = runPass(E, l0, nc, lap0, lap1, st, c0))) return rc;
+            CK(cudaMemcpyAsync(E->hCnt + 2 * c0, E->dOutCnt + 2 * c0, (size_t)2 * nc * sizeof(int), cudaMemcpyDeviceToHost, st));
+            if (kps) {
+                if (kpPinned)
+                    CK(cudaMemcpy2DAsync(kps + (size_t)(base + c0) * cap, (size_t)cap * sizeof(orbx_keypoint), E->dOutKp + (size_t)c0 * g.outCap,
+                                         (size_t)g.outCap * sizeof(orbx_keypoint), (size_t)rowsOut * sizeof(orbx_keypoint), nc, cudaMemcpyDeviceToHost, st));
+                else
+                    CK(cudaMemcpyAsync(E->hKp + (size_t)c0 * g.outCap, E->dOutKp + (size_t)c0 * g.outCap, (size_t)nc * g.outCap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+            }
+            if (desc) {
+                if (dsPinned)
+                    CK(cudaMemcpy2DAsync(desc + (size_t)(base + c0) * cap * 32, (size_t)cap * 32, E->dOutDesc + (size_t)c0 * g.outCap * 32,
+                                         (size_t)g.outCap * 32, (size_t)rowsOut * 32, nc, cudaMemcpyDeviceToHost, st));
+                else
+                    CK(cudaMemcpyAsync(E->hDesc + (size_t)c0 * g.outCap * 32, E->dOutDesc + (size_t)c0 * g.outCap * 32, (size_t)nc * g.outCap * 32, cudaMemcpyDeviceToHost, st));
+            }
         }
-        CK(cudaMemcpyAsync(E->dLvl0, E->hImg, plane * n, cudaMemcpyHostToDevice, E->stream));
-        Level0 l0{E->dLvl0, plane, p0};
-        if ((rc = runPass(E, l0, n, lap0, lap1, E->stream))) return rc;
-        if ((rc = stageResults(E, n, E->stream))) return rc;
+        CK(cudaStreamSynchronize(E->stream));
+        CK(cudaStreamSynchronize(E->stream2));
+        E->lastFrames = n;
+        if ((rc = collectStageTimes(E))) return rc;
         for (int f = 0; f < n; ++f) {
             const int cnt = E->hCnt[2 * f];
             n_out[base + f] = cnt;
             mono_out[base + f] = E->hCnt[2 * f + 1];
             if (cnt > cap) { status = ORBX_ERR_CAPACITY; continue; }
-            if (kps) memcpy(kps + (size_t)(base + f) * cap, E->hKp + (size_t)f * g.outCap, (size_t)cnt * sizeof(orbx_keypoint));
-            if (desc) memcpy(desc + (size_t)(base + f) * cap * 32, E->hDesc + (size_t)f * g.outCap * 32, (size_t)cnt * 32);
+            if (kps && !kpPinned) memcpy(kps + (size_t)(base + f) * cap, E->hKp + (size_t)f * g.outCap, (size_t)cnt * sizeof(orbx_keypoint));
+            if (desc && !dsPinned) memcpy(desc + (size_t)(base + f) * cap * 32, E->hDesc + (size_t)f * g.outCap * 32, (size_t)cnt * 32);
         }
     }
     return status;
@@ -491,6 +561,17 @@ int orbx_results_device(orbx_handle h, int frame, const orbx_keypoint** d_kps, c
     if (d_desc) *d_desc = reinterpret_cast<const uint32_t*>(E->dOutDesc + (size_t)frame * E->geom.outCap * 32);
     if (n_out) *n_out = cnt[0];
     if (mono_out) *mono_out = cnt[1];
+    return ORBX_OK;
+}
+
+int orbx_results_batch_device(orbx_handle h, const orbx_keypoint** d_kps, const uint8_t** d_desc, const int** d_counts, int* frame_stride) {
+    if (!h) return ORBX_ERR_INVALID;
+    E_FROM(h);
+    if (!E->W) return ORBX_ERR_INVALID;
+    if (d_kps) *d_kps = E->dOutKp;
+    if (d_desc) *d_desc = E->dOutDesc;
+    if (d_counts) *d_counts = E->dOutCnt;
+    if (frame_stride) *frame_stride = E->geom.outCap;
     return ORBX_OK;
 }
 

@@ -38,12 +38,12 @@ __host__ __device__ inline size_t tree_smem_layout(int P, int scanCap, TreeSmem*
 __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
                                                          const uint32_t* __restrict__ cand, const int* __restrict__ cellCount,
                                                          uint64_t* qtA, uint64_t* qtB, uint64_t* lvlKp, int* lvlCnt,
-                                                         int P, int scanCap) {
+                                                         int P, int scanCap, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int sW[33];
     TreeSmem S;
     tree_smem_layout(P, scanCap, &S, smem);
-    const int l = blockIdx.x, frame = blockIdx.y;
+    const int l = blockIdx.x, frame = frameBase + blockIdx.y;
     const LevelGeom& L = g->lv[l];
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     const int cb = L.cellBegin, nc = L.cellEnd - L.cellBegin;
@@ -95,10 +95,10 @@ struct WorkItem { short level; short pad; int x, y; int dst; };   // keypoint in
 constexpr int kFinalThreads = 256;
 __global__ void __launch_bounds__(kFinalThreads) k_finalize(const DevGeom* __restrict__ g, const uint64_t* __restrict__ lvlKp,
                                                             const int* __restrict__ lvlCnt, int lap0, int lap1,
-                                                            orbx_keypoint* outKp, int* outCnt, WorkItem* work) {
+                                                            orbx_keypoint* outKp, int* outCnt, WorkItem* work, int frameBase) {
     __shared__ int sOff[kMaxLevels + 1];
     __shared__ int sWarp[kFinalThreads / 32 + 1];
-    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int frame = frameBase + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int L = g->nlevels;
     if (tid == 0) {
         int o = 0;
@@ -189,8 +189,8 @@ constexpr int kDescWarps = 8;
 __global__ void __launch_bounds__(kDescWarps * 32) k_orient_brief(const DevGeom* __restrict__ g, Level0 l0,
                                                                   const WorkItem* __restrict__ work,
                                                                   const int* __restrict__ outCnt, orbx_keypoint* outKp,
-                                                                  uint8_t* outDesc) {
-    const int frame = blockIdx.y;
+                                                                  uint8_t* outDesc, int frameBase) {
+    const int frame = frameBase + blockIdx.y;
     const int o = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (o >= outCnt[2 * frame]) return;

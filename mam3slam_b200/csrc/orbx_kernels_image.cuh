@@ -25,10 +25,10 @@ __device__ __forceinline__ const uint8_t* level_ptr(const DevGeom* g, const Leve
 // bytes and writes 1 byte per output pixel; taps come from a table built once per shape on the host.
 // grid (ceil(w/128), ceil(h/8), B), block (32, 8).
 __global__ void __launch_bounds__(256) k_pyr_level(const DevGeom* __restrict__ g, Level0 l0, int l,
-                                                   const ResizeTap* __restrict__ taps) {
+                                                   const ResizeTap* __restrict__ taps, int frameBase) {
     const LevelGeom& D = g->lv[l];
     const LevelGeom& S = g->lv[l - 1];
-    const int frame = blockIdx.z;
+    const int frame = frameBase + blockIdx.z;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
     const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (y >= D.h || x4 >= D.w) return;
@@ -109,66 +109,119 @@ __device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
 // grid (nCells, B), block 256.  dynamic smem: tile + score tile.
 constexpr int kFastThreads = 256;
 
+// FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes (VIMNMX3.U16x2 / native on sm_100a:
+// 64 3-input min/max per clk per SM, tools/microbench.cu).  d'[k] = ring[k] - v + 256 per lane (no borrow between lanes:
+// 1 <= d' <= 511), sliding 9-window minima and maxima as min3(min3, min3, min3), then
+//   s = max( max_k min9[k] - 256, 256 - min_k max9[k], 0 ).
+__device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t (&r)[16]) {
+    const uint32_t c = 0x01000100u - v2;
+    uint32_t d[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) d[k] = r[k] + c;
+    uint32_t tmin[16], tmax[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        tmin[k] = __vimin3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        tmax[k] = __vimax3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+    }
+    uint32_t a9[16], b9[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        a9[k] = __vimin3_u16x2(tmin[k], tmin[(k + 3) & 15], tmin[(k + 6) & 15]);
+        b9[k] = __vimax3_u16x2(tmax[k], tmax[(k + 3) & 15], tmax[(k + 6) & 15]);
+    }
+    uint32_t A = __vimax3_u16x2(a9[0], a9[1], a9[2]), B = __vimin3_u16x2(b9[0], b9[1], b9[2]);
+#pragma unroll
+    for (int k = 3; k < 15; k += 2) { A = __vimax3_u16x2(A, a9[k], a9[k + 1]); B = __vimin3_u16x2(B, b9[k], b9[k + 1]); }
+    A = __vmaxu2(A, a9[15]); B = __vminu2(B, b9[15]);
+    const uint32_t s = __vimax3_u16x2(A, 0x02000200u - B, 0x01000100u);
+    return s - 0x01000100u;
+}
+
+// One CTA per reference FAST cell.  The cell's pixels (+3 ring halo) are read with aligned 32-bit loads and expanded in
+// shared memory to u16 lanes in TWO copies (pairs starting at even / odd x), so that any two horizontally adjacent pixels
+// are one aligned 32-bit shared load; each thread then computes the strength of two pixels per pass (fast_strength_x2),
+// once per pixel at minThFAST.  The reference's per-cell logic runs on the shared score tile: NMS at iniThFAST; if that
+// leaves the cell empty, NMS at minThFAST (src/ORBextractor.cc:826-846).  Neighbours outside the cell's tested interior
+// count as 0, exactly like a cv::FAST call on the sub-image.  Survivors are compacted in raster order into the cell's
+// fixed slot range.  grid (nCells, B), block 256.  dynamic smem: 2 x rows x pitchW words + score tile.
 __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
                                                              const FastCell* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ cellCount,
-                                                             int tilePitchMax, int tileRowsMax) {
+                                                             int pitchW, int tileRowsMax, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
     const FastCell c = cells[blockIdx.x];
-    const int frame = blockIdx.y;
+    const int frame = frameBase + blockIdx.y;
     const int tid = threadIdx.x;
     int pitch;
     const uint8_t* img = level_ptr(g, l0, c.level, frame, &pitch);
     const int w = c.w, h = c.h;
     const int tw = w + 6, th = h + 6;
-    uint8_t* tile = smem;                                  // th rows x tp
+    uint32_t* SA = reinterpret_cast<uint32_t*>(smem);                // pairs starting at even X: (X, X+1)
+    uint32_t* SB = SA + (size_t)tileRowsMax * pitchW;                // pairs starting at odd X
+    uint8_t* score = reinterpret_cast<uint8_t*>(SB + (size_t)tileRowsMax * pitchW);   // (h+2) x (w+2), apron = 0
+    const int sp = w + 2;
     const int gx0 = c.x0 - 3, gy0 = c.y0 - 3;
     const uint8_t* origin = img + (size_t)gy0 * pitch + gx0;
-    const int a = (int)((uintptr_t)origin & 3);            // leading bytes so that rows start word-aligned
     const bool aligned = (pitch & 3) == 0;
-    const int tp = tilePitchMax;                            // multiple of 4
-    uint8_t* score = smem + (size_t)tileRowsMax * tp;      // (h+2) x (w+2), apron = 0
-    const int sp = w + 2;
+    const int a = aligned ? (int)((uintptr_t)origin & 3) : 0;        // X = tile x + a; rows start word-aligned when aligned
 
     if (aligned) {
         const int wordsPerRow = (tw + a + 3) >> 2;
         const uint8_t* base = origin - a;
         for (int i = tid; i < wordsPerRow * th; i += kFastThreads) {
-            int ry = i / wordsPerRow, rw = i - ry * wordsPerRow;
-            uint32_t v = *reinterpret_cast<const uint32_t*>(base + (size_t)ry * pitch + 4 * rw);
-            *reinterpret_cast<uint32_t*>(tile + ry * tp + 4 * rw) = v;
+            const int ry = i / wordsPerRow, rw = i - ry * wordsPerRow;
+            const uint8_t* src = base + (size_t)ry * pitch + 4 * rw;
+            const uint32_t v = *reinterpret_cast<const uint32_t*>(src);
+            const uint32_t nx = src[4];
+            const uint32_t p0 = v & 255u, p1 = (v >> 8) & 255u, p2 = (v >> 16) & 255u, p3 = v >> 24;
+            uint32_t* ra = SA + ry * pitchW + 2 * rw;
+            uint32_t* rb = SB + ry * pitchW + 2 * rw;
+            ra[0] = p0 | (p1 << 16); ra[1] = p2 | (p3 << 16);
+            rb[0] = p1 | (p2 << 16); rb[1] = p3 | (nx << 16);
         }
     } else {
-        for (int i = tid; i < tw * th; i += kFastThreads) {
-            int ry = i / tw, rx = i - ry * tw;
-            tile[ry * tp + rx + a] = origin[(size_t)ry * pitch + rx];
+        const int pairsPerRow = (tw + 2) >> 1;
+        for (int i = tid; i < pairsPerRow * th; i += kFastThreads) {
+            const int ry = i / pairsPerRow, rp = i - ry * pairsPerRow;
+            const uint8_t* src = origin + (size_t)ry * pitch + 2 * rp;
+            const uint32_t p0 = src[0], p1 = src[1], p2 = src[2];
+            SA[ry * pitchW + rp] = p0 | (p1 << 16);
+            SB[ry * pitchW + rp] = p1 | (p2 << 16);
         }
     }
     for (int i = tid; i < (h + 2) * sp; i += kFastThreads) score[i] = 0;
     __syncthreads();
 
     const int minTh = g->minTh, iniTh = g->iniTh;
-    const int npx = w * h;
-    for (int p = tid; p < npx; p += kFastThreads) {
-        const int py = p / w, px = p - py * w;
-        const uint8_t* ctr = tile + (py + 3) * tp + px + 3 + a;
-        const int v = ctr[0];
-        // compass pre-test: every 9-arc contains at least two of ring points 0,4,8,12
-        const int r0 = ctr[3 * tp], r4 = ctr[3], r8 = ctr[-3 * tp], r12 = ctr[-3];
-        const int hi = (r0 > v + minTh) + (r4 > v + minTh) + (r8 > v + minTh) + (r12 > v + minTh);
-        const int lo = (r0 < v - minTh) + (r4 < v - minTh) + (r8 < v - minTh) + (r12 < v - minTh);
-        if (hi < 2 && lo < 2) continue;
-        int r[16];
-        r[0] = r0;               r[1] = ctr[3 * tp + 1];   r[2] = ctr[2 * tp + 2];   r[3] = ctr[tp + 3];
-        r[4] = r4;               r[5] = ctr[-tp + 3];      r[6] = ctr[-2 * tp + 2];  r[7] = ctr[-3 * tp + 1];
-        r[8] = r8;               r[9] = ctr[-3 * tp - 1];  r[10] = ctr[-2 * tp - 2]; r[11] = ctr[-tp - 3];
-        r[12] = r12;             r[13] = ctr[tp - 3];      r[14] = ctr[2 * tp - 2];  r[15] = ctr[3 * tp - 1];
-        const int s = fast_strength(v, r);
-        if (s > minTh) score[(py + 1) * sp + px + 1] = (uint8_t)s;
+    {
+        // tested pixel (px, py) = tile (px+3, py+3); pair start X = px0 + 3 + a + dx with px0 even
+        const int ap = a + 3;
+        const uint32_t* E = ((ap & 1) ? SB : SA) + (ap >> 1);          // even dx: index px0/2 + dx/2
+        const uint32_t* O = ((ap & 1) ? SA : SB) + ((ap + 1) >> 1);    // odd dx : index px0/2 + (dx-1)/2
+        const int pw = (w + 1) >> 1;
+        const int npairs = pw * h;
+        const int P = pitchW;
+        for (int p = tid; p < npairs; p += kFastThreads) {
+            const int py = p / pw, pc = p - py * pw;
+            const int b = (py + 3) * P + pc;
+            const uint32_t v2 = E[b];
+            uint32_t r[16];
+            r[0] = E[b + 3 * P];       r[1] = O[b + 3 * P];       r[2] = E[b + 2 * P + 1];   r[3] = O[b + P + 1];
+            r[4] = O[b + 1];           r[5] = O[b - P + 1];       r[6] = E[b - 2 * P + 1];   r[7] = O[b - 3 * P];
+            r[8] = E[b - 3 * P];       r[9] = O[b - 3 * P - 1];   r[10] = E[b - 2 * P - 1];  r[11] = O[b - P - 2];
+            r[12] = O[b - 2];          r[13] = O[b + P - 2];      r[14] = E[b + 2 * P - 1];  r[15] = O[b + 3 * P - 1];
+            const uint32_t s2 = fast_strength_x2(v2, r);
+            const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
+            uint8_t* sc = score + (py + 1) * sp + 2 * pc + 1;
+            if (s0 > minTh) sc[0] = (uint8_t)s0;
+            if (s1 > minTh && 2 * pc + 1 < w) sc[1] = (uint8_t)s1;
+        }
     }
     __syncthreads();
 
     // NMS at both thresholds over a contiguous raster chunk per thread (<= 32 pixels)
+    const int npx = w * h;
     const int per = (npx + kFastThreads - 1) / kFastThreads;
     const int pb = tid * per, pe = min(pb + per, npx);
     uint32_t keepIni = 0, keepMin = 0;
@@ -240,10 +293,10 @@ __device__ __forceinline__ int reflect101_dev(int p, int n) {
 
 struct BlurTiles { int start[kMaxLevels + 1]; int tilesX[kMaxLevels]; };
 
-__global__ void __launch_bounds__(256) k_blur7(const DevGeom* __restrict__ g, Level0 l0, BlurTiles bt) {
+__global__ void __launch_bounds__(256) k_blur7(const DevGeom* __restrict__ g, Level0 l0, BlurTiles bt, int frameBase) {
     __shared__ uint8_t in[(kBlurTH + 6) * (kBlurTW + 8)];
     __shared__ uint16_t hb[(kBlurTH + 6) * kBlurTW];
-    const int frame = blockIdx.y;
+    const int frame = frameBase + blockIdx.y;
     int l = 0;
     while (l + 1 < g->nlevels && (int)blockIdx.x >= bt.start[l + 1]) ++l;
     const int t = blockIdx.x - bt.start[l];

@@ -112,6 +112,19 @@ class ORBextractor:
         self._frames = min(nimg, self.max_batch)
         return [(int(mono[i]), kps[i, :n[i]].copy(), desc[i, :n[i]].copy()) for i in range(nimg)]
 
+    def extract_batch_into(self, images, kps, desc, n_out, mono_out, vLappingArea=(0, 1000)):
+        """Lowest-overhead host path: `images` [n,h,w] uint8 C-contiguous, results written into caller-owned arrays
+        kps [n,cap] KEYPOINT_DTYPE, desc [n,cap,32] uint8, n_out / mono_out [n] int32.  Page-locked arrays (e.g.
+        torch.empty(..., pin_memory=True).numpy()) are used by the library in place, without a staging copy."""
+        nimg, h, w = images.shape
+        assert images.dtype == np.uint8 and images.flags.c_contiguous
+        cap = kps.shape[1]
+        base = images.ctypes.data
+        ptrs = (C.c_void_p * nimg)(*[base + i * h * w for i in range(nimg)])
+        check(self._L.orbx_extract_batch(self._h, ptrs, nimg, w, h, w, int(vLappingArea[0]), int(vLappingArea[1]),
+                                         _p(kps), _p(desc), cap, _p(n_out), _p(mono_out)), self._h, "orbx_extract_batch")
+        self._frames = min(nimg, self.max_batch)
+
     # ---- device-resident mode ----
     def extract_device(self, d_ptr, image_bytes, nimg, width, height, stride, vLappingArea=(0, 1000), stream=None):
         check(self._L.orbx_extract_device(self._h, C.c_void_p(d_ptr), image_bytes, nimg, width, height, stride,
@@ -137,6 +150,13 @@ class ORBextractor:
         check(self._L.orbx_results_device(self._h, frame, C.byref(dk), C.byref(dd), C.byref(n), C.byref(mono)), self._h,
               "orbx_results_device")
         return dk.value, dd.value, n.value, mono.value
+
+    def results_batch_device(self):
+        """(d_kps, d_desc, d_counts, frame_stride): the device arrays holding the last pass's results of all frames."""
+        dk, dd, dc, st = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_int(0)
+        check(self._L.orbx_results_batch_device(self._h, C.byref(dk), C.byref(dd), C.byref(dc), C.byref(st)), self._h,
+              "orbx_results_batch_device")
+        return dk.value, dd.value, dc.value, st.value
 
     # ---- mvImagePyramid (include/ORBextractor.h:83) and stage taps ----
     def level_size(self, level):

@@ -174,6 +174,18 @@ class ORBmatcher:
                                           C.byref(nm)), self._h, "orbm_search_frame")
         return nm.value, km
 
+    def track_batch_device(self, nframes, d_kps, d_desc, d_counts, frame_stride, bounds, scale_factors, th, d_kp_match,
+                           d_nmatches, ORBdist=100, count_stride=2, stream=None):
+        """Device-resident SearchByProjection(Cur, Last) over consecutive frames of an extractor batch (orbm_track_batch_device)."""
+        b, sf = _c(bounds, np.float32), _c(scale_factors, np.float32)
+        check_m(self._L.orbm_track_batch_device(self._h, int(nframes), C.c_void_p(d_kps), C.c_void_p(d_desc), C.c_void_p(d_counts),
+                                                int(frame_stride), int(count_stride), _p(b), _p(sf), len(sf), float(th), int(ORBdist),
+                                                int(self.mbCheckOrientation), C.c_void_p(d_kp_match), C.c_void_p(d_nmatches),
+                                                C.c_void_p(stream or 0)), self._h, "orbm_track_batch_device")
+
+    def track_evaluations(self):
+        return int(self._L.orbm_track_evaluations(self._h))
+
     # ---- M7: SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) ----
     def SearchByProjection_Sim3(self, KF, matched, scale_factors, valid, u, v, level, qdesc, th, ratioHamming=1.0):
         m = _c(matched, np.uint8).copy()

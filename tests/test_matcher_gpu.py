@@ -265,3 +265,38 @@ def test_distinctive_descriptors(M):
     best = M.ComputeDistinctiveDescriptors(desc, off)
     want = [om.distinctive_descriptor(desc[off[p]:off[p + 1]]) for p in range(len(sizes))]
     assert best.tolist() == want
+
+
+def test_track_batch_device_equals_pairwise_oracle(M):
+    """config[1]: extraction results stay in HBM, SearchByProjection(Cur, Last) runs for every consecutive pair of the batch
+    in one launch; each pair must equal the oracle's sequential search on the fetched keypoints / descriptors."""
+    import torch
+    from mam3slam_b200 import ORBextractor, synth
+    nf = 6
+    frames = synth.stream(752, 480, 3, nf)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_batch=nf)
+    dev = torch.from_numpy(frames).cuda()
+    ex.extract_device(dev.data_ptr(), 752 * 480, nf, 752, 480, 752)
+    ex.synchronize()
+    dk, dd, dc, stride = ex.results_batch_device()
+    kpm = torch.empty((nf, stride), dtype=torch.int32, device="cuda")
+    nm = torch.empty(nf, dtype=torch.int32, device="cuda")
+    sf = ex.GetScaleFactors()
+    bounds = (0.0, 0.0, 752.0, 480.0)
+    for ori in (True, False):
+        M.mbCheckOrientation = ori
+        M.track_batch_device(nf, dk, dd, dc, stride, bounds, sf, 15.0, kpm.data_ptr(), nm.data_ptr())
+        evals = M.track_evaluations()
+        kpm_h, nm_h = kpm.cpu().numpy(), nm.cpu().numpy()
+        res = [ex.fetch(f) for f in range(nf)]
+        assert nm_h[0] == 0 and (kpm_h[0] == -1).all()
+        for i in range(1, nf):
+            _, k1, d1 = res[i - 1]
+            _, k2, d2 = res[i]
+            onm, okm = om.search_frame(k2, d2, bounds, np.zeros(len(k2), np.uint8), sf, np.ones(len(k1), np.uint8), k1["x"], k1["y"],
+                                       k1["octave"], k1["angle"], d1, 15.0, 100, ori)
+            assert nm_h[i] == onm and np.array_equal(kpm_h[i, :len(k2)], okm) and (kpm_h[i, len(k2):] == -1).all()
+            assert onm > 100
+        assert evals > 10000
+    M.mbCheckOrientation = True
+    ex.close()
