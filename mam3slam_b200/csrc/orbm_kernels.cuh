@@ -146,7 +146,7 @@ struct SearchParams {
     unsigned long long* evals;
 };
 
-constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 384, kSlots = 32;
+constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 192, kSlots = 64;
 
 // dynamic shared memory of a search CTA: slabs + match state (+ the staged target frame); host and device agree on this
 __host__ __device__ inline size_t search_smem_bytes(int n, int state, bool stage) {
@@ -270,15 +270,19 @@ __device__ __forceinline__ void best_update(Best& b, uint32_t key, uint32_t entr
     else if (key < b.k2) { b.k2 = key; b.e2 = entry; }
 }
 
-// Resolve one query: best (and second best) among its candidates that are not blocked by the match state, acceptance by
-// the reference's rule, state update, result write.  Executed by one full warp.  `slab` holds the first min(count, kSlab)
-// candidates in scan order; more than kSlab candidates (rare) are re-walked here.
-__device__ __forceinline__ void resolve_query(const SearchParams& P, const FrameDev& T, int q, const uint32_t* slab, int count,
-                                              float qa, uint8_t* occS, uint16_t* mdS, int* m21S) {
+constexpr uint32_t kNoEntry = 0xffffffffu, kOverflowEntry = 0xfffffffeu;     // real entries are < 0x80800000 (dist <= 256)
+
+__device__ __forceinline__ bool rule_needs_second(int rule) {
+    return rule == RULE_LOCAL_MAP || rule == RULE_RATIO_LE || rule == RULE_RATIO_LT || rule == RULE_INIT;
+}
+
+// Best and second-best candidate of query q among those not blocked by the match state.  Warp-collective; every lane gets
+// the result (kNoEntry = none).  `slab` holds the candidates in scan order; more than kSlab of them (rare) are re-walked.
+__device__ __forceinline__ void scan_candidates(const SearchParams& P, const FrameDev& T, int q, const uint32_t* slab, int count,
+                                                const uint8_t* occS, const uint16_t* mdS, uint32_t& e1out, uint32_t& e2out) {
     const int lane = threadIdx.x & 31;
     const bool lastMin = P.rule == RULE_LAST_MIN;
-    const bool needSecond = P.rule == RULE_LOCAL_MAP || P.rule == RULE_RATIO_LE || P.rule == RULE_RATIO_LT || P.rule == RULE_INIT;
-    Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = 0;
+    Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = kNoEntry;
     if (count <= kSlab) {
         for (int p = lane; p < count; p += 32) {
             const uint32_t e = slab[p];
@@ -306,57 +310,53 @@ __device__ __forceinline__ void resolve_query(const SearchParams& P, const Frame
     const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
     const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);
     const unsigned wmask = __ballot_sync(0xffffffffu, win);
-    const int wl = wmask ? __ffs(wmask) - 1 : 0;
-    const uint32_t e1 = __shfl_sync(0xffffffffu, b.e1, wl);
-    uint32_t m2 = 0xffffffffu, e2 = 0;
-    if (needSecond) {
+    e1out = wmask ? __shfl_sync(0xffffffffu, b.e1, __ffs(wmask) - 1) : kNoEntry;
+    e2out = kNoEntry;
+    if (rule_needs_second(P.rule)) {
         const uint32_t cand2 = win ? b.k2 : b.k1;
-        m2 = __reduce_min_sync(0xffffffffu, cand2);
+        const uint32_t m2 = __reduce_min_sync(0xffffffffu, cand2);
         const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
-        const int sl = smask ? __ffs(smask) - 1 : 0;
-        e2 = __shfl_sync(0xffffffffu, win ? b.e2 : b.e1, sl);
+        if (smask) e2out = __shfl_sync(0xffffffffu, win ? b.e2 : b.e1, __ffs(smask) - 1);
     }
-    if (lane == 0) {
-        const bool has1 = m1 != 0xffffffffu, has2 = m2 != 0xffffffffu;
-        const int bestDist = has1 ? (int)(e1 >> 23) : 256;
-        const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
-        const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
-        const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
-        const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
-        bool accept = false;
-        switch (P.rule) {
-            case RULE_LOCAL_MAP:
-                accept = has1 && bestDist <= ORBM_TH_HIGH &&
-                         !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
-                break;
-            case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
-            case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-            case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-            case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
-            case RULE_LAST_MIN: accept = has1; break;
-            default: accept = false; break;
-        }
-        int bin = -1;
-        if (accept) {
-            if (P.state == 1) occS[bestIdx] = 1;
-            if (P.state == 2) {
-                const int prev = m21S[bestIdx];
-                if (prev >= 0) P.qResult[prev] = -1;          // the earlier, worse match loses the keypoint (:706-710)
-                m21S[bestIdx] = q;
-                mdS[bestIdx] = (uint16_t)bestDist;
-            }
-            if (P.checkOri) {
-                float rot = __fsub_rn(qa, T.kp4[bestIdx].z);
-                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
-                if (bin == ORBM_HISTO_LENGTH) bin = 0;
-            }
-        }
-        P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
-        P.qDist[q] = bestDist;
-        P.qBin[q] = bin;
+}
+
+// Acceptance by the reference's rule, match-state update and result write of one query.  Executed by ONE thread.
+// state 2 (M5): the new owner is recorded in m21S; the queries that lost their keypoint are cleared after the loop.
+__device__ __forceinline__ void commit_query(const SearchParams& P, const FrameDev& T, int q, uint32_t e1, uint32_t e2, float qa,
+                                             uint8_t* occS, uint16_t* mdS, int* m21S) {
+    const bool has1 = e1 != kNoEntry, has2 = e2 != kNoEntry;
+    const int bestDist = has1 ? (int)(e1 >> 23) : 256;
+    const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
+    const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
+    const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
+    const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
+    bool accept = false;
+    switch (P.rule) {
+        case RULE_LOCAL_MAP:
+            accept = has1 && bestDist <= ORBM_TH_HIGH &&
+                     !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
+            break;
+        case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
+        case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+        case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
+        case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
+        case RULE_LAST_MIN: accept = has1; break;
+        default: accept = false; break;
     }
-    __syncwarp();
+    int bin = -1;
+    if (accept) {
+        if (P.state == 1) occS[bestIdx] = 1;
+        if (P.state == 2) { m21S[bestIdx] = q; mdS[bestIdx] = (uint16_t)bestDist; }      // (:706-713)
+        if (P.checkOri) {
+            float rot = __fsub_rn(qa, T.kp4[bestIdx].z);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
+            if (bin == ORBM_HISTO_LENGTH) bin = 0;
+        }
+    }
+    P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
+    P.qDist[q] = bestDist;
+    P.qBin[q] = bin;
 }
 
 // gather + distances of query q into a slab (scan order preserved by ballot compaction); returns the candidate count
@@ -380,15 +380,22 @@ __device__ __forceinline__ int gather_query(const SearchParams& P, const FrameDe
 
 // One CTA per search (state != 0) or per slice of queries (state == 0).
 // dynamic smem: kSlots slabs | match state (occupancy bytes [n], or matched distance u16 [n] + match21 int [n]) | staged frame.
-// Stateful searches: warp 0 is the RESOLVER — it walks the queries in the reference's order and is the only warp that reads
-// or writes the match state; warps 1..15 are PRODUCERS that gather candidates / distances for later queries into a ring of
-// slabs (ready[slot] = q+1 publishes a slab, `done` frees it).  The sequential part of the reference loop thus costs two
-// shared-memory round trips and one redux per query, and no warp spins on the critical path.
+//
+// Stateful searches reproduce the reference's sequential loop by SPECULATION.  The match state only ever blocks more
+// candidates (an occupied keypoint stays occupied; vMatchedDistance only decreases), so the best / second-best candidate a
+// query saw against an OLDER state is still its best / second-best as long as neither has been blocked since.
+//   warps 1..15 (producers): gather candidates + distances of query q into slab q % kSlots, reduce them against the state
+//       as it is at that moment, publish (best, second, angle) -> ready[slot] = q + 1.
+//   warp 0 (resolver): takes 32 consecutive queries at a time, one per lane.  A query is "clean" when its speculative
+//       best / second are still unblocked and no earlier query of the same batch wins one of them; clean prefixes commit
+//       in parallel (distinct keypoints), the rest of the batch is replayed one query at a time (slab re-scan only when
+//       the speculation failed).  `done` frees the slabs.
 __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, int ctaIdx, int nCtas) {
     __shared__ volatile int ready[kSlots];
     __shared__ volatile int done;
     __shared__ int slotCount[kSlots];
     __shared__ float slotAngle[kSlots];
+    __shared__ uint32_t slotE1[kSlots], slotE2[kSlots];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int n = P.tgt.n;
     uint32_t* slabs = reinterpret_cast<uint32_t*>(dyn);
@@ -418,32 +425,75 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
     if (tid == 0) done = 0;
     __syncthreads();
 
+    const bool needSecond = rule_needs_second(P.rule);
     unsigned long long nEval = 0;
     if (P.state == 0) {
         // independent queries: every warp gathers and resolves its own
         uint32_t* slab = slabs + (size_t)wid * kSlab;
         for (int q = ctaIdx * kSearchWarps + wid; q < P.nq; q += kSearchWarps * nCtas) {
             const int count = gather_query(P, T, q, slab, nEval);
-            resolve_query(P, T, q, slab, count, P.checkOri ? P.qangle[q] : 0.f, occS, mdS, m21S);
+            uint32_t e1, e2;
+            scan_candidates(P, T, q, slab, count, occS, mdS, e1, e2);
+            if (lane == 0) commit_query(P, T, q, e1, e2, P.checkOri ? P.qangle[q] : 0.f, occS, mdS, m21S);
+            __syncwarp();
         }
     } else if (wid == 0) {
-        for (int q = 0; q < P.nq; ++q) {
+        for (int q0 = 0; q0 < P.nq; q0 += 32) {
+            const int q = q0 + lane;
+            const bool live = q < P.nq;
             const int slot = q % kSlots;
-            if (lane == 0) while (ready[slot] != q + 1) { }
+            if (live) while (ready[slot] != q + 1) { }
             __syncwarp();
-            __threadfence_block();
-            resolve_query(P, T, q, slabs + (size_t)slot * kSlab, slotCount[slot], slotAngle[slot], occS, mdS, m21S);
-            if (lane == 0) { __threadfence_block(); done = q + 1; }
+            uint32_t e1 = kNoEntry, e2 = kNoEntry;
+            float qa = 0.f;
+            bool bad = false;
+            if (live) {
+                e1 = slotE1[slot]; e2 = slotE2[slot]; qa = slotAngle[slot];
+                if (e1 == kOverflowEntry) bad = true;
+                else {
+                    if (e1 != kNoEntry && blocked(P, occS, mdS, e1)) bad = true;
+                    if (e2 != kNoEntry && blocked(P, occS, mdS, e2)) bad = true;
+                }
+            }
+            // in-batch conflicts: an earlier query's winner is my winner or my runner-up
+            const int i1 = (e1 < kOverflowEntry) ? (int)(e1 & 0x7ffff) : -1;
+            const int i2 = (e1 < kOverflowEntry && e2 != kNoEntry) ? (int)(e2 & 0x7ffff) : -1;
+            const unsigned same = __match_any_sync(0xffffffffu, i1);
+            if (i1 >= 0 && (same & ((1u << lane) - 1))) bad = true;
+            if (needSecond) {
+                for (int j = 0; j < 31; ++j) {
+                    const int o = __shfl_sync(0xffffffffu, i1, j);
+                    if (j < lane && o >= 0 && o == i2) bad = true;
+                }
+            }
+            const unsigned badMask = __ballot_sync(0xffffffffu, bad);
+            const int first = badMask ? __ffs(badMask) - 1 : 32;
+            if (live && lane < first) commit_query(P, T, q, e1, e2, qa, occS, mdS, m21S);
+            __syncwarp();
+            for (int i = first; i < 32 && q0 + i < P.nq; ++i) {          // replay in order, whole warp per query
+                const int qq = q0 + i, s = qq % kSlots;
+                uint32_t a1 = slotE1[s], a2 = slotE2[s];
+                const bool redo = a1 == kOverflowEntry || (a1 != kNoEntry && blocked(P, occS, mdS, a1)) ||
+                                  (a2 != kNoEntry && blocked(P, occS, mdS, a2));
+                if (redo) scan_candidates(P, T, qq, slabs + (size_t)s * kSlab, slotCount[s], occS, mdS, a1, a2);
+                if (lane == 0) commit_query(P, T, qq, a1, a2, slotAngle[s], occS, mdS, m21S);
+                __syncwarp();
+            }
+            if (lane == 0) done = min(q0 + 32, P.nq);
         }
     } else {
         for (int q = wid - 1; q < P.nq; q += kSearchWarps - 1) {
             const int slot = q % kSlots;
-            if (lane == 0) while (q - done >= kSlots) { __nanosleep(64); }
+            if (lane == 0) while (q - done >= kSlots) { __nanosleep(32); }
             __syncwarp();
-            const int count = gather_query(P, T, q, slabs + (size_t)slot * kSlab, nEval);
+            uint32_t* slab = slabs + (size_t)slot * kSlab;
+            const int count = gather_query(P, T, q, slab, nEval);
+            uint32_t e1 = kOverflowEntry, e2 = kNoEntry;
+            if (count <= kSlab) scan_candidates(P, T, q, slab, count, occS, mdS, e1, e2);
             if (lane == 0) {
                 slotCount[slot] = count;
                 slotAngle[slot] = P.checkOri ? P.qangle[q] : 0.f;
+                slotE1[slot] = e1; slotE2[slot] = e2;
                 __threadfence_block();
                 ready[slot] = q + 1;
             }
@@ -454,9 +504,14 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) nEval += __shfl_xor_sync(0xffffffffu, nEval, o);
     if (lane == 0 && nEval) atomicAdd(P.evals, nEval);
-    if (P.state == 1) {
-        __syncthreads();
-        for (int i = tid; i < n; i += kSearchThreads) P.occ[i] = occS[i];
+    if (P.state != 0) __syncthreads();
+    if (P.state == 1) for (int i = tid; i < n; i += kSearchThreads) P.occ[i] = occS[i];
+    if (P.state == 2) {
+        // a query keeps its match only if it is still the owner of the keypoint (vnMatches12[vnMatches21[i2]] = -1, :708)
+        for (int q = tid; q < P.nq; q += kSearchThreads) {
+            const int r = P.qResult[q];
+            if (r >= 0 && m21S[r] != q) P.qResult[q] = -1;
+        }
     }
 }
 

@@ -186,8 +186,8 @@ int configureShape(Extractor* E, int W, int H) {
             G.tabY = (int)taps.size(); makeTaps(P.h, G.h, true, taps);
         }
         E->blurTiles.start[l] = tileStart;
-        E->blurTiles.tilesX[l] = (G.w + kBlurTW - 1) / kBlurTW;
-        tileStart += E->blurTiles.tilesX[l] * ((G.h + kBlurTH - 1) / kBlurTH);
+        E->blurTiles.tilesX[l] = (G.w + kBlurStripW - 1) / kBlurStripW;
+        tileStart += E->blurTiles.tilesX[l] * ((G.h + kBlurStripH - 1) / kBlurStripH);
     }
     E->blurTiles.start[L] = tileStart;
     E->blurTilesTotal = tileStart;
@@ -262,7 +262,7 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
                                                             E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb);
     ++E->launches;
     mark();
-    k_blur7<<<dim3(E->blurTilesTotal, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
+    k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
     ++E->launches;
     mark();
     k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork, fb);

@@ -281,9 +281,15 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
 
 // ---------------------------------------------------------------------------------------------------------------
 // E6: cv::GaussianBlur 7x7 sigma 2 on 8U = separable fixed-point kernel [18,34,48,56,48,34,18]/256, no intermediate
-// rounding, (sum + 2^15) >> 16, BORDER_REFLECT_101 at the edge of the (unpadded) level.  One CTA blurs a 64x32
-// tile: load 70x38 u8 -> horizontal pass to 64x38 u16 -> vertical pass -> u8.  grid (tiles over all levels, B).
-constexpr int kBlurTW = 64, kBlurTH = 32;
+// rounding, (sum + 2^15) >> 16, BORDER_REFLECT_101 at the edge of the (unpadded) level.
+// One WARP blurs a strip of 120 x 30 pixels and keeps everything in registers: lane i owns the 4 pixels of one aligned
+// 32-bit word (lanes 0 and 31 only supply the horizontal halo through shuffles), and the warp slides down the strip:
+//   horizontal pass  4 px = 6 PRMT (unaligned byte windows) + 8 IDP.4A  -> h <= 65280 (16 bit)
+//   vertical pass    consecutive rows are packed as u16 pairs (h[r-1], h[r]) so that one IDP.2A applies two taps;
+//                    4 px = 4 PRMT + 12 IDP.2A + 4 IMAD (seventh tap, carries the rounding constant)
+// ~13 instructions per pixel instead of ~45 with byte-wise shared-memory passes; no shared memory, no block barrier.
+// grid (ceil(jobs/8), B), block 256 (8 independent warps).
+constexpr int kBlurStripW = 120, kBlurStripH = 30;
 
 __device__ __forceinline__ int reflect101_dev(int p, int n) {
     if (n == 1) return 0;
@@ -291,44 +297,90 @@ __device__ __forceinline__ int reflect101_dev(int p, int n) {
     return p;
 }
 
+// same for -3 <= p <= n+2 and n >= 4 (every pyramid level is >= 35 px, orbx_api.cu): one reflection suffices
+__device__ __forceinline__ int reflect101_near(int p, int n) {
+    p = abs(p);
+    return p >= n ? 2 * (n - 1) - p : p;
+}
+
 struct BlurTiles { int start[kMaxLevels + 1]; int tilesX[kMaxLevels]; };
 
+// the 4 bytes at columns x..x+3 of a row, BORDER_REFLECT_101 outside [0, w)
+__device__ __forceinline__ uint32_t blur_load_word(const uint8_t* __restrict__ row, int x, int w, bool aligned) {
+    if (aligned && x >= 0 && x + 3 < w) return *reinterpret_cast<const uint32_t*>(row + x);
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int xx = reflect101_near(min(max(x + k, -3), w + 2), w);
+        v |= (uint32_t)row[xx] << (8 * k);
+    }
+    return v;
+}
+
 __global__ void __launch_bounds__(256) k_blur7(const DevGeom* __restrict__ g, Level0 l0, BlurTiles bt, int frameBase) {
-    __shared__ uint8_t in[(kBlurTH + 6) * (kBlurTW + 8)];
-    __shared__ uint16_t hb[(kBlurTH + 6) * kBlurTW];
+    const int lane = threadIdx.x & 31;
+    const int job = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int nl = g->nlevels;
+    if (job >= bt.start[nl]) return;
     const int frame = frameBase + blockIdx.y;
     int l = 0;
-    while (l + 1 < g->nlevels && (int)blockIdx.x >= bt.start[l + 1]) ++l;
-    const int t = blockIdx.x - bt.start[l];
-    const int tx = t % bt.tilesX[l], ty = t / bt.tilesX[l];
+    while (l + 1 < nl && job >= bt.start[l + 1]) ++l;
+    const int t = job - bt.start[l];
+    const int ty = t / bt.tilesX[l], tx = t - ty * bt.tilesX[l];
     const LevelGeom& L = g->lv[l];
+    const int w = L.w, h = L.h;
     int pitch;
     const uint8_t* src = level_ptr(g, l0, l, frame, &pitch);
-    const int x0 = tx * kBlurTW, y0 = ty * kBlurTH;
-    const int tid = threadIdx.x;
-    constexpr int IP = kBlurTW + 8;
-    for (int i = tid; i < (kBlurTH + 6) * (kBlurTW + 6); i += 256) {
-        const int ry = i / (kBlurTW + 6), rx = i - ry * (kBlurTW + 6);
-        const int sy = reflect101_dev(min(y0 + ry - 3, L.h + 2), L.h);
-        const int sx = reflect101_dev(min(x0 + rx - 3, L.w + 2), L.w);
-        in[ry * IP + rx] = src[(size_t)sy * pitch + sx];
-    }
-    __syncthreads();
-    for (int i = tid; i < (kBlurTH + 6) * kBlurTW; i += 256) {
-        const int ry = i / kBlurTW, rx = i - ry * kBlurTW;
-        const uint8_t* p = in + ry * IP + rx;
-        hb[i] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-    }
-    __syncthreads();
+    const bool aligned = (((uintptr_t)src | (uintptr_t)pitch) & 3) == 0;
+    const int x = tx * kBlurStripW + 4 * (lane - 1);           // first column of this lane's word
+    const int y0 = ty * kBlurStripH;
     uint8_t* dst = g->blur[l] + (size_t)frame * L.planeBytes;
-    for (int i = tid; i < kBlurTH * kBlurTW; i += 256) {
-        const int ry = i / kBlurTW, rx = i - ry * kBlurTW;
-        const int x = x0 + rx, y = y0 + ry;
-        if (x >= L.w || y >= L.h) continue;
-        const uint16_t* p = hb + ry * kBlurTW + rx;
-        const uint32_t acc = 18u * (p[0] + p[6 * kBlurTW]) + 34u * (p[kBlurTW] + p[5 * kBlurTW]) +
-                             48u * (p[2 * kBlurTW] + p[4 * kBlurTW]) + 56u * p[3 * kBlurTW];
-        dst[(size_t)y * L.pitch + x] = (uint8_t)((acc + 32768u) >> 16);
+    const int dp = L.pitch;
+    const bool writer = lane >= 1 && lane <= 30 && x < w;
+    const bool fullWord = x + 3 < w;
+
+    uint32_t ring[6][4];            // ring[r % 6][j] = (h[r-1], h[r]) of pixel j as u16 pair
+    uint32_t hprev[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ring[i][j] = 0;
+
+    const int rowsNeeded = min(kBlurStripH, h - y0) + 6;
+    for (int r0 = 0; r0 < rowsNeeded; r0 += 6) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const int r = r0 + k;                               // strip row r = image row y0 + r - 3
+            const int yo = y0 + r - 6;                          // output row completed by this input row
+            const int sy = reflect101_near(min(y0 + r - 3, h + 2), h);
+            const uint32_t C = blur_load_word(src + (size_t)sy * pitch, x, w, aligned);
+            const uint32_t Lw = __shfl_up_sync(0xffffffffu, C, 1);
+            const uint32_t Rw = __shfl_down_sync(0xffffffffu, C, 1);
+            uint32_t hc[4];
+            hc[0] = __dp4a(__byte_perm(Lw, C, 0x4321), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x4321), 0x00122230u, 0u));
+            hc[1] = __dp4a(__byte_perm(Lw, C, 0x5432), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x5432), 0x00122230u, 0u));
+            hc[2] = __dp4a(__byte_perm(Lw, C, 0x6543), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x6543), 0x00122230u, 0u));
+            hc[3] = __dp4a(C, 0x38302212u, __dp4a(Rw, 0x00122230u, 0u));
+            uint32_t v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t pr = __byte_perm(hprev[j], hc[j], 0x5410);      // (h[r-1], h[r])
+                // output row y = r-3 (strip rows): taps h[r-6..r] = pairs r-5, r-3, r-1 and h[r]
+                uint32_t acc = hc[j] * 18u + 32768u;
+                acc = __dp2a_lo(ring[(k + 1) % 6][j], 0x2212u, acc);           // pair r-5 = (h[r-6], h[r-5]) . (18, 34)
+                acc = __dp2a_lo(ring[(k + 3) % 6][j], 0x3830u, acc);           // pair r-3 = (h[r-4], h[r-3]) . (48, 56)
+                acc = __dp2a_lo(ring[(k + 5) % 6][j], 0x2230u, acc);           // pair r-1 = (h[r-2], h[r-1]) . (48, 34)
+                v[j] = acc;
+                ring[k][j] = pr;
+                hprev[j] = hc[j];
+            }
+            if (r >= 6 && yo < h && writer) {
+                const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+                uint8_t* d = dst + (size_t)yo * dp + x;
+                if (fullWord) *reinterpret_cast<uint32_t*>(d) = o;
+                else for (int j = 0; j < 4 && x + j < w; ++j) d[j] = (uint8_t)(o >> (8 * j));
+            }
+        }
     }
 }
 

@@ -25,6 +25,13 @@ template <int OP> __device__ __forceinline__ uint32_t op(uint32_t a, uint32_t b,
     if (OP == 13) return a + b + c;                           // IADD3
     if (OP == 14) return __vabsdiffu4(a, b);
     if (OP == 15) return __vadd2(a, b);
+    if (OP == 16) return __dp4a(a, b, c);                     // IDP.4A u8
+    if (OP == 17) return __dp2a_lo(a, b, c);                  // IDP.2A u16 x u8
+    if (OP == 18) return __funnelshift_r(a, b, c);            // SHF
+    if (OP == 19) return (a & b) ^ c;                         // LOP3
+    if (OP == 20) return __shfl_xor_sync(0xffffffffu, a, 1) + c;   // SHFL + IADD
+    if (OP == 21) return __vavgu4(a, b);
+    if (OP == 22) return __vadd4(a, b);
     return 0;
 }
 
@@ -84,5 +91,12 @@ int main() {
     run<13>("iadd3", 1);
     run<14>("vabsdiffu4", 1);
     run<15>("vadd2", 1);
+    run<16>("dp4a u8", 1);
+    run<17>("dp2a_lo u16xu8", 1);
+    run<18>("funnelshift", 1);
+    run<19>("lop3", 1);
+    run<20>("shfl_xor+add", 2);
+    run<21>("vavgu4", 1);
+    run<22>("vadd4", 1);
     return 0;
 }
