@@ -174,13 +174,14 @@ int orbm_create(int device, orbm_handle* out) {
     orbm_matcher* M = new orbm_matcher();
     M->device = device;
     if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&M->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc((void**)&M->dEvals, 8) != cudaSuccess) {
+        cudaMalloc((void**)&M->dEvals, 128) != cudaSuccess) {
         fprintf(stderr, "orbm_create: %s\n", cudaGetErrorString(cudaGetLastError()));
         delete M;
         return ORBM_ERR_CUDA;
     }
     cudaDeviceGetAttribute(&M->smCount, cudaDevAttrMultiProcessorCount, device);
-    cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_search<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_search<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     *out = M;
     return ORBM_OK;
 }
@@ -289,7 +290,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     const size_t oAng = S.take<float>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oElig = S.take<uint8_t>(std::max(n, 1));
     const size_t oOcc = S.take<uint8_t>(std::max(n, 1));
     const size_t inEnd = S.off;
-    const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(1);
+    const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(16);
     const size_t outEnd = S.off;
     int rc = ensureScratch(M, outEnd);
     if (rc) return rc;
@@ -304,7 +305,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     if (io.occ && n) memcpy(S.host<uint8_t>(oOcc), io.occ, n);
     *S.host<unsigned long long>(oEv) = 0;
     CKM(cudaMemcpyAsync(M->scratch, M->pinned, inEnd, cudaMemcpyHostToDevice, M->stream));
-    CKM(cudaMemsetAsync(S.dev<unsigned long long>(oEv), 0, 8, M->stream));
+    CKM(cudaMemsetAsync(S.dev<unsigned long long>(oEv), 0, 128, M->stream));
     P.tgt = devView(T);
     P.nq = nq;
     P.qwin = S.dev<float4>(oWin); P.qlev = S.dev<int2>(oLev); P.qrun = S.dev<int2>(oRun);
@@ -317,8 +318,11 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     P.stageTgt = (P.state != 0 && search_smem_bytes(n, P.state, true) <= kSearchSmemMax && nq >= 64) ? 1 : 0;
     const size_t smem = search_smem_bytes(n, P.state, P.stageTgt != 0);
     if (smem > kSearchSmemMax) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
-    const int grid = P.state != 0 ? 1 : std::max(1, std::min((nq + kSearchWarps - 1) / kSearchWarps, M->smCount * 2));
-    k_search<<<grid, kSearchThreads, smem, M->stream>>>(P);
+    // window searches walk one query per lane (32 per warp), BoW / triangulation runs one query per warp
+    const int units = P.source == 0 ? (nq + 31) / 32 : nq;
+    const int grid = P.state != 0 ? 1 : std::max(1, std::min(units, M->smCount * 2));
+    if (P.source == 0) k_search<true><<<grid, kSearchThreads, smem, M->stream>>>(P);
+    else k_search<false><<<grid, kSearchThreads, smem, M->stream>>>(P);
     ++M->launches;
     if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
     CKM(cudaGetLastError());
@@ -840,7 +844,7 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
     static bool attr = false;
     if (!attr) { cudaFuncSetAttribute(k_track_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
-    CKM(cudaMemsetAsync(M->dEvals, 0, 8, st));
+    CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));
     k_track_prepare<<<dim3((frame_stride + 255) / 256, nframes), 256, 0, st>>>(T);
     k_track_grid<<<nframes, kGridThreads, 0, st>>>(T);
     M->launches += 2;
@@ -863,4 +867,13 @@ extern "C" long long orbm_track_evaluations(orbm_handle M) {
     if (cudaDeviceSynchronize() != cudaSuccess) return -1;
     if (cudaMemcpy(&v, M->dEvals, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
     return (long long)v;
+}
+
+// developer aid, not part of include/orbm.h: the 16 counters of the last tracking step ([0] = evaluations; the rest are
+// cycle / replay counters that exist only in builds with -DORBM_STATS)
+extern "C" int orbm_debug_track_counters(orbm_handle M, unsigned long long* out16) {
+    if (!M || !out16) return ORBM_ERR_INVALID;
+    cudaSetDevice(M->device);
+    if (cudaDeviceSynchronize() != cudaSuccess) return ORBM_ERR_CUDA;
+    return cudaMemcpy(out16, M->dEvals, 128, cudaMemcpyDeviceToHost) == cudaSuccess ? ORBM_OK : ORBM_ERR_CUDA;
 }

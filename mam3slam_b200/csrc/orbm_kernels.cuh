@@ -19,6 +19,10 @@
 //                 tiles filled with TMA bulk copies; 256-bit popcount through a carry-save adder tree (4 POPC instead of
 //                 8: POPC issues at 16/clk/SM on B200, LOP3 at 128/clk/SM — tools/microbench.cu).
 #pragma once
+#include <climits>
+#ifdef ORBM_STATS
+#include <cstdio>
+#endif
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/orbm.h"
@@ -186,13 +190,38 @@ __device__ __forceinline__ void walk_candidates(const SearchParams& P, const Fra
         if (minCY >= kGridRows) return;
         const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, T.minY), r), T.invH)));
         if (maxCY < 0) return;
-        for (int ix = minCX; ix <= maxCX; ++ix) {
-            if (minCY > maxCY) break;
-            const int rb = T.cellOff[ix * kGridRows + minCY], re = T.cellOff[ix * kGridRows + maxCY + 1];
-            for (int base = rb; base < re; base += 32) {
-                const int e = base + lane;
+        if (minCY > maxCY) return;
+        // The reference visits the cells column by column (ix outer, iy inner) and, inside a cell, in insertion order; with
+        // the column-major CSR grid the candidates of one column are ONE contiguous run.  Lane c fetches the run of column
+        // minCX + c, a warp prefix sum flattens the runs, and the lanes then enumerate the flattened sequence (same order),
+        // so the dependent-load chain (offsets -> index -> keypoint -> descriptor) is walked once per 32 candidates
+        // instead of once per column.
+        const int ncol = maxCX - minCX + 1;
+        for (int c0 = 0; c0 < ncol; c0 += 32) {
+            int rb = 0, len = 0;
+            if (c0 + lane < ncol) {
+                const int ix = minCX + c0 + lane;
+                rb = T.cellOff[ix * kGridRows + minCY];
+                len = T.cellOff[ix * kGridRows + maxCY + 1] - rb;
+            }
+            int incl = len;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            for (int base = 0; base < total; base += 32) {
+                const int p = base + lane;
+                // column of position p = first lane whose inclusive sum exceeds p
+                int j = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int t = __shfl_sync(0xffffffffu, incl, j + step - 1);
+                    if (t <= p) j += step;
+                }
+                j = min(j, 31);
+                const int rbj = __shfl_sync(0xffffffffu, rb, j), inj = __shfl_sync(0xffffffffu, incl, j), lnj = __shfl_sync(0xffffffffu, len, j);
                 bool ok = false; uint32_t entry = 0;
-                if (e < re) {
+                if (p < total) {
+                    const int e = rbj + (p - (inj - lnj));
                     const int idx = T.cellIdx[e];
                     const float4 k = T.kp4[idx];
                     const int oct = __float_as_int(k.w);
@@ -320,43 +349,147 @@ __device__ __forceinline__ void scan_candidates(const SearchParams& P, const Fra
     }
 }
 
-// Acceptance by the reference's rule, match-state update and result write of one query.  Executed by ONE thread.
-// state 2 (M5): the new owner is recorded in m21S; the queries that lost their keypoint are cleared after the loop.
-__device__ __forceinline__ void commit_query(const SearchParams& P, const FrameDev& T, int q, uint32_t e1, uint32_t e2, float qa,
-                                             uint8_t* occS, uint16_t* mdS, int* m21S) {
+// Acceptance test of the reference's rule on the best / second-best surviving candidates (kNoEntry = none).
+__device__ __forceinline__ bool decide_query(const SearchParams& P, uint32_t e1, uint32_t e2) {
     const bool has1 = e1 != kNoEntry, has2 = e2 != kNoEntry;
     const int bestDist = has1 ? (int)(e1 >> 23) : 256;
-    const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
     const int bestLevel = has1 ? (int)((e1 >> 19) & 15) : -1;
     const int bestDist2 = has2 ? (int)(e2 >> 23) : P.none2;
     const int bestLevel2 = has2 ? (int)((e2 >> 19) & 15) : -1;
-    bool accept = false;
-    switch (P.rule) {
-        case RULE_LOCAL_MAP:
-            accept = has1 && bestDist <= ORBM_TH_HIGH &&
-                     !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
-            break;
-        case RULE_BEST_LE: accept = has1 && (float)bestDist <= P.thF; break;
-        case RULE_RATIO_LE: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-        case RULE_RATIO_LT: accept = has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2); break;
-        case RULE_INIT: accept = has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio); break;
-        case RULE_LAST_MIN: accept = has1; break;
-        default: accept = false; break;
-    }
+    // an if-chain on purpose: a jump table (BRX) in this very large kernel faulted with "illegal instruction" on sm_100a
+    const int rule = P.rule;
+    if (rule == RULE_BEST_LE) return has1 && (float)bestDist <= P.thF;
+    if (rule == RULE_LOCAL_MAP)
+        return has1 && bestDist <= ORBM_TH_HIGH &&
+               !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(P.nnratio, (float)(has2 ? bestDist2 : 256)));
+    if (rule == RULE_RATIO_LE) return has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2);
+    if (rule == RULE_RATIO_LT) return has1 && bestDist < P.thI && (float)bestDist < __fmul_rn(P.nnratio, (float)bestDist2);
+    if (rule == RULE_INIT) return has1 && bestDist <= P.thI && (float)bestDist < __fmul_rn((float)bestDist2, P.nnratio);
+    if (rule == RULE_LAST_MIN) return has1;
+    return false;
+}
+
+// Match-state update of an accepted query (state 2, M5: the new owner is recorded in m21S; the queries that lost their
+// keypoint are cleared after the loop).
+__device__ __forceinline__ void update_state(const SearchParams& P, int q, uint32_t e1, uint8_t* occS, uint16_t* mdS, int* m21S) {
+    const int bestIdx = (int)(e1 & 0x7ffff);
+    if (P.state == 1) occS[bestIdx] = 1;
+    if (P.state == 2) { m21S[bestIdx] = q; mdS[bestIdx] = (uint16_t)(e1 >> 23); }      // (:706-713)
+}
+
+// Result write of one query: accepted keypoint (or -1), best distance, rotation-histogram bin of the accept event.
+__device__ __forceinline__ void write_result(const SearchParams& P, const FrameDev& T, int q, uint32_t e1, bool accept, float qa) {
+    const bool has1 = e1 != kNoEntry;
+    const int bestDist = has1 ? (int)(e1 >> 23) : 256;
+    const int bestIdx = has1 ? (int)(e1 & 0x7ffff) : -1;
     int bin = -1;
-    if (accept) {
-        if (P.state == 1) occS[bestIdx] = 1;
-        if (P.state == 2) { m21S[bestIdx] = q; mdS[bestIdx] = (uint16_t)bestDist; }      // (:706-713)
-        if (P.checkOri) {
-            float rot = __fsub_rn(qa, T.kp4[bestIdx].z);
-            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-            bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
-            if (bin == ORBM_HISTO_LENGTH) bin = 0;
-        }
+    if (accept && P.checkOri) {
+        float rot = __fsub_rn(qa, T.kp4[bestIdx].z);
+        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+        bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
+        if (bin == ORBM_HISTO_LENGTH) bin = 0;
     }
     P.qResult[q] = (accept || P.rule == RULE_NONE) ? bestIdx : -1;
     P.qDist[q] = bestDist;
     P.qBin[q] = bin;
+}
+
+// Executed by ONE thread.
+__device__ __forceinline__ void apply_query(const SearchParams& P, const FrameDev& T, int q, uint32_t e1, bool accept, float qa,
+                                            uint8_t* occS, uint16_t* mdS, int* m21S) {
+    if (accept) update_state(P, q, e1, occS, mdS, m21S);
+    write_result(P, T, q, e1, accept, qa);
+}
+
+__device__ __forceinline__ void commit_query(const SearchParams& P, const FrameDev& T, int q, uint32_t e1, uint32_t e2, float qa,
+                                             uint8_t* occS, uint16_t* mdS, int* m21S) {
+    apply_query(P, T, q, e1, decide_query(P, e1, e2), qa, occS, mdS, m21S);
+}
+
+// ---- lane-per-query walk of a grid window ---------------------------------------------------------------------------
+// A tracking window holds a handful of candidates, so a warp per query leaves most lanes idle.  Here every LANE walks the
+// window of its own query in the reference's order (Frame::GetFeaturesInArea, src/Frame.cc:657-723: columns outer, rows
+// inner, insertion order inside a cell) and keeps the first four candidates in (distance, scan position) order that the
+// match state does not block.  `count` = how many unblocked candidates were seen; count <= 4 means the list is complete.
+struct Top4 { uint32_t t0, t1, t2, t3; int count; };
+
+__device__ __forceinline__ void top4_insert(Top4& s, uint32_t e) {
+    const uint32_t d = e >> 23;                       // strict '<' keeps earlier candidates first among equal distances
+    if (d < (s.t3 >> 23)) {
+        if (d < (s.t2 >> 23)) {
+            s.t3 = s.t2;
+            if (d < (s.t1 >> 23)) {
+                s.t2 = s.t1;
+                if (d < (s.t0 >> 23)) { s.t1 = s.t0; s.t0 = e; } else s.t1 = e;
+            } else s.t2 = e;
+        } else s.t3 = e;
+    }
+}
+
+__device__ __forceinline__ void lane_walk(const SearchParams& P, const FrameDev& T, int q, const uint8_t* occS, const uint16_t* mdS,
+                                          Top4& s, unsigned long long& nEval) {
+    s.t0 = s.t1 = s.t2 = s.t3 = kNoEntry; s.count = 0;
+    const float4 w = P.qwin[q];
+    const int2 lv = P.qlev[q];
+    const float x = w.x, y = w.y, r = w.z;
+    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, T.minX), r), T.invW)));
+    if (minCX >= kGridCols) return;
+    const int maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, T.minX), r), T.invW)));
+    if (maxCX < 0) return;
+    const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, T.minY), r), T.invH)));
+    if (minCY >= kGridRows) return;
+    const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, T.minY), r), T.invH)));
+    if (maxCY < 0 || minCY > maxCY) return;
+    uint32_t qd[8];
+    {
+        const uint4 a = reinterpret_cast<const uint4*>(P.qdesc)[2 * q], b = reinterpret_cast<const uint4*>(P.qdesc)[2 * q + 1];
+        qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
+    }
+    const uint4* drows = reinterpret_cast<const uint4*>(T.desc);
+    int ix = minCX, e = 0, re = 0;
+    while (true) {
+        if (e >= re) {                                  // next column: one contiguous CSR run (column-major grid)
+            if (ix > maxCX) break;
+            e = T.cellOff[ix * kGridRows + minCY];
+            re = T.cellOff[ix * kGridRows + maxCY + 1];
+            ++ix;
+            continue;
+        }
+        const int idx = T.cellIdx[e++];
+        const float4 k = T.kp4[idx];
+        const int oct = __float_as_int(k.w);
+        bool ok = oct >= lv.x && oct <= lv.y && fabsf(__fsub_rn(k.x, x)) < r && fabsf(__fsub_rn(k.y, y)) < r;
+        if (ok && P.chi2) {
+            const float ex = __fsub_rn(x, k.x), ey = __fsub_rn(y, k.y);
+            const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+            ok = !((double)__fmul_rn(e2, P.invSigma2[oct]) > 5.99);
+        }
+        if (ok && P.elig) ok = P.elig[idx] != 0;
+        if (!ok) continue;
+        const int d = hamming8(qd, drows[2 * idx], drows[2 * idx + 1]);
+        ++nEval;
+        const uint32_t entry = pack_entry(d, oct, idx);
+        if (blocked(P, occS, mdS, entry)) continue;
+        ++s.count;
+        top4_insert(s, entry);
+    }
+}
+
+// first and second entry of a Top4 list that the CURRENT state does not block; returns how many were found (0..2)
+__device__ __forceinline__ int top4_pick(const SearchParams& P, const Top4& s, const uint8_t* occS, const uint16_t* mdS,
+                                         uint32_t& u1, uint32_t& u2) {
+    // the four state reads are independent; an absent entry counts as blocked
+    const bool k0 = s.t0 != kNoEntry && !(P.state != 0 && blocked(P, occS, mdS, s.t0));
+    const bool k1 = s.t1 != kNoEntry && !(P.state != 0 && blocked(P, occS, mdS, s.t1));
+    const bool k2 = s.t2 != kNoEntry && !(P.state != 0 && blocked(P, occS, mdS, s.t2));
+    const bool k3 = s.t3 != kNoEntry && !(P.state != 0 && blocked(P, occS, mdS, s.t3));
+    const unsigned m = (unsigned)k0 | ((unsigned)k1 << 1) | ((unsigned)k2 << 2) | ((unsigned)k3 << 3);
+    const int a = __ffs(m) - 1;                       // first survivor (or -1)
+    const unsigned m2 = m & (m - 1);
+    const int b = __ffs(m2) - 1;                      // second survivor (or -1)
+    u1 = a == 0 ? s.t0 : a == 1 ? s.t1 : a == 2 ? s.t2 : a == 3 ? s.t3 : kNoEntry;
+    u2 = b == 1 ? s.t1 : b == 2 ? s.t2 : b == 3 ? s.t3 : kNoEntry;
+    return (m != 0) + (m2 != 0);
 }
 
 // gather + distances of query q into a slab (scan order preserved by ballot compaction); returns the candidate count
@@ -390,6 +523,10 @@ __device__ __forceinline__ int gather_query(const SearchParams& P, const FrameDe
 //       best / second are still unblocked and no earlier query of the same batch wins one of them; clean prefixes commit
 //       in parallel (distinct keypoints), the rest of the batch is replayed one query at a time (slab re-scan only when
 //       the speculation failed).  `done` frees the slabs.
+// kWindow selects the code that is compiled in: true = grid-window searches (lane per query), false = BoW / triangulation
+// runs (warp per query).  Two kernels instead of one: with both bodies in a single ~8000-instruction kernel the BoW path
+// faulted with "illegal instruction" on sm_100a (nvcc 12.9) although only dead code had been added.
+template <bool kWindow>
 __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, int ctaIdx, int nCtas) {
     __shared__ volatile int ready[kSlots];
     __shared__ volatile int done;
@@ -397,6 +534,9 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
     __shared__ float slotAngle[kSlots];
     __shared__ uint32_t slotE1[kSlots], slotE2[kSlots];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+#ifdef ORBM_STATS
+    const long long kStart = clock64();
+#endif
     const int n = P.tgt.n;
     uint32_t* slabs = reinterpret_cast<uint32_t*>(dyn);
     uint8_t* stateBase = dyn + (size_t)kSlots * kSlab * 4;
@@ -427,23 +567,165 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
 
     const bool needSecond = rule_needs_second(P.rule);
     unsigned long long nEval = 0;
-    if (P.state == 0) {
+#ifdef ORBM_STATS
+    const long long kT0 = clock64();
+    if (tid == 0) atomicAdd(P.evals + 10, (unsigned long long)(kT0 - kStart));
+#endif
+    if (kWindow && P.state == 0) {
+        // grid windows, independent queries: one query per lane
+        for (int b = ctaIdx + wid * nCtas; b * 32 < P.nq; b += kSearchWarps * nCtas) {      // spread batches over CTAs first
+            const int q = b * 32 + lane;
+            if (q < P.nq) {
+                Top4 t;
+                lane_walk(P, T, q, occS, mdS, t, nEval);
+                commit_query(P, T, q, t.t0, t.t1, P.checkOri ? P.qangle[q] : 0.f, occS, mdS, m21S);
+            }
+        }
+    } else if (kWindow) {
+        // grid windows against a match state: producers walk 32 queries per warp (one per lane) against the state as it is
+        // and publish each query's Top4; the resolver validates and commits a batch of 32 at a time (see above; with four
+        // candidates on file a blocked winner usually has its successor at hand and no second walk is needed).
+        constexpr int kRingB = 32;
+        uint4* hdrT = reinterpret_cast<uint4*>(dyn);                    // reuses the slab region: kRingB * 32 * 24 B = 24 KB
+        int* hdrCount = reinterpret_cast<int*>(hdrT + kRingB * 32);
+        float* hdrAngle = reinterpret_cast<float*>(hdrCount + kRingB * 32);
+        const int nb = (P.nq + 31) >> 5;
+        if (wid == 0) {
+            const int needed = needSecond ? 2 : 1;
+#ifdef ORBM_STATS
+            long long tWait = 0, tRes = 0; int nIter = 0, nWalk = 0;
+#endif
+            for (int b = 0; b < nb; ++b) {
+#ifdef ORBM_STATS
+                const long long c0 = clock64();
+#endif
+                const int q = b * 32 + lane;
+                const int at = (b % kRingB) * 32 + lane;
+                if (lane == 0) while (ready[b % kRingB] != b + 1) { }
+                __syncwarp();
+#ifdef ORBM_STATS
+                const long long c1 = clock64(); tWait += c1 - c0;
+#endif
+                bool pending = q < P.nq;
+                Top4 t; float qa = 0.f;
+                { const uint4 v = hdrT[at]; t.t0 = v.x; t.t1 = v.y; t.t2 = v.z; t.t3 = v.w; t.count = hdrCount[at]; qa = hdrAngle[at]; }
+                uint32_t r1 = kNoEntry; bool racc = false;           // this lane's outcome, written once after the loop
+                while (true) {
+                    const unsigned R = __ballot_sync(0xffffffffu, pending);
+                    if (!R) break;
+#ifdef ORBM_STATS
+                    ++nIter; const long long i0 = clock64();
+#endif
+                    uint32_t u1 = kNoEntry, u2 = kNoEntry;
+                    bool insufficient = false;
+                    if (pending) insufficient = top4_pick(P, t, occS, mdS, u1, u2) < needed && t.count > 4;
+                    const int lowest = __ffs(R) - 1;
+                    if (__shfl_sync(0xffffffffu, (int)insufficient, lowest)) {
+                        // every earlier query is committed and the four candidates on file do not settle the lowest pending
+                        // one: the whole warp walks its window again against the state as it is now (exact)
+                        uint32_t e1, e2;
+                        scan_candidates(P, T, b * 32 + lowest, nullptr, INT_MAX, occS, mdS, e1, e2);
+                        if (lane == lowest) { u1 = e1; u2 = e2; insufficient = false; }
+#ifdef ORBM_STATS
+                        if (lane == 0) atomicAdd(P.evals + 5, 1ull);
+#endif
+                    }
+                    const bool acc = pending && !insufficient && decide_query(P, u1, u2);
+#ifdef ORBM_STATS
+                    const long long i1c = clock64();
+#endif
+                    // an earlier pending query that is about to claim my best or second best invalidates my view
+                    const int claim = acc ? (int)(u1 & 0x7ffff) : -1;
+                    const int w1 = (pending && u1 != kNoEntry) ? (int)(u1 & 0x7ffff) : -2 - lane;     // unique when absent
+                    const int w2 = (pending && u2 != kNoEntry) ? (int)(u2 & 0x7ffff) : -2;
+                    const unsigned lower = (1u << lane) - 1;
+                    const unsigned accMask = __ballot_sync(0xffffffffu, acc);
+                    bool conflict = (__match_any_sync(0xffffffffu, w1) & accMask & lower) != 0;      // claim == that lane's w1
+                    if (needSecond) {
+#pragma unroll
+                        for (int j = 0; j < 31; ++j) {
+                            const int cj = __shfl_sync(0xffffffffu, claim, j);
+                            if (j < lane && cj >= 0 && cj == w2) conflict = true;
+                        }
+                    }
+                    const unsigned badMask = __ballot_sync(0xffffffffu, pending && (insufficient || conflict));
+                    const int first = badMask ? __ffs(badMask) - 1 : 32;      // never the lowest pending lane: progress
+#ifdef ORBM_STATS
+                    const long long i2c = clock64();
+#endif
+                    if (pending && lane < first) {
+                        if (acc) update_state(P, q, u1, occS, mdS, m21S);
+                        r1 = u1; racc = acc; pending = false;
+                    }
+                    __syncwarp();
+#ifdef ORBM_STATS
+                    if (lane == 0) { atomicAdd(P.evals + 11, (unsigned long long)(i1c - i0)); atomicAdd(P.evals + 12, (unsigned long long)(i2c - i1c)); atomicAdd(P.evals + 13, (unsigned long long)(clock64() - i2c)); }
+#endif
+                }
+                if (q < P.nq) write_result(P, T, q, r1, racc, qa);
+                if (lane == 0) done = b + 1;
+#ifdef ORBM_STATS
+                tRes += clock64() - c1;
+#endif
+            }
+#ifdef ORBM_STATS
+            if (lane == 0) { atomicAdd(P.evals + 1, (unsigned long long)tWait); atomicAdd(P.evals + 3, (unsigned long long)tRes); atomicAdd(P.evals + 4, (unsigned long long)nIter); atomicAdd(P.evals + 6, 1ull); }
+#endif
+        } else {
+#ifdef ORBM_STATS
+            long long pWait = 0, pWork = 0;
+#endif
+            for (int b = wid - 1; b < nb; b += kSearchWarps - 1) {
+#ifdef ORBM_STATS
+                const long long p0 = clock64();
+#endif
+                const int q = b * 32 + lane;
+                const int at = (b % kRingB) * 32 + lane;
+                if (lane == 0) while (b - done >= kRingB) { __nanosleep(32); }
+                __syncwarp();
+#ifdef ORBM_STATS
+                const long long p1 = clock64(); pWait += p1 - p0;
+#endif
+                Top4 t; t.t0 = t.t1 = t.t2 = t.t3 = kNoEntry; t.count = 0;
+                float qa = 0.f;
+                if (q < P.nq) { lane_walk(P, T, q, occS, mdS, t, nEval); if (P.checkOri) qa = P.qangle[q]; }
+                hdrT[at] = make_uint4(t.t0, t.t1, t.t2, t.t3); hdrCount[at] = t.count; hdrAngle[at] = qa;
+                __syncwarp();
+                if (lane == 0) { __threadfence_block(); ready[b % kRingB] = b + 1; }
+#ifdef ORBM_STATS
+                pWork += clock64() - p1;
+#endif
+            }
+#ifdef ORBM_STATS
+            if (lane == 0) { atomicAdd(P.evals + 7, (unsigned long long)pWait); atomicAdd(P.evals + 8, (unsigned long long)pWork); }
+#endif
+        }
+    } else if (!kWindow && P.state == 0) {
         // independent queries: every warp gathers and resolves its own
         uint32_t* slab = slabs + (size_t)wid * kSlab;
-        for (int q = ctaIdx * kSearchWarps + wid; q < P.nq; q += kSearchWarps * nCtas) {
+        for (int q = ctaIdx + wid * nCtas; q < P.nq; q += kSearchWarps * nCtas) {
             const int count = gather_query(P, T, q, slab, nEval);
             uint32_t e1, e2;
             scan_candidates(P, T, q, slab, count, occS, mdS, e1, e2);
             if (lane == 0) commit_query(P, T, q, e1, e2, P.checkOri ? P.qangle[q] : 0.f, occS, mdS, m21S);
             __syncwarp();
         }
-    } else if (wid == 0) {
+    } else if (!kWindow && wid == 0) {
+#ifdef ORBM_STATS
+        long long tWait = 0, tPar = 0, tRep = 0; int nRep = 0, nRedo = 0;
+#endif
         for (int q0 = 0; q0 < P.nq; q0 += 32) {
+#ifdef ORBM_STATS
+            long long c0 = clock64();
+#endif
             const int q = q0 + lane;
             const bool live = q < P.nq;
             const int slot = q % kSlots;
             if (live) while (ready[slot] != q + 1) { }
             __syncwarp();
+#ifdef ORBM_STATS
+            long long c1 = clock64(); tWait += c1 - c0;
+#endif
             uint32_t e1 = kNoEntry, e2 = kNoEntry;
             float qa = 0.f;
             bool bad = false;
@@ -470,22 +752,43 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
             const int first = badMask ? __ffs(badMask) - 1 : 32;
             if (live && lane < first) commit_query(P, T, q, e1, e2, qa, occS, mdS, m21S);
             __syncwarp();
+#ifdef ORBM_STATS
+            long long c2 = clock64(); tPar += c2 - c1;
+#endif
             for (int i = first; i < 32 && q0 + i < P.nq; ++i) {          // replay in order, whole warp per query
                 const int qq = q0 + i, s = qq % kSlots;
                 uint32_t a1 = slotE1[s], a2 = slotE2[s];
                 const bool redo = a1 == kOverflowEntry || (a1 != kNoEntry && blocked(P, occS, mdS, a1)) ||
                                   (a2 != kNoEntry && blocked(P, occS, mdS, a2));
+#ifdef ORBM_STATS
+                ++nRep; nRedo += redo;
+#endif
                 if (redo) scan_candidates(P, T, qq, slabs + (size_t)s * kSlab, slotCount[s], occS, mdS, a1, a2);
                 if (lane == 0) commit_query(P, T, qq, a1, a2, slotAngle[s], occS, mdS, m21S);
                 __syncwarp();
             }
             if (lane == 0) done = min(q0 + 32, P.nq);
+#ifdef ORBM_STATS
+            tRep += clock64() - c2;
+#endif
         }
+#ifdef ORBM_STATS
+        if (lane == 0) { atomicAdd(P.evals + 1, (unsigned long long)tWait); atomicAdd(P.evals + 2, (unsigned long long)tPar); atomicAdd(P.evals + 3, (unsigned long long)tRep); atomicAdd(P.evals + 4, (unsigned long long)nRep); atomicAdd(P.evals + 5, (unsigned long long)nRedo); atomicAdd(P.evals + 6, 1ull); }
+#endif
     } else {
+#ifdef ORBM_STATS
+        long long pWait = 0, pWork = 0;
+#endif
         for (int q = wid - 1; q < P.nq; q += kSearchWarps - 1) {
             const int slot = q % kSlots;
+#ifdef ORBM_STATS
+            long long p0 = clock64();
+#endif
             if (lane == 0) while (q - done >= kSlots) { __nanosleep(32); }
             __syncwarp();
+#ifdef ORBM_STATS
+            long long p1 = clock64(); pWait += p1 - p0;
+#endif
             uint32_t* slab = slabs + (size_t)slot * kSlab;
             const int count = gather_query(P, T, q, slab, nEval);
             uint32_t e1 = kOverflowEntry, e2 = kNoEntry;
@@ -498,8 +801,17 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
                 ready[slot] = q + 1;
             }
             __syncwarp();
+#ifdef ORBM_STATS
+            pWork += clock64() - p1;
+#endif
         }
+#ifdef ORBM_STATS
+        if (lane == 0) { atomicAdd(P.evals + 7, (unsigned long long)pWait); atomicAdd(P.evals + 8, (unsigned long long)pWork); }
+#endif
     }
+#ifdef ORBM_STATS
+    if (tid == 0) atomicAdd(P.evals + 9, (unsigned long long)(clock64() - kT0));
+#endif
     // evaluation count (reporting only)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) nEval += __shfl_xor_sync(0xffffffffu, nEval, o);
@@ -516,9 +828,10 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
 }
 
 
-__global__ void __launch_bounds__(kSearchThreads) k_search(const SearchParams P) {
+template <bool kWindow>
+__global__ void __launch_bounds__(kSearchThreads, 1) k_search(const SearchParams P) {
     extern __shared__ __align__(16) uint8_t dyn[];
-    search_cta(P, dyn, blockIdx.x, gridDim.x);
+    search_cta<kWindow>(P, dyn, blockIdx.x, gridDim.x);
 }
 
 // rotation-consistency epilogue (e.g. src/ORBmatcher.cc:1862-1884): histogram of accept events, three maxima, drop the rest
@@ -595,7 +908,7 @@ __global__ void __launch_bounds__(kGridThreads) k_track_grid(const TrackBatch T)
     grid_build_cta(n, T.cellOf + (size_t)f * T.stride, T.cellOff + (size_t)f * (kGridCells + 1), T.cellIdx + (size_t)f * T.stride);
 }
 
-__global__ void __launch_bounds__(kSearchThreads) k_track_search(const TrackBatch T) {
+__global__ void __launch_bounds__(kSearchThreads, 1) k_track_search(const TrackBatch T) {
     extern __shared__ __align__(16) uint8_t dyn[];
     const int cur = blockIdx.x + 1, last = blockIdx.x;
     SearchParams P;
@@ -619,7 +932,7 @@ __global__ void __launch_bounds__(kSearchThreads) k_track_search(const TrackBatc
     P.tri = 0; P.coarse = 0; P.ep0 = P.ep1 = 0.f; P.scale2 = nullptr; P.sigma2 = nullptr;
     P.qResult = T.qResult + (size_t)cur * T.stride; P.qDist = T.qDist + (size_t)cur * T.stride; P.qBin = T.qBin + (size_t)cur * T.stride;
     P.evals = T.evals;
-    search_cta(P, dyn, 0, 1);
+    search_cta<true>(P, dyn, 0, 1);
 }
 
 // rotation filter + scatter into the reference's output (CurrentFrame.mvpMapPoints[i2] = pMP  ->  kpMatch[i2] = query)

@@ -198,7 +198,7 @@ int configureShape(Extractor* E, int W, int H) {
     E->treeSmem = tree_smem_layout(E->poolCap, E->scanCap, nullptr, nullptr);
     E->fastTilePitch = (((maxCellW + 6 + 3 + 3) >> 2) + 1) * 2 + 1;      // words per row of each u16x2 pair copy (odd: spreads banks)
     E->fastTileRows = maxCellH + 6;
-    E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (size_t)(maxCellH + 2) * (maxCellW + 2) + 16;
+    E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (((size_t)(maxCellH + 2) * (maxCellW + 2) + 3) & ~(size_t)3) + 16;
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
     CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -101,12 +101,6 @@ __device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
     return best;
 }
 
-// One CTA per reference FAST cell.  The cell's pixels (+3 ring halo) are staged in shared memory with aligned
-// 32-bit loads, every tested pixel's strength is computed once at minThFAST, then the reference's per-cell logic
-// runs on the shared score tile: NMS at iniThFAST; if that leaves the cell empty, NMS at minThFAST
-// (src/ORBextractor.cc:826-846).  Neighbours outside the cell's tested interior count as 0, exactly like a
-// cv::FAST call on the sub-image.  Survivors are compacted in raster order into the cell's fixed slot range.
-// grid (nCells, B), block 256.  dynamic smem: tile + score tile.
 constexpr int kFastThreads = 256;
 
 // FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes (VIMNMX3.U16x2 / native on sm_100a:
@@ -143,13 +137,21 @@ __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t
 // are one aligned 32-bit shared load; each thread then computes the strength of two pixels per pass (fast_strength_x2),
 // once per pixel at minThFAST.  The reference's per-cell logic runs on the shared score tile: NMS at iniThFAST; if that
 // leaves the cell empty, NMS at minThFAST (src/ORBextractor.cc:826-846).  Neighbours outside the cell's tested interior
-// count as 0, exactly like a cv::FAST call on the sub-image.  Survivors are compacted in raster order into the cell's
-// fixed slot range.  grid (nCells, B), block 256.  dynamic smem: 2 x rows x pitchW words + score tile.
+// count as 0, exactly like a cv::FAST call on the sub-image.
+// Corners are sparse, so the strength pass also sets one bit per corner in a raster-order bitmap; NMS then visits only
+// the set bits (one bitmap word per thread), keeps its verdicts as two more bitmap words (ini / min threshold) and the
+// survivors are compacted in raster order with a popcount prefix sum - no second pass over all pixels, no sorting.
+// grid (nCells, B), block 256.  dynamic smem: 2 x rows x pitchW words + score tile.
+constexpr int kFastMaskWords = kFastThreads;       // a cell holds at most 32 * kFastThreads pixels (checked on the host)
+
 __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
                                                              const FastCell* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ cellCount,
                                                              int pitchW, int tileRowsMax, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ uint32_t cmask[kFastMaskWords];
+    __shared__ int warpSum[kFastThreads / 32];
+    __shared__ int total;
     const FastCell c = cells[blockIdx.x];
     const int frame = frameBase + blockIdx.y;
     const int tid = threadIdx.x;
@@ -163,22 +165,27 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     const int sp = w + 2;
     const int gx0 = c.x0 - 3, gy0 = c.y0 - 3;
     const uint8_t* origin = img + (size_t)gy0 * pitch + gx0;
-    const bool aligned = (pitch & 3) == 0;
+    const bool aligned = (((uintptr_t)img | (uintptr_t)pitch) & 3) == 0;
     const int a = aligned ? (int)((uintptr_t)origin & 3) : 0;        // X = tile x + a; rows start word-aligned when aligned
+    const int npx = w * h, nwords = (npx + 31) >> 5;
 
     if (aligned) {
+        // 16 threads per tile row (typical cells need 11-12 words per row)
         const int wordsPerRow = (tw + a + 3) >> 2;
         const uint8_t* base = origin - a;
-        for (int i = tid; i < wordsPerRow * th; i += kFastThreads) {
-            const int ry = i / wordsPerRow, rw = i - ry * wordsPerRow;
-            const uint8_t* src = base + (size_t)ry * pitch + 4 * rw;
-            const uint32_t v = *reinterpret_cast<const uint32_t*>(src);
-            const uint32_t nx = src[4];
-            const uint32_t p0 = v & 255u, p1 = (v >> 8) & 255u, p2 = (v >> 16) & 255u, p3 = v >> 24;
-            uint32_t* ra = SA + ry * pitchW + 2 * rw;
-            uint32_t* rb = SB + ry * pitchW + 2 * rw;
-            ra[0] = p0 | (p1 << 16); ra[1] = p2 | (p3 << 16);
-            rb[0] = p1 | (p2 << 16); rb[1] = p3 | (nx << 16);
+        const int lx = tid & 15;
+        for (int ry = tid >> 4; ry < th; ry += kFastThreads / 16) {
+            const uint8_t* rowp = base + (size_t)ry * pitch;
+            uint32_t* ra = SA + ry * pitchW;
+            uint32_t* rb = SB + ry * pitchW;
+            for (int rw = lx; rw < wordsPerRow; rw += 16) {
+                const uint32_t v = *reinterpret_cast<const uint32_t*>(rowp + 4 * rw);
+                const uint32_t nx = rowp[4 * rw + 4];
+                ra[2 * rw] = __byte_perm(v, 0, 0x4140);          // (p0, p1) as u16 lanes
+                ra[2 * rw + 1] = __byte_perm(v, 0, 0x4342);      // (p2, p3)
+                rb[2 * rw] = __byte_perm(v, 0, 0x4241);          // (p1, p2)
+                rb[2 * rw + 1] = __byte_perm(v, nx, 0x5453);     // (p3, next p0); nx is zero-extended, its byte 1 is 0
+            }
         }
     } else {
         const int pairsPerRow = (tw + 2) >> 1;
@@ -190,7 +197,11 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
             SB[ry * pitchW + rp] = p1 | (p2 << 16);
         }
     }
-    for (int i = tid; i < (h + 2) * sp; i += kFastThreads) score[i] = 0;
+    {
+        uint32_t* sw = reinterpret_cast<uint32_t*>(score);           // the score tile is 4-byte aligned and padded (host)
+        for (int i = tid; i < ((h + 2) * sp + 3) >> 2; i += kFastThreads) sw[i] = 0;
+        cmask[tid] = 0;
+    }
     __syncthreads();
 
     const int minTh = g->minTh, iniTh = g->iniTh;
@@ -202,8 +213,10 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
         const int pw = (w + 1) >> 1;
         const int npairs = pw * h;
         const int P = pitchW;
+        // (py, pc) of pair p advance by a constant step per pass: one division per thread instead of one per pair
+        const int stepY = kFastThreads / pw, stepC = kFastThreads - stepY * pw;
+        int py = tid / pw, pc = tid - py * pw;
         for (int p = tid; p < npairs; p += kFastThreads) {
-            const int py = p / pw, pc = p - py * pw;
             const int b = (py + 3) * P + pc;
             const uint32_t v2 = E[b];
             uint32_t r[16];
@@ -213,40 +226,46 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
             r[12] = O[b - 2];          r[13] = O[b + P - 2];      r[14] = E[b + 2 * P - 1];  r[15] = O[b + 3 * P - 1];
             const uint32_t s2 = fast_strength_x2(v2, r);
             const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
-            uint8_t* sc = score + (py + 1) * sp + 2 * pc + 1;
-            if (s0 > minTh) sc[0] = (uint8_t)s0;
-            if (s1 > minTh && 2 * pc + 1 < w) sc[1] = (uint8_t)s1;
+            const bool c0 = s0 > minTh, c1 = s1 > minTh && 2 * pc + 1 < w;
+            if (c0 || c1) {
+                uint8_t* sc = score + (py + 1) * sp + 2 * pc + 1;
+                const int bit = py * w + 2 * pc;
+                if (c0) { sc[0] = (uint8_t)s0; atomicOr(&cmask[bit >> 5], 1u << (bit & 31)); }
+                if (c1) { sc[1] = (uint8_t)s1; atomicOr(&cmask[(bit + 1) >> 5], 1u << ((bit + 1) & 31)); }
+            }
+            py += stepY; pc += stepC;
+            if (pc >= pw) { pc -= pw; ++py; }
         }
     }
     __syncthreads();
 
-    // NMS at both thresholds over a contiguous raster chunk per thread (<= 32 pixels)
-    const int npx = w * h;
-    const int per = (npx + kFastThreads - 1) / kFastThreads;
-    const int pb = tid * per, pe = min(pb + per, npx);
+    // NMS at both thresholds, corners only: thread t owns bitmap word t (raster pixels 32t .. 32t+31)
     uint32_t keepIni = 0, keepMin = 0;
-    for (int p = pb; p < pe; ++p) {
-        const int py = p / w, px = p - py * w;
-        const uint8_t* sc = score + (py + 1) * sp + px + 1;
-        const int s = sc[0];
-        if (s == 0) continue;
-        int nbMin = 0, nbIni = 0;     // max neighbour stored score at each threshold
+    if (tid < nwords) {
+        uint32_t m = cmask[tid];
+        while (m) {
+            const int bpos = __ffs(m) - 1;
+            m &= m - 1;
+            const int p = tid * 32 + bpos;
+            const int py = p / w, px = p - py * w;
+            const uint8_t* sc = score + (py + 1) * sp + px + 1;
+            const int s = sc[0];
+            int nbMin = 0, nbIni = 0;     // max neighbour stored score at each threshold
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy)
+            for (int dy = -1; dy <= 1; ++dy)
 #pragma unroll
-            for (int dx = -1; dx <= 1; ++dx) {
-                if (dx == 0 && dy == 0) continue;
-                const int q = sc[dy * sp + dx];
-                nbMin = max(nbMin, q);
-                nbIni = max(nbIni, q > iniTh ? q : 0);
-            }
-        // stored scores are strength-1 on both sides of the comparison; strength 0 means "not a corner" (score 0)
-        const int mine = s - 1;
-        if (mine > max(nbMin - 1, 0)) keepMin |= 1u << (p - pb);
-        if (s > iniTh && mine > max(nbIni - 1, 0)) keepIni |= 1u << (p - pb);
+                for (int dx = -1; dx <= 1; ++dx) {
+                    if (dx == 0 && dy == 0) continue;
+                    const int q = sc[dy * sp + dx];
+                    nbMin = max(nbMin, q);
+                    nbIni = max(nbIni, q > iniTh ? q : 0);
+                }
+            // stored scores are strength-1 on both sides of the comparison; strength 0 means "not a corner" (score 0)
+            const int mine = s - 1;
+            if (mine > max(nbMin - 1, 0)) keepMin |= 1u << bpos;
+            if (s > iniTh && mine > max(nbIni - 1, 0)) keepIni |= 1u << bpos;
+        }
     }
-    __shared__ int warpSum[kFastThreads / 32];
-    __shared__ int total;
     const int lane = tid & 31, wid = tid >> 5;
     const int anyIni = __syncthreads_or(keepIni != 0);
     const uint32_t keep = anyIni ? keepIni : keepMin;
@@ -271,7 +290,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     while (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        const int p = pb + b;
+        const int p = tid * 32 + b;
         const int py = p / w, px = p - py * w;
         const int s = score[(py + 1) * sp + px + 1];
         out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
