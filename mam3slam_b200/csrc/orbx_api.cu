@@ -35,7 +35,7 @@ struct Extractor {
     ResizeTap* dTaps = nullptr;
     BlurTiles blurTiles;
     int blurTilesTotal = 0;
-    int fastTilePitch = 0, fastTileRows = 0;
+    int fastTilePitch = 0, fastTileRows = 0, fastThreads = kFastThreads;
     size_t fastSmem = 0, treeSmem = 0;
     int poolCap = 0, scanCap = 0;
     int maxLevelW4 = 0;
@@ -124,7 +124,7 @@ int configureShape(Extractor* E, int W, int H) {
     g.nlevels = L; g.iniTh = E->cfg.ini_th_fast; g.minTh = E->cfg.min_th_fast;
     E->cells.clear();
     std::vector<ResizeTap> taps;
-    size_t qtOff = 0; int kpOff = 0, candOff = 0, maxCells = 0, maxCellW = 0, maxCellH = 0;
+    size_t qtOff = 0; int kpOff = 0, candOff = 0, maxCells = 0, maxCellW = 0, maxCellH = 0, maxCellPx = 0;
     E->poolCap = 0;
     int tileStart = 0;
     for (int l = 0; l < L; ++l) {
@@ -169,6 +169,7 @@ int configureShape(Extractor* E, int W, int H) {
                 c.outOffset = candOff;
                 candOff += c.cap; G.candCap += c.cap;
                 if (c.w > 255 || c.h > 255 || c.w * c.h > 32 * kFastThreads) { E->err = "FAST cell too large"; return ORBX_ERR_UNSUPPORTED; }
+                maxCellPx = std::max<int>(maxCellPx, c.w * c.h);
                 maxCellW = std::max<int>(maxCellW, c.w); maxCellH = std::max<int>(maxCellH, c.h);
                 E->cells.push_back(c);
             }
@@ -202,7 +203,14 @@ int configureShape(Extractor* E, int W, int H) {
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
     CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    CK(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    // fewer threads per cell when the cells are small: the per-thread fixed cost (prologue, scans, barriers) is spread over
+    // more pixels; every thread owns a raster chunk of at most 32 pixels
+    const char* ft = getenv("ORBX_FAST_THREADS");
+    E->fastThreads = maxCellPx <= 32 * 64 ? 64 : maxCellPx <= 32 * 128 ? 128 : 256;
+    if (ft && (atoi(ft) == 64 || atoi(ft) == 128 || atoi(ft) == 256) && maxCellPx <= 32 * atoi(ft)) E->fastThreads = atoi(ft);
+    CK(cudaFuncSetAttribute(k_fast_cells<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
 
     // device buffers
     for (int l = 0; l < L; ++l) {
@@ -254,8 +262,12 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
         ++E->launches;
     }
     mark();
-    k_fast_cells<<<dim3(g.nCells, n), kFastThreads, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount,
-                                                                        E->fastTilePitch, E->fastTileRows, fb);
+    if (E->fastThreads == 64)
+        k_fast_cells<64><<<dim3(g.nCells, n), 64, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
+    else if (E->fastThreads == 128)
+        k_fast_cells<128><<<dim3(g.nCells, n), 128, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
+    else
+        k_fast_cells<256><<<dim3(g.nCells, n), 256, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
     ++E->launches;
     mark();
     k_octree<<<dim3(L, n), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,

@@ -101,7 +101,7 @@ __device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
     return best;
 }
 
-constexpr int kFastThreads = 256;
+constexpr int kFastThreads = 256;          // widest variant; a cell may hold at most 32 * threads pixels
 
 // FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes (VIMNMX3.U16x2 / native on sm_100a:
 // 64 3-input min/max per clk per SM, tools/microbench.cu).  d'[k] = ring[k] - v + 256 per lane (no borrow between lanes:
@@ -142,15 +142,14 @@ __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t
 // the set bits (one bitmap word per thread), keeps its verdicts as two more bitmap words (ini / min threshold) and the
 // survivors are compacted in raster order with a popcount prefix sum - no second pass over all pixels, no sorting.
 // grid (nCells, B), block 256.  dynamic smem: 2 x rows x pitchW words + score tile.
-constexpr int kFastMaskWords = kFastThreads;       // a cell holds at most 32 * kFastThreads pixels (checked on the host)
-
-__global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
+template <int kThreads>
+__global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
                                                              const FastCell* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ cellCount,
                                                              int pitchW, int tileRowsMax, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ uint32_t cmask[kFastMaskWords];
-    __shared__ int warpSum[kFastThreads / 32];
+    __shared__ uint32_t cmask[kThreads + 1];           // raster-order corner bitmap (+1: the slice read below may touch it)
+    __shared__ int warpSum[kThreads / 32];
     __shared__ int total;
     const FastCell c = cells[blockIdx.x];
     const int frame = frameBase + blockIdx.y;
@@ -174,7 +173,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
         const int wordsPerRow = (tw + a + 3) >> 2;
         const uint8_t* base = origin - a;
         const int lx = tid & 15;
-        for (int ry = tid >> 4; ry < th; ry += kFastThreads / 16) {
+        for (int ry = tid >> 4; ry < th; ry += kThreads / 16) {
             const uint8_t* rowp = base + (size_t)ry * pitch;
             uint32_t* ra = SA + ry * pitchW;
             uint32_t* rb = SB + ry * pitchW;
@@ -189,7 +188,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
         }
     } else {
         const int pairsPerRow = (tw + 2) >> 1;
-        for (int i = tid; i < pairsPerRow * th; i += kFastThreads) {
+        for (int i = tid; i < pairsPerRow * th; i += kThreads) {
             const int ry = i / pairsPerRow, rp = i - ry * pairsPerRow;
             const uint8_t* src = origin + (size_t)ry * pitch + 2 * rp;
             const uint32_t p0 = src[0], p1 = src[1], p2 = src[2];
@@ -199,8 +198,9 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     }
     {
         uint32_t* sw = reinterpret_cast<uint32_t*>(score);           // the score tile is 4-byte aligned and padded (host)
-        for (int i = tid; i < ((h + 2) * sp + 3) >> 2; i += kFastThreads) sw[i] = 0;
+        for (int i = tid; i < ((h + 2) * sp + 3) >> 2; i += kThreads) sw[i] = 0;
         cmask[tid] = 0;
+        if (tid == 0) cmask[kThreads] = 0;
     }
     __syncthreads();
 
@@ -214,9 +214,9 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
         const int npairs = pw * h;
         const int P = pitchW;
         // (py, pc) of pair p advance by a constant step per pass: one division per thread instead of one per pair
-        const int stepY = kFastThreads / pw, stepC = kFastThreads - stepY * pw;
+        const int stepY = kThreads / pw, stepC = kThreads - stepY * pw;
         int py = tid / pw, pc = tid - py * pw;
-        for (int p = tid; p < npairs; p += kFastThreads) {
+        for (int p = tid; p < npairs; p += kThreads) {
             const int b = (py + 3) * P + pc;
             const uint32_t v2 = E[b];
             uint32_t r[16];
@@ -239,16 +239,21 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     }
     __syncthreads();
 
-    // NMS at both thresholds, corners only: thread t owns bitmap word t (raster pixels 32t .. 32t+31)
+    // NMS at both thresholds, corners only.  Every thread owns a contiguous raster chunk (<= 32 pixels, so the survivors
+    // come out in raster order) and visits just the corner bits of its slice of the bitmap.
+    const int per = (npx + kThreads - 1) / kThreads;
+    const int pb = tid * per, pe = min(pb + per, npx);
     uint32_t keepIni = 0, keepMin = 0;
-    if (tid < nwords) {
-        uint32_t m = cmask[tid];
+    if (pb < pe) {
+        uint32_t m = __funnelshift_r(cmask[pb >> 5], cmask[(pb >> 5) + 1], pb & 31);
+        if (pe - pb < 32) m &= (1u << (pe - pb)) - 1;
+        int py = pb / w, px = pb - py * w;             // chunk origin; a corner's coordinates follow by carry, no division
         while (m) {
             const int bpos = __ffs(m) - 1;
             m &= m - 1;
-            const int p = tid * 32 + bpos;
-            const int py = p / w, px = p - py * w;
-            const uint8_t* sc = score + (py + 1) * sp + px + 1;
+            int cy = py, cx = px + bpos;
+            while (cx >= w) { cx -= w; ++cy; }
+            const uint8_t* sc = score + (cy + 1) * sp + cx + 1;
             const int s = sc[0];
             int nbMin = 0, nbIni = 0;     // max neighbour stored score at each threshold
 #pragma unroll
@@ -276,11 +281,11 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     if (lane == 31) warpSum[wid] = incl;
     __syncthreads();
     if (wid == 0) {
-        int v = lane < kFastThreads / 32 ? warpSum[lane] : 0;
+        int v = lane < kThreads / 32 ? warpSum[lane] : 0;
         int iv = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += t; }
-        if (lane < kFastThreads / 32) warpSum[lane] = iv - v;
+        if (lane < kThreads / 32) warpSum[lane] = iv - v;
         if (lane == 31) total = iv;
     }
     __syncthreads();
@@ -290,7 +295,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast_cells(const DevGeom* __re
     while (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        const int p = tid * 32 + b;
+        const int p = pb + b;
         const int py = p / w, px = p - py * w;
         const int s = score[(py + 1) * sp + px + 1];
         out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
