@@ -18,6 +18,9 @@ struct Extractor {
     orbx_config cfg;
     int device = 0;
     cudaStream_t stream = nullptr, stream2 = nullptr;
+    cudaStream_t aux[2] = {nullptr, nullptr};          // side streams: the blur runs beside FAST + quadtree
+    cudaEvent_t evFork[2] = {nullptr, nullptr}, evJoin[2] = {nullptr, nullptr};
+    bool overlap = true;
     int chunk = 0;                   // frames per pipelined sub-batch of the host path (0 = auto)
     std::string err;
     long long launches = 0;
@@ -262,6 +265,11 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
         ++E->launches;
     }
     mark();
+    // The blur needs only the pyramid, and the quadtree (latency-bound, ~1/3 of the issue slots) leaves most of the SMs'
+    // issue bandwidth unused: run the blur on a side stream beside the quadtree and join before the descriptors.
+    // With stage timing on, everything stays on one stream so that the per-stage events mean what they say.
+    const int slot = st == E->stream2 ? 1 : 0;
+    const bool side = E->overlap && !E->timing && E->aux[slot];
     if (E->fastThreads == 64)
         k_fast_cells<64><<<dim3(g.nCells, n), 64, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
     else if (E->fastThreads == 128)
@@ -270,16 +278,23 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
         k_fast_cells<256><<<dim3(g.nCells, n), 256, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
     ++E->launches;
     mark();
-    k_octree<<<dim3(L, n), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,
+    if (side) {
+        CK(cudaEventRecord(E->evFork[slot], st));
+        CK(cudaStreamWaitEvent(E->aux[slot], E->evFork[slot], 0));
+        k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
+        CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
+    }
+    k_octree<<<dim3(n, L), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,
                                                             E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb);
     ++E->launches;
     mark();
-    k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
+    if (!side) k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
     ++E->launches;
     mark();
     k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork, fb);
     ++E->launches;
     mark();
+    if (side) CK(cudaStreamWaitEvent(st, E->evJoin[slot], 0));
     k_orient_brief<<<dim3((g.outCap + kDescWarps - 1) / kDescWarps, n), kDescWarps * 32, 0, st>>>(
         E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
     ++E->launches;
@@ -348,6 +363,12 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     if ((e = cudaSetDevice(E->device)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamCreateWithFlags(&E->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamCreateWithFlags(&E->stream2, cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
+    for (int i = 0; i < 2; ++i) {
+        if ((e = cudaStreamCreateWithFlags(&E->aux[i], cudaStreamNonBlocking)) != cudaSuccess) return fail(e);
+        if ((e = cudaEventCreateWithFlags(&E->evFork[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
+        if ((e = cudaEventCreateWithFlags(&E->evJoin[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
+    }
+    if (const char* ov = getenv("ORBX_OVERLAP")) E->overlap = atoi(ov) != 0;
     if (const char* c = getenv("ORBX_CHUNK")) E->chunk = atoi(c);
     for (auto& ev : E->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e);
     // algorithm constants: circular-patch half-widths (:453-468) and the BRIEF pattern
@@ -377,6 +398,11 @@ void orbx_destroy(orbx_handle h) {
     for (auto& ev : E->ev) if (ev) cudaEventDestroy(ev);
     if (E->stream) cudaStreamDestroy(E->stream);
     if (E->stream2) cudaStreamDestroy(E->stream2);
+    for (int i = 0; i < 2; ++i) {
+        if (E->aux[i]) { cudaStreamSynchronize(E->aux[i]); cudaStreamDestroy(E->aux[i]); }
+        if (E->evFork[i]) cudaEventDestroy(E->evFork[i]);
+        if (E->evJoin[i]) cudaEventDestroy(E->evJoin[i]);
+    }
     delete h;
 }
 

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
     __shared__ int sW[33];
     TreeSmem S;
     tree_smem_layout(P, scanCap, &S, smem);
-    const int l = blockIdx.x, frame = frameBase + blockIdx.y;
+    const int l = blockIdx.y, frame = frameBase + blockIdx.x;      // level-major launch order: the heavy fine levels start first
     const LevelGeom& L = g->lv[l];
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     const int cb = L.cellBegin, nc = L.cellEnd - L.cellBegin;
