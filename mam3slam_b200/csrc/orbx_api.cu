@@ -39,6 +39,7 @@ struct Extractor {
     BlurTiles blurTiles;
     int blurTilesTotal = 0;
     int fastTilePitch = 0, fastTileRows = 0, fastThreads = kFastThreads;
+    bool pyrFast[kMaxLevels] = {};                  // level may use k_pyr_level_fast (4 pixels read <= 8 source bytes)
     size_t fastSmem = 0, treeSmem = 0;
     int poolCap = 0, scanCap = 0;
     int maxLevelW4 = 0;
@@ -188,6 +189,12 @@ int configureShape(Extractor* E, int W, int H) {
             G.areaFast = (P.w == 2 * G.w && P.h == 2 * G.h) ? 1 : 0;
             G.tabX = (int)taps.size(); makeTaps(P.w, G.w, false, taps);
             G.tabY = (int)taps.size(); makeTaps(P.h, G.h, true, taps);
+            bool ok = !G.areaFast && (P.pitch & 3) == 0;
+            for (int x = 0; x < G.w && ok; x += 4) {
+                const int last = std::min(x + 3, G.w - 1);
+                if (std::min(taps[G.tabX + last].ofs + 1, P.w - 1) - taps[G.tabX + x].ofs > 7) ok = false;
+            }
+            E->pyrFast[l] = ok;
         }
         E->blurTiles.start[l] = tileStart;
         E->blurTiles.tilesX[l] = (G.w + kBlurStripW - 1) / kBlurStripW;
@@ -261,7 +268,13 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
     mark();
     for (int l = 1; l < L; ++l) {
         dim3 grid((g.lv[l].w + 127) / 128, (g.lv[l].h + 7) / 8, n), block(32, 8);
-        k_pyr_level<<<grid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);
+        const bool srcAligned = l > 1 || ((((uintptr_t)l0.base | (uintptr_t)l0.pitch | (uintptr_t)l0.frameBytes) & 3) == 0);
+        if (E->pyrFast[l] && srcAligned) {
+            dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + 8 * kPyrRows - 1) / (8 * kPyrRows), n);
+            k_pyr_level_fast<<<fgrid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);
+        } else {
+            k_pyr_level<<<grid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);
+        }
         ++E->launches;
     }
     mark();

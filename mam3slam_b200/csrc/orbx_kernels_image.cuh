@@ -73,6 +73,80 @@ __global__ void __launch_bounds__(256) k_pyr_level(const DevGeom* __restrict__ g
     }
 }
 
+// E1, fast path (scale factor <= 2, word-aligned source rows).  A thread produces 4 adjacent pixels of 4 consecutive rows.
+// Horizontal taps: the (at most 7) source bytes its 4 pixels read are cut out of three aligned words with two funnel
+// shifts, each pixel's pair (p[a], p[a+1]) is picked with one PRMT (selector precomputed from the tap table) and weighted
+// with one IDP.2A against its (c0, c1) pair.  Source rows are shared by consecutive output rows (1.2 source rows per output
+// row), so the horizontal results of the last two source rows stay in registers.  Vertical pass: two IMAD.HI per pixel on
+// operands pre-shifted so that hi32((h>>4 << 16) * b) == (b * (h>>4)) >> 16.  ~13 instructions per pixel instead of ~65.
+// grid (ceil(w/128), ceil(h/32), B), block (32, 8).
+constexpr int kPyrRows = 4;
+
+__global__ void __launch_bounds__(256) k_pyr_level_fast(const DevGeom* __restrict__ g, Level0 l0, int l,
+                                                        const ResizeTap* __restrict__ taps, int frameBase) {
+    const LevelGeom& D = g->lv[l];
+    const LevelGeom& S = g->lv[l - 1];
+    const int frame = frameBase + blockIdx.z;
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int yb = (blockIdx.y * 8 + threadIdx.y) * kPyrRows;
+    if (x4 >= D.w || yb >= D.h) return;
+    int sp;
+    const uint8_t* src = level_ptr(g, l0, l - 1, frame, &sp);
+    uint8_t* dst = g->lvl[l] + (size_t)frame * D.planeBytes;
+    // per-thread column setup
+    uint32_t coef[4], sel[4];
+    const ResizeTap t0 = taps[D.tabX + x4];
+    const int a0 = t0.ofs;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const ResizeTap t = taps[D.tabX + min(x4 + k, D.w - 1)];
+        const int r0 = t.ofs - a0, r1 = min(t.ofs + 1, S.w - 1) - a0;
+        sel[k] = (uint32_t)r0 | ((uint32_t)r1 << 4);
+        coef[k] = (uint32_t)(uint16_t)t.c0 | ((uint32_t)(uint16_t)t.c1 << 16);
+    }
+    const int maxWord = (S.w - 1) >> 2;
+    const int w0i = a0 >> 2, w1i = min(w0i + 1, maxWord), w2i = min(w0i + 2, maxWord);
+    const int sh = (a0 & 3) * 8;
+    uint32_t hA[4], hB[4];                  // pre-shifted horizontal results of source rows rA, rB
+    int rA = -1, rB = -1;
+    auto hrow = [&](int r, uint32_t (&h)[4]) {
+        const uint32_t* rowp = reinterpret_cast<const uint32_t*>(src + (size_t)r * sp);
+        const uint32_t W0 = rowp[w0i], W1 = rowp[w1i], W2 = rowp[w2i];
+        const uint32_t lo = __funnelshift_r(W0, W1, sh), hi = __funnelshift_r(W1, W2, sh);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t hk = __dp2a_lo(coef[k], __byte_perm(lo, hi, sel[k]), 0u);     // p[a]*c0 + p[a1]*c1
+            h[k] = (hk << 12) & 0xffff0000u;                                             // (hk >> 4) << 16
+        }
+    };
+#pragma unroll
+    for (int j = 0; j < kPyrRows; ++j) {
+        const int y = yb + j;
+        if (y >= D.h) break;
+        const ResizeTap ty = taps[D.tabY + y];
+        const int s0 = min(max(ty.ofs, 0), S.h - 1), s1 = min(max(ty.ofs + 1, 0), S.h - 1);
+        // bring rows s0, s1 into (hA, hB); consecutive output rows usually need only one new source row
+        if (s0 == rB) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) hA[k] = hB[k];
+            rA = rB; rB = -1;
+        } else if (s0 != rA) { hrow(s0, hA); rA = s0; }
+        if (s1 == rA) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) hB[k] = hA[k];
+            rB = rA;
+        } else if (s1 != rB) { hrow(s1, hB); rB = s1; }
+        const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = (__umulhi(hA[k], b0) + __umulhi(hB[k], b1) + 2u) >> 2;
+        const uint32_t packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+        uint8_t* d = dst + (size_t)y * D.pitch + x4;
+        if (x4 + 3 < D.w) *reinterpret_cast<uint32_t*>(d) = packed;
+        else for (int k = 0; k < 4 && x4 + k < D.w; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // E2: FAST-9/16 strength of one pixel: s = max over the 16 cyclic 9-arcs of max(min(v - ring), min(ring - v)).
 // cv::FAST declares a corner at threshold t iff s > t and reports response s-1.
