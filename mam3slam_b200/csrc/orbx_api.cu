@@ -21,6 +21,10 @@ struct Extractor {
     cudaStream_t aux[2] = {nullptr, nullptr};          // side streams: the blur runs beside FAST + quadtree
     cudaEvent_t evFork[2] = {nullptr, nullptr}, evJoin[2] = {nullptr, nullptr};
     bool overlap = true;
+    // CUDA graphs of the launch sequence of one pass, keyed by everything the kernels' arguments depend on
+    struct PassGraph { const uint8_t* base; size_t frameBytes; int pitch, n, lap0, lap1, fb, slot; cudaGraphExec_t exec; int kernels; };
+    std::vector<PassGraph> graphs;
+    bool useGraphs = true;
     int chunk = 0;                   // frames per pipelined sub-batch of the host path (0 = auto)
     std::string err;
     long long launches = 0;
@@ -79,6 +83,8 @@ struct Extractor {
 int cvRoundF(float v) { return (int)lrintf(v); }
 
 void freeShape(Extractor* E) {
+    for (auto& G : E->graphs) cudaGraphExecDestroy(G.exec);      // they hold pointers into the buffers freed below
+    E->graphs.clear();
     for (void* p : E->allocs) cudaFree(p);
     E->allocs.clear();
     if (E->hImg) cudaFreeHost(E->hImg);
@@ -258,7 +264,7 @@ int configureShape(Extractor* E, int W, int H) {
 
 // The launch sequence of one pass over frames [fb, fb+n) of the handle's buffers; level 0 of frame fb+i lives at
 // l0.base + i*l0.frameBytes.
-int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb = 0) {
+int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb) {
     const DevGeom& g = E->geom;
     const int L = g.nlevels;
     const bool tm = E->timing && fb == 0;
@@ -313,7 +319,45 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
     ++E->launches;
     mark();
     CK(cudaGetLastError());
-    if (fb == 0) { E->lastFrames = n; E->lastL0 = l0; }
+    return ORBX_OK;
+}
+
+// One pass = 13 kernel launches (+ the side-stream fork / join).  At 16 frames per sub-batch that is ~0.3 ms of GPU work
+// behind ~20 driver calls, so the host path was launch-bound; the sequence is captured once per argument set into a CUDA
+// graph and replayed with a single call.  Stage timing (events between the kernels) uses the plain launches.
+int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb = 0) {
+    Level0 l0abs = l0;
+    int rc = ORBX_OK;
+    if (!E->useGraphs || E->timing) {
+        rc = launchPass(E, l0, n, lap0, lap1, st, fb);
+    } else {
+        const int slot = st == E->stream2 ? 1 : 0;
+        Extractor::PassGraph* hit = nullptr;
+        for (auto& G : E->graphs)
+            if (G.base == l0.base && G.frameBytes == l0.frameBytes && G.pitch == l0.pitch && G.n == n && G.lap0 == lap0 && G.lap1 == lap1 &&
+                G.fb == fb && G.slot == slot) { hit = &G; break; }
+        if (!hit) {
+            if (E->graphs.size() >= 64) { for (auto& G : E->graphs) cudaGraphExecDestroy(G.exec); E->graphs.clear(); }
+            const long long before = E->launches;
+            cudaGraph_t graph = nullptr;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            rc = launchPass(E, l0, n, lap0, lap1, st, fb);
+            cudaError_t ce = cudaStreamEndCapture(st, &graph);
+            if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+            CK(ce);
+            Extractor::PassGraph G{l0.base, l0.frameBytes, l0.pitch, n, lap0, lap1, fb, slot, nullptr, (int)(E->launches - before)};
+            E->launches = before;
+            ce = cudaGraphInstantiate(&G.exec, graph, 0);
+            cudaGraphDestroy(graph);
+            CK(ce);
+            E->graphs.push_back(G);
+            hit = &E->graphs.back();
+        }
+        CK(cudaGraphLaunch(hit->exec, st));
+        E->launches += hit->kernels;
+    }
+    if (rc) return rc;
+    if (fb == 0) { E->lastFrames = n; E->lastL0 = l0abs; }
     else E->lastFrames = std::max(E->lastFrames, fb + n);
     return ORBX_OK;
 }
@@ -382,6 +426,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
         if ((e = cudaEventCreateWithFlags(&E->evJoin[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
     }
     if (const char* ov = getenv("ORBX_OVERLAP")) E->overlap = atoi(ov) != 0;
+    if (const char* gr = getenv("ORBX_GRAPHS")) E->useGraphs = atoi(gr) != 0;
     if (const char* c = getenv("ORBX_CHUNK")) E->chunk = atoi(c);
     for (auto& ev : E->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e);
     // algorithm constants: circular-patch half-widths (:453-468) and the BRIEF pattern
@@ -494,7 +539,7 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int 
     const int B = E->cfg.max_batch;
     const int p0 = g.lv[0].pitch;
     const size_t plane = g.lv[0].planeBytes;
-    int C = E->chunk > 0 ? E->chunk : (B >= 32 ? B / 4 : (B >= 8 ? B / 2 : B));
+    int C = E->chunk > 0 ? E->chunk : (B >= 8 ? B / 2 : B);      // two sub-batches: smaller ones lose more to kernel tails than they hide
     C = std::max(1, std::min(C, B));
     const bool inPinned = isPinned(imgs[0]) && isPinned(imgs[nimg - 1]);
     const bool kpPinned = kps && isPinned(kps) && isPinned(kps + (size_t)nimg * cap - 1);
