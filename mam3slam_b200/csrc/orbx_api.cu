@@ -43,6 +43,7 @@ struct Extractor {
     BlurTiles blurTiles;
     int blurTilesTotal = 0;
     int fastTilePitch = 0, fastTileRows = 0, fastThreads = kFastThreads;
+    bool fastPitchConst = false;
     bool pyrFast[kMaxLevels] = {};                  // level may use k_pyr_level_fast (4 pixels read <= 8 source bytes)
     size_t fastSmem = 0, treeSmem = 0;
     int poolCap = 0, scanCap = 0;
@@ -214,6 +215,8 @@ int configureShape(Extractor* E, int W, int H) {
     E->scanCap = std::max(std::max(E->poolCap, maxCells), 64) + 8;
     E->treeSmem = tree_smem_layout(E->poolCap, E->scanCap, nullptr, nullptr);
     E->fastTilePitch = (((maxCellW + 6 + 3 + 3) >> 2) + 1) * 2 + 1;      // words per row of each u16x2 pair copy (odd: spreads banks)
+    E->fastPitchConst = E->fastTilePitch <= 33;      // the usual 35-px cells: compile-time pitch (k_fast_cells<., 33>)
+    if (E->fastPitchConst) E->fastTilePitch = 33;
     E->fastTileRows = maxCellH + 6;
     E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (((size_t)(maxCellH + 2) * (maxCellW + 2) + 3) & ~(size_t)3) + 16;
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
@@ -224,9 +227,12 @@ int configureShape(Extractor* E, int W, int H) {
     const char* ft = getenv("ORBX_FAST_THREADS");
     E->fastThreads = maxCellPx <= 32 * 64 ? 64 : maxCellPx <= 32 * 128 ? 128 : 256;
     if (ft && (atoi(ft) == 64 || atoi(ft) == 128 || atoi(ft) == 256) && maxCellPx <= 32 * atoi(ft)) E->fastThreads = atoi(ft);
-    CK(cudaFuncSetAttribute(k_fast_cells<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<64, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<128, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<128, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<256, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(cudaFuncSetAttribute(k_fast_cells<256, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
 
     // device buffers
     for (int l = 0; l < L; ++l) {
@@ -289,12 +295,16 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     // With stage timing on, everything stays on one stream so that the per-stage events mean what they say.
     const int slot = st == E->stream2 ? 1 : 0;
     const bool side = E->overlap && !E->timing && E->aux[slot];
-    if (E->fastThreads == 64)
-        k_fast_cells<64><<<dim3(g.nCells, n), 64, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
-    else if (E->fastThreads == 128)
-        k_fast_cells<128><<<dim3(g.nCells, n), 128, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
-    else
-        k_fast_cells<256><<<dim3(g.nCells, n), 256, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb);
+    {
+        const dim3 fg(g.nCells, n);
+#define ORBX_FAST_LAUNCH(T, P) k_fast_cells<T, P><<<fg, T, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb)
+        if (E->fastPitchConst) {
+            if (E->fastThreads == 64) ORBX_FAST_LAUNCH(64, 33); else if (E->fastThreads == 128) ORBX_FAST_LAUNCH(128, 33); else ORBX_FAST_LAUNCH(256, 33);
+        } else {
+            if (E->fastThreads == 64) ORBX_FAST_LAUNCH(64, 0); else if (E->fastThreads == 128) ORBX_FAST_LAUNCH(128, 0); else ORBX_FAST_LAUNCH(256, 0);
+        }
+#undef ORBX_FAST_LAUNCH
+    }
     ++E->launches;
     mark();
     if (side) {

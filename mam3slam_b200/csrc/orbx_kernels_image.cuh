@@ -178,19 +178,16 @@ __device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
 constexpr int kFastThreads = 256;          // widest variant; a cell may hold at most 32 * threads pixels
 
 // FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes (VIMNMX3.U16x2 / native on sm_100a:
-// 64 3-input min/max per clk per SM, tools/microbench.cu).  d'[k] = ring[k] - v + 256 per lane (no borrow between lanes:
-// 1 <= d' <= 511), sliding 9-window minima and maxima as min3(min3, min3, min3), then
-//   s = max( max_k min9[k] - 256, 256 - min_k max9[k], 0 ).
+// 64 3-input min/max per clk per SM, tools/microbench.cu).  Sliding 9-window minima and maxima of the ring as
+// min3(min3, min3, min3), then  s = max( max_k min9[k] - v, v - min_k max9[k], 0 )  per lane.
 __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t (&r)[16]) {
-    const uint32_t c = 0x01000100u - v2;
-    uint32_t d[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) d[k] = r[k] + c;
+    // min / max commute with the per-lane offset (256 - v), so the windows run on the raw ring values and the centre is
+    // applied once at the end
     uint32_t tmin[16], tmax[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        tmin[k] = __vimin3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
-        tmax[k] = __vimax3_u16x2(d[k], d[(k + 1) & 15], d[(k + 2) & 15]);
+        tmin[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+        tmax[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
     }
     uint32_t a9[16], b9[16];
 #pragma unroll
@@ -202,7 +199,8 @@ __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t
 #pragma unroll
     for (int k = 3; k < 15; k += 2) { A = __vimax3_u16x2(A, a9[k], a9[k + 1]); B = __vimin3_u16x2(B, b9[k], b9[k + 1]); }
     A = __vmaxu2(A, a9[15]); B = __vminu2(B, b9[15]);
-    const uint32_t s = __vimax3_u16x2(A, 0x02000200u - B, 0x01000100u);
+    // per lane: A + 256 - v and v + 256 - B are in [1, 511]: no borrow between the two u16 lanes
+    const uint32_t s = __vimax3_u16x2(A + (0x01000100u - v2), (v2 + 0x01000100u) - B, 0x01000100u);
     return s - 0x01000100u;
 }
 
@@ -216,12 +214,13 @@ __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t
 // the set bits (one bitmap word per thread), keeps its verdicts as two more bitmap words (ini / min threshold) and the
 // survivors are compacted in raster order with a popcount prefix sum - no second pass over all pixels, no sorting.
 // grid (nCells, B), block 256.  dynamic smem: 2 x rows x pitchW words + score tile.
-template <int kThreads>
+template <int kThreads, int kPitch>      // kPitch: compile-time tile pitch in words (0 = use the pitchW argument)
 __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
                                                              const FastCell* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ cellCount,
-                                                             int pitchW, int tileRowsMax, int frameBase) {
+                                                             int pitchWArg, int tileRowsMax, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
+    const int pitchW = kPitch ? kPitch : pitchWArg;    // a constant pitch turns the 17 ring addresses into immediates
     __shared__ uint32_t cmask[kThreads + 1];           // raster-order corner bitmap (+1: the slice read below may touch it)
     __shared__ int warpSum[kThreads / 32];
     __shared__ int total;
@@ -247,17 +246,32 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
         const int wordsPerRow = (tw + a + 3) >> 2;
         const uint8_t* base = origin - a;
         const int lx = tid & 15;
-        for (int ry = tid >> 4; ry < th; ry += kThreads / 16) {
-            const uint8_t* rowp = base + (size_t)ry * pitch;
-            uint32_t* ra = SA + ry * pitchW;
-            uint32_t* rb = SB + ry * pitchW;
-            for (int rw = lx; rw < wordsPerRow; rw += 16) {
-                const uint32_t v = *reinterpret_cast<const uint32_t*>(rowp + 4 * rw);
-                const uint32_t nx = rowp[4 * rw + 4];
-                ra[2 * rw] = __byte_perm(v, 0, 0x4140);          // (p0, p1) as u16 lanes
-                ra[2 * rw + 1] = __byte_perm(v, 0, 0x4342);      // (p2, p3)
-                rb[2 * rw] = __byte_perm(v, 0, 0x4241);          // (p1, p2)
-                rb[2 * rw + 1] = __byte_perm(v, nx, 0x5453);     // (p3, next p0); nx is zero-extended, its byte 1 is 0
+        constexpr int RS = kThreads / 16;               // rows per pass
+        for (int rw = lx; rw < wordsPerRow; rw += 16) {
+            for (int ryb = tid >> 4; ryb < th; ryb += 4 * RS) {
+                // four rows in flight: all loads are issued before the first expansion
+                uint32_t v[4], nx[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int ry = ryb + j * RS;
+                    if (ry < th) {
+                        const uint8_t* rowp = base + (size_t)ry * pitch + 4 * rw;
+                        v[j] = *reinterpret_cast<const uint32_t*>(rowp);
+                        nx[j] = rowp[4];
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int ry = ryb + j * RS;
+                    if (ry < th) {
+                        uint32_t* ra = SA + ry * pitchW + 2 * rw;
+                        uint32_t* rb = SB + ry * pitchW + 2 * rw;
+                        ra[0] = __byte_perm(v[j], 0, 0x4140);          // (p0, p1) as u16 lanes
+                        ra[1] = __byte_perm(v[j], 0, 0x4342);          // (p2, p3)
+                        rb[0] = __byte_perm(v[j], 0, 0x4241);          // (p1, p2)
+                        rb[1] = __byte_perm(v[j], nx[j], 0x5453);      // (p3, next p0); nx is zero-extended, its byte 1 is 0
+                    }
+                }
             }
         }
     } else {
