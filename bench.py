@@ -179,13 +179,13 @@ def knn_bench(args, torch, dist, rank, world, local):
     dd = torch.empty((NQ, K), dtype=torch.int16, device="cuda")
     di = torch.empty((NQ, K), dtype=torch.int32, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
-    gath_d = [torch.empty_like(dd) for _ in range(world)]
+    gath_d = [torch.empty_like(dd).view(torch.uint8) for _ in range(world)]       # 16-bit distances travel as bytes
     gath_i = [torch.empty_like(di) for _ in range(world)]
 
     def step():
         m.knn_device(D, q.data_ptr(), NQ, K, dd.data_ptr(), di.data_ptr(), st)
         if world > 1:
-            dist.all_gather(gath_d, dd)
+            dist.all_gather(gath_d, dd.view(torch.uint8))
             dist.all_gather(gath_i, di)
 
     for _ in range(3):
@@ -206,7 +206,7 @@ def knn_bench(args, torch, dist, rank, world, local):
     ms = float(ms.item())
     # correctness of the merged result on rank 0: the planted neighbour (distance 1) is found for every query
     if world > 1:
-        md, mi = ORBmatcher.knn_merge(torch.stack(gath_d).cpu().numpy().view(np.uint16), torch.stack(gath_i).cpu().numpy())
+        md, mi = ORBmatcher.knn_merge(torch.stack(gath_d).cpu().numpy().view(np.uint16).reshape(world, NQ, K), torch.stack(gath_i).cpu().numpy())
     else:
         md, mi = dd.cpu().numpy().view(np.uint16), di.cpu().numpy()
     ok = bool((md[:, 0] <= 1).all())
