@@ -459,13 +459,17 @@ __global__ void __launch_bounds__(256) k_blur7(const DevGeom* __restrict__ g, Le
         for (int j = 0; j < 4; ++j) ring[i][j] = 0;
 
     const int rowsNeeded = min(kBlurStripH, h - y0) + 6;
+    // the words of the next three strip rows are in flight while the current one is worked on (the loop is latency-bound
+    // otherwise: one DRAM round trip per row)
+    auto rowWord = [&](int r) { return blur_load_word(src + (size_t)reflect101_near(min(y0 + r - 3, h + 2), h) * pitch, x, w, aligned); };
+    uint32_t Cq[3] = {rowWord(0), rowWord(1), rowWord(2)};
     for (int r0 = 0; r0 < rowsNeeded; r0 += 6) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) {
             const int r = r0 + k;                               // strip row r = image row y0 + r - 3
             const int yo = y0 + r - 6;                          // output row completed by this input row
-            const int sy = reflect101_near(min(y0 + r - 3, h + 2), h);
-            const uint32_t C = blur_load_word(src + (size_t)sy * pitch, x, w, aligned);
+            const uint32_t C = Cq[k % 3];
+            Cq[k % 3] = rowWord(r + 3);
             const uint32_t Lw = __shfl_up_sync(0xffffffffu, C, 1);
             const uint32_t Rw = __shfl_down_sync(0xffffffffu, C, 1);
             uint32_t hc[4];
