@@ -249,22 +249,34 @@ def run_gpu(args):
         host[i] = np.roll(host[i], (i // len(frames)) * 3, axis=1)
     dev = torch.from_numpy(host).cuda()
     img_bytes = W * H
-    ex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
-    mt = ORBmatcher(0.9, True, device=local)
+    # `pipes` independent (extractor, matcher, stream) triples work on alternating batches of the SAME frame stream, so that the
+    # tracking step and the kernel tails of batch i overlap the extraction of batch i+1 (each handle owns its buffers, so
+    # nothing is overwritten while it is still being read).  pipes = 1 is the strictly serial schedule.
+    npipes = max(1, args.pipes)
+    pipes = []
+    for _ in range(npipes):
+        pex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
+        pmt = ORBmatcher(0.9, True, device=local)
+        pts = torch.cuda.Stream()          # a real (non-NULL) stream: CUDA events below are recorded on it
+        pex.extract_device(dev.data_ptr(), img_bytes, B, W, H, W, (0, 1000), pts.cuda_stream)   # allocates the shape-dependent buffers
+        torch.cuda.synchronize()
+        pdk, pdd, pdc, pstride = pex.results_batch_device()
+        pipes.append(dict(ex=pex, mt=pmt, ts=pts, st=pts.cuda_stream, dk=pdk, dd=pdd, dc=pdc,
+                          kpm=torch.empty((B, pstride), dtype=torch.int32, device="cuda"),
+                          nmt=torch.empty(B, dtype=torch.int32, device="cuda")))
+    ex, mt, tstream = pipes[0]["ex"], pipes[0]["mt"], pipes[0]["ts"]
     sf = ex.GetScaleFactors()
-    tstream = torch.cuda.Stream()          # a real (non-NULL) stream: CUDA events below are recorded on it
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
-    ex.extract_device(dev.data_ptr(), img_bytes, B, W, H, W, (0, 1000), stream)   # allocates the shape-dependent buffers
-    torch.cuda.synchronize()
-    dk, dd, dc, stride = ex.results_batch_device()
-    kpm = torch.empty((B, stride), dtype=torch.int32, device="cuda")
-    nmt = torch.empty(B, dtype=torch.int32, device="cuda")
+    dk, dd, dc, stride = pipes[0]["dk"], pipes[0]["dd"], pipes[0]["dc"], ex.results_batch_device()[3]
+    kpm, nmt = pipes[0]["kpm"], pipes[0]["nmt"]
 
     def step_device(i):
         s = i % nsets
-        ex.extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), stream)
-        mt.track_batch_device(B, dk, dd, dc, stride, BOUNDS, sf, TH_TRACK, kpm.data_ptr(), nmt.data_ptr(), stream=stream)
+        P = pipes[i % npipes]
+        P["ex"].extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), P["st"])
+        P["mt"].track_batch_device(B, P["dk"], P["dd"], P["dc"], stride, BOUNDS, sf, TH_TRACK, P["kpm"].data_ptr(), P["nmt"].data_ptr(),
+                                   stream=P["st"])
 
     def barrier():
         torch.cuda.synchronize()
@@ -279,15 +291,21 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    l0 = ex.launch_count() + mt.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    def launches_now():
+        return sum(P["ex"].launch_count() + P["mt"].launch_count() for P in pipes)
+    l0 = launches_now()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e0.record(pipes[args.warmup % npipes]["ts"])      # every stream is idle here (barrier above); this pipe takes the first timed step
     for i in range(args.steps):
         step_device(args.warmup + i)
-    e1.record()
+    ends = []
+    for P in pipes:
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(P["ts"])
+        ends.append(e)
     barrier()
-    ms = e0.elapsed_time(e1)
-    launches = ex.launch_count() + mt.launch_count() - l0
+    ms = max(e0.elapsed_time(e) for e in ends)
+    launches = launches_now() - l0
     nkp = float(np.mean([ex.fetch(f)[1].shape[0] for f in range(min(B, 4))]))
     track_evals = mt.track_evaluations()
     nmatch = float(nmt[1:].float().mean().item())
@@ -356,7 +374,9 @@ def run_gpu(args):
             "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
                        "matches_per_frame": nmatch, "hamming_evaluations_per_frame": track_evals / max(B - 1, 1),
                        "l2_policy": f"{nsets} distinct input batches rotated ({nsets * B * img_bytes / 1e6:.0f} MB > "
-                                    "126 MB L2); all intermediates rewritten every step"},
+                                    "126 MB L2); all intermediates rewritten every step",
+                       "schedule": (f"{npipes} handle pairs on {npipes} CUDA streams take alternating batches of the one frame stream "
+                                    "(tracking of batch i overlaps extraction of batch i+1)") if npipes > 1 else "serial, one stream"},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8 + stride * 4 + 4))},
             "gpu_launches": int(launches),
@@ -406,6 +426,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="frames in flight per GPU per step")
     ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
     ap.add_argument("--cpu-frames", type=int, default=400, help="frames timed for cpu_baseline")
+    ap.add_argument("--pipes", type=int, default=2, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
     args = ap.parse_args()
