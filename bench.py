@@ -253,8 +253,9 @@ def run_gpu(args):
     # tracking step and the kernel tails of batch i overlap the extraction of batch i+1 (each handle owns its buffers, so
     # nothing is overwritten while it is still being read).  pipes = 1 is the strictly serial schedule.
     npipes = max(1, args.pipes)
+    epipes = max(1, args.e2e_pipes)
     pipes = []
-    for _ in range(npipes):
+    for _ in range(max(npipes, epipes)):
         pex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
         pmt = ORBmatcher(0.9, True, device=local)
         pts = torch.cuda.Stream()          # a real (non-NULL) stream: CUDA events below are recorded on it
@@ -292,14 +293,14 @@ def run_gpu(args):
     if rank == 0:
         sampler.start()
     def launches_now():
-        return sum(P["ex"].launch_count() + P["mt"].launch_count() for P in pipes)
+        return sum(P["ex"].launch_count() + P["mt"].launch_count() for P in pipes[:npipes])
     l0 = launches_now()
     e0 = torch.cuda.Event(enable_timing=True)
     e0.record(pipes[args.warmup % npipes]["ts"])      # every stream is idle here (barrier above); this pipe takes the first timed step
     for i in range(args.steps):
         step_device(args.warmup + i)
     ends = []
-    for P in pipes:
+    for P in pipes[:npipes]:
         e = torch.cuda.Event(enable_timing=True)
         e.record(P["ts"])
         ends.append(e)
@@ -331,26 +332,48 @@ def run_gpu(args):
 
     # ---- e2e: page-locked host buffers through the C-ABI calls (H2D of frames, D2H of keypoints / descriptors / matches) ----
     cap = stride
-    kps_h = torch.empty((B, cap * KEYPOINT_DTYPE.itemsize), dtype=torch.uint8).pin_memory().numpy().view(KEYPOINT_DTYPE).reshape(B, cap)
-    desc_h = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory().numpy()
-    n_h, mono_h = np.zeros(B, np.int32), np.zeros(B, np.int32)
-    kpm_h = torch.empty((B, stride), dtype=torch.int32).pin_memory()
-    nm_h = torch.empty(B, dtype=torch.int32).pin_memory()
     host_batches = [host[s * B:(s + 1) * B] for s in range(nsets)]
+    for P in pipes:
+        P["kps_h"] = torch.empty((B, cap * KEYPOINT_DTYPE.itemsize), dtype=torch.uint8).pin_memory().numpy().view(KEYPOINT_DTYPE).reshape(B, cap)
+        P["desc_h"] = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory().numpy()
+        P["n_h"], P["mono_h"] = np.zeros(B, np.int32), np.zeros(B, np.int32)
+        P["kpm_h"] = torch.empty((B, stride), dtype=torch.int32).pin_memory()
+        P["nm_h"] = torch.empty(B, dtype=torch.int32).pin_memory()
 
     def step_e2e(i):
-        ex.extract_batch_into(host_batches[i % nsets], kps_h, desc_h, n_h, mono_h)
-        mt.track_batch_device(B, dk, dd, dc, stride, BOUNDS, sf, TH_TRACK, kpm.data_ptr(), nmt.data_ptr(), stream=stream)
-        kpm_h.copy_(kpm, non_blocking=True)
-        nm_h.copy_(nmt, non_blocking=True)
-        tstream.synchronize()
+        # the calls a user makes, with HOST buffers: frames in, keypoints + descriptors + matches out, then a stream sync
+        P = pipes[i % epipes]
+        P["ex"].extract_batch_into(host_batches[i % nsets], P["kps_h"], P["desc_h"], P["n_h"], P["mono_h"])
+        with torch.cuda.stream(P["ts"]):
+            P["mt"].track_batch_device(B, P["dk"], P["dd"], P["dc"], stride, BOUNDS, sf, TH_TRACK, P["kpm"].data_ptr(),
+                                       P["nmt"].data_ptr(), stream=P["st"])
+            P["kpm_h"].copy_(P["kpm"], non_blocking=True)
+            P["nm_h"].copy_(P["nmt"], non_blocking=True)
+        P["ts"].synchronize()
 
-    for i in range(min(args.warmup, 3)):
-        step_e2e(i)
+    def run_e2e(first, count):
+        # one host thread per handle pair, like one Tracking thread per extractor in the reference; thread p takes steps
+        # p, p + epipes, ... so that the copies of one batch overlap the kernels of the other
+        if epipes == 1:
+            for i in range(first, first + count):
+                step_e2e(i)
+            return
+        import threading
+
+        def worker(p):
+            torch.cuda.set_device(local)
+            for i in range(first + ((p - first) % epipes), first + count, epipes):
+                step_e2e(i)
+        th = [threading.Thread(target=worker, args=(p,)) for p in range(epipes)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+
+    run_e2e(0, max(min(args.warmup, 3), epipes))
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        step_e2e(i)
+    run_e2e(0, args.steps)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
@@ -376,7 +399,8 @@ def run_gpu(args):
                        "l2_policy": f"{nsets} distinct input batches rotated ({nsets * B * img_bytes / 1e6:.0f} MB > "
                                     "126 MB L2); all intermediates rewritten every step",
                        "schedule": (f"{npipes} handle pairs on {npipes} CUDA streams take alternating batches of the one frame stream "
-                                    "(tracking of batch i overlaps extraction of batch i+1)") if npipes > 1 else "serial, one stream"},
+                                    "(tracking of batch i overlaps extraction of batch i+1)") if npipes > 1 else "serial, one stream",
+                       "e2e_schedule": f"{epipes} host threads, one handle pair each, take alternating batches; every call is synchronous"},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8 + stride * 4 + 4))},
             "gpu_launches": int(launches),
@@ -427,6 +451,7 @@ def main():
     ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
     ap.add_argument("--cpu-frames", type=int, default=400, help="frames timed for cpu_baseline")
     ap.add_argument("--pipes", type=int, default=2, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
+    ap.add_argument("--e2e-pipes", type=int, default=3, help="host threads (one handle pair each) of the end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
     args = ap.parse_args()

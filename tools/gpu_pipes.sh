@@ -1,5 +1,5 @@
 #!/bin/bash
-for p in 1 2 3; do
+for p in ${PIPES:-1 2 3}; do
   echo "== pipes $p"
   timeout 300 python bench.py --no-cpu --no-knn --steps 20 --pipes $p 2>/dev/null | python -c "
 import json,sys
