@@ -187,10 +187,32 @@ __device__ void split_nodes(TreeSmem& S, int cur, int T, uint64_t* const (&buf)[
     }
 }
 __device__ void split_big_nodes(TreeSmem& S, int cur, int T, uint64_t* const (&buf)[2], int (*sCnt)[4]) {
-    for (int t = 0; t < T; ++t) {
-        const int node = S.proc[t];
+    // Big nodes exist only in the first two or three passes; the list of them is gathered first (order is irrelevant: the
+    // nodes are disjoint) so that the CTA does not walk all T entries in lock step just to skip them.
+    __shared__ int sBig[32];
+    __shared__ int sNBig;
+    if (threadIdx.x == 0) sNBig = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < T; t += kTreeThreads)
+        if ((int)S.cnt[cur][S.proc[t]] >= kCtaPartitionMin) { const int at = atomicAdd(&sNBig, 1); if (at < 32) sBig[at] = t; }
+    __syncthreads();
+    const int nBig = sNBig;
+    if (nBig == 0) return;
+    if (nBig > 32) {                 // more than the list holds (n >= 33 * 1024 keys in one level): the plain walk
+        for (int t = 0; t < T; ++t) {
+            const int node = S.proc[t];
+            const int cnt = (int)S.cnt[cur][node];
+            if (cnt < kCtaPartitionMin) continue;        // uniform across the CTA
+            const uint32_t bf = S.beg[cur][node];
+            const int beg = (int)(bf & 0x7fffffffu), flag = (int)(bf >> 31);
+            const uint4 c = cta_partition4(buf[flag], buf[flag ^ 1], beg, cnt, beg, split_of(S.rect[cur][node]), sCnt);
+            if (threadIdx.x == 0) S.cc[node] = c;
+        }
+        return;
+    }
+    for (int i = 0; i < nBig; ++i) {
+        const int node = S.proc[sBig[i]];
         const int cnt = (int)S.cnt[cur][node];
-        if (cnt < kCtaPartitionMin) continue;        // uniform across the CTA
         const uint32_t bf = S.beg[cur][node];
         const int beg = (int)(bf & 0x7fffffffu), flag = (int)(bf >> 31);
         const uint4 c = cta_partition4(buf[flag], buf[flag ^ 1], beg, cnt, beg, split_of(S.rect[cur][node]), sCnt);
