@@ -107,7 +107,8 @@ int orbx_download_candidates(orbx_handle h, int frame, int level, int* out, int 
 /* keypoints kept by the quadtree, list order; out = n x 3 ints (x, y relative to minBorder, response) */
 int orbx_download_level_keypoints(orbx_handle h, int frame, int level, int* out, int cap, int* n_out);
 /* device-side emulation of libstdc++ std::sort with compareNodes (src/ORBextractor.cc:538-553): perm = order of
- * the input indices after sorting (size, ul_x) pairs.  mode 0 = full sort, 1 = heap-sort fallback only */
+ * the input indices after sorting (size, ul_x) pairs.  mode 0 = full sort by one thread, 1 = heap-sort fallback only,
+ * 2 = the warp-parallel form the quadtree kernel runs (n <= 65535) */
 int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n, int* perm, int mode);
 /* standalone DistributeOctTree (src/ORBextractor.cc:555-779) on device: keys n x 3 ints (x, y, response) */
 int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,

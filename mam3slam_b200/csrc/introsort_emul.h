@@ -148,4 +148,47 @@ ISE_HD void sort(Elem* e, int n) {
     }
 }
 
+// ---- the same sort as independent work items (what the GPU runs on the lanes of one warp) ------------------------------
+// The sub-ranges produced by the introsort loop are disjoint, so they can be partitioned by different workers in any order.
+// The final insertion pass never moves an element across a range boundary either: a partition leaves  left <= pivot <=
+// right, and insertion stops at the first element that is not greater (strict '<'), so it is the same as a stable
+// insertion sort of every leaf range (<= 16 elements, or heap-sorted) on its own.  The decomposition below is checked
+// against the real std::sort in tests/test_abi_and_host.py (sort_rounds) and on the device (orbx_debug_sort_nodes mode 2).
+
+// one introsort step on [first, last) (more than 16 elements, depth > 0): returns the cut
+ISE_HD int split_step(Elem* e, int first, int last) {
+    const int mid = first + (last - first) / 2;
+    median_to_first(e, first, first + 1, mid, last - 1);
+    return unguarded_partition(e, first + 1, last, first);
+}
+
+#ifndef __CUDACC__
+// host form of the round-based schedule (ranges of one round in arbitrary order)
+inline void sort_rounds(Elem* e, int n, bool reverse_order) {
+    if (n <= 1) return;
+    int lg = 0;
+    for (int t = n; t > 1; t >>= 1) ++lg;
+    struct R { int first, last, depth; };
+    R* cur = new R[n + 1]; R* nxt = new R[n + 1]; R* leaf = new R[n + 1];
+    int nc = 0, nl = 0;
+    if (n > 16) cur[nc++] = R{0, n, 2 * lg}; else leaf[nl++] = R{0, n, 0};
+    while (nc > 0) {
+        int nn = 0;
+        for (int k = 0; k < nc; ++k) {
+            const R r = cur[reverse_order ? nc - 1 - k : k];
+            if (r.depth == 0) { heap_sort(e, r.first, r.last); continue; }
+            const int cut = split_step(e, r.first, r.last);
+            const R ch[2] = {R{r.first, cut, r.depth - 1}, R{cut, r.last, r.depth - 1}};
+            for (const R& c : ch) {
+                if (c.last - c.first > 16) nxt[nn++] = c;
+                else if (c.last - c.first > 1) leaf[nl++] = c;
+            }
+        }
+        R* t = cur; cur = nxt; nxt = t; nc = nn;
+    }
+    for (int k = 0; k < nl; ++k) { const R r = leaf[reverse_order ? nl - 1 - k : k]; insertion_sort(e, r.first, r.last); }
+    delete[] cur; delete[] nxt; delete[] leaf;
+}
+#endif
+
 }  // namespace ise

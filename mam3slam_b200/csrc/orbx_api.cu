@@ -790,7 +790,7 @@ int orbx_download_level_keypoints(orbx_handle h, int frame, int level, int* out,
 }
 
 int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n, int* perm, int mode) {
-    if (!h || n < 0) return ORBX_ERR_INVALID;
+    if (!h || n < 0 || (mode == 2 && n > 65535)) return ORBX_ERR_INVALID;
     E_FROM(h);
     CK(cudaSetDevice(E->device));
     std::vector<ise::Elem> e(std::max(n, 1));
@@ -798,7 +798,10 @@ int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n
     ise::Elem* d = nullptr;
     CK(cudaMalloc((void**)&d, e.size() * sizeof(ise::Elem)));
     cudaError_t er = cudaMemcpy(d, e.data(), e.size() * sizeof(ise::Elem), cudaMemcpyHostToDevice);
-    if (er == cudaSuccess) { k_debug_sort<<<1, 32, 0, E->stream>>>(d, n, mode); ++E->launches; er = cudaStreamSynchronize(E->stream); }
+    uint32_t* scratch = nullptr;
+    if (er == cudaSuccess) er = cudaMalloc((void**)&scratch, ((size_t)3 * n + 16) * sizeof(uint32_t));
+    if (er == cudaSuccess) { k_debug_sort<<<1, 32, 0, E->stream>>>(d, n, mode, scratch); ++E->launches; er = cudaStreamSynchronize(E->stream); }
+    cudaFree(scratch);
     if (er == cudaSuccess) er = cudaMemcpy(e.data(), d, e.size() * sizeof(ise::Elem), cudaMemcpyDeviceToHost);
     cudaFree(d);
     CK(er);

@@ -29,6 +29,7 @@ __host__ __device__ inline size_t tree_smem_layout(int P, int scanCap, TreeSmem*
         S->pend = (ise::Elem*)(base + pe); S->cc = (uint4*)(base + cc);
         S->scanA = (int*)(base + sa); S->scanB = (int*)(base + sb);
         S->proc = (uint16_t*)(base + pr); S->dv = base + dv;
+        S->scanCap = scanCap;
     }
     return o;
 }
@@ -80,8 +81,11 @@ __global__ void __launch_bounds__(kTreeThreads) k_debug_distribute(uint64_t* buf
     distribute_tree(buf, n, N, nIni, hX, treeH, S, out, outCount);
 }
 
-__global__ void k_debug_sort(ise::Elem* e, int n, int mode) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
+// mode 0: single-thread std::sort emulation, 1: heap sort alone, 2: the warp version the quadtree uses (scratch: 3n+8 ints)
+__global__ void k_debug_sort(ise::Elem* e, int n, int mode, uint32_t* scratch) {
+    if (mode == 2) {
+        warp_sort_nodes(e, n, scratch, scratch + n + 4, scratch + 2 * n + 8);
+    } else if (threadIdx.x == 0 && blockIdx.x == 0) {
         if (mode == 1) ise::heap_sort(e, 0, n);
         else ise::sort(e, n);
     }

@@ -33,6 +33,7 @@ struct TreeSmem {                   // carved out of dynamic shared memory, size
     int* scanB;
     uint16_t* proc;                 // processing order (list positions)
     uint8_t* dv;                    // node was split in this pass
+    int scanCap;                    // ints in scanA / scanB
 };
 
 __device__ __forceinline__ int warp_incl_scan(int v, int lane) {
@@ -284,6 +285,65 @@ __device__ int apply_splits(TreeSmem& S, int cur, int listSize, int T, int* sWar
     return neTot + listSize - T;
 }
 
+// std::sort emulation by ONE WARP (see introsort_emul.h: the ranges of the introsort loop are independent work items and the
+// final insertion pass is a stable insertion sort of each leaf range).  Rounds: lane i partitions the i-th active range
+// (> 16 elements) once; the children go to the next round's list or, when small, to the leaf list; slots are handed out
+// with ballots, so no atomics and no ordering assumptions.  listA / listB: 2 ints per active range (first | last << 16,
+// depth), at most n / 17 ranges each; leaves: 1 int per leaf, at most n.  Critical path ~2n element steps instead of
+// ~n log2(n / 16) + the insertion pass of a single thread.
+__device__ void warp_sort_nodes(ise::Elem* e, int n, uint32_t* listA, uint32_t* listB, uint32_t* leaves) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lower = (1u << lane) - 1;
+    if (n <= 16) { if (lane == 0) ise::insertion_sort(e, 0, n); __syncwarp(); return; }
+    int lg = 0;
+    for (int t = n; t > 1; t >>= 1) ++lg;
+    if (lane == 0) { listA[0] = (uint32_t)n << 16; listA[1] = 2 * lg; }
+    __syncwarp();
+    uint32_t* cur = listA; uint32_t* nxt = listB;
+    int nA = 1, nLeaf = 0;
+    while (nA > 0) {
+        int nN = 0;
+        for (int base = 0; base < nA; base += 32) {
+            const int i = base + lane;
+            uint32_t c0 = 0, c1 = 0, d = 0;
+            bool has = false;
+            if (i < nA) {
+                const uint32_t r = cur[2 * i];
+                const int first = (int)(r & 0xffffu), last = (int)(r >> 16);
+                d = cur[2 * i + 1];
+                if (d == 0) {
+                    ise::heap_sort(e, first, last);                 // depth limit reached: std::__partial_sort of the range
+                } else {
+                    --d;
+                    const int cut = ise::split_step(e, first, last);
+                    c0 = (uint32_t)first | ((uint32_t)cut << 16);
+                    c1 = (uint32_t)cut | ((uint32_t)last << 16);
+                    has = true;
+                }
+            }
+            const int s0 = (int)(c0 >> 16) - (int)(c0 & 0xffffu), s1 = (int)(c1 >> 16) - (int)(c1 & 0xffffu);
+            const bool a0 = has && s0 > 16, a1 = has && s1 > 16;
+            const bool l0 = has && !a0 && s0 > 1, l1 = has && !a1 && s1 > 1;
+            const unsigned mA0 = __ballot_sync(0xffffffffu, a0), mA1 = __ballot_sync(0xffffffffu, a1);
+            const unsigned mL0 = __ballot_sync(0xffffffffu, l0), mL1 = __ballot_sync(0xffffffffu, l1);
+            if (a0) { const int s = nN + __popc(mA0 & lower); nxt[2 * s] = c0; nxt[2 * s + 1] = d; }
+            if (a1) { const int s = nN + __popc(mA0) + __popc(mA1 & lower); nxt[2 * s] = c1; nxt[2 * s + 1] = d; }
+            nN += __popc(mA0) + __popc(mA1);
+            if (l0) leaves[nLeaf + __popc(mL0 & lower)] = c0;
+            if (l1) leaves[nLeaf + __popc(mL0) + __popc(mL1 & lower)] = c1;
+            nLeaf += __popc(mL0) + __popc(mL1);
+        }
+        __syncwarp();
+        uint32_t* t = cur; cur = nxt; nxt = t;
+        nA = nN;
+    }
+    for (int i = lane; i < nLeaf; i += 32) {
+        const uint32_t r = leaves[i];
+        ise::insertion_sort(e, (int)(r & 0xffffu), (int)(r >> 16));
+    }
+    __syncwarp();
+}
+
 // The whole DistributeOctTree for one level.  Keys are in buf[0][0..n) in the reference's vToDistributeKeys order.
 // Writes the kept keys (one per final node, list order) to out[0..*outCount).
 __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIni, float hX, int treeH,
@@ -345,8 +405,9 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
                 const int prev2 = listSize;
                 for (int e = tid; e < m; e += kTreeThreads) S.proc[e] = (uint16_t)S.pend[e].id;
                 __syncthreads();
-                // std::sort emulation by one thread while the other warps pre-split every pending node
-                if (tid == 0) ise::sort(S.pend, m);
+                // std::sort emulation by warp 0 while the other warps pre-split every pending node
+                if (wid == 0) warp_sort_nodes(S.pend, m, reinterpret_cast<uint32_t*>(S.scanB), reinterpret_cast<uint32_t*>(S.scanB) + (S.scanCap >> 1),
+                                              reinterpret_cast<uint32_t*>(S.scanA));
                 split_nodes(S, cur, m, buf, sCnt, 1);
                 __syncthreads();
                 split_big_nodes(S, cur, m, buf, sCnt);

@@ -200,6 +200,7 @@ class ORBextractor:
         return out[:n.value].copy()
 
     def debug_sort_nodes(self, size, ulx, heap_only=False):
+        """heap_only doubles as the mode: 0 / False = one-thread std::sort emulation, 1 / True = heap sort, 2 = warp-parallel form."""
         size = np.ascontiguousarray(size, np.int32)
         ulx = np.ascontiguousarray(ulx, np.int32)
         perm = np.empty(len(size), np.int32)

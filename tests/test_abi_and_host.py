@@ -76,7 +76,11 @@ def test_sort_emulation_matches_std_sort(oracle_mod, emul, n):
         rng = np.random.default_rng(1000 * n + seed)
         size = rng.integers(2, 2 + (3 if seed < 2 else 40), n)
         ulx = rng.integers(0, 6 if seed % 2 == 0 else 700, n)
-        assert np.array_equal(_emul_sort(emul, size, ulx), oracle_mod.sort_nodes(size, ulx)), (n, seed)
+        ref = oracle_mod.sort_nodes(size, ulx)
+        assert np.array_equal(_emul_sort(emul, size, ulx), ref), (n, seed)
+        # the round-based schedule (independent ranges, per-leaf insertion) the GPU warp runs, in two work orders
+        assert np.array_equal(_emul_sort(emul, size, ulx, 2), ref), (n, seed)
+        assert np.array_equal(_emul_sort(emul, size, ulx, 3), ref), (n, seed)
 
 
 def test_sort_emulation_adversarial(oracle_mod, emul):
@@ -85,7 +89,10 @@ def test_sort_emulation_adversarial(oracle_mod, emul):
     for size in (np.arange(n), np.arange(n)[::-1], np.full(n, 5), np.minimum(np.arange(n), n - 1 - np.arange(n)),
                  np.arange(n) % 2, (np.arange(n) * 7919) % 13):
         ulx = np.zeros(n, np.int32)
-        assert np.array_equal(_emul_sort(emul, size, ulx), oracle_mod.sort_nodes(size, ulx))
+        ref = oracle_mod.sort_nodes(size, ulx)
+        assert np.array_equal(_emul_sort(emul, size, ulx), ref)
+        assert np.array_equal(_emul_sort(emul, size, ulx, 2), ref)
+        assert np.array_equal(_emul_sort(emul, size, ulx, 3), ref)
 
 
 def _build_adapter_demo(tmpdir):

@@ -106,3 +106,22 @@ def test_batch_equals_single(oracle_mod):
         m1, k1, d1 = ex1(img)
         assert mono == m1 and np.array_equal(kps, k1) and np.array_equal(desc, d1)
     ex1.close(); exb.close()
+
+
+@pytest.mark.gpu
+def test_device_sort_emulation_matches_std_sort(oracle_mod):
+    """The quadtree's node sort on the device (one-thread form and the warp-parallel form the kernel runs) moves elements
+    exactly like libstdc++'s std::sort on heavily tied (size, UL.x) keys, including inputs that reach the heap-sort fallback."""
+    ex = ORBextractor(1000, 1.2, 8, 20, 7)
+    cases = []
+    for n in (0, 1, 2, 15, 16, 17, 33, 100, 257, 1000, 4000):
+        for seed in range(3):
+            rng = np.random.default_rng(77 * n + seed)
+            cases.append((rng.integers(2, 2 + (3 if seed < 2 else 40), n), rng.integers(0, 6 if seed % 2 == 0 else 700, n)))
+    n = 3000
+    for size in (np.arange(n), np.arange(n)[::-1], np.full(n, 5), np.minimum(np.arange(n), n - 1 - np.arange(n)), np.arange(n) % 2):
+        cases.append((size, np.zeros(n, np.int32)))
+    for size, ulx in cases:
+        ref = oracle_mod.sort_nodes(size, ulx)
+        assert np.array_equal(ex.debug_sort_nodes(size, ulx, 0), ref)
+        assert np.array_equal(ex.debug_sort_nodes(size, ulx, 2), ref)
