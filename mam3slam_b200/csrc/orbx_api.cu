@@ -324,7 +324,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     ++E->launches;
     mark();
     if (side) CK(cudaStreamWaitEvent(st, E->evJoin[slot], 0));
-    k_orient_brief<<<dim3((g.outCap + kDescWarps - 1) / kDescWarps, n), kDescWarps * 32, 0, st>>>(
+    k_orient_brief<<<dim3((g.outCap + kDescWarps * kDescGroup - 1) / (kDescWarps * kDescGroup), n), kDescWarps * 32, 0, st>>>(
         E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
     ++E->launches;
     mark();

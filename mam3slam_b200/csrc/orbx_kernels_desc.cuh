@@ -186,63 +186,95 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-// E5 + E7: one warp per keypoint.  Orientation: lanes = columns u=-15..15 of the radius-15 disc on the UNBLURRED
-// level, int32 moments, shuffle reduction.  Descriptor: lane i produces byte i (8 of the 256 tests) on the BLURRED
-// level; pattern points rotated in float with separately rounded products (no FMA), cvRound = round-half-even.
-constexpr int kDescWarps = 8;
+// E5 + E7: one warp per GROUP of kDescGroup keypoints.
+//   1. orientation of each keypoint in turn: lanes = columns u = -15..15 of the radius-15 disc on the UNBLURRED level, int32
+//      moments, shuffle reduction; lane j keeps the moments of keypoint j.
+//   2. the first kDescGroup lanes finish their own keypoint: fastAtan2, then cos / sin in double narrowed to float - one
+//      instruction stream for the whole group.
+//   3. descriptor of each keypoint in turn: lane i produces byte i (8 of the 256 tests) on the BLURRED level; the lane's 8
+//      tests live in registers as floats for the whole group (no per-keypoint table reads or int->float conversions);
+//      pattern points rotated in float with separately rounded products (no FMA), cvRound = round-half-even.
+#ifndef ORBX_DESC_GROUP
+#define ORBX_DESC_GROUP 4
+#endif
+constexpr int kDescWarps = 8, kDescGroup = ORBX_DESC_GROUP;
 __global__ void __launch_bounds__(kDescWarps * 32) k_orient_brief(const DevGeom* __restrict__ g, Level0 l0,
                                                                   const WorkItem* __restrict__ work,
                                                                   const int* __restrict__ outCnt, orbx_keypoint* outKp,
                                                                   uint8_t* outDesc, int frameBase) {
     const int frame = frameBase + blockIdx.y;
-    const int o = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    const int o0 = (blockIdx.x * kDescWarps + (threadIdx.x >> 5)) * kDescGroup;
     const int lane = threadIdx.x & 31;
-    if (o >= outCnt[2 * frame]) return;
-    const WorkItem w = work[(size_t)frame * g->outCap + o];
-    int pitch;
-    const uint8_t* img = level_ptr(g, l0, w.level, frame, &pitch);
-    const uint8_t* ctr = img + (size_t)w.y * pitch + w.x;
-    int m10 = 0, m01 = 0;
+    const int total = outCnt[2 * frame];
+    if (o0 >= total) return;
+    const int ng = min(kDescGroup, total - o0);
+    // lane j < ng holds keypoint j of the group
+    WorkItem mine; mine.level = 0; mine.pad = 0; mine.x = 0; mine.y = 0; mine.dst = 0;
+    if (lane < ng) mine = work[(size_t)frame * g->outCap + o0 + lane];
+    // this lane's 8 tests
+    float px0[8], py0[8], px1[8], py1[8];
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+        const char4 t = c_pattern[lane * 8 + bit];
+        px0[bit] = (float)t.x; py0[bit] = (float)t.y; px1[bit] = (float)t.z; py1[bit] = (float)t.w;
+    }
     const int u = lane - kHalfPatch;
-    if (lane < 31) {
-        const int au = abs(u);
-#pragma unroll 1
+    const int vm = lane < 31 ? c_umax[abs(u)] : -1;          // lane 31 holds no column
+    int myM10 = 0, myM01 = 0;
+    for (int j = 0; j < ng; ++j) {
+        const int lev = __shfl_sync(0xffffffffu, (int)mine.level, j);
+        const int kx = __shfl_sync(0xffffffffu, mine.x, j), ky = __shfl_sync(0xffffffffu, mine.y, j);
+        int pitch;
+        const uint8_t* img = level_ptr(g, l0, lev, frame, &pitch);
+        const uint8_t* ctr = img + (size_t)ky * pitch + kx;
+        int m10 = 0, m01 = 0;
+        // the disc mask is symmetric in (u, v) (:453-468 makes it so): column u spans the rows |v| <= umax[|u|].  Fully
+        // unrolled so that the 31 byte loads of a lane are in flight together.
+#pragma unroll
         for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-            if (au <= c_umax[abs(v)]) {
+            if ((v < 0 ? -v : v) <= vm) {
                 const int val = ctr[v * pitch + u];
                 m10 += u * val;
                 m01 += v * val;
             }
         }
-    }
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, s);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+        for (int s = 16; s > 0; s >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, s);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+        }
+        if (lane == j) { myM10 = m10; myM01 = m01; }
     }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-    orbx_keypoint* kp = outKp + (size_t)frame * g->outCap + w.dst;
-    if (lane == 0) kp->angle = angle;
-
-    constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
-    const float rad = __fmul_rn(angle, factorPI);
-    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
-    const LevelGeom& G = g->lv[w.level];
-    const uint8_t* bc = g->blur[w.level] + (size_t)frame * G.planeBytes + (size_t)w.y * G.pitch + w.x;
-    const int bp = G.pitch;
-    int byte = 0;
+    float ca = 0.f, sb = 0.f;
+    if (lane < ng) {
+        const float angle = fast_atan2_deg((float)myM01, (float)myM10);
+        outKp[(size_t)frame * g->outCap + mine.dst].angle = angle;
+        constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const double rad = (double)__fmul_rn(angle, factorPI);
+        double sd, cd;
+        sincos(rad, &sd, &cd);
+        ca = (float)cd; sb = (float)sd;
+    }
+    for (int j = 0; j < ng; ++j) {
+        const float a = __shfl_sync(0xffffffffu, ca, j), b = __shfl_sync(0xffffffffu, sb, j);
+        const int lev = __shfl_sync(0xffffffffu, (int)mine.level, j);
+        const int kx = __shfl_sync(0xffffffffu, mine.x, j), ky = __shfl_sync(0xffffffffu, mine.y, j);
+        const int dst = __shfl_sync(0xffffffffu, mine.dst, j);
+        const LevelGeom& G = g->lv[lev];
+        const int bp = G.pitch;
+        const uint8_t* bc = g->blur[lev] + (size_t)frame * G.planeBytes + (size_t)ky * bp + kx;
+        int byte = 0;
 #pragma unroll
-    for (int bit = 0; bit < 8; ++bit) {
-        const char4 t = c_pattern[lane * 8 + bit];
-        const float x0 = (float)t.x, y0 = (float)t.y, x1 = (float)t.z, y1 = (float)t.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int v0 = bc[r0 * bp + c0], v1 = bc[r1 * bp + c1];
-        byte |= (v0 < v1 ? 1 : 0) << bit;
+        for (int bit = 0; bit < 8; ++bit) {
+            const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(px0[bit], b), __fmul_rn(py0[bit], a)));
+            const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px0[bit], a), __fmul_rn(py0[bit], b)));
+            const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px1[bit], b), __fmul_rn(py1[bit], a)));
+            const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px1[bit], a), __fmul_rn(py1[bit], b)));
+            const int v0 = bc[r0 * bp + c0], v1 = bc[r1 * bp + c1];
+            byte |= (v0 < v1 ? 1 : 0) << bit;
+        }
+        outDesc[((size_t)frame * g->outCap + dst) * 32 + lane] = (uint8_t)byte;
     }
-    outDesc[((size_t)frame * g->outCap + w.dst) * 32 + lane] = (uint8_t)byte;
 }
 
 }  // namespace orbx
