@@ -406,7 +406,10 @@ def run_gpu(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                         "frac": ach / pk["hbm_gbs"], "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(dom) if B == 64 else None,
+                         "traffic_source": "profiles/r1c_ncu_full_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, 64 frames per launch)",
+                         "peak_kind": pk_kind,
+                         "alu": fast_alu_roofline(acc.get("fast"), B),
                          "stage_ms_per_step": acc,
                          "note": "integer/issue-bound path: see DESIGN.md 4; pipeline_* = 1.93 MB algorithmic bytes per frame",
                          "pipeline_alg_gbs": ALG_BYTES_PER_FRAME * fps / 1e9 / world,
@@ -423,6 +426,25 @@ def run_gpu(args):
     ex.close(); mt.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+# DRAM bytes per launch (64 EuRoC frames) of each stage's kernel(s), from the committed ncu --set full capture
+NCU_DRAM_BYTES_PER_LAUNCH = {"pyramid": 75.4e6, "fast": 72.2e6, "octree": 14.5e6, "blur": 115.1e6, "finalize": 0.56e6,
+                             "orient_brief": 147.3e6, "track": 8.7e6}
+
+
+def fast_alu_roofline(fast_ms, B):
+    """FAST is bound by the min/max network, not by HBM: 79 VIMNMX3.U16x2 per pixel PAIR (tmin/tmax 32, min9/max9 32, the two
+    16-way reductions 15), issued at 64 /clk/SM.  Peak = the rate tools/microbench.cu measured on this B200 pool
+    (profiles/int_peaks_b200.txt: vimin3_u16x2 18417 G/s)."""
+    if not fast_ms:
+        return None
+    lv = [(752, 480), (627, 400), (522, 333), (435, 278), (363, 231), (302, 193), (252, 161), (210, 134)]
+    tested = sum((w - 32) * (h - 32) for w, h in lv)          # FAST runs 16 px inside every level (EDGE_THRESHOLD - 3)
+    ops = tested / 2 * 79 * B
+    ach = ops / (fast_ms * 1e-3)
+    return {"op": "VIMNMX3.U16x2", "per_pixel_pair": 79, "achieved_ops_per_s": ach, "peak_ops_per_s": 18417.2e9,
+            "frac": ach / 18417.2e9}
 
 
 def stage_algorithmic_bytes(nkp, evals_per_frame=20000.0):

@@ -75,6 +75,26 @@ def test_odd_shapes_and_params(oracle_mod):
     _compare(synth.frame(960, 960, 7), 1500, oracle_mod)            # the reference's test YAML shape
     _compare(synth.frame(500, 333, 8), 300, oracle_mod, levels=4, scale=1.5, ini=30, mn=10)
     _compare(synth.frame(512, 512, 9), 800, oracle_mod, levels=3, scale=2.0)   # exact 2x: INTER_AREA path
+    # rows that are not word-aligned (odd width = odd stride): the byte-wise variants of pyramid / FAST staging / blur
+    _compare(synth.frame(501, 335, 13), 400, oracle_mod, levels=5)
+    _compare(synth.frame(643, 481, 14), 600, oracle_mod)
+    # scale factor above 2: four output pixels read more than 8 source bytes -> the generic resize kernel
+    _compare(synth.frame(800, 600, 15), 500, oracle_mod, levels=3, scale=2.5)
+
+
+def test_strided_views(oracle_mod):
+    """operator() on a sub-matrix view (row stride > width, aligned and unaligned), like a cv::Mat ROI: same result as on
+    a contiguous copy, which in turn is compared with the oracle."""
+    big = synth.frame(900, 520, 16)
+    for (x0, w) in ((0, 752), (3, 752), (5, 641)):
+        view = big[10:490, x0:x0 + w]
+        assert view.strides[0] == 900 and not view.flags["C_CONTIGUOUS"]
+        ex = ORBextractor(1000, 1.2, 8, 20, 7)
+        m1, k1, d1 = ex(view)
+        m2, k2, d2 = ex(np.ascontiguousarray(view))
+        assert m1 == m2 and np.array_equal(k1, k2) and np.array_equal(d1, d2)
+        ex.close()
+        _compare(np.ascontiguousarray(view), 1000, oracle_mod)
 
 
 def test_flat_and_noise_images(oracle_mod):
