@@ -300,3 +300,68 @@ def test_track_batch_device_equals_pairwise_oracle(M):
         assert evals > 10000
     M.mbCheckOrientation = True
     ex.close()
+
+
+def test_contention_many_queries_few_keypoints(M):
+    """Adversarial for the speculative commit: hundreds of queries whose windows cover the same small cluster of keypoints
+    with near-identical descriptors, so that (a) most speculative winners are taken by an earlier query of the same batch,
+    (b) all four candidates on file are often blocked and the window has to be walked again, (c) steals chain (M5)."""
+    rng = np.random.default_rng(5)
+    bounds = (0.0, 0.0, 752.0, 480.0)
+    n2 = 600
+    k2 = np.zeros(n2, sc.KP)
+    k2["x"] = 300 + rng.random(n2).astype(np.float32) * 60
+    k2["y"] = 200 + rng.random(n2).astype(np.float32) * 60
+    k2["octave"] = rng.integers(0, 3, n2)
+    k2["angle"] = rng.random(n2).astype(np.float32) * 360
+    k2["size"] = 31; k2["response"] = 50; k2["class_id"] = -1
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    d2 = np.repeat(base[None], n2, 0)
+    flips = rng.integers(0, 256, (n2, 6))
+    for j in range(6):
+        d2[np.arange(n2), flips[:, j] >> 3] ^= (1 << (flips[:, j] & 7)).astype(np.uint8)
+    nq = 900
+    qd = np.repeat(base[None], nq, 0)
+    f2 = rng.integers(0, 256, (nq, 3))
+    for j in range(3):
+        qd[np.arange(nq), f2[:, j] >> 3] ^= (1 << (f2[:, j] & 7)).astype(np.uint8)
+    u = (300 + rng.random(nq) * 60).astype(np.float32)
+    v = (200 + rng.random(nq) * 60).astype(np.float32)
+    octave = rng.integers(0, 3, nq).astype(np.int32)
+    angle = (rng.random(nq) * 360).astype(np.float32)
+    valid = np.ones(nq, np.uint8)
+    scale = (1.2 ** np.arange(8)).astype(np.float32)
+    F = M.frame(k2, d2, bounds)
+    for th in (15.0, 40.0):
+        for ori in (False, True):
+            M.mbCheckOrientation = ori
+            occ = (rng.random(n2) < 0.05).astype(np.uint8)
+            nm, km = M.SearchByProjection_Frame(F, occ, scale, valid, u, v, octave, angle, qd, th, 100)
+            onm, okm = om.search_frame(k2, d2, bounds, occ, scale, valid, u, v, octave, angle, qd, th, 100, ori)
+            assert nm == onm and np.array_equal(km, okm), (th, ori)
+            assert onm > 100
+    M.mbCheckOrientation = True
+    # best / second-best rule under the same contention (M1)
+    vc = np.ones(nq, np.float32)
+    for ratio in (0.7, 0.95):
+        M.mfNNratio = ratio
+        occ = np.zeros(n2, np.uint8)
+        nm, km, occ_after = M.SearchByProjection_LocalMap(F, occ, scale, valid, u, v, octave, vc, qd, 8.0)
+        onm, okm, oocc = om.search_local_map(k2, d2, bounds, occ, scale, valid, u, v, octave, vc, qd, 8.0, ratio)
+        assert nm == onm and np.array_equal(km, okm) and np.array_equal(occ_after, oocc), ratio
+    M.mfNNratio = 0.9
+    F.close()
+    # M5 with chains of steals: frame 1 = the queries as keypoints at level 0
+    k1 = np.zeros(nq, sc.KP)
+    k1["x"], k1["y"], k1["angle"] = u, v, angle
+    k1["size"] = 31; k1["response"] = 50; k1["class_id"] = -1
+    k2b = k2.copy(); k2b["octave"] = 0
+    F1, F2 = M.frame(k1, qd, bounds), M.frame(k2b, d2, bounds)
+    prev = np.stack([k1["x"], k1["y"]], 1)
+    for ori in (True, False):
+        M.mbCheckOrientation = ori
+        nm, m12, pm = M.SearchForInitialization(F1, F2, prev, 30)
+        onm, om12, opm = om.search_initialization(k1, qd, k2b, d2, bounds, prev, 30, M.mfNNratio, ori)
+        assert nm == onm and np.array_equal(m12, om12) and np.array_equal(pm, opm), ori
+    M.mbCheckOrientation = True
+    F1.close(); F2.close()
