@@ -227,6 +227,20 @@ __global__ void __launch_bounds__(kDescWarps * 32) k_orient_brief(const DevGeom*
         int pitch;
         const uint8_t* img = level_ptr(g, l0, lev, frame, &pitch);
         const uint8_t* ctr = img + (size_t)ky * pitch + kx;
+        {
+            // the descriptor phase will sample the blurred level in a 37x37 window whose position is known now but whose
+            // sample offsets depend on the angle: pull the window towards L1 / L2 while the orientation is being computed
+            const LevelGeom& G = g->lv[lev];
+            const uint8_t* bw = g->blur[lev] + (size_t)frame * G.planeBytes + (size_t)(ky - 18) * G.pitch + (kx - 18);
+            const uint8_t* r0p = bw + (size_t)lane * G.pitch;
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(r0p));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(r0p + 36));
+            if (lane < 5) {
+                const uint8_t* r1p = bw + (size_t)(32 + lane) * G.pitch;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(r1p));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(r1p + 36));
+            }
+        }
         int m10 = 0, m01 = 0;
         // the disc mask is symmetric in (u, v) (:453-468 makes it so): column u spans the rows |v| <= umax[|u|].  Fully
         // unrolled so that the 31 byte loads of a lane are in flight together.
