@@ -717,7 +717,10 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
     CKM(cudaSetDevice(M->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
-    const int qblocks = (nq + kKnnThreads - 1) / kKnnThreads;
+    // two queries per thread when the list is short (registers) and there are enough queries to fill the blocks
+    const char* qe = getenv("ORBM_KNN_QPT");
+    const int qpt = (k <= 4 && nq >= 2 * kKnnThreads && qe && atoi(qe) == 2) ? 2 : 1;      // measured slower on B200; kept for experiments
+    const int qblocks = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
     // chunks: about 4 resident CTAs per SM over all query blocks, each a multiple of the tile, at most 2^23 rows
     long long target = std::max<long long>(1, ((long long)M->smCount * 4 + qblocks - 1) / qblocks);
     long long rowsPerChunk = (db->n + target - 1) / std::max<long long>(target, 1);
@@ -731,8 +734,12 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
         CKM(cudaMalloc((void**)&M->knnPart, need));
         M->knnPartBytes = need;
     }
-    k_knn<<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n, db->rowOffset,
-                                                          (int)rowsPerChunk, k, M->knnPart);
+    if (qpt == 2)
+        k_knn<2, 4><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n, db->rowOffset,
+                                                                    (int)rowsPerChunk, k, M->knnPart);
+    else
+        k_knn<1, kKnnMaxK><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
+                                                                          db->rowOffset, (int)rowsPerChunk, k, M->knnPart);
     k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx);
     M->launches += 2;
     M->lastEvals = (long long)nq * db->n;

@@ -958,7 +958,7 @@ __global__ void __launch_bounds__(256) k_track_finish(const TrackBatch T) {
 // brute-force k-NN.  grid (query blocks, db chunks); block kKnnThreads; thread = query.
 constexpr int kKnnThreads = 256, kKnnTileRows = 128, kKnnMaxK = 16;
 
-// 256-bit Hamming distance with a carry-save adder tree: 8 xor words -> ones/twos/fours/eights -> 4 popc
+// 256-bit Hamming distance with a carry-save adder tree: 8 xor words -> 4 words of weight 1, 1, 2, 4 -> 4 popc
 __device__ __forceinline__ void csa(uint32_t& h, uint32_t& l, uint32_t a, uint32_t b, uint32_t c) {
     l = a ^ b ^ c;                      // LOP3 0x96
     h = (a & b) | (c & (a | b));        // LOP3 0xe8 (majority)
@@ -966,40 +966,44 @@ __device__ __forceinline__ void csa(uint32_t& h, uint32_t& l, uint32_t a, uint32
 __device__ __forceinline__ int hamming_csa(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
     const uint32_t x0 = q[0] ^ a.x, x1 = q[1] ^ a.y, x2 = q[2] ^ a.z, x3 = q[3] ^ a.w;
     const uint32_t x4 = q[4] ^ b.x, x5 = q[5] ^ b.y, x6 = q[6] ^ b.z, x7 = q[7] ^ b.w;
-    uint32_t t0, o0, t1, o1, t2, o2, f0, tw, f1, tw2, ei, fo;
+    uint32_t t0, o0, t1, o1, t2, o2, f0, tw;
     csa(t0, o0, x0, x1, x2);
     csa(t1, o1, x3, x4, x5);
-    csa(t2, o2, o0, o1, x6);            // ones so far: o2 (+ x7)
-    const uint32_t ones = o2 ^ x7, c7 = o2 & x7;     // half adder
-    csa(f0, tw, t0, t1, t2);
-    tw2 = tw ^ c7; f1 = tw & c7;        // half adder on the twos
-    ei = f0 & f1; fo = f0 ^ f1;         // fours: f0 + f1 -> fo (4s) + ei (8s)
-    return __popc(ones) + 2 * __popc(tw2) + 4 * __popc(fo) + 8 * __popc(ei);
+    csa(t2, o2, o0, o1, x6);            // weight 1 left: o2 and x7
+    csa(f0, tw, t0, t1, t2);            // weight 2: tw, weight 4: f0
+    // four words remain (weights 1, 1, 2, 4): stopping here costs the same 4 POPC as a full ones/twos/fours/eights
+    // reduction but 6 LOP3 less (LOP3 issues at 64 /clk/SM on sm_100a, POPC at 16: 16 LOP3 + 4 POPC balance the two pipes)
+    return __popc(o2) + __popc(x7) + 2 * __popc(tw) + 4 * __popc(f0);
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // dist/idx partial lists: part[(chunk * nq + q) * k + t] = key (dist << 32 | global row)
+// kQ queries per thread (q, q + kKnnThreads, ...): one pair of 16-byte row loads serves kQ evaluations, and the kQ independent
+// carry-save trees give the scheduler instruction-level parallelism; kK = compile-time bound of k (list kept in registers).
+template <int kQ, int kK>
 __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict__ qdesc, int nq, const uint32_t* __restrict__ db,
                                                      long long ndb, long long rowOffset, int rowsPerChunk, int k,
                                                      unsigned long long* __restrict__ part) {
     __shared__ __align__(128) uint4 tile[2][kKnnTileRows * 2];
     __shared__ __align__(8) unsigned long long mbar[2];
     const int tid = threadIdx.x;
-    const int q = blockIdx.x * kKnnThreads + tid;
+    const int qBase = blockIdx.x * kKnnThreads * kQ + tid;
     const long long r0 = (long long)blockIdx.y * rowsPerChunk;
     const long long r1 = min(ndb, r0 + rowsPerChunk);
     const int nrows = (int)max(0LL, r1 - r0);
-    uint32_t qd[8];
-    {
-        const int qq = min(q, nq - 1);
-        const uint4 a = reinterpret_cast<const uint4*>(qdesc)[2 * qq], b = reinterpret_cast<const uint4*>(qdesc)[2 * qq + 1];
-        qd[0] = a.x; qd[1] = a.y; qd[2] = a.z; qd[3] = a.w; qd[4] = b.x; qd[5] = b.y; qd[6] = b.z; qd[7] = b.w;
-    }
-    uint32_t best[kKnnMaxK];     // keys dist << 23 | chunk-local row, ascending
+    uint32_t qd[kQ][8];
+    uint32_t best[kQ][kK];       // keys dist << 23 | chunk-local row, ascending
+    uint32_t worst[kQ];
 #pragma unroll
-    for (int t = 0; t < kKnnMaxK; ++t) best[t] = 0xffffffffu;
-    uint32_t worst = 0xffffffffu;
+    for (int j = 0; j < kQ; ++j) {
+        const int qq = min(qBase + j * kKnnThreads, nq - 1);
+        const uint4 a = reinterpret_cast<const uint4*>(qdesc)[2 * qq], b = reinterpret_cast<const uint4*>(qdesc)[2 * qq + 1];
+        qd[j][0] = a.x; qd[j][1] = a.y; qd[j][2] = a.z; qd[j][3] = a.w; qd[j][4] = b.x; qd[j][5] = b.y; qd[j][6] = b.z; qd[j][7] = b.w;
+#pragma unroll
+        for (int t = 0; t < kK; ++t) best[j][t] = 0xffffffffu;
+        worst[j] = 0xffffffffu;
+    }
 
     const int ntiles = (nrows + kKnnTileRows - 1) / kKnnTileRows;
     if (tid == 0) {
@@ -1032,29 +1036,55 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict_
         }
         const int rows = min(kKnnTileRows, nrows - t * kKnnTileRows);
         const uint32_t rowBase = (uint32_t)(t * kKnnTileRows);
-#pragma unroll 4
-        for (int r = 0; r < rows; ++r) {
-            const int d = hamming_csa(qd, tile[s][2 * r], tile[s][2 * r + 1]);
-            const uint32_t key = ((uint32_t)d << 23) | (rowBase + (uint32_t)r);
-            if (key < worst) {
-                // sorted insertion into the k best (k <= kKnnMaxK): bubble the new key through, drop the largest
-                uint32_t carry = key;
+        auto offer = [&](int j, uint32_t key) {
+            // sorted insertion into the k best: bubble the new key through, drop the largest
+            uint32_t carry = key;
 #pragma unroll
-                for (int u = 0; u < kKnnMaxK; ++u) {
-                    if (u < k) { const uint32_t lo = min(best[u], carry), hi = max(best[u], carry); best[u] = lo; carry = hi; worst = lo; }
+            for (int u = 0; u < kK; ++u) {
+                if (u < k) { const uint32_t lo = min(best[j][u], carry), hi = max(best[j][u], carry); best[j][u] = lo; carry = hi; worst[j] = lo; }
+            }
+        };
+        // four rows at a time: one comparison of the smallest of their keys against the current k-th best decides whether
+        // any of them can enter the list (almost never, once the list has warmed up)
+        int r = 0;
+        for (; r + 4 <= rows; r += 4) {
+#pragma unroll
+            for (int j = 0; j < kQ; ++j) {
+                uint32_t key[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int d = hamming_csa(qd[j], tile[s][2 * (r + i)], tile[s][2 * (r + i) + 1]);
+                    key[i] = ((uint32_t)d << 23) | (rowBase + (uint32_t)(r + i));
                 }
+                const uint32_t m = min(min(key[0], key[1]), min(key[2], key[3]));
+                if (m < worst[j]) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) if (key[i] < worst[j]) offer(j, key[i]);
+                }
+            }
+        }
+        for (; r < rows; ++r) {
+#pragma unroll
+            for (int j = 0; j < kQ; ++j) {
+                const int d = hamming_csa(qd[j], tile[s][2 * r], tile[s][2 * r + 1]);
+                const uint32_t key = ((uint32_t)d << 23) | (rowBase + (uint32_t)r);
+                if (key < worst[j]) offer(j, key);
             }
         }
         __syncthreads();      // everyone is done with stage s before it is refilled (issue(t+2) happens next iteration)
     }
-    if (q < nq) {
-        unsigned long long* out = part + ((size_t)blockIdx.y * nq + q) * k;
 #pragma unroll
-        for (int u = 0; u < kKnnMaxK; ++u) {
-            if (u < k) {
-                const uint32_t key = best[u];
-                out[u] = key == 0xffffffffu ? 0xffffffffffffffffull
-                                            : (((unsigned long long)(key >> 23)) << 32) | (unsigned long long)(rowOffset + r0 + (key & 0x7fffffu));
+    for (int j = 0; j < kQ; ++j) {
+        const int q = qBase + j * kKnnThreads;
+        if (q < nq) {
+            unsigned long long* out = part + ((size_t)blockIdx.y * nq + q) * k;
+#pragma unroll
+            for (int u = 0; u < kK; ++u) {
+                if (u < k) {
+                    const uint32_t key = best[j][u];
+                    out[u] = key == 0xffffffffu ? 0xffffffffffffffffull
+                                                : (((unsigned long long)(key >> 23)) << 32) | (unsigned long long)(rowOffset + r0 + (key & 0x7fffffu));
+                }
             }
         }
     }
