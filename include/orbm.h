@@ -158,6 +158,51 @@ int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq
  * points: descriptors of point p are rows [off[p], off[p+1]); best[p] = row (relative) with the least median distance */
 int orbm_distinctive_descriptors(orbm_handle h, const uint8_t* desc, const int* off, int npoints, int* best);
 
+/* ---- Frame-side steps next to the searches ---- */
+
+/* replaces cv::undistortPoints(mat, mat, K, mDistCoef, Mat(), mK) in Frame::UndistortKeyPoints (src/Frame.cc:747-780) and
+ * Frame::ComputeImageBounds (src/Frame.cc:782-812).  K4 = {fx, fy, cx, cy}; dist = k1 k2 p1 p2 [k3 [k4 k5 k6 [s1..s4]]]
+ * (ndist 4, 5, 8 or 12); xy / out: n x 2 floats (HOST; may alias).  Double arithmetic, result bit-identical to OpenCV's.
+ * The caller keeps the reference's shortcut: when dist[0] == 0 the keypoints are used as they are. */
+int orbm_undistort_points(orbm_handle h, const float* xy, int n, const float* K4, const float* dist, int ndist,
+                          float* out);
+/* device-resident batch: frame f holds d_counts[f * count_stride] keypoints at d_kps + f * frame_stride (the layout
+ * orbx_extract_batch_device writes); d_kps_un receives the same records with pt undistorted (mvKeysUn).  Asynchronous. */
+int orbm_undistort_keypoints_device(orbm_handle h, int nframes, const orbx_keypoint* d_kps, const int* d_counts,
+                                    int frame_stride, int count_stride, const float* K4, const float* dist, int ndist,
+                                    orbx_keypoint* d_kps_un, void* stream);
+
+/* DBoW2 vocabulary tree as plain arrays (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h m_nodes): node 0 is the root; the
+ * children of node p are children[child_off[p] .. child_off[p+1]) in the order of m_nodes[p].children; a node without
+ * children is a word with id word_id[p] and weight weight[p].  weighting: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY
+ * (BowVector.h:39-45); norm: 0 none, 1 L1, 2 L2 (m_scoring_object->mustNormalize; ORBvoc is TF_IDF + L1). */
+typedef struct orbm_vocab_s* orbm_vocab;
+typedef struct {
+    int nnodes, levels;
+    const int* child_off;      /* nnodes + 1 */
+    const int* children;       /* child_off[nnodes] node ids */
+    const uint8_t* node_desc;  /* nnodes x 32 (row 0 unused) */
+    const int* word_id;        /* nnodes, read at leaves */
+    const double* weight;      /* nnodes, read at leaves */
+    int weighting, norm;
+} orbm_vocab_view;
+int orbm_vocab_create(orbm_handle h, const orbm_vocab_view* view, orbm_vocab* out);   /* validates and uploads the tree */
+void orbm_vocab_destroy(orbm_handle h, orbm_vocab v);
+/* replaces mpORBvocabulary->transform(vCurrentDesc, mBowVec, mFeatVec, 4) (src/Frame.cc:738-745;
+ * TemplatedVocabulary.h:1127-1198).  desc: n x 32 (HOST).  feat_word[i] = word of feature i, or -(word+1) when the
+ * word is stopped (weight 0) and the feature is left out of both vectors; feat_node[i] = its node `levelsup` levels above
+ * the leaves (either may be NULL).  BowVector: *n_bow (word, value) pairs in ascending word order (capacity n).
+ * FeatureVector as the CSR the SearchByBoW entry points take: *n_fv ascending node ids, fv_off (n + 1 ints),
+ * fv_idx (n ints, ascending feature index inside a node). */
+int orbm_bow_transform(orbm_handle h, orbm_vocab v, const uint8_t* desc, int n, int levelsup, int* feat_word,
+                       int* feat_node, int* n_bow, int* bow_word, double* bow_value, int* n_fv, int* fv_node,
+                       int* fv_off, int* fv_idx);
+/* device-resident batch of the descent only (per-feature word / node ids), for descriptors left in HBM by the
+ * extractor; same frame layout as orbm_track_batch_device.  Asynchronous on `stream`. */
+int orbm_bow_transform_device(orbm_handle h, orbm_vocab v, int nframes, const uint8_t* d_desc, const int* d_counts,
+                              int frame_stride, int count_stride, int levelsup, int* d_feat_word, int* d_feat_node,
+                              void* stream);
+
 /* Hamming evaluations performed by the last search call (for matches/s reporting); the track variant waits for the
  * device and reads the counter of the last orbm_track_batch_device */
 long long orbm_track_evaluations(orbm_handle h);

@@ -70,6 +70,12 @@ class OrbmFrameView(C.Structure):
                 ("max_x", C.c_float), ("max_y", C.c_float), ("on_device", C.c_int)]
 
 
+class OrbmVocabView(C.Structure):
+    _fields_ = [("nnodes", C.c_int), ("levels", C.c_int), ("child_off", C.c_void_p), ("children", C.c_void_p),
+                ("node_desc", C.c_void_p), ("word_id", C.c_void_p), ("weight", C.c_void_p), ("weighting", C.c_int),
+                ("norm", C.c_int)]
+
+
 class OrbmFeatVec(C.Structure):
     _fields_ = [("n_nodes", C.c_int), ("node", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p)]
 
@@ -114,6 +120,13 @@ def _bind_matcher(L):
     L.orbm_knn_merge.argtypes = [vp, vp, i32, i32, i32, vp, vp]
     L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp]
     L.orbm_track_batch_device.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, i32, f32, i32, i32, vp, vp, vp]
+    L.orbm_undistort_points.argtypes = [vp, vp, i32, vp, vp, i32, vp]
+    L.orbm_undistort_keypoints_device.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp, i32, vp, vp]
+    L.orbm_vocab_create.argtypes = [vp, C.POINTER(OrbmVocabView), C.POINTER(vp)]
+    L.orbm_vocab_destroy.argtypes = [vp, vp]
+    L.orbm_vocab_destroy.restype = None
+    L.orbm_bow_transform.argtypes = [vp, vp, vp, i32, i32, vp, vp, ip, vp, vp, ip, vp, vp, vp]
+    L.orbm_bow_transform_device.argtypes = [vp, vp, i32, vp, vp, i32, i32, i32, vp, vp, vp]
     L.orbm_track_evaluations.restype = ll
     L.orbm_track_evaluations.argtypes = [vp]
 

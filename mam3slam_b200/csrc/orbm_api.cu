@@ -884,3 +884,225 @@ extern "C" int orbm_debug_track_counters(orbm_handle M, unsigned long long* out1
     if (cudaDeviceSynchronize() != cudaSuccess) return ORBM_ERR_CUDA;
     return cudaMemcpy(out16, M->dEvals, 128, cudaMemcpyDeviceToHost) == cudaSuccess ? ORBM_OK : ORBM_ERR_CUDA;
 }
+
+// ---- Frame-side steps: undistortion and the DBoW2 transform ----------------------------------------------
+#include "orbm_kernels_frame.cuh"
+
+struct orbm_vocab_s {
+    int* childOff = nullptr; int* children = nullptr; uint4* desc = nullptr; int* wordId = nullptr; double* weight = nullptr;
+    int nnodes = 0, levels = 0, maxDepth = 0, weighting = 0, norm = 0, nwords = 0;
+    std::vector<double> wordWeight;      // host copy, indexed by word id (BowVector assembly)
+};
+
+namespace {
+
+int makeUndistortParams(orbm_matcher* M, const float* K4, const float* dist, int ndist, UndistortParams* P) {
+    if (!K4 || !dist || !(ndist == 4 || ndist == 5 || ndist == 8 || ndist == 12)) return ORBM_ERR_INVALID;
+    if (!(K4[0] != 0.f) || !(K4[1] != 0.f)) { M->err = "zero focal length"; return ORBM_ERR_INVALID; }
+    memset(P, 0, sizeof(*P));
+    for (int i = 0; i < ndist; ++i) P->k[i] = (double)dist[i];
+    P->fx = K4[0]; P->fy = K4[1]; P->cx = K4[2]; P->cy = K4[3];
+    P->ifx = 1. / P->fx; P->ify = 1. / P->fy;
+    return ORBM_OK;
+}
+
+VocabDev vocabDev(const orbm_vocab_s* v) {
+    VocabDev V;
+    V.childOff = v->childOff; V.children = v->children; V.desc = v->desc; V.wordId = v->wordId; V.weight = v->weight;
+    V.nnodes = v->nnodes; V.levels = v->levels; V.maxDepth = v->maxDepth;
+    return V;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbm_undistort_points(orbm_handle M, const float* xy, int n, const float* K4, const float* dist, int ndist, float* out) {
+    if (!M || n < 0 || (n > 0 && (!xy || !out))) return ORBM_ERR_INVALID;
+    UndistortParams P;
+    int rc = makeUndistortParams(M, K4, dist, ndist, &P);
+    if (rc) return rc;
+    if (n == 0) return ORBM_OK;
+    CKM(cudaSetDevice(M->device));
+    Stage S(M);
+    const size_t oIn = S.take<float>((size_t)n * 2), oOut = S.take<float>((size_t)n * 2);
+    rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    memcpy(S.host<float>(oIn), xy, (size_t)n * 8);
+    CKM(cudaMemcpyAsync(S.dev<float>(oIn), S.host<float>(oIn), (size_t)n * 8, cudaMemcpyHostToDevice, M->stream));
+    k_undistort<<<dim3((n + 255) / 256, 1), 256, 0, M->stream>>>(S.dev<uint8_t>(oIn), S.dev<uint8_t>(oOut), 8, nullptr, 0, n, n, 0, P);
+    ++M->launches;
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync(S.host<float>(oOut), S.dev<float>(oOut), (size_t)n * 8, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    memcpy(out, S.host<float>(oOut), (size_t)n * 8);
+    return ORBM_OK;
+}
+
+int orbm_undistort_keypoints_device(orbm_handle M, int nframes, const orbx_keypoint* d_kps, const int* d_counts, int frame_stride,
+                                    int count_stride, const float* K4, const float* dist, int ndist, orbx_keypoint* d_kps_un,
+                                    void* stream) {
+    if (!M || nframes < 1 || nframes > 65535 || !d_kps || !d_counts || frame_stride < 1 || count_stride < 1 || !d_kps_un)
+        return ORBM_ERR_INVALID;
+    UndistortParams P;
+    int rc = makeUndistortParams(M, K4, dist, ndist, &P);
+    if (rc) return rc;
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    static_assert(sizeof(orbx_keypoint) == 28, "cv::KeyPoint layout");
+    const int bx = std::min((frame_stride + 255) / 256, 64);
+    k_undistort<<<dim3(bx, nframes), 256, 0, st>>>(reinterpret_cast<const uint8_t*>(d_kps), reinterpret_cast<uint8_t*>(d_kps_un),
+                                                   (int)sizeof(orbx_keypoint), d_counts, count_stride, frame_stride, 0, 1, P);
+    ++M->launches;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+int orbm_vocab_create(orbm_handle M, const orbm_vocab_view* v, orbm_vocab* out) {
+    if (!M || !v || !out || v->nnodes < 2 || v->levels < 1 || !v->child_off || !v->children || !v->node_desc || !v->word_id ||
+        !v->weight || v->weighting < 0 || v->weighting > 3 || v->norm < 0 || v->norm > 2)
+        return ORBM_ERR_INVALID;
+    const int nn = v->nnodes;
+    // the arrays must describe one tree rooted at node 0 (the device loop follows them without further checks)
+    if (v->child_off[0] != 0) { M->err = "child_off[0] != 0"; return ORBM_ERR_INVALID; }
+    for (int p = 0; p < nn; ++p)
+        if (v->child_off[p + 1] < v->child_off[p]) { M->err = "child_off not monotone"; return ORBM_ERR_INVALID; }
+    const int nch = v->child_off[nn];
+    if (nch != nn - 1) { M->err = "children do not form a tree (expected nnodes - 1 edges)"; return ORBM_ERR_INVALID; }
+    std::vector<int> depth(nn, -1);
+    std::vector<int> order; order.reserve(nn);
+    depth[0] = 0; order.push_back(0);
+    int maxDepth = 0, nwords = 0;
+    for (size_t h = 0; h < order.size(); ++h) {
+        const int p = order[h];
+        for (int c = v->child_off[p]; c < v->child_off[p + 1]; ++c) {
+            const int id = v->children[c];
+            if (id <= 0 || id >= nn || depth[id] >= 0) { M->err = "child id out of range or reached twice"; return ORBM_ERR_INVALID; }
+            depth[id] = depth[p] + 1; maxDepth = std::max(maxDepth, depth[id]);
+            order.push_back(id);
+        }
+        if (v->child_off[p] == v->child_off[p + 1]) {
+            if (v->word_id[p] < 0) { M->err = "negative word id"; return ORBM_ERR_INVALID; }
+            nwords = std::max(nwords, v->word_id[p] + 1);
+        }
+    }
+    if ((int)order.size() != nn) { M->err = "nodes unreachable from the root"; return ORBM_ERR_INVALID; }
+    CKM(cudaSetDevice(M->device));
+    orbm_vocab_s* V = new orbm_vocab_s();
+    V->nnodes = nn; V->levels = v->levels; V->maxDepth = maxDepth; V->weighting = v->weighting; V->norm = v->norm; V->nwords = nwords;
+    V->wordWeight.assign(nwords, 0.0);
+    for (int p = 0; p < nn; ++p)
+        if (v->child_off[p] == v->child_off[p + 1]) V->wordWeight[v->word_id[p]] = v->weight[p];
+    cudaError_t e = cudaSuccess;
+    auto up = [&](void** dst, const void* src, size_t bytes) {
+        if (e != cudaSuccess) return;
+        e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
+        if (e == cudaSuccess && bytes) e = cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
+    };
+    up((void**)&V->childOff, v->child_off, (size_t)(nn + 1) * 4);
+    up((void**)&V->children, v->children, (size_t)nch * 4);
+    up((void**)&V->desc, v->node_desc, (size_t)nn * 32);
+    up((void**)&V->wordId, v->word_id, (size_t)nn * 4);
+    up((void**)&V->weight, v->weight, (size_t)nn * 8);
+    if (e != cudaSuccess) {
+        cudaFree(V->childOff); cudaFree(V->children); cudaFree(V->desc); cudaFree(V->wordId); cudaFree(V->weight);
+        delete V;
+        CKM(e);
+    }
+    *out = V;
+    return ORBM_OK;
+}
+
+void orbm_vocab_destroy(orbm_handle M, orbm_vocab V) {
+    if (!M || !V) return;
+    cudaSetDevice(M->device);
+    cudaStreamSynchronize(M->stream);
+    cudaFree(V->childOff); cudaFree(V->children); cudaFree(V->desc); cudaFree(V->wordId); cudaFree(V->weight);
+    delete V;
+}
+
+int orbm_bow_transform_device(orbm_handle M, orbm_vocab V, int nframes, const uint8_t* d_desc, const int* d_counts, int frame_stride,
+                              int count_stride, int levelsup, int* d_feat_word, int* d_feat_node, void* stream) {
+    if (!M || !V || nframes < 1 || nframes > 65535 || !d_desc || !d_counts || frame_stride < 1 || count_stride < 1 || levelsup < 0 ||
+        !d_feat_word || !d_feat_node)
+        return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    const int bx = std::min((frame_stride + 127) / 128, 256);
+    k_bow_descend<<<dim3(bx, nframes), 128, 0, st>>>(vocabDev(V), reinterpret_cast<const uint4*>(d_desc), d_counts, count_stride,
+                                                     frame_stride, 0, levelsup, d_feat_word, d_feat_node);
+    ++M->launches;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+int orbm_bow_transform(orbm_handle M, orbm_vocab V, const uint8_t* desc, int n, int levelsup, int* feat_word, int* feat_node,
+                       int* n_bow, int* bow_word, double* bow_value, int* n_fv, int* fv_node, int* fv_off, int* fv_idx) {
+    if (!M || !V || n < 0 || (n > 0 && !desc) || levelsup < 0 || !n_bow || !n_fv || !fv_off ||
+        (n > 0 && (!bow_word || !bow_value || !fv_node || !fv_idx)))
+        return ORBM_ERR_INVALID;
+    *n_bow = 0; *n_fv = 0; fv_off[0] = 0;
+    if (n == 0) return ORBM_OK;
+    CKM(cudaSetDevice(M->device));
+    Stage S(M);
+    const size_t oD = S.take<uint8_t>((size_t)n * 32), oW = S.take<int>(n), oN = S.take<int>(n);
+    int rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    memcpy(S.host<uint8_t>(oD), desc, (size_t)n * 32);
+    CKM(cudaMemcpyAsync(S.dev<uint8_t>(oD), S.host<uint8_t>(oD), (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
+    k_bow_descend<<<dim3((n + 127) / 128, 1), 128, 0, M->stream>>>(vocabDev(V), S.dev<uint4>(oD), nullptr, 0, n, n, levelsup,
+                                                                  S.dev<int>(oW), S.dev<int>(oN));
+    ++M->launches;
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync(S.host<int>(oW), S.dev<int>(oW), (size_t)(oN - oW) + (size_t)n * 4, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    const int* w = S.host<int>(oW);
+    const int* nd = S.host<int>(oN);
+    if (feat_word) memcpy(feat_word, w, (size_t)n * 4);
+    if (feat_node) memcpy(feat_node, nd, (size_t)n * 4);
+    // BowVector (BowVector.cpp:35-88): per word the weights are added in feature order, the norm runs over ascending words.
+    // FeatureVector (FeatureVector.cpp:32-46): ascending node ids, feature indices in insertion (= ascending) order.
+    std::vector<uint64_t> byWord, byNode;
+    byWord.reserve(n); byNode.reserve(n);
+    for (int i = 0; i < n; ++i) {
+        if (w[i] < 0) continue;                                         // stopped word
+        byWord.push_back(((uint64_t)(uint32_t)w[i] << 32) | (uint32_t)i);
+        byNode.push_back(((uint64_t)(uint32_t)nd[i] << 32) | (uint32_t)i);
+    }
+    std::sort(byWord.begin(), byWord.end());
+    std::sort(byNode.begin(), byNode.end());
+    const bool tf = V->weighting == 0 || V->weighting == 1;
+    int nb = 0;
+    for (size_t a = 0; a < byWord.size();) {
+        const int word = (int)(byWord[a] >> 32);
+        const double wt = V->wordWeight[word];
+        double val = wt;
+        size_t b = a + 1;
+        for (; b < byWord.size() && (int)(byWord[b] >> 32) == word; ++b)
+            if (tf) val += wt;                                          // addWeight; addIfNotExist keeps the first
+        bow_word[nb] = word; bow_value[nb] = val; ++nb;
+        a = b;
+    }
+    if (tf && nb > 0 && V->norm == 0) {
+        const double cnt = (double)nb;
+        for (int a = 0; a < nb; ++a) bow_value[a] /= cnt;
+    }
+    if (V->norm != 0) {
+        double norm = 0.0;
+        if (V->norm == 1) { for (int a = 0; a < nb; ++a) norm += std::fabs(bow_value[a]); }
+        else { for (int a = 0; a < nb; ++a) norm += bow_value[a] * bow_value[a]; norm = std::sqrt(norm); }
+        if (norm > 0.0) for (int a = 0; a < nb; ++a) bow_value[a] /= norm;
+    }
+    *n_bow = nb;
+    int nf = 0, o = 0;
+    for (size_t a = 0; a < byNode.size(); ++a) {
+        const int node = (int)(byNode[a] >> 32);
+        if (nf == 0 || fv_node[nf - 1] != node) { fv_node[nf] = node; fv_off[nf] = o; ++nf; }
+        fv_idx[o++] = (int)(uint32_t)byNode[a];
+    }
+    fv_off[nf] = o;
+    *n_fv = nf;
+    return ORBM_OK;
+}
+
+}  // extern "C"

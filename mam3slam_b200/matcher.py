@@ -8,7 +8,7 @@ the reference; all Hamming work runs in the CUDA library (no CPU fallback).
 import ctypes as C
 import numpy as np
 
-from ._lib import lib, check_m, OrbmFrameView, OrbmFeatVec
+from ._lib import lib, check_m, OrbmFrameView, OrbmFeatVec, OrbmVocabView
 from .extractor import KEYPOINT_DTYPE
 
 
@@ -99,6 +99,56 @@ class KnnDatabase:
         if getattr(self, "_db", None) and self._m._h:
             self._m._L.orbm_db_destroy(self._m._h, self._db)
             self._db = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class ORBVocabulary:
+    """DBoW2 vocabulary tree resident in HBM (orbm_vocab) — the part of ORBVocabulary (include/ORBVocabulary.h;
+    Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) that Frame::ComputeBoW / KeyFrame::ComputeBoW use.  The tree arrives as
+    plain arrays (see include/orbm.h orbm_vocab_view); TF_IDF weighting and L1 norm are ORBvoc's settings."""
+    TF_IDF, TF, IDF, BINARY = 0, 1, 2, 3
+
+    def __init__(self, matcher, levels, child_off, children, node_desc, word_id, weight, weighting=0, norm=1):
+        self._m = matcher
+        self._keep = [_c(child_off, np.int32), _c(children, np.int32), _c(node_desc, np.uint8), _c(word_id, np.int32),
+                      _c(weight, np.float64)]
+        co, ch, nd, wi, we = self._keep
+        view = OrbmVocabView(len(co) - 1, int(levels), co.ctypes.data, ch.ctypes.data, nd.ctypes.data, wi.ctypes.data,
+                             we.ctypes.data, int(weighting), int(norm))
+        self._v = C.c_void_p()
+        check_m(matcher._L.orbm_vocab_create(matcher._h, C.byref(view), C.byref(self._v)), matcher._h, "orbm_vocab_create")
+
+    def transform(self, desc, levelsup=4):
+        """transform(features, BowVector&, FeatureVector&, levelsup): returns ((bow_word, bow_value), (fv_node, fv_off,
+        fv_idx), feat_word, feat_node)."""
+        desc = _c(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        fw, fn = np.empty(n, np.int32), np.empty(n, np.int32)
+        bw, bv = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.float64)
+        vn, vo, vi = np.empty(max(n, 1), np.int32), np.empty(n + 1, np.int32), np.empty(max(n, 1), np.int32)
+        nb, nf = C.c_int(0), C.c_int(0)
+        m = self._m
+        check_m(m._L.orbm_bow_transform(m._h, self._v, _p(desc), n, int(levelsup), _p(fw), _p(fn), C.byref(nb), _p(bw), _p(bv),
+                                        C.byref(nf), _p(vn), _p(vo), _p(vi)), m._h, "orbm_bow_transform")
+        nb, nf = nb.value, nf.value
+        return (bw[:nb].copy(), bv[:nb].copy()), (vn[:nf].copy(), vo[:nf + 1].copy(), vi[:vo[nf]].copy()), fw, fn
+
+    def transform_device(self, nframes, d_desc, d_counts, frame_stride, levelsup, d_feat_word, d_feat_node, count_stride=1,
+                         stream=None):
+        m = self._m
+        check_m(m._L.orbm_bow_transform_device(m._h, self._v, int(nframes), C.c_void_p(d_desc), C.c_void_p(d_counts),
+                                               int(frame_stride), int(count_stride), int(levelsup), C.c_void_p(d_feat_word),
+                                               C.c_void_p(d_feat_node), C.c_void_p(stream or 0)), m._h, "orbm_bow_transform_device")
+
+    def close(self):
+        if getattr(self, "_v", None) and self._m._h:
+            self._m._L.orbm_vocab_destroy(self._m._h, self._v)
+            self._v = None
 
     def __del__(self):
         try:
@@ -296,3 +346,24 @@ class ORBmatcher:
         check_m(self._L.orbm_distinctive_descriptors(self._h, _p(desc), _p(off), len(off) - 1, _p(best)), self._h,
                 "orbm_distinctive_descriptors")
         return best
+
+    # ---- 8(f): Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cc:747-812) ----
+    def UndistortPoints(self, xy, K4, dist):
+        """cv::undistortPoints(xy, K, dist, R=I, P=K); K4 = (fx, fy, cx, cy).  As in the reference, callers skip the call when
+        dist[0] == 0."""
+        xy = _c(xy, np.float32).reshape(-1, 2)
+        K4, dist = _c(K4, np.float32), _c(dist, np.float32)
+        out = np.empty_like(xy)
+        check_m(self._L.orbm_undistort_points(self._h, _p(xy), len(xy), _p(K4), _p(dist), len(dist), _p(out)), self._h,
+                "orbm_undistort_points")
+        return out
+
+    def undistort_keypoints_device(self, nframes, d_kps, d_counts, frame_stride, K4, dist, d_kps_un, count_stride=1, stream=None):
+        K4, dist = _c(K4, np.float32), _c(dist, np.float32)
+        check_m(self._L.orbm_undistort_keypoints_device(self._h, int(nframes), C.c_void_p(d_kps), C.c_void_p(d_counts),
+                                                        int(frame_stride), int(count_stride), _p(K4), _p(dist), len(dist),
+                                                        C.c_void_p(d_kps_un), C.c_void_p(stream or 0)), self._h,
+                "orbm_undistort_keypoints_device")
+
+    def vocabulary(self, levels, child_off, children, node_desc, word_id, weight, weighting=0, norm=1):
+        return ORBVocabulary(self, levels, child_off, children, node_desc, word_id, weight, weighting, norm)

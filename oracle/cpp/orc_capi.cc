@@ -222,5 +222,14 @@ void orc_knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint1
     knn(q, nq, db, ndb, k, dist, idx, threads);
 }
 int orc_distinctive_descriptor(const uint8_t* desc, int n) { return distinctive_descriptor(desc, n); }
+void orc_undistort_points(const float* xy, int n, const float* K, const float* dist, int ndist, float* out) {
+    undistort_points(xy, n, K, dist, ndist, out);
+}
+void orc_bow_transform(int nnodes, int L, const int* childOff, const int* children, const uint8_t* ndesc, const int* wordId,
+                       const double* weight, int weighting, int norm, const uint8_t* desc, int n, int levelsup, int* featWord,
+                       int* featNode, int* nBow, int* bowWord, double* bowValue, int* nFv, int* fvNode, int* fvOff, int* fvIdx) {
+    VocabView V{nnodes, L, childOff, children, ndesc, wordId, weight, weighting, norm};
+    bow_transform(V, desc, n, levelsup, featWord, featNode, nBow, bowWord, bowValue, nFv, fvNode, fvOff, fvIdx);
+}
 
 }  // extern "C"

@@ -4,6 +4,8 @@
 #include <climits>
 #include <cmath>
 #include <cstring>
+#include <map>
+#include <vector>
 #include <thread>
 
 namespace orc {
@@ -456,6 +458,93 @@ int distinctive_descriptor(const uint8_t* desc, int N) {
         if (median < BestMedian) { BestMedian = median; BestIdx = i; }
     }
     return BestIdx;
+}
+
+// ---- Frame::UndistortKeyPoints (src/Frame.cc:747-780): cv::undistortPoints restated ---------------------------------------
+void undistort_points(const float* xy, int n, const float* K, const float* dist, int ndist, float* out) {
+    double k[12] = {0};
+    for (int i = 0; i < ndist && i < 12; i++) k[i] = dist[i];
+    const double fx = K[0], fy = K[1], cx = K[2], cy = K[3];
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        const double u = xy[2 * i], v = xy[2 * i + 1];
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        // RR = P * R = K: third row (0, 0, 1) -> ww = 1
+        const double xx = fx * x + 0. * y + cx, yy = 0. * x + fy * y + cy, ww = 1. / (0. * x + 0. * y + 1.);
+        out[2 * i] = (float)(xx * ww);
+        out[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
+// ---- DBoW2 transform (TemplatedVocabulary.h:1218-1260) -------------------------------------------------------------------------
+void bow_descend(const VocabView& V, const uint8_t* feature, int levelsup, int* wordId, double* weight, int* nodeId) {
+    const int nid_level = V.L - levelsup;
+    if (nid_level <= 0) *nodeId = 0;  // root
+    int final_id = 0, current_level = 0;
+    do {
+        ++current_level;
+        const int b = V.childOff[final_id], e = V.childOff[final_id + 1];
+        final_id = V.children[b];
+        double best_d = descriptor_distance(feature, V.desc + 32 * (size_t)final_id);
+        for (int c = b + 1; c < e; c++) {
+            const int id = V.children[c];
+            const double d = descriptor_distance(feature, V.desc + 32 * (size_t)id);
+            if (d < best_d) { best_d = d; final_id = id; }
+        }
+        if (current_level == nid_level) *nodeId = final_id;
+    } while (V.childOff[final_id + 1] != V.childOff[final_id]);
+    *wordId = V.wordId[final_id];
+    *weight = V.weight[final_id];
+}
+
+void bow_transform(const VocabView& V, const uint8_t* desc, int n, int levelsup, int* featWord, int* featNode,
+                   int* nBow, int* bowWord, double* bowValue, int* nFv, int* fvNode, int* fvOff, int* fvIdx) {
+    std::map<int, double> v;                         // DBoW2::BowVector
+    std::map<int, std::vector<unsigned>> fv;         // DBoW2::FeatureVector
+    const bool tf = V.weighting == 0 || V.weighting == 1;
+    for (int i = 0; i < n; i++) {
+        int id = 0, nid = 0; double w = 0;
+        bow_descend(V, desc + 32 * (size_t)i, levelsup, &id, &w, &nid);
+        featWord[i] = id; featNode[i] = nid;
+        if (w > 0) {  // not stopped
+            if (tf) v[id] += w;                      // addWeight
+            else v.insert({id, w});                  // addIfNotExist
+            fv[nid].push_back((unsigned)i);
+        } else {
+            featWord[i] = -1 - id;                   // stopped word: reported as -(id+1)
+        }
+    }
+    if (tf && !v.empty() && V.norm == 0) {
+        const double nd = (double)v.size();
+        for (auto& kv : v) kv.second /= nd;
+    }
+    if (V.norm != 0) {
+        double norm = 0.0;
+        if (V.norm == 1) { for (auto& kv : v) norm += std::fabs(kv.second); }
+        else { for (auto& kv : v) norm += kv.second * kv.second; norm = std::sqrt(norm); }
+        if (norm > 0.0) for (auto& kv : v) kv.second /= norm;
+    }
+    int a = 0;
+    for (auto& kv : v) { bowWord[a] = kv.first; bowValue[a] = kv.second; a++; }
+    *nBow = a;
+    int b = 0, o = 0;
+    for (auto& kv : fv) {
+        fvNode[b] = kv.first; fvOff[b] = o;
+        for (unsigned f : kv.second) fvIdx[o++] = (int)f;
+        b++;
+    }
+    fvOff[b] = o;
+    *nFv = b;
 }
 
 }  // namespace orc

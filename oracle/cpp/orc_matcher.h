@@ -98,4 +98,29 @@ void knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t*
 // least median distance to the others
 int distinctive_descriptor(const uint8_t* desc, int n);
 
+// 8(f) rank 1 (last part): Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cc:747-780,782-812).  Both call
+// cv::undistortPoints(mat, mat, K, distCoef, Mat(), K) — OpenCV (external dependency, find_package(OpenCV 4.4),
+// CMakeLists.txt:38; calib3d/src/undistort.dispatch.cpp, cvUndistortPointsInternal) with the default criteria
+// (5 iterations, no epsilon test), R = I, P = K, no tilt terms.  All arithmetic is double on float inputs; the result is
+// rounded to float.  Pinned bit-exact against cv2.undistortPoints (tests/golden/cv2_undistort.npz).
+// K = {fx, fy, cx, cy}; dist = k1 k2 p1 p2 [k3 [k4 k5 k6 [s1 s2 s3 s4]]] (ndist in {4,5,8,12}); xy: n x 2 floats.
+void undistort_points(const float* xy, int n, const float* K, const float* dist, int ndist, float* out);
+
+// 8(f) rank 3: DBoW2 TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup)
+// (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1127-1198 and the per-feature descent :1218-1260; BowVector.cpp:35-88;
+// FeatureVector.cpp:32-46), called by Frame::ComputeBoW with levelsup = 4 (src/Frame.cc:738-745).
+// The vocabulary tree is given as plain arrays: children of node p are children[childOff[p] .. childOff[p+1]) in the
+// order of m_nodes[p].children; a node with no children is a leaf (word).  weighting: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY
+// (BowVector.h:39-45); norm: 0 none, 1 L1, 2 L2 (what m_scoring_object->mustNormalize yields, ScoringObject.h:74-89).
+struct VocabView {
+    int nnodes, L;
+    const int* childOff; const int* children; const uint8_t* desc; const int* wordId; const double* weight;
+    int weighting, norm;
+};
+// per feature: word id, weight and the node `levelsup` levels above the leaves
+void bow_descend(const VocabView& V, const uint8_t* feature, int levelsup, int* wordId, double* weight, int* nodeId);
+// whole transform; outputs are flattened maps in key order.  bowWord/bowValue need n entries, fvNode n, fvOff n+1, fvIdx n.
+void bow_transform(const VocabView& V, const uint8_t* desc, int n, int levelsup, int* featWord, int* featNode,
+                   int* nBow, int* bowWord, double* bowValue, int* nFv, int* fvNode, int* fvOff, int* fvIdx);
+
 }  // namespace orc

@@ -42,6 +42,8 @@ def _L():
                                                i, i, vp]
         L.orc_fuse_candidates.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, i, vp, vp]
         L.orc_distinctive_descriptor.argtypes = [vp, i]
+        L.orc_undistort_points.argtypes = [vp, i, vp, vp, i, vp]
+        L.orc_bow_transform.argtypes = [i, i, vp, vp, vp, vp, vp, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L._matcher_ready = True
     return L
 
@@ -191,3 +193,32 @@ def knn(q, db, k, threads=1):
 def distinctive_descriptor(desc):
     desc = _c(desc, np.uint8)
     return int(_L().orc_distinctive_descriptor(_p(desc), len(desc)))
+
+
+def undistort_points(xy, K, dist):
+    """cv::undistortPoints(xy, K, dist, R=I, P=K) as Frame::UndistortKeyPoints calls it (src/Frame.cc:768).
+    K = (fx, fy, cx, cy)."""
+    xy, K, dist = _c(xy, np.float32).reshape(-1, 2), _c(K, np.float32), _c(dist, np.float32)
+    out = np.empty_like(xy)
+    _L().orc_undistort_points(_p(xy), len(xy), _p(K), _p(dist), len(dist), _p(out))
+    return out
+
+
+def bow_transform(voc, desc, levelsup=4):
+    """DBoW2 transform(features, BowVector, FeatureVector, levelsup).  voc: dict with L, child_off, children, desc, word_id,
+    weight, weighting, norm (see orc_matcher.h VocabView).  Returns dict(word, node, bow_word, bow_value, fv_node, fv_off,
+    fv_idx)."""
+    desc = _c(desc, np.uint8).reshape(-1, 32)
+    n = len(desc)
+    co, ch = _c(voc["child_off"], np.int32), _c(voc["children"], np.int32)
+    nd, wi, we = _c(voc["desc"], np.uint8), _c(voc["word_id"], np.int32), _c(voc["weight"], np.float64)
+    fw, fn = np.empty(n, np.int32), np.empty(n, np.int32)
+    bw, bv = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.float64)
+    vn, vo, vi = np.empty(max(n, 1), np.int32), np.empty(n + 1, np.int32), np.empty(max(n, 1), np.int32)
+    nb, nf = C.c_int(0), C.c_int(0)
+    _L().orc_bow_transform(len(co) - 1, int(voc["L"]), _p(co), _p(ch), _p(nd), _p(wi), _p(we), int(voc["weighting"]),
+                           int(voc["norm"]), _p(desc), n, int(levelsup), _p(fw), _p(fn), C.byref(nb), _p(bw), _p(bv),
+                           C.byref(nf), _p(vn), _p(vo), _p(vi))
+    nb, nf = nb.value, nf.value
+    return dict(word=fw, node=fn, bow_word=bw[:nb].copy(), bow_value=bv[:nb].copy(), fv_node=vn[:nf].copy(),
+                fv_off=vo[:nf + 1].copy(), fv_idx=vi[:vo[nf]].copy())

@@ -60,3 +60,69 @@ def knn_data(ndb, nq, seed=1234, planted=True):
             for b in bits:
                 q[i, b >> 3] ^= 1 << (b & 7)
     return q, db
+
+
+def make_vocab(k=10, L=4, seed=3, stop_frac=0.05, ragged=True, weighting=0, norm=1):
+    """Synthetic DBoW2 vocabulary tree in the array form of include/orbm.h (the real ORBvoc.txt is absent from the reference
+    checkout).  Node ids are a random permutation so that siblings are NOT contiguous, some inner nodes have fewer than k
+    children and some leaves sit above level L (k-means yields both), sibling descriptors contain exact duplicates (ties go to
+    the first child) and a fraction of the words is stopped (weight 0)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    parents = [(-1, 0)]                        # (parent position, depth) in creation order; position 0 = root
+    desc = [np.zeros(32, np.uint8)]
+    kids = [[]]
+    frontier = [0]
+    for depth in range(1, L + 1):
+        nxt = []
+        for p in frontier:
+            if ragged and depth > 1 and rng.random() < 0.03:
+                continue                       # p stays a leaf above level L
+            nk = k if not ragged or depth == 1 or rng.random() < 0.8 else int(rng.integers(1, k + 1))
+            base = desc[p] if depth > 1 else rng.integers(0, 256, 32, dtype=np.uint8)
+            for c in range(nk):
+                d = base.copy() if depth > 1 else rng.integers(0, 256, 32, dtype=np.uint8)
+                flips = rng.choice(256, int(rng.integers(8, 60)), replace=False)
+                np.bitwise_xor.at(d, flips // 8, (1 << (flips % 8)).astype(np.uint8))
+                if c > 0 and rng.random() < 0.05:
+                    d = desc[kids[p][int(rng.integers(0, c))]].copy()      # duplicate sibling: tie
+                desc.append(d)
+                kids.append([])
+                kids[p].append(len(desc) - 1)
+                nxt.append(len(desc) - 1)
+        frontier = nxt
+    nn = len(desc)
+    perm = np.concatenate([[0], 1 + rng.permutation(nn - 1)]).astype(np.int64)     # position -> node id (root stays 0)
+    inv = np.empty(nn, np.int64)
+    inv[perm] = np.arange(nn)
+    child_off = np.zeros(nn + 1, np.int32)
+    children = []
+    node_desc = np.zeros((nn, 32), np.uint8)
+    word_id = np.full(nn, -1, np.int32)
+    weight = np.zeros(nn, np.float64)
+    nw = 0
+    for nid in range(nn):                      # DBoW2 numbers the words in node-id order (createWords)
+        pos = int(inv[nid])
+        node_desc[nid] = desc[pos]
+        children.extend(int(perm[c]) for c in kids[pos])
+        child_off[nid + 1] = len(children)
+        if not kids[pos]:
+            word_id[nid] = nw
+            nw += 1
+            weight[nid] = 0.0 if rng.random() < stop_frac else float(rng.uniform(0.01, 9.0))
+    return dict(L=L, child_off=child_off, children=np.array(children, np.int32), desc=node_desc, word_id=word_id, weight=weight,
+                weighting=weighting, norm=norm, nwords=nw)
+
+
+def vocab_features(voc, n, seed=11):
+    """descriptors near random leaves of the tree (so that the descent is not a coin toss at every level), plus pure noise"""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    leaves = np.nonzero(voc["word_id"] >= 0)[0]
+    src = voc["desc"][rng.choice(leaves, n)].copy()
+    for i in range(n):
+        flips = rng.choice(256, int(rng.integers(0, 50)), replace=False)
+        np.bitwise_xor.at(src[i], flips // 8, (1 << (flips % 8)).astype(np.uint8))
+    src[::17] = rng.integers(0, 256, (len(src[::17]), 32), dtype=np.uint8)
+    if n > 40:
+        src[5] = src[23]                       # identical features land in the same word
+        src[31] = src[23]
+    return src
