@@ -179,8 +179,8 @@ int configureShape(Extractor* E, int W, int H) {
                 c.cap = ((c.w + 1) / 2) * ((c.h + 1) / 2);    // 3x3 strict maxima cannot be denser
                 c.outOffset = candOff;
                 candOff += c.cap; G.candCap += c.cap;
-                if (c.w > 255 || c.h > 255 || c.w * c.h > 32 * kFastThreads) { E->err = "FAST cell too large"; return ORBX_ERR_UNSUPPORTED; }
-                maxCellPx = std::max<int>(maxCellPx, c.w * c.h);
+                if (c.w > 255 || c.h > 255 || ((c.w + 1) & ~1) * c.h > 32 * kFastThreads) { E->err = "FAST cell too large"; return ORBX_ERR_UNSUPPORTED; }
+                maxCellPx = std::max<int>(maxCellPx, ((c.w + 1) & ~1) * c.h);      // pixel slots: rows padded to whole pairs
                 maxCellW = std::max<int>(maxCellW, c.w); maxCellH = std::max<int>(maxCellH, c.h);
                 E->cells.push_back(c);
             }
@@ -218,7 +218,7 @@ int configureShape(Extractor* E, int W, int H) {
     E->fastPitchConst = E->fastTilePitch <= 33;      // the usual 35-px cells: compile-time pitch (k_fast_cells<., 33>)
     if (E->fastPitchConst) E->fastTilePitch = 33;
     E->fastTileRows = maxCellH + 6;
-    E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (((size_t)(maxCellH + 2) * (maxCellW + 2) + 3) & ~(size_t)3) + 16;
+    E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (((size_t)(maxCellH + 2) * (maxCellW + 4) + 3) & ~(size_t)3) + 16;
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
     CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

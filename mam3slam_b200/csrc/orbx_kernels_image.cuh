@@ -221,7 +221,8 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
                                                              int pitchWArg, int tileRowsMax, int frameBase) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int pitchW = kPitch ? kPitch : pitchWArg;    // a constant pitch turns the 17 ring addresses into immediates
-    __shared__ uint32_t cmask[kThreads + 1];           // raster-order corner bitmap (+1: the slice read below may touch it)
+    // candidate bitmaps by PAIR index (bit p = pair p holds a candidate in its even / odd pixel), written with ballots
+    __shared__ uint32_t cmE[kThreads / 2 + 2], cmO[kThreads / 2 + 2];
     __shared__ int warpSum[kThreads / 32];
     __shared__ int total;
     const FastCell c = cells[blockIdx.x];
@@ -233,13 +234,16 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
     const int tw = w + 6, th = h + 6;
     uint32_t* SA = reinterpret_cast<uint32_t*>(smem);                // pairs starting at even X: (X, X+1)
     uint32_t* SB = SA + (size_t)tileRowsMax * pitchW;                // pairs starting at odd X
-    uint8_t* score = reinterpret_cast<uint8_t*>(SB + (size_t)tileRowsMax * pitchW);   // (h+2) x (w+2), apron = 0
-    const int sp = w + 2;
+    // raw strengths of ALL tested pixels, one byte each: pixel (px, py) at (py+1)*sp + px + 2, so that a pair (even px)
+    // is one aligned 16-bit store; rows 0 and h+1 and the columns px = -1 and px = w stay 0 (the apron)
+    uint8_t* score = reinterpret_cast<uint8_t*>(SB + (size_t)tileRowsMax * pitchW);
+    const int sp = (w + 4) & ~1;
     const int gx0 = c.x0 - 3, gy0 = c.y0 - 3;
     const uint8_t* origin = img + (size_t)gy0 * pitch + gx0;
     const bool aligned = (((uintptr_t)img | (uintptr_t)pitch) & 3) == 0;
     const int a = aligned ? (int)((uintptr_t)origin & 3) : 0;        // X = tile x + a; rows start word-aligned when aligned
-    const int npx = w * h, nwords = (npx + 31) >> 5;
+    const int pw = (w + 1) >> 1;                 // pairs per row; the last one is half empty when w is odd
+    const int npairs = pw * h;
 
     if (aligned) {
         // 16 threads per tile row (typical cells need 11-12 words per row)
@@ -285,81 +289,90 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
         }
     }
     {
-        uint32_t* sw = reinterpret_cast<uint32_t*>(score);           // the score tile is 4-byte aligned and padded (host)
-        for (int i = tid; i < ((h + 2) * sp + 3) >> 2; i += kThreads) sw[i] = 0;
-        cmask[tid] = 0;
-        if (tid == 0) cmask[kThreads] = 0;
+        uint16_t* s16 = reinterpret_cast<uint16_t*>(score);          // apron only: every tested pixel is written below
+        const int sp2 = sp >> 1;
+        for (int i = tid; i < sp2; i += kThreads) { s16[i] = 0; s16[(h + 1) * sp2 + i] = 0; }
+        for (int i = tid; i < h; i += kThreads) {
+            s16[(i + 1) * sp2] = 0;                                   // px = -1 (and the unused byte before it)
+            if (!(w & 1)) s16[(i + 1) * sp2 + ((w + 2) >> 1)] = 0;    // px = w; for odd w the last pair's store covers it
+        }
     }
     __syncthreads();
 
     const int minTh = g->minTh, iniTh = g->iniTh;
+    const int lane = tid & 31, wid = tid >> 5;
     {
         // tested pixel (px, py) = tile (px+3, py+3); pair start X = px0 + 3 + a + dx with px0 even
         const int ap = a + 3;
         const uint32_t* E = ((ap & 1) ? SB : SA) + (ap >> 1);          // even dx: index px0/2 + dx/2
         const uint32_t* O = ((ap & 1) ? SA : SB) + ((ap + 1) >> 1);    // odd dx : index px0/2 + (dx-1)/2
-        const int pw = (w + 1) >> 1;
-        const int npairs = pw * h;
         const int P = pitchW;
         // (py, pc) of pair p advance by a constant step per pass: one division per thread instead of one per pair
         const int stepY = kThreads / pw, stepC = kThreads - stepY * pw;
         int py = tid / pw, pc = tid - py * pw;
-        for (int p = tid; p < npairs; p += kThreads) {
-            const int b = (py + 3) * P + pc;
-            const uint32_t v2 = E[b];
-            uint32_t r[16];
-            r[0] = E[b + 3 * P];       r[1] = O[b + 3 * P];       r[2] = E[b + 2 * P + 1];   r[3] = O[b + P + 1];
-            r[4] = O[b + 1];           r[5] = O[b - P + 1];       r[6] = E[b - 2 * P + 1];   r[7] = O[b - 3 * P];
-            r[8] = E[b - 3 * P];       r[9] = O[b - 3 * P - 1];   r[10] = E[b - 2 * P - 1];  r[11] = O[b - P - 2];
-            r[12] = O[b - 2];          r[13] = O[b + P - 2];      r[14] = E[b + 2 * P - 1];  r[15] = O[b + 3 * P - 1];
-            const uint32_t s2 = fast_strength_x2(v2, r);
-            const int s0 = (int)(s2 & 0xffffu), s1 = (int)(s2 >> 16);
-            const bool c0 = s0 > minTh, c1 = s1 > minTh && 2 * pc + 1 < w;
-            if (c0 || c1) {
-                uint8_t* sc = score + (py + 1) * sp + 2 * pc + 1;
-                const int bit = py * w + 2 * pc;
-                if (c0) { sc[0] = (uint8_t)s0; atomicOr(&cmask[bit >> 5], 1u << (bit & 31)); }
-                if (c1) { sc[1] = (uint8_t)s1; atomicOr(&cmask[(bit + 1) >> 5], 1u << ((bit + 1) & 31)); }
+        // whole warps run the loop (the ballots need every lane); lanes past the last pair only vote 'no'
+        for (int p0 = wid * 32; p0 < npairs; p0 += kThreads) {
+            bool c0 = false, c1 = false;
+            if (p0 + lane < npairs) {
+                const int b = (py + 3) * P + pc;
+                const uint32_t v2 = E[b];
+                uint32_t r[16];
+                r[0] = E[b + 3 * P];       r[1] = O[b + 3 * P];       r[2] = E[b + 2 * P + 1];   r[3] = O[b + P + 1];
+                r[4] = O[b + 1];           r[5] = O[b - P + 1];       r[6] = E[b - 2 * P + 1];   r[7] = O[b - 3 * P];
+                r[8] = E[b - 3 * P];       r[9] = O[b - 3 * P - 1];   r[10] = E[b - 2 * P - 1];  r[11] = O[b - P - 2];
+                r[12] = O[b - 2];          r[13] = O[b + P - 2];      r[14] = E[b + 2 * P - 1];  r[15] = O[b + 3 * P - 1];
+                uint32_t s2 = fast_strength_x2(v2, r);
+                if (2 * pc + 1 >= w) s2 &= 0xffffu;                    // the odd pixel of the last pair lies outside the cell
+                *reinterpret_cast<uint16_t*>(score + (py + 1) * sp + 2 * pc + 2) = (uint16_t)__byte_perm(s2, 0, 0x4420);
+                c0 = (int)(s2 & 0xffffu) > minTh;
+                c1 = (int)(s2 >> 16) > minTh;
+                py += stepY; pc += stepC;
+                if (pc >= pw) { pc -= pw; ++py; }
             }
-            py += stepY; pc += stepC;
-            if (pc >= pw) { pc -= pw; ++py; }
+            const uint32_t bE = __ballot_sync(0xffffffffu, c0), bO = __ballot_sync(0xffffffffu, c1);
+            if (lane == 0) { cmE[p0 >> 5] = bE; cmO[p0 >> 5] = bO; }
         }
+        // the two words after the last one are read by the funnel shifts below
+        if (tid < 2) { cmE[((npairs + 31) >> 5) + tid] = 0; cmO[((npairs + 31) >> 5) + tid] = 0; }
     }
     __syncthreads();
 
-    // NMS at both thresholds, corners only.  Every thread owns a contiguous raster chunk (<= 32 pixels, so the survivors
-    // come out in raster order) and visits just the corner bits of its slice of the bitmap.
-    const int per = (npx + kThreads - 1) / kThreads;
-    const int pb = tid * per, pe = min(pb + per, npx);
+    // NMS, candidates only.  A corner survives iff its strength exceeds all 8 neighbours' (cv::FAST compares the stored
+    // scores, strength - 1 for corners and 0 otherwise: a neighbour at or below the threshold can never win against a
+    // corner above it, so comparing raw strengths is the same test at either threshold); cells keep the iniThFAST
+    // survivors, or the minThFAST ones when there are none (src/ORBextractor.cc:826-846).
+    // Every thread owns a contiguous run of <= 16 pairs = 32 pixel slots in padded raster order (row width w2 = 2 * pw).
+    const int w2 = 2 * pw;
+    const int per = (npairs + kThreads - 1) / kThreads;
+    const int pb = tid * per, pe = min(pb + per, npairs);
     uint32_t keepIni = 0, keepMin = 0;
     if (pb < pe) {
-        uint32_t m = __funnelshift_r(cmask[pb >> 5], cmask[(pb >> 5) + 1], pb & 31);
-        if (pe - pb < 32) m &= (1u << (pe - pb)) - 1;
-        int py = pb / w, px = pb - py * w;             // chunk origin; a corner's coordinates follow by carry, no division
+        uint32_t z = (__funnelshift_r(cmE[pb >> 5], cmE[(pb >> 5) + 1], pb & 31) & 0xffffu) |
+                     (__funnelshift_r(cmO[pb >> 5], cmO[(pb >> 5) + 1], pb & 31) << 16);
+        if (pe - pb < 16) z &= ((1u << (pe - pb)) - 1) * 0x00010001u;
+        // perfect shuffle: bit i of the low half -> bit 2i, bit i of the high half -> bit 2i+1
+        uint32_t t;
+        t = (z ^ (z >> 8)) & 0x0000ff00u; z ^= t ^ (t << 8);
+        t = (z ^ (z >> 4)) & 0x00f000f0u; z ^= t ^ (t << 4);
+        t = (z ^ (z >> 2)) & 0x0c0c0c0cu; z ^= t ^ (t << 2);
+        t = (z ^ (z >> 1)) & 0x22222222u; z ^= t ^ (t << 1);
+        uint32_t m = z;
+        const int py = pb / pw, px = 2 * (pb - py * pw);   // chunk origin; a corner's coordinates follow by carry, no division
         while (m) {
             const int bpos = __ffs(m) - 1;
             m &= m - 1;
             int cy = py, cx = px + bpos;
-            while (cx >= w) { cx -= w; ++cy; }
-            const uint8_t* sc = score + (cy + 1) * sp + cx + 1;
+            while (cx >= w2) { cx -= w2; ++cy; }
+            const uint8_t* sc = score + (cy + 1) * sp + cx + 2;
             const int s = sc[0];
-            int nbMin = 0, nbIni = 0;     // max neighbour stored score at each threshold
-#pragma unroll
-            for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-                for (int dx = -1; dx <= 1; ++dx) {
-                    if (dx == 0 && dy == 0) continue;
-                    const int q = sc[dy * sp + dx];
-                    nbMin = max(nbMin, q);
-                    nbIni = max(nbIni, q > iniTh ? q : 0);
-                }
-            // stored scores are strength-1 on both sides of the comparison; strength 0 means "not a corner" (score 0)
-            const int mine = s - 1;
-            if (mine > max(nbMin - 1, 0)) keepMin |= 1u << bpos;
-            if (s > iniTh && mine > max(nbIni - 1, 0)) keepIni |= 1u << bpos;
+            const int nb = __vimax3_s32(__vimax3_s32(sc[-sp - 1], sc[-sp], sc[-sp + 1]),
+                                        __vimax3_s32(sc[sp - 1], sc[sp], sc[sp + 1]), max((int)sc[-1], (int)sc[1]));
+            if (s > nb) {
+                keepMin |= 1u << bpos;
+                if (s > iniTh) keepIni |= 1u << bpos;
+            }
         }
     }
-    const int lane = tid & 31, wid = tid >> 5;
     const int anyIni = __syncthreads_or(keepIni != 0);
     const uint32_t keep = anyIni ? keepIni : keepMin;
     const int cnt = __popc(keep);
@@ -383,9 +396,9 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
     while (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        const int p = pb + b;
-        const int py = p / w, px = p - py * w;
-        const int s = score[(py + 1) * sp + px + 1];
+        const int p = 2 * pb + b;
+        const int py = p / w2, px = p - py * w2;
+        const int s = score[(py + 1) * sp + px + 2];
         out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
     }
     if (tid == 0) cellCount[(size_t)frame * g->nCells + blockIdx.x] = total;
