@@ -103,6 +103,17 @@ int orbm_fuse_candidates(orbm_handle h, orbm_frame kf, const float* scale_factor
                          int nq, const uint8_t* valid, const float* u, const float* v, const int* level,
                          const uint8_t* qdesc, float th, int chi2_gate, int* best_idx, int* best_dist);
 
+/* replaces SearchBySim3(KF1, KF2, vpMatches12, S12, th) (:1457-1674; no caller in the reference tree, kept for the class
+ * surface).  Slot i of a keyframe stands for its map point: valid1[i] = the point survives the pre-checks (:1500-1531: present,
+ * not already matched, not bad, positive depth, in image, inside the scale-invariance range), (u12, v12) = its projection
+ * into KF2, level12 = PredictScale, qdesc1 = MapPoint::GetDescriptor rows (n1 x 32); likewise 2 -> 1.  Each direction keeps
+ * the best keypoint (levels [l-1, l], first minimum) when its distance <= TH_HIGH; matches12[i1] = i2 where both
+ * directions agree, else -1; *nfound = the reference's return value. */
+int orbm_search_by_sim3(orbm_handle h, orbm_frame kf1, orbm_frame kf2, const float* scale_factors1,
+                        const float* scale_factors2, int nlevels, const uint8_t* valid1, const float* u12, const float* v12,
+                        const int* level12, const uint8_t* qdesc1, const uint8_t* valid2, const float* u21, const float* v21,
+                        const int* level21, const uint8_t* qdesc2, float th, int* matches12, int* nfound);
+
 /* Device-resident tracking step (BASELINE config[1]: per-frame extraction + SearchByProjection on one GPU): for every
  * frame i >= 1 of a batch of extractor results that never left HBM (d_kps / d_desc / d_counts = the arrays behind
  * orbx_results_device: frame f at d_kps + f*frame_stride, its keypoint count at d_counts[f*count_stride]) runs

@@ -496,6 +496,51 @@ int orbm_fuse_candidates(orbm_handle M, orbm_frame kf, const float* scale_factor
     return ORBM_OK;
 }
 
+// M8: src/ORBmatcher.cc:1457-1674 — one stateless window search per direction, then the agreement check
+static int sim3OneWay(orbm_matcher* M, const orbm_frame_s* T, const float* sf, int nlevels, int nq, const uint8_t* valid,
+                      const float* u, const float* v, const int* level, const uint8_t* qdesc, float th, std::vector<int>& match) {
+    SearchIO io;
+    match.assign(nq, -1);
+    for (int q = 0; q < nq; ++q) {
+        if (!valid[q]) continue;
+        const int l = level[q];
+        if (l < 0 || l >= nlevels) return ORBM_ERR_INVALID;
+        io.qwin.push_back(make_float4(u[q], v[q], th * sf[l], 0));
+        io.qlev.push_back(make_int2(l - 1, l));
+        io.qsrc.push_back(q);
+    }
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc;
+    SearchParams P = baseParams();
+    P.source = 0; P.state = 0; P.rule = RULE_NONE;
+    const int rc = runSearch(M, T, P, io);
+    if (rc) return rc;
+    for (int q = 0; q < io.nq; ++q)
+        if (io.result[q] >= 0 && io.dist[q] <= ORBM_TH_HIGH) match[io.qsrc[q]] = io.result[q];   // bestDist<=TH_HIGH (:1569,1649)
+    return ORBM_OK;
+}
+int orbm_search_by_sim3(orbm_handle M, orbm_frame kf1, orbm_frame kf2, const float* scale_factors1, const float* scale_factors2,
+                        int nlevels, const uint8_t* valid1, const float* u12, const float* v12, const int* level12,
+                        const uint8_t* qdesc1, const uint8_t* valid2, const float* u21, const float* v21, const int* level21,
+                        const uint8_t* qdesc2, float th, int* matches12, int* nfound) {
+    if (!M || !kf1 || !kf2 || !scale_factors1 || !scale_factors2 || !matches12 || !nfound) return ORBM_ERR_INVALID;
+    if ((kf1->n && (!valid1 || !u12 || !v12 || !level12 || !qdesc1)) || (kf2->n && (!valid2 || !u21 || !v21 || !level21 || !qdesc2)))
+        return ORBM_ERR_INVALID;
+    std::vector<int> m1, m2;
+    int rc = sim3OneWay(M, kf2, scale_factors2, nlevels, kf1->n, valid1, u12, v12, level12, qdesc1, th, m1);
+    long long ev = M->lastEvals;
+    if (rc) return rc;
+    if ((rc = sim3OneWay(M, kf1, scale_factors1, nlevels, kf2->n, valid2, u21, v21, level21, qdesc2, th, m2))) return rc;
+    M->lastEvals += ev;
+    int n = 0;
+    for (int i1 = 0; i1 < kf1->n; ++i1) {                      // "check agreement" (:1655-1671)
+        const int idx2 = m1[i1];
+        matches12[i1] = (idx2 >= 0 && m2[idx2] == i1) ? idx2 : -1;
+        n += matches12[i1] >= 0;
+    }
+    *nfound = n;
+    return ORBM_OK;
+}
+
 // M5: src/ORBmatcher.cc:648-763
 int orbm_search_initialization(orbm_handle M, orbm_frame f1, orbm_frame f2, float* prev_matched, int window_size, float nnratio,
                                int check_orientation, int* matches12, int* nmatches) {

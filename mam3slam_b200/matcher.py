@@ -307,6 +307,21 @@ class ORBmatcher:
                 "orbm_fuse_candidates")
         return bi, bd
 
+    # ---- M8: SearchBySim3 (src/ORBmatcher.cc:1457-1674) ----
+    def SearchBySim3(self, KF1, KF2, scale_factors1, scale_factors2, valid1, u12, v12, level12, qdesc1, valid2, u21, v21,
+                     level21, qdesc2, th):
+        sf1, sf2 = _c(scale_factors1, np.float32), _c(scale_factors2, np.float32)
+        a = [_c(valid1, np.uint8), _c(u12, np.float32), _c(v12, np.float32), _c(level12, np.int32), _c(qdesc1, np.uint8)]
+        b = [_c(valid2, np.uint8), _c(u21, np.float32), _c(v21, np.float32), _c(level21, np.int32), _c(qdesc2, np.uint8)]
+        if len(a[0]) != KF1.n or len(b[0]) != KF2.n:
+            raise ValueError("one query per keypoint slot of each keyframe")
+        out = np.full(KF1.n, -1, np.int32)
+        nf = C.c_int(0)
+        check_m(self._L.orbm_search_by_sim3(self._h, KF1._f, KF2._f, _p(sf1), _p(sf2), len(sf1), *[_p(x) for x in a],
+                                            *[_p(x) for x in b], float(th), _p(out), C.byref(nf)), self._h,
+                "orbm_search_by_sim3")
+        return nf.value, out
+
     # ---- M11: brute-force k-NN ----
     def database(self, rows, row_offset=0):
         return KnnDatabase(self, rows, row_offset)

@@ -218,6 +218,13 @@ void orc_fuse_candidates(int n, const void* kps, const uint8_t* desc, const floa
     FrameView f = makeView(n, kps, desc, bounds);
     fuse_candidates(f, scaleFactors, invSigma2, nq, valid, u, v, level, qdesc, th, chi2Gate != 0, bestIdx, bestDist);
 }
+int orc_search_by_sim3(int n1, const void* kps1, const uint8_t* desc1, const float* bounds1, int n2, const void* kps2,
+                       const uint8_t* desc2, const float* bounds2, const float* sf1, const float* sf2, const uint8_t* valid1,
+                       const float* u12, const float* v12, const int* level12, const uint8_t* qdesc1, const uint8_t* valid2,
+                       const float* u21, const float* v21, const int* level21, const uint8_t* qdesc2, float th, int* matches12) {
+    FrameView f1 = makeView(n1, kps1, desc1, bounds1), f2 = makeView(n2, kps2, desc2, bounds2);
+    return search_by_sim3(f1, f2, sf1, sf2, valid1, u12, v12, level12, qdesc1, valid2, u21, v21, level21, qdesc2, th, matches12);
+}
 void orc_knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads) {
     knn(q, nq, db, ndb, k, dist, idx, threads);
 }

@@ -407,6 +407,46 @@ void fuse_candidates(const FrameView& KF, const float* scaleFactors, const float
     }
 }
 
+// ---- M8: src/ORBmatcher.cc:1457-1674 (no caller in the tree; kept for the class surface) ---------------------------
+// The per-point pre-checks (map point present / not yet matched / not bad, positive depth, IsInImage, distance
+// invariance, PredictScale) are the caller's: valid/u/v/level per keypoint slot of each keyframe.
+static void sim3_one_way(const FrameView& KF, const float* scaleFactors, int nq, const uint8_t* valid, const float* u,
+                         const float* v, const int* level, const uint8_t* qdesc, float th, std::vector<int>& vnMatch) {
+    std::vector<int> vIndices;
+    vnMatch.assign(nq, -1);
+    for (int i = 0; i < nq; i++) {
+        if (!valid[i]) continue;
+        const int nPredictedLevel = level[i];
+        const float radius = th * scaleFactors[nPredictedLevel];
+        KF.features_in_area(u[i], v[i], radius, -1, -1, vIndices);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = qdesc + 32 * (size_t)i;
+        int bestDist = INT_MAX, bestIdx = -1;
+        for (int idx : vIndices) {
+            const KP& kp = KF.kps[idx];
+            if (kp.octave < nPredictedLevel - 1 || kp.octave > nPredictedLevel) continue;
+            const int dist = descriptor_distance(dMP, KF.desc + 32 * (size_t)idx);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= TH_HIGH) vnMatch[i] = bestIdx;
+    }
+}
+int search_by_sim3(const FrameView& K1, const FrameView& K2, const float* scaleFactors1, const float* scaleFactors2,
+                   const uint8_t* valid1, const float* u12, const float* v12, const int* level12, const uint8_t* qdesc1,
+                   const uint8_t* valid2, const float* u21, const float* v21, const int* level21, const uint8_t* qdesc2, float th,
+                   int* matches12) {
+    std::vector<int> vnMatch1, vnMatch2;
+    sim3_one_way(K2, scaleFactors2, K1.n, valid1, u12, v12, level12, qdesc1, th, vnMatch1);   // KF1 points into KF2
+    sim3_one_way(K1, scaleFactors1, K2.n, valid2, u21, v21, level21, qdesc2, th, vnMatch2);   // KF2 points into KF1
+    int nFound = 0;
+    for (int i1 = 0; i1 < K1.n; i1++) {
+        matches12[i1] = -1;
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { matches12[i1] = idx2; nFound++; }
+    }
+    return nFound;
+}
+
 // ---- M11: brute-force k-NN, strict '<' scan order => ties go to the lowest row --------------------------------------
 static inline int popdist(const uint64_t* a, const uint64_t* b) {
     return __builtin_popcountll(a[0] ^ b[0]) + __builtin_popcountll(a[1] ^ b[1]) +

@@ -91,6 +91,15 @@ void fuse_candidates(const FrameView& KF, const float* scaleFactors, const float
                      const uint8_t* valid, const float* u, const float* v, const int* level, const uint8_t* qdesc,
                      float th, bool chi2Gate, int* bestIdx, int* bestDist);
 
+// M8  SearchBySim3 (:1457-1674): bidirectional projection search + mutual agreement.  Query i of direction 1->2 is the
+//     map point of KF1's keypoint i (descriptor row i of `qdesc1`), projected into KF2 at (u12, v12) with predicted
+//     level level12; valid1[i] = it survives the reference's pre-checks (:1500-1531).  matches12[i1] = i2 or -1.
+//     qdesc1 / qdesc2 = MapPoint::GetDescriptor() of each slot (n1 x 32, n2 x 32).
+int search_by_sim3(const FrameView& K1, const FrameView& K2, const float* scaleFactors1, const float* scaleFactors2,
+                   const uint8_t* valid1, const float* u12, const float* v12, const int* level12, const uint8_t* qdesc1,
+                   const uint8_t* valid2, const float* u21, const float* v21, const int* level21, const uint8_t* qdesc2, float th,
+                   int* matches12);
+
 // M11 brute-force k-NN (config 5): per query the k smallest distances, ties -> lowest row
 void knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads);
 

@@ -41,6 +41,7 @@ def _L():
         L.orc_search_triangulation.argtypes = [i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp,
                                                i, i, vp]
         L.orc_fuse_candidates.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, i, vp, vp]
+        L.orc_search_by_sim3.argtypes = [i, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, f, vp]
         L.orc_distinctive_descriptor.argtypes = [vp, i]
         L.orc_undistort_points.argtypes = [vp, i, vp, vp, i, vp]
         L.orc_bow_transform.argtypes = [i, i, vp, vp, vp, vp, vp, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp]
@@ -180,6 +181,20 @@ def fuse_candidates(kps, desc, bounds, scale_factors, inv_sigma2, valid, u, v, l
     _L().orc_fuse_candidates(len(kps), _p(kps), _p(desc), _p(b), _p(sf), _p(is2), len(valid), _p(valid), _p(u), _p(v),
                              _p(level), _p(qd), float(th), int(chi2_gate), _p(bi), _p(bd))
     return bi, bd
+
+
+def search_by_sim3(kps1, desc1, bounds1, kps2, desc2, bounds2, sf1, sf2, valid1, u12, v12, level12, qdesc1, valid2, u21, v21,
+                   level21, qdesc2, th):
+    """M8 SearchBySim3.  Returns (nFound, matches12[n1])."""
+    kps1, desc1, b1 = _kp(kps1), _c(desc1, np.uint8), _bounds(bounds1)
+    kps2, desc2, b2 = _kp(kps2), _c(desc2, np.uint8), _bounds(bounds2)
+    sf1, sf2 = _c(sf1, np.float32), _c(sf2, np.float32)
+    a = [_c(valid1, np.uint8), _c(u12, np.float32), _c(v12, np.float32), _c(level12, np.int32), _c(qdesc1, np.uint8)]
+    b = [_c(valid2, np.uint8), _c(u21, np.float32), _c(v21, np.float32), _c(level21, np.int32), _c(qdesc2, np.uint8)]
+    out = np.full(len(kps1), -1, np.int32)
+    n = _L().orc_search_by_sim3(len(kps1), _p(kps1), _p(desc1), _p(b1), len(kps2), _p(kps2), _p(desc2), _p(b2), _p(sf1), _p(sf2),
+                                *[_p(x) for x in a], *[_p(x) for x in b], float(th), _p(out))
+    return n, out
 
 
 def knn(q, db, k, threads=1):

@@ -1,0 +1,304 @@
+"""GPU: every search / fuse member of the C++ drop-in ORBmatcher (mam3slam_b200/cpp/ORBmatcher.h — the reference's class
+surface, include/ORBmatcher.h:36-103) called the way Tracking / LocalMapping / LoopClosing call it, on mock Frame / KeyFrame /
+MapPoint objects (tests/native/slam_shim.h), against the oracle fed with the flattened inputs computed here in numpy float32.
+The geometry is deliberately simple (identity rotations, K = I, depth 1) so that the projections the adapter computes on the
+host are reproducible bit for bit; what is under test is the adapter's plumbing: pre-checks, occupancy, write-back, the
+order of the Fuse mutations."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import matcher as om
+from tests import matcher_scenarios as sc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+f32 = np.float32
+
+
+def _node_of(desc, bits=5):
+    return (((desc[:, 0].astype(np.int32) ^ (desc[:, 7].astype(np.int32) << 1)) & ((1 << bits) - 1)) * 3 + 5).astype(np.int32)
+
+
+def _fv(node):
+    nodes = np.unique(node)
+    off, idx = [0], []
+    for nd in nodes:
+        idx.extend(np.nonzero(node == nd)[0].tolist())
+        off.append(len(idx))
+    return nodes.astype(np.int32), np.array(off, np.int32), np.array(idx, np.int32)
+
+
+def _scenario():
+    (k1, d1), (k2, d2), bounds, tabs = sc.frame_pair()
+    rng = np.random.default_rng(41)
+    n1, n2 = len(k1), len(k2)
+    t1 = np.zeros(3, f32)
+    t2 = np.array([4.6875, -1.5, 0.015625], f32)          # epipole of KF1 in KF2 at (300, -96)
+    pos, desc, level, src = [], [], [], []
+
+    def add_points(k, d, t, sel, flip):
+        ids = np.full(len(k), -1, np.int32)
+        for i in np.nonzero(sel)[0]:
+            pc = np.array([k["x"][i] + f32(rng.integers(-8, 9)) / f32(8), k["y"][i] + f32(rng.integers(-8, 9)) / f32(8), 1], f32)
+            ids[i] = len(pos)
+            pos.append(pc - t)
+            dd = d[i].copy()
+            dd[rng.random(32) < flip] ^= np.uint8(1 << int(rng.integers(0, 8)))
+            desc.append(dd)
+            level.append(int(np.clip(k["octave"][i] + rng.integers(0, 2), 0, 7)))
+            src.append(i)
+        return ids
+
+    kf1_mp = add_points(k1, d1, t1, rng.random(n1) < 0.7, 0.05)      # set A: seen in KF1
+    kf2_mp = add_points(k2, d2, t2, rng.random(n2) < 0.6, 0.05)      # set B: seen in KF2
+    extra = add_points(k2, d2, t2, rng.random(n2) < 0.5, 0.08)       # set C: near KF2 keypoints, not observed there
+    nmp = len(pos)
+    pos = np.array(pos, f32)
+    normal = np.tile(np.array([0, 0, 1e4], f32), (nmp, 1))
+    normal[rng.random(nmp) < 0.05] = np.array([0, 0, -1], f32)
+    bad = (rng.random(nmp) < 0.05).astype(np.uint8)
+    nobs = rng.integers(0, 6, nmp).astype(np.int32)
+    c_ids = extra[extra >= 0]
+    a_ids = kf1_mp[kf1_mp >= 0]
+    pts = np.concatenate([c_ids, a_ids[::3], np.full(20, -1, np.int32)]).astype(np.int32)
+    rng.shuffle(pts)
+    # tracking fields (Frame::isInFrustum results) for the local-map search: projections near the frame-2 keypoints
+    projx = np.zeros(nmp, f32); projy = np.zeros(nmp, f32)
+    for ids, k in ((kf1_mp, k1), (kf2_mp, k2), (extra, k2)):
+        m = ids >= 0
+        projx[ids[m]] = k["x"][m] + rng.uniform(-2, 2, m.sum()).astype(f32)
+        projy[ids[m]] = k["y"][m] + rng.uniform(-2, 2, m.sum()).astype(f32)
+    S = dict(k1=k1, d1=d1, k2=k2, d2=d2, bounds=np.array(bounds, f32), scale=tabs["scale"].astype(f32),
+             sigma2=tabs["sigma2"].astype(f32), invsigma2=tabs["inv_sigma2"].astype(f32), node1=_node_of(d1), node2=_node_of(d2),
+             mp_pos=pos, mp_normal=normal, mp_level=np.array(level, np.int32), mp_desc=np.array(desc, np.uint8), mp_bad=bad,
+             mp_nobs=nobs, mp_inview=(rng.random(nmp) < 0.85).astype(np.uint8), mp_projx=projx, mp_projy=projy,
+             mp_depth=rng.uniform(1, 60, nmp).astype(f32), mp_viewcos=rng.uniform(0.99, 1.0, nmp).astype(f32),
+             mp_tracklevel=np.array(level, np.int32), kf1_mp=kf1_mp, kf2_mp=kf2_mp, t1=t1, t2=t2, pts=pts,
+             already=a_ids[::5].astype(np.int32), outlier1=(rng.random(n1) < 0.1).astype(np.uint8))
+    m12_init = np.full(n1, -1, np.int32)
+    b_ids = kf2_mp[kf2_mp >= 0]
+    pick = rng.choice(n1, 40, replace=False)
+    m12_init[pick] = rng.choice(b_ids, 40, replace=False)
+    S["m12_init"] = m12_init
+    return S, tabs
+
+
+def _write(S, path):
+    with open(path, "wb") as f:
+        f.write(struct.pack("<i", len(S)))
+        for name, a in S.items():
+            raw = np.ascontiguousarray(a).tobytes()
+            f.write(name.encode().ljust(16, b"\0"))
+            f.write(struct.pack("<q", len(raw)))
+            f.write(raw)
+
+
+def _run(tmp_path, S):
+    exe = os.path.join(str(tmp_path), "matcher_adapter_demo")
+    libdir = os.path.join(ROOT, "mam3slam_b200")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", "-o", exe,
+                           os.path.join(ROOT, "tests", "native", "matcher_adapter_demo.cc"), "-L" + libdir, "-lmam3slam_b200",
+                           "-Wl,-rpath," + libdir])
+    scen = os.path.join(str(tmp_path), "scenario.bin")
+    _write(S, scen)
+    out = subprocess.run([exe, scen], capture_output=True, text=True, check=True).stdout
+    res = {}
+    for line in out.splitlines():
+        p = line.split()
+        res[p[0]] = (int(p[1]), np.array([int(x) for x in p[3:]], np.int64))
+        assert len(res[p[0]][1]) == int(p[2])
+    return res
+
+
+def _proj(pos, t):
+    pc = pos + t
+    return pc[:, 0] / pc[:, 2], pc[:, 1] / pc[:, 2], pc
+
+
+def test_matcher_adapter_compiles(tmp_path):
+    """CPU: the full class surface builds as C++14 against the shims and links against the C ABI."""
+    exe = os.path.join(str(tmp_path), "mad")
+    libdir = os.path.join(ROOT, "mam3slam_b200")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", "-o", exe,
+                           os.path.join(ROOT, "tests", "native", "matcher_adapter_demo.cc"), "-L" + libdir, "-lmam3slam_b200",
+                           "-Wl,-rpath," + libdir])
+
+
+@pytest.mark.gpu
+def test_matcher_adapter_every_member(tmp_path):
+    S, tabs = _scenario()
+    R = _run(tmp_path, S)
+    k1, d1, k2, d2, bounds = S["k1"], S["d1"], S["k2"], S["d2"], tuple(S["bounds"])
+    scale, n1, n2 = S["scale"], len(S["k1"]), len(S["k2"])
+    kf1, kf2, pts = S["kf1_mp"], S["kf2_mp"], S["pts"]
+    pos, lvl, mdesc, bad, nobs = S["mp_pos"], S["mp_level"], S["mp_desc"], S["mp_bad"].astype(bool), S["mp_nobs"]
+    t1, t2 = S["t1"], S["t2"]
+    local = pts[pts >= 0]
+    in_bounds = lambda u, v: (u >= bounds[0]) & (u <= bounds[2]) & (v >= bounds[1]) & (v <= bounds[3])      # Frame tests
+    in_image = lambda u, v: (u >= bounds[0]) & (u < bounds[2]) & (v >= bounds[1]) & (v < bounds[3])         # KeyFrame::IsInImage
+    occ_obs = ((kf2 >= 0) & (nobs[np.maximum(kf2, 0)] > 0)).astype(np.uint8)
+
+    # M1 Tracking::SearchLocalPoints
+    valid = (S["mp_inview"][local] != 0) & ~(S["mp_depth"][local] > f32(40)) & ~bad[local]
+    nm, km, _ = om.search_local_map(k2, d2, bounds, occ_obs, scale, valid.astype(np.uint8), S["mp_projx"][local], S["mp_projy"][local],
+                                    S["mp_tracklevel"][local], S["mp_viewcos"][local], mdesc[local], 3.0, 0.8)
+    ret, got = R["local_map"]
+    assert ret == nm and nm > 30 and np.array_equal(got, np.where(km >= 0, local[np.maximum(km, 0)], kf2))
+
+    # M2 Tracking::TrackWithMotionModel
+    q = np.maximum(kf1, 0)
+    u, v, pc = _proj(pos[q], t2)
+    valid = (kf1 >= 0) & (S["outlier1"] == 0) & ~(f32(1) / pc[:, 2] < 0) & in_bounds(u, v)
+    nm, km = om.search_frame(k2, d2, bounds, occ_obs, scale, valid.astype(np.uint8), u, v, k1["octave"], k1["angle"], mdesc[q], 15.0,
+                             100, True)
+    ret, got = R["frame"]
+    assert ret == nm and nm > 50 and np.array_equal(got, np.where(km >= 0, kf1[np.maximum(km, 0)], kf2))
+
+    # M3 Tracking::Relocalization
+    valid = (kf1 >= 0) & ~bad[q] & ~np.isin(kf1, S["already"]) & in_bounds(u, v)
+    nm, km = om.search_frame(k2, d2, bounds, (kf2 >= 0).astype(np.uint8), scale, valid.astype(np.uint8), u, v, lvl[q], k1["angle"],
+                             mdesc[q], 10.0, 100, True)
+    ret, got = R["reloc"]
+    assert ret == nm and nm > 20 and np.array_equal(got, np.where(km >= 0, kf1[np.maximum(km, 0)], kf2))
+
+    # M7 LoopClosing: Sim3 projections into KF2 (Tcw = [I | t2])
+    ul, vl, pcl = _proj(pos[local], t2)
+    visible = (pcl[:, 2] >= 0) & in_image(ul, vl) & (S["mp_normal"][local, 2] > 0)
+    valid = ~bad[local] & ~np.isin(local, kf2[kf2 >= 0]) & visible
+    for name, ratio in (("sim3proj", 1.5), ("sim3proj_kfs", 1.0)):
+        nm, km = om.search_sim3(k2, d2, bounds, (kf2 >= 0).astype(np.uint8), scale, valid.astype(np.uint8), ul, vl, lvl[local],
+                                mdesc[local], 4, ratio)
+        ret, got = R[name]
+        assert ret == nm and nm > 20 and np.array_equal(got[:n2], np.where(km >= 0, local[np.maximum(km, 0)], kf2))
+        if name == "sim3proj_kfs":
+            assert np.array_equal(got[n2:], np.where(km >= 0, np.where(km % 2 == 1, 1, 2), 0))
+
+    # M4 SearchByBoW
+    fv1, fv2 = _fv(S["node1"]), _fv(S["node2"])
+    e1 = ((kf1 >= 0) & ~bad[q]).astype(np.uint8)
+    q2 = np.maximum(kf2, 0)
+    e2 = ((kf2 >= 0) & ~bad[q2]).astype(np.uint8)
+    nm, mf = om.search_bow_kf_frame(k1, d1, fv1, e1, k2, d2, fv2, 0.7, True)
+    ret, got = R["bow_kf_f"]
+    assert ret == nm and nm > 20 and np.array_equal(got, np.where(mf >= 0, kf1[np.maximum(mf, 0)], -1))
+    nm, m12 = om.search_bow_kf_kf(k1, d1, fv1, e1, k2, d2, fv2, e2, 0.7, True)
+    ret, got = R["bow_kf_kf"]
+    assert ret == nm and nm > 10 and np.array_equal(got, np.where(m12 >= 0, kf2[np.maximum(m12, 0)], -1))
+
+    # M5 Tracking::MonocularInitialization
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(f32)
+    nm, m12, prev_after = om.search_initialization(k1, d1, k2, d2, bounds, prev, 100, 0.9, True)
+    ret, got = R["init"]
+    assert ret == nm and nm > 20 and np.array_equal(got[:n1], m12)
+    assert np.array_equal(got[n1:].astype(np.int32), np.ascontiguousarray(prev_after, f32).view(np.int32).reshape(-1))
+
+    # M6 LocalMapping::CreateNewMapPoints
+    c2 = (-t1) + t2
+    ep = np.array([c2[0] / c2[2], c2[1] / c2[2]], f32)
+    t12 = (-t2) + t1
+    F12 = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]], f32)
+    free1, free2 = (kf1 < 0).astype(np.uint8), (kf2 < 0).astype(np.uint8)
+    for name, coarse in (("tri", False), ("tri_coarse", True)):
+        nm, m12 = om.search_triangulation(k1, d1, fv1, free1, k2, d2, fv2, free2, ep, scale, F12, S["sigma2"], coarse, False)
+        ret, got = R[name]
+        i1 = np.nonzero(m12 >= 0)[0]
+        assert ret == nm and np.array_equal(got, np.stack([i1, m12[i1]], 1).reshape(-1))
+        assert nm > (5 if coarse else 0)
+    assert R["tri_stereo"][0] == 0 and R["tri_stereo"][1][0] == 0
+
+    # M8 SearchBySim3
+    t12s = t1 - t2
+    t21s = -t12s
+    init = S["m12_init"]
+    already1 = init >= 0
+    already2 = np.zeros(n2, bool)
+    slot_in_kf2 = {int(m): i for i, m in enumerate(kf2) if m >= 0}
+    for m in init[init >= 0]:
+        already2[slot_in_kf2[int(m)]] = True
+
+    def one_dir(kf, alr, t_own, t_rel):
+        qq = np.maximum(kf, 0)
+        p_other = (pos[qq] + t_own) + t_rel
+        invz = (1.0 / p_other[:, 2].astype(np.float64)).astype(f32)
+        uu, vv = p_other[:, 0] * invz, p_other[:, 1] * invz
+        ok = (kf >= 0) & ~alr & ~bad[qq] & ~(p_other[:, 2] < 0) & in_image(uu, vv)
+        return ok.astype(np.uint8), uu, vv, lvl[qq], mdesc[qq]
+
+    a = one_dir(kf1, already1, t1, t21s)
+    b = one_dir(kf2, already2, t2, t12s)
+    nf, m12 = om.search_by_sim3(k1, d1, bounds, k2, d2, bounds, scale, scale, *a, *b, 7.5)
+    ret, got = R["sim3mutual"]
+    assert ret == nf and nf > 10 and np.array_equal(got, np.where(m12 >= 0, kf2[np.maximum(m12, 0)], init))
+
+    # M9 LocalMapping::SearchInNeighbors — candidates from the oracle, mutations replayed in order
+    pq = np.maximum(pts, 0)
+    up, vp, pcp = _proj(pos[pq], t2)
+    geom = (pts >= 0) & (pcp[:, 2] >= 0) & in_image(up, vp) & (S["mp_normal"][pq, 2] > 0)
+    bi, bd = om.fuse_candidates(k2, d2, bounds, scale, S["invsigma2"], geom.astype(np.uint8), up, vp, lvl[pq], mdesc[pq], 3.0, True)
+    slots1, slots2 = kf1.copy(), kf2.copy()
+    obs = [dict() for _ in range(len(pos))]              # mp -> {kf number: slot}
+    for i, m in enumerate(kf1):
+        if m >= 0: obs[m][1] = i
+    for i, m in enumerate(kf2):
+        if m >= 0: obs[m][2] = i
+    isbad, no = bad.copy(), nobs.copy()
+    slots = {1: slots1, 2: slots2}
+    events, nfused = [], 0
+
+    def replace(a_, b_):
+        events.extend([ord("R"), a_, b_])
+        isbad[a_] = True
+        for kfn, idx in sorted(obs[a_].items()):
+            if kfn not in obs[b_]:
+                slots[kfn][idx] = b_; obs[b_][kfn] = idx; no[b_] += 1
+            else:
+                slots[kfn][idx] = -1
+        obs[a_] = {}
+        no[a_] = 0
+
+    for i, m in enumerate(pts):
+        if m < 0 or isbad[m] or 2 in obs[m]:
+            continue
+        if not geom[i] or bi[i] < 0 or bd[i] > 50:
+            continue
+        inkf = slots2[bi[i]]
+        if inkf >= 0:
+            if not isbad[inkf]:
+                if no[inkf] > no[m]: replace(m, inkf)
+                else: replace(inkf, m)
+        else:
+            obs[m][2] = int(bi[i]); no[m] += 1
+            events.extend([ord("A"), m, int(bi[i])])
+            slots2[bi[i]] = m
+            events.extend([ord("M"), m, int(bi[i])])
+        nfused += 1
+    ret, got = R["fuse"]
+    assert ret == nfused and nfused > 30 and np.array_equal(got, slots2)
+    assert np.array_equal(R["fuse_events"][1], np.array(events, np.int64))
+    assert ord("R") in events and ord("A") in events
+
+    # M9 LoopClosing::SearchAndFuse
+    in_kf2 = kf2[(kf2 >= 0) & ~bad[q2]]
+    valid = ~bad[local] & ~np.isin(local, in_kf2) & visible
+    bi, bd = om.fuse_candidates(k2, d2, bounds, scale, S["invsigma2"], valid.astype(np.uint8), ul, vl, lvl[local], mdesc[local], 4.0,
+                                False)
+    slots2 = kf2.copy()
+    repl = np.full(len(local), -1, np.int64)
+    events, nfused = [], 0
+    for i, m in enumerate(local):
+        if not valid[i] or bi[i] < 0 or bd[i] > 50:
+            continue
+        inkf = slots2[bi[i]]
+        if inkf >= 0:
+            if not bad[inkf]:
+                repl[i] = inkf
+        else:
+            events.extend([ord("A"), m, int(bi[i]), ord("M"), m, int(bi[i])])
+            slots2[bi[i]] = m
+        nfused += 1
+    ret, got = R["fuse_sim3"]
+    assert ret == nfused and nfused > 30 and np.array_equal(got, repl)
+    assert np.array_equal(R["fuse_sim3_events"][1], np.array(events, np.int64))

@@ -185,6 +185,31 @@ def test_fuse_candidates(M, pair):
     KF.close()
 
 
+def test_search_by_sim3(M, pair):
+    """M8: both projection directions, TH_HIGH acceptance, mutual agreement."""
+    (k1, d1), (k2, d2), bounds, tabs = pair
+    rng = np.random.default_rng(23)
+    n1, n2 = len(k1), len(k2)
+    # map-point descriptors = the keypoint's own row with a few bits flipped; projections = jittered keypoint positions
+    q1, q2 = d1.copy(), d2.copy()
+    q1[rng.random(q1.shape) < 0.02] ^= 0x10
+    q2[rng.random(q2.shape) < 0.02] ^= 0x04
+    u12, v12 = _jitter(k1["x"], 31, 2), _jitter(k1["y"], 32, 2)
+    u21, v21 = _jitter(k2["x"], 33, 2), _jitter(k2["y"], 34, 2)
+    l12 = np.clip(k1["octave"] + rng.integers(0, 2, n1), 0, 7).astype(np.int32)
+    l21 = np.clip(k2["octave"] + rng.integers(0, 2, n2), 0, 7).astype(np.int32)
+    v1 = (rng.random(n1) < 0.85).astype(np.uint8)
+    v2 = (rng.random(n2) < 0.85).astype(np.uint8)
+    K1, K2 = M.frame(k1, d1, bounds), M.frame(k2, d2, bounds)
+    for th in (7.5, 12.0):
+        nf, m12 = M.SearchBySim3(K1, K2, tabs["scale"], tabs["scale"], v1, u12, v12, l12, q1, v2, u21, v21, l21, q2, th)
+        onf, om12 = om.search_by_sim3(k1, d1, bounds, k2, d2, bounds, tabs["scale"], tabs["scale"], v1, u12, v12, l12, q1, v2,
+                                      u21, v21, l21, q2, th)
+        assert nf == onf and np.array_equal(m12, om12)
+        assert onf > 10
+    K1.close(); K2.close()
+
+
 def test_empty_and_degenerate_inputs(M, pair):
     (k1, d1), (k2, d2), bounds, tabs = pair
     F = M.frame(k2, d2, bounds)

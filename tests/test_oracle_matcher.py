@@ -122,3 +122,39 @@ def test_distinctive_descriptor_vs_numpy():
         D = _popdist(d[:, None, :], d[None, :, :])
         med = np.sort(D, axis=1)[:, int(0.5 * (n - 1))]
         assert om.distinctive_descriptor(d) == int(np.argmin(med))
+
+
+def test_search_by_sim3_vs_numpy():
+    """M8: each direction = first minimum over the window candidates of levels [l-1, l], accepted at <= TH_HIGH; result =
+    mutual agreement.  Restated with numpy on top of the (numpy-pinned) GetFeaturesInArea."""
+    (k1, d1), (k2, d2), bounds, tabs = sc.frame_pair()
+    rng = np.random.default_rng(29)
+    n1, n2 = len(k1), len(k2)
+    l12 = np.clip(k1["octave"] + rng.integers(0, 2, n1), 0, 7).astype(np.int32)
+    l21 = np.clip(k2["octave"] + rng.integers(0, 2, n2), 0, 7).astype(np.int32)
+    v1 = (rng.random(n1) < 0.9).astype(np.uint8)
+    v2 = (rng.random(n2) < 0.9).astype(np.uint8)
+    th = 9.0
+
+    def one_way(kq, dq, valid, lev, kt, dt):
+        out = np.full(len(kq), -1)
+        for i in range(len(kq)):
+            if not valid[i]:
+                continue
+            r = np.float32(th) * tabs["scale"][lev[i]]
+            cand = om.features_in_area(kt, bounds, float(kq["x"][i]), float(kq["y"][i]), float(r), -1, -1)
+            cand = cand[(kt["octave"][cand] >= lev[i] - 1) & (kt["octave"][cand] <= lev[i])]
+            if len(cand) == 0:
+                continue
+            dist = _popdist(dt[cand], dq[i][None, :])
+            j = int(np.argmin(dist))                  # first minimum
+            if dist[j] <= 100:
+                out[i] = cand[j]
+        return out
+
+    m1 = one_way(k1, d1, v1, l12, k2, d2)
+    m2 = one_way(k2, d2, v2, l21, k1, d1)
+    want = np.array([m1[i] if m1[i] >= 0 and m2[m1[i]] == i else -1 for i in range(n1)])
+    nf, m12 = om.search_by_sim3(k1, d1, bounds, k2, d2, bounds, tabs["scale"], tabs["scale"], v1, k1["x"], k1["y"], l12, d1, v2,
+                                k2["x"], k2["y"], l21, d2, th)
+    assert np.array_equal(m12, want) and nf == (want >= 0).sum() and nf > 20
