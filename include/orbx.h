@@ -95,6 +95,15 @@ int orbx_results_batch_device(orbx_handle h, const orbx_keypoint** d_kps, const 
 int orbx_fetch_results(orbx_handle h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
                        int* mono_index_out);
 
+/* replaces Frame::ComputeStereoMatches (src/Frame.cc:811-981; SURVEY.md 8f rank 4 — the product is monocular, the stereo
+ * constructor is kept for completeness): `left` / `right` are the two extractor objects of Frame's stereo constructor
+ * (src/Frame.cc:122-125), each holding the single frame of its last orbx_extract (keypoints, descriptors and
+ * mvImagePyramid stay device-resident).  mb = baseline in metres, mbf = baseline * fx.  u_right / depth (HOST, cap floats
+ * each) receive mvuRight / mvDepth for the *n_left left keypoints (-1 = no stereo match); *n_kept = matches kept after the
+ * median-SAD outlier filter. */
+int orbx_stereo_matches(orbx_handle left, orbx_handle right, float mb, float mbf, float* u_right, float* depth, int cap,
+                        int* n_left, int* n_kept);
+
 /* replaces the public mvImagePyramid (include/ORBextractor.h:83): level `level` of frame `frame` of the last
  * pass, with (padded != 0) or without the 19-px BORDER_REFLECT_101 ring.  dst_stride in bytes. */
 int orbx_level_size(orbx_handle h, int level, int* width, int* height);

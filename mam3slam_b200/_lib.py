@@ -48,6 +48,7 @@ def lib():
     L.orbx_results_batch_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), ip]
     L.orbx_fetch_results.argtypes = [vp, i32, vp, vp, i32, ip, ip]
     L.orbx_level_size.argtypes = [vp, i32, ip, ip]
+    L.orbx_stereo_matches.argtypes = [vp, vp, f32, f32, vp, vp, i32, ip, ip]
     L.orbx_download_level.argtypes = [vp, i32, i32, i32, vp, i32]
     L.orbx_download_blurred.argtypes = [vp, i32, i32, vp, i32]
     L.orbx_download_candidates.argtypes = [vp, i32, i32, vp, i32, ip]

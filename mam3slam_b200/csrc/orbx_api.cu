@@ -1,6 +1,7 @@
 // C ABI of the B200-native ORB extractor: handle management, geometry tables, launch sequence.
 // Host-side logic mirrors ORBextractor's constructor and operator() (src/ORBextractor.cc:409-469, 1086-1168).
 #include "orbx_kernels_desc.cuh"
+#include "orbx_kernels_stereo.cuh"
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -849,6 +850,48 @@ int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int 
         out[3 * i] = (int)(res[i] & 0xffff); out[3 * i + 1] = (int)((res[i] >> 16) & 0xffff); out[3 * i + 2] = (int)((res[i] >> 32) & 0xff);
     }
     return ORBX_OK;
+}
+
+// Frame::ComputeStereoMatches (src/Frame.cc:811-981)
+int orbx_stereo_matches(orbx_handle left, orbx_handle right, float mb, float mbf, float* u_right, float* depth, int cap,
+                        int* n_left, int* n_kept) {
+    if (!left || !right || !u_right || !depth || !n_left || !n_kept || !(mb > 0.f)) return ORBX_ERR_INVALID;
+    Extractor* EL = static_cast<Extractor*>(left);
+    Extractor* ER = static_cast<Extractor*>(right);
+    Extractor* E = EL;
+    if (EL->device != ER->device || EL->lastFrames < 1 || ER->lastFrames < 1 || EL->cfg.nlevels != ER->cfg.nlevels ||
+        EL->cfg.scale_factor != ER->cfg.scale_factor) {
+        EL->err = "orbx_stereo_matches: both extractors must hold one extracted frame, on the same device, with the same pyramid";
+        return ORBX_ERR_INVALID;
+    }
+    CK(cudaSetDevice(EL->device));
+    CK(cudaStreamSynchronize(ER->stream));
+    const int L = EL->cfg.nlevels, outCap = EL->geom.outCap;
+    StereoParams P;
+    for (int l = 0; l < L; ++l) { P.scale[l] = EL->scale[l]; P.invScale[l] = EL->invScale[l]; P.colsR[l] = ER->geom.lv[l].w; }
+    P.mb = mb; P.mbf = mbf;
+    float* dU = nullptr;                       // uRight | depth | sad | kept
+    CK(cudaMalloc((void**)&dU, (size_t)outCap * 12 + 16));
+    float* dD = dU + outCap;
+    int* dSad = (int*)(dD + outCap);
+    int* dKept = dSad + outCap;
+    k_stereo_search<<<(outCap + kStereoWarps - 1) / kStereoWarps, kStereoWarps * 32, 0, EL->stream>>>(
+        EL->dGeom, EL->lastL0, ER->dGeom, ER->lastL0, EL->dOutKp, (const uint32_t*)EL->dOutDesc, EL->dOutCnt, ER->dOutKp,
+        (const uint32_t*)ER->dOutDesc, ER->dOutCnt, P, dU, dD, dSad);
+    k_stereo_filter<<<1, 1024, 0, EL->stream>>>(EL->dOutCnt, dSad, dU, dD, dKept);
+    EL->launches += 2;
+    int hn[2] = {0, 0};
+    cudaError_t e = cudaMemcpyAsync(&hn[0], EL->dOutCnt, 4, cudaMemcpyDeviceToHost, EL->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&hn[1], dKept, 4, cudaMemcpyDeviceToHost, EL->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(EL->stream);
+    if (e == cudaSuccess && hn[0] <= cap && hn[0] > 0) {
+        e = cudaMemcpy(u_right, dU, (size_t)hn[0] * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(depth, dD, (size_t)hn[0] * 4, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(dU);
+    CK(e);
+    *n_left = hn[0]; *n_kept = hn[1];
+    return hn[0] <= cap ? ORBX_OK : ORBX_ERR_CAPACITY;
 }
 
 long long orbx_launch_count(orbx_handle h) { return h ? static_cast<Extractor*>(h)->launches : 0; }

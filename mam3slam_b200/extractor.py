@@ -231,3 +231,15 @@ class ORBextractor:
         ms = np.zeros(7, np.float32)
         check(self._L.orbx_stage_times(self._h, _p(ms)), self._h, "orbx_stage_times")
         return dict(zip(["pyramid", "fast", "octree", "blur", "finalize", "orient_brief", "total"], ms.tolist()))
+
+
+def ComputeStereoMatches(left, right, mb, mbf):
+    """Frame::ComputeStereoMatches (reference src/Frame.cc:811-981) on the device-resident results of the two extractor
+    objects of a stereo Frame (each after one single-frame call).  Returns (kept, mvuRight[N], mvDepth[N])."""
+    cap = left._cap()
+    ur = np.empty(cap, np.float32)
+    dp = np.empty(cap, np.float32)
+    n, kept = C.c_int(0), C.c_int(0)
+    check(left._L.orbx_stereo_matches(left._h, right._h, float(mb), float(mbf), _p(ur), _p(dp), cap, C.byref(n), C.byref(kept)),
+          left._h, "orbx_stereo_matches")
+    return kept.value, ur[:n.value].copy(), dp[:n.value].copy()

@@ -82,3 +82,14 @@ def stream(w=752, h=480, seed=0, nframes=8):
             rot = float(np.clip(rot + rng.normal(0, 0.5), -2, 2))
         out[t] = warp(base, w, h, dx, dy, rot) if t else base[64:64 + h, 64:64 + w]
     return out
+
+
+def stereo_pair(w=752, h=480, seed=0, disparity=17.3, noise=2):
+    """(left, right) of a rectified pair: the right image sees the base texture shifted by a sub-pixel disparity (a
+    fronto-parallel plane) plus a little sensor noise, so that Frame::ComputeStereoMatches has matches to refine."""
+    base = base_texture(w, h, seed)
+    left = np.ascontiguousarray(base[64:64 + h, 64:64 + w])
+    right = warp(base, w, h, float(disparity), 0.0, 0.0).astype(np.int16)
+    rng = np.random.Generator(np.random.PCG64(seed + 7919))
+    right += rng.integers(-noise, noise + 1, right.shape, dtype=np.int16)
+    return left, np.clip(right, 0, 255).astype(np.uint8)

@@ -225,6 +225,12 @@ int orc_search_by_sim3(int n1, const void* kps1, const uint8_t* desc1, const flo
     FrameView f1 = makeView(n1, kps1, desc1, bounds1), f2 = makeView(n2, kps2, desc2, bounds2);
     return search_by_sim3(f1, f2, sf1, sf2, valid1, u12, v12, level12, qdesc1, valid2, u21, v21, level21, qdesc2, th, matches12);
 }
+int orc_stereo_matches(int N, const void* kL, const uint8_t* dL, int Nr, const void* kR, const uint8_t* dR, int nlevels,
+                       const uint8_t* const* pyrL, const int* strideL, const uint8_t* const* pyrR, const int* strideR,
+                       const int* colsR, const float* sf, const float* isf, float mb, float mbf, float* uRight, float* depth) {
+    return stereo_matches(N, (const KP*)kL, dL, Nr, (const KP*)kR, dR, nlevels, pyrL, strideL, pyrR, strideR, colsR, sf, isf, mb,
+                          mbf, uRight, depth);
+}
 void orc_knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads) {
     knn(q, nq, db, ndb, k, dist, idx, threads);
 }

@@ -447,6 +447,104 @@ int search_by_sim3(const FrameView& K1, const FrameView& K2, const float* scaleF
     return nFound;
 }
 
+// ---- 8(f) rank 4: Frame::ComputeStereoMatches (src/Frame.cc:811-981) ------------------------------------------------
+// mvImagePyramid[l] of each extractor is given as a plain plane (the level ROI; every access below stays inside it for
+// keypoints the extractor can produce: >= 16 level-pixels from the border).  cv::norm(IL, IR, NORM_L1) on 8-bit windows is
+// an exact integer sum.  The row table vRowIndices is not materialised: its row `vL` lists, in ascending iR, exactly the
+// right keypoints with floor(y - r) <= (int)vL <= ceil(y + r), r = 2 * scale[octave] (:825-838).
+int stereo_matches(int N, const KP* keysL, const uint8_t* descL, int Nr, const KP* keysR, const uint8_t* descR, int nlevels,
+                   const uint8_t* const* pyrL, const int* strideL, const uint8_t* const* pyrR, const int* strideR,
+                   const int* colsR, const float* scaleFactors, const float* invScaleFactors, float mb, float mbf,
+                   float* mvuRight, float* mvDepth) {
+    (void)nlevels;
+    for (int i = 0; i < N; i++) { mvuRight[i] = -1.0f; mvDepth[i] = -1.0f; }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const float minZ = mb;
+    const float minD = 0;
+    const float maxD = mbf / minZ;
+    std::vector<std::pair<int, int>> vDistIdx;
+    vDistIdx.reserve(N);
+    for (int iL = 0; iL < N; iL++) {
+        const KP& kpL = keysL[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y;
+        const float uL = kpL.x;
+        const int row = (int)vL;                                    // vRowIndices[vL]
+        const float minU = uL - maxD;
+        const float maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH;
+        size_t bestIdxR = 0;
+        const uint8_t* dL = descL + 32 * (size_t)iL;
+        for (int iR = 0; iR < Nr; iR++) {
+            const KP& kpR = keysR[iR];
+            const float r = 2.0f * scaleFactors[kpR.octave];
+            const int maxr = (int)std::ceil(kpR.y + r);
+            const int minr = (int)std::floor(kpR.y - r);
+            if (row < minr || row > maxr) continue;                 // iR is not in vRowIndices[row]
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = descriptor_distance(dL, descR + 32 * (size_t)iR);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            const float uR0 = keysR[bestIdxR].x;
+            const float scaleFactor = invScaleFactors[kpL.octave];
+            const float scaleduL = std::round(kpL.x * scaleFactor);
+            const float scaledvL = std::round(kpL.y * scaleFactor);
+            const float scaleduR0 = std::round(uR0 * scaleFactor);
+            const int w = 5;
+            const uint8_t* IL = pyrL[kpL.octave] + (size_t)((int)(scaledvL - w)) * strideL[kpL.octave] + (int)(scaleduL - w);
+            int bestDistS = INT_MAX;
+            int bestincR = 0;
+            const int L = 5;
+            float vDists[2 * 5 + 1];
+            const float iniu = scaleduR0 + L - w;
+            const float endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= colsR[kpL.octave]) continue;
+            for (int incR = -L; incR <= +L; incR++) {
+                const uint8_t* IR = pyrR[kpL.octave] + (size_t)((int)(scaledvL - w)) * strideR[kpL.octave] +
+                                    (int)(scaleduR0 + incR - w);
+                long sum = 0;
+                for (int y = 0; y < 2 * w + 1; y++)
+                    for (int x = 0; x < 2 * w + 1; x++)
+                        sum += std::abs((int)IL[y * strideL[kpL.octave] + x] - (int)IR[y * strideR[kpL.octave] + x]);
+                const float dist = (float)(double)sum;
+                if (dist < bestDistS) { bestDistS = dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1];
+            const float dist2 = vDists[L + bestincR];
+            const float dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = scaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+                mvDepth[iL] = mbf / disparity;
+                mvuRight[iL] = bestuR;
+                vDistIdx.push_back(std::pair<int, int>(bestDistS, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return 0;                                  // the reference would index an empty vector here
+    std::sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    int kept = (int)vDistIdx.size();
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist) break;
+        mvuRight[vDistIdx[i].second] = -1;
+        mvDepth[vDistIdx[i].second] = -1;
+        kept--;
+    }
+    return kept;
+}
+
 // ---- M11: brute-force k-NN, strict '<' scan order => ties go to the lowest row --------------------------------------
 static inline int popdist(const uint64_t* a, const uint64_t* b) {
     return __builtin_popcountll(a[0] ^ b[0]) + __builtin_popcountll(a[1] ^ b[1]) +

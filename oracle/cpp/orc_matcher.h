@@ -100,6 +100,14 @@ int search_by_sim3(const FrameView& K1, const FrameView& K2, const float* scaleF
                    const uint8_t* valid2, const float* u21, const float* v21, const int* level21, const uint8_t* qdesc2, float th,
                    int* matches12);
 
+// 8(f) rank 4: Frame::ComputeStereoMatches (src/Frame.cc:811-981).  pyrL / pyrR = mvImagePyramid of the left / right
+// extractor as plain planes (nlevels pointers + row strides), colsR = widths of the right levels.  Writes mvuRight /
+// mvDepth (N floats each, -1 = no match); returns the number of stereo matches kept.
+int stereo_matches(int N, const KP* keysL, const uint8_t* descL, int Nr, const KP* keysR, const uint8_t* descR, int nlevels,
+                   const uint8_t* const* pyrL, const int* strideL, const uint8_t* const* pyrR, const int* strideR,
+                   const int* colsR, const float* scaleFactors, const float* invScaleFactors, float mb, float mbf,
+                   float* mvuRight, float* mvDepth);
+
 // M11 brute-force k-NN (config 5): per query the k smallest distances, ties -> lowest row
 void knn(const uint8_t* q, int nq, const uint8_t* db, long ndb, int k, uint16_t* dist, int32_t* idx, int threads);
 

@@ -42,6 +42,7 @@ def _L():
                                                i, i, vp]
         L.orc_fuse_candidates.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, f, i, vp, vp]
         L.orc_search_by_sim3.argtypes = [i, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, f, vp]
+        L.orc_stereo_matches.argtypes = [i, vp, vp, i, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, f, f, vp, vp]
         L.orc_distinctive_descriptor.argtypes = [vp, i]
         L.orc_undistort_points.argtypes = [vp, i, vp, vp, i, vp]
         L.orc_bow_transform.argtypes = [i, i, vp, vp, vp, vp, vp, i, i, vp, i, i, vp, vp, vp, vp, vp, vp, vp, vp, vp]
@@ -195,6 +196,22 @@ def search_by_sim3(kps1, desc1, bounds1, kps2, desc2, bounds2, sf1, sf2, valid1,
     n = _L().orc_search_by_sim3(len(kps1), _p(kps1), _p(desc1), _p(b1), len(kps2), _p(kps2), _p(desc2), _p(b2), _p(sf1), _p(sf2),
                                 *[_p(x) for x in a], *[_p(x) for x in b], float(th), _p(out))
     return n, out
+
+
+def stereo_matches(kpsL, descL, kpsR, descR, pyrL, pyrR, scale, inv_scale, mb, mbf):
+    """Frame::ComputeStereoMatches.  pyrL / pyrR: lists of 2-D uint8 level planes.  Returns (kept, mvuRight[N], mvDepth[N])."""
+    kpsL, descL, kpsR, descR = _kp(kpsL), _c(descL, np.uint8), _kp(kpsR), _c(descR, np.uint8)
+    pl = [np.ascontiguousarray(a, np.uint8) for a in pyrL]
+    pr = [np.ascontiguousarray(a, np.uint8) for a in pyrR]
+    n = len(pl)
+    ptr = lambda planes: (C.c_void_p * n)(*[a.ctypes.data for a in planes])
+    sl = np.array([a.shape[1] for a in pl], np.int32)
+    sr = np.array([a.shape[1] for a in pr], np.int32)
+    sf, isf = _c(scale, np.float32), _c(inv_scale, np.float32)
+    ur = np.empty(len(kpsL), np.float32); dp = np.empty(len(kpsL), np.float32)
+    kept = _L().orc_stereo_matches(len(kpsL), _p(kpsL), _p(descL), len(kpsR), _p(kpsR), _p(descR), n, ptr(pl), _p(sl), ptr(pr),
+                                   _p(sr), _p(sr), _p(sf), _p(isf), float(mb), float(mbf), _p(ur), _p(dp))
+    return kept, ur, dp
 
 
 def knn(q, db, k, threads=1):
