@@ -155,3 +155,8 @@ def check(status, handle=None, what=""):
         if detail:
             msg += ": " + detail
     raise NativeError(f"{what} failed ({status}): {msg}")
+
+
+def device_count():
+    """Number of CUDA devices the library sees (0 on a CPU-only host)."""
+    return int(lib().orbx_device_count())
