@@ -159,7 +159,7 @@ def run_reference(args):
                                        "each), oracle/cpp restatement of ORBextractor + SearchByProjection (reference needs "
                                        "OpenCV C++/Eigen: not buildable here)"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def knn_bench(args, torch, dist, rank, world, local):
@@ -422,7 +422,7 @@ def run_gpu(args):
             line["cpu_baseline"] = {"value": n / wall, "unit": "frames/s", "cores": 1, "kind": "port",
                                     "sample": f"{n} frames of the same stream (extraction + SearchByProjection), 1 thread, "
                                               "oracle/cpp restatement"}
-        print(json.dumps(line))
+        emit(line)
     ex.close(); mt.close()
     if world > 1:
         dist.destroy_process_group()
@@ -463,7 +463,24 @@ def stage_algorithmic_bytes(nkp, evals_per_frame=20000.0):
     }
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else written to fd 1 while the bench runs (e.g.
+    the "NCCL version ..." banner NCCL prints on communicator creation) has been diverted to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
