@@ -162,6 +162,80 @@ def run_reference(args):
     emit(line)
 
 
+def kitti_bench(args, torch, dist, rank, world, local):
+    """BASELINE config 3: KITTI-shaped 1241x376 frames, 2000 kp: device-resident extraction of 32 frames per step, and
+    SearchForTriangulation (LocalMapping::CreateNewMapPoints: ratio 0.6, no orientation check) on keyframe pairs (t, t+5)
+    through the host-buffer C ABI.  BoW node ids are a hash of descriptor bits (the ORB vocabulary file is absent from the
+    reference checkout).  Returns a dict for the JSON line."""
+    from mam3slam_b200 import ORBextractor, ORBmatcher, synth
+    KW, KH, KN, KB = 1241, 376, 2000, 32
+    frames = synth.stream(KW, KH, 100 + rank, 8)
+    host = np.concatenate([np.roll(frames, 5 * r, axis=2) for r in range(KB // len(frames))])
+    dev = torch.from_numpy(host).cuda()
+    ex = ORBextractor(KN, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=KB)
+    ts = torch.cuda.Stream()
+    def step():
+        ex.extract_device(dev.data_ptr(), KW * KH, KB, KW, KH, KW, (0, 1000), ts.cuda_stream)
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 10
+    e0.record(ts)
+    for _ in range(iters):
+        step()
+    e1.record(ts)
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    res = [ex.fetch(f) for f in range(8)]                   # (mono, keypoints, descriptors) of the 8 distinct frames
+    nkp = float(np.mean([len(r[1]) for r in res]))
+    # keyframe pairs (t, t+5): unmatched keypoints (60 %) searched under a sideways-translation epipolar geometry
+    m = ORBmatcher(0.6, False, device=local)
+    bounds = (0.0, 0.0, float(KW), float(KH))
+    sf = ex.GetScaleFactors()
+    sig2 = ex.GetScaleSigmaSquares()
+    rng = np.random.default_rng(5)
+    def featvec(desc):
+        node = ((desc[:, 0].astype(np.int32) ^ (desc[:, 7].astype(np.int32) << 1)) & 63) * 3 + 5
+        nodes = np.unique(node)
+        order = np.argsort(node, kind="stable")
+        off = np.concatenate([[0], np.cumsum([(node == nd).sum() for nd in nodes])]).astype(np.int32)
+        return nodes.astype(np.int32), off, order.astype(np.int32)
+    F12 = np.array([[0, 0, 0.02], [0, 0, -1.0], [-0.02, 1.0, 0]], np.float32)
+    ep = np.array([KW * 0.8, KH * 0.5], np.float32)
+    pairs = []
+    for a, b in ((0, 5), (1, 6), (2, 7)):
+        (_, k1, d1), (_, k2, d2) = res[a], res[b]
+        pairs.append((m.frame(k1, d1, bounds), featvec(d1), (rng.random(len(k1)) < 0.6).astype(np.uint8),
+                      m.frame(k2, d2, bounds), featvec(d2), (rng.random(len(k2)) < 0.6).astype(np.uint8)))
+    def tri():
+        tot, ev = 0, 0
+        for K1, fv1, f1, K2, fv2, f2 in pairs:
+            nm, _ = m.SearchForTriangulation(K1, fv1, f1, K2, fv2, f2, ep, sf, F12, sig2 * 9, False)
+            tot += nm; ev += m.last_evaluations()
+        return tot, ev
+    tri()
+    t0 = time.perf_counter()
+    reps = 10
+    for _ in range(reps):
+        nm, ev = tri()
+    dt = (time.perf_counter() - t0) / (reps * len(pairs))
+    out = {"workload": f"KITTI-shaped {KW}x{KH}, {KN} kp: extraction of {KB} device-resident frames per step; SearchForTriangulation "
+                       f"on keyframe pairs (t, t+5), host buffers, synchronous calls",
+           "extract_frames_per_s": KB * world / (ms * 1e-3), "ms_per_step": ms, "keypoints_per_frame": nkp,
+           "triangulation_calls_per_s": world / dt, "triangulation_matches_per_call": nm / len(pairs),
+           "triangulation_evaluations_per_call": ev / len(pairs)}
+    for P in pairs:
+        P[0].close(); P[3].close()
+    m.close(); ex.close()
+    return out
+
+
 def knn_bench(args, torch, dist, rank, world, local):
     """BASELINE config 5: 1 M x 2000 brute-force k-NN (k = 2), database rows sharded over the ranks, per-rank top-k lists
     all-gathered (NCCL) and merged with the (dist, global row) rule.  Returns a dict for the JSON line."""
@@ -384,6 +458,7 @@ def run_gpu(args):
     ms, e2e_ms = tms.tolist()
     total_frames = B * args.steps * world
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
+    kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
     if rank == 0:
         pk, pk_kind = peaks()
         fps = total_frames / (ms * 1e-3)
@@ -415,6 +490,7 @@ def run_gpu(args):
                          "pipeline_alg_gbs": ALG_BYTES_PER_FRAME * fps / 1e9 / world,
                          "pipeline_frac": ALG_BYTES_PER_FRAME * fps / 1e9 / world / pk["hbm_gbs"]},
             "hamming": {"track_evaluations_per_s": track_evals * world / (acc["track"] * 1e-3), "knn": hamming},
+            "kitti": kitti,
         }
         if world == 1 and not args.no_cpu:
             cf = make_frames(0, 8)
@@ -492,6 +568,7 @@ def main():
     ap.add_argument("--pipes", type=int, default=2, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
     ap.add_argument("--e2e-pipes", type=int, default=3, help="host threads (one handle pair each) of the end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-kitti", action="store_true", help="skip the KITTI-shaped leg (config 3)")
     ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
