@@ -510,17 +510,18 @@ NCU_DRAM_BYTES_PER_LAUNCH = {"pyramid": 75.4e6, "fast": 72.8e6, "octree": 14.7e6
 
 
 def fast_alu_roofline(fast_ms, B):
-    """FAST is bound by the min/max network, not by HBM: 79 VIMNMX3.U16x2 per pixel PAIR (tmin/tmax 32, min9/max9 32, the two
-    16-way reductions 15), issued at 64 /clk/SM.  Peak = the rate tools/microbench.cu measured on this B200 pool
-    (profiles/int_peaks_b200.txt: vimin3_u16x2 18417 G/s)."""
+    """FAST is bound by the min/max network, not by HBM.  Per pixel PAIR the strength network issues 48 two-input
+    VIMNMX.U16x2 + 2 (final reduction) and 22 + 1 three-input VIMNMX3.U16x2 = 94 ALU-pipe slots of a two-input op (a
+    three-input op costs two: tools/microbench.cu, profiles/int_peaks_b200.txt: vminu2 36264 G/s, vimin3_u16x2 18417 G/s)."""
     if not fast_ms:
         return None
     lv = [(752, 480), (627, 400), (522, 333), (435, 278), (363, 231), (302, 193), (252, 161), (210, 134)]
     tested = sum((w - 32) * (h - 32) for w, h in lv)          # FAST runs 16 px inside every level (EDGE_THRESHOLD - 3)
-    ops = tested / 2 * 79 * B
+    slots = (50 + 2 * 23) * 1.0
+    ops = tested / 2 * slots * B
     ach = ops / (fast_ms * 1e-3)
-    return {"op": "VIMNMX3.U16x2", "per_pixel_pair": 79, "achieved_ops_per_s": ach, "peak_ops_per_s": 18417.2e9,
-            "frac": ach / 18417.2e9}
+    return {"op": "VIMNMX.U16x2 slots (3-input = 2)", "per_pixel_pair": slots, "instructions_per_pixel_pair": 73,
+            "achieved_ops_per_s": ach, "peak_ops_per_s": 36264.3e9, "frac": ach / 36264.3e9}
 
 
 def stage_algorithmic_bytes(nkp, evals_per_frame=20000.0):

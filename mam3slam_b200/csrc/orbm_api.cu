@@ -1,10 +1,12 @@
 // C ABI of the B200-native ORB matcher (include/orbm.h): handle / frame management, query marshalling, launches.
 // Host-side logic mirrors what each ORBmatcher method does before and after its Hamming loop (src/ORBmatcher.cc).
 #include "orbm_kernels.cuh"
+#include "orbx_internal.h"
 #include <algorithm>
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -38,6 +40,7 @@ struct orbm_matcher {
     long long launches = 0;
     long long lastEvals = 0;
     int smCount = 148;
+    int prio = 0;                    // launch priority of the tracking step (latency-bound; 0 = none)
     // growable device scratch for queries / results
     void* scratch = nullptr; size_t scratchBytes = 0;
     void* pinned = nullptr; size_t pinnedBytes = 0;
@@ -180,6 +183,12 @@ int orbm_create(int device, orbm_handle* out) {
         return ORBM_ERR_CUDA;
     }
     cudaDeviceGetAttribute(&M->smCount, cudaDevAttrMultiProcessorCount, device);
+    {
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);
+        M->prio = greatest;
+        if (const char* pr = getenv("ORBX_PRIO")) M->prio = atoi(pr) ? greatest : 0;
+    }
     cudaFuncSetAttribute(k_search<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_search<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     *out = M;
@@ -897,12 +906,13 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     static bool attr = false;
     if (!attr) { cudaFuncSetAttribute(k_track_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
     CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));
-    k_track_prepare<<<dim3((frame_stride + 255) / 256, nframes), 256, 0, st>>>(T);
-    k_track_grid<<<nframes, kGridThreads, 0, st>>>(T);
+    // the whole step is latency-bound (one CTA per frame pair): dispatched ahead of the queued CTAs of other handles' kernels
+    CKM(orbx::launch_prio(k_track_prepare, dim3((frame_stride + 255) / 256, nframes), dim3(256), 0, st, M->prio, T));
+    CKM(orbx::launch_prio(k_track_grid, dim3(nframes), dim3(kGridThreads), 0, st, M->prio, T));
     M->launches += 2;
     if (nframes > 1) {
-        k_track_search<<<nframes - 1, kSearchThreads, smem, st>>>(T);
-        k_track_finish<<<nframes - 1, 256, 0, st>>>(T);
+        CKM(orbx::launch_prio(k_track_search, dim3(nframes - 1), dim3(kSearchThreads), smem, st, M->prio, T));
+        CKM(orbx::launch_prio(k_track_finish, dim3(nframes - 1), dim3(256), 0, st, M->prio, T));
         M->launches += 2;
     } else {
         CKM(cudaMemsetAsync(d_nmatches, 0, sizeof(int), st));

@@ -26,6 +26,7 @@ struct Extractor {
     struct PassGraph { const uint8_t* base; size_t frameBytes; int pitch, n, lap0, lap1, fb, slot; cudaGraphExec_t exec; int kernels; };
     std::vector<PassGraph> graphs;
     bool useGraphs = true;
+    int prio = 0;                    // launch priority of the latency-bound kernels (0 = none)
     int chunk = 0;                   // frames per pipelined sub-batch of the host path (0 = auto)
     std::string err;
     long long launches = 0;
@@ -314,14 +315,15 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
-    k_octree<<<dim3(n, L), kTreeThreads, E->treeSmem, st>>>(E->dGeom, E->dCells, E->dCand, E->dCellCount, E->dQtA, E->dQtB,
-                                                            E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb);
+    CK(launch_prio(k_octree, dim3(n, L), dim3(kTreeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
+                   E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb));
     ++E->launches;
     mark();
     if (!side) k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
     ++E->launches;
     mark();
-    k_finalize<<<n, kFinalThreads, 0, st>>>(E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp, E->dOutCnt, E->dWork, fb);
+    CK(launch_prio(k_finalize, dim3(n), dim3(kFinalThreads), 0, st, E->prio, E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp,
+                   E->dOutCnt, E->dWork, fb));
     ++E->launches;
     mark();
     if (side) CK(cudaStreamWaitEvent(st, E->evJoin[slot], 0));
@@ -438,6 +440,12 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     }
     if (const char* ov = getenv("ORBX_OVERLAP")) E->overlap = atoi(ov) != 0;
     if (const char* gr = getenv("ORBX_GRAPHS")) E->useGraphs = atoi(gr) != 0;
+    {
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);
+        E->prio = greatest;
+        if (const char* pr = getenv("ORBX_PRIO")) E->prio = atoi(pr) ? greatest : 0;
+    }
     if (const char* c = getenv("ORBX_CHUNK")) E->chunk = atoi(c);
     for (auto& ev : E->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e);
     // algorithm constants: circular-patch half-widths (:453-468) and the BRIEF pattern

@@ -69,4 +69,19 @@ struct DevGeom {
     uint8_t* blur[kMaxLevels];
 };
 
+// Launch with a scheduling priority (cudaLaunchAttributePriority; captured into graph kernel nodes as well).  The short,
+// latency-bound kernels (quadtree, finalize, the tracking step) are given the highest priority so that their CTAs are
+// dispatched ahead of the tens of thousands of queued CTAs of the throughput kernels (FAST, blur) of ANOTHER handle working
+// on the same GPU; prio = 0 is a plain launch.
+template <class... KArgs, class... Args>
+inline cudaError_t launch_prio(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int prio, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributePriority;
+    at[0].val.priority = prio;
+    cfg.attrs = at; cfg.numAttrs = prio ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 }  // namespace orbx

@@ -177,28 +177,41 @@ __device__ __forceinline__ int fast_strength(int v, const int (&r)[16]) {
 
 constexpr int kFastThreads = 256;          // widest variant; a cell may hold at most 32 * threads pixels
 
-// FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes (VIMNMX3.U16x2 / native on sm_100a:
-// 64 3-input min/max per clk per SM, tools/microbench.cu).  Sliding 9-window minima and maxima of the ring as
-// min3(min3, min3, min3), then  s = max( max_k min9[k] - v, v - min_k max9[k], 0 )  per lane.
+// FAST-9/16 strength of TWO horizontally adjacent pixels at once in u16x2 lanes:
+//   s = max( max_i min(W_i) - v, v - min_i max(W_i), 0 ),  W_i = the 9 ring pixels r[i..i+8] (cyclic), i = 0..15.
+// min / max commute with the per-lane offset (256 - v), so the windows run on the raw ring values and the centre is applied
+// once at the end.  Cost model (tools/microbench.cu, profiles/int_peaks_b200.txt): the 2-input VIMNMX.U16x2 issues at 128
+// /clk/SM, the 3-input VIMNMX3.U16x2 at 64 — a 3-input op costs two ALU-pipe slots, and this kernel is bound by that pipe.
+// The windows are therefore evaluated in PAIRS: W_2k and W_2k+1 share the 8 pixels C_k = r[2k+1..2k+8], and
+//   max( min(W_2k), min(W_2k+1) ) = min( min(C_k), max(r[2k], r[2k+9]) )          (lattice distributivity)
+// with min(C_k) = min(qq[k], qq[k+2]), qq[k] = min(q[k], q[k+1]), q[k] = min(r[2k+1], r[2k+2]).  Per side: 8 + 8 + 8
+// two-input ops, 8 three-input ops and a 4-op reduction = 36 instructions / 47 pipe slots (the plain sliding-window form,
+// min3 over min3, took 40 / 79).  Pure min / max identities: the result is bit-identical.
 __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t (&r)[16]) {
-    // min / max commute with the per-lane offset (256 - v), so the windows run on the raw ring values and the centre is
-    // applied once at the end
-    uint32_t tmin[16], tmax[16];
+    uint32_t q[8], Q[8];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        tmin[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-        tmax[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+    for (int k = 0; k < 8; ++k) {
+        q[k] = __vminu2(r[2 * k + 1], r[(2 * k + 2) & 15]);
+        Q[k] = __vmaxu2(r[2 * k + 1], r[(2 * k + 2) & 15]);
     }
-    uint32_t a9[16], b9[16];
+    uint32_t qq[8], QQ[8];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        a9[k] = __vimin3_u16x2(tmin[k], tmin[(k + 3) & 15], tmin[(k + 6) & 15]);
-        b9[k] = __vimax3_u16x2(tmax[k], tmax[(k + 3) & 15], tmax[(k + 6) & 15]);
+    for (int k = 0; k < 8; ++k) {
+        qq[k] = __vminu2(q[k], q[(k + 1) & 7]);
+        QQ[k] = __vmaxu2(Q[k], Q[(k + 1) & 7]);
     }
-    uint32_t A = __vimax3_u16x2(a9[0], a9[1], a9[2]), B = __vimin3_u16x2(b9[0], b9[1], b9[2]);
+    uint32_t a[8], b[8];
 #pragma unroll
-    for (int k = 3; k < 15; k += 2) { A = __vimax3_u16x2(A, a9[k], a9[k + 1]); B = __vimin3_u16x2(B, b9[k], b9[k + 1]); }
-    A = __vmaxu2(A, a9[15]); B = __vminu2(B, b9[15]);
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t e = __vmaxu2(r[2 * k], r[(2 * k + 9) & 15]);
+        const uint32_t E = __vminu2(r[2 * k], r[(2 * k + 9) & 15]);
+        a[k] = __vimin3_u16x2(qq[k], qq[(k + 2) & 7], e);
+        b[k] = __vimax3_u16x2(QQ[k], QQ[(k + 2) & 7], E);
+    }
+    uint32_t A = __vimax3_u16x2(a[0], a[1], a[2]), B = __vimin3_u16x2(b[0], b[1], b[2]);
+    A = __vimax3_u16x2(A, a[3], a[4]); B = __vimin3_u16x2(B, b[3], b[4]);
+    A = __vimax3_u16x2(A, a[5], a[6]); B = __vimin3_u16x2(B, b[5], b[6]);
+    A = __vmaxu2(A, a[7]); B = __vminu2(B, b[7]);
     // per lane: A + 256 - v and v + 256 - B are in [1, 511]: no borrow between the two u16 lanes
     const uint32_t s = __vimax3_u16x2(A + (0x01000100u - v2), (v2 + 0x01000100u) - B, 0x01000100u);
     return s - 0x01000100u;
