@@ -162,6 +162,38 @@ def run_reference(args):
     emit(line)
 
 
+def latency_bench(args, torch, local, frames):
+    """What ONE agent's Tracking thread sees (SURVEY.md 8d 'GPU timing (a)'): one synchronous ORBextractor::operator() call per
+    frame with host buffers (H2D of the image and D2H of keypoints + descriptors inside the call), then one
+    SearchByProjection(Cur, Last, th = 15) call with host arrays.  Median over 100 calls after 10 warm-up calls."""
+    from mam3slam_b200 import ORBextractor, ORBmatcher
+    ex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local)
+    m = ORBmatcher(0.9, True, device=local)
+    sf = ex.GetScaleFactors()
+    pin = torch.from_numpy(np.ascontiguousarray(frames[:8])).pin_memory().numpy()
+    t_ex, t_sp = [], []
+    last, F = None, None
+    for i in range(110):
+        t0 = time.perf_counter()
+        _, k, d = ex(pin[i % len(pin)])
+        t1 = time.perf_counter()
+        if last is not None and len(k):
+            F = m.frame(k, d, BOUNDS) if F is None else (F.update(k, d, BOUNDS) or F)
+            lk, ld = last
+            m.SearchByProjection_Frame(F, np.zeros(len(k), np.uint8), sf, np.ones(len(lk), np.uint8), lk["x"], lk["y"], lk["octave"],
+                                       lk["angle"], ld, TH_TRACK)
+        t2 = time.perf_counter()
+        if i >= 10:
+            t_ex.append(t1 - t0); t_sp.append(t2 - t1)
+        last = (k, d)
+    if F is not None:
+        F.close()
+    m.close(); ex.close()
+    e, s_ = float(np.median(t_ex)), float(np.median(t_sp))
+    return {"operator_call_ms": e * 1e3, "search_by_projection_call_ms": s_ * 1e3, "single_stream_frames_per_s": 1.0 / (e + s_),
+            "note": "one frame in flight, synchronous calls, host buffers (pinned image)"}
+
+
 def kitti_bench(args, torch, dist, rank, world, local):
     """BASELINE config 3: KITTI-shaped 1241x376 frames, 2000 kp: device-resident extraction of 32 frames per step, and
     SearchForTriangulation (LocalMapping::CreateNewMapPoints: ratio 0.6, no orientation check) on keyframe pairs (t, t+5)
@@ -459,6 +491,7 @@ def run_gpu(args):
     total_frames = B * args.steps * world
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
+    latency = latency_bench(args, torch, local, frames) if rank == 0 else None
     if rank == 0:
         pk, pk_kind = peaks()
         fps = total_frames / (ms * 1e-3)
@@ -491,6 +524,7 @@ def run_gpu(args):
                          "pipeline_frac": ALG_BYTES_PER_FRAME * fps / 1e9 / world / pk["hbm_gbs"]},
             "hamming": {"track_evaluations_per_s": track_evals * world / (acc["track"] * 1e-3), "knn": hamming},
             "kitti": kitti,
+            "latency": latency,
         }
         if world == 1 and not args.no_cpu:
             cf = make_frames(0, 8)
