@@ -902,6 +902,14 @@ int orbx_stereo_matches(orbx_handle left, orbx_handle right, float mb, float mbf
     return hn[0] <= cap ? ORBX_OK : ORBX_ERR_CAPACITY;
 }
 
+#ifdef ORBX_TREE_PROFILE
+extern "C" int orbx_debug_tree_profile(long long* out16, int reset) {
+    if (reset) { long long z[16] = {}; cudaMemcpyToSymbol(g_treeProf, z, sizeof(z)); return 0; }
+    cudaDeviceSynchronize();
+    return cudaMemcpyFromSymbol(out16, g_treeProf, 16 * sizeof(long long)) == cudaSuccess ? 0 : -1;
+}
+#endif
+
 long long orbx_launch_count(orbx_handle h) { return h ? static_cast<Extractor*>(h)->launches : 0; }
 void* orbx_stream(orbx_handle h) { return h ? (void*)static_cast<Extractor*>(h)->stream : nullptr; }
 

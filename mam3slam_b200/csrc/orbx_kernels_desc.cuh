@@ -49,6 +49,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     const int cb = L.cellBegin, nc = L.cellEnd - L.cellBegin;
     const int* cc = cellCount + (size_t)frame * g->nCells + cb;
+    TPROF_T0();
     for (int i = tid; i < nc; i += kTreeThreads) S.scanA[i] = cc[i];
     __syncthreads();
     const int n = block_exscan(S.scanA, nc, sW);
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
         }
     }
     __syncthreads();
+    TPROF(0);
     uint64_t* const buf[2] = {bufA, bufB};
     distribute_tree(buf, n, L.quota, L.nIni, L.hX, L.treeH, S,
                     lvlKp + (size_t)frame * g->kpCapFrame + L.kpOffset, lvlCnt + frame * g->nlevels + l);

@@ -84,36 +84,75 @@ struct RootClass {
 };
 
 // Stable 4-way partition of src[beg, beg+cnt) into dst starting at outBase, by one warp.  Returns class counts.
+// The loops are bound by the L2 round trip of their key loads, not by the ballots: keys are therefore fetched kPartU
+// blocks of 32 at a time (all loads of a group are issued before the first one is used), and a node of at most
+// 32 * kPartU keys — every node from the third pass on — is read exactly once, its keys staying in registers between the
+// counting and the scattering step.
+constexpr int kPartU = 8;
+template <class F>
+__device__ __forceinline__ void partition_count_block(int q, int& n0, int& n1, int& n2, int& n3) {
+    n0 += __popc(__ballot_sync(0xffffffffu, q == 0));
+    n1 += __popc(__ballot_sync(0xffffffffu, q == 1));
+    n2 += __popc(__ballot_sync(0xffffffffu, q == 2));
+    n3 += __popc(__ballot_sync(0xffffffffu, q == 3));
+}
+__device__ __forceinline__ void partition_scatter_block(uint64_t* dst, uint64_t k, int q, uint32_t lt, int& o0, int& o1, int& o2, int& o3) {
+    const uint32_t b0 = __ballot_sync(0xffffffffu, q == 0), b1 = __ballot_sync(0xffffffffu, q == 1);
+    const uint32_t b2 = __ballot_sync(0xffffffffu, q == 2), b3 = __ballot_sync(0xffffffffu, q == 3);
+    if (q == 0) dst[o0 + __popc(b0 & lt)] = k;
+    else if (q == 1) dst[o1 + __popc(b1 & lt)] = k;
+    else if (q == 2) dst[o2 + __popc(b2 & lt)] = k;
+    else if (q == 3) dst[o3 + __popc(b3 & lt)] = k;
+    o0 += __popc(b0); o1 += __popc(b1); o2 += __popc(b2); o3 += __popc(b3);
+}
+// src[lo, hi) in groups of kPartU blocks: fn(blockStart, key, valid) for every block of 32, in order
+template <class Fn>
+__device__ __forceinline__ void for_key_groups(const uint64_t* src, int lo, int hi, Fn fn) {
+    const int lane = threadIdx.x & 31;
+    for (int base = lo; base < hi; base += 32 * kPartU) {
+        uint64_t k[kPartU];
+#pragma unroll
+        for (int u = 0; u < kPartU; ++u) {
+            const int i = base + 32 * u + lane;
+            k[u] = i < hi ? src[i] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < kPartU; ++u) {
+            if (base + 32 * u >= hi) break;                     // warp-uniform
+            fn(k[u], base + 32 * u + lane < hi);
+        }
+    }
+}
 template <class F>
 __device__ __forceinline__ uint4 warp_partition4(const uint64_t* src, uint64_t* dst, int beg, int cnt, int outBase, F cls) {
     const int lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1;
     int n0 = 0, n1 = 0, n2 = 0, n3 = 0;
-    uint64_t keep = 0; int keepQ = -1;
-    for (int base = 0; base < cnt; base += 32) {
-        const int i = base + lane;
-        int q = -1; uint64_t k = 0;
-        if (i < cnt) { k = src[beg + i]; q = cls(k); }
-        n0 += __popc(__ballot_sync(0xffffffffu, q == 0));
-        n1 += __popc(__ballot_sync(0xffffffffu, q == 1));
-        n2 += __popc(__ballot_sync(0xffffffffu, q == 2));
-        n3 += __popc(__ballot_sync(0xffffffffu, q == 3));
-        keep = k; keepQ = q;
+    if (cnt <= 32 * kPartU) {
+        uint64_t k[kPartU]; int q[kPartU];
+#pragma unroll
+        for (int u = 0; u < kPartU; ++u) {
+            const int i = 32 * u + lane;
+            k[u] = i < cnt ? src[beg + i] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < kPartU; ++u) {
+            q[u] = -1;
+            if (32 * u >= cnt) continue;                        // warp-uniform
+            if (32 * u + lane < cnt) q[u] = cls(k[u]);
+            partition_count_block<F>(q[u], n0, n1, n2, n3);
+        }
+        int o0 = outBase, o1 = o0 + n0, o2 = o1 + n1, o3 = o2 + n2;
+#pragma unroll
+        for (int u = 0; u < kPartU; ++u) {
+            if (32 * u >= cnt) continue;
+            partition_scatter_block(dst, k[u], q[u], lt, o0, o1, o2, o3);
+        }
+        return make_uint4(n0, n1, n2, n3);
     }
+    for_key_groups(src, beg, beg + cnt, [&](uint64_t k, bool valid) { partition_count_block<F>(valid ? cls(k) : -1, n0, n1, n2, n3); });
     int o0 = outBase, o1 = o0 + n0, o2 = o1 + n1, o3 = o2 + n2;
-    for (int base = 0; base < cnt; base += 32) {
-        const int i = base + lane;
-        int q; uint64_t k;
-        if (cnt <= 32) { q = keepQ; k = keep; }
-        else { q = -1; k = 0; if (i < cnt) { k = src[beg + i]; q = cls(k); } }
-        const uint32_t b0 = __ballot_sync(0xffffffffu, q == 0), b1 = __ballot_sync(0xffffffffu, q == 1);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, q == 2), b3 = __ballot_sync(0xffffffffu, q == 3);
-        if (q == 0) dst[o0 + __popc(b0 & lt)] = k;
-        else if (q == 1) dst[o1 + __popc(b1 & lt)] = k;
-        else if (q == 2) dst[o2 + __popc(b2 & lt)] = k;
-        else if (q == 3) dst[o3 + __popc(b3 & lt)] = k;
-        o0 += __popc(b0); o1 += __popc(b1); o2 += __popc(b2); o3 += __popc(b3);
-    }
+    for_key_groups(src, beg, beg + cnt, [&](uint64_t k, bool valid) { partition_scatter_block(dst, k, valid ? cls(k) : -1, lt, o0, o1, o2, o3); });
     return make_uint4(n0, n1, n2, n3);
 }
 
@@ -127,15 +166,7 @@ __device__ uint4 cta_partition4(const uint64_t* src, uint64_t* dst, int beg, int
     chunk = (chunk + 31) & ~31;
     const int cb = min(wid * chunk, cnt), ce = min(cb + chunk, cnt);
     int n0 = 0, n1 = 0, n2 = 0, n3 = 0;
-    for (int base = cb; base < ce; base += 32) {
-        const int i = base + lane;
-        int q = -1;
-        if (i < ce) q = cls(src[beg + i]);
-        n0 += __popc(__ballot_sync(0xffffffffu, q == 0));
-        n1 += __popc(__ballot_sync(0xffffffffu, q == 1));
-        n2 += __popc(__ballot_sync(0xffffffffu, q == 2));
-        n3 += __popc(__ballot_sync(0xffffffffu, q == 3));
-    }
+    for_key_groups(src, beg + cb, beg + ce, [&](uint64_t k, bool valid) { partition_count_block<F>(valid ? cls(k) : -1, n0, n1, n2, n3); });
     if (lane == 0) { sCnt[wid][0] = n0; sCnt[wid][1] = n1; sCnt[wid][2] = n2; sCnt[wid][3] = n3; }
     __syncthreads();
     int t0 = 0, t1 = 0, t2 = 0, t3 = 0, p0 = 0, p1 = 0, p2 = 0, p3 = 0;
@@ -144,18 +175,7 @@ __device__ uint4 cta_partition4(const uint64_t* src, uint64_t* dst, int beg, int
         t0 += sCnt[w][0]; t1 += sCnt[w][1]; t2 += sCnt[w][2]; t3 += sCnt[w][3];
     }
     int o0 = outBase + p0, o1 = outBase + t0 + p1, o2 = outBase + t0 + t1 + p2, o3 = outBase + t0 + t1 + t2 + p3;
-    for (int base = cb; base < ce; base += 32) {
-        const int i = base + lane;
-        int q = -1; uint64_t k = 0;
-        if (i < ce) { k = src[beg + i]; q = cls(k); }
-        const uint32_t b0 = __ballot_sync(0xffffffffu, q == 0), b1 = __ballot_sync(0xffffffffu, q == 1);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, q == 2), b3 = __ballot_sync(0xffffffffu, q == 3);
-        if (q == 0) dst[o0 + __popc(b0 & lt)] = k;
-        else if (q == 1) dst[o1 + __popc(b1 & lt)] = k;
-        else if (q == 2) dst[o2 + __popc(b2 & lt)] = k;
-        else if (q == 3) dst[o3 + __popc(b3 & lt)] = k;
-        o0 += __popc(b0); o1 += __popc(b1); o2 += __popc(b2); o3 += __popc(b3);
-    }
+    for_key_groups(src, beg + cb, beg + ce, [&](uint64_t k, bool valid) { partition_scatter_block(dst, k, valid ? cls(k) : -1, lt, o0, o1, o2, o3); });
     __syncthreads();
     return make_uint4(t0, t1, t2, t3);
 }
@@ -344,6 +364,15 @@ __device__ void warp_sort_nodes(ise::Elem* e, int n, uint32_t* listA, uint32_t* 
     __syncwarp();
 }
 
+#ifdef ORBX_TREE_PROFILE
+__device__ long long g_treeProf[16];
+#define TPROF_T0() long long tp_ = clock64()
+#define TPROF(i) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) { long long n_ = clock64(); g_treeProf[i] += n_ - tp_; tp_ = n_; } } while (0)
+#else
+#define TPROF_T0()
+#define TPROF(i)
+#endif
+
 // The whole DistributeOctTree for one level.  Keys are in buf[0][0..n) in the reference's vToDistributeKeys order.
 // Writes the kept keys (one per final node, list order) to out[0..*outCount).
 __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIni, float hX, int treeH,
@@ -353,6 +382,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
     __shared__ int sT;
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     if (n == 0) { if (tid == 0) *outCount = 0; return; }
+    TPROF_T0();
 
     // roots: stable grouping of the keys by (int)(x / hX) into buf[1]
     int outBase = 0;
@@ -381,6 +411,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
     }
     __syncthreads();
     int listSize = sT;
+    TPROF(1);
 
     bool finish = false;
     while (!finish) {
@@ -392,12 +423,16 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
         for (int i = tid; i < listSize; i += kTreeThreads)
             if (S.cnt[cur][i] > 1) S.proc[S.scanA[i]] = (uint16_t)i;
         __syncthreads();
+        TPROF(2);
         split_big_nodes(S, cur, T, buf, sCnt);
+        TPROF(3);
         split_nodes(S, cur, T, buf, sCnt, 0);
         __syncthreads();
+        TPROF(4);
         int m;
         listSize = apply_splits(S, cur, listSize, T, sWarp, &m);
         cur ^= 1;
+        TPROF(5);
         if (listSize >= N || listSize == prevSize) {
             finish = true;
         } else if (listSize + 3 * m > N) {
@@ -429,6 +464,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
                 __syncthreads();
                 listSize = apply_splits(S, cur, listSize, T2, sWarp, &m);
                 cur ^= 1;
+                TPROF(7);
                 if (listSize >= N || listSize == prev2) finish = true;
             }
         }
@@ -455,6 +491,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
         if (lane == 0) out[i] = bestKey;
     }
     if (tid == 0) *outCount = listSize;
+    TPROF(8);
 }
 
 }  // namespace orbx
