@@ -21,7 +21,10 @@ namespace orbx {
 
 constexpr int kTreeThreads = 512;
 constexpr int kTreeWarps = kTreeThreads / 32;
-constexpr int kCtaPartitionMin = 1024;   // nodes with at least this many keys are partitioned by the whole CTA
+#ifndef ORBX_CTA_PART_MIN
+#define ORBX_CTA_PART_MIN 1024
+#endif
+constexpr int kCtaPartitionMin = ORBX_CTA_PART_MIN;   // nodes with at least this many keys are partitioned by the whole CTA
 
 struct TreeSmem {                   // carved out of dynamic shared memory, sized by poolCap P and scanCap
     ushort4* rect[2];               // x0,y0,x1,y1
