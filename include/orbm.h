@@ -165,6 +165,13 @@ int orbm_knn_device(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k
 int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq, int k, uint16_t* out_dist,
                    int32_t* out_idx);
 
+/* the same merge on the device, for lists that an all-gather left in HBM: shard s has its nq x k uint16 distances at
+ * d_dist + s * shard_stride_bytes and its nq x k int32 global row ids at d_idx + s * shard_stride_bytes (both device
+ * pointers; one buffer per rank holding ids and distances can be gathered with a single collective).  Asynchronous on
+ * `stream` (NULL = the handle's stream). */
+int orbm_knn_merge_device(orbm_handle h, const void* d_dist, const void* d_idx, size_t shard_stride_bytes, int nshards, int nq,
+                          int k, uint16_t* d_out_dist, int32_t* d_out_idx, void* stream);
+
 /* replaces the selection in MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:366-396) for a batch of map
  * points: descriptors of point p are rows [off[p], off[p+1]); best[p] = row (relative) with the least median distance */
 int orbm_distinctive_descriptors(orbm_handle h, const uint8_t* desc, const int* off, int npoints, int* best);

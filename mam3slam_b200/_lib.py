@@ -109,6 +109,7 @@ def _bind_matcher(L):
     L.orbm_search_frame.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, i32, i32, vp, ip]
     L.orbm_search_sim3.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, i32, f32, vp, ip]
     L.orbm_search_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, vp, ip]
+    L.orbm_knn_merge_device.argtypes = [vp, vp, vp, C.c_size_t, i32, i32, i32, vp, vp, vp]
     L.orbm_fuse_candidates.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, f32, i32, vp, vp]
     L.orbm_search_by_sim3.argtypes = [vp, vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, ip]
     L.orbm_search_bow_kf_frame.argtypes = [vp, vp, fvp, vp, vp, fvp, f32, i32, vp, ip]

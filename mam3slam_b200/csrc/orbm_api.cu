@@ -839,6 +839,19 @@ int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq
     return ORBM_OK;
 }
 
+int orbm_knn_merge_device(orbm_handle M, const void* d_dist, const void* d_idx, size_t shard_stride_bytes, int nshards, int nq,
+                          int k, uint16_t* d_out_dist, int32_t* d_out_idx, void* stream) {
+    if (!M || !d_dist || !d_idx || nshards < 1 || nq < 0 || k < 1 || !d_out_dist || !d_out_idx) return ORBM_ERR_INVALID;
+    if (nq == 0) return ORBM_OK;
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    k_knn_merge_shards<<<(nq + 7) / 8, 256, 0, st>>>((const uint8_t*)d_dist, (const uint8_t*)d_idx, shard_stride_bytes, nshards, nq, k,
+                                                     d_out_dist, d_out_idx);
+    ++M->launches;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors selection (src/MapPoint.cc:366-396), batched over map points
 int orbm_distinctive_descriptors(orbm_handle M, const uint8_t* desc, const int* off, int npoints, int* best) {
     if (!M || !off || npoints < 0 || !best || (npoints > 0 && off[npoints] > 0 && !desc)) return ORBM_ERR_INVALID;

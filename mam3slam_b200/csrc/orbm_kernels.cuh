@@ -1116,6 +1116,37 @@ __global__ void __launch_bounds__(256) k_knn_merge(const unsigned long long* __r
     }
 }
 
+// merge of the per-SHARD top-k lists after the all-gather (config 5): shard s keeps its nq x k distances at
+// dist + s * strideBytes and its global row ids at idx + s * strideBytes.  Same rule as the single scan: (distance, global
+// row) ascending, so the result equals the unsharded search bit for bit.  One warp per query.
+__global__ void __launch_bounds__(256) k_knn_merge_shards(const uint8_t* __restrict__ dist, const uint8_t* __restrict__ idx,
+                                                          size_t strideBytes, int nshards, int nq, int k,
+                                                          uint16_t* __restrict__ outDist, int32_t* __restrict__ outIdx) {
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const int total = nshards * k;
+    unsigned long long prev = 0; bool first = true;
+    for (int t = 0; t < k; ++t) {
+        unsigned long long m = 0xffffffffffffffffull;
+        for (int e = lane; e < total; e += 32) {
+            const int c = e / k, u = e - c * k;
+            const int32_t row = reinterpret_cast<const int32_t*>(idx + (size_t)c * strideBytes)[(size_t)q * k + u];
+            const uint16_t d = reinterpret_cast<const uint16_t*>(dist + (size_t)c * strideBytes)[(size_t)q * k + u];
+            if (row < 0) continue;
+            const unsigned long long key = ((unsigned long long)d << 32) | (uint32_t)row;
+            if ((first || key > prev) && key < m) m = key;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(0xffffffffu, m, o); m = x < m ? x : m; }
+        if (lane == 0) {
+            if (m == 0xffffffffffffffffull) { outDist[(size_t)q * k + t] = 65535; outIdx[(size_t)q * k + t] = -1; }
+            else { outDist[(size_t)q * k + t] = (uint16_t)(m >> 32); outIdx[(size_t)q * k + t] = (int32_t)(m & 0xffffffffull); }
+        }
+        if (m == 0xffffffffffffffffull) { for (int u = t + 1; u < k && lane == 0; ++u) { outDist[(size_t)q * k + u] = 65535; outIdx[(size_t)q * k + u] = -1; } break; }
+        prev = m; first = false;
+    }
+}
+
 // MapPoint::ComputeDistinctiveDescriptors selection (src/MapPoint.cc:366-396): one warp per map point (N <= 32 rows
 // handled lane = row; larger N loops).  median = sorted row distances [0.5*(N-1)] (self distance 0 included).
 __global__ void __launch_bounds__(256) k_distinctive(const uint32_t* __restrict__ desc, const int* __restrict__ off, int npoints,

@@ -282,6 +282,32 @@ def test_knn_full_size_properties(M):
     Dp.close(); D.close()
 
 
+def test_knn_merge_device_equals_host_merge(M):
+    """config 5 exchange step: per-shard lists laid out as one (ids | distances) buffer per rank, merged on the device."""
+    import torch
+    q, db = sc.knn_data(8000, 300)
+    k, shards = 4, 4
+    nq = len(q)
+    nb_i, nb_d = nq * k * 4, nq * k * 2
+    buf = np.zeros((shards, nb_i + nb_d), np.uint8)
+    parts_d, parts_i = [], []
+    for s in range(shards):
+        d, i = om.knn(q, db[s * 2000:(s + 1) * 2000], k)
+        i = i + s * 2000
+        if s == 2:
+            d[:, -1] = 65535; i[:, -1] = -1            # a shard that returned fewer than k rows
+        parts_d.append(d); parts_i.append(i)
+        buf[s, :nb_i] = i.astype(np.int32).reshape(-1).view(np.uint8)
+        buf[s, nb_i:] = d.astype(np.uint16).reshape(-1).view(np.uint8)
+    want_d, want_i = M.knn_merge(np.stack(parts_d), np.stack(parts_i))
+    g = torch.from_numpy(buf).cuda()
+    od = torch.empty((nq, k), dtype=torch.int16, device="cuda")
+    oi = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+    M.knn_merge_device(g.data_ptr() + nb_i, g.data_ptr(), nb_i + nb_d, shards, nq, k, od.data_ptr(), oi.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(od.cpu().numpy().view(np.uint16), want_d) and np.array_equal(oi.cpu().numpy(), want_i)
+
+
 def test_distinctive_descriptors(M):
     rng = np.random.default_rng(23)
     sizes = [1, 2, 3, 5, 8, 13, 21, 34, 40]
