@@ -48,6 +48,10 @@ struct Extractor {
     bool fastPitchConst = false;
     bool pyrFast[kMaxLevels] = {};                  // level may use k_pyr_level_fast (4 pixels read <= 8 source bytes)
     size_t fastSmem = 0, treeSmem = 0;
+    // FAST cells in two launch groups: [0, fastNA) of dCellOrder = cells of at most fastRowsA tile rows (shared memory fastSmemA)
+    int* dCellOrder = nullptr;
+    int fastNA = 0, fastRowsA = 0;
+    size_t fastSmemA = 0;
     int poolCap = 0, scanCap = 0;
     int maxLevelW4 = 0;
 
@@ -221,6 +225,37 @@ int configureShape(Extractor* E, int W, int H) {
     if (E->fastPitchConst) E->fastTilePitch = 33;
     E->fastTileRows = maxCellH + 6;
     E->fastSmem = (size_t)2 * E->fastTileRows * E->fastTilePitch * 4 + (((size_t)(maxCellH + 2) * (maxCellW + 4) + 3) & ~(size_t)3) + 16;
+    {
+        // The tallest cell (a coarse level with two or three cell rows) sets fastSmem; at EuRoC that is 18.7 KB per CTA = 12
+        // CTAs per SM, although 86 % of the cells would fit 16 (the register limit of the 64-thread kernel).  Pick the largest
+        // CTA count per SM k for which at least 60 % of the cells fit the per-CTA budget and launch those cells separately.
+        auto need = [&](int h) {
+            return (size_t)2 * (h + 6) * E->fastTilePitch * 4 + ((((size_t)(h + 2) * (maxCellW + 4)) + 3) & ~(size_t)3) + 16;
+        };
+        int hA = 0;
+        for (int k = 16; k >= 13 && !hA; --k) {
+            const size_t budget = (size_t)(233472 / k) / 128 * 128 - 1024 - 512;       // driver reserve + static, 128-B granules
+            int h = maxCellH;
+            while (h > 0 && need(h) > budget) --h;
+            size_t fit = 0;
+            for (const FastCell& c : E->cells) fit += c.h <= h;
+            if (h > 0 && h < maxCellH && fit * 10 >= E->cells.size() * 6) hA = h;
+            if (h >= maxCellH) break;                                                  // everything fits already
+        }
+        std::vector<int> order;
+        for (size_t i = 0; i < E->cells.size(); ++i) if (!hA || E->cells[i].h <= hA) order.push_back((int)i);
+        E->fastNA = (int)order.size();
+        for (size_t i = 0; i < E->cells.size(); ++i) if (hA && E->cells[i].h > hA) order.push_back((int)i);
+        E->fastRowsA = hA ? hA + 6 : E->fastTileRows;
+        E->fastSmemA = hA ? need(hA) : E->fastSmem;
+        if (getenv("ORBX_FAST_GROUPS") && atoi(getenv("ORBX_FAST_GROUPS")) == 0) {     // A/B switch: one launch sized for the tallest cell
+            E->fastNA = (int)order.size(); E->fastRowsA = E->fastTileRows; E->fastSmemA = E->fastSmem;
+            for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+        }
+        int rc2;
+        if ((rc2 = devAlloc(E, &E->dCellOrder, order.size()))) return rc2;
+        CK(cudaMemcpy(E->dCellOrder, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
+    }
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
     CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
     CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -298,8 +333,16 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     const int slot = st == E->stream2 ? 1 : 0;
     const bool side = E->overlap && !E->timing && E->aux[slot];
     {
-        const dim3 fg(g.nCells, n);
-#define ORBX_FAST_LAUNCH(T, P) k_fast_cells<T, P><<<fg, T, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch, E->fastTileRows, fb)
+#define ORBX_FAST_LAUNCH(T, P)                                                                                                       \
+    do {                                                                                                                           \
+        if (E->fastNA > 0)                                                                                                         \
+            k_fast_cells<T, P><<<dim3(E->fastNA, n), T, E->fastSmemA, st>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount,       \
+                                                                           E->fastTilePitch, E->fastRowsA, fb, E->dCellOrder, 0);  \
+        if (g.nCells > E->fastNA)                                                                                                  \
+            k_fast_cells<T, P><<<dim3(g.nCells - E->fastNA, n), T, E->fastSmem, st>>>(E->dGeom, l0, E->dCells, E->dCand,             \
+                                                                                     E->dCellCount, E->fastTilePitch,              \
+                                                                                     E->fastTileRows, fb, E->dCellOrder, E->fastNA); \
+    } while (0)
         if (E->fastPitchConst) {
             if (E->fastThreads == 64) ORBX_FAST_LAUNCH(64, 33); else if (E->fastThreads == 128) ORBX_FAST_LAUNCH(128, 33); else ORBX_FAST_LAUNCH(256, 33);
         } else {
@@ -307,7 +350,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         }
 #undef ORBX_FAST_LAUNCH
     }
-    ++E->launches;
+    E->launches += g.nCells > E->fastNA ? 2 : 1;
     mark();
     if (side) {
         CK(cudaEventRecord(E->evFork[slot], st));

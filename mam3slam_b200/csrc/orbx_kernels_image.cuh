@@ -231,14 +231,18 @@ template <int kThreads, int kPitch>      // kPitch: compile-time tile pitch in w
 __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restrict__ g, Level0 l0,
                                                              const FastCell* __restrict__ cells,
                                                              uint32_t* __restrict__ cand, int* __restrict__ cellCount,
-                                                             int pitchWArg, int tileRowsMax, int frameBase) {
+                                                             int pitchWArg, int tileRowsMax, int frameBase,
+                                                             const int* __restrict__ cellOrder, int orderBase) {
     extern __shared__ __align__(16) uint8_t smem[];
     const int pitchW = kPitch ? kPitch : pitchWArg;    // a constant pitch turns the 17 ring addresses into immediates
     // candidate bitmaps by PAIR index (bit p = pair p holds a candidate in its even / odd pixel), written with ballots
     __shared__ uint32_t cmE[kThreads / 2 + 2], cmO[kThreads / 2 + 2];
     __shared__ int warpSum[kThreads / 32];
     __shared__ int total;
-    const FastCell c = cells[blockIdx.x];
+    // cells are launched in groups of similar height (cellOrder): the dynamic shared memory of a launch is sized for its own
+    // group, so that the many ordinary cells are not held to the occupancy of the few tall ones of the coarse levels
+    const int cellId = cellOrder[orderBase + blockIdx.x];
+    const FastCell c = cells[cellId];
     const int frame = frameBase + blockIdx.y;
     const int tid = threadIdx.x;
     int pitch;
@@ -414,7 +418,7 @@ __global__ void __launch_bounds__(kThreads) k_fast_cells(const DevGeom* __restri
         const int s = score[(py + 1) * sp + px + 2];
         out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
     }
-    if (tid == 0) cellCount[(size_t)frame * g->nCells + blockIdx.x] = total;
+    if (tid == 0) cellCount[(size_t)frame * g->nCells + cellId] = total;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
