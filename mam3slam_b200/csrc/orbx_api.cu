@@ -26,6 +26,7 @@ struct Extractor {
     struct PassGraph { const uint8_t* base; size_t frameBytes; int pitch, n, lap0, lap1, fb, slot; cudaGraphExec_t exec; int kernels; };
     std::vector<PassGraph> graphs;
     bool useGraphs = true;
+    bool blurEarly = true;           // blur forked right after the pyramid (beside FAST + quadtree); ORBX_BLUR_EARLY=0: beside the quadtree only
     int prio = 0;                    // launch priority of the latency-bound kernels (0 = none)
     int chunk = 0;                   // frames per pipelined sub-batch of the host path (0 = auto)
     std::string err;
@@ -332,6 +333,13 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     // With stage timing on, everything stays on one stream so that the per-stage events mean what they say.
     const int slot = st == E->stream2 ? 1 : 0;
     const bool side = E->overlap && !E->timing && E->aux[slot];
+    const bool early = side && E->blurEarly;       // fork right after the pyramid: blur || (FAST -> quadtree)
+    if (early) {
+        CK(cudaEventRecord(E->evFork[slot], st));
+        CK(cudaStreamWaitEvent(E->aux[slot], E->evFork[slot], 0));
+        k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
+        CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
+    }
     {
 #define ORBX_FAST_LAUNCH(T, P)                                                                                                       \
     do {                                                                                                                           \
@@ -352,7 +360,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     }
     E->launches += g.nCells > E->fastNA ? 2 : 1;
     mark();
-    if (side) {
+    if (side && !early) {
         CK(cudaEventRecord(E->evFork[slot], st));
         CK(cudaStreamWaitEvent(E->aux[slot], E->evFork[slot], 0));
         k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
@@ -483,6 +491,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     }
     if (const char* ov = getenv("ORBX_OVERLAP")) E->overlap = atoi(ov) != 0;
     if (const char* gr = getenv("ORBX_GRAPHS")) E->useGraphs = atoi(gr) != 0;
+    if (const char* be = getenv("ORBX_BLUR_EARLY")) E->blurEarly = atoi(be) != 0;
     {
         int least = 0, greatest = 0;
         cudaDeviceGetStreamPriorityRange(&least, &greatest);
