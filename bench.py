@@ -532,7 +532,7 @@ def run_gpu(args):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
                          "frac": ach / pk["hbm_gbs"], "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(dom) if B == 64 else None,
-                         "traffic_source": "profiles/r1f_ncu_full_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, 64 frames per launch)",
+                         "traffic_source": "profiles/r1g_ncu_full_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, 64 frames per launch)",
                          "peak_kind": pk_kind,
                          "alu": fast_alu_roofline(acc.get("fast"), B),
                          "stage_ms_per_step": acc,
@@ -556,8 +556,8 @@ def run_gpu(args):
 
 
 # DRAM bytes per launch (64 EuRoC frames) of each stage's kernel(s), from the committed ncu --set full capture
-NCU_DRAM_BYTES_PER_LAUNCH = {"pyramid": 75.4e6, "fast": 72.7e6, "octree": 15.1e6, "blur": 115.7e6, "finalize": 0.56e6,
-                             "orient_brief": 149.8e6, "track": 8.7e6}
+NCU_DRAM_BYTES_PER_LAUNCH = {"pyramid": 75.4e6, "fast": 71.0e6, "octree": 15.4e6, "blur": 116.6e6, "finalize": 0.56e6,
+                             "orient_brief": 150.7e6, "track": 8.6e6}
 
 
 def fast_alu_roofline(fast_ms, B):
