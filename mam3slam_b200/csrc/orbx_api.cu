@@ -402,7 +402,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     return ORBX_OK;
 }
 
-// One pass = 13 kernel launches (+ the side-stream fork / join).  At 16 frames per sub-batch that is ~0.3 ms of GPU work
+// One pass = 13 kernel launches, 14 with two FAST groups (+ the side-stream fork / join).  At 16 frames per sub-batch that is ~0.3 ms of GPU work
 // behind ~20 driver calls, so the host path was launch-bound; the sequence is captured once per argument set into a CUDA
 // graph and replayed with a single call.  Stage timing (events between the kernels) uses the plain launches.
 int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb = 0) {
