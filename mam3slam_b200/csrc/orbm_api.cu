@@ -189,8 +189,10 @@ int orbm_create(int device, orbm_handle* out) {
         M->prio = greatest;
         if (const char* pr = getenv("ORBX_PRIO")) M->prio = atoi(pr) ? greatest : 0;
     }
-    cudaFuncSetAttribute(k_search<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    cudaFuncSetAttribute(k_search<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    // per (function, device): set for THIS handle's device (orbx_internal.h raise_dyn_smem)
+    orbx::raise_dyn_smem((const void*)k_search<true>, device, 200 * 1024);
+    orbx::raise_dyn_smem((const void*)k_search<false>, device, 200 * 1024);
+    orbx::raise_dyn_smem((const void*)k_track_search, device, 200 * 1024);
     *out = M;
     return ORBM_OK;
 }
@@ -916,8 +918,6 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     T.stageTgt = search_smem_bytes(frame_stride, 1, true) <= kSearchSmemMax ? 1 : 0;
     const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0);
     if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(k_track_search, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
     CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));
     // the whole step is latency-bound (one CTA per frame pair): dispatched ahead of the queued CTAs of other handles' kernels
     CKM(orbx::launch_prio(k_track_prepare, dim3((frame_stride + 255) / 256, nframes), dim3(256), 0, st, M->prio, T));

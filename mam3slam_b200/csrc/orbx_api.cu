@@ -1,6 +1,7 @@
 // C ABI of the B200-native ORB extractor: handle management, geometry tables, launch sequence.
 // Host-side logic mirrors ORBextractor's constructor and operator() (src/ORBextractor.cc:409-469, 1086-1168).
 #include "orbx_kernels_desc.cuh"
+#include "orbx_kernels_fast.cuh"
 #include "orbx_kernels_stereo.cuh"
 #include <cmath>
 #include <cstdio>
@@ -21,6 +22,12 @@ struct Extractor {
     cudaStream_t stream = nullptr, stream2 = nullptr;
     cudaStream_t aux[2] = {nullptr, nullptr};          // side streams: the blur runs beside FAST + quadtree
     cudaEvent_t evFork[2] = {nullptr, nullptr}, evJoin[2] = {nullptr, nullptr};
+    // completion of the last pass of each slot and the stream it ran on: a pass on ANOTHER stream (a caller's stream handed to
+    // orbx_extract_device) first waits for it - the handle's buffers and side streams are shared - and every entry point that
+    // reads results waits for it, whatever stream the pass ran on (the handle's streams are non-blocking: the legacy-stream
+    // copies would not order against them)
+    cudaEvent_t evDone[2] = {nullptr, nullptr};
+    cudaStream_t lastSt[2] = {nullptr, nullptr};
     bool overlap = true;
     // CUDA graphs of the launch sequence of one pass, keyed by everything the kernels' arguments depend on
     struct PassGraph { const uint8_t* base; size_t frameBytes; int pitch, n, lap0, lap1, fb, slot; cudaGraphExec_t exec; int kernels; };
@@ -55,6 +62,12 @@ struct Extractor {
     bool fastEarly = false;          // ORBX_FAST_EARLY=1: FAST of level 0 launched beside the pyramid (e2e +1.7 %, device-resident -2 %)
     cudaEvent_t evStart[2] = {nullptr, nullptr}, evF0[2] = {nullptr, nullptr};
     size_t fastSmemA = 0;
+    // second-generation FAST (orbx_kernels_fast.cuh): image-wide strength pass + per-cell select pass
+    int fastGen = 2;                 // ORBX_FAST_GEN=1: the first-generation one-CTA-per-cell kernel (A/B switch)
+    bool fastCompass = false;        // ORBX_FAST_COMPASS=1: warp-uniform compass early-out in the strength pass
+    FsPlan fsPlan{};
+    FsMaps fsMaps{};
+    uint2* dCbits = nullptr;
     int poolCap = 0, scanCap = 0;
     int maxLevelW4 = 0;
 
@@ -91,6 +104,33 @@ struct Extractor {
     } while (0)
 
 int cvRoundF(float v) { return (int)lrintf(v); }
+
+// cuTensorMapEncodeTiled through the runtime (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn tensorMapEncoder() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// 3-D u8 tensor {x, y, frame} of one pyramid level for k_fast_score's tile loads.  false: TMA cannot address it (base, row
+// pitch or frame stride not a multiple of 16 bytes) and the kernel stages that level with plain loads.
+bool encodeLevelMap(CUtensorMap* m, const uint8_t* base, int w, int h, int frames, size_t pitch, size_t frameBytes) {
+    EncodeTiledFn enc = tensorMapEncoder();
+    static const bool off = getenv("ORBX_FAST_TMA") && atoi(getenv("ORBX_FAST_TMA")) == 0;      // A/B switch: plain-load staging
+    if (off || !enc || (((uintptr_t)base | pitch | frameBytes) & 15) != 0 || frames < 1) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frameBytes};
+    const cuuint32_t box[3] = {(cuuint32_t)kFsBoxW, (cuuint32_t)kFsBoxH, 1};
+    const cuuint32_t es[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 void freeShape(Extractor* E) {
     for (auto& G : E->graphs) cudaGraphExecDestroy(G.exec);      // they hold pointers into the buffers freed below
@@ -263,31 +303,57 @@ int configureShape(Extractor* E, int W, int H) {
         CK(cudaMemcpy(E->dCellOrder, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
     }
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
-    CK(cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->treeSmem));
-    CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(raise_dyn_smem((const void*)k_octree, E->device, E->treeSmem));
+    CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
     // fewer threads per cell when the cells are small: the per-thread fixed cost (prologue, scans, barriers) is spread over
     // more pixels; every thread owns a raster chunk of at most 32 pixels
     const char* ft = getenv("ORBX_FAST_THREADS");
     E->fastThreads = maxCellPx <= 32 * 64 ? 64 : maxCellPx <= 32 * 128 ? 128 : 256;
     if (ft && (atoi(ft) == 64 || atoi(ft) == 128 || atoi(ft) == 256) && maxCellPx <= 32 * atoi(ft)) E->fastThreads = atoi(ft);
-    CK(cudaFuncSetAttribute(k_fast_cells<64, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<128, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<128, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<256, 33>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
-    CK(cudaFuncSetAttribute(k_fast_cells<256, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<64, 33>, E->device, E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<64, 0>, E->device, E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<128, 33>, E->device, E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<128, 0>, E->device, E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<256, 33>, E->device, E->fastSmem));
+    CK(raise_dyn_smem((const void*)k_fast_cells<256, 0>, E->device, E->fastSmem));
+
+    // strength-pass plan: per level ceil(testedW / 64) x ceil(testedH / 28) warp jobs, fine levels first
+    {
+        FsPlan& P = E->fsPlan;
+        memset(&P, 0, sizeof(P));
+        int job = 0, bitsOff = 0;
+        for (int l = 0; l < L; ++l) {
+            const LevelGeom& G = g.lv[l];
+            P.lv[l].jobBegin = job;
+            P.lv[l].nCx = (G.w - kEdge - kFsX0 + kFsCols - 1) / kFsCols;
+            P.lv[l].nSy = (G.h - 2 * kEdge + 2 * kFsRows - 1) / (2 * kFsRows);
+            P.lv[l].bitsOffset = bitsOff;
+            job += P.lv[l].nCx * P.lv[l].nSy;
+            bitsOff += 2 * P.lv[l].nSy * 16 * P.lv[l].nCx;
+        }
+        for (int l = L; l < kMaxLevels; ++l) P.lv[l].jobBegin = job;
+        P.nJobs = job; P.bitsPerFrame = bitsOff;
+        for (const FastCell& c : E->cells)
+            if (c.w * c.h > 32 * kSelMaxWords) { E->err = "FAST cell too large"; return ORBX_ERR_UNSUPPORTED; }
+    }
 
     // device buffers
     for (int l = 0; l < L; ++l) {
         int rc;
         if (l > 0) { if ((rc = devAlloc(E, &g.lvl[l], g.lv[l].planeBytes * B + 256))) return rc; }
         if ((rc = devAlloc(E, &g.blur[l], g.lv[l].planeBytes * B + 256))) return rc;
+        if ((rc = devAlloc(E, &g.score[l], g.lv[l].planeBytes * B + 256))) return rc;
+        CK(cudaMemset(g.score[l], 0, g.lv[l].planeBytes * B + 256));
     }
     int rc;
     if ((rc = devAlloc(E, &E->dLvl0, g.lv[0].planeBytes * B + 256))) return rc;
     g.lvl[0] = E->dLvl0;
     if ((rc = devAlloc(E, &E->dCand, (size_t)g.candCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dCellCount, (size_t)g.nCells * B))) return rc;
+    if ((rc = devAlloc(E, &E->dCbits, (size_t)E->fsPlan.bitsPerFrame * B))) return rc;
+    memset(&E->fsMaps, 0, sizeof(E->fsMaps));
+    for (int l = 1; l < L; ++l)
+        E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
     if ((rc = devAlloc(E, &E->dQtA, g.qtCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dQtB, g.qtCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dLvlKp, (size_t)g.kpCapFrame * B))) return rc;
@@ -325,7 +391,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     const bool side = E->overlap && !E->timing && E->aux[slot];
     // FAST on level 0 reads only the input image: its cells go first, on the side stream, beside the (latency-bound) chain
     // of pyramid launches
-    const int nA0 = side && E->fastEarly ? E->fastNA0 : 0;
+    const int nA0 = side && E->fastEarly && E->fastGen < 2 ? E->fastNA0 : 0;
 #define ORBX_FAST_GROUP(T, P, STREAM, BASE, COUNT, ROWS, SMEM)                                                                      \
     k_fast_cells<T, P><<<dim3(COUNT, n), T, SMEM, STREAM>>>(E->dGeom, l0, E->dCells, E->dCand, E->dCellCount, E->fastTilePitch,   \
                                                             ROWS, fb, E->dCellOrder, BASE)
@@ -370,8 +436,21 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
-    if (E->fastNA > nA0) ORBX_FAST_DISPATCH(st, nA0, E->fastNA - nA0, E->fastRowsA, E->fastSmemA);
-    if (g.nCells > E->fastNA) ORBX_FAST_DISPATCH(st, E->fastNA, g.nCells - E->fastNA, E->fastTileRows, E->fastSmem);
+    if (E->fastGen >= 2) {
+        // level 0 is the caller's image: its tensor map depends on this pass's pointer / pitch / frame stride
+        FsMaps maps = E->fsMaps;
+        const size_t fstride = (fb + n == 1) ? (((size_t)l0.pitch * g.lv[0].h + 15) & ~(size_t)15) : l0.frameBytes;
+        maps.tmaOk[0] = encodeLevelMap(&maps.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, fstride) ? 1 : 0;
+        const dim3 sgrid((E->fsPlan.nJobs + kFsWarps - 1) / kFsWarps, n);
+        if (E->fastCompass) k_fast_score<true><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, E->dCbits, fb);
+        else k_fast_score<false><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, E->dCbits, fb);
+        k_fast_select<<<dim3((g.nCells + kSelWarps - 1) / kSelWarps, n), kSelWarps * 32, 0, st>>>(E->dGeom, E->dCells, E->fsPlan, E->dCbits,
+                                                                                               E->dCand, E->dCellCount, fb);
+        E->launches += 2;
+    } else {
+        if (E->fastNA > nA0) ORBX_FAST_DISPATCH(st, nA0, E->fastNA - nA0, E->fastRowsA, E->fastSmemA);
+        if (g.nCells > E->fastNA) ORBX_FAST_DISPATCH(st, E->fastNA, g.nCells - E->fastNA, E->fastTileRows, E->fastSmem);
+    }
     if (nA0 > 0) CK(cudaStreamWaitEvent(st, E->evF0[slot], 0));
 #undef ORBX_FAST_DISPATCH
 #undef ORBX_FAST_GROUP
@@ -408,10 +487,12 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
 int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st, int fb = 0) {
     Level0 l0abs = l0;
     int rc = ORBX_OK;
+    const int slot = st == E->stream2 ? 1 : 0;
+    for (int s2 = 0; s2 < 2; ++s2)          // order this pass after earlier passes of the handle that ran on other streams
+        if (E->lastSt[s2] && E->lastSt[s2] != st && (s2 == slot || fb == 0)) CK(cudaStreamWaitEvent(st, E->evDone[s2], 0));
     if (!E->useGraphs || E->timing) {
         rc = launchPass(E, l0, n, lap0, lap1, st, fb);
     } else {
-        const int slot = st == E->stream2 ? 1 : 0;
         Extractor::PassGraph* hit = nullptr;
         for (auto& G : E->graphs)
             if (G.base == l0.base && G.frameBytes == l0.frameBytes && G.pitch == l0.pitch && G.n == n && G.lap0 == lap0 && G.lap1 == lap1 &&
@@ -437,8 +518,17 @@ int runPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t st,
         E->launches += hit->kernels;
     }
     if (rc) return rc;
+    CK(cudaEventRecord(E->evDone[slot], st));
+    E->lastSt[slot] = st;
     if (fb == 0) { E->lastFrames = n; E->lastL0 = l0abs; }
     else E->lastFrames = std::max(E->lastFrames, fb + n);
+    return ORBX_OK;
+}
+
+// wait for every pass launched on this handle, whatever stream it ran on
+int syncPasses(Extractor* E) {
+    for (int s = 0; s < 2; ++s)
+        if (E->lastSt[s]) CK(cudaEventSynchronize(E->evDone[s]));
     return ORBX_OK;
 }
 
@@ -505,12 +595,15 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
         if ((e = cudaEventCreateWithFlags(&E->evFork[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
         if ((e = cudaEventCreateWithFlags(&E->evJoin[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
         if ((e = cudaEventCreateWithFlags(&E->evStart[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
+        if ((e = cudaEventCreateWithFlags(&E->evDone[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
         if ((e = cudaEventCreateWithFlags(&E->evF0[i], cudaEventDisableTiming)) != cudaSuccess) return fail(e);
     }
     if (const char* ov = getenv("ORBX_OVERLAP")) E->overlap = atoi(ov) != 0;
     if (const char* gr = getenv("ORBX_GRAPHS")) E->useGraphs = atoi(gr) != 0;
     if (const char* be = getenv("ORBX_BLUR_EARLY")) E->blurEarly = atoi(be) != 0;
     if (const char* fe = getenv("ORBX_FAST_EARLY")) E->fastEarly = atoi(fe) != 0;
+    if (const char* fg = getenv("ORBX_FAST_GEN")) E->fastGen = atoi(fg) == 1 ? 1 : 2;
+    if (const char* fc = getenv("ORBX_FAST_COMPASS")) E->fastCompass = atoi(fc) != 0;
     {
         int least = 0, greatest = 0;
         cudaDeviceGetStreamPriorityRange(&least, &greatest);
@@ -551,6 +644,7 @@ void orbx_destroy(orbx_handle h) {
         if (E->evFork[i]) cudaEventDestroy(E->evFork[i]);
         if (E->evJoin[i]) cudaEventDestroy(E->evJoin[i]);
         if (E->evStart[i]) cudaEventDestroy(E->evStart[i]);
+        if (E->evDone[i]) { cudaEventSynchronize(E->evDone[i]); cudaEventDestroy(E->evDone[i]); }
         if (E->evF0[i]) cudaEventDestroy(E->evF0[i]);
     }
     delete h;
@@ -733,6 +827,8 @@ int orbx_synchronize(orbx_handle h) {
     if (!h) return ORBX_ERR_INVALID;
     E_FROM(h);
     CK(cudaSetDevice(E->device));
+    int rc = syncPasses(E);
+    if (rc) return rc;
     CK(cudaStreamSynchronize(E->stream));
     return collectStageTimes(E);
 }
@@ -743,6 +839,7 @@ int orbx_results_device(orbx_handle h, int frame, const orbx_keypoint** d_kps, c
     if (frame < 0 || frame >= E->lastFrames) return ORBX_ERR_INVALID;
     CK(cudaSetDevice(E->device));
     int cnt[2];
+    { int rc = syncPasses(E); if (rc) return rc; }
     CK(cudaMemcpyAsync(cnt, E->dOutCnt + 2 * frame, sizeof(cnt), cudaMemcpyDeviceToHost, E->stream));
     CK(cudaStreamSynchronize(E->stream));
     if (d_kps) *d_kps = E->dOutKp + (size_t)frame * E->geom.outCap;
@@ -787,6 +884,7 @@ int orbx_level_size(orbx_handle h, int level, int* width, int* height) {
 
 static int downloadPlane(Extractor* E, const uint8_t* dsrc, int pitch, int w, int hgt, int padded, uint8_t* dst, int dst_stride) {
     std::vector<uint8_t> tmp((size_t)w * hgt);
+    { int rc = syncPasses(E); if (rc) return rc; }
     CK(cudaStreamSynchronize(E->stream));
     CK(cudaMemcpy2D(tmp.data(), w, dsrc, pitch, w, hgt, cudaMemcpyDeviceToHost));
     if (!padded) {
@@ -831,6 +929,7 @@ int orbx_download_candidates(orbx_handle h, int frame, int level, int* out, int 
     E_FROM(h);
     if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
     CK(cudaSetDevice(E->device));
+    { int rc = syncPasses(E); if (rc) return rc; }
     CK(cudaStreamSynchronize(E->stream));
     const DevGeom& g = E->geom;
     const LevelGeom& G = g.lv[level];
@@ -856,6 +955,7 @@ int orbx_download_level_keypoints(orbx_handle h, int frame, int level, int* out,
     E_FROM(h);
     if (frame < 0 || frame >= E->lastFrames || level < 0 || level >= E->cfg.nlevels) return ORBX_ERR_INVALID;
     CK(cudaSetDevice(E->device));
+    { int rc = syncPasses(E); if (rc) return rc; }
     CK(cudaStreamSynchronize(E->stream));
     const DevGeom& g = E->geom;
     const LevelGeom& G = g.lv[level];
@@ -904,7 +1004,7 @@ int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int 
     const int scanCap = std::max(P, 64) + 8;
     const size_t smem = tree_smem_layout(P, scanCap, nullptr, nullptr);
     if (smem > 200 * 1024) return ORBX_ERR_UNSUPPORTED;
-    CK(cudaFuncSetAttribute(k_debug_distribute, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
     std::vector<uint64_t> k(std::max(n, 1));
     for (int i = 0; i < n; ++i)
         k[i] = (uint64_t)(uint32_t)keys[3 * i] | ((uint64_t)(uint32_t)keys[3 * i + 1] << 16) | ((uint64_t)(uint32_t)keys[3 * i + 2] << 32);
@@ -946,6 +1046,8 @@ int orbx_stereo_matches(orbx_handle left, orbx_handle right, float mb, float mbf
         return ORBX_ERR_INVALID;
     }
     CK(cudaSetDevice(EL->device));
+    { Extractor* E = ER; int rc = syncPasses(E); if (rc) return rc; }
+    { int rc = syncPasses(EL); if (rc) return rc; }
     CK(cudaStreamSynchronize(ER->stream));
     const int L = EL->cfg.nlevels, outCap = EL->geom.outCap;
     StereoParams P;

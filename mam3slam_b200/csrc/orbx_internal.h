@@ -4,6 +4,8 @@
 //   lvl[l]      B planes of level l, unpadded, row pitch = align128(w_l).  Level 0 is the input image itself
 //               (copied in on the host path, aliased on the device-resident path).
 //   blur[l]     B planes, same pitch: 7x7 fixed-point Gaussian of level l (the reference's per-level workingMat).
+//   score[l]    B planes, same pitch: FAST strength of every tested pixel (k_fast_score); cbits: one 'strength > minThFAST'
+//               bit per pixel, B x bitsPerFrame uint2 (layout in orbx_kernels_fast.cuh).
 //   cand        B x candCap packed FAST candidates (u32: x_local | y_local<<8 | score<<16 inside the owning cell),
 //               one fixed worst-case slot range per cell; cellCount B x nCells.
 //   qtA/qtB     B x sum_l candCapLevel[l] u64 quadtree keys (x | y<<16 | score<<32), ping-pong buffers.
@@ -12,7 +14,10 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <map>
+#include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/orbx.h"
 
@@ -67,7 +72,23 @@ struct DevGeom {
     LevelGeom lv[kMaxLevels];
     uint8_t* lvl[kMaxLevels];      // base of B planes
     uint8_t* blur[kMaxLevels];
+    uint8_t* score[kMaxLevels];    // FAST strength of every pixel (k_fast_score), same pitch as the level
 };
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize belongs to a (function, device) pair, not to a handle: two extractors with
+// different nfeatures on one GPU (Tracking's 5x initialisation extractor beside the regular one, src/Tracking.cc:591-606), or
+// agents sharing a GPU, would lower each other's limit if every handle wrote its own size.  The limit is therefore only
+// ever RAISED, per device, under a lock; the device must be current.
+inline cudaError_t raise_dyn_smem(const void* kern, int device, size_t bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, size_t> cur;
+    std::lock_guard<std::mutex> lk(mu);
+    size_t& c = cur[std::make_pair(kern, device)];
+    if (bytes <= c) return cudaSuccess;
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) c = bytes;
+    return e;
+}
 
 // Launch with a scheduling priority (cudaLaunchAttributePriority; captured into graph kernel nodes as well).  The short,
 // latency-bound kernels (quadtree, finalize, the tracking step) are given the highest priority so that their CTAs are

@@ -1,0 +1,305 @@
+// E2, second generation: grid-cell FAST as two passes (reference behaviour: src/ORBextractor.cc:781-872; pixel arithmetic
+// = cv::FAST 9/16 with 3x3 non-max suppression, SURVEY.md A3, restated in oracle/cpp/orc_primitives.h).
+//
+//   k_fast_score   image-wide, regular: the FAST strength of EVERY pixel of a level's tested region, written as one byte
+//                  per pixel into a score plane, plus one "strength > minThFAST" bit per pixel.
+//                  The tested regions of the reference's cells tile the level without overlap (cell j tests the columns
+//                  [16 + j*wCell + 3, 16 + (j+1)*wCell + 3)), and a pixel's strength does not depend on its cell, so this
+//                  pass ignores the cell grid.  What IS per cell - neighbours outside the cell count as 0 in the 3x3
+//                  non-max suppression, the iniThFAST -> minThFAST fallback, the raster output order - happens in
+//   k_fast_select  one warp per reference cell: gathers the cell's corner bits, runs the (sparse) non-max suppression
+//                  on the score plane with the cell's own border masks, applies the ini / min rule and writes the
+//                  survivors in raster order (same output format as k_fast_cells: cand + cellCount).
+//
+// k_fast_score is the hot kernel (73-instruction u16x2 min/max network per pixel pair, fast_strength_x2).  Design:
+//   * a WARP owns a 64-px x 28-row patch: lanes 0-15 take the upper 14-row strip, lanes 16-31 the lower one, each lane
+//     4 adjacent pixels.  Its 96 x (28+6) input tile is staged by ONE 3-D TMA tile load (cp.async.bulk.tensor,
+//     tensor = {x, y, frame}, zero fill outside the level) signalled on a per-warp mbarrier; no block barrier anywhere.
+//     Rows are 96 bytes = 24 words, so the two half-warps (14 rows apart = 336 words = 16 mod 32) read disjoint banks:
+//     every LDS is conflict free.
+//   * a lane walks DOWN its 14 rows with a 7-row sliding window held in registers.  A new row costs 3 LDS + 10 ALU ops:
+//     the 10 bytes x-3 .. x+6 are cut into the eight u16x2 operands G(d) = (p[x+d], p[x+d+2]), d = -3..4.  With pixel
+//     lanes (x, x+2) and (x+1, x+3) every ring operand of the first pair is a G(d) and of the second pair G(d+1): no
+//     per-pixel address arithmetic, no shared-memory expansion pass, no ring loads (the first generation spent 17 LDS
+//     + ~55 bookkeeping instructions per pixel pair around the 73-instruction network).
+//   * the strengths of 4 pixels leave as one aligned 32-bit store; the corner bits accumulate in two registers per lane
+//     and leave as one 64-bit store per strip.
+// Layout of the corner bits: cbits[frame][level][strip s][column group q] (uint2), column group q = pixels 16+4q .. +3,
+// strip s = rows 19+14s .. +13; .x bit r = pixel 0 row r, bit 16+r = pixel 2; .y bit r = pixel 1, bit 16+r = pixel 3.
+#pragma once
+#include "orbx_kernels_image.cuh"
+#include <cuda.h>          // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
+
+namespace orbx {
+
+constexpr int kFsRows = 14;                      // rows per strip (one half-warp)
+constexpr int kFsCols = 64;                      // pixels per strip row (16 lanes x 4)
+constexpr int kFsHaloX = 16;                     // the tile starts 16 columns left of the patch: TMA wants the box start 16-byte aligned
+                                                 // in the innermost dimension (x0 - 16 = 64 * cx), the ring needs only 3
+constexpr int kFsBoxW = 96;                      // staged bytes per tile row: columns x0-16 .. x0+79 (x0-3 .. x0+66 used)
+constexpr int kFsBoxH = 2 * kFsRows + 6;         // 34 tile rows: two strips + the 3-row ring halo on both sides
+constexpr int kFsTileBytes = kFsBoxW * kFsBoxH;  // 3264
+constexpr int kFsTileStride = 3328;              // 128-byte multiple (TMA destination alignment)
+constexpr int kFsWarps = 4;
+#ifndef ORBX_FS_MINBLOCKS
+#define ORBX_FS_MINBLOCKS 5            // CTAs per SM the strength kernel is compiled for (96 registers; 4 -> 127 registers, no spill)
+#endif
+constexpr int kFsX0 = 16, kFsY0 = 19;            // first column group starts at x = 16 (aligned stores); first tested row
+
+struct FsLevel { int jobBegin, nCx, nSy, bitsOffset; };          // bitsOffset: in uint2 units inside a frame's cbits
+struct FsPlan { int nJobs, bitsPerFrame; FsLevel lv[kMaxLevels]; };
+struct alignas(64) FsMaps { CUtensorMap m[kMaxLevels]; int tmaOk[kMaxLevels]; };
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// the eight u16x2 operands of one tile row for a lane: o[i] = (p[x+d], p[x+d+2]), d = i-3, from the three words that hold
+// the bytes x-4 .. x+7
+__device__ __forceinline__ void fs_expand(uint32_t (&o)[8], const uint32_t* __restrict__ rp) {
+    const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
+    const uint32_t t = __funnelshift_r(w0, w1, 16), t2 = __funnelshift_r(w1, w2, 16);
+    o[0] = __byte_perm(w0, 0, 0x4341);
+    o[1] = t & 0x00ff00ffu;
+    o[2] = __byte_perm(t, 0, 0x4341);
+    o[3] = w1 & 0x00ff00ffu;
+    o[4] = __byte_perm(w1, 0, 0x4341);
+    o[5] = t2 & 0x00ff00ffu;
+    o[6] = __byte_perm(t2, 0, 0x4341);
+    o[7] = w2 & 0x00ff00ffu;
+}
+
+// Upper bound of the strength from the four compass pixels only: every 9-arc of the ring contains r0 or r8 AND r4 or
+// r12, so min over an arc <= min(max(r0,r8), max(r4,r12)) (bright side; mirrored for the dark side).  A pixel whose bound
+// is <= minThFAST is no corner at either threshold and can never win a non-max comparison against one, so its stored
+// strength may be anything <= minThFAST: 0 is written and the 73-instruction network is skipped (exact).
+__device__ __forceinline__ uint32_t fs_compass_bound(uint32_t v2, uint32_t r0, uint32_t r4, uint32_t r8, uint32_t r12) {
+    const uint32_t A = __vminu2(__vmaxu2(r0, r8), __vmaxu2(r4, r12));
+    const uint32_t B = __vmaxu2(__vminu2(r0, r8), __vminu2(r4, r12));
+    return __vimax3_u16x2(A + (0x01000100u - v2), (v2 + 0x01000100u) - B, 0x01000100u);      // biased by 256 per lane
+}
+
+// ring position k = (dx, dy), index 0 = (0, +3), in the order cv::FAST walks the circle
+#define FS_RING_DX(k) ((k) == 0 ? 0 : (k) == 1 ? 1 : (k) == 2 ? 2 : (k) == 3 ? 3 : (k) == 4 ? 3 : (k) == 5 ? 3 : (k) == 6 ? 2 : (k) == 7 ? 1 : \
+                       (k) == 8 ? 0 : (k) == 9 ? -1 : (k) == 10 ? -2 : (k) == 11 ? -3 : (k) == 12 ? -3 : (k) == 13 ? -3 : (k) == 14 ? -2 : -1)
+#define FS_RING_DY(k) ((k) == 0 ? 3 : (k) == 1 ? 3 : (k) == 2 ? 2 : (k) == 3 ? 1 : (k) == 4 ? 0 : (k) == 5 ? -1 : (k) == 6 ? -2 : (k) == 7 ? -3 : \
+                       (k) == 8 ? -3 : (k) == 9 ? -3 : (k) == 10 ? -2 : (k) == 11 ? -1 : (k) == 12 ? 0 : (k) == 13 ? 1 : (k) == 14 ? 2 : 3)
+
+// grid (ceil(nJobs / 4), B), block 128 = 4 independent warps.  kEarly: warp-uniform compass early-out.
+template <bool kEarly>
+__global__ void __launch_bounds__(kFsWarps * 32, ORBX_FS_MINBLOCKS) k_fast_score(const __grid_constant__ FsMaps maps, const DevGeom* __restrict__ g,
+                                                               Level0 l0, const FsPlan plan, uint2* __restrict__ cbits, int frameBase) {
+    __shared__ __align__(128) uint8_t tiles[kFsWarps][kFsTileStride];
+    __shared__ __align__(8) uint64_t mbar[kFsWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int job = blockIdx.x * kFsWarps + warp;
+    if (job >= plan.nJobs) return;                      // warps are independent: no block-wide barrier below
+    int l = 0;
+    while (l + 1 < g->nlevels && job >= plan.lv[l + 1].jobBegin) ++l;
+    const FsLevel fl = plan.lv[l];
+    const int jl = job - fl.jobBegin;
+    const int sy = jl / fl.nCx, cx = jl - sy * fl.nCx;
+    const int frame = frameBase + blockIdx.y;
+    const LevelGeom& L = g->lv[l];
+    const int x0 = kFsX0 + kFsCols * cx, y0 = kFsY0 + 2 * kFsRows * sy;
+    uint8_t* tile = tiles[warp];
+
+    if (maps.tmaOk[l]) {
+        const uint32_t bar = smem_addr(&mbar[warp]);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kFsTileBytes) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                         :: "r"(smem_addr(tile)), "l"(reinterpret_cast<uint64_t>(&maps.m[l])), "r"(bar), "r"(x0 - kFsHaloX), "r"(y0 - 3), "r"(frame)
+                         : "memory");
+        }
+        __syncwarp();
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar), "r"(0) : "memory");
+    } else {
+        // rows that TMA cannot address (base, pitch or frame size not a multiple of 16 bytes: only a caller's level 0):
+        // the same tile, byte by byte, zero outside the level
+        int pitch;
+        const uint8_t* img = level_ptr(g, l0, l, frame, &pitch);
+        for (int i = lane; i < kFsBoxH * (kFsBoxW / 4); i += 32) {
+            const int ry = i / (kFsBoxW / 4), rw = i - ry * (kFsBoxW / 4);
+            const int y = y0 - 3 + ry, x = x0 - kFsHaloX + 4 * rw;
+            uint32_t v = 0;
+            if (y < L.h) {
+                const uint8_t* rowp = img + (size_t)y * pitch;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) if (x + k < L.w) v |= (uint32_t)rowp[x + k] << (8 * k);
+            }
+            reinterpret_cast<uint32_t*>(tile)[i] = v;
+        }
+        __syncwarp();
+    }
+
+    const int half = lane >> 4, j = lane & 15;
+    const uint32_t* trow = reinterpret_cast<const uint32_t*>(tile) + half * kFsRows * (kFsBoxW / 4) + (kFsHaloX / 4 - 1) + j;
+    const int x = x0 + 4 * j;
+    const int pitch = L.pitch;
+    const int ys = y0 + half * kFsRows;
+    uint8_t* sp = g->score[l] + (size_t)frame * L.planeBytes + (size_t)ys * pitch + x;
+    const int rowsOk = x < pitch ? L.h - ys : 0;        // rows of this lane that lie inside the plane
+    // strengths stay biased by 256 per u16 lane (s + 256 in [256, 511]): the low byte IS the strength, and
+    // s > minTh  <=>  bit 15 of (s + 256) + (0x7eff - minTh)
+    const uint32_t cmp = (0x7effu - (uint32_t)g->minTh) * 0x00010001u;
+
+    uint32_t G[7][8];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) fs_expand(G[k], trow + k * (kFsBoxW / 4));
+    uint32_t accA = 0, accB = 0;
+#pragma unroll 1
+    for (int it = 0; it < kFsRows / 7; ++it) {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            // output row c = 7*it + k uses tile rows c .. c+6, held in window slots (k + dy + 3) % 7
+            fs_expand(G[(k + 6) % 7], trow + (7 * it + k + 6) * (kFsBoxW / 4));
+            const uint32_t vA = G[(k + 3) % 7][3], vB = G[(k + 3) % 7][4];
+            bool run = true;
+            if (kEarly) {
+                const uint32_t bA = fs_compass_bound(vA, G[(k + 6) % 7][3], G[(k + 3) % 7][6], G[k % 7][3], G[(k + 3) % 7][0]);
+                const uint32_t bB = fs_compass_bound(vB, G[(k + 6) % 7][4], G[(k + 3) % 7][7], G[k % 7][4], G[(k + 3) % 7][1]);
+                run = __any_sync(0xffffffffu, (((bA + cmp) | (bB + cmp)) & 0x80008000u) != 0);
+            }
+            uint32_t sA = 0x01000100u, sB = 0x01000100u;
+            if (run) {
+                uint32_t rA[16], rB[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    rA[i] = G[(k + 3 + FS_RING_DY(i)) % 7][FS_RING_DX(i) + 3];
+                    rB[i] = G[(k + 3 + FS_RING_DY(i)) % 7][FS_RING_DX(i) + 4];
+                }
+                sA = fast_strength_biased_x2(vA, rA);
+                sB = fast_strength_biased_x2(vB, rB);
+            }
+            if (7 * it + k < rowsOk) *reinterpret_cast<uint32_t*>(sp) = __byte_perm(sA, sB, 0x6240);      // s(x), s(x+1), s(x+2), s(x+3)
+            sp += pitch;
+            accA = ((accA >> 1) & 0x7fff7fffu) | ((sA + cmp) & 0x80008000u);
+            accB = ((accB >> 1) & 0x7fff7fffu) | ((sB + cmp) & 0x80008000u);
+        }
+    }
+    // row c sits at bit c + 16 - kFsRows of each half
+    accA = (accA >> (16 - kFsRows)) & 0x3fff3fffu;
+    accB = (accB >> (16 - kFsRows)) & 0x3fff3fffu;
+    cbits[(size_t)frame * plan.bitsPerFrame + fl.bitsOffset + (size_t)(2 * sy + half) * (16 * fl.nCx) + 16 * cx + j] = make_uint2(accA, accB);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One warp per reference FAST cell (src/ORBextractor.cc:805-868).  grid (ceil(nCells / 4), B), block 128.
+constexpr int kSelWarps = 4;
+constexpr int kSelMaxWords = 256;                // raster bitmap of a cell: <= 8192 pixel slots (checked on the host)
+constexpr int kSelList = 32 * 2 * kFsRows;       // corners one round of 32 bit words can hold
+
+__global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
+                                                                const FsPlan plan, const uint2* __restrict__ cbits,
+                                                                uint32_t* __restrict__ cand, int* __restrict__ cellCount, int frameBase) {
+    __shared__ uint32_t sKeep[kSelWarps][2][kSelMaxWords];       // survivors of the 3x3 NMS at minThFAST / iniThFAST, raster order
+    __shared__ uint16_t sList[kSelWarps][kSelList];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int cellId = blockIdx.x * kSelWarps + warp;
+    if (cellId >= g->nCells) return;
+    const FastCell c = cells[cellId];
+    const int frame = frameBase + blockIdx.y;
+    const LevelGeom& L = g->lv[c.level];
+    const FsLevel fl = plan.lv[c.level];
+    const int pitch = L.pitch;
+    const uint8_t* S = g->score[c.level] + (size_t)frame * L.planeBytes + (size_t)c.y0 * pitch + c.x0;    // cell origin
+    const uint32_t* bits = reinterpret_cast<const uint32_t*>(cbits + (size_t)frame * plan.bitsPerFrame + fl.bitsOffset);
+    const int w = c.w, h = c.h;
+    const int nG = 16 * fl.nCx;
+    const int sLo = (c.y0 - kFsY0) / kFsRows, sHi = (c.y0 + h - 1 - kFsY0) / kFsRows;
+    const int gLo = (c.x0 - kFsX0) >> 2, gHi = (c.x0 + w - 1 - kFsX0) >> 2;
+    const int nGc = gHi - gLo + 1;
+    const int nW = (sHi - sLo + 1) * nGc * 2;
+    const int nwr = (w * h + 31) >> 5;
+    uint32_t* keepMin = sKeep[warp][0];
+    uint32_t* keepIni = sKeep[warp][1];
+    for (int i = lane; i < nwr; i += 32) { keepMin[i] = 0; keepIni[i] = 0; }
+    __syncwarp();
+    const int iniTh = g->iniTh;
+    uint16_t* list = sList[warp];
+
+    for (int base = 0; base < nW; base += 32) {
+        const int i = base + lane;
+        uint32_t word = 0;
+        int xs = 0, ys = 0;
+        if (i < nW) {
+            const int k = i & 1, t = i >> 1;
+            const int s = t / nGc, q = t - s * nGc;
+            word = bits[((size_t)(sLo + s) * nG + gLo + q) * 2 + k];
+            xs = kFsX0 + 4 * (gLo + q) + k - c.x0;               // local x of the low half's pixel; the high half's is xs + 2
+            ys = kFsY0 + kFsRows * (sLo + s) - c.y0;             // local y of bit 0
+            const int rlo = max(-ys, 0), rhi = min(h - 1 - ys, kFsRows - 1);
+            const uint32_t rowmask = ((2u << rhi) - 1u) & ~((1u << rlo) - 1u);
+            uint32_t m = 0;
+            if (xs >= 0 && xs < w) m |= rowmask;
+            if (xs + 2 >= 0 && xs + 2 < w) m |= rowmask << 16;
+            word &= m;
+        }
+        const int cnt = __popc(word);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        int pos = incl - cnt;
+        while (word) {
+            const int b = __ffs(word) - 1;
+            word &= word - 1;
+            list[pos++] = (uint16_t)((xs + 2 * (b >> 4)) | ((ys + (b & 15)) << 8));
+        }
+        __syncwarp();
+        // 3x3 non-max suppression of the listed corners, balanced over the lanes.  Neighbours outside the cell's tested
+        // interior count as 0, exactly like a cv::FAST call on the cell's sub-image; a neighbour at or below minThFAST can
+        // never beat a corner, so comparing raw strengths is the same test at either threshold.
+        for (int q = lane; q < total; q += 32) {
+            const int e = list[q];
+            const int lx = e & 255, ly = e >> 8;
+            const uint8_t* sc = S + (size_t)ly * pitch + lx;
+            const int s = sc[0];
+            const bool Lf = lx > 0, Rt = lx < w - 1, Up = ly > 0, Dn = ly < h - 1;
+            const int a0 = Lf ? sc[-1] : 0, a1 = Rt ? sc[1] : 0;
+            const int u0 = Up && Lf ? sc[-pitch - 1] : 0, u1 = Up ? sc[-pitch] : 0, u2 = Up && Rt ? sc[-pitch + 1] : 0;
+            const int d0 = Dn && Lf ? sc[pitch - 1] : 0, d1 = Dn ? sc[pitch] : 0, d2 = Dn && Rt ? sc[pitch + 1] : 0;
+            const int nb = __vimax3_s32(__vimax3_s32(u0, u1, u2), __vimax3_s32(d0, d1, d2), max(a0, a1));
+            if (s > nb) {
+                const int p = ly * w + lx;
+                atomicOr(&keepMin[p >> 5], 1u << (p & 31));
+                if (s > iniTh) atomicOr(&keepIni[p >> 5], 1u << (p & 31));
+            }
+        }
+        __syncwarp();
+    }
+
+    // cells keep the iniThFAST survivors, or the minThFAST ones when there are none (:826-846); raster order
+    const int per = (nwr + 31) >> 5;
+    const int wb = lane * per, we = min(wb + per, nwr);
+    uint32_t anyI = 0;
+    for (int i = wb; i < we; ++i) anyI |= keepIni[i];
+    const uint32_t* keep = __any_sync(0xffffffffu, anyI != 0) ? keepIni : keepMin;
+    int cnt = 0;
+    for (int i = wb; i < we; ++i) cnt += __popc(keep[i]);
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    int rank = incl - cnt;
+    uint32_t* out = cand + (size_t)frame * g->candCapFrame + c.outOffset;
+    const uint32_t inv = w > 1 ? 0xffffffffu / (uint32_t)w + 1u : 0u;          // p / w = umulhi(p, inv) for p < 2^16
+    for (int i = wb; i < we; ++i) {
+        uint32_t m = keep[i];
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            const int p = i * 32 + b;
+            const int py = w > 1 ? (int)__umulhi((uint32_t)p, inv) : p, px = p - py * w;
+            const int s = S[(size_t)py * pitch + px];
+            out[rank++] = (uint32_t)px | ((uint32_t)py << 8) | ((uint32_t)(s - 1) << 16);
+        }
+    }
+    if (lane == 0) cellCount[(size_t)frame * g->nCells + cellId] = total;
+}
+
+}  // namespace orbx

@@ -187,7 +187,8 @@ constexpr int kFastThreads = 256;          // widest variant; a cell may hold at
 // with min(C_k) = min(qq[k], qq[k+2]), qq[k] = min(q[k], q[k+1]), q[k] = min(r[2k+1], r[2k+2]).  Per side: 8 + 8 + 8
 // two-input ops, 8 three-input ops and a 4-op reduction = 36 instructions / 47 pipe slots (the plain sliding-window form,
 // min3 over min3, took 40 / 79).  Pure min / max identities: the result is bit-identical.
-__device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t (&r)[16]) {
+// fast_strength_biased_x2 returns s + 256 in each u16 lane (the callers that pack bytes or test bit patterns use it as is).
+__device__ __forceinline__ uint32_t fast_strength_biased_x2(uint32_t v2, const uint32_t (&r)[16]) {
     uint32_t q[8], Q[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -213,8 +214,11 @@ __device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t
     A = __vimax3_u16x2(A, a[5], a[6]); B = __vimin3_u16x2(B, b[5], b[6]);
     A = __vmaxu2(A, a[7]); B = __vminu2(B, b[7]);
     // per lane: A + 256 - v and v + 256 - B are in [1, 511]: no borrow between the two u16 lanes
-    const uint32_t s = __vimax3_u16x2(A + (0x01000100u - v2), (v2 + 0x01000100u) - B, 0x01000100u);
-    return s - 0x01000100u;
+    return __vimax3_u16x2(A + (0x01000100u - v2), (v2 + 0x01000100u) - B, 0x01000100u);
+}
+
+__device__ __forceinline__ uint32_t fast_strength_x2(uint32_t v2, const uint32_t (&r)[16]) {
+    return fast_strength_biased_x2(v2, r) - 0x01000100u;
 }
 
 // One CTA per reference FAST cell.  The cell's pixels (+3 ring halo) are read with aligned 32-bit loads and expanded in
