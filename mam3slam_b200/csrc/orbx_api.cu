@@ -66,8 +66,9 @@ struct Extractor {
     int fastGen = 2;                 // ORBX_FAST_GEN=1: the first-generation one-CTA-per-cell kernel (A/B switch)
     bool fastCompass = false;        // ORBX_FAST_COMPASS=1: warp-uniform compass early-out in the strength pass
     FsPlan fsPlan{};
-    FsMaps fsMaps{};
-    uint2* dCbits = nullptr;
+    FsMaps fsMaps{}, scoreMaps{};    // tensor maps of the pyramid levels (level 0 per pass) and of the score planes
+    NmsTabs nmsTabs{};               // same-cell column / row masks of the non-max suppression
+    uint2* dCbits = nullptr;         // survivor bits (k_fast_nms -> k_fast_select)
     int poolCap = 0, scanCap = 0;
     int maxLevelW4 = 0;
 
@@ -120,13 +121,13 @@ EncodeTiledFn tensorMapEncoder() {
 
 // 3-D u8 tensor {x, y, frame} of one pyramid level for k_fast_score's tile loads.  false: TMA cannot address it (base, row
 // pitch or frame stride not a multiple of 16 bytes) and the kernel stages that level with plain loads.
-bool encodeLevelMap(CUtensorMap* m, const uint8_t* base, int w, int h, int frames, size_t pitch, size_t frameBytes) {
+bool encodeLevelMap(CUtensorMap* m, const uint8_t* base, int w, int h, int frames, size_t pitch, size_t frameBytes, int boxH = kFsBoxH) {
     EncodeTiledFn enc = tensorMapEncoder();
     static const bool off = getenv("ORBX_FAST_TMA") && atoi(getenv("ORBX_FAST_TMA")) == 0;      // A/B switch: plain-load staging
     if (off || !enc || (((uintptr_t)base | pitch | frameBytes) & 15) != 0 || frames < 1) return false;
     const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frameBytes};
-    const cuuint32_t box[3] = {(cuuint32_t)kFsBoxW, (cuuint32_t)kFsBoxH, 1};
+    const cuuint32_t box[3] = {(cuuint32_t)kFsBoxW, (cuuint32_t)boxH, 1};
     const cuuint32_t es[3] = {1, 1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -352,8 +353,37 @@ int configureShape(Extractor* E, int W, int H) {
     if ((rc = devAlloc(E, &E->dCellCount, (size_t)g.nCells * B))) return rc;
     if ((rc = devAlloc(E, &E->dCbits, (size_t)E->fsPlan.bitsPerFrame * B))) return rc;
     memset(&E->fsMaps, 0, sizeof(E->fsMaps));
-    for (int l = 1; l < L; ++l)
-        E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
+    memset(&E->scoreMaps, 0, sizeof(E->scoreMaps));
+    for (int l = 0; l < L; ++l) {
+        if (l > 0) E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
+        E->scoreMaps.tmaOk[l] = encodeLevelMap(&E->scoreMaps.m[l], g.score[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kNmsBoxH) ? 1 : 0;
+    }
+    {
+        // same-cell masks of the 3x3 suppression.  The cells of a level form a regular grid (src/ORBextractor.cc:805-821: the
+        // column range depends only on j, the row range only on i), so "neighbour in the same cell" = column test AND row test.
+        // col[x]: bit 0 = x-1 is in x's cell column, bit 1 = x+1 is, bit 2 = x is in some cell column.
+        // row[y]: {0 / ~0: the row above counts, the row below counts, 0 / 0x80008000: y is in some cell row, 0}
+        std::vector<uint8_t> col; std::vector<uint4> row;
+        NmsTabs& T = E->nmsTabs;
+        for (int l = 0; l < L; ++l) {
+            const int nc = kFsX0 + kFsCols * E->fsPlan.lv[l].nCx + 8, nr = kFsY0 + 2 * kFsRows * E->fsPlan.lv[l].nSy + 8;
+            T.colOff[l] = (int)col.size(); T.rowOff[l] = (int)row.size();
+            col.resize(col.size() + ((nc + 3) & ~3), 0);
+            row.resize(row.size() + nr, make_uint4(0, 0, 0, 0));
+            uint8_t* C = col.data() + T.colOff[l]; uint4* R = row.data() + T.rowOff[l];
+            for (int ci = g.lv[l].cellBegin; ci < g.lv[l].cellEnd; ++ci) {
+                const FastCell& c = E->cells[ci];
+                for (int x = c.x0; x < c.x0 + c.w; ++x) C[x] = (uint8_t)(4 | (x > c.x0 ? 1 : 0) | (x < c.x0 + c.w - 1 ? 2 : 0));
+                for (int y = c.y0; y < c.y0 + c.h; ++y) R[y] = make_uint4(y > c.y0 ? ~0u : 0u, y < c.y0 + c.h - 1 ? ~0u : 0u, 0x80008000u, 0u);
+            }
+        }
+        uint8_t* dCol = nullptr; uint4* dRow = nullptr;
+        if ((rc = devAlloc(E, &dCol, col.size()))) return rc;
+        if ((rc = devAlloc(E, &dRow, row.size()))) return rc;
+        CK(cudaMemcpy(dCol, col.data(), col.size(), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(dRow, row.data(), row.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+        T.col = dCol; T.row = dRow;
+    }
     if ((rc = devAlloc(E, &E->dQtA, g.qtCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dQtB, g.qtCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dLvlKp, (size_t)g.kpCapFrame * B))) return rc;
@@ -442,11 +472,12 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         const size_t fstride = (fb + n == 1) ? (((size_t)l0.pitch * g.lv[0].h + 15) & ~(size_t)15) : l0.frameBytes;
         maps.tmaOk[0] = encodeLevelMap(&maps.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, fstride) ? 1 : 0;
         const dim3 sgrid((E->fsPlan.nJobs + kFsWarps - 1) / kFsWarps, n);
-        if (E->fastCompass) k_fast_score<true><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, E->dCbits, fb);
-        else k_fast_score<false><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, E->dCbits, fb);
+        if (E->fastCompass) k_fast_score<true><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, fb);
+        else k_fast_score<false><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, fb);
+        k_fast_nms<<<sgrid, kFsWarps * 32, 0, st>>>(E->scoreMaps, E->dGeom, E->fsPlan, E->nmsTabs, E->dCbits, fb);
         k_fast_select<<<dim3((g.nCells + kSelWarps - 1) / kSelWarps, n), kSelWarps * 32, 0, st>>>(E->dGeom, E->dCells, E->fsPlan, E->dCbits,
                                                                                                E->dCand, E->dCellCount, fb);
-        E->launches += 2;
+        E->launches += 3;
     } else {
         if (E->fastNA > nA0) ORBX_FAST_DISPATCH(st, nA0, E->fastNA - nA0, E->fastRowsA, E->fastSmemA);
         if (g.nCells > E->fastNA) ORBX_FAST_DISPATCH(st, E->fastNA, g.nCells - E->fastNA, E->fastTileRows, E->fastSmem);

@@ -86,7 +86,7 @@ __device__ __forceinline__ uint32_t fs_compass_bound(uint32_t v2, uint32_t r0, u
 // grid (ceil(nJobs / 4), B), block 128 = 4 independent warps.  kEarly: warp-uniform compass early-out.
 template <bool kEarly>
 __global__ void __launch_bounds__(kFsWarps * 32, ORBX_FS_MINBLOCKS) k_fast_score(const __grid_constant__ FsMaps maps, const DevGeom* __restrict__ g,
-                                                               Level0 l0, const FsPlan plan, uint2* __restrict__ cbits, int frameBase) {
+                                                               Level0 l0, const FsPlan plan, int frameBase) {
     __shared__ __align__(128) uint8_t tiles[kFsWarps][kFsTileStride];
     __shared__ __align__(8) uint64_t mbar[kFsWarps];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -146,11 +146,11 @@ __global__ void __launch_bounds__(kFsWarps * 32, ORBX_FS_MINBLOCKS) k_fast_score
     // strengths stay biased by 256 per u16 lane (s + 256 in [256, 511]): the low byte IS the strength, and
     // s > minTh  <=>  bit 15 of (s + 256) + (0x7eff - minTh)
     const uint32_t cmp = (0x7effu - (uint32_t)g->minTh) * 0x00010001u;
+    (void)cmp;
 
     uint32_t G[7][8];
 #pragma unroll
     for (int k = 0; k < 6; ++k) fs_expand(G[k], trow + k * (kFsBoxW / 4));
-    uint32_t accA = 0, accB = 0;
 #pragma unroll 1
     for (int it = 0; it < kFsRows / 7; ++it) {
 #pragma unroll
@@ -177,21 +177,128 @@ __global__ void __launch_bounds__(kFsWarps * 32, ORBX_FS_MINBLOCKS) k_fast_score
             }
             if (7 * it + k < rowsOk) *reinterpret_cast<uint32_t*>(sp) = __byte_perm(sA, sB, 0x6240);      // s(x), s(x+1), s(x+2), s(x+3)
             sp += pitch;
-            accA = ((accA >> 1) & 0x7fff7fffu) | ((sA + cmp) & 0x80008000u);
-            accB = ((accB >> 1) & 0x7fff7fffu) | ((sB + cmp) & 0x80008000u);
         }
     }
-    // row c sits at bit c + 16 - kFsRows of each half
-    accA = (accA >> (16 - kFsRows)) & 0x3fff3fffu;
-    accB = (accB >> (16 - kFsRows)) & 0x3fff3fffu;
-    cbits[(size_t)frame * plan.bitsPerFrame + fl.bitsOffset + (size_t)(2 * sy + half) * (16 * fl.nCx) + 16 * cx + j] = make_uint2(accA, accB);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// One warp per reference FAST cell (src/ORBextractor.cc:805-868).  grid (ceil(nCells / 4), B), block 128.
+// 3x3 non-max suppression, dense and SIMD, image-wide (same warp patches and lane layout as k_fast_score).
+// cv::FAST keeps a corner iff its score exceeds all 8 neighbours' scores INSIDE the sub-image it was called on
+// (src/ORBextractor.cc:826: one call per cell), so a neighbour that lies in another cell's tested interior counts as 0.
+// The cells of a level form a regular grid, hence "same cell" separates into a column test and a row test: colTab[x] says
+// whether x-1 / x+1 belong to the same cell column as x (and whether x is in any cell), rowTab[y] the same for rows, as
+// ready-made AND masks.  On the synthetic stream ~80 % of the pixels exceed minThFAST, so the suppression is done for every
+// pixel in u16x2 lanes (~16 instructions per pixel pair) rather than per corner; its output - one bit per SURVIVOR - is
+// sparse (<= 1/4 of the pixels by construction, ~3 % here).  A survivor at minThFAST that also exceeds iniThFAST is a
+// survivor at iniThFAST (the comparison is on raw strengths), so one bit plane serves both thresholds.
+// Score tile: 96 x 30 bytes by one TMA tile load per warp (rows y0-1 .. y0+28).
+constexpr int kNmsBoxH = 2 * kFsRows + 2;
+constexpr int kNmsTileBytes = kFsBoxW * kNmsBoxH;     // 2880
+constexpr int kNmsTileStride = 2944;                  // 128-byte multiple
+
+struct NmsTabs { const uint8_t* col; const uint4* row; int colOff[kMaxLevels], rowOff[kMaxLevels]; };
+
+__global__ void __launch_bounds__(kFsWarps * 32) k_fast_nms(const __grid_constant__ FsMaps smaps, const DevGeom* __restrict__ g,
+                                                            const FsPlan plan, const NmsTabs tabs, uint2* __restrict__ sbits, int frameBase) {
+    __shared__ __align__(128) uint8_t tiles[kFsWarps][kNmsTileStride];
+    __shared__ __align__(8) uint64_t mbar[kFsWarps];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int job = blockIdx.x * kFsWarps + warp;
+    if (job >= plan.nJobs) return;
+    int l = 0;
+    while (l + 1 < g->nlevels && job >= plan.lv[l + 1].jobBegin) ++l;
+    const FsLevel fl = plan.lv[l];
+    const int jl = job - fl.jobBegin;
+    const int sy = jl / fl.nCx, cx = jl - sy * fl.nCx;
+    const int frame = frameBase + blockIdx.y;
+    const LevelGeom& L = g->lv[l];
+    const int x0 = kFsX0 + kFsCols * cx, y0 = kFsY0 + 2 * kFsRows * sy;
+    uint8_t* tile = tiles[warp];
+    if (smaps.tmaOk[l]) {
+        const uint32_t bar = smem_addr(&mbar[warp]);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kNmsTileBytes) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                         :: "r"(smem_addr(tile)), "l"(reinterpret_cast<uint64_t>(&smaps.m[l])), "r"(bar), "r"(x0 - kFsHaloX), "r"(y0 - 1), "r"(frame)
+                         : "memory");
+        }
+        __syncwarp();
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar), "r"(0) : "memory");
+    } else {
+        const uint8_t* S = g->score[l] + (size_t)frame * L.planeBytes;
+        for (int i = lane; i < kNmsBoxH * (kFsBoxW / 4); i += 32) {
+            const int ry = i / (kFsBoxW / 4), rw = i - ry * (kFsBoxW / 4);
+            const int y = y0 - 1 + ry, x = x0 - kFsHaloX + 4 * rw;
+            uint32_t v = 0;
+            if (y < L.h && x + 3 < L.pitch) v = *reinterpret_cast<const uint32_t*>(S + (size_t)y * L.pitch + x);
+            if (y < L.h && x + 3 >= L.w) {                       // the plane's padding columns are not part of the level
+#pragma unroll
+                for (int k = 0; k < 4; ++k) if (x + k >= L.w) v &= ~(0xffu << (8 * k));
+            }
+            reinterpret_cast<uint32_t*>(tile)[i] = v;
+        }
+        __syncwarp();
+    }
+
+    const int half = lane >> 4, j = lane & 15;
+    const uint32_t* trow = reinterpret_cast<const uint32_t*>(tile) + half * kFsRows * (kFsBoxW / 4) + (kFsHaloX / 4 - 1) + j;
+    const int x = x0 + 4 * j;
+    const int ys = y0 + half * kFsRows;
+    // column masks of this lane's four pixels: pair A = (x, x+2), pair B = (x+1, x+3)
+    const uint32_t cf = *reinterpret_cast<const uint32_t*>(tabs.col + tabs.colOff[l] + x);
+    const uint32_t f0 = cf & 255u, f1 = (cf >> 8) & 255u, f2 = (cf >> 16) & 255u, f3 = cf >> 24;
+    const uint32_t al = (f0 & 1u ? 0x000000ffu : 0u) | (f2 & 1u ? 0x00ff0000u : 0u);
+    const uint32_t ar = (f0 & 2u ? 0x000000ffu : 0u) | (f2 & 2u ? 0x00ff0000u : 0u);
+    const uint32_t bl = (f1 & 1u ? 0x000000ffu : 0u) | (f3 & 1u ? 0x00ff0000u : 0u);
+    const uint32_t br = (f1 & 2u ? 0x000000ffu : 0u) | (f3 & 2u ? 0x00ff0000u : 0u);
+    const uint32_t inA = (f0 & 4u ? 0x00008000u : 0u) | (f2 & 4u ? 0x80000000u : 0u);
+    const uint32_t inB = (f1 & 4u ? 0x00008000u : 0u) | (f3 & 4u ? 0x80000000u : 0u);
+    const uint32_t cmp = (0x7fffu - (uint32_t)g->minTh) * 0x00010001u;       // s > minTh  <=>  bit 15 of s + cmp
+    const uint4* rtab = tabs.row + tabs.rowOff[l] + ys;
+
+    uint32_t hA[3], hB[3], cA[2], cB[2], lA[2], lB[2];      // rolling: row maxima of 3 rows, centre + left/right maxima of 2
+    uint32_t accA = 0, accB = 0;
+#pragma unroll
+    for (int r = 0; r < kFsRows + 2; ++r) {
+        const uint32_t* rp = trow + r * (kFsBoxW / 4);
+        const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
+        const uint32_t Al = __funnelshift_r(w0, w1, 24) & al;          // (x-1, x+1) where they are same-cell neighbours
+        const uint32_t A = w1 & 0x00ff00ffu;                            // (x, x+2)
+        const uint32_t Bc = __byte_perm(w1, 0, 0x4341);                 // (x+1, x+3)
+        const uint32_t Ar = Bc & ar, Bl = A & bl;
+        const uint32_t Br = __funnelshift_r(w1, w2, 16) & br;           // (x+2, x+4)
+        hA[r % 3] = __vimax3_u16x2(Al, A, Ar);
+        hB[r % 3] = __vimax3_u16x2(Bl, Bc, Br);
+        cA[r % 2] = A; cB[r % 2] = Bc;
+        lA[r % 2] = __vmaxu2(Al, Ar); lB[r % 2] = __vmaxu2(Bl, Br);
+        if (r >= 2) {
+            // output row r-2 of the strip: centre = tile row r-1, above = r-2, below = r
+            const uint4 rm = rtab[r - 2];                               // {above counts, below counts, row is inside a cell}
+            const uint32_t nbA = __vimax3_u16x2(hA[(r - 2) % 3] & rm.x, hA[r % 3] & rm.y, lA[(r - 1) % 2]);
+            const uint32_t nbB = __vimax3_u16x2(hB[(r - 2) % 3] & rm.x, hB[r % 3] & rm.y, lB[(r - 1) % 2]);
+            const uint32_t sA = cA[(r - 1) % 2], sB = cB[(r - 1) % 2];
+            const uint32_t tA = ((sA + 0x7fff7fffu) - nbA) & (sA + cmp) & (inA & rm.z);      // s > nb  &&  s > minTh  &&  inside
+            const uint32_t tB = ((sB + 0x7fff7fffu) - nbB) & (sB + cmp) & (inB & rm.z);
+            accA = ((accA >> 1) & 0x7fff7fffu) | tA;
+            accB = ((accB >> 1) & 0x7fff7fffu) | tB;
+        }
+    }
+    accA = (accA >> (16 - kFsRows)) & 0x3fff3fffu;                       // row c sits at bit c + 16 - kFsRows of each half
+    accB = (accB >> (16 - kFsRows)) & 0x3fff3fffu;
+    sbits[(size_t)frame * plan.bitsPerFrame + fl.bitsOffset + (size_t)(2 * sy + half) * (16 * fl.nCx) + 16 * cx + j] = make_uint2(accA, accB);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// One warp per reference FAST cell (src/ORBextractor.cc:805-868): gathers the cell's survivor bits (sparse), applies the
+// iniThFAST / minThFAST rule and writes the survivors in raster order.  grid (ceil(nCells / 4), B), block 128.
 constexpr int kSelWarps = 4;
 constexpr int kSelMaxWords = 256;                // raster bitmap of a cell: <= 8192 pixel slots (checked on the host)
-constexpr int kSelList = 32 * 2 * kFsRows;       // corners one round of 32 bit words can hold
+constexpr int kSelList = 32 * 2 * kFsRows;       // survivors one round of 32 bit words can hold
 
 __global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
                                                                 const FsPlan plan, const uint2* __restrict__ cbits,
@@ -251,24 +358,14 @@ __global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* _
             list[pos++] = (uint16_t)((xs + 2 * (b >> 4)) | ((ys + (b & 15)) << 8));
         }
         __syncwarp();
-        // 3x3 non-max suppression of the listed corners, balanced over the lanes.  Neighbours outside the cell's tested
-        // interior count as 0, exactly like a cv::FAST call on the cell's sub-image; a neighbour at or below minThFAST can
-        // never beat a corner, so comparing raw strengths is the same test at either threshold.
+        // the listed pixels survived the 3x3 suppression (k_fast_nms); file them in raster order, at both thresholds
         for (int q = lane; q < total; q += 32) {
             const int e = list[q];
             const int lx = e & 255, ly = e >> 8;
-            const uint8_t* sc = S + (size_t)ly * pitch + lx;
-            const int s = sc[0];
-            const bool Lf = lx > 0, Rt = lx < w - 1, Up = ly > 0, Dn = ly < h - 1;
-            const int a0 = Lf ? sc[-1] : 0, a1 = Rt ? sc[1] : 0;
-            const int u0 = Up && Lf ? sc[-pitch - 1] : 0, u1 = Up ? sc[-pitch] : 0, u2 = Up && Rt ? sc[-pitch + 1] : 0;
-            const int d0 = Dn && Lf ? sc[pitch - 1] : 0, d1 = Dn ? sc[pitch] : 0, d2 = Dn && Rt ? sc[pitch + 1] : 0;
-            const int nb = __vimax3_s32(__vimax3_s32(u0, u1, u2), __vimax3_s32(d0, d1, d2), max(a0, a1));
-            if (s > nb) {
-                const int p = ly * w + lx;
-                atomicOr(&keepMin[p >> 5], 1u << (p & 31));
-                if (s > iniTh) atomicOr(&keepIni[p >> 5], 1u << (p & 31));
-            }
+            const int s = S[(size_t)ly * pitch + lx];
+            const int p = ly * w + lx;
+            atomicOr(&keepMin[p >> 5], 1u << (p & 31));
+            if (s > iniTh) atomicOr(&keepIni[p >> 5], 1u << (p & 31));
         }
         __syncwarp();
     }
