@@ -161,6 +161,20 @@ int orbm_knn(orbm_handle h, orbm_db db, const uint8_t* q, int nq, int k, uint16_
 /* device-resident variant: d_q, d_dist, d_idx are device pointers; asynchronous on `stream` (NULL = handle stream) */
 int orbm_knn_device(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx,
                     void* stream);
+/* Allocation-free variant of orbm_knn_device.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same result bit for bit; the call itself performs no cudaMalloc / cudaFree / allocating
+ * library call.  Its scratch (per-chunk partial top-k lists) is a file-scope device array of ORBM_KNN_STATIC_MAX_ENTRIES
+ * 64-bit keys (8 MiB) that every GPU loading the library holds until the process exits.  The call needs
+ * chunks x nq x k entries (chunks ~ 4 x SM count / ceil(nq / 256): ~74 on a B200 at nq = 2000); larger requests return
+ * ORBM_ERR_CAPACITY with the numbers in orbm_last_error().  The database must be device-resident
+ * (orbm_db_create(..., rows_on_device = 1, ...), created beforehand).  The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress): make that one call outside stream capture.  All calls on a device SHARE the array, which keeps the
+ * previous call's contents (nothing needs to start at zero: every entry read is written first by the same call): calls
+ * that overlap on the GPU - different streams, concurrent graph replays - race and must be serialised by the caller. */
+#define ORBM_KNN_STATIC_MAX_ENTRIES (1u << 20)
+int orbm_knn_device_static(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist,
+                           int32_t* d_idx, void* stream);
 /* merge of per-shard top-k lists (nshards x nq x k, e.g. after an all-gather): same tie rule on global row ids */
 int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq, int k, uint16_t* out_dist,
                    int32_t* out_idx);

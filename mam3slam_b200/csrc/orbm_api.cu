@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -797,6 +798,69 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
         k_knn<1, kKnnMaxK><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
                                                                           db->rowOffset, (int)rowsPerChunk, k, M->knnPart);
     k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx);
+    M->launches += 2;
+    M->lastEvals = (long long)nq * db->n;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+// ---- allocation-free k-NN (no counterpart in the reference) ----------------
+// Same search as orbm_knn_device, for callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+// that forbid it).  The per-chunk partial top-k lists - the scratch orbm_knn_device keeps in a cudaMalloc'ed buffer - live in a
+// file-scope device array of fixed size: ORBM_KNN_STATIC_MAX_ENTRIES 64-bit keys = 8 MiB, held by every GPU that loads the
+// library until the process exits.  Host code must not hand the array's NAME to a kernel (on the host it is a stand-in, not a
+// device address): the address is resolved once per device with cudaGetSymbolAddress, with that device current.
+// Nothing in the array has to start at zero: k_knn writes every entry k_knn_merge reads (chunk < nchunks, query < nq, slot <
+// k) in the same call, so the contents left by the previous call are never read.  All calls share the one array per device:
+// calls that overlap on the GPU (different streams, or graphs replayed concurrently) race - serialise them.
+static __device__ __align__(256) unsigned long long g_knnStaticPart[ORBM_KNN_STATIC_MAX_ENTRIES];
+
+namespace {
+constexpr int kMaxDevicesStatic = 64;
+unsigned long long* g_knnStaticPtr[kMaxDevicesStatic] = {};
+std::mutex g_knnStaticMu;
+
+// device address of g_knnStaticPart on `device` (which must be current); resolved once per device
+cudaError_t knnStaticAddress(int device, unsigned long long** out) {
+    std::lock_guard<std::mutex> lk(g_knnStaticMu);
+    if (device < 0 || device >= kMaxDevicesStatic) return cudaErrorInvalidDevice;
+    if (!g_knnStaticPtr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_knnStaticPart);
+        if (e != cudaSuccess) return e;
+        g_knnStaticPtr[device] = static_cast<unsigned long long*>(p);
+    }
+    *out = g_knnStaticPtr[device];
+    return cudaSuccess;
+}
+}  // namespace
+
+int orbm_knn_device_static(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
+    if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
+    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    // the chunking of orbm_knn_device (one query per thread): the result does not depend on it, the scratch size does
+    const int qblocks = (nq + kKnnThreads - 1) / kKnnThreads;
+    const long long target = std::max<long long>(1, ((long long)M->smCount * 4 + qblocks - 1) / qblocks);
+    long long rowsPerChunk = (db->n + target - 1) / target;
+    rowsPerChunk = std::max<long long>(kKnnTileRows, (rowsPerChunk + kKnnTileRows - 1) / kKnnTileRows * kKnnTileRows);
+    rowsPerChunk = std::min<long long>(rowsPerChunk, 1LL << 22);
+    const int nchunks = (int)std::max<long long>(1, (db->n + rowsPerChunk - 1) / rowsPerChunk);
+    const unsigned long long need = (unsigned long long)nchunks * (unsigned long long)nq * (unsigned long long)k;
+    if (need > (unsigned long long)ORBM_KNN_STATIC_MAX_ENTRIES) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "orbm_knn_device_static: %d chunks x %d queries x k=%d = %llu scratch entries exceed the static "
+                 "maximum of %llu (ORBM_KNN_STATIC_MAX_ENTRIES); use fewer queries per call or orbm_knn_device",
+                 nchunks, nq, k, need, (unsigned long long)ORBM_KNN_STATIC_MAX_ENTRIES);
+        M->err = msg;
+        return ORBM_ERR_CAPACITY;
+    }
+    unsigned long long* part = nullptr;
+    CKM(knnStaticAddress(M->device, &part));
+    k_knn<1, kKnnMaxK><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
+                                                                      db->rowOffset, (int)rowsPerChunk, k, part);
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(part, nchunks, nq, k, d_dist, d_idx);
     M->launches += 2;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());

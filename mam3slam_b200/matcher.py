@@ -343,6 +343,12 @@ class ORBmatcher:
         check_m(self._L.orbm_knn_device(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist), C.c_void_p(d_idx),
                                         C.c_void_p(stream or 0)), self._h, "orbm_knn_device")
 
+    def knn_device_static(self, db, d_q, nq, k, d_dist, d_idx, stream=None):
+        """orbm_knn_device_static: the same search with its scratch in a fixed-size static device array; the call allocates
+        nothing (include/orbm.h).  No counterpart in the reference."""
+        check_m(self._L.orbm_knn_device_static(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist),
+                                               C.c_void_p(d_idx), C.c_void_p(stream or 0)), self._h, "orbm_knn_device_static")
+
     def knn_merge_device(self, d_dist, d_idx, shard_stride_bytes, nshards, nq, k, d_out_dist, d_out_idx, stream=None):
         """Device-side merge of all-gathered per-shard top-k lists (include/orbm.h); pointers are device addresses."""
         check_m(self._L.orbm_knn_merge_device(self._h, C.c_void_p(d_dist), C.c_void_p(d_idx), int(shard_stride_bytes), int(nshards),
