@@ -98,6 +98,17 @@ WORKLOAD = ("single-agent EuRoC-shaped 752x480 synthetic mono stream per GPU, 10
 POPC_PEAK = 4.635e12                     # measured on this pool's B200 (profiles/int_peaks_b200.txt): 16.5 popc/clk/SM
 
 
+def common_config(args):
+    """`config` of the JSON line: the SAME dict in both arms (the driver compares them).  What differs between the arms - the
+    bounded CPU sample, the measured keypoint / match counts, the schedules - lives under other keys (`cpu_baseline.sample`,
+    `workload_stats`, `schedule`)."""
+    nbytes = args.sets * args.batch * W * H
+    return {"workload": WORKLOAD, "frames_per_batch_per_gpu": args.batch, "batches_per_step": args.batches_per_step,
+            "frames_per_step_per_gpu": args.batch * args.batches_per_step,
+            "l2_policy": f"{args.sets} distinct input batches rotated ({nbytes / 1e6:.0f} MB > 126 MB L2); all intermediates "
+                         "rewritten every batch"}
+
+
 def cpu_reference_run(frames, iters, threads):
     """Times the CPU restatement (oracle/) of the hot path — ORBextractor::operator() on every frame followed by
     SearchByProjection(Cur, Last) against the previous frame — on `iters` frames split over `threads` host threads
@@ -141,7 +152,7 @@ def run_reference(args):
         return
     threads = os.cpu_count() or 1
     frames = make_frames(0, 8)
-    per_step = max(threads * 2, 8)
+    per_step = threads * 8                  # every thread runs 8 consecutive frames of its stream: all but its first are matched
     for _ in range(min(args.warmup, 1)):
         cpu_reference_run(frames, threads, threads)
     tot_t, tot_f = 0.0, 0
@@ -153,11 +164,13 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frames_per_step": per_step},
+            "config": common_config(args),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
-                             "sample": f"{per_step} frames per step x {args.steps} steps, {threads} threads (one agent stream "
-                                       "each), oracle/cpp restatement of ORBextractor + SearchByProjection (reference needs "
-                                       "OpenCV C++/Eigen: not buildable here)"},
+                             "sample": f"{per_step} frames per step x {args.steps} steps, {threads} threads (one agent stream of 8 "
+                                       "consecutive frames each per step), oracle/cpp restatement of ORBextractor + "
+                                       "SearchByProjection (the extractor restatement is bit-identical to the reference's own "
+                                       "ORBextractor.cc, tests/test_oracle_vs_ref.py; ORBmatcher.cc needs Eigen/Sophus/DBoW2: "
+                                       "not buildable here)"},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
 
@@ -192,6 +205,47 @@ def latency_bench(args, torch, local, frames):
     e, s_ = float(np.median(t_ex)), float(np.median(t_sp))
     return {"operator_call_ms": e * 1e3, "search_by_projection_call_ms": s_ * 1e3, "single_stream_frames_per_s": 1.0 / (e + s_),
             "note": "one frame in flight, synchronous calls, host buffers (pinned image)"}
+
+
+def sparse_bench(args, torch, local, rank):
+    """the dense synthetic texture (26 k FAST candidates per frame) loads FAST's sparse paths and the
+    quadtree unrepresentatively.  The same device-resident extraction on a SPARSE-texture stream (synth.stream(sparse=True):
+    smooth shading + shape edges, ~11 k candidates), strictly serial on one stream, with the exact compass early-out of the
+    FAST strength pass off and on (ORBX_FAST_COMPASS; byte-identical results, tests/test_env_switches_gpu.py)."""
+    from mam3slam_b200 import ORBextractor, synth
+    B = args.batch
+    fr = synth.stream(W, H, 500 + rank, min(B, 32), sparse=True)
+    host = np.concatenate([np.roll(fr, 3 * r, axis=2) for r in range((2 * B + len(fr) - 1) // len(fr))])[:2 * B]
+    dev = torch.from_numpy(host).cuda()
+    ts = torch.cuda.Stream()
+    out = {"workload": f"sparse-texture 752x480 stream, extraction only, {B} device-resident frames per batch, one stream"}
+    for name, flag in (("compass_off", "0"), ("compass_on", "1")):
+        os.environ["ORBX_FAST_COMPASS"] = flag
+        ex = ORBextractor(NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH, device=local, max_batch=B)
+        os.environ.pop("ORBX_FAST_COMPASS")
+        def step(i):
+            ex.extract_device(dev.data_ptr() + (i % 2) * B * W * H, W * H, B, W, H, W, (0, 1000), ts.cuda_stream)
+        for i in range(4):
+            step(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 20
+        e0.record(ts)
+        for i in range(iters):
+            step(i)
+        e1.record(ts)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        out[name] = {"frames_per_s": B / (ms * 1e-3), "ms_per_batch": ms}
+        if name == "compass_off":
+            ex.set_stage_timing(True)
+            step(0); torch.cuda.synchronize(); ex.synchronize()
+            out["stage_ms_per_batch"] = ex.stage_times()
+            ex.set_stage_timing(False)
+            out["keypoints_per_frame"] = float(np.mean([len(ex.fetch(f)[1]) for f in range(4)]))
+            out["fast_candidates_per_frame"] = float(np.mean([sum(len(ex.candidates(l, f)) for l in range(NLEVELS)) for f in range(2)]))
+        ex.close()
+    return out
 
 
 def kitti_bench(args, torch, dist, rank, world, local):
@@ -328,12 +382,30 @@ def knn_bench(args, torch, dist, rank, world, local):
         md, mi = dd.cpu().numpy().view(np.uint16), di.cpu().numpy()
     ok = bool((md[:, 0] <= 1).all())
     evals = float(NDB) * NQ
+    eps = evals / (ms * 1e-3)
     out = {"workload": f"brute-force k-NN {NDB} x {NQ}, k={K}, db rows sharded over {world} GPU(s), one all-gather + device merge inside the timed step",
-           "ms": ms, "evaluations_per_s": evals / (ms * 1e-3), "planted_neighbours_found": ok,
-           "roofline_int": {"bound": "popc", "achieved_popc_equiv_per_s": 8 * evals / (ms * 1e-3), "peak_popc_per_s": POPC_PEAK * world,
-                            "frac": 8 * evals / (ms * 1e-3) / (POPC_PEAK * world),
-                            "note": "8 popc per 256-bit evaluation by definition; the kernel issues 4 (carry-save adder tree), so "
-                                    "frac may exceed 1"}}
+           "ms": ms, "evaluations_per_s": eps, "planted_neighbours_found": ok,
+           "roofline_int": {"bound": "popc", "popc_issued_per_evaluation": 4, "achieved_popc_per_s": 4 * eps,
+                            "peak_popc_per_s": POPC_PEAK * world, "frac": 4 * eps / (POPC_PEAK * world),
+                            "popc8_equivalent_frac": 8 * eps / (POPC_PEAK * world),
+                            "note": "frac = POPC instructions the kernel ISSUES (4 per 256-bit evaluation: carry-save adder tree in "
+                                    "LOP3 halves the naive 8) against the measured POPC rate (16.5 /clk/SM, "
+                                    "profiles/int_peaks_b200.txt); popc8_equivalent_frac charges the naive 8 and may exceed 1"}}
+    if rank == 0 and not args.no_cpu:
+        # CPU baseline for Hamming matches/s: the oracle's popcount brute force on ALL host threads over a
+        # 50 k-row subsample of the same database and the same 2000 queries; evaluations/s do not depend on the row count, so the
+        # full-size figure is the same rate (labelled extrapolated: the 1 M x 2000 search itself is not run on the CPU)
+        from oracle import matcher as om
+        sub, threads = 50_000, os.cpu_count() or 1
+        db_h, q_h = db[:sub].cpu().numpy(), q.cpu().numpy()
+        om.knn(q_h[:64], db_h, K, threads)
+        t0 = time.perf_counter()
+        om.knn(q_h, db_h, K, threads)
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": sub * NQ / dt, "unit": "evaluations/s", "cores": threads, "kind": "port",
+                               "sample": f"{sub} x {NQ} of the same rows / queries, k={K}, oracle/cpp popcount scan "
+                                         "(ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2058-2074, in a strict-< k-NN loop)",
+                               "extrapolated_full_search_s": NDB * NQ / (sub * NQ / dt)}
     D.close(); m.close()
     return out
 
@@ -389,12 +461,18 @@ def run_gpu(args):
     dk, dd, dc, stride = pipes[0]["dk"], pipes[0]["dd"], pipes[0]["dc"], ex.results_batch_device()[3]
     kpm, nmt = pipes[0]["kpm"], pipes[0]["nmt"]
 
-    def step_device(i):
-        s = i % nsets
-        P = pipes[i % npipes]
+    bps = max(1, args.batches_per_step)
+
+    def batch_device(j):
+        s = j % nsets
+        P = pipes[j % npipes]
         P["ex"].extract_device(dev.data_ptr() + s * B * img_bytes, img_bytes, B, W, H, W, (0, 1000), P["st"])
         P["mt"].track_batch_device(B, P["dk"], P["dd"], P["dc"], stride, BOUNDS, sf, TH_TRACK, P["kpm"].data_ptr(), P["nmt"].data_ptr(),
                                    stream=P["st"])
+
+    def step_device(i):                    # one step = bps batches of B frames (consecutive batches alternate between the pipes)
+        for b in range(bps):
+            batch_device(i * bps + b)
 
     def barrier():
         torch.cuda.synchronize()
@@ -407,7 +485,7 @@ def run_gpu(args):
     # graph of each argument set exists before anything is timed (the extractor captures one graph per input base address)
     import math
     for i in range(nsets * npipes // math.gcd(nsets, npipes)):
-        step_device(i)
+        batch_device(i)
     torch.cuda.synchronize()
     for i in range(args.warmup):
         step_device(i)
@@ -419,7 +497,7 @@ def run_gpu(args):
         return sum(P["ex"].launch_count() + P["mt"].launch_count() for P in pipes[:npipes])
     l0 = launches_now()
     e0 = torch.cuda.Event(enable_timing=True)
-    e0.record(pipes[args.warmup % npipes]["ts"])      # every stream is idle here (barrier above); this pipe takes the first timed step
+    e0.record(pipes[(args.warmup * bps) % npipes]["ts"])      # every stream is idle here (barrier above); this pipe takes the first timed batch
     for i in range(args.steps):
         step_device(args.warmup + i)
     ends = []
@@ -463,7 +541,7 @@ def run_gpu(args):
         P["kpm_h"] = torch.empty((B, stride), dtype=torch.int32).pin_memory()
         P["nm_h"] = torch.empty(B, dtype=torch.int32).pin_memory()
 
-    def step_e2e(i):
+    def batch_e2e(i):
         # the calls a user makes, with HOST buffers: frames in, keypoints + descriptors + matches out, then a stream sync
         P = pipes[i % epipes]
         P["ex"].extract_batch_into(host_batches[i % nsets], P["kps_h"], P["desc_h"], P["n_h"], P["mono_h"])
@@ -479,14 +557,14 @@ def run_gpu(args):
         # p, p + epipes, ... so that the copies of one batch overlap the kernels of the other
         if epipes == 1:
             for i in range(first, first + count):
-                step_e2e(i)
+                batch_e2e(i)
             return
         import threading
 
         def worker(p):
             torch.cuda.set_device(local)
             for i in range(first + ((p - first) % epipes), first + count, epipes):
-                step_e2e(i)
+                batch_e2e(i)
         th = [threading.Thread(target=worker, args=(p,)) for p in range(epipes)]
         for t in th:
             t.start()
@@ -496,7 +574,7 @@ def run_gpu(args):
     run_e2e(0, max(min(args.warmup, 3), epipes))
     barrier()
     t0 = time.perf_counter()
-    run_e2e(0, args.steps)
+    run_e2e(0, args.steps * bps)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
@@ -505,59 +583,135 @@ def run_gpu(args):
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms, e2e_ms = tms.tolist()
-    total_frames = B * args.steps * world
+    total_frames = B * bps * args.steps * world
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
     latency = latency_bench(args, torch, local, frames) if rank == 0 else None
+    sparse = sparse_bench(args, torch, local, rank) if rank == 0 and not args.no_sparse else None
     if rank == 0:
         pk, pk_kind = peaks()
         fps = total_frames / (ms * 1e-3)
         stage_bytes = stage_algorithmic_bytes(nkp, track_evals / max(B - 1, 1))
         dom = max((k for k in acc if k != "total"), key=lambda k: acc[k])
         ach = stage_bytes[dom] * B / (acc[dom] * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(dom) if B == 64 else (None, None)
         line = {
             "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
-                       "matches_per_frame": nmatch, "hamming_evaluations_per_frame": track_evals / max(B - 1, 1),
-                       "l2_policy": f"{nsets} distinct input batches rotated ({nsets * B * img_bytes / 1e6:.0f} MB > "
-                                    "126 MB L2); all intermediates rewritten every step",
-                       "schedule": (f"{npipes} handle pairs on {npipes} CUDA streams take alternating batches of the one frame stream "
+            "config": common_config(args),
+            "workload_stats": {"keypoints_per_frame": nkp, "matches_per_frame": nmatch,
+                               "hamming_evaluations_per_frame": track_evals / max(B - 1, 1),
+                               "texture": "dense synthetic texture: ~26 k FAST candidates per frame, far denser than EuRoC imagery "
+                                          "(SURVEY A8); see `sparse` for a sparse-texture stream"},
+            "schedule": {"device": (f"{npipes} handle pairs on {npipes} CUDA streams take alternating batches of the one frame stream "
                                     "(tracking of batch i overlaps extraction of batch i+1)") if npipes > 1 else "serial, one stream",
-                       "e2e_schedule": f"{epipes} host threads, one handle pair each, take alternating batches; every call is synchronous"},
+                         "e2e": f"{epipes} host threads, one handle pair each, take alternating batches; every call is synchronous"},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
-                    "h2d_bytes_per_step": int(B * W * H), "d2h_bytes_per_step": int(B * (cap * 60 + 8 + stride * 4 + 4))},
+                    "h2d_bytes_per_step": int(bps * B * W * H), "d2h_bytes_per_step": int(bps * B * (cap * 60 + 8 + stride * 4 + 4))},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": ach / pk["hbm_gbs"], "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(dom) if B == 64 else None,
-                         "traffic_source": "profiles/r1g_ncu_full_summary.csv (dram__bytes_read.sum + dram__bytes_write.sum, 64 frames per launch)",
+                         "frac": ach / pk["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
                          "peak_kind": pk_kind,
                          "alu": fast_alu_roofline(acc.get("fast"), B),
-                         "stage_ms_per_step": acc,
-                         "note": "integer/issue-bound path: see DESIGN.md 4; pipeline_* = 1.93 MB algorithmic bytes per frame",
+                         "stage_ms_per_batch": acc,
+                         "note": "per launch = one batch of 64 frames; integer/issue-bound path: see DESIGN.md 4; pipeline_* = 1.93 MB "
+                                 "algorithmic bytes per frame",
                          "pipeline_alg_gbs": ALG_BYTES_PER_FRAME * fps / 1e9 / world,
                          "pipeline_frac": ALG_BYTES_PER_FRAME * fps / 1e9 / world / pk["hbm_gbs"]},
             "hamming": {"track_evaluations_per_s": track_evals * world / (acc["track"] * 1e-3), "knn": hamming},
             "kitti": kitti,
             "latency": latency,
+            "sparse": sparse,
         }
         if world == 1 and not args.no_cpu:
             cf = make_frames(0, 8)
             wall, n = cpu_reference_run(cf, args.cpu_frames, 1)
             line["cpu_baseline"] = {"value": n / wall, "unit": "frames/s", "cores": 1, "kind": "port",
                                     "sample": f"{n} frames of the same stream (extraction + SearchByProjection), 1 thread, "
-                                              "oracle/cpp restatement"}
+                                              "oracle/cpp restatement (extractor bit-identical to the reference's own "
+                                              "ORBextractor.cc compiled against a cv:: shim, tests/test_oracle_vs_ref.py)"}
+            line["cpu_baseline_cv2"] = cv2_baseline(cf)
         emit(line)
     ex.close(); mt.close()
     if world > 1:
         dist.destroy_process_group()
 
 
-# DRAM bytes per launch (64 EuRoC frames) of each stage's kernel(s), from the committed ncu --set full capture
-NCU_DRAM_BYTES_PER_LAUNCH = {"pyramid": 75.4e6, "fast": 71.0e6, "octree": 15.4e6, "blur": 116.6e6, "finalize": 0.56e6,
-                             "orient_brief": 150.7e6, "track": 8.6e6}
+STAGE_KERNELS = {"pyramid": ("k_pyr_level",), "fast": ("k_fast_score", "k_fast_nms", "k_fast_select", "k_fast_cells"),
+                 "octree": ("k_octree",), "blur": ("k_blur7",), "finalize": ("k_finalize",), "orient_brief": ("k_orient_brief",),
+                 "track": ("k_track_",)}
+
+
+def ncu_traffic(stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch (one batch of 64 EuRoC frames) of a stage's kernels, summed over
+    the kernels of ONE batch, read from the newest committed `ncu --set full` summary under profiles/ (tools/ncu_summary.py).
+    Returns (bytes or None, source file or None): nothing is hard-coded, so a stale number cannot survive a new profile."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary.csv")))
+    if not files:
+        return None, None
+    try:
+        with open(files[-1]) as f:
+            rows = list(csv.reader(f))
+        hdr, units = rows[0], rows[1]
+        ik, ir, iw = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        tot, batches = 0.0, 0
+        for r in rows[2:]:
+            batches += "k_octree" in r[ik]                  # one quadtree launch per batch: the capture may hold several batches
+            if any(k in r[ik] for k in STAGE_KERNELS[stage]):
+                tot += float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+        if tot == 0.0:
+            return None, None
+        return tot / max(batches, 1), os.path.relpath(files[-1], ROOT)
+    except Exception:
+        return None, None
+
+
+def cv2_baseline(frames):
+    """Secondary CPU baseline with the REAL OpenCV (SIMD), to show the scalar port is not a straw man.
+    (a) cv2.ORB with the reference's settings - OpenCV's own ORB: the same pixel stages (pyramid, FAST-9/16 + NMS, IC angle,
+    7x7 blur, rBRIEF) but NOT the reference's per-cell FAST fallback and quadtree; (b) the reference's pixel primitives alone
+    on whole levels (cv2.resize + copyMakeBorder, cv2.FAST at 20, GaussianBlur).  One thread (cv2.setNumThreads(1))."""
+    try:
+        import cv2
+    except Exception as e:                                   # cv2 is part of the image; never fatal for the bench line
+        return {"unavailable": str(e)}
+    from oracle.py import cv2_pipeline as cp
+    old = cv2.getNumThreads()
+    cv2.setNumThreads(1)
+    try:
+        orb = cv2.ORB_create(nfeatures=NFEAT, scaleFactor=SCALE, nlevels=NLEVELS, edgeThreshold=19, firstLevel=0, WTA_K=2,
+                             scoreType=cv2.ORB_FAST_SCORE, patchSize=31, fastThreshold=INI_TH)
+        orb.detectAndCompute(frames[0], None)
+        n, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < 3.0:
+            orb.detectAndCompute(frames[n % len(frames)], None)
+            n += 1
+        t_orb = (time.perf_counter() - t0) / n
+        st = {"pyramid": 0.0, "fast_whole_level": 0.0, "blur": 0.0}
+        det = cv2.FastFeatureDetector_create(INI_TH, True)
+        reps = 10
+        for i in range(reps):
+            img = frames[i % len(frames)]
+            t0 = time.perf_counter(); pyr = cp.pyramid(img, SCALE, NLEVELS); t1 = time.perf_counter()
+            for _, roi in pyr:
+                det.detect(np.ascontiguousarray(roi))
+            t2 = time.perf_counter()
+            for _, roi in pyr:
+                cp.blur(roi)
+            t3 = time.perf_counter()
+            st["pyramid"] += (t1 - t0) / reps; st["fast_whole_level"] += (t2 - t1) / reps; st["blur"] += (t3 - t2) / reps
+    finally:
+        cv2.setNumThreads(old)
+    return {"value": 1.0 / t_orb, "unit": "frames/s", "cores": 1, "kind": "cv2.ORB (OpenCV %s, SIMD), extraction only" % cv2.__version__,
+            "ms_per_frame": t_orb * 1e3, "primitive_ms_per_frame": {k: v * 1e3 for k, v in st.items()},
+            "sample": f"{n} calls of cv2.ORB.detectAndCompute on the same 752x480 stream (1000 kp, 8 levels @1.2, FAST 20, FAST_SCORE); "
+                      "OpenCV's ORB has no per-cell minThFAST fallback and no quadtree, so it is a lower bound on the CPU cost of "
+                      "the reference's extractor with real OpenCV primitives"}
 
 
 def fast_alu_roofline(fast_ms, B):
@@ -611,10 +765,12 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="frames in flight per GPU per step")
+    ap.add_argument("--batch", type=int, default=64, help="frames per batch (one extractor pass) per GPU")
+    ap.add_argument("--batches-per-step", type=int, default=16,
+                    help="batches per step: a step is 1024 frames (~12 ms on a B200) so that the driver's 20 steps time >= 0.2 s")
     ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
     ap.add_argument("--cpu-frames", type=int, default=400, help="frames timed for cpu_baseline")
     ap.add_argument("--pipes", type=int, default=2, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
@@ -622,6 +778,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-kitti", action="store_true", help="skip the KITTI-shaped leg (config 3)")
     ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
+    ap.add_argument("--no-sparse", action="store_true", help="skip the sparse-texture leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -19,11 +19,14 @@ def _box(a, k):
     return (s / (k * k)).astype(np.float32)
 
 
-def base_texture(w, h, seed, margin=64):
+def base_texture(w, h, seed, margin=64, octaves=(1, 2, 4, 8, 16)):
+    """octaves: box sizes of the noise components.  The default (with the 1- and 2-px components) is a DENSE texture: ~26 k
+    FAST candidates per 752x480 frame; octaves=(8, 16, 32) leaves smooth shading + the shapes' edges, a SPARSE texture closer
+    to indoor imagery (a few thousand candidates, most cells decided by a handful of strong corners)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     H, W = h + 2 * margin, w + 2 * margin
     acc = np.zeros((H, W), np.float32)
-    for k in (1, 2, 4, 8, 16):
+    for k in octaves:
         acc += _box(rng.standard_normal((H, W)).astype(np.float32), k) * k
     acc -= acc.min()
     acc *= 255.0 / acc.max()
@@ -65,13 +68,17 @@ def warp(base, w, h, dx, dy, rot_deg, margin=64):
     return np.clip(np.rint(v), 0, 255).astype(np.uint8)
 
 
-def frame(w=752, h=480, seed=0):
-    return np.ascontiguousarray(base_texture(w, h, seed)[64:64 + h, 64:64 + w])
+SPARSE_OCTAVES = (8, 16, 32)
 
 
-def stream(w=752, h=480, seed=0, nframes=8):
+def frame(w=752, h=480, seed=0, sparse=False):
+    octs = SPARSE_OCTAVES if sparse else (1, 2, 4, 8, 16)
+    return np.ascontiguousarray(base_texture(w, h, seed, octaves=octs)[64:64 + h, 64:64 + w])
+
+
+def stream(w=752, h=480, seed=0, nframes=8, sparse=False):
     """[nframes, h, w] uint8 frames of one agent: random-walk motion over one base texture."""
-    base = base_texture(w, h, seed)
+    base = base_texture(w, h, seed, octaves=SPARSE_OCTAVES if sparse else (1, 2, 4, 8, 16))
     rng = np.random.Generator(np.random.PCG64(seed + 100003))
     dx = dy = rot = 0.0
     out = np.empty((nframes, h, w), np.uint8)

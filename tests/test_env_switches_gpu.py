@@ -24,6 +24,8 @@ for mono, k, d in res:
 small = ORBextractor(300, 1.2, 5, 20, 7)
 mono, k, d = small(synth.frame(333, 257, 1))
 h.update(k.tobytes()); h.update(d.tobytes())
+mono, k, d = ex(synth.frame(752, 480, 9, sparse=True))          # sparse texture: cells decided by the minThFAST fallback
+h.update(np.int32(mono).tobytes()); h.update(k.tobytes()); h.update(d.tobytes())
 print(h.hexdigest())
 ''' % ROOT
 
@@ -39,5 +41,8 @@ def _digest(env_extra):
 def test_schedule_switches_do_not_change_results():
     base = _digest({})
     for env in ({"ORBX_FAST_GROUPS": "0"}, {"ORBX_BLUR_EARLY": "0"}, {"ORBX_FAST_EARLY": "1"}, {"ORBX_PRIO": "0"},
-                {"ORBX_GRAPHS": "0"}, {"ORBX_OVERLAP": "0"}, {"ORBX_FAST_EARLY": "1", "ORBX_BLUR_EARLY": "0", "ORBX_GRAPHS": "0"}):
+                {"ORBX_GRAPHS": "0"}, {"ORBX_OVERLAP": "0"}, {"ORBX_FAST_EARLY": "1", "ORBX_BLUR_EARLY": "0", "ORBX_GRAPHS": "0"},
+                # FAST: first-generation per-cell kernel, compass early-out of the strength pass, plain-load tile staging (no TMA)
+                {"ORBX_FAST_GEN": "1"}, {"ORBX_FAST_GEN": "1", "ORBX_FAST_GROUPS": "0"}, {"ORBX_FAST_COMPASS": "1"},
+                {"ORBX_FAST_TMA": "0"}, {"ORBX_FAST_TMA": "0", "ORBX_FAST_COMPASS": "1", "ORBX_GRAPHS": "0"}):
         assert _digest(env) == base, env

@@ -5,7 +5,7 @@ python - <<'PY'
 import json
 d = json.load(open('gpurun_out/bench_only.json'))
 print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/step', round(d['ms_per_step'], 3))
-print({k: round(v, 4) for k, v in d['roofline']['stage_ms_per_step'].items()})
+print({k: round(v, 4) for k, v in d['roofline']['stage_ms_per_batch'].items()})
 PY
 tail -3 gpurun_out/bench_only.err
 true

@@ -5,5 +5,5 @@ for t in 64 128 256; do
   echo "== ORBX_FAST_THREADS=$t"
   ORBX_FAST_THREADS=$t timeout 300 python bench.py --no-cpu --no-knn --steps 10 2>/dev/null | python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); print('value', round(d['value']), {k: round(v,4) for k,v in d['roofline']['stage_ms_per_step'].items()})"
+d=json.loads(sys.stdin.read()); print('value', round(d['value']), {k: round(v,4) for k,v in d['roofline']['stage_ms_per_batch'].items()})"
 done

@@ -8,7 +8,7 @@ python - <<'PY'
 import json
 d = json.load(open('gpurun_out/bench_quick.json'))
 print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/step', round(d['ms_per_step'], 3))
-print({k: round(v, 4) for k, v in d['roofline']['stage_ms_per_step'].items()})
+print({k: round(v, 4) for k, v in d['roofline']['stage_ms_per_batch'].items()})
 print('knn ms', d.get('hamming', {}).get('knn', {}).get('ms'))
 print('latency', d.get('latency'))
 print('kitti', {k: (round(v, 3) if isinstance(v, float) else v) for k, v in (d.get('kitti') or {}).items() if k != 'workload'})

@@ -6,7 +6,7 @@ cat gpurun_out/r2a_pytest.log
 B="timeout 300 python bench.py --no-cpu --no-knn --no-kitti --steps 50"
 show() { python -c "
 import json,sys
-d=json.loads(sys.stdin.read()); print('value', round(d['value']), 'e2e', round(d['e2e']['value']), {k: round(v,4) for k,v in d['roofline']['stage_ms_per_step'].items()})"; }
+d=json.loads(sys.stdin.read()); print('value', round(d['value']), 'e2e', round(d['e2e']['value']), {k: round(v,4) for k,v in d['roofline']['stage_ms_per_batch'].items()})"; }
 echo "== gen1";  ORBX_FAST_GEN=1 $B 2>gpurun_out/r2a_err1.log | show
 echo "== gen2";  $B 2>gpurun_out/r2a_err2.log | tee gpurun_out/r2a_bench_gen2.json | show
 echo "== gen2 compass"; ORBX_FAST_COMPASS=1 $B 2>/dev/null | show
