@@ -175,6 +175,10 @@ int orbm_knn_device(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k
 #define ORBM_KNN_STATIC_MAX_ENTRIES (1u << 20)
 int orbm_knn_device_static(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist,
                            int32_t* d_idx, void* stream);
+/* test aid (no counterpart in the reference): number of allocating CUDA calls (cudaMalloc, cudaMallocHost, stream creation) this
+ * library's matcher side has made since it was loaded.  The C++ adapter's pooled ORBmatcher objects and
+ * orbm_knn_device_static must leave it unchanged in steady state (tests/test_cpp_adapter_gpu.py, tests/test_zz_no_alloc.py). */
+long long orbm_debug_alloc_count(void);
 /* merge of per-shard top-k lists (nshards x nq x k, e.g. after an all-gather): same tie rule on global row ids */
 int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq, int k, uint16_t* out_dist,
                    int32_t* out_idx);

@@ -121,6 +121,8 @@ def _bind_matcher(L):
     L.orbm_knn.argtypes = [vp, vp, vp, i32, i32, vp, vp]
     L.orbm_knn_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
     L.orbm_knn_device_static.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
+    L.orbm_debug_alloc_count.restype = C.c_longlong
+    L.orbm_debug_alloc_count.argtypes = []
     L.orbm_knn_merge.argtypes = [vp, vp, i32, i32, i32, vp, vp]
     L.orbm_distinctive_descriptors.argtypes = [vp, vp, vp, i32, vp]
     L.orbm_track_batch_device.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, i32, f32, i32, i32, vp, vp, vp]

@@ -28,15 +28,29 @@ public:
     static const int TH_HIGH = ORBM_TH_HIGH;
     static const int HISTO_LENGTH = ORBM_HISTO_LENGTH;
 
-    ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = 0) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {
+    // The reference constructs an ORBmatcher as a stack local on every tracking / mapping / loop-closing call
+    // (src/Tracking.cc:2393,2648,2789,3146,3359,3398, src/LocalMapping.cc:528,882, src/LoopClosing.cc:904-905,1541,3185,3225).
+    // Construction must therefore be free: the CUDA-side state (orbm handle = stream + scratch, two device frame slots) comes
+    // from a thread_local pool - the constructor pops a set for `device` (creating one only when the pool has none), the
+    // destructor pushes it back.  In steady state neither makes a CUDA API call; the pool's sets are destroyed when the thread
+    // exits.  A set is only ever used by the thread that owns it, like the reference's per-call objects.
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = 0) : mfNNratio(nnratio), mbCheckOrientation(checkOri), device_(device) {
+        std::vector<PoolSet>& free = pool().free;
+        for (size_t i = free.size(); i-- > 0;)
+            if (free[i].device == device) {
+                h_ = free[i].h; a_ = free[i].a; b_ = free[i].b;
+                free.erase(free.begin() + (long)i);
+                return;
+            }
         const int rc = orbm_create(device, &h_);
         if (rc != ORBM_OK) throw std::runtime_error(std::string("orbm_create: ") + orbm_strerror(rc));   // no CPU fallback
     }
     ~ORBmatcher() {
-        if (a_) orbm_frame_destroy(h_, a_);
-        if (b_) orbm_frame_destroy(h_, b_);
-        orbm_destroy(h_);
+        PoolSet s; s.h = h_; s.a = a_; s.b = b_; s.device = device_;
+        pool().free.push_back(s);
     }
+    // sets waiting in the calling thread's pool (tests)
+    static size_t PooledSets() { return pool().free.size(); }
     ORBmatcher(const ORBmatcher&) = delete;
     ORBmatcher& operator=(const ORBmatcher&) = delete;
 
@@ -512,8 +526,21 @@ private:
     void check(int rc, const char* what) {
         if (rc != ORBM_OK) throw std::runtime_error(std::string(what) + ": " + orbm_strerror(rc) + " " + orbm_last_error(h_));
     }
+    struct PoolSet { orbm_handle h = nullptr; orbm_frame a = nullptr, b = nullptr; int device = 0; };
+    struct Pool {
+        std::vector<PoolSet> free;
+        ~Pool() {
+            for (PoolSet& s : free) {
+                if (s.a) orbm_frame_destroy(s.h, s.a);
+                if (s.b) orbm_frame_destroy(s.h, s.b);
+                orbm_destroy(s.h);
+            }
+        }
+    };
+    static Pool& pool() { thread_local Pool p; return p; }
     orbm_handle h_ = nullptr;
-    orbm_frame a_ = nullptr, b_ = nullptr;     // two device frame slots, reused across calls
+    orbm_frame a_ = nullptr, b_ = nullptr;     // two device frame slots, reused across calls (and, through the pool, across objects)
+    int device_ = 0;
 };
 
 }  // namespace MAM3SLAM

@@ -3,6 +3,7 @@
 #include "orbm_kernels.cuh"
 #include "orbx_internal.h"
 #include <algorithm>
+#include <atomic>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -11,6 +12,13 @@
 #include <mutex>
 #include <string>
 #include <vector>
+
+// every allocating CUDA call of the matcher goes through these, so that tests can assert that a steady-state call sequence (the
+// adapter's pooled objects, the allocation-free entry point) performs none: orbm_debug_alloc_count()
+static std::atomic<long long> g_allocCalls{0};
+template <class T> static cudaError_t cMalloc(T** p, size_t n) { ++g_allocCalls; return cudaMalloc((void**)p, n); }
+template <class T> static cudaError_t cMallocHost(T** p, size_t n) { ++g_allocCalls; return cudaMallocHost((void**)p, n); }
+static cudaError_t cStreamCreate(cudaStream_t* s, unsigned flags) { ++g_allocCalls; return cudaStreamCreateWithFlags(s, flags); }
 
 using namespace orbm;
 
@@ -67,8 +75,8 @@ int ensureScratch(orbm_matcher* M, size_t bytes) {
     if (M->pinned) cudaFreeHost(M->pinned);
     M->scratch = nullptr; M->pinned = nullptr; M->scratchBytes = M->pinnedBytes = 0;
     const size_t want = std::max<size_t>(bytes * 2, 1 << 20);
-    CKM(cudaMalloc(&M->scratch, want));
-    CKM(cudaMallocHost(&M->pinned, want));
+    CKM(cMalloc(&M->scratch, want));
+    CKM(cMallocHost(&M->pinned, want));
     M->scratchBytes = M->pinnedBytes = want;
     return ORBM_OK;
 }
@@ -99,13 +107,13 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
         freeFrameBuffers(f);
         const int cap = std::max(n, 1024);
         if (needOwn) {
-            CKM(cudaMalloc((void**)&f->kpsDev, (size_t)cap * sizeof(orbx_keypoint)));
-            CKM(cudaMalloc((void**)&f->descDev, (size_t)cap * 32));
+            CKM(cMalloc((void**)&f->kpsDev, (size_t)cap * sizeof(orbx_keypoint)));
+            CKM(cMalloc((void**)&f->descDev, (size_t)cap * 32));
         }
-        CKM(cudaMalloc((void**)&f->kp4, (size_t)cap * sizeof(float4)));
-        CKM(cudaMalloc((void**)&f->cellOf, (size_t)cap * sizeof(int)));
-        CKM(cudaMalloc((void**)&f->cellOff, (size_t)(kGridCells + 1) * sizeof(int)));
-        CKM(cudaMalloc((void**)&f->cellIdx, (size_t)cap * sizeof(int)));
+        CKM(cMalloc((void**)&f->kp4, (size_t)cap * sizeof(float4)));
+        CKM(cMalloc((void**)&f->cellOf, (size_t)cap * sizeof(int)));
+        CKM(cMalloc((void**)&f->cellOff, (size_t)(kGridCells + 1) * sizeof(int)));
+        CKM(cMalloc((void**)&f->cellIdx, (size_t)cap * sizeof(int)));
         f->cap = cap; f->ownsInput = needOwn;
     }
     f->n = n;
@@ -177,8 +185,8 @@ int orbm_create(int device, orbm_handle* out) {
     if (device < 0 || device >= ndev) return ORBM_ERR_INVALID;
     orbm_matcher* M = new orbm_matcher();
     M->device = device;
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&M->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc((void**)&M->dEvals, 128) != cudaSuccess) {
+    if (cudaSetDevice(device) != cudaSuccess || cStreamCreate(&M->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cMalloc((void**)&M->dEvals, 128) != cudaSuccess) {
         fprintf(stderr, "orbm_create: %s\n", cudaGetErrorString(cudaGetLastError()));
         delete M;
         return ORBM_ERR_CUDA;
@@ -496,7 +504,7 @@ int orbm_fuse_candidates(orbm_handle M, orbm_frame kf, const float* scale_factor
     float* dSig = nullptr;
     if (chi2_gate) {
         CKM(cudaSetDevice(M->device));
-        CKM(cudaMalloc((void**)&dSig, (size_t)nlevels * sizeof(float)));
+        CKM(cMalloc((void**)&dSig, (size_t)nlevels * sizeof(float)));
         cudaError_t e = cudaMemcpyAsync(dSig, inv_sigma2, (size_t)nlevels * sizeof(float), cudaMemcpyHostToDevice, M->stream);
         if (e != cudaSuccess) { cudaFree(dSig); CKM(e); }
         P.invSigma2 = dSig;
@@ -729,7 +737,7 @@ int orbm_search_triangulation(orbm_handle M, orbm_frame kf1, const orbm_featvec*
     if (F12) memcpy(P.F, F12, sizeof(P.F));
     CKM(cudaSetDevice(M->device));
     float* dTab = nullptr;
-    CKM(cudaMalloc((void**)&dTab, (size_t)2 * nlevels * sizeof(float)));
+    CKM(cMalloc((void**)&dTab, (size_t)2 * nlevels * sizeof(float)));
     std::vector<float> tab(2 * (size_t)nlevels, 0.f);
     for (int l = 0; l < nlevels; ++l) { tab[l] = scale_factors2[l]; tab[nlevels + l] = sigma2 ? sigma2[l] : 0.f; }
     cudaError_t e = cudaMemcpyAsync(dTab, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, M->stream);
@@ -753,7 +761,7 @@ int orbm_db_create(orbm_handle M, const uint8_t* rows, long long ndb, int rows_o
     if (rows_on_device) {
         db->rows = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(rows)); db->owns = false;
     } else {
-        cudaError_t e = cudaMalloc((void**)&db->rows, (size_t)std::max<long long>(ndb, 1) * 32);
+        cudaError_t e = cMalloc((void**)&db->rows, (size_t)std::max<long long>(ndb, 1) * 32);
         if (e == cudaSuccess && ndb) e = cudaMemcpy(db->rows, rows, (size_t)ndb * 32, cudaMemcpyHostToDevice);
         if (e != cudaSuccess) { if (db->rows) cudaFree(db->rows); delete db; CKM(e); }
         db->owns = true;
@@ -788,7 +796,7 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     if (need > M->knnPartBytes) {
         if (M->knnPart) cudaFree(M->knnPart);
         M->knnPart = nullptr; M->knnPartBytes = 0;
-        CKM(cudaMalloc((void**)&M->knnPart, need));
+        CKM(cMalloc((void**)&M->knnPart, need));
         M->knnPartBytes = need;
     }
     if (qpt == 2)
@@ -803,6 +811,9 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     CKM(cudaGetLastError());
     return ORBM_OK;
 }
+
+// test aid: number of allocating CUDA calls (cudaMalloc / cudaMallocHost / cudaStreamCreate) the matcher library has made so far
+long long orbm_debug_alloc_count(void) { return g_allocCalls.load(); }
 
 // ---- allocation-free k-NN (no counterpart in the reference) ----------------
 // Same search as orbm_knn_device, for callers that may not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
@@ -962,7 +973,7 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     if (off > M->trackBytes) {
         if (M->trackBuf) { CKM(cudaStreamSynchronize(st)); cudaFree(M->trackBuf); }
         M->trackBuf = nullptr; M->trackBytes = 0;
-        CKM(cudaMalloc(&M->trackBuf, off));
+        CKM(cMalloc(&M->trackBuf, off));
         M->trackBytes = off;
     }
     uint8_t* b = (uint8_t*)M->trackBuf;
@@ -1128,7 +1139,7 @@ int orbm_vocab_create(orbm_handle M, const orbm_vocab_view* v, orbm_vocab* out) 
     cudaError_t e = cudaSuccess;
     auto up = [&](void** dst, const void* src, size_t bytes) {
         if (e != cudaSuccess) return;
-        e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
+        e = cMalloc(dst, std::max<size_t>(bytes, 16));
         if (e == cudaSuccess && bytes) e = cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice);
     };
     up((void**)&V->childOff, v->child_off, (size_t)(nn + 1) * 4);

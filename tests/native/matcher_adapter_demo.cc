@@ -4,6 +4,7 @@
 // Python side to compare against the oracle.  argv[1] = scenario file.
 #include "slam_shim.h"
 #include "../../mam3slam_b200/cpp/ORBmatcher.h"
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -134,9 +135,51 @@ static void emitEvents(const char* name) {
     emit(name, (int)g_events.size(), o);
 }
 
+// `pool` mode: the reference constructs an ORBmatcher per call (src/Tracking.cc:2789: `ORBmatcher matcher(0.9,true);` inside
+// TrackWithMotionModel).  With the adapter's thread_local pool that must cost the same as reusing one object and must not
+// allocate: N calls with a matcher constructed per call against N calls on one object, plus the library's allocation counter.
+static int poolMode(const char* path) {
+    const int N = 1000;
+    auto W = build(path);
+    const std::vector<MapPoint*> pristine = W->F2.mvpMapPoints;
+    std::vector<int> first, last;
+    {   // warm-up: the first object creates the pooled set and its device frame slot
+        MAM3SLAM::ORBmatcher m(0.9f, true);
+        m.SearchByProjection(W->F2, W->F1, 15.0f, true);
+        first = ids(W->F2.mvpMapPoints);
+    }
+    const long long alloc0 = orbm_debug_alloc_count();
+    auto t0 = std::chrono::steady_clock::now();
+    int r = 0;
+    for (int i = 0; i < N; i++) {
+        W->F2.mvpMapPoints = pristine;
+        MAM3SLAM::ORBmatcher matcher(0.9f, true);                            // per call, as the reference does
+        r = matcher.SearchByProjection(W->F2, W->F1, 15.0f, true);
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    last = ids(W->F2.mvpMapPoints);
+    const long long alloc1 = orbm_debug_alloc_count();
+    double reusedUs = 0;
+    {
+        MAM3SLAM::ORBmatcher one(0.9f, true);
+        auto t2 = std::chrono::steady_clock::now();
+        for (int i = 0; i < N; i++) {
+            W->F2.mvpMapPoints = pristine;
+            r = one.SearchByProjection(W->F2, W->F1, 15.0f, true);
+        }
+        reusedUs = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t2).count() / N;
+    }
+    const double perCallUs = std::chrono::duration<double, std::micro>(t1 - t0).count() / N;
+    std::vector<int> o = {N, (int)(perCallUs * 10), (int)(reusedUs * 10), (int)(alloc1 - alloc0), (int)MAM3SLAM::ORBmatcher::PooledSets(),
+                          first == last ? 1 : 0};
+    emit("pool", r, o);
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) return 2;
     const char* path = argv[1];
+    if (argc >= 3 && std::string(argv[2]) == "pool") return poolMode(path);
     MAM3SLAM::ORBmatcher matcher(0.8f, true);            // Tracking::SearchLocalPoints (src/Tracking.cc:3146)
     {   // Tracking::SearchLocalPoints -> SearchByProjection(Frame, local map points, th)
         auto W = build(path);

@@ -96,7 +96,7 @@ def _write(S, path):
             f.write(raw)
 
 
-def _run(tmp_path, S):
+def _run(tmp_path, S, extra=()):
     exe = os.path.join(str(tmp_path), "matcher_adapter_demo")
     libdir = os.path.join(ROOT, "mam3slam_b200")
     subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", "-o", exe,
@@ -104,7 +104,7 @@ def _run(tmp_path, S):
                            "-Wl,-rpath," + libdir])
     scen = os.path.join(str(tmp_path), "scenario.bin")
     _write(S, scen)
-    out = subprocess.run([exe, scen], capture_output=True, text=True, check=True).stdout
+    out = subprocess.run([exe, scen] + list(extra), capture_output=True, text=True, check=True).stdout
     res = {}
     for line in out.splitlines():
         p = line.split()
@@ -302,3 +302,19 @@ def test_matcher_adapter_every_member(tmp_path):
     ret, got = R["fuse_sim3"]
     assert ret == nfused and nfused > 30 and np.array_equal(got, repl)
     assert np.array_equal(R["fuse_sim3_events"][1], np.array(events, np.int64))
+
+
+@pytest.mark.gpu
+def test_matcher_constructed_per_call_is_free(tmp_path):
+    """The reference builds an ORBmatcher as a stack local on every call (src/Tracking.cc:2789 and eleven more sites).  The
+    adapter's thread_local pool must make that free: 1000 calls with a matcher constructed per call take the same time as
+    1000 calls on one object (within 10 %), perform no allocating CUDA call after the first, and return the same matches."""
+    S, _ = _scenario()
+    ret, v = _run(tmp_path, S, ("pool",))["pool"]
+    n, per_call, reused, allocs, pooled, same = (int(x) for x in v)
+    per_call, reused = per_call / 10.0, reused / 10.0
+    print(f"per-call construction {per_call:.1f} us/call, reused object {reused:.1f} us/call, allocating CUDA calls {allocs}")
+    assert n == 1000 and ret > 0 and same == 1
+    assert allocs == 0
+    assert pooled == 1                                    # every temporary returned its set; none was created twice
+    assert per_call <= 1.10 * reused + 5.0, (per_call, reused)

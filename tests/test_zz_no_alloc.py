@@ -42,7 +42,9 @@ def test_static_scratch_knn_matches_allocating_entry_point(oracle_mod):
         q_dev = torch.from_numpy(q).cuda()
         D = KnnDatabase(m, None, row_offset=row_offset, device_ptr=rows_dev.data_ptr(), n=ndb)
         d_ref, i_ref = _run(m, D, q_dev, nq, k, static=False)
+        allocs = m._L.orbm_debug_alloc_count()
         d_new, i_new = _run(m, D, q_dev, nq, k, static=True)
+        assert m._L.orbm_debug_alloc_count() == allocs        # the library made no cudaMalloc / cudaMallocHost / stream creation
         assert np.array_equal(d_new, d_ref) and np.array_equal(i_new, i_ref)
         od, oi = om.knn(q, rows, k)                            # and both against the CPU oracle
         assert np.array_equal(d_new, od) and np.array_equal(i_new, oi + row_offset)
