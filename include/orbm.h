@@ -148,6 +148,17 @@ int orbm_search_triangulation(orbm_handle h, orbm_frame kf1, const orbm_featvec*
                               orbm_frame kf2, const orbm_featvec* fv2, const uint8_t* free2, const float* ep,
                               const float* scale_factors2, const float* F12, const float* sigma2, int nlevels,
                               int coarse, int check_orientation, int* matches12, int* nmatches);
+/* SearchForTriangulation (:907-1146) for cameras whose epipolar predicate stays with the caller: the reference calls the virtual
+ * pCamera1->epipolarConstrain (:1072), and the only settings it ships are KannalaBrandt8, whose predicate triangulates through
+ * an SVD (src/CameraModels/KannalaBrandt8.cpp:216-220, 306-380).  For every keypoint i1 of KF1 this returns the KF2 candidates
+ * that survive all tests the reference makes BEFORE that predicate (same vocabulary node, no map point, DescriptorDistance <=
+ * TH_LOW, outside the epipole disc :1026-1032), in the reference's scan order: cand_idx2 / cand_dist are n1 x cap ints,
+ * cand_count[i1] the true number (ORBM_ERR_CAPACITY if any exceeds cap: call again with a larger cap).  The caller then runs
+ * the reference's inner loop over them with its own camera object (mam3slam_b200/cpp/ORBmatcher.h does). */
+int orbm_triangulation_candidates(orbm_handle h, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* free1,
+                                  orbm_frame kf2, const orbm_featvec* fv2, const uint8_t* free2, const float* ep,
+                                  const float* scale_factors2, int nlevels, int cap, int* cand_idx2, int* cand_dist,
+                                  int* cand_count);
 
 /* ---- brute-force k-NN Hamming search (BASELINE config 5: cross-map search at scale) ----
  * For each of nq queries the k smallest distances over ndb rows, ties to the lowest row (a strict '<' scan).

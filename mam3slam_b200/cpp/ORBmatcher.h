@@ -10,6 +10,7 @@
 #ifndef MAM3SLAM_B200_ORBMATCHER_H
 #define MAM3SLAM_B200_ORBMATCHER_H
 
+#include <cmath>
 #include <cstring>
 #include <set>
 #include <stdexcept>
@@ -240,7 +241,11 @@ public:
     }
 
     // SearchForTriangulation(KeyFrame *pKF1, KeyFrame *pKF2, vector<pair<size_t,size_t>> &vMatchedPairs, bOnlyStereo, bCoarse)
-    // (src/ORBmatcher.cc:907-1146), monocular + Pinhole (a fisheye pair passes bCoarse and tests on the host).
+    // (src/ORBmatcher.cc:907-1146), monocular.  The reference tests each candidate with the virtual
+    // pCamera1->epipolarConstrain (:1072).  Pinhole pairs (GetType() == CAM_PINHOLE) take the device path, which evaluates
+    // Pinhole's fundamental-matrix test inside the kernel; every other camera (KannalaBrandt8: the only settings the reference
+    // ships) takes searchForTriangulationHostPredicate below, where the device produces the candidates and the caller's own
+    // camera object judges them in the reference's order - the same matches as the reference for ANY GeometricCamera.
     template <class KeyFrameT>
     int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
                                const bool bOnlyStereo, const bool bCoarse = false) {
@@ -273,12 +278,88 @@ public:
         bindFrame(*pKF2, b_);
         std::vector<int> vMatches12(pKF1->N, -1);
         int nmatches = 0;
+        if (!bCoarse && (pKF1->mpCamera->GetType() != 0u || pKF2->mpCamera->GetType() != 0u)) {      // not CAM_PINHOLE (GeometricCamera.h:95)
+            nmatches = searchForTriangulationHostPredicate(pKF1, pKF2, fv1, fv2, free1, free2, epf, R12, t12, vMatches12);
+            vMatchedPairs.reserve(nmatches);
+            for (size_t i = 0, iend = vMatches12.size(); i < iend; i++)
+                if (vMatches12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
+            return nmatches;
+        }
         check(orbm_search_triangulation(h_, a_, &fv1.view, free1.data(), b_, &fv2.view, free2.data(), epf, pKF2->mvScaleFactors.data(),
                                         F, pKF2->mvLevelSigma2.data(), (int)pKF2->mvScaleFactors.size(), bCoarse, mbCheckOrientation,
                                         vMatches12.data(), &nmatches), "orbm_search_triangulation");
         vMatchedPairs.reserve(nmatches);
         for (size_t i = 0, iend = vMatches12.size(); i < iend; i++)           // :1135-1143
             if (vMatches12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
+        return nmatches;
+    }
+
+    // The inner loop of SearchForTriangulation (:995-1078) over the device-made candidate lists, with the caller's cameras.
+    // The lists hold, in scan order, exactly the candidates that reach `bCoarse || pCamera1->epipolarConstrain(...)` when the
+    // running bestDist is ignored; applying `dist > bestDist -> continue` here restores the reference's sequence of predicate
+    // calls and its "last minimum among those that pass" result.  Then the rotation histogram (:1092-1133).
+    template <class KeyFrameT, class FeatVecT, class Mat3T, class Vec3T>
+    int searchForTriangulationHostPredicate(KeyFrameT* pKF1, KeyFrameT* pKF2, FeatVecT& fv1, FeatVecT& fv2, const std::vector<uint8_t>& free1,
+                                            const std::vector<uint8_t>& free2, const float* epf, const Mat3T& R12, const Vec3T& t12,
+                                            std::vector<int>& vMatches12) {
+        const int n1 = pKF1->N;
+        int cap = 16;
+        std::vector<int> ci, cd, cc(n1, 0);
+        for (;;) {
+            ci.assign((size_t)n1 * cap, -1); cd.assign((size_t)n1 * cap, 0);
+            const int rc = orbm_triangulation_candidates(h_, a_, &fv1.view, free1.data(), b_, &fv2.view, free2.data(), epf,
+                                                         pKF2->mvScaleFactors.data(), (int)pKF2->mvScaleFactors.size(), cap, ci.data(),
+                                                         cd.data(), cc.data());
+            if (rc == ORBM_ERR_CAPACITY) { for (int c : cc) if (c > cap) cap = c; continue; }
+            check(rc, "orbm_triangulation_candidates");
+            break;
+        }
+        auto* pCamera1 = pKF1->mpCamera;
+        auto* pCamera2 = pKF2->mpCamera;
+        const float factor = 1.0f / HISTO_LENGTH;                              // :943
+        std::vector<int> binOf(n1, -1), binSize(HISTO_LENGTH, 0);
+        int nmatches = 0;
+        for (size_t p1 = 0; p1 < fv1.idx.size(); p1++) {                       // nodes in order, each node's list in order (:955-966)
+            const int idx1 = fv1.idx[p1];                                       // (a keypoint belongs to exactly one node)
+            if (!cc[idx1]) continue;
+            const auto& kp1 = pKF1->mvKeysUn[idx1];
+            int bestDist = TH_LOW, bestIdx2 = -1;                               // :995-996
+            for (int c = 0; c < cc[idx1]; c++) {
+                const int idx2 = ci[(size_t)idx1 * cap + c], dist = cd[(size_t)idx1 * cap + c];
+                if (dist > bestDist) continue;                                  // :1017
+                const auto& kp2 = pKF2->mvKeysUn[idx2];
+                if (pCamera1->epipolarConstrain(pCamera2, kp1, kp2, R12, t12, pKF1->mvLevelSigma2[kp1.octave],
+                                                pKF2->mvLevelSigma2[kp2.octave])) {                       // :1072
+                    bestIdx2 = idx2; bestDist = dist;
+                }
+            }
+            if (bestIdx2 < 0) continue;
+            vMatches12[idx1] = bestIdx2;
+            nmatches++;
+            if (mbCheckOrientation) {                                           // :1092-1103
+                float rot = kp1.angle - pKF2->mvKeysUn[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                binOf[idx1] = bin; binSize[bin]++;
+            }
+        }
+        if (mbCheckOrientation) {                                               // :1112-1133, ComputeThreeMaxima :2012-2053
+            int top[3] = {-1, -1, -1}, size[3] = {0, 0, 0};
+            for (int i = 0; i < HISTO_LENGTH; i++) {
+                int at = binSize[i] > size[0] ? 0 : binSize[i] > size[1] ? 1 : binSize[i] > size[2] ? 2 : 3;
+                for (int k = 2; k > at; k--) { top[k] = top[k - 1]; size[k] = size[k - 1]; }
+                if (at < 3) { top[at] = i; size[at] = binSize[i]; }
+            }
+            if (size[1] < 0.1f * (float)size[0]) top[1] = top[2] = -1;
+            else if (size[2] < 0.1f * (float)size[0]) top[2] = -1;
+            for (int idx1 = 0; idx1 < n1; idx1++) {
+                const int b = binOf[idx1];
+                if (b < 0 || b == top[0] || b == top[1] || b == top[2]) continue;
+                vMatches12[idx1] = -1;
+                nmatches--;
+            }
+        }
         return nmatches;
     }
 

@@ -752,6 +752,61 @@ int orbm_search_triangulation(orbm_handle M, orbm_frame kf1, const orbm_featvec*
     return ORBM_OK;
 }
 
+// SearchForTriangulation for cameras whose epipolar predicate stays on the host (any GeometricCamera; the reference ships only
+// KannalaBrandt8 settings, whose predicate triangulates through an Eigen SVD: src/CameraModels/KannalaBrandt8.cpp:216-220,
+// 306-380).  Returns, per keypoint i1 of KF1, the candidates the reference's inner loop would hand to
+// pCamera1->epipolarConstrain if its running `bestDist` were ignored: KF2 keypoints of the same vocabulary node, without a map
+// point, DescriptorDistance <= TH_LOW, outside the epipole's 10-px-per-scale disc - in the reference's scan order.
+int orbm_triangulation_candidates(orbm_handle M, orbm_frame kf1, const orbm_featvec* fv1, const uint8_t* free1, orbm_frame kf2,
+                                  const orbm_featvec* fv2, const uint8_t* free2, const float* ep, const float* scale_factors2,
+                                  int nlevels, int cap, int* cand_idx2, int* cand_dist, int* cand_count) {
+    if (!M || !kf1 || !kf2 || !free1 || !free2 || !ep || !scale_factors2 || nlevels < 1 || cap < 1 || !cand_idx2 || !cand_dist ||
+        !cand_count || !validFeatVec(fv1, kf1->n) || !validFeatVec(fv2, kf2->n))
+        return ORBM_ERR_INVALID;
+    for (int i = 0; i < kf1->n; ++i) cand_count[i] = 0;
+    SearchIO io;
+    joinQueries(fv1, fv2, free1, io);
+    M->lastEvals = 0;
+    if (io.nq == 0) return ORBM_OK;
+    CKM(cudaSetDevice(M->device));
+    const int nq = io.nq, n2 = kf2->n;
+    Stage S(M);
+    const size_t oSrc = S.take<int>(nq), oRun = S.take<int2>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oFree = S.take<uint8_t>(std::max(n2, 1));
+    const size_t oTab = S.take<float>(nlevels), oEv = S.take<unsigned long long>(1);
+    const size_t inEnd = S.off;
+    const size_t oCnt = S.take<int>(nq), oIdx = S.take<int>((size_t)nq * cap), oDist = S.take<int>((size_t)nq * cap);
+    int rc = ensureScratch(M, S.off);
+    if (rc) return rc;
+    memcpy(S.host<int>(oSrc), io.qsrc.data(), (size_t)nq * sizeof(int));
+    memcpy(S.host<int2>(oRun), io.qrun.data(), (size_t)nq * sizeof(int2));
+    if (io.nBow) memcpy(S.host<int>(oBow), io.bowIdx, (size_t)io.nBow * sizeof(int));
+    if (n2) memcpy(S.host<uint8_t>(oFree), free2, (size_t)n2);
+    memcpy(S.host<float>(oTab), scale_factors2, (size_t)nlevels * sizeof(float));
+    *S.host<unsigned long long>(oEv) = 0;
+    CKM(cudaMemcpyAsync(M->scratch, M->pinned, inEnd, cudaMemcpyHostToDevice, M->stream));
+    k_tri_candidates<<<(nq + 7) / 8, 256, 0, M->stream>>>(nq, S.dev<int>(oSrc), S.dev<int2>(oRun), S.dev<int>(oBow), kf1->descDev,
+                                                          kf2->descDev, kf2->kp4, S.dev<uint8_t>(oFree), S.dev<float>(oTab), ep[0], ep[1],
+                                                          ORBM_TH_LOW, cap, S.dev<int>(oIdx), S.dev<int>(oDist), S.dev<int>(oCnt),
+                                                          S.dev<unsigned long long>(oEv));
+    ++M->launches;
+    CKM(cudaGetLastError());
+    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oEv, (uint8_t*)M->scratch + oEv, S.off - oEv, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaStreamSynchronize(M->stream));
+    M->lastEvals = (long long)*S.host<unsigned long long>(oEv);
+    const int* hc = S.host<int>(oCnt); const int* hi = S.host<int>(oIdx); const int* hd = S.host<int>(oDist);
+    int status = ORBM_OK;
+    for (int q = 0; q < nq; ++q) {
+        const int i1 = io.qsrc[q];
+        cand_count[i1] = hc[q];                                 // the true number: > cap means the lists were cut
+        if (hc[q] > cap) status = ORBM_ERR_CAPACITY;
+        const int m = std::min(hc[q], cap);
+        memcpy(cand_idx2 + (size_t)i1 * cap, hi + (size_t)q * cap, (size_t)m * sizeof(int));
+        memcpy(cand_dist + (size_t)i1 * cap, hd + (size_t)q * cap, (size_t)m * sizeof(int));
+    }
+    if (status == ORBM_ERR_CAPACITY) M->err = "orbm_triangulation_candidates: a keypoint has more candidates than `cap`; call again with a larger cap";
+    return status;
+}
+
 // ---- brute-force k-NN ----------------------------------------------------------------------------------------------------
 int orbm_db_create(orbm_handle M, const uint8_t* rows, long long ndb, int rows_on_device, long long row_offset, orbm_db* out) {
     if (!M || !out || ndb < 0 || (ndb > 0 && !rows)) return ORBM_ERR_INVALID;

@@ -955,6 +955,56 @@ __global__ void __launch_bounds__(256) k_track_finish(const TrackBatch T) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// SearchForTriangulation with a caller-side epipolar predicate (any GeometricCamera, e.g. KannalaBrandt8): the candidates of
+// every query keypoint of KF1 that survive everything the reference tests BEFORE pCamera1->epipolarConstrain
+// (src/ORBmatcher.cc:1000-1033: no map point in KF2, DescriptorDistance <= TH_LOW, the epipole-distance test), in the
+// reference's scan order (the KF2 feature list of the common vocabulary node).  The host then runs the reference's inner loop
+// over these few candidates with the caller's own camera object.  One warp per query; a lane takes one candidate per round;
+// the survivors of a round are written in scan order by a ballot rank.
+__global__ void __launch_bounds__(256) k_tri_candidates(int nq, const int* __restrict__ qsrc, const int2* __restrict__ qrun,
+                                                        const int* __restrict__ bowIdx, const uint32_t* __restrict__ desc1,
+                                                        const uint32_t* __restrict__ desc2, const float4* __restrict__ kp4_2,
+                                                        const uint8_t* __restrict__ free2, const float* __restrict__ scale2,
+                                                        float ep0, float ep1, int th, int cap, int* __restrict__ outIdx,
+                                                        int* __restrict__ outDist, int* __restrict__ outCount,
+                                                        unsigned long long* __restrict__ evals) {
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const int i1 = qsrc[q];
+    const int2 run = qrun[q];
+    uint32_t d1[8];
+    {
+        const uint4 a = reinterpret_cast<const uint4*>(desc1 + (size_t)8 * i1)[0], b = reinterpret_cast<const uint4*>(desc1 + (size_t)8 * i1)[1];
+        d1[0] = a.x; d1[1] = a.y; d1[2] = a.z; d1[3] = a.w; d1[4] = b.x; d1[5] = b.y; d1[6] = b.z; d1[7] = b.w;
+    }
+    int count = 0, ev = 0;
+    for (int base = run.x; base < run.y; base += 32) {
+        const int p = base + lane;
+        bool ok = false;
+        int idx2 = -1, dist = 0;
+        if (p < run.y) {
+            idx2 = bowIdx[p];
+            if (free2[idx2]) {                                                  // :1001-1005 (vbMatched2 is never set in the reference)
+                const uint4* r = reinterpret_cast<const uint4*>(desc2 + (size_t)8 * idx2);
+                dist = hamming8(d1, r[0], r[1]);
+                ++ev;
+                if (dist <= th) {                                               // :1017 (the running best is applied by the host)
+                    const float4 k = kp4_2[idx2];
+                    const float dx = __fsub_rn(ep0, k.x), dy = __fsub_rn(ep1, k.y);      // :1026-1032, no FMA contraction
+                    ok = !(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, scale2[__float_as_int(k.w)]));
+                }
+            }
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        const int pos = count + __popc(m & ((1u << lane) - 1u));
+        if (ok && pos < cap) { outIdx[(size_t)q * cap + pos] = idx2; outDist[(size_t)q * cap + pos] = dist; }
+        count += __popc(m);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ev += __shfl_xor_sync(0xffffffffu, ev, o);
+    if (lane == 0) { outCount[q] = count; if (ev) atomicAdd(evals, (unsigned long long)ev); }
+}
+
 // brute-force k-NN.  grid (query blocks, db chunks); block kKnnThreads; thread = query.
 constexpr int kKnnThreads = 256, kKnnTileRows = 128, kKnnMaxK = 16;
 

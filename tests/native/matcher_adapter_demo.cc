@@ -254,6 +254,18 @@ int main(int argc, char** argv) {
         r = m06.SearchForTriangulation(&W->KF1, &W->KF2, pairs, true, false);
         emit("tri_stereo", r, std::vector<int>(1, (int)pairs.size()));
     }
+    for (int ori = 0; ori < 2; ori++) {   // the same pair seen through a non-Pinhole camera: the predicate is the camera's own (:1072)
+        auto W = build(path);
+        W->KF1.mpCamera->mnType = 1;                     // CAM_FISHEYE (KF1 and KF2 share the camera object, like one agent's keyframes)
+        MAM3SLAM::ORBmatcher mf(0.6f, ori != 0);
+        std::vector<std::pair<size_t, size_t> > pairs;
+        const int r = mf.SearchForTriangulation(&W->KF1, &W->KF2, pairs, false, false);
+        std::vector<int> o;
+        o.push_back((int)W->KF1.mpCamera->calls);
+        o.push_back((int)(W->KF1.mpCamera->callHash & 0x7fffffffu));
+        for (auto& p : pairs) { o.push_back((int)p.first); o.push_back((int)p.second); }
+        emit(ori ? "tri_fisheye_ori" : "tri_fisheye", r, o);
+    }
     {
         auto W = build(path);
         const float* t1 = arr<float>(W->blob, "t1");

@@ -72,8 +72,24 @@ struct Sim3 {                                    // Sophus::Sim3f
 };
 struct Camera {                                  // GeometricCamera / Pinhole (src/CameraModels/Pinhole.cpp:32-38, 96-100)
     float fx = 1, fy = 1, cx = 0, cy = 0;
+    unsigned mnType = 0;                         // CAM_PINHOLE = 0, CAM_FISHEYE = 1 (include/CameraModels/GeometricCamera.h:93-96)
+    unsigned GetType() const { return mnType; }
     Vec2 project(const Vec3& p) const { return Vec2{{fx * p(0) / p(2) + cx, fy * p(1) / p(2) + cy}}; }
     Mat3 toK_() const { Mat3 K; K(0, 0) = fx; K(0, 2) = cx; K(1, 1) = fy; K(1, 2) = cy; return K; }
+    // Stand-in for a non-Pinhole GeometricCamera::epipolarConstrain (KannalaBrandt8's triangulates through an SVD): any pure
+    // predicate of its arguments will do to test that the adapter calls the CALLER'S camera, on the reference's candidates and
+    // in the reference's order.  It logs its calls: count and an order-sensitive hash of (kp1.x, kp2.y) bit patterns.
+    long calls = 0; uint32_t callHash = 0;
+    bool epipolarConstrain(Camera* /*other*/, const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const Mat3& /*R12*/, const Vec3& t12,
+                           const float sigmaLevel, const float unc) {
+        uint32_t a, b;
+        std::memcpy(&a, &kp1.pt.x, 4); std::memcpy(&b, &kp2.pt.y, 4);
+        callHash = callHash * 1000003u + (a ^ (b * 31u));
+        ++calls;
+        const float v = (kp1.pt.y - kp2.pt.y) + t12(1);
+        const float w = kp1.pt.x - kp2.pt.x;
+        return v * v < 9.0f * unc && w * w < 40000.0f * sigmaLevel;
+    }
 };
 
 struct KeyFrame;

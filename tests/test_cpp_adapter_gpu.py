@@ -209,6 +209,77 @@ def test_matcher_adapter_every_member(tmp_path):
         assert nm > (5 if coarse else 0)
     assert R["tri_stereo"][0] == 0 and R["tri_stereo"][1][0] == 0
 
+    # M6 through a non-Pinhole camera (the reference ships KannalaBrandt8 settings only): candidates from the device, the
+    # predicate from the caller's camera object.  Expected values: the reference's loop (src/ORBmatcher.cc:955-1133) restated
+    # here with the shim camera's mock predicate in float32 - matches, number and ORDER of the predicate calls.
+    def ref_loop(check_ori):
+        m12 = np.full(n1, -1, np.int64)
+        calls, h = 0, 0
+        bins = {}
+        nodes2 = {int(nd): fv2[2][fv2[1][j]:fv2[1][j + 1]] for j, nd in enumerate(fv2[0])}
+        for j, nd in enumerate(fv1[0]):
+            if int(nd) not in nodes2:
+                continue
+            for i1 in fv1[2][fv1[1][j]:fv1[1][j + 1]]:
+                if not free1[i1]:
+                    continue
+                best_d, best = 50, -1
+                for i2 in nodes2[int(nd)]:
+                    if not free2[i2]:
+                        continue
+                    d = int(np.unpackbits(d1[i1] ^ d2[i2]).sum())
+                    if d > 50 or d > best_d:
+                        continue
+                    ex, ey = f32(ep[0] - k2["x"][i2]), f32(ep[1] - k2["y"][i2])
+                    if f32(f32(ex * ex) + f32(ey * ey)) < f32(f32(100) * scale[k2["octave"][i2]]):
+                        continue
+                    a = int(np.array([k1["x"][i1]], f32).view(np.uint32)[0])
+                    b = int(np.array([k2["y"][i2]], f32).view(np.uint32)[0])
+                    h = (h * 1000003 + (a ^ ((b * 31) & 0xffffffff))) & 0xffffffff
+                    calls += 1
+                    v = f32(f32(k1["y"][i1] - k2["y"][i2]) + t12[1])
+                    w = f32(k1["x"][i1] - k2["x"][i2])
+                    if f32(v * v) < f32(f32(9) * S["sigma2"][k2["octave"][i2]]) and f32(w * w) < f32(f32(40000) * S["sigma2"][k1["octave"][i1]]):
+                        best, best_d = int(i2), d
+                if best >= 0:
+                    m12[i1] = best
+                    if check_ori:
+                        rot = f32(k1["angle"][i1] - k2["angle"][best])
+                        if rot < 0:
+                            rot = f32(rot + f32(360))
+                        b_ = int(np.floor(float(f32(rot * f32(f32(1) / f32(30)))) + 0.5))    # C round(): half away from zero; rot >= 0
+                        bins.setdefault(0 if b_ == 30 else b_, []).append(int(i1))
+        if check_ori:
+            size = np.zeros(30, np.int64)
+            for b_, v_ in bins.items():
+                size[b_] = len(v_)
+            top, mx = [-1, -1, -1], [0, 0, 0]
+            for i in range(30):
+                s_ = int(size[i])
+                if s_ > mx[0]:
+                    mx, top = [s_, mx[0], mx[1]], [i, top[0], top[1]]
+                elif s_ > mx[1]:
+                    mx, top = [mx[0], s_, mx[1]], [top[0], i, top[1]]
+                elif s_ > mx[2]:
+                    mx[2], top[2] = s_, i
+            if mx[1] < f32(0.1) * f32(mx[0]):
+                top[1] = top[2] = -1
+            elif mx[2] < f32(0.1) * f32(mx[0]):
+                top[2] = -1
+            for b_, v_ in bins.items():
+                if b_ not in top:
+                    m12[v_] = -1
+        return m12, calls, h & 0x7fffffff
+
+    for name, ori in (("tri_fisheye", False), ("tri_fisheye_ori", True)):
+        m12, calls, h = ref_loop(ori)
+        ret, got = R[name]
+        i1 = np.nonzero(m12 >= 0)[0]
+        assert got[0] == calls and got[1] == h, (name, got[:2], calls, h)
+        assert ret == len(i1) and np.array_equal(got[2:], np.stack([i1, m12[i1]], 1).reshape(-1)), name
+        assert calls > 50 and 0 < len(i1)
+    assert not np.array_equal(R["tri_fisheye"][1][2:], R["tri"][1])          # the mock predicate is not the Pinhole test
+
     # M8 SearchBySim3
     t12s = t1 - t2
     t21s = -t12s
