@@ -72,22 +72,25 @@ int orbm_features_in_area(orbm_handle h, orbm_frame f, float x, float y, float r
  * Common arguments: nq queries; valid[q] = the query survives the reference's pre-checks; qdesc = nq x 32 bytes
  * (MapPoint::GetDescriptor); scale_factors = mvScaleFactors (nlevels floats); kp_match[n] (out) = index of the query
  * assigned to keypoint i or -1 (the reference writes F.mvpMapPoints[i] = pMP); *nmatches = the reference's return
- * value.  occupied[n] (in/out) = slot already holds a map point that blocks matching; accepted matches occupy their
- * slot for later queries (sequential semantics of the reference loop). */
+ * value (it counts assignments).  occupied[n] (in/out) = slot already holds a map point that blocks matching.  Sequential
+ * semantics of the reference loop: an accepted match is written into the slot, and it blocks the slot for later queries
+ * iff q_occupies[q] != 0, i.e. the query's MapPoint has Observations() > 0 (src/ORBmatcher.cc:92-94, 1745-1747); a
+ * later query may otherwise take the same keypoint and overwrite it (kp_match = the LAST one).  q_occupies = NULL: every
+ * match occupies (the KeyFrame variant :1955, and every map point a mono system tracks). */
 
 /* replaces SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints) (src/ORBmatcher.cc:43-213),
  * mono branch.  level = mnTrackScaleLevel, view_cos = mTrackViewCos (RadiusByViewingCos :215-221). */
 int orbm_search_local_map(orbm_handle h, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels,
                           int nq, const uint8_t* valid, const float* proj_x, const float* proj_y, const int* level,
                           const float* view_cos, const uint8_t* qdesc, float th, float nnratio, int* kp_match,
-                          int* nmatches);
+                          int* nmatches, const uint8_t* q_occupies);
 /* replaces SearchByProjection(Frame& Cur, const Frame& Last, th, bMono=true) (:1676-1887) and
  * SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:1889-2010): octave = last octave / predicted
  * level, qangle = angle of the source keypoint, th_dist = TH_HIGH or ORBdist. */
 int orbm_search_frame(orbm_handle h, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
                       const uint8_t* valid, const float* u, const float* v, const int* octave, const float* qangle,
                       const uint8_t* qdesc, float th, int th_dist, int check_orientation, int* kp_match,
-                      int* nmatches);
+                      int* nmatches, const uint8_t* q_occupies);
 /* replaces SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) (:427-532) and its pointKFs
  * overload (:534-646): matched[n] in/out = vpMatched[i] != NULL. */
 int orbm_search_sim3(orbm_handle h, orbm_frame kf, uint8_t* matched, const float* scale_factors, int nlevels, int nq,

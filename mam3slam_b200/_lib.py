@@ -105,8 +105,8 @@ def _bind_matcher(L):
     L.orbm_frame_destroy.restype = None
     L.orbm_frame_grid.argtypes = [vp, vp, vp, vp]
     L.orbm_features_in_area.argtypes = [vp, vp, f32, f32, f32, i32, i32, vp, i32, ip]
-    L.orbm_search_local_map.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, f32, vp, ip]
-    L.orbm_search_frame.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, i32, i32, vp, ip]
+    L.orbm_search_local_map.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, f32, vp, ip, vp]
+    L.orbm_search_frame.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, f32, i32, i32, vp, ip, vp]
     L.orbm_search_sim3.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, i32, f32, vp, ip]
     L.orbm_search_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, vp, ip]
     L.orbm_knn_merge_device.argtypes = [vp, vp, vp, C.c_size_t, i32, i32, i32, vp, vp, vp]

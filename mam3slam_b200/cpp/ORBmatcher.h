@@ -65,7 +65,7 @@ public:
     template <class FrameT> int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool /*bMono*/) {
         const auto Tcw = CurrentFrame.GetPose();
         const int N = LastFrame.N;
-        std::vector<uint8_t> valid(N, 0), qdesc((size_t)N * 32);
+        std::vector<uint8_t> valid(N, 0), qdesc((size_t)N * 32), qocc(N, 0);
         std::vector<float> u(N, 0.f), v(N, 0.f), ang(N, 0.f);
         std::vector<int> oct(N, 0);
         for (int i = 0; i < N; i++) {                                         // :1696-1729
@@ -78,6 +78,7 @@ public:
             if (uv(0) < CurrentFrame.mnMinX || uv(0) > CurrentFrame.mnMaxX) continue;
             if (uv(1) < CurrentFrame.mnMinY || uv(1) > CurrentFrame.mnMaxY) continue;
             valid[i] = 1; u[i] = uv(0); v[i] = uv(1);
+            qocc[i] = pMP->Observations() > 0;                                  // whether this point, once assigned, blocks its keypoint (:1745-1747)
             oct[i] = LastFrame.mvKeys[i].octave;
             ang[i] = LastFrame.mvKeysUn[i].angle;
             const auto d = pMP->GetDescriptor();
@@ -91,7 +92,7 @@ public:
         int nmatches = 0;
         check(orbm_search_frame(h_, a_, occ.data(), CurrentFrame.mvScaleFactors.data(), (int)CurrentFrame.mvScaleFactors.size(), N,
                                 valid.data(), u.data(), v.data(), oct.data(), ang.data(), qdesc.data(), th, TH_HIGH,
-                                mbCheckOrientation, kpMatch.data(), &nmatches), "orbm_search_frame");
+                                mbCheckOrientation, kpMatch.data(), &nmatches, qocc.data()), "orbm_search_frame");
         for (int i2 = 0; i2 < CurrentFrame.N; i2++)
             if (kpMatch[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = LastFrame.mvpMapPoints[kpMatch[i2]];
         return nmatches;
@@ -103,7 +104,7 @@ public:
     int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3, const bool bFarPoints = false,
                            const float thFarPoints = 50.0f) {
         const int nq = (int)vpMapPoints.size();
-        std::vector<uint8_t> valid(nq, 0), qdesc((size_t)nq * 32);
+        std::vector<uint8_t> valid(nq, 0), qdesc((size_t)nq * 32), qocc(nq, 0);
         std::vector<float> px(nq, 0.f), py(nq, 0.f), vc(nq, 0.f);
         std::vector<int> lvl(nq, 0);
         for (int i = 0; i < nq; i++) {                                        // :51-63
@@ -112,6 +113,7 @@ public:
             if (bFarPoints && pMP->mTrackDepth > thFarPoints) continue;
             if (pMP->isBad()) continue;
             valid[i] = 1; px[i] = pMP->mTrackProjX; py[i] = pMP->mTrackProjY; lvl[i] = pMP->mnTrackScaleLevel; vc[i] = pMP->mTrackViewCos;
+            qocc[i] = pMP->Observations() > 0;                                 // once assigned, does it block its keypoint (:92-94)
             const auto d = pMP->GetDescriptor();
             std::memcpy(&qdesc[(size_t)i * 32], d.template ptr<uint8_t>(), 32);
         }
@@ -122,7 +124,7 @@ public:
         int nmatches = 0;
         check(orbm_search_local_map(h_, a_, occ.data(), F.mvScaleFactors.data(), (int)F.mvScaleFactors.size(), nq, valid.data(),
                                     px.data(), py.data(), lvl.data(), vc.data(), qdesc.data(), th, mfNNratio, kpMatch.data(),
-                                    &nmatches), "orbm_search_local_map");
+                                    &nmatches, qocc.data()), "orbm_search_local_map");
         for (int i = 0; i < F.N; i++) if (kpMatch[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[kpMatch[i]];
         return nmatches;
     }
@@ -160,7 +162,7 @@ public:
         int nmatches = 0;
         check(orbm_search_frame(h_, a_, occ.data(), CurrentFrame.mvScaleFactors.data(), (int)CurrentFrame.mvScaleFactors.size(), nq,
                                 Q.valid.data(), Q.u.data(), Q.v.data(), Q.level.data(), ang.data(), Q.desc.data(), th, ORBdist,
-                                mbCheckOrientation, kpMatch.data(), &nmatches), "orbm_search_frame");
+                                mbCheckOrientation, kpMatch.data(), &nmatches, nullptr), "orbm_search_frame");   // :1955: any point blocks
         for (int i2 = 0; i2 < CurrentFrame.N; i2++)
             if (kpMatch[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = vpMPs[kpMatch[i2]];
         return nmatches;

@@ -295,6 +295,7 @@ struct SearchIO {
     const int* bowIdx = nullptr; int nBow = 0;
     const uint8_t* elig = nullptr;
     uint8_t* occ = nullptr;                 // in/out, n bytes
+    const uint8_t* qocc = nullptr;          // per ORIGINAL query (indexed through qsrc): its match occupies the keypoint; NULL = always
     std::vector<int> result, dist;
 };
 
@@ -308,7 +309,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     Stage S(M);
     const size_t oWin = S.take<float4>(nq), oLev = S.take<int2>(nq), oRun = S.take<int2>(nq), oDesc = S.take<uint32_t>((size_t)nq * 8);
     const size_t oAng = S.take<float>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oElig = S.take<uint8_t>(std::max(n, 1));
-    const size_t oOcc = S.take<uint8_t>(std::max(n, 1));
+    const size_t oOcc = S.take<uint8_t>(std::max(n, 1)), oQocc = S.take<uint8_t>(nq);
     const size_t inEnd = S.off;
     const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(16);
     const size_t outEnd = S.off;
@@ -323,6 +324,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     if (io.nBow) memcpy(S.host<int>(oBow), io.bowIdx, (size_t)io.nBow * sizeof(int));
     if (io.elig && n) memcpy(S.host<uint8_t>(oElig), io.elig, n);
     if (io.occ && n) memcpy(S.host<uint8_t>(oOcc), io.occ, n);
+    if (io.qocc) for (int q = 0; q < nq; ++q) S.host<uint8_t>(oQocc)[q] = io.qocc[io.qsrc[q]];
     *S.host<unsigned long long>(oEv) = 0;
     CKM(cudaMemcpyAsync(M->scratch, M->pinned, inEnd, cudaMemcpyHostToDevice, M->stream));
     CKM(cudaMemsetAsync(S.dev<unsigned long long>(oEv), 0, 128, M->stream));
@@ -332,6 +334,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     P.qdesc = S.dev<uint32_t>(oDesc); P.qangle = S.dev<float>(oAng); P.bowIdx = S.dev<int>(oBow);
     P.elig = io.elig ? S.dev<uint8_t>(oElig) : nullptr;
     P.occ = io.occ ? S.dev<uint8_t>(oOcc) : nullptr;
+    P.qocc = io.qocc ? S.dev<uint8_t>(oQocc) : nullptr;
     P.qResult = S.dev<int>(oRes); P.qDist = S.dev<int>(oDist); P.qBin = S.dev<int>(oBin);
     P.evals = S.dev<unsigned long long>(oEv);
     // stateful searches run on one CTA: stage the target frame on chip; stateless ones spread over many CTAs instead
@@ -404,7 +407,8 @@ int orbm_features_in_area(orbm_handle M, orbm_frame f, float x, float y, float r
 // M1: src/ORBmatcher.cc:43-213 (mono branch)
 int orbm_search_local_map(orbm_handle M, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
                           const uint8_t* valid, const float* proj_x, const float* proj_y, const int* level,
-                          const float* view_cos, const uint8_t* qdesc, float th, float nnratio, int* kp_match, int* nmatches) {
+                          const float* view_cos, const uint8_t* qdesc, float th, float nnratio, int* kp_match, int* nmatches,
+                          const uint8_t* q_occupies) {
     if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
     const bool bFactor = th != 1.0;
     SearchIO io;
@@ -418,7 +422,7 @@ int orbm_search_local_map(orbm_handle M, orbm_frame f, uint8_t* occupied, const 
         io.qlev.push_back(levelBounds(l - 1, l));
         io.qsrc.push_back(q);
     }
-    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied;
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied; io.qocc = q_occupies;
     SearchParams P = baseParams();
     P.source = 0; P.state = 1; P.rule = RULE_LOCAL_MAP; P.nnratio = nnratio;
     int rc = runSearch(M, f, P, io);
@@ -432,7 +436,8 @@ int orbm_search_local_map(orbm_handle M, orbm_frame f, uint8_t* occupied, const 
 // M2 / M3: src/ORBmatcher.cc:1676-1887 (mono), :1889-2010
 int orbm_search_frame(orbm_handle M, orbm_frame f, uint8_t* occupied, const float* scale_factors, int nlevels, int nq,
                       const uint8_t* valid, const float* u, const float* v, const int* octave, const float* qangle,
-                      const uint8_t* qdesc, float th, int th_dist, int check_orientation, int* kp_match, int* nmatches) {
+                      const uint8_t* qdesc, float th, int th_dist, int check_orientation, int* kp_match, int* nmatches,
+                      const uint8_t* q_occupies) {
     if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
     SearchIO io;
     for (int q = 0; q < nq; ++q) {
@@ -445,13 +450,20 @@ int orbm_search_frame(orbm_handle M, orbm_frame f, uint8_t* occupied, const floa
         io.qangle.push_back(qangle ? qangle[q] : 0.f);
         io.qsrc.push_back(q);
     }
-    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied;
+    io.nq = (int)io.qsrc.size(); io.qdescSrc = qdesc; io.occ = occupied; io.qocc = q_occupies;
     SearchParams P = baseParams();
     P.source = 0; P.state = 1; P.rule = RULE_BEST_LE; P.thF = (float)th_dist; P.checkOri = check_orientation && qangle;
     int rc = runSearch(M, f, P, io);
     if (rc) return rc;
+    // assignments in query order (a later one overwrites: only possible after a non-occupying match), then the keypoints of
+    // the matches the rotation histogram dropped are cleared (:1862-1884); nmatches = assignments - dropped
     int nm = 0;
-    for (int q = 0; q < io.nq; ++q) if (io.result[q] >= 0) { kp_match[io.result[q]] = io.qsrc[q]; ++nm; }
+    for (int q = 0; q < io.nq; ++q) {
+        const int r = io.result[q];
+        if (r >= 0) { kp_match[r] = io.qsrc[q]; ++nm; }
+        else if (r <= -2) kp_match[-2 - r] = io.qsrc[q];
+    }
+    for (int q = 0; q < io.nq; ++q) if (io.result[q] <= -2) kp_match[-2 - io.result[q]] = -1;
     *nmatches = nm;
     return ORBM_OK;
 }

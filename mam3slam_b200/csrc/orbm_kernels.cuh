@@ -137,6 +137,8 @@ struct SearchParams {
     const float* qangle;
     const uint8_t* elig;         // target-side eligibility (may be NULL)
     uint8_t* occ;                // target-side occupancy bytes, in/out (NULL when state == 0)
+    const uint8_t* qocc;         // state 1: query q's accepted match blocks its keypoint for later queries iff qocc[q] (the
+                                 // assigned MapPoint has Observations() > 0, src/ORBmatcher.cc:92-94, 1745-1747); NULL = always
     int state;                   // 0 = none, 1 = occupancy (claim on accept), 2 = steal-if-better (M5)
     int stageTgt;                // 1 = the launch has room to stage the target frame (grid, kp4, descriptors) in shared memory
     int rule;
@@ -373,7 +375,7 @@ __device__ __forceinline__ bool decide_query(const SearchParams& P, uint32_t e1,
 // keypoint are cleared after the loop).
 __device__ __forceinline__ void update_state(const SearchParams& P, int q, uint32_t e1, uint8_t* occS, uint16_t* mdS, int* m21S) {
     const int bestIdx = (int)(e1 & 0x7ffff);
-    if (P.state == 1) occS[bestIdx] = 1;
+    if (P.state == 1 && (!P.qocc || P.qocc[q])) occS[bestIdx] = 1;
     if (P.state == 2) { m21S[bestIdx] = q; mdS[bestIdx] = (uint16_t)(e1 >> 23); }      // (:706-713)
 }
 
@@ -835,7 +837,10 @@ __global__ void __launch_bounds__(kSearchThreads, 1) k_search(const SearchParams
 }
 
 // rotation-consistency epilogue (e.g. src/ORBmatcher.cc:1862-1884): histogram of accept events, three maxima, drop the rest
-__device__ __forceinline__ void rot_filter_cta(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
+// encode: a dropped query leaves -(k + 2) instead of -1, k = the keypoint it had been assigned: with non-occupying matches
+// (qocc) two queries can have been assigned the same keypoint, and the reference clears the KEYPOINT of every dropped
+// histogram entry (CurrentFrame.mvpMapPoints[rotHist[i][j]] = NULL, :1876), so the host needs to know which one that was
+__device__ __forceinline__ void rot_filter_cta(int nq, const int* __restrict__ qBin, int* __restrict__ qResult, bool encode = false) {
     __shared__ int hist[ORBM_HISTO_LENGTH];
     __shared__ int keep[3];
     const int tid = threadIdx.x;
@@ -858,11 +863,11 @@ __device__ __forceinline__ void rot_filter_cta(int nq, const int* __restrict__ q
     __syncthreads();
     for (int q = tid; q < nq; q += blockDim.x) {
         const int b = qBin[q];
-        if (b >= 0 && b != keep[0] && b != keep[1] && b != keep[2]) qResult[q] = -1;
+        if (b >= 0 && b != keep[0] && b != keep[1] && b != keep[2]) qResult[q] = (encode && qResult[q] >= 0) ? -2 - qResult[q] : -1;
     }
 }
 __global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
-    rot_filter_cta(nq, qBin, qResult);
+    rot_filter_cta(nq, qBin, qResult, true);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -926,6 +931,7 @@ __global__ void __launch_bounds__(kSearchThreads, 1) k_track_search(const TrackB
     P.qangle = T.qangle + (size_t)last * T.stride;
     P.elig = nullptr;
     P.occ = T.occ + (size_t)cur * T.stride;
+    P.qocc = nullptr;                  // every keypoint of the last frame stands for an observed map point: a match occupies
     P.stageTgt = T.stageTgt;
     P.state = 1; P.rule = RULE_BEST_LE; P.thF = T.thF; P.thI = 0; P.nnratio = 0.f; P.none2 = 256;
     P.checkOri = T.checkOri; P.chi2 = 0; P.invSigma2 = nullptr;

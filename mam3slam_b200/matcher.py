@@ -199,7 +199,10 @@ class ORBmatcher:
         return MatchFrame(self, kps, desc, bounds, on_device, n)
 
     # ---- M1: SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) ----
-    def SearchByProjection_LocalMap(self, F, occupied, scale_factors, valid, proj_x, proj_y, level, view_cos, qdesc, th=1.0):
+    def SearchByProjection_LocalMap(self, F, occupied, scale_factors, valid, proj_x, proj_y, level, view_cos, qdesc, th=1.0,
+                                    q_occupies=None):
+        """q_occupies[q] = the query's MapPoint has Observations() > 0 (src/ORBmatcher.cc:92-94); None = every match occupies."""
+        qo = None if q_occupies is None else _c(q_occupies, np.uint8)
         occ = _c(occupied, np.uint8).copy()
         sf = _c(scale_factors, np.float32)
         valid, px, py = _c(valid, np.uint8), _c(proj_x, np.float32), _c(proj_y, np.float32)
@@ -207,12 +210,15 @@ class ORBmatcher:
         km = np.full(F.n, -1, np.int32)
         nm = C.c_int(0)
         check_m(self._L.orbm_search_local_map(self._h, F._f, _p(occ), _p(sf), len(sf), len(valid), _p(valid), _p(px), _p(py),
-                                              _p(level), _p(vc), _p(qd), float(th), self.mfNNratio, _p(km), C.byref(nm)),
+                                              _p(level), _p(vc), _p(qd), float(th), self.mfNNratio, _p(km), C.byref(nm),
+                                              None if qo is None else _p(qo)),
                 self._h, "orbm_search_local_map")
         return nm.value, km, occ
 
     # ---- M2 / M3: SearchByProjection(Frame& Cur, Frame& Last, th, bMono) / (Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) ----
-    def SearchByProjection_Frame(self, F, occupied, scale_factors, valid, u, v, octave, qangle, qdesc, th, ORBdist=100):
+    def SearchByProjection_Frame(self, F, occupied, scale_factors, valid, u, v, octave, qangle, qdesc, th, ORBdist=100,
+                                 q_occupies=None):
+        qo = None if q_occupies is None else _c(q_occupies, np.uint8)          # src/ORBmatcher.cc:1745-1747
         occ = _c(occupied, np.uint8).copy()
         sf = _c(scale_factors, np.float32)
         valid, u, v = _c(valid, np.uint8), _c(u, np.float32), _c(v, np.float32)
@@ -221,7 +227,7 @@ class ORBmatcher:
         nm = C.c_int(0)
         check_m(self._L.orbm_search_frame(self._h, F._f, _p(occ), _p(sf), len(sf), len(valid), _p(valid), _p(u), _p(v), _p(octave),
                                           _p(qa), _p(qd), float(th), int(ORBdist), int(self.mbCheckOrientation), _p(km),
-                                          C.byref(nm)), self._h, "orbm_search_frame")
+                                          C.byref(nm), None if qo is None else _p(qo)), self._h, "orbm_search_frame")
         return nm.value, km
 
     def track_batch_device(self, nframes, d_kps, d_desc, d_counts, frame_stride, bounds, scale_factors, th, d_kp_match,

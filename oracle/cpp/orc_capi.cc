@@ -166,15 +166,17 @@ int orc_rot_bin(float a1, float a2) { return rot_bin(a1, a2); }
 
 int orc_search_local_map(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* occupied,
                          const float* scaleFactors, int nq, const uint8_t* valid, const float* projX, const float* projY,
-                         const int* level, const float* viewCos, const uint8_t* qdesc, float th, float nnratio, int* kpMatch) {
+                         const int* level, const float* viewCos, const uint8_t* qdesc, float th, float nnratio, int* kpMatch,
+                         const uint8_t* qocc) {
     FrameView f = makeView(n, kps, desc, bounds);
-    return search_local_map(f, occupied, scaleFactors, nq, valid, projX, projY, level, viewCos, qdesc, th, nnratio, kpMatch);
+    return search_local_map(f, occupied, scaleFactors, nq, valid, projX, projY, level, viewCos, qdesc, th, nnratio, kpMatch, qocc);
 }
 int orc_search_frame(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* occupied,
                      const float* scaleFactors, int nq, const uint8_t* valid, const float* u, const float* v,
-                     const int* octave, const float* qangle, const uint8_t* qdesc, float th, int thDist, int checkOri, int* kpMatch) {
+                     const int* octave, const float* qangle, const uint8_t* qdesc, float th, int thDist, int checkOri, int* kpMatch,
+                     const uint8_t* qocc) {
     FrameView f = makeView(n, kps, desc, bounds);
-    return search_frame(f, occupied, scaleFactors, nq, valid, u, v, octave, qangle, qdesc, th, thDist, checkOri != 0, kpMatch);
+    return search_frame(f, occupied, scaleFactors, nq, valid, u, v, octave, qangle, qdesc, th, thDist, checkOri != 0, kpMatch, qocc);
 }
 int orc_search_sim3(int n, const void* kps, const uint8_t* desc, const float* bounds, uint8_t* matched,
                     const float* scaleFactors, int nq, const uint8_t* valid, const float* u, const float* v,

@@ -115,7 +115,7 @@ struct RotHist {
 // ---- M1: src/ORBmatcher.cc:43-213 (mono branch), RadiusByViewingCos :215-221 -------------------------------------
 int search_local_map(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
                      const float* projX, const float* projY, const int* level, const float* viewCos,
-                     const uint8_t* qdesc, float th, float nnratio, int* kpMatch) {
+                     const uint8_t* qdesc, float th, float nnratio, int* kpMatch, const uint8_t* qocc) {
     int nmatches = 0;
     const bool bFactor = th != 1.0;
     std::vector<int> vIndices;
@@ -141,7 +141,8 @@ int search_local_map(const FrameView& F, uint8_t* occupied, const float* scaleFa
             if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
             if (bestLevel != bestLevel2 || bestDist <= nnratio * bestDist2) {
                 kpMatch[bestIdx] = iMP;
-                occupied[bestIdx] = 1;
+                // F.mvpMapPoints[bestIdx] = pMP (:188): later queries skip the slot iff THAT point has Observations() > 0 (:92-94)
+                occupied[bestIdx] = qocc ? qocc[iMP] : 1;
                 nmatches++;
             }
         }
@@ -152,7 +153,7 @@ int search_local_map(const FrameView& F, uint8_t* occupied, const float* scaleFa
 // ---- M2 / M3: src/ORBmatcher.cc:1676-1887 (mono: neither bForward nor bBackward), :1889-2010 ---------------------
 int search_frame(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
                  const float* u, const float* v, const int* octave, const float* qangle, const uint8_t* qdesc,
-                 float th, int thDist, bool checkOri, int* kpMatch) {
+                 float th, int thDist, bool checkOri, int* kpMatch, const uint8_t* qocc) {
     int nmatches = 0;
     RotHist rot;
     std::vector<int> vIndices2;
@@ -171,7 +172,9 @@ int search_frame(const FrameView& F, uint8_t* occupied, const float* scaleFactor
         }
         if (bestDist <= thDist) {
             kpMatch[bestIdx2] = i;
-            occupied[bestIdx2] = 1;
+            // CurrentFrame.mvpMapPoints[bestIdx2] = pMP (:1770): it blocks later queries iff pMP->Observations() > 0 (:1745-1747);
+            // qocc == nullptr: any assigned point blocks (the KeyFrame variant, :1955)
+            occupied[bestIdx2] = qocc ? qocc[i] : 1;
             nmatches++;
             if (checkOri) rot.add(qangle[i], F.kps[bestIdx2].angle, bestIdx2);
         }

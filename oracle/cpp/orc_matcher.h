@@ -47,17 +47,18 @@ int rot_bin(float angle1, float angle2);
 
 // M1  SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) (src/ORBmatcher.cc:43-213), mono branch.
 //     valid[q] = mbTrackInView && !far && !isBad;  occupied[i] = mvpMapPoints[i] && Observations()>0 (in/out: a new
-//     assignment occupies the slot, see DESIGN.md "matcher assumptions").  kpMatch[i] = query assigned to keypoint i.
+//     assignment occupies the slot iff qocc[q] = the query's map point has Observations() > 0; qocc == nullptr: always).
+//     kpMatch[i] = LAST query assigned to keypoint i; the return value counts assignments, as the reference's nmatches++ does.
 int search_local_map(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
                      const float* projX, const float* projY, const int* level, const float* viewCos,
-                     const uint8_t* qdesc, float th, float nnratio, int* kpMatch);
+                     const uint8_t* qdesc, float th, float nnratio, int* kpMatch, const uint8_t* qocc = nullptr);
 
 // M2 / M3  SearchByProjection(Frame& Cur, const Frame& Last, th, bMono) (:1676-1887, mono) and
 //     SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:1889-2010): window th*scale[octave],
 //     levels [octave-1, octave+1], accept best <= thDist, claim, rotation histogram.
 int search_frame(const FrameView& F, uint8_t* occupied, const float* scaleFactors, int nq, const uint8_t* valid,
                  const float* u, const float* v, const int* octave, const float* qangle, const uint8_t* qdesc,
-                 float th, int thDist, bool checkOri, int* kpMatch);
+                 float th, int thDist, bool checkOri, int* kpMatch, const uint8_t* qocc = nullptr);
 
 // M7  SearchByProjection(KeyFrame*, Sim3, points, matched, th, ratioHamming) (:427-532 and :534-646)
 int search_sim3(const FrameView& KF, uint8_t* matched, const float* scaleFactors, int nq, const uint8_t* valid,

@@ -32,8 +32,8 @@ def _L():
                                            C.c_int, C.c_void_p]
         L.orc_rot_bin.argtypes = [C.c_float, C.c_float]
         vp, i, f = C.c_void_p, C.c_int, C.c_float
-        L.orc_search_local_map.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, f, f, vp]
-        L.orc_search_frame.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, f, i, i, vp]
+        L.orc_search_local_map.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, f, f, vp, vp]
+        L.orc_search_frame.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, vp, f, i, i, vp, vp]
         L.orc_search_sim3.argtypes = [i, vp, vp, vp, vp, vp, i, vp, vp, vp, vp, vp, i, f, vp]
         L.orc_search_initialization.argtypes = [i, vp, vp, i, vp, vp, vp, vp, i, f, i, vp]
         L.orc_search_bow_kf_frame.argtypes = [i, vp, vp, i, vp, vp, vp, vp, i, vp, vp, i, vp, vp, vp, f, i, vp]
@@ -81,8 +81,11 @@ def rot_bin(a1, a2):
     return int(_L().orc_rot_bin(float(a1), float(a2)))
 
 
-def search_local_map(kps, desc, bounds, occupied, scale_factors, valid, proj_x, proj_y, level, view_cos, qdesc, th, nnratio):
-    """M1.  Returns (nmatches, kpMatch[n], occupied_after[n])."""
+def search_local_map(kps, desc, bounds, occupied, scale_factors, valid, proj_x, proj_y, level, view_cos, qdesc, th, nnratio,
+                     q_occupies=None):
+    """M1.  Returns (nmatches, kpMatch[n], occupied_after[n]).  q_occupies[q] = the query's map point has Observations() > 0
+    (src/ORBmatcher.cc:92-94): only then does its match block the keypoint for later queries; None = always."""
+    qo = None if q_occupies is None else _c(q_occupies, np.uint8)
     kps, desc, b = _kp(kps), _c(desc, np.uint8), _bounds(bounds)
     occ = _c(occupied, np.uint8).copy()
     sf = _c(scale_factors, np.float32)
@@ -90,13 +93,14 @@ def search_local_map(kps, desc, bounds, occupied, scale_factors, valid, proj_x, 
     level, vc, qd = _c(level, np.int32), _c(view_cos, np.float32), _c(qdesc, np.uint8)
     km = np.full(len(kps), -1, np.int32)
     n = _L().orc_search_local_map(len(kps), _p(kps), _p(desc), _p(b), _p(occ), _p(sf), len(valid), _p(valid), _p(px), _p(py),
-                                  _p(level), _p(vc), _p(qd), float(th), float(nnratio), _p(km))
+                                  _p(level), _p(vc), _p(qd), float(th), float(nnratio), _p(km), None if qo is None else _p(qo))
     return n, km, occ
 
 
 def search_frame(kps, desc, bounds, occupied, scale_factors, valid, u, v, octave, qangle, qdesc, th, th_dist=TH_HIGH,
-                 check_ori=True):
-    """M2 / M3.  Returns (nmatches, kpMatch[n])."""
+                 check_ori=True, q_occupies=None):
+    """M2 / M3.  Returns (nmatches, kpMatch[n]).  q_occupies: as in search_local_map (src/ORBmatcher.cc:1745-1747)."""
+    qo = None if q_occupies is None else _c(q_occupies, np.uint8)
     kps, desc, b = _kp(kps), _c(desc, np.uint8), _bounds(bounds)
     occ = _c(occupied, np.uint8).copy()
     sf = _c(scale_factors, np.float32)
@@ -104,7 +108,8 @@ def search_frame(kps, desc, bounds, occupied, scale_factors, valid, u, v, octave
     octave, qa, qd = _c(octave, np.int32), _c(qangle, np.float32), _c(qdesc, np.uint8)
     km = np.full(len(kps), -1, np.int32)
     n = _L().orc_search_frame(len(kps), _p(kps), _p(desc), _p(b), _p(occ), _p(sf), len(valid), _p(valid), _p(u), _p(v),
-                              _p(octave), _p(qa), _p(qd), float(th), int(th_dist), int(check_ori), _p(km))
+                              _p(octave), _p(qa), _p(qd), float(th), int(th_dist), int(check_ori), _p(km),
+                              None if qo is None else _p(qo))
     return n, km
 
 

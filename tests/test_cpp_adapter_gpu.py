@@ -144,7 +144,8 @@ def test_matcher_adapter_every_member(tmp_path):
     # M1 Tracking::SearchLocalPoints
     valid = (S["mp_inview"][local] != 0) & ~(S["mp_depth"][local] > f32(40)) & ~bad[local]
     nm, km, _ = om.search_local_map(k2, d2, bounds, occ_obs, scale, valid.astype(np.uint8), S["mp_projx"][local], S["mp_projy"][local],
-                                    S["mp_tracklevel"][local], S["mp_viewcos"][local], mdesc[local], 3.0, 0.8)
+                                    S["mp_tracklevel"][local], S["mp_viewcos"][local], mdesc[local], 3.0, 0.8,
+                                    q_occupies=nobs[local] > 0)          # a zero-observation point does not block its keypoint (:92-94)
     ret, got = R["local_map"]
     assert ret == nm and nm > 30 and np.array_equal(got, np.where(km >= 0, local[np.maximum(km, 0)], kf2))
 
@@ -153,7 +154,7 @@ def test_matcher_adapter_every_member(tmp_path):
     u, v, pc = _proj(pos[q], t2)
     valid = (kf1 >= 0) & (S["outlier1"] == 0) & ~(f32(1) / pc[:, 2] < 0) & in_bounds(u, v)
     nm, km = om.search_frame(k2, d2, bounds, occ_obs, scale, valid.astype(np.uint8), u, v, k1["octave"], k1["angle"], mdesc[q], 15.0,
-                             100, True)
+                             100, True, q_occupies=nobs[q] > 0)          # :1745-1747
     ret, got = R["frame"]
     assert ret == nm and nm > 50 and np.array_equal(got, np.where(km >= 0, kf1[np.maximum(km, 0)], kf2))
 

@@ -391,6 +391,15 @@ def test_contention_many_queries_few_keypoints(M):
             onm, okm = om.search_frame(k2, d2, bounds, occ, scale, valid, u, v, octave, angle, qd, th, 100, ori)
             assert nm == onm and np.array_equal(km, okm), (th, ori)
             assert onm > 100
+            # the same with map points of which only some have Observations() > 0 (src/ORBmatcher.cc:1745-1747): a match by a
+            # zero-observation point does not block its keypoint, later queries overwrite it, nmatches counts every assignment,
+            # and the rotation histogram clears the keypoint of every dropped entry even when a later assignment survived
+            qocc = (rng.random(nq) < 0.6).astype(np.uint8)
+            nm, km = M.SearchByProjection_Frame(F, occ, scale, valid, u, v, octave, angle, qd, th, 100, q_occupies=qocc)
+            onm, okm = om.search_frame(k2, d2, bounds, occ, scale, valid, u, v, octave, angle, qd, th, 100, ori, q_occupies=qocc)
+            assert nm == onm and np.array_equal(km, okm), (th, ori, "q_occupies")
+            if not ori:
+                assert onm > (okm >= 0).sum()            # overwrites did happen: more assignments than matched keypoints
     M.mbCheckOrientation = True
     # best / second-best rule under the same contention (M1)
     vc = np.ones(nq, np.float32)
@@ -400,6 +409,11 @@ def test_contention_many_queries_few_keypoints(M):
         nm, km, occ_after = M.SearchByProjection_LocalMap(F, occ, scale, valid, u, v, octave, vc, qd, 8.0)
         onm, okm, oocc = om.search_local_map(k2, d2, bounds, occ, scale, valid, u, v, octave, vc, qd, 8.0, ratio)
         assert nm == onm and np.array_equal(km, okm) and np.array_equal(occ_after, oocc), ratio
+        qocc = (rng.random(nq) < 0.5).astype(np.uint8)                          # src/ORBmatcher.cc:92-94
+        nm, km, occ_after = M.SearchByProjection_LocalMap(F, occ, scale, valid, u, v, octave, vc, qd, 8.0, q_occupies=qocc)
+        onm, okm, oocc = om.search_local_map(k2, d2, bounds, occ, scale, valid, u, v, octave, vc, qd, 8.0, ratio, q_occupies=qocc)
+        assert nm == onm and np.array_equal(km, okm) and np.array_equal(occ_after, oocc), (ratio, "q_occupies")
+        assert onm > (okm >= 0).sum()
     M.mfNNratio = 0.9
     F.close()
     # M5 with chains of steals: frame 1 = the queries as keypoints at level 0
