@@ -3,8 +3,10 @@
 // (std::list for the quadtree, std::sort for the "largest node first" phase) so libstdc++'s list order and
 // introsort tie behaviour are inherited rather than modelled.
 //
-// Parity: UNPINNED by the reference (it ships no tests or golden vectors for this path);
-// pinned instead stage by stage against cv2 4.13.0 (tests/test_oracle_vs_cv2.py, tests/golden/).
+// Parity: PINNED to the reference's own source.  oracle/_ref/liborb_ref.so is /root/reference/src/ORBextractor.cc compiled
+// unmodified against the header shim oracle/ref_shim/ (recipe: oracle/Makefile `ref`), and tests/test_oracle_vs_ref.py asserts
+// that this restatement equals it bit for bit (keypoints, order, responses, angles, descriptors, monoIndex, pyramid levels,
+// per-level kept lists).  The pixel primitives both share are pinned to cv2 4.13.0 (tests/test_oracle_vs_cv2.py, tests/golden/).
 #pragma once
 #include "orc_primitives.h"
 #include <list>
