@@ -67,6 +67,8 @@ struct Extractor {
     bool fastCompass = false;        // ORBX_FAST_COMPASS=1: warp-uniform compass early-out in the strength pass
     FsPlan fsPlan{};
     FsMaps fsMaps{}, scoreMaps{};    // tensor maps of the pyramid levels (level 0 per pass) and of the score planes
+    FsMaps blurMaps{};               // the pyramid levels again, with the blur's 144 x 36 box
+    bool blurTma = true;             // ORBX_BLUR_TMA=0: the register-only k_blur7 (A/B switch; also the fallback when level 0 is not TMA-addressable)
     NmsTabs nmsTabs{};               // same-cell column / row masks of the non-max suppression
     uint2* dCbits = nullptr;         // survivor bits (k_fast_nms -> k_fast_select)
     int poolCap = 0, scanCap = 0;
@@ -121,13 +123,14 @@ EncodeTiledFn tensorMapEncoder() {
 
 // 3-D u8 tensor {x, y, frame} of one pyramid level for k_fast_score's tile loads.  false: TMA cannot address it (base, row
 // pitch or frame stride not a multiple of 16 bytes) and the kernel stages that level with plain loads.
-bool encodeLevelMap(CUtensorMap* m, const uint8_t* base, int w, int h, int frames, size_t pitch, size_t frameBytes, int boxH = kFsBoxH) {
+bool encodeLevelMap(CUtensorMap* m, const uint8_t* base, int w, int h, int frames, size_t pitch, size_t frameBytes, int boxH = kFsBoxH,
+                    int boxW = kFsBoxW) {
     EncodeTiledFn enc = tensorMapEncoder();
     static const bool off = getenv("ORBX_FAST_TMA") && atoi(getenv("ORBX_FAST_TMA")) == 0;      // A/B switch: plain-load staging
     if (off || !enc || (((uintptr_t)base | pitch | frameBytes) & 15) != 0 || frames < 1) return false;
     const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)frames};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frameBytes};
-    const cuuint32_t box[3] = {(cuuint32_t)kFsBoxW, (cuuint32_t)boxH, 1};
+    const cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1};
     const cuuint32_t es[3] = {1, 1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -304,6 +307,14 @@ int configureShape(Extractor* E, int W, int H) {
         CK(cudaMemcpy(E->dCellOrder, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
     }
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
+    // A quadtree CTA is 512 threads x 64 registers: two of them hold an SM's whole register file for ~100 us while issuing at
+    // ~40 %, and no CTA of another handle's kernels can co-reside.  ORBX_TREE_CTAS=k caps the resident quadtree CTAs per SM at k
+    // by padding the dynamic shared memory request (the occupancy limiter that needs no recompilation).
+    if (const char* tc = getenv("ORBX_TREE_CTAS")) {
+        const int k = atoi(tc);
+        if (k >= 1 && k <= 4) E->treeSmem = std::max<size_t>(E->treeSmem, (size_t)(227 * 1024 / (k + 1)) + 1024);
+        if (E->treeSmem > 220 * 1024) E->treeSmem = 220 * 1024;
+    }
     CK(raise_dyn_smem((const void*)k_octree, E->device, E->treeSmem));
     CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
     // fewer threads per cell when the cells are small: the per-thread fixed cost (prologue, scans, barriers) is spread over
@@ -354,9 +365,11 @@ int configureShape(Extractor* E, int W, int H) {
     if ((rc = devAlloc(E, &E->dCbits, (size_t)E->fsPlan.bitsPerFrame * B))) return rc;
     memset(&E->fsMaps, 0, sizeof(E->fsMaps));
     memset(&E->scoreMaps, 0, sizeof(E->scoreMaps));
+    memset(&E->blurMaps, 0, sizeof(E->blurMaps));
     for (int l = 0; l < L; ++l) {
         if (l > 0) E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
         E->scoreMaps.tmaOk[l] = encodeLevelMap(&E->scoreMaps.m[l], g.score[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kNmsBoxH) ? 1 : 0;
+        if (l > 0) E->blurMaps.tmaOk[l] = encodeLevelMap(&E->blurMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kBtBoxH, kBtBoxW) ? 1 : 0;
     }
     {
         // same-cell masks of the 3x3 suppression.  The cells of a level form a regular grid (src/ORBextractor.cc:805-821: the
@@ -419,6 +432,17 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     mark();
     const int slot = st == E->stream2 ? 1 : 0;
     const bool side = E->overlap && !E->timing && E->aux[slot];
+    // the blur of all levels: TMA-staged tiles when every level (incl. the caller's level 0) is TMA-addressable
+    const size_t l0stride = (fb + n == 1) ? (((size_t)l0.pitch * g.lv[0].h + 15) & ~(size_t)15) : l0.frameBytes;
+    auto launchBlur = [&](cudaStream_t bs) {
+        const dim3 bgrid((E->blurTilesTotal + 7) / 8, n);
+        bool tma = E->blurTma;
+        FsMaps bm = E->blurMaps;
+        if (tma) bm.tmaOk[0] = encodeLevelMap(&bm.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride, kBtBoxH, kBtBoxW) ? 1 : 0;
+        for (int l = 0; l < L && tma; ++l) tma = bm.tmaOk[l] != 0;
+        if (tma) k_blur7_tma<<<bgrid, 256, 0, bs>>>(bm, E->dGeom, E->blurTiles, fb);
+        else k_blur7<<<bgrid, 256, 0, bs>>>(E->dGeom, l0, E->blurTiles, fb);
+    };
     // FAST on level 0 reads only the input image: its cells go first, on the side stream, beside the (latency-bound) chain
     // of pyramid launches
     const int nA0 = side && E->fastEarly && E->fastGen < 2 ? E->fastNA0 : 0;
@@ -463,14 +487,13 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     if (early) {
         CK(cudaEventRecord(E->evFork[slot], st));
         CK(cudaStreamWaitEvent(E->aux[slot], E->evFork[slot], 0));
-        k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
+        launchBlur(E->aux[slot]);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
     if (E->fastGen >= 2) {
         // level 0 is the caller's image: its tensor map depends on this pass's pointer / pitch / frame stride
         FsMaps maps = E->fsMaps;
-        const size_t fstride = (fb + n == 1) ? (((size_t)l0.pitch * g.lv[0].h + 15) & ~(size_t)15) : l0.frameBytes;
-        maps.tmaOk[0] = encodeLevelMap(&maps.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, fstride) ? 1 : 0;
+        maps.tmaOk[0] = encodeLevelMap(&maps.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride) ? 1 : 0;
         const dim3 sgrid((E->fsPlan.nJobs + kFsWarps - 1) / kFsWarps, n);
         if (E->fastCompass) k_fast_score<true><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, fb);
         else k_fast_score<false><<<sgrid, kFsWarps * 32, 0, st>>>(maps, E->dGeom, l0, E->fsPlan, fb);
@@ -489,14 +512,14 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     if (side && !early) {
         CK(cudaEventRecord(E->evFork[slot], st));
         CK(cudaStreamWaitEvent(E->aux[slot], E->evFork[slot], 0));
-        k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, E->aux[slot]>>>(E->dGeom, l0, E->blurTiles, fb);
+        launchBlur(E->aux[slot]);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
     CK(launch_prio(k_octree, dim3(n, L), dim3(kTreeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
                    E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb));
     ++E->launches;
     mark();
-    if (!side) k_blur7<<<dim3((E->blurTilesTotal + 7) / 8, n), 256, 0, st>>>(E->dGeom, l0, E->blurTiles, fb);
+    if (!side) launchBlur(st);
     ++E->launches;
     mark();
     CK(launch_prio(k_finalize, dim3(n), dim3(kFinalThreads), 0, st, E->prio, E->dGeom, E->dLvlKp, E->dLvlCnt, lap0, lap1, E->dOutKp,
@@ -635,6 +658,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     if (const char* fe = getenv("ORBX_FAST_EARLY")) E->fastEarly = atoi(fe) != 0;
     if (const char* fg = getenv("ORBX_FAST_GEN")) E->fastGen = atoi(fg) == 1 ? 1 : 2;
     if (const char* fc = getenv("ORBX_FAST_COMPASS")) E->fastCompass = atoi(fc) != 0;
+    if (const char* bt = getenv("ORBX_BLUR_TMA")) E->blurTma = atoi(bt) != 0;
     {
         int least = 0, greatest = 0;
         cudaDeviceGetStreamPriorityRange(&least, &greatest);

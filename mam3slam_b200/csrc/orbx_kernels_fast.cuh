@@ -298,13 +298,11 @@ __global__ void __launch_bounds__(kFsWarps * 32) k_fast_nms(const __grid_constan
 // iniThFAST / minThFAST rule and writes the survivors in raster order.  grid (ceil(nCells / 4), B), block 128.
 constexpr int kSelWarps = 4;
 constexpr int kSelMaxWords = 256;                // raster bitmap of a cell: <= 8192 pixel slots (checked on the host)
-constexpr int kSelList = 32 * 2 * kFsRows;       // survivors one round of 32 bit words can hold
 
 __global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
                                                                 const FsPlan plan, const uint2* __restrict__ cbits,
                                                                 uint32_t* __restrict__ cand, int* __restrict__ cellCount, int frameBase) {
     __shared__ uint32_t sKeep[kSelWarps][2][kSelMaxWords];       // survivors of the 3x3 NMS at minThFAST / iniThFAST, raster order
-    __shared__ uint16_t sList[kSelWarps][kSelList];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cellId = blockIdx.x * kSelWarps + warp;
     if (cellId >= g->nCells) return;
@@ -327,48 +325,33 @@ __global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* _
     for (int i = lane; i < nwr; i += 32) { keepMin[i] = 0; keepIni[i] = 0; }
     __syncwarp();
     const int iniTh = g->iniTh;
-    uint16_t* list = sList[warp];
 
-    for (int base = 0; base < nW; base += 32) {
-        const int i = base + lane;
-        uint32_t word = 0;
-        int xs = 0, ys = 0;
-        if (i < nW) {
-            const int k = i & 1, t = i >> 1;
-            const int s = t / nGc, q = t - s * nGc;
-            word = bits[((size_t)(sLo + s) * nG + gLo + q) * 2 + k];
-            xs = kFsX0 + 4 * (gLo + q) + k - c.x0;               // local x of the low half's pixel; the high half's is xs + 2
-            ys = kFsY0 + kFsRows * (sLo + s) - c.y0;             // local y of bit 0
-            const int rlo = max(-ys, 0), rhi = min(h - 1 - ys, kFsRows - 1);
-            const uint32_t rowmask = ((2u << rhi) - 1u) & ~((1u << rlo) - 1u);
-            uint32_t m = 0;
-            if (xs >= 0 && xs < w) m |= rowmask;
-            if (xs + 2 >= 0 && xs + 2 < w) m |= rowmask << 16;
-            word &= m;
-        }
-        const int cnt = __popc(word);
-        int incl = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        int pos = incl - cnt;
+    // survivors are sparse (~1 per 28-pixel word): every lane walks the set bits of its own words and files each survivor in
+    // the cell's raster-order bitmaps, at both thresholds (no staging list, no prefix sum: the order comes from the bitmaps)
+    for (int i = lane; i < nW; i += 32) {
+        const int k = i & 1, t = i >> 1;
+        const int s = t / nGc, q = t - s * nGc;
+        uint32_t word = bits[((size_t)(sLo + s) * nG + gLo + q) * 2 + k];
+        if (!word) continue;
+        const int xs = kFsX0 + 4 * (gLo + q) + k - c.x0;         // local x of the low half's pixel; the high half's is xs + 2
+        const int ys = kFsY0 + kFsRows * (sLo + s) - c.y0;       // local y of bit 0
+        const int rlo = max(-ys, 0), rhi = min(h - 1 - ys, kFsRows - 1);
+        const uint32_t rowmask = ((2u << rhi) - 1u) & ~((1u << rlo) - 1u);
+        uint32_t m = 0;
+        if (xs >= 0 && xs < w) m |= rowmask;
+        if (xs + 2 >= 0 && xs + 2 < w) m |= rowmask << 16;
+        word &= m;
         while (word) {
             const int b = __ffs(word) - 1;
             word &= word - 1;
-            list[pos++] = (uint16_t)((xs + 2 * (b >> 4)) | ((ys + (b & 15)) << 8));
-        }
-        __syncwarp();
-        // the listed pixels survived the 3x3 suppression (k_fast_nms); file them in raster order, at both thresholds
-        for (int q = lane; q < total; q += 32) {
-            const int e = list[q];
-            const int lx = e & 255, ly = e >> 8;
-            const int s = S[(size_t)ly * pitch + lx];
+            const int lx = xs + 2 * (b >> 4), ly = ys + (b & 15);
+            const int sc = S[(size_t)ly * pitch + lx];
             const int p = ly * w + lx;
             atomicOr(&keepMin[p >> 5], 1u << (p & 31));
-            if (s > iniTh) atomicOr(&keepIni[p >> 5], 1u << (p & 31));
+            if (sc > iniTh) atomicOr(&keepIni[p >> 5], 1u << (p & 31));
         }
-        __syncwarp();
     }
+    __syncwarp();
 
     // cells keep the iniThFAST survivors, or the minThFAST ones when there are none (:826-846); raster order
     const int per = (nwr + 31) >> 5;
@@ -397,6 +380,131 @@ __global__ void __launch_bounds__(kSelWarps * 32) k_fast_select(const DevGeom* _
         }
     }
     if (lane == 0) cellCount[(size_t)frame * g->nCells + cellId] = total;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// E6, TMA-staged variant of k_blur7 (same arithmetic: separable fixed-point [18,34,48,56,48,34,18]/256, (sum + 2^15) >> 16,
+// BORDER_REFLECT_101; src/ORBextractor.cc:1131-1133).  k_blur7 waits on DRAM once per strip row (issue-active 51 % for 75 M
+// warp-instructions).  Here a warp's 120 x 30 strip arrives as ONE 144 x 36-byte tile by a 3-D TMA load (zero fill outside the
+// level) into shared memory; the register pipeline of k_blur7 (horizontal taps through neighbour shuffles, vertical taps on
+// packed row pairs) then reads its rows with conflict-free LDS.  TMA wants the box start 16-byte aligned in x: the tile starts
+// at gx = floor16(x0 - 4), and the strip's words sit r = (x0 - 4 - gx) / 4 words into each tile row.
+// REFLECT_101 at the level's edges is patched in shared memory after the load: mirrored columns first (rows inside the level),
+// then whole mirrored rows, so that corners are mirrored in both directions.
+constexpr int kBtBoxW = 144, kBtBoxH = kBlurStripH + 6;       // 36 rows
+constexpr int kBtRowW = kBtBoxW / 4;                          // 36 words per tile row
+constexpr int kBtTileBytes = kBtBoxW * kBtBoxH;               // 5184
+constexpr int kBtTileStride = 5248;                           // 128-byte multiple
+
+__global__ void __launch_bounds__(256) k_blur7_tma(const __grid_constant__ FsMaps maps, const DevGeom* __restrict__ g, BlurTiles bt,
+                                                   int frameBase) {
+    __shared__ __align__(128) uint8_t tiles[8][kBtTileStride];
+    __shared__ __align__(8) uint64_t mbar[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int job = blockIdx.x * 8 + warp;
+    const int nl = g->nlevels;
+    if (job >= bt.start[nl]) return;                           // warps are independent: no block barrier below
+    const int frame = frameBase + blockIdx.y;
+    int l = 0;
+    while (l + 1 < nl && job >= bt.start[l + 1]) ++l;
+    const int t = job - bt.start[l];
+    const int ty = t / bt.tilesX[l], tx = t - ty * bt.tilesX[l];
+    const LevelGeom& L = g->lv[l];
+    const int w = L.w, h = L.h;
+    const int x0 = tx * kBlurStripW, y0 = ty * kBlurStripH;
+    const int gx = (x0 - 4) & ~15, gy = y0 - 3;                // tile origin in level coordinates (may be negative: zero fill)
+    uint8_t* tile = tiles[warp];
+    {
+        const uint32_t bar = smem_addr(&mbar[warp]);
+        if (lane == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kBtTileBytes) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                         :: "r"(smem_addr(tile)), "l"(reinterpret_cast<uint64_t>(&maps.m[l])), "r"(bar), "r"(gx), "r"(gy), "r"(frame)
+                         : "memory");
+        }
+        __syncwarp();
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar), "r"(0) : "memory");
+    }
+    // BORDER_REFLECT_101 patches (every level is >= 35 px wide and high, so a mirror source is always inside the tile)
+    const bool edgeL = x0 == 0, edgeR = x0 + kBlurStripW + 3 > w, edgeT = y0 == 0, edgeB = y0 + kBlurStripH + 3 > h;
+    if (edgeL | edgeR | edgeT | edgeB) {
+        if (edgeL | edgeR) {
+            for (int ry = lane; ry < kBtBoxH; ry += 32) {
+                const int y = gy + ry;
+                if (y < 0 || y >= h) continue;
+                uint8_t* row = tile + ry * kBtBoxW;
+                if (edgeL) { row[-1 - gx] = row[1 - gx]; row[-2 - gx] = row[2 - gx]; row[-3 - gx] = row[3 - gx]; }
+                if (edgeR) {
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) if (w + j - gx < kBtBoxW) row[w + j - gx] = row[w - 2 - j - gx];
+                }
+            }
+            __syncwarp();
+        }
+        if (edgeT | edgeB) {
+            uint32_t* tw = reinterpret_cast<uint32_t*>(tile);
+            for (int i = lane; i < 3 * kBtRowW; i += 32) {
+                const int j = i / kBtRowW, c = i - j * kBtRowW;
+                if (edgeT) tw[(-1 - j - gy) * kBtRowW + c] = tw[(1 + j - gy) * kBtRowW + c];          // row -(j+1) <- row j+1
+                if (edgeB && h + j - gy < kBtBoxH) tw[(h + j - gy) * kBtRowW + c] = tw[(h - 2 - j - gy) * kBtRowW + c];
+            }
+            __syncwarp();
+        }
+    }
+
+    const int x = x0 + 4 * (lane - 1);                         // first column of this lane's word
+    const uint32_t* tcol = reinterpret_cast<const uint32_t*>(tile) + ((x0 - 4 - gx) >> 2) + lane;
+    uint8_t* dst = g->blur[l] + (size_t)frame * L.planeBytes;
+    const int dp = L.pitch;
+    const bool writer = lane >= 1 && lane <= 30 && x < w;
+    const bool fullWord = x + 3 < w;
+
+    uint32_t ring[6][4];            // ring[r % 6][j] = (h[r-1], h[r]) of pixel j as u16 pair
+    uint32_t hprev[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ring[i][j] = 0;
+
+    const int rowsNeeded = min(kBlurStripH, h - y0) + 6;
+    for (int r0 = 0; r0 < rowsNeeded; r0 += 6) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            const int r = r0 + k;                               // tile row r = level row y0 + r - 3
+            const int yo = y0 + r - 6;                          // output row completed by this input row
+            const uint32_t C = tcol[min(r, kBtBoxH - 1) * kBtRowW];
+            const uint32_t Lw = __shfl_up_sync(0xffffffffu, C, 1);
+            const uint32_t Rw = __shfl_down_sync(0xffffffffu, C, 1);
+            uint32_t hc[4];
+            hc[0] = __dp4a(__byte_perm(Lw, C, 0x4321), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x4321), 0x00122230u, 0u));
+            hc[1] = __dp4a(__byte_perm(Lw, C, 0x5432), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x5432), 0x00122230u, 0u));
+            hc[2] = __dp4a(__byte_perm(Lw, C, 0x6543), 0x38302212u, __dp4a(__byte_perm(C, Rw, 0x6543), 0x00122230u, 0u));
+            hc[3] = __dp4a(C, 0x38302212u, __dp4a(Rw, 0x00122230u, 0u));
+            uint32_t v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t pr = __byte_perm(hprev[j], hc[j], 0x5410);      // (h[r-1], h[r])
+                uint32_t acc = hc[j] * 18u + 32768u;
+                acc = __dp2a_lo(ring[(k + 1) % 6][j], 0x2212u, acc);           // pair r-5 = (h[r-6], h[r-5]) . (18, 34)
+                acc = __dp2a_lo(ring[(k + 3) % 6][j], 0x3830u, acc);           // pair r-3 = (h[r-4], h[r-3]) . (48, 56)
+                acc = __dp2a_lo(ring[(k + 5) % 6][j], 0x2230u, acc);           // pair r-1 = (h[r-2], h[r-1]) . (48, 34)
+                v[j] = acc;
+                ring[k][j] = pr;
+                hprev[j] = hc[j];
+            }
+            if (r >= 6 && yo < h && writer) {
+                const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+                uint8_t* d = dst + (size_t)yo * dp + x;
+                if (fullWord) *reinterpret_cast<uint32_t*>(d) = o;
+                else for (int j = 0; j < 4 && x + j < w; ++j) d[j] = (uint8_t)(o >> (8 * j));
+            }
+        }
+    }
 }
 
 }  // namespace orbx

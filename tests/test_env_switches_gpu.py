@@ -44,5 +44,7 @@ def test_schedule_switches_do_not_change_results():
                 {"ORBX_GRAPHS": "0"}, {"ORBX_OVERLAP": "0"}, {"ORBX_FAST_EARLY": "1", "ORBX_BLUR_EARLY": "0", "ORBX_GRAPHS": "0"},
                 # FAST: first-generation per-cell kernel, compass early-out of the strength pass, plain-load tile staging (no TMA)
                 {"ORBX_FAST_GEN": "1"}, {"ORBX_FAST_GEN": "1", "ORBX_FAST_GROUPS": "0"}, {"ORBX_FAST_COMPASS": "1"},
-                {"ORBX_FAST_TMA": "0"}, {"ORBX_FAST_TMA": "0", "ORBX_FAST_COMPASS": "1", "ORBX_GRAPHS": "0"}):
+                {"ORBX_FAST_TMA": "0"}, {"ORBX_FAST_TMA": "0", "ORBX_FAST_COMPASS": "1", "ORBX_GRAPHS": "0"},
+                # blur: register-only kernel instead of the TMA-staged one; quadtree CTAs capped per SM
+                {"ORBX_BLUR_TMA": "0"}, {"ORBX_BLUR_TMA": "0", "ORBX_OVERLAP": "0"}, {"ORBX_TREE_CTAS": "1"}):
         assert _digest(env) == base, env
