@@ -68,6 +68,9 @@ struct Extractor {
     FsPlan fsPlan{};
     FsMaps fsMaps{}, scoreMaps{};    // tensor maps of the pyramid levels (level 0 per pass) and of the score planes
     FsMaps blurMaps{};               // the pyramid levels again, with the blur's 144 x 36 box
+    FsMaps descMaps{};               // the BLURRED planes with the descriptor's 64 x 37 box
+    FsMaps oriMaps{};                // the pyramid levels with the orientation disc's 48 x 31 box (level 0 per pass)
+    bool descTma = true;             // ORBX_DESC_TMA=0: k_orient_brief with global gathers (A/B switch)
     bool blurTma = true;             // ORBX_BLUR_TMA=0: the register-only k_blur7 (A/B switch; also the fallback when level 0 is not TMA-addressable)
     NmsTabs nmsTabs{};               // same-cell column / row masks of the non-max suppression
     uint2* dCbits = nullptr;         // survivor bits (k_fast_nms -> k_fast_select)
@@ -317,6 +320,7 @@ int configureShape(Extractor* E, int W, int H) {
     }
     CK(raise_dyn_smem((const void*)k_octree, E->device, E->treeSmem));
     CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
+    CK(raise_dyn_smem((const void*)k_orient_brief_tma, E->device, kDtSmemBytes));
     // fewer threads per cell when the cells are small: the per-thread fixed cost (prologue, scans, barriers) is spread over
     // more pixels; every thread owns a raster chunk of at most 32 pixels
     const char* ft = getenv("ORBX_FAST_THREADS");
@@ -366,9 +370,13 @@ int configureShape(Extractor* E, int W, int H) {
     memset(&E->fsMaps, 0, sizeof(E->fsMaps));
     memset(&E->scoreMaps, 0, sizeof(E->scoreMaps));
     memset(&E->blurMaps, 0, sizeof(E->blurMaps));
+    memset(&E->descMaps, 0, sizeof(E->descMaps));
+    memset(&E->oriMaps, 0, sizeof(E->oriMaps));
     for (int l = 0; l < L; ++l) {
         if (l > 0) E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
         E->scoreMaps.tmaOk[l] = encodeLevelMap(&E->scoreMaps.m[l], g.score[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kNmsBoxH) ? 1 : 0;
+        E->descMaps.tmaOk[l] = encodeLevelMap(&E->descMaps.m[l], g.blur[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kDtBoxH, kDtBoxW) ? 1 : 0;
+        if (l > 0) E->oriMaps.tmaOk[l] = encodeLevelMap(&E->oriMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kOtBoxH, kOtBoxW) ? 1 : 0;
         if (l > 0) E->blurMaps.tmaOk[l] = encodeLevelMap(&E->blurMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kBtBoxH, kBtBoxW) ? 1 : 0;
     }
     {
@@ -527,8 +535,16 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     ++E->launches;
     mark();
     if (side) CK(cudaStreamWaitEvent(st, E->evJoin[slot], 0));
-    k_orient_brief<<<dim3((g.outCap + kDescWarps * kDescGroup - 1) / (kDescWarps * kDescGroup), n), kDescWarps * 32, 0, st>>>(
-        E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
+    bool dtma = E->descTma;
+    FsMaps om = E->oriMaps;
+    if (dtma) om.tmaOk[0] = encodeLevelMap(&om.m[0], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride, kOtBoxH, kOtBoxW) ? 1 : 0;
+    for (int l = 0; l < L && dtma; ++l) dtma = E->descMaps.tmaOk[l] != 0 && om.tmaOk[l] != 0;
+    if (dtma)
+        k_orient_brief_tma<<<dim3((g.outCap + kDtWarps * kDescGroup - 1) / (kDtWarps * kDescGroup), n), kDtWarps * 32, kDtSmemBytes, st>>>(
+            E->descMaps, om, E->dGeom, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
+    else
+        k_orient_brief<<<dim3((g.outCap + kDescWarps * kDescGroup - 1) / (kDescWarps * kDescGroup), n), kDescWarps * 32, 0, st>>>(
+            E->dGeom, l0, E->dWork, E->dOutCnt, E->dOutKp, E->dOutDesc, fb);
     ++E->launches;
     mark();
     CK(cudaGetLastError());
@@ -659,6 +675,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     if (const char* fg = getenv("ORBX_FAST_GEN")) E->fastGen = atoi(fg) == 1 ? 1 : 2;
     if (const char* fc = getenv("ORBX_FAST_COMPASS")) E->fastCompass = atoi(fc) != 0;
     if (const char* bt = getenv("ORBX_BLUR_TMA")) E->blurTma = atoi(bt) != 0;
+    if (const char* dt = getenv("ORBX_DESC_TMA")) E->descTma = atoi(dt) != 0;
     {
         int least = 0, greatest = 0;
         cudaDeviceGetStreamPriorityRange(&least, &greatest);

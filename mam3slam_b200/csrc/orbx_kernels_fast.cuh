@@ -27,7 +27,7 @@
 // Layout of the corner bits: cbits[frame][level][strip s][column group q] (uint2), column group q = pixels 16+4q .. +3,
 // strip s = rows 19+14s .. +13; .x bit r = pixel 0 row r, bit 16+r = pixel 2; .y bit r = pixel 1, bit 16+r = pixel 3.
 #pragma once
-#include "orbx_kernels_image.cuh"
+#include "orbx_kernels_desc.cuh"
 #include <cuda.h>          // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
 
 namespace orbx {
@@ -504,6 +504,128 @@ __global__ void __launch_bounds__(256) k_blur7_tma(const __grid_constant__ FsMap
                 else for (int j = 0; j < 4 && x + j < w; ++j) d[j] = (uint8_t)(o >> (8 * j));
             }
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// E5 + E7, TMA-staged variant of k_orient_brief (same arithmetic, same outputs; src/ORBextractor.cc:76-146).  In k_orient_brief
+// each of a keypoint's 16 warp-wide byte gathers on the blurred plane touches ~23 L1 sectors (149 MB of DRAM traffic per batch
+// for 84 MB algorithmic).  Here lane 0 requests, before anything else, the blurred 37-row window of each keypoint of the warp's
+// group as a 64 x 37-byte 3-D TMA tile (box start floor16(x - 18)): the loads land while the orientation moments are computed
+// on the unblurred level, and the 16 gathers become shared-memory byte loads.  Rotated pattern coordinates are at most
+// round(13 * sqrt(2)) = 18 in either direction, and keypoints lie >= 19 px inside their level, so the window never leaves it.
+// The orientation window gets the same treatment (ncu: its 31 row loads with run-time pitch arithmetic were 44 % of the stall
+// samples and ~450 of the kernel's 884 warp-instructions per keypoint): a 48 x 31-byte tile of the UNBLURRED level (box start
+// floor16(x - 15)), read with one LDS per row at an immediate offset.
+constexpr int kDtWarps = 4;
+constexpr int kDtBoxW = 64, kDtBoxH = 37, kDtTileBytes = kDtBoxW * kDtBoxH, kDtTileStride = 2432;
+constexpr int kOtBoxW = 48, kOtBoxH = 31, kOtTileBytes = kOtBoxW * kOtBoxH, kOtTileStride = 1536;
+constexpr int kDtSmemBytes = kDtWarps * kDescGroup * (kDtTileStride + kOtTileStride);      // 63,488 B: 3 CTAs per SM
+
+__global__ void __launch_bounds__(kDtWarps * 32) k_orient_brief_tma(const __grid_constant__ FsMaps bmaps, const __grid_constant__ FsMaps omaps,
+                                                                     const DevGeom* __restrict__ g, const WorkItem* __restrict__ work,
+                                                                     const int* __restrict__ outCnt, orbx_keypoint* outKp,
+                                                                     uint8_t* outDesc, int frameBase) {
+    extern __shared__ __align__(128) uint8_t dsm[];
+    typedef uint8_t (*BlurTilesT)[kDescGroup][kDtTileStride];
+    typedef uint8_t (*OriTilesT)[kDescGroup][kOtTileStride];
+    BlurTilesT tiles = reinterpret_cast<BlurTilesT>(dsm);                                            // [warp][keypoint][2432]
+    OriTilesT otiles = reinterpret_cast<OriTilesT>(dsm + kDtWarps * kDescGroup * kDtTileStride);    // [warp][keypoint][1536]
+    __shared__ __align__(8) uint64_t mbar[kDtWarps][2];
+    const int frame = frameBase + blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int o0 = (blockIdx.x * kDtWarps + warp) * kDescGroup;
+    const int total = outCnt[2 * frame];
+    if (o0 >= total) return;                                   // warps are independent: no block barrier below
+    const int ng = min(kDescGroup, total - o0);
+    WorkItem mine; mine.level = 0; mine.pad = 0; mine.x = 0; mine.y = 0; mine.dst = 0;
+    if (lane < ng) mine = work[(size_t)frame * g->outCap + o0 + lane];
+    const uint32_t bar = smem_addr(&mbar[warp][0]), obar = smem_addr(&mbar[warp][1]);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(obar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(obar), "r"(ng * kOtTileBytes) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(ng * kDtTileBytes) : "memory");
+    }
+    __syncwarp();
+    if (lane < ng) {                                           // two tile requests per keypoint of the group: orientation window first
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     :: "r"(smem_addr(otiles[warp][lane])), "l"(reinterpret_cast<uint64_t>(&omaps.m[mine.level])), "r"(obar),
+                        "r"((mine.x - kHalfPatch) & ~15), "r"(mine.y - kHalfPatch), "r"(frame)
+                     : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     :: "r"(smem_addr(tiles[warp][lane])), "l"(reinterpret_cast<uint64_t>(&bmaps.m[mine.level])), "r"(bar),
+                        "r"((mine.x - 18) & ~15), "r"(mine.y - 18), "r"(frame)
+                     : "memory");
+    }
+    // this lane's 8 tests
+    float px0[8], py0[8], px1[8], py1[8];
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+        const char4 t = c_pattern[lane * 8 + bit];
+        px0[bit] = (float)t.x; py0[bit] = (float)t.y; px1[bit] = (float)t.z; py1[bit] = (float)t.w;
+    }
+    const int u = lane - kHalfPatch;
+    const int vm = lane < 31 ? c_umax[abs(u)] : -1;          // lane 31 holds no column
+    int myM10 = 0, myM01 = 0;
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(obar), "r"(0) : "memory");
+    }
+    for (int j = 0; j < ng; ++j) {
+        const int kx = __shfl_sync(0xffffffffu, mine.x, j);
+        // centre of the disc inside the tile: row 15, column kx - floor16(kx - 15); lane 31 (u = 16) reads column <= 47 and is masked
+        const uint8_t* ctr = otiles[warp][j] + kHalfPatch * kOtBoxW + (kx - ((kx - kHalfPatch) & ~15));
+        int m10 = 0, m01 = 0;
+#pragma unroll
+        for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+            const int val = ((v < 0 ? -v : v) <= vm) ? (int)ctr[v * kOtBoxW + u] : 0;
+            m10 += u * val;
+            m01 += v * val;
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, s);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+        }
+        if (lane == j) { myM10 = m10; myM01 = m01; }
+    }
+    float ca = 0.f, sb = 0.f;
+    if (lane < ng) {
+        const float angle = fast_atan2_deg((float)myM01, (float)myM10);
+        outKp[(size_t)frame * g->outCap + mine.dst].angle = angle;
+        constexpr float factorPI = (float)(3.14159265358979323846 / 180.f);
+        const double rad = (double)__fmul_rn(angle, factorPI);
+        double sd, cd;
+        sincos(rad, &sd, &cd);
+        ca = (float)cd; sb = (float)sd;
+    }
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar), "r"(0) : "memory");
+    }
+    for (int j = 0; j < ng; ++j) {
+        const float a = __shfl_sync(0xffffffffu, ca, j), b = __shfl_sync(0xffffffffu, sb, j);
+        const int kx = __shfl_sync(0xffffffffu, mine.x, j);
+        const int dst = __shfl_sync(0xffffffffu, mine.dst, j);
+        // centre of the window inside the tile: row 18, column kx - floor16(kx - 18)
+        const uint8_t* bc = tiles[warp][j] + 18 * kDtBoxW + (kx - ((kx - 18) & ~15));
+        int byte = 0;
+#pragma unroll
+        for (int bit = 0; bit < 8; ++bit) {
+            const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(px0[bit], b), __fmul_rn(py0[bit], a)));
+            const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px0[bit], a), __fmul_rn(py0[bit], b)));
+            const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px1[bit], b), __fmul_rn(py1[bit], a)));
+            const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px1[bit], a), __fmul_rn(py1[bit], b)));
+            const int v0 = bc[r0 * kDtBoxW + c0], v1 = bc[r1 * kDtBoxW + c1];
+            byte |= (v0 < v1 ? 1 : 0) << bit;
+        }
+        outDesc[((size_t)frame * g->outCap + dst) * 32 + lane] = (uint8_t)byte;
     }
 }
 
