@@ -70,6 +70,9 @@ struct Extractor {
     FsMaps blurMaps{};               // the pyramid levels again, with the blur's 144 x 36 box
     FsMaps descMaps{};               // the BLURRED planes with the descriptor's 64 x 37 box
     FsMaps oriMaps{};                // the pyramid levels with the orientation disc's 48 x 31 box (level 0 per pass)
+    FsMaps pyrMaps{};                // m[l] = SOURCE level l-1 with the box of the resize to level l (m[1] per pass)
+    PyrBox pyrBox[kMaxLevels] = {};  // boxW = 0: level l keeps k_pyr_level_fast / k_pyr_level
+    bool pyrTma = true;              // ORBX_PYR_TMA=0 (A/B switch)
     bool descTma = true;             // ORBX_DESC_TMA=0: k_orient_brief with global gathers (A/B switch)
     bool blurTma = true;             // ORBX_BLUR_TMA=0: the register-only k_blur7 (A/B switch; also the fallback when level 0 is not TMA-addressable)
     NmsTabs nmsTabs{};               // same-cell column / row masks of the non-max suppression
@@ -258,6 +261,25 @@ int configureShape(Extractor* E, int W, int H) {
                 if (std::min(taps[G.tabX + last].ofs + 1, P.w - 1) - taps[G.tabX + x].ofs > 7) ok = false;
             }
             E->pyrFast[l] = ok;
+            // box of the TMA-staged resize: the exact source extent of a 128 x 32 destination tile, from the tap tables
+            E->pyrBox[l] = PyrBox{0, 0};
+            if (ok) {
+                int ex = 0, ey = 0;
+                for (int X0 = 0; X0 < G.w; X0 += 128) {
+                    const int lastGroup = std::min(X0 + 124, (G.w - 1) & ~3);
+                    const int start = taps[G.tabX + X0].ofs & ~15;
+                    const int end = (taps[G.tabX + lastGroup].ofs & ~3) + 11;       // the third word a thread reads
+                    ex = std::max(ex, end - start + 1);
+                }
+                for (int Y0 = 0; Y0 < G.h; Y0 += 32) {
+                    const int Yl = std::min(Y0 + 31, G.h - 1);
+                    const int gy = std::min(std::max(taps[G.tabY + Y0].ofs, 0), P.h - 1);
+                    const int last = std::min(std::max(taps[G.tabY + Yl].ofs + 1, 0), P.h - 1);
+                    ey = std::max(ey, last - gy + 1);
+                }
+                const int bw = (ex + 15) & ~15;
+                if (bw <= 256 && ey <= 256 && (size_t)bw * ey <= 40 * 1024) E->pyrBox[l] = PyrBox{bw, ey};
+            }
         }
         E->blurTiles.start[l] = tileStart;
         E->blurTiles.tilesX[l] = (G.w + kBlurStripW - 1) / kBlurStripW;
@@ -372,10 +394,14 @@ int configureShape(Extractor* E, int W, int H) {
     memset(&E->blurMaps, 0, sizeof(E->blurMaps));
     memset(&E->descMaps, 0, sizeof(E->descMaps));
     memset(&E->oriMaps, 0, sizeof(E->oriMaps));
+    memset(&E->pyrMaps, 0, sizeof(E->pyrMaps));
     for (int l = 0; l < L; ++l) {
         if (l > 0) E->fsMaps.tmaOk[l] = encodeLevelMap(&E->fsMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes) ? 1 : 0;
         E->scoreMaps.tmaOk[l] = encodeLevelMap(&E->scoreMaps.m[l], g.score[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kNmsBoxH) ? 1 : 0;
         E->descMaps.tmaOk[l] = encodeLevelMap(&E->descMaps.m[l], g.blur[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kDtBoxH, kDtBoxW) ? 1 : 0;
+        if (l > 1 && E->pyrBox[l].boxW)
+            E->pyrMaps.tmaOk[l] = encodeLevelMap(&E->pyrMaps.m[l], g.lvl[l - 1], g.lv[l - 1].w, g.lv[l - 1].h, B, (size_t)g.lv[l - 1].pitch,
+                                                 g.lv[l - 1].planeBytes, E->pyrBox[l].boxH, E->pyrBox[l].boxW) ? 1 : 0;
         if (l > 0) E->oriMaps.tmaOk[l] = encodeLevelMap(&E->oriMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kOtBoxH, kOtBoxW) ? 1 : 0;
         if (l > 0) E->blurMaps.tmaOk[l] = encodeLevelMap(&E->blurMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kBtBoxH, kBtBoxW) ? 1 : 0;
     }
@@ -479,7 +505,14 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
     for (int l = 1; l < L; ++l) {
         dim3 grid((g.lv[l].w + 127) / 128, (g.lv[l].h + 7) / 8, n), block(32, 8);
         const bool srcAligned = l > 1 || ((((uintptr_t)l0.base | (uintptr_t)l0.pitch | (uintptr_t)l0.frameBytes) & 3) == 0);
-        if (E->pyrFast[l] && srcAligned) {
+        bool ptma = E->pyrTma && E->pyrFast[l] && srcAligned && E->pyrBox[l].boxW > 0;
+        CUtensorMap pm = E->pyrMaps.m[l];
+        if (ptma && l == 1) ptma = encodeLevelMap(&pm, l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride, E->pyrBox[1].boxH, E->pyrBox[1].boxW);
+        else if (ptma) ptma = E->pyrMaps.tmaOk[l] != 0;
+        if (ptma) {
+            dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + 8 * kPyrRows - 1) / (8 * kPyrRows), n);
+            k_pyr_level_tma<<<fgrid, block, (size_t)E->pyrBox[l].boxW * E->pyrBox[l].boxH, st>>>(pm, E->dGeom, l, E->dTaps, E->pyrBox[l], fb);
+        } else if (E->pyrFast[l] && srcAligned) {
             dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + 8 * kPyrRows - 1) / (8 * kPyrRows), n);
             k_pyr_level_fast<<<fgrid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);
         } else {
@@ -676,6 +709,7 @@ int orbx_create(const orbx_config* cfg, orbx_handle* out) {
     if (const char* fc = getenv("ORBX_FAST_COMPASS")) E->fastCompass = atoi(fc) != 0;
     if (const char* bt = getenv("ORBX_BLUR_TMA")) E->blurTma = atoi(bt) != 0;
     if (const char* dt = getenv("ORBX_DESC_TMA")) E->descTma = atoi(dt) != 0;
+    if (const char* pt = getenv("ORBX_PYR_TMA")) E->pyrTma = atoi(pt) != 0;
     {
         int least = 0, greatest = 0;
         cudaDeviceGetStreamPriorityRange(&least, &greatest);

@@ -629,4 +629,103 @@ __global__ void __launch_bounds__(kDtWarps * 32) k_orient_brief_tma(const __grid
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// E1, TMA-staged variant of k_pyr_level_fast (same arithmetic: cv::resize INTER_LINEAR in 11-bit fixed point, see there;
+// src/ORBextractor.cc:1170-1195).  A CTA produces a 128 x 32 tile of level l; the source region its taps touch (known exactly
+// from the tap tables: the host sizes the box per level, PyrBox) arrives as ONE 3-D TMA tile of level l-1, and every thread's
+// three source words per row come from shared memory instead of three dependent global loads with clamped indices.  A tap
+// never selects a byte beyond the source row (the tables clamp), so the zero fill / neighbouring bytes that replace the
+// clamped duplicate words are never selected: bit-identical.
+// grid (ceil(w/128), ceil(h/32), B), block (32, 8); dynamic smem = boxW * boxH.
+struct PyrBox { int boxW, boxH; };
+
+__global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ CUtensorMap srcMap, const DevGeom* __restrict__ g, int l,
+                                                       const ResizeTap* __restrict__ taps, PyrBox pb, int frameBase) {
+    extern __shared__ __align__(128) uint8_t ptile[];
+    __shared__ __align__(8) uint64_t mbar;
+    const LevelGeom& D = g->lv[l];
+    const LevelGeom& S = g->lv[l - 1];
+    const int frame = frameBase + blockIdx.z;
+    const int X0 = blockIdx.x * 128, Y0 = blockIdx.y * 32;
+    // tile origin in the source level: first tap of the CTA's first column (16-byte aligned) / first row (clamped like the taps)
+    const int gx = taps[D.tabX + X0].ofs & ~15;
+    const int gy = min(max(taps[D.tabY + Y0].ofs, 0), S.h - 1);
+    const int tid = threadIdx.y * 32 + threadIdx.x;
+    const uint32_t bar = smem_addr(&mbar);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(pb.boxW * pb.boxH) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                     :: "r"(smem_addr(ptile)), "l"(reinterpret_cast<uint64_t>(&srcMap)), "r"(bar), "r"(gx), "r"(gy), "r"(frame)
+                     : "memory");
+    }
+    __syncthreads();                                           // the barrier object is initialised before anyone polls it
+    const int x4 = X0 + threadIdx.x * 4;
+    const int yb = Y0 + threadIdx.y * kPyrRows;
+    const bool active = x4 < D.w && yb < D.h;
+    uint32_t coef[4], sel[4];
+    int wofs = 0, sh = 0;
+    if (active) {                                              // per-thread column setup overlaps the tile's flight
+        const ResizeTap t0 = taps[D.tabX + x4];
+        const int a0 = t0.ofs;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const ResizeTap t = taps[D.tabX + min(x4 + k, D.w - 1)];
+            const int r0 = t.ofs - a0, r1 = min(t.ofs + 1, S.w - 1) - a0;
+            sel[k] = (uint32_t)r0 | ((uint32_t)r1 << 4);
+            coef[k] = (uint32_t)(uint16_t)t.c0 | ((uint32_t)(uint16_t)t.c1 << 16);
+        }
+        wofs = ((a0 & ~3) - gx) >> 2;                          // word of the tile row that holds byte a0
+        sh = (a0 & 3) * 8;
+    }
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar), "r"(0) : "memory");
+    }
+    if (!active) return;
+    uint8_t* dst = g->lvl[l] + (size_t)frame * D.planeBytes;
+    const int rowW = pb.boxW >> 2;
+    const uint32_t* tw = reinterpret_cast<const uint32_t*>(ptile) + wofs;
+    uint32_t hA[4], hB[4];
+    int rA = -1, rB = -1;
+    auto hrow = [&](int r, uint32_t (&h)[4]) {
+        const uint32_t* rowp = tw + (r - gy) * rowW;
+        const uint32_t W0 = rowp[0], W1 = rowp[1], W2 = rowp[2];
+        const uint32_t lo = __funnelshift_r(W0, W1, sh), hi = __funnelshift_r(W1, W2, sh);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t hk = __dp2a_lo(coef[k], __byte_perm(lo, hi, sel[k]), 0u);     // p[a]*c0 + p[a1]*c1
+            h[k] = (hk << 12) & 0xffff0000u;                                             // (hk >> 4) << 16
+        }
+    };
+#pragma unroll
+    for (int j = 0; j < kPyrRows; ++j) {
+        const int y = yb + j;
+        if (y >= D.h) break;
+        const ResizeTap ty = taps[D.tabY + y];
+        const int s0 = min(max(ty.ofs, 0), S.h - 1), s1 = min(max(ty.ofs + 1, 0), S.h - 1);
+        if (s0 == rB) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) hA[k] = hB[k];
+            rA = rB; rB = -1;
+        } else if (s0 != rA) { hrow(s0, hA); rA = s0; }
+        if (s1 == rA) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) hB[k] = hA[k];
+            rB = rA;
+        } else if (s1 != rB) { hrow(s1, hB); rB = s1; }
+        const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = (__umulhi(hA[k], b0) + __umulhi(hB[k], b1) + 2u) >> 2;
+        const uint32_t packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+        uint8_t* d = dst + (size_t)y * D.pitch + x4;
+        if (x4 + 3 < D.w) *reinterpret_cast<uint32_t*>(d) = packed;
+        else for (int k = 0; k < 4 && x4 + k < D.w; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+    }
+}
+
 }  // namespace orbx

@@ -48,5 +48,8 @@ def test_schedule_switches_do_not_change_results():
                 # blur: register-only kernel instead of the TMA-staged one; quadtree CTAs capped per SM
                 {"ORBX_BLUR_TMA": "0"}, {"ORBX_BLUR_TMA": "0", "ORBX_OVERLAP": "0"}, {"ORBX_TREE_CTAS": "1"},
                 # orientation + BRIEF with global gathers instead of TMA-staged windows
-                {"ORBX_DESC_TMA": "0"}, {"ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_GEN": "1"}):
+                {"ORBX_DESC_TMA": "0"}, {"ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_GEN": "1"},
+                # pyramid levels with direct global loads instead of TMA-staged source tiles; everything pre-TMA at once
+                {"ORBX_PYR_TMA": "0"},
+                {"ORBX_PYR_TMA": "0", "ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_TMA": "0", "ORBX_GRAPHS": "0"}):
         assert _digest(env) == base, env
