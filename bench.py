@@ -207,6 +207,94 @@ def latency_bench(args, torch, local, frames):
             "note": "one frame in flight, synchronous calls, host buffers (pinned image)"}
 
 
+def search_latency_rows(local):
+    """One row per ORBmatcher search member: per-call time through the product the way the C++ adapter calls it
+    - an ORBmatcher CONSTRUCTED PER CALL, as the reference does (`ORBmatcher matcher(0.9,true);` inside every tracking /
+    mapping / loop-closing function, e.g. src/Tracking.cc:2789), its frame slot(s) re-bound, host arrays in, host arrays out -
+    beside the CPU port's (oracle/cpp) time for the same call on one host thread.  Median over 30 / 8 calls after 3 warm-ups.
+    Inputs: two consecutive EuRoC-shaped frames of the synthetic stream (tests/matcher_scenarios.py)."""
+    from mam3slam_b200 import ORBmatcher
+    from oracle import matcher as om
+    from tests import matcher_scenarios as sc
+    (k1, d1), (k2, d2), bounds, tabs = sc.frame_pair(W, H, NFEAT, 0)
+    rng = np.random.default_rng(3)
+    n1, n2 = len(k1), len(k2)
+    scale, sig2, isig2 = tabs["scale"], tabs["sigma2"], tabs["inv_sigma2"]
+    jit = lambda a, amp: (a + rng.uniform(-amp, amp, len(a))).astype(np.float32)
+    u, v = jit(k1["x"], 4), jit(k1["y"], 4)
+    u2, v2 = jit(k2["x"], 2), jit(k2["y"], 2)
+    lvl = np.clip(k1["octave"] + rng.integers(0, 2, n1), 0, NLEVELS - 1).astype(np.int32)
+    lvl2 = np.clip(k2["octave"] + rng.integers(0, 2, n2), 0, NLEVELS - 1).astype(np.int32)
+    ones1, ones2 = np.ones(n1, np.uint8), np.ones(n2, np.uint8)
+    occ = np.zeros(n2, np.uint8)
+    vc = np.ones(n1, np.float32)
+    fv1, fv2 = sc.feat_vec(d1), sc.feat_vec(d2)
+    fv1t, fv2t = sc.feat_vec(d1, 5), sc.feat_vec(d2, 5)
+    F12 = np.array([[0, 0, 0.02], [0, 0, -1.0], [-0.02, 1.0, 0]], np.float32)
+    ep = np.array([W * 0.8, H * 0.5], np.float32)
+    prev = np.stack([k1["x"], k1["y"]], 1)
+
+    def gpu(nn, ori, fn, two=False):
+        def call():
+            m = ORBmatcher(nn, ori, device=local)
+            A = m.slot(0, k2, d2, bounds) if not two else m.slot(0, k1, d1, bounds)
+            B = m.slot(1, k2, d2, bounds) if two else None
+            r = fn(m, A, B)
+            m.close()
+            return r
+        return call
+
+    rows = [
+        ("M1 SearchByProjection(Frame, local map points)", "src/ORBmatcher.cc:43-213",
+         gpu(0.8, True, lambda m, A, B: m.SearchByProjection_LocalMap(A, occ, scale, ones1, u, v, lvl, vc, d1, 3.0)),
+         lambda: om.search_local_map(k2, d2, bounds, occ, scale, ones1, u, v, lvl, vc, d1, 3.0, 0.8)),
+        ("M2 SearchByProjection(Cur, Last)", ":1676-1887",
+         gpu(0.9, True, lambda m, A, B: m.SearchByProjection_Frame(A, occ, scale, ones1, u, v, k1["octave"], k1["angle"], d1, 15.0)),
+         lambda: om.search_frame(k2, d2, bounds, occ, scale, ones1, u, v, k1["octave"], k1["angle"], d1, 15.0, 100, True)),
+        ("M3 SearchByProjection(Frame, KeyFrame, found)", ":1889-2010",
+         gpu(0.9, True, lambda m, A, B: m.SearchByProjection_Frame(A, occ, scale, ones1, u, v, lvl, k1["angle"], d1, 10.0, 64)),
+         lambda: om.search_frame(k2, d2, bounds, occ, scale, ones1, u, v, lvl, k1["angle"], d1, 10.0, 64, True)),
+        ("M4 SearchByBoW(KeyFrame, Frame)", ":223-425",
+         gpu(0.7, True, lambda m, A, B: m.SearchByBoW_KF_Frame(A, fv1, ones1, B, fv2), True),
+         lambda: om.search_bow_kf_frame(k1, d1, fv1, ones1, k2, d2, fv2, 0.7, True)),
+        ("M4 SearchByBoW(KeyFrame, KeyFrame)", ":765-905",
+         gpu(0.8, True, lambda m, A, B: m.SearchByBoW_KF_KF(A, fv1, ones1, B, fv2, ones2), True),
+         lambda: om.search_bow_kf_kf(k1, d1, fv1, ones1, k2, d2, fv2, ones2, 0.8, True)),
+        ("M5 SearchForInitialization", ":648-763",
+         gpu(0.9, True, lambda m, A, B: m.SearchForInitialization(A, B, prev, 100), True),
+         lambda: om.search_initialization(k1, d1, k2, d2, bounds, prev, 100, 0.9, True)),
+        ("M6 SearchForTriangulation (Pinhole)", ":907-1146",
+         gpu(0.6, False, lambda m, A, B: m.SearchForTriangulation(A, fv1t, ones1, B, fv2t, ones2, ep, scale, F12, sig2 * 9, False), True),
+         lambda: om.search_triangulation(k1, d1, fv1t, ones1, k2, d2, fv2t, ones2, ep, scale, F12, sig2 * 9, False, False)),
+        ("M7 SearchByProjection(KeyFrame, Sim3, points)", ":427-646",
+         gpu(0.9, True, lambda m, A, B: m.SearchByProjection_Sim3(A, occ, scale, ones1, u, v, lvl, d1, 8, 1.5)),
+         lambda: om.search_sim3(k2, d2, bounds, occ, scale, ones1, u, v, lvl, d1, 8, 1.5)),
+        ("M8 SearchBySim3", ":1457-1674",
+         gpu(0.75, True, lambda m, A, B: m.SearchBySim3(A, B, scale, scale, ones1, u, v, lvl, d1, ones2, u2, v2, lvl2, d2, 7.5), True),
+         lambda: om.search_by_sim3(k1, d1, bounds, k2, d2, bounds, scale, scale, ones1, u, v, lvl, d1, ones2, u2, v2, lvl2, d2, 7.5)),
+        ("M9 Fuse (candidate part)", ":1148-1455",
+         gpu(0.6, True, lambda m, A, B: m.Fuse_candidates(A, scale, isig2, ones1, u, v, lvl, d1, 3.0, True)),
+         lambda: om.fuse_candidates(k2, d2, bounds, scale, isig2, ones1, u, v, lvl, d1, 3.0, True)),
+    ]
+
+    def med(fn, warm, reps):
+        for _ in range(warm):
+            fn()
+        t = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); t.append(time.perf_counter() - t0)
+        return float(np.median(t)) * 1e3
+
+    out = []
+    for name, ref, g, c in rows:
+        g_ms, c_ms = med(g, 3, 30), med(c, 1, 8)
+        out.append({"member": name, "reference": ref, "gpu_call_ms": g_ms, "cpu_port_call_ms": c_ms, "ratio": c_ms / g_ms})
+    ORBmatcher.drain_pool()
+    return {"note": "ORBmatcher constructed per call (pooled handle + frame slots), frame(s) re-uploaded and grid rebuilt per call, "
+                    f"host arrays in / out, synchronous; {n1} / {n2} keypoints; CPU = oracle/cpp on one thread through ctypes",
+            "rows": out}
+
+
 def sparse_bench(args, torch, local, rank):
     """the dense synthetic texture (26 k FAST candidates per frame) loads FAST's sparse paths and the
     quadtree unrepresentatively.  The same device-resident extraction on a SPARSE-texture stream (synth.stream(sparse=True):
@@ -587,6 +675,8 @@ def run_gpu(args):
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
     latency = latency_bench(args, torch, local, frames) if rank == 0 else None
+    if latency is not None and not args.no_cpu:
+        latency["search_members"] = search_latency_rows(local)
     sparse = sparse_bench(args, torch, local, rank) if rank == 0 and not args.no_sparse else None
     if rank == 0:
         pk, pk_kind = peaks()
@@ -773,7 +863,7 @@ def main():
                     help="batches per step: a step is 1024 frames (~12 ms on a B200) so that the driver's 20 steps time >= 0.2 s")
     ap.add_argument("--sets", type=int, default=8, help="distinct input batches (input working set > L2)")
     ap.add_argument("--cpu-frames", type=int, default=400, help="frames timed for cpu_baseline")
-    ap.add_argument("--pipes", type=int, default=2, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
+    ap.add_argument("--pipes", type=int, default=3, help="extractor/matcher handle pairs working on alternating batches (1 = serial)")
     ap.add_argument("--e2e-pipes", type=int, default=3, help="host threads (one handle pair each) of the end-to-end leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-kitti", action="store_true", help="skip the KITTI-shaped leg (config 3)")

@@ -6,6 +6,7 @@ MapPoint-dependent predicate arrives as a per-element array, exactly as the C++ 
 the reference; all Hamming work runs in the CUDA library (no CPU fallback).
 """
 import ctypes as C
+import threading
 import numpy as np
 
 from ._lib import lib, check_m, OrbmFrameView, OrbmFeatVec, OrbmVocabView
@@ -162,17 +163,59 @@ class ORBmatcher:
     TH_LOW = 50
     HISTO_LENGTH = 30
 
+    # The reference constructs an ORBmatcher per call (a stack local in every tracking / mapping / loop-closing function), so
+    # construction must be free: like the C++ adapter (cpp/ORBmatcher.h), the CUDA-side state - orbm handle (stream +
+    # scratch) and two device frame slots - comes from a per-thread pool.  __init__ pops a set for the device, close() pushes it
+    # back; drain_pool() destroys what the calling thread's pool holds.
+    _POOL = threading.local()
+
+    @classmethod
+    def _pool(cls):
+        if not hasattr(cls._POOL, "sets"):
+            cls._POOL.sets = []
+        return cls._POOL.sets
+
     def __init__(self, nnratio=0.6, checkOri=True, device=0):
         self._L = lib()
         self.mfNNratio = float(nnratio)
         self.mbCheckOrientation = bool(checkOri)
+        self._device = int(device)
+        sets = self._pool()
+        for i in range(len(sets) - 1, -1, -1):
+            if sets[i][0] == self._device:
+                _, self._h, self._slots = sets.pop(i)
+                return
         self._h = C.c_void_p()
-        check_m(self._L.orbm_create(int(device), C.byref(self._h)), None, "orbm_create")
+        self._slots = [None, None]
+        check_m(self._L.orbm_create(self._device, C.byref(self._h)), None, "orbm_create")
 
     def close(self):
         if getattr(self, "_h", None):
-            self._L.orbm_destroy(self._h)
+            self._pool().append((self._device, self._h, self._slots))
             self._h = None
+            self._slots = [None, None]
+
+    def slot(self, i, kps, desc, bounds, on_device=False, n=None):
+        """One of the matcher's two persistent device frame slots (the adapter's a_ / b_), bound to a frame: created on first
+        use, afterwards only re-uploaded - no allocation in steady state, also across pooled ORBmatcher objects."""
+        F = self._slots[i]
+        if F is None:
+            F = self._slots[i] = MatchFrame(self, kps, desc, bounds, on_device, n)
+        else:
+            F._m = self
+            F.update(kps, desc, bounds, on_device, n)
+        return F
+
+    @classmethod
+    def drain_pool(cls):
+        L = lib()
+        for _, h, slots in cls._pool():
+            for F in slots:
+                if F is not None and F._f:
+                    L.orbm_frame_destroy(h, F._f)
+                    F._f = None
+            L.orbm_destroy(h)
+        cls._pool().clear()
 
     def __del__(self):
         try:
