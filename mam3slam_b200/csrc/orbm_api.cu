@@ -296,6 +296,8 @@ struct SearchIO {
     const uint8_t* elig = nullptr;
     uint8_t* occ = nullptr;                 // in/out, n bytes
     const uint8_t* qocc = nullptr;          // per ORIGINAL query (indexed through qsrc): its match occupies the keypoint; NULL = always
+    std::vector<int2> nodeQ;                // BoW: query range of every shared node (k_search_nodes), empty = single-CTA path
+    const uint8_t* qdescDev = nullptr;      // BoW, node-parallel: the source frame's descriptors in HBM (rows gathered on the device)
     std::vector<int> result, dist;
 };
 
@@ -310,6 +312,9 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     const size_t oWin = S.take<float4>(nq), oLev = S.take<int2>(nq), oRun = S.take<int2>(nq), oDesc = S.take<uint32_t>((size_t)nq * 8);
     const size_t oAng = S.take<float>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oElig = S.take<uint8_t>(std::max(n, 1));
     const size_t oOcc = S.take<uint8_t>(std::max(n, 1)), oQocc = S.take<uint8_t>(nq);
+    const bool byNode = !io.nodeQ.empty() && io.qdescDev && P.source == 1 && P.state == 1;
+    const int nNodes = (int)io.nodeQ.size();
+    const size_t oNode = S.take<int2>(std::max(nNodes, 1)), oSrc = S.take<int>(byNode ? nq : 1), oTicket = S.take<unsigned int>(4);
     const size_t inEnd = S.off;
     const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(16);
     const size_t outEnd = S.off;
@@ -319,8 +324,14 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     if (!io.qlev.empty()) memcpy(S.host<int2>(oLev), io.qlev.data(), (size_t)nq * sizeof(int2));
     if (!io.qrun.empty()) memcpy(S.host<int2>(oRun), io.qrun.data(), (size_t)nq * sizeof(int2));
     if (!io.qangle.empty()) memcpy(S.host<float>(oAng), io.qangle.data(), (size_t)nq * sizeof(float));
-    uint8_t* hd = S.host<uint8_t>(oDesc);
-    for (int q = 0; q < nq; ++q) memcpy(hd + 32 * (size_t)q, io.qdescSrc + 32 * (size_t)io.qsrc[q], 32);
+    if (byNode) {
+        memcpy(S.host<int2>(oNode), io.nodeQ.data(), (size_t)nNodes * sizeof(int2));
+        memcpy(S.host<int>(oSrc), io.qsrc.data(), (size_t)nq * sizeof(int));
+        *S.host<unsigned int>(oTicket) = 0;
+    } else {
+        uint8_t* hd = S.host<uint8_t>(oDesc);
+        for (int q = 0; q < nq; ++q) memcpy(hd + 32 * (size_t)q, io.qdescSrc + 32 * (size_t)io.qsrc[q], 32);
+    }
     if (io.nBow) memcpy(S.host<int>(oBow), io.bowIdx, (size_t)io.nBow * sizeof(int));
     if (io.elig && n) memcpy(S.host<uint8_t>(oElig), io.elig, n);
     if (io.occ && n) memcpy(S.host<uint8_t>(oOcc), io.occ, n);
@@ -344,10 +355,18 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     // window searches walk one query per lane (32 per warp), BoW / triangulation runs one query per warp
     const int units = P.source == 0 ? (nq + 31) / 32 : nq;
     const int grid = P.state != 0 ? 1 : std::max(1, std::min(units, M->smCount * 2));
-    if (P.source == 0) k_search<true><<<grid, kSearchThreads, smem, M->stream>>>(P);
-    else k_search<false><<<grid, kSearchThreads, smem, M->stream>>>(P);
-    ++M->launches;
-    if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
+    if (byNode) {
+        // BoW: a warp per shared node, rotation filter fused into the last CTA (orbm_kernels.cuh, k_search_nodes)
+        P.nodeQ = S.dev<int2>(oNode); P.nNodes = nNodes; P.qsrc = S.dev<int>(oSrc);
+        P.qdescBase = reinterpret_cast<const uint32_t*>(io.qdescDev); P.ticket = S.dev<unsigned int>(oTicket);
+        k_search_nodes<<<(nNodes + kNodeWarps - 1) / kNodeWarps, kNodeWarps * 32, 0, M->stream>>>(P);
+        ++M->launches;
+    } else {
+        if (P.source == 0) k_search<true><<<grid, kSearchThreads, smem, M->stream>>>(P);
+        else k_search<false><<<grid, kSearchThreads, smem, M->stream>>>(P);
+        ++M->launches;
+        if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
+    }
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oRes, (uint8_t*)M->scratch + oRes, outEnd - oRes, cudaMemcpyDeviceToHost, M->stream));
     if (io.occ && n) CKM(cudaMemcpyAsync(S.host<uint8_t>(oOcc), S.dev<uint8_t>(oOcc), n, cudaMemcpyDeviceToHost, M->stream));
@@ -631,19 +650,32 @@ bool validFeatVec(const orbm_featvec* fv, int n) {
     return true;
 }
 
+// A DBoW2 FeatureVector lists every feature under exactly one node; a hand-built orbm_featvec need not.  The node-parallel
+// search (k_search_nodes) relies on it for side 2.  ORBM_BOW_NODES=0 forces the single-CTA path (A/B switch).
+bool listsEachFeatureOnce(const orbm_featvec* fv, int n) {
+    static const bool enabled = [] { const char* e = getenv("ORBM_BOW_NODES"); return !(e && e[0] == '0'); }();
+    if (!enabled) return false;
+    if (fv->n_nodes == 0) return true;
+    std::vector<uint8_t> seen((size_t)std::max(n, 1), 0);
+    for (int i = fv->off[0]; i < fv->off[fv->n_nodes]; ++i) { if (seen[fv->idx[i]]) return false; seen[fv->idx[i]] = 1; }
+    return true;
+}
+
 // The merge-join of two DBoW2::FeatureVector maps (e.g. src/ORBmatcher.cc:241-392): for every shared node, every
 // eligible feature of side 1 becomes a query (in node order, then list order) whose candidates are the node's run of
 // side 2.
-void joinQueries(const orbm_featvec* a, const orbm_featvec* b, const uint8_t* elig1, SearchIO& io) {
+void joinQueries(const orbm_featvec* a, const orbm_featvec* b, const uint8_t* elig1, SearchIO& io, bool nodeRanges = false) {
     int ia = 0, ib = 0;
     while (ia < a->n_nodes && ib < b->n_nodes) {
         if (a->node[ia] == b->node[ib]) {
+            const int q0 = (int)io.qsrc.size();
             for (int p = a->off[ia]; p < a->off[ia + 1]; ++p) {
                 const int i1 = a->idx[p];
                 if (elig1 && !elig1[i1]) continue;
                 io.qrun.push_back(make_int2(b->off[ib] - b->off[0], b->off[ib + 1] - b->off[0]));
                 io.qsrc.push_back(i1);
             }
+            if (nodeRanges && (int)io.qsrc.size() > q0) io.nodeQ.push_back(make_int2(q0, (int)io.qsrc.size()));
             ++ia; ++ib;
         } else if (a->node[ia] < b->node[ib]) {
             ia = (int)(std::lower_bound(a->node, a->node + a->n_nodes, b->node[ib]) - a->node);
@@ -677,12 +709,14 @@ int orbm_search_bow_kf_frame(orbm_handle M, orbm_frame kf, const orbm_featvec* f
     int rc = ensureHostKps(M, kf);
     if (rc) return rc;
     std::vector<uint8_t> d1;
-    if ((rc = fetchDescHost(M, kf, d1))) return rc;
+    const bool byNode = listsEachFeatureOnce(fv_f, f->n);
+    if (!byNode && (rc = fetchDescHost(M, kf, d1))) return rc;
     for (int j = 0; j < f->n; ++j) match_f[j] = -1;
     SearchIO io;
-    joinQueries(fv_kf, fv_f, elig1, io);
+    joinQueries(fv_kf, fv_f, elig1, io, byNode);
     for (int q = 0; q < io.nq; ++q) io.qangle.push_back(kf->kpsHost[io.qsrc[q]].angle);
     io.qdescSrc = d1.data();
+    if (byNode) io.qdescDev = reinterpret_cast<const uint8_t*>(kf->descDev);
     std::vector<uint8_t> occ((size_t)std::max(f->n, 1), 0);        // vpMapPointMatches starts all NULL (:227)
     io.occ = occ.data();
     SearchParams P = baseParams();
@@ -703,12 +737,14 @@ int orbm_search_bow_kf_kf(orbm_handle M, orbm_frame kf1, const orbm_featvec* fv1
     int rc = ensureHostKps(M, kf1);
     if (rc) return rc;
     std::vector<uint8_t> d1;
-    if ((rc = fetchDescHost(M, kf1, d1))) return rc;
+    const bool byNode = listsEachFeatureOnce(fv2, kf2->n);
+    if (!byNode && (rc = fetchDescHost(M, kf1, d1))) return rc;
     for (int i = 0; i < kf1->n; ++i) matches12[i] = -1;
     SearchIO io;
-    joinQueries(fv1, fv2, elig1, io);
+    joinQueries(fv1, fv2, elig1, io, byNode);
     for (int q = 0; q < io.nq; ++q) io.qangle.push_back(kf1->kpsHost[io.qsrc[q]].angle);
     io.qdescSrc = d1.data();
+    if (byNode) io.qdescDev = reinterpret_cast<const uint8_t*>(kf1->descDev);
     io.elig = elig2;
     std::vector<uint8_t> occ((size_t)std::max(kf2->n, 1), 0);      // vbMatched2 (:778)
     io.occ = occ.data();

@@ -150,6 +150,11 @@ struct SearchParams {
     int* qDist;                  // best distance
     int* qBin;                   // rotation bin of the accept event or -1
     unsigned long long* evals;
+    // node-parallel BoW searches (k_search_nodes): queries [nodeQ[j].x, nodeQ[j].y) belong to shared node j and all of them
+    // scan the same run; the query descriptor is row qsrc[q] of qdescBase (the source frame's descriptors in HBM)
+    const int2* nodeQ; int nNodes;
+    const int* qsrc; const uint32_t* qdescBase;
+    unsigned int* ticket;        // CTAs-done counter for the fused rotation epilogue (zeroed by the host)
 };
 
 constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 192, kSlots = 64;
@@ -868,6 +873,175 @@ __device__ __forceinline__ void rot_filter_cta(int nq, const int* __restrict__ q
 }
 __global__ void __launch_bounds__(256) k_rot_filter(int nq, const int* __restrict__ qBin, int* __restrict__ qResult) {
     rot_filter_cta(nq, qBin, qResult, true);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// SearchByBoW with one WARP PER SHARED NODE (M4a / M4b).  The match state of these two functions is the occupancy of side 2
+// (vpMapPointMatches[realIdxF] != NULL, src/ORBmatcher.cc:276; vbMatched2[idx2], :826), and a feature of side 2 belongs to
+// exactly ONE node of its FeatureVector, so queries of different nodes can never block each other: only the queries INSIDE a
+// node are order-dependent.  A warp walks the queries of its node in the reference's order; when the node's run of side 2 has
+// at most 32 features (the usual case: ~16 per node at levelsup 4) every lane keeps one candidate descriptor in registers and
+// a query costs one uniform descriptor load, 8 POPC and two warp min-reductions.  The host checks that no side-2 feature is
+// listed under two nodes (a hand-built orbm_featvec could do that) and otherwise uses the single-CTA path (k_search<false>).
+// Fused epilogue: the last CTA to finish runs the rotation-consistency filter (no second launch on the latency path).
+constexpr int kNodeWarps = 2;
+
+// rotation bin of an accept event (e.g. src/ORBmatcher.cc:310-318): qa = query angle, ta = angle of the accepted keypoint
+__device__ __forceinline__ int rot_bin(float qa, float ta) {
+    float rot = __fsub_rn(qa, ta);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 1.0f / ORBM_HISTO_LENGTH));
+    if (bin == ORBM_HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+// Register path of a node: lane l keeps candidates l, l + 32, ... (kC of them: descriptor, index, octave, angle) for the whole
+// node and the queries arrive 32 at a time, one per lane, then broadcast by shuffles: the sequential loop touches no memory
+// except its own result stores.
+template <int kC>
+__device__ __forceinline__ void bow_node_regs(const SearchParams& P, int2 qr, int2 run, unsigned long long& nEval) {
+    const int lane = threadIdx.x & 31;
+    const FrameDev& T = P.tgt;
+    const uint4* drows = reinterpret_cast<const uint4*>(T.desc);
+    const uint4* qrows = reinterpret_cast<const uint4*>(P.qdescBase);
+    const bool needSecond = rule_needs_second(P.rule);
+    const int len = run.y - run.x;
+    uint4 ca[kC], cb[kC];
+    int cidx[kC], coct[kC];
+    float cang[kC];
+    unsigned haveM = 0, blk = 0;
+#pragma unroll
+    for (int j = 0; j < kC; ++j) {
+        const int p = lane + 32 * j;
+        ca[j] = cb[j] = make_uint4(0, 0, 0, 0); cidx[j] = 0; coct[j] = 0; cang[j] = 0.f;
+        if (p < len) {
+            const int idx = P.bowIdx[run.x + p];
+            cidx[j] = idx;
+            if (!P.elig || P.elig[idx] != 0) haveM |= 1u << j;
+            ca[j] = drows[2 * idx]; cb[j] = drows[2 * idx + 1];
+            const float4 k = T.kp4[idx];
+            coct[j] = __float_as_int(k.w); cang[j] = k.z;
+            if (P.occ[idx] != 0) blk |= 1u << j;
+        }
+    }
+    const int nHave = __popc(haveM);
+    for (int q0 = qr.x; q0 < qr.y; q0 += 32) {
+        const int nb = min(32, qr.y - q0);
+        uint4 ma = make_uint4(0, 0, 0, 0), mb = ma;
+        float mang = 0.f;
+        int mocc = 1;
+        if (lane < nb) {
+            const int src = P.qsrc[q0 + lane];
+            ma = qrows[2 * src]; mb = qrows[2 * src + 1];
+            if (P.checkOri) mang = P.qangle[q0 + lane];
+            if (P.qocc) mocc = P.qocc[q0 + lane] != 0;
+        }
+        for (int i = 0; i < nb; ++i) {
+            uint32_t qd[8];
+            qd[0] = __shfl_sync(0xffffffffu, ma.x, i); qd[1] = __shfl_sync(0xffffffffu, ma.y, i);
+            qd[2] = __shfl_sync(0xffffffffu, ma.z, i); qd[3] = __shfl_sync(0xffffffffu, ma.w, i);
+            qd[4] = __shfl_sync(0xffffffffu, mb.x, i); qd[5] = __shfl_sync(0xffffffffu, mb.y, i);
+            qd[6] = __shfl_sync(0xffffffffu, mb.z, i); qd[7] = __shfl_sync(0xffffffffu, mb.w, i);
+            const float qa = __shfl_sync(0xffffffffu, mang, i);
+            const int occupies = __shfl_sync(0xffffffffu, mocc, i);
+            Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = kNoEntry;
+#pragma unroll
+            for (int j = 0; j < kC; ++j) {
+                const int d = hamming8(qd, ca[j], cb[j]);
+                if (((haveM & ~blk) >> j) & 1u) best_update(b, ((uint32_t)d << 20) | (uint32_t)(lane + 32 * j), pack_entry(d, coct[j], cidx[j]));
+            }
+            nEval += nHave;
+            const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
+            const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);          // keys are distinct: at most one lane
+            const unsigned wmask = __ballot_sync(0xffffffffu, win);
+            const int wl = wmask ? __ffs(wmask) - 1 : 0;
+            const int wj = (int)((m1 & 0xfffffu) >> 5);
+            float ta = 0.f;
+#pragma unroll
+            for (int j = 0; j < kC; ++j) if (j == wj) ta = cang[j];
+            ta = __shfl_sync(0xffffffffu, ta, wl);
+            uint32_t e1 = __shfl_sync(0xffffffffu, b.e1, wl), e2 = kNoEntry;
+            if (!wmask) e1 = kNoEntry;
+            if (needSecond) {
+                const uint32_t cand2 = win ? b.k2 : b.k1;
+                const uint32_t m2 = __reduce_min_sync(0xffffffffu, cand2);
+                const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
+                const uint32_t t2 = __shfl_sync(0xffffffffu, win ? b.e2 : b.e1, smask ? __ffs(smask) - 1 : 0);
+                if (smask) e2 = t2;
+            }
+            const bool accept = decide_query(P, e1, e2);
+            if (lane == 0) {
+                const int q = q0 + i;
+                const bool has1 = e1 != kNoEntry;
+                P.qResult[q] = accept ? (int)(e1 & 0x7ffff) : -1;
+                P.qDist[q] = has1 ? (int)(e1 >> 23) : 256;
+                P.qBin[q] = (accept && P.checkOri) ? rot_bin(qa, ta) : -1;
+            }
+            if (accept && win && occupies) { blk |= 1u << wj; P.occ[e1 & 0x7ffff] = 1; }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kNodeWarps * 32) k_search_nodes(const SearchParams P) {
+    const int lane = threadIdx.x & 31;
+    const int node = blockIdx.x * kNodeWarps + (threadIdx.x >> 5);
+    unsigned long long nEval = 0;
+    if (node < P.nNodes) {
+        const int2 qr = P.nodeQ[node];
+        const int2 run = P.qrun[qr.x];
+        const FrameDev& T = P.tgt;
+        const uint4* drows = reinterpret_cast<const uint4*>(T.desc);
+        const uint4* qrows = reinterpret_cast<const uint4*>(P.qdescBase);
+        volatile uint8_t* occV = P.occ;
+        const bool needSecond = rule_needs_second(P.rule);
+        const int len = run.y - run.x;
+        if (len <= 32) bow_node_regs<1>(P, qr, run, nEval);
+        else if (len <= 64) bow_node_regs<2>(P, qr, run, nEval);
+        else if (len <= 128) bow_node_regs<4>(P, qr, run, nEval);
+        else {
+            // very long run: candidates re-read per query (L1 / L2), occupancy through memory
+            for (int q = qr.x; q < qr.y; ++q) {
+                const int src = P.qsrc[q];
+                const uint4 qa4 = qrows[2 * src], qb4 = qrows[2 * src + 1];
+                const uint32_t qd[8] = {qa4.x, qa4.y, qa4.z, qa4.w, qb4.x, qb4.y, qb4.z, qb4.w};
+                Best b; b.k1 = b.k2 = 0xffffffffu; b.e1 = b.e2 = kNoEntry;
+                for (int p = lane; p < len; p += 32) {
+                    const int idx = P.bowIdx[run.x + p];
+                    if (P.elig && P.elig[idx] == 0) continue;
+                    const int d = hamming8(qd, drows[2 * idx], drows[2 * idx + 1]);
+                    ++nEval;
+                    if (occV[idx] != 0) continue;
+                    best_update(b, ((uint32_t)d << 20) | (uint32_t)p, pack_entry(d, __float_as_int(T.kp4[idx].w), idx));
+                }
+                const uint32_t m1 = __reduce_min_sync(0xffffffffu, b.k1);
+                const bool win = (b.k1 == m1) && (m1 != 0xffffffffu);
+                const unsigned wmask = __ballot_sync(0xffffffffu, win);
+                uint32_t e1 = kNoEntry, e2 = kNoEntry;
+                if (wmask) e1 = __shfl_sync(0xffffffffu, b.e1, __ffs(wmask) - 1);
+                if (needSecond) {
+                    const uint32_t cand2 = win ? b.k2 : b.k1;
+                    const uint32_t m2 = __reduce_min_sync(0xffffffffu, cand2);
+                    const unsigned smask = __ballot_sync(0xffffffffu, cand2 == m2 && m2 != 0xffffffffu);
+                    if (smask) e2 = __shfl_sync(0xffffffffu, win ? b.e2 : b.e1, __ffs(smask) - 1);
+                }
+                if (lane == 0) { commit_query(P, T, q, e1, e2, P.checkOri ? P.qangle[q] : 0.f, P.occ, nullptr, nullptr); __threadfence_block(); }
+                __syncwarp();
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nEval += __shfl_xor_sync(0xffffffffu, nEval, o);
+    if (lane == 0 && nEval) atomicAdd(P.evals, nEval);
+    if (!P.checkOri) return;
+    // last CTA done: rotation-consistency filter over all queries (results of the other CTAs are visible after the fence)
+    __shared__ int isLast;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) isLast = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!isLast) return;
+    __threadfence();
+    rot_filter_cta(P.nq, P.qBin, P.qResult, true);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -144,6 +144,38 @@ def test_search_by_bow(M, pair, ratio):
     K1.close(); K2.close()
 
 
+@pytest.mark.parametrize("bits", [2, 4, 6])
+def test_search_by_bow_node_parallel_paths(M, pair, bits):
+    """M4a / M4b run one warp per shared node (k_search_nodes).  bits = 2: four nodes with runs of ~250 features (the
+    memory path for runs > 32), bits = 4: runs around the 32-candidate boundary, bits = 6: the register path.  A side-2
+    vector that lists one feature under two nodes must take the single-CTA path and still match the oracle."""
+    (k1, d1), (k2, d2), bounds, _ = pair
+    rng = np.random.default_rng(77 + bits)
+    fv1, fv2 = sc.feat_vec(d1, bits), sc.feat_vec(d2, bits)
+    e1 = (rng.random(len(k1)) < 0.85).astype(np.uint8)
+    e2 = (rng.random(len(k2)) < 0.85).astype(np.uint8)
+    K1, K2 = M.frame(k1, d1, bounds), M.frame(k2, d2, bounds)
+    nodes2, off2, idx2 = fv2
+    dup_idx = np.concatenate([idx2[:off2[1]], idx2[off2[-2]:off2[-2] + 3], idx2[off2[1]:]]).astype(np.int32)   # first node also lists three
+    dup_off = off2.copy(); dup_off[1:] += 3                                                                    # features of the last one
+    fv2_dup = (nodes2, dup_off.astype(np.int32), dup_idx)
+    M.mfNNratio = 0.8
+    total = 0
+    for ori in (True, False):
+        M.mbCheckOrientation = ori
+        for fvb in (fv2, fv2_dup):
+            nm, mf = M.SearchByBoW_KF_Frame(K1, fv1, e1, K2, fvb)
+            onm, omf = om.search_bow_kf_frame(k1, d1, fv1, e1, k2, d2, fvb, 0.8, ori)
+            assert nm == onm and np.array_equal(mf, omf)
+            nm2, m12 = M.SearchByBoW_KF_KF(K1, fv1, e1, K2, fvb, e2)
+            onm2, om12 = om.search_bow_kf_kf(k1, d1, fv1, e1, k2, d2, fvb, e2, 0.8, ori)
+            assert nm2 == onm2 and np.array_equal(m12, om12)
+            total += onm + onm2
+    assert total > 100
+    M.mfNNratio, M.mbCheckOrientation = 0.9, True
+    K1.close(); K2.close()
+
+
 @pytest.mark.parametrize("coarse", [False, True])
 def test_search_for_triangulation(M, pair, coarse):
     """M6: last minimum wins, epipole rejection, Pinhole epipolar constraint with the caller's F12."""
