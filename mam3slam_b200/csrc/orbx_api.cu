@@ -261,7 +261,7 @@ int configureShape(Extractor* E, int W, int H) {
                 if (std::min(taps[G.tabX + last].ofs + 1, P.w - 1) - taps[G.tabX + x].ofs > 7) ok = false;
             }
             E->pyrFast[l] = ok;
-            // box of the TMA-staged resize: the exact source extent of a 128 x 32 destination tile, from the tap tables
+            // box of the TMA-staged resize: the exact source extent of a 128 x 64 destination tile, from the tap tables
             E->pyrBox[l] = PyrBox{0, 0};
             if (ok) {
                 int ex = 0, ey = 0;
@@ -271,14 +271,17 @@ int configureShape(Extractor* E, int W, int H) {
                     const int end = (taps[G.tabX + lastGroup].ofs & ~3) + 11;       // the third word a thread reads
                     ex = std::max(ex, end - start + 1);
                 }
-                for (int Y0 = 0; Y0 < G.h; Y0 += 32) {
-                    const int Yl = std::min(Y0 + 31, G.h - 1);
+                for (int Y0 = 0; Y0 < G.h; Y0 += kPrTileH) {
+                    const int Yl = std::min(Y0 + kPrTileH - 1, G.h - 1);
                     const int gy = std::min(std::max(taps[G.tabY + Y0].ofs, 0), P.h - 1);
                     const int last = std::min(std::max(taps[G.tabY + Yl].ofs + 1, 0), P.h - 1);
                     ey = std::max(ey, last - gy + 1);
                 }
+                bool rowsPlain = true;      // k_pyr_level_tma walks the source rows s0, s0 + 1: no clamped row taps (never for a scale > 1)
+                for (int y = 0; y < G.h; ++y)
+                    if (taps[G.tabY + y].ofs < 0 || taps[G.tabY + y].ofs + 1 > P.h - 1 || (y && taps[G.tabY + y].ofs < taps[G.tabY + y - 1].ofs)) rowsPlain = false;
                 const int bw = (ex + 15) & ~15;
-                if (bw <= 256 && ey <= 256 && (size_t)bw * ey <= 40 * 1024) E->pyrBox[l] = PyrBox{bw, ey};
+                if (rowsPlain && bw <= 256 && ey <= 256 && (size_t)bw * ey <= 40 * 1024) E->pyrBox[l] = PyrBox{bw, ey};
             }
         }
         E->blurTiles.start[l] = tileStart;
@@ -510,8 +513,8 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         if (ptma && l == 1) ptma = encodeLevelMap(&pm, l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride, E->pyrBox[1].boxH, E->pyrBox[1].boxW);
         else if (ptma) ptma = E->pyrMaps.tmaOk[l] != 0;
         if (ptma) {
-            dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + 8 * kPyrRows - 1) / (8 * kPyrRows), n);
-            k_pyr_level_tma<<<fgrid, block, (size_t)E->pyrBox[l].boxW * E->pyrBox[l].boxH, st>>>(pm, E->dGeom, l, E->dTaps, E->pyrBox[l], fb);
+            dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + kPrTileH - 1) / kPrTileH, n);
+            k_pyr_level_tma<<<fgrid, 256, (size_t)E->pyrBox[l].boxW * E->pyrBox[l].boxH, st>>>(pm, E->dGeom, l, E->dTaps, E->pyrBox[l], fb);
         } else if (E->pyrFast[l] && srcAligned) {
             dim3 fgrid((g.lv[l].w + 127) / 128, (g.lv[l].h + 8 * kPyrRows - 1) / (8 * kPyrRows), n);
             k_pyr_level_fast<<<fgrid, block, 0, st>>>(E->dGeom, l0, l, E->dTaps, fb);

@@ -630,14 +630,19 @@ __global__ void __launch_bounds__(kDtWarps * 32) k_orient_brief_tma(const __grid
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// E1, TMA-staged variant of k_pyr_level_fast (same arithmetic: cv::resize INTER_LINEAR in 11-bit fixed point, see there;
-// src/ORBextractor.cc:1170-1195).  A CTA produces a 128 x 32 tile of level l; the source region its taps touch (known exactly
-// from the tap tables: the host sizes the box per level, PyrBox) arrives as ONE 3-D TMA tile of level l-1, and every thread's
-// three source words per row come from shared memory instead of three dependent global loads with clamped indices.  A tap
-// never selects a byte beyond the source row (the tables clamp), so the zero fill / neighbouring bytes that replace the
-// clamped duplicate words are never selected: bit-identical.
-// grid (ceil(w/128), ceil(h/32), B), block (32, 8); dynamic smem = boxW * boxH.
+// E1, TMA-staged pyramid level (same arithmetic as k_pyr_level_fast: cv::resize INTER_LINEAR in 11-bit fixed point, see there;
+// src/ORBextractor.cc:1170-1195).  A CTA produces a 128 x 64 tile of level l; the source region its taps touch (known exactly
+// from the tap tables: the host sizes the box per level, PyrBox) arrives as ONE 3-D TMA tile of level l-1.  A tap never
+// selects a byte beyond the source row (the tables clamp), so the zero fill / neighbouring bytes that stand where the clamped
+// duplicate words would be are never selected: bit-identical.
+// A warp owns 128 columns x 8 output rows and walks the SOURCE rows it needs top to bottom: each source row gets its
+// horizontal pass exactly once (3 LDS, 2 SHF and per pixel PRMT + IDP.2A + 2 bit ops), the previous row's result stays in
+// registers, and an output row is emitted whenever the walk reaches its lower tap row - a warp-uniform test, so there is no
+// per-row reuse bookkeeping; the eight row taps of the warp sit in lanes 0-7 and are broadcast by shuffles (the first TMA
+// version spent 44 instructions per pixel, most of them on bookkeeping and tap reloads; this one ~12).
+// grid (ceil(w/128), ceil(h/64), B), block 256; dynamic smem = boxW * boxH.
 struct PyrBox { int boxW, boxH; };
+constexpr int kPrTileH = 64, kPrRowsPerWarp = 8;
 
 __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ CUtensorMap srcMap, const DevGeom* __restrict__ g, int l,
                                                        const ResizeTap* __restrict__ taps, PyrBox pb, int frameBase) {
@@ -646,11 +651,11 @@ __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ C
     const LevelGeom& D = g->lv[l];
     const LevelGeom& S = g->lv[l - 1];
     const int frame = frameBase + blockIdx.z;
-    const int X0 = blockIdx.x * 128, Y0 = blockIdx.y * 32;
+    const int X0 = blockIdx.x * 128, Y0 = blockIdx.y * kPrTileH;
     // tile origin in the source level: first tap of the CTA's first column (16-byte aligned) / first row (clamped like the taps)
     const int gx = taps[D.tabX + X0].ofs & ~15;
     const int gy = min(max(taps[D.tabY + Y0].ofs, 0), S.h - 1);
-    const int tid = threadIdx.y * 32 + threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t bar = smem_addr(&mbar);
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
@@ -661,14 +666,15 @@ __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ C
                      : "memory");
     }
     __syncthreads();                                           // the barrier object is initialised before anyone polls it
-    const int x4 = X0 + threadIdx.x * 4;
-    const int yb = Y0 + threadIdx.y * kPyrRows;
-    const bool active = x4 < D.w && yb < D.h;
+    // lanes right of the level keep walking with the last column group (the row taps are exchanged by full-warp shuffles) and store nothing
+    const int x4 = min(X0 + lane * 4, (D.w - 1) & ~3);
+    const int yb = Y0 + warp * kPrRowsPerWarp;
+    const int yEnd = min(yb + kPrRowsPerWarp, D.h);
+    const bool active = yb < D.h;                               // warp-uniform
     uint32_t coef[4], sel[4];
     int wofs = 0, sh = 0;
     if (active) {                                              // per-thread column setup overlaps the tile's flight
-        const ResizeTap t0 = taps[D.tabX + x4];
-        const int a0 = t0.ofs;
+        const int a0 = taps[D.tabX + x4].ofs;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const ResizeTap t = taps[D.tabX + min(x4 + k, D.w - 1)];
@@ -686,45 +692,42 @@ __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ C
                          : "=r"(done) : "r"(bar), "r"(0) : "memory");
     }
     if (!active) return;
-    uint8_t* dst = g->lvl[l] + (size_t)frame * D.planeBytes;
     const int rowW = pb.boxW >> 2;
-    const uint32_t* tw = reinterpret_cast<const uint32_t*>(ptile) + wofs;
-    uint32_t hA[4], hB[4];
-    int rA = -1, rB = -1;
-    auto hrow = [&](int r, uint32_t (&h)[4]) {
-        const uint32_t* rowp = tw + (r - gy) * rowW;
-        const uint32_t W0 = rowp[0], W1 = rowp[1], W2 = rowp[2];
-        const uint32_t lo = __funnelshift_r(W0, W1, sh), hi = __funnelshift_r(W1, W2, sh);
+    const int nrows = yEnd - yb;
+    // lane j keeps the vertical tap of output row yb + j (the host admits only levels whose row taps never clamp: s1 = s0 + 1)
+    const ResizeTap myT = taps[D.tabY + min(yb + (lane & (kPrRowsPerWarp - 1)), D.h - 1)];
+    const uint32_t myC = (uint32_t)(uint16_t)myT.c0 | ((uint32_t)(uint16_t)myT.c1 << 16);
+    const int pitch = D.pitch;
+    int fullI, wLeft;                                          // pinned in registers: the compiler otherwise recomputes them from tid / ctaid per row
+    asm volatile("mov.u32 %0, %1;" : "=r"(fullI) : "r"((int)(X0 + lane * 4 + 3 < D.w)));
+    asm volatile("mov.u32 %0, %1;" : "=r"(wLeft) : "r"(X0 + lane * 4 < D.w ? D.w - x4 : 0));
+    uint8_t* d = g->lvl[l] + (size_t)frame * D.planeBytes + (size_t)yb * pitch + x4;
+    int r = __shfl_sync(0xffffffffu, myT.ofs, 0) - 1;          // the walk computes row r + 1 next
+    const uint32_t* rowp = reinterpret_cast<const uint32_t*>(ptile) + wofs + (r - gy) * rowW;
+    uint32_t h[4] = {0, 0, 0, 0}, hPrev[4] = {0, 0, 0, 0};
+    for (int j = 0; j < nrows; ++j) {
+        const int s1 = __shfl_sync(0xffffffffu, myT.ofs, j) + 1;
+        const uint32_t cc = __shfl_sync(0xffffffffu, myC, j);
+#pragma unroll 1
+        while (r < s1) {                                        // horizontal pass of the next source row: (p[a]*c0 + p[a1]*c1) & ~15
+            ++r; rowp += rowW;
+            const uint32_t W0 = rowp[0], W1 = rowp[1], W2 = rowp[2];
+            const uint32_t lo = __funnelshift_r(W0, W1, sh), hi = __funnelshift_r(W1, W2, sh);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t hk = __dp2a_lo(coef[k], __byte_perm(lo, hi, sel[k]), 0u);     // p[a]*c0 + p[a1]*c1
-            h[k] = (hk << 12) & 0xffff0000u;                                             // (hk >> 4) << 16
+            for (int k = 0; k < 4; ++k) {
+                hPrev[k] = h[k];
+                h[k] = __dp2a_lo(coef[k], __byte_perm(lo, hi, sel[k]), 0u) & 0xfffffff0u;
+            }
         }
-    };
-#pragma unroll
-    for (int j = 0; j < kPyrRows; ++j) {
-        const int y = yb + j;
-        if (y >= D.h) break;
-        const ResizeTap ty = taps[D.tabY + y];
-        const int s0 = min(max(ty.ofs, 0), S.h - 1), s1 = min(max(ty.ofs + 1, 0), S.h - 1);
-        if (s0 == rB) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) hA[k] = hB[k];
-            rA = rB; rB = -1;
-        } else if (s0 != rA) { hrow(s0, hA); rA = s0; }
-        if (s1 == rA) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) hB[k] = hA[k];
-            rB = rA;
-        } else if (s1 != rB) { hrow(s1, hB); rB = s1; }
-        const uint32_t b0 = (uint32_t)ty.c0, b1 = (uint32_t)ty.c1;
+        // ((b0 * (hA >> 4)) >> 16) + ((b1 * (hB >> 4)) >> 16) with h = 16 * (h >> 4) and b << 12: one IMAD.HI each
+        const uint32_t b0 = (cc & 0xffffu) << 12, b1 = (cc >> 16) << 12;
         uint32_t v[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) v[k] = (__umulhi(hA[k], b0) + __umulhi(hB[k], b1) + 2u) >> 2;
+        for (int k = 0; k < 4; ++k) v[k] = (__umulhi(h[k], b1) + (__umulhi(hPrev[k], b0) + 2u)) >> 2;
         const uint32_t packed = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
-        uint8_t* d = dst + (size_t)y * D.pitch + x4;
-        if (x4 + 3 < D.w) *reinterpret_cast<uint32_t*>(d) = packed;
-        else for (int k = 0; k < 4 && x4 + k < D.w; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+        if (fullI) *reinterpret_cast<uint32_t*>(d) = packed;
+        else for (int k = 0; k < 4 && k < wLeft; ++k) d[k] = (uint8_t)(packed >> (8 * k));
+        d += pitch;
     }
 }
 

@@ -1,18 +1,12 @@
 #!/bin/bash
-# quick GPU check: extractor + matcher parity, bench line
+# extractor parity + a short bench (stage times) after a kernel change
 mkdir -p gpurun_out
-timeout 400 python -m pytest tests -x -q -m gpu --timeout 90 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
-tail -12 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py --no-cpu > gpurun_out/bench_quick.json 2> gpurun_out/bench_quick.err; echo "bench exit $?"
+timeout 1500 python -m pytest tests/test_extractor_gpu.py tests/test_extractor_vs_ref_gpu.py tests/test_env_switches_gpu.py -x -q -m gpu > gpurun_out/quick_tests.log 2>&1; echo "tests rc $?"; tail -3 gpurun_out/quick_tests.log
+timeout 900 python bench.py --steps 10 --warmup 3 --no-kitti --no-knn --no-sparse --no-cpu > gpurun_out/quick_bench.json 2> gpurun_out/quick_bench.err; echo "bench rc $?"; tail -3 gpurun_out/quick_bench.err
 python - <<'PY'
 import json
-d = json.load(open('gpurun_out/bench_quick.json'))
-print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/step', round(d['ms_per_step'], 3))
-print({k: round(v, 4) for k, v in d['roofline']['stage_ms_per_batch'].items()})
-print('knn ms', d.get('hamming', {}).get('knn', {}).get('ms'))
-print('latency', d.get('latency'))
-print('kitti', {k: (round(v, 3) if isinstance(v, float) else v) for k, v in (d.get('kitti') or {}).items() if k != 'workload'})
+d=json.load(open('gpurun_out/quick_bench.json'))
+print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/step', round(d['ms_per_step'],3))
+print(d['roofline'].get('stage_ms_per_batch'))
+print({k:v for k,v in d['latency'].items() if k!='search_members'})
 PY
-tail -3 gpurun_out/bench_quick.err
-[ -x tools/microbench ] && [ -n "$MICRO" ] && tools/microbench > gpurun_out/microbench.txt && tail -8 gpurun_out/microbench.txt
-true
