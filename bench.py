@@ -438,41 +438,68 @@ def knn_bench(args, torch, dist, rank, world, local):
     md_dev = torch.empty((NQ, K), dtype=torch.int16, device="cuda")
     mi_dev = torch.empty((NQ, K), dtype=torch.int32, device="cuda")
 
-    def step():
+    def step_nccl():
         m.knn_device(D, q.data_ptr(), NQ, K, dd.data_ptr(), di.data_ptr(), st)
-        if world > 1:                  # the complete sharded search: local top-k, one all-gather, k-way merge on every rank
+        if world > 1:                  # the library-collective form: local top-k, one NCCL all-gather, k-way merge on every rank
             dist.all_gather_into_tensor(gath, out)
             m.knn_merge_device(gath.data_ptr() + nb_i, gath.data_ptr(), nb_i + nb_d, world, NQ, K, md_dev.data_ptr(),
                                mi_dev.data_ptr(), st)
 
-    for _ in range(3):
-        step()
-    torch.cuda.synchronize()
+    # the product path on N > 1 GPUs: the scan kernel stores its merged lists into every rank's exchange buffer over NVLink peer
+    # stores and the merge kernel waits for the arrival counters (orbm_knn_sharded): no collective call at all
+    xchg = None
+    xd_dev = torch.empty((NQ, K), dtype=torch.int16, device="cuda")
+    xi_dev = torch.empty((NQ, K), dtype=torch.int32, device="cuda")
     if world > 1:
+        from mam3slam_b200.matcher import KnnExchange
+
+        def gather(b):
+            outl = [None] * world
+            dist.all_gather_object(outl, b)
+            return outl
+        xchg = KnnExchange(m, rank, world, NQ, K).connect(gather)
         dist.barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    iters = 10
-    e0.record()
-    for _ in range(iters):
-        step()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms = float(ms.item())
+
+    def step_peer():
+        m.knn_sharded(xchg, D, q.data_ptr(), NQ, K, xd_dev.data_ptr(), xi_dev.data_ptr(), st)
+
+    def timed(step):
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 10
+        e0.record()
+        for _ in range(iters):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms_nccl = timed(step_nccl)
+    ms = timed(step_peer) if world > 1 else ms_nccl
     # correctness of the merged result on rank 0: the planted neighbour (distance 1) is found for every query
     if world > 1:
         md, mi = ORBmatcher.knn_merge(torch.stack(gath_d).cpu().numpy().view(np.uint16).reshape(world, NQ, K), torch.stack(gath_i).cpu().numpy())
         if not (np.array_equal(md, md_dev.cpu().numpy().view(np.uint16)) and np.array_equal(mi, mi_dev.cpu().numpy())):
             raise SystemExit("bench.py: device merge of the sharded k-NN lists differs from the host merge")
+        if xchg.status() != 0 or not (np.array_equal(md, xd_dev.cpu().numpy().view(np.uint16)) and np.array_equal(mi, xi_dev.cpu().numpy())):
+            raise SystemExit("bench.py: peer-exchange sharded k-NN differs from the all-gather + host merge")
     else:
         md, mi = dd.cpu().numpy().view(np.uint16), di.cpu().numpy()
     ok = bool((md[:, 0] <= 1).all())
     evals = float(NDB) * NQ
     eps = evals / (ms * 1e-3)
-    out = {"workload": f"brute-force k-NN {NDB} x {NQ}, k={K}, db rows sharded over {world} GPU(s), one all-gather + device merge inside the timed step",
-           "ms": ms, "evaluations_per_s": eps, "planted_neighbours_found": ok,
+    out = {"workload": f"brute-force k-NN {NDB} x {NQ}, k={K}, db rows sharded over {world} GPU(s)" +
+                       ("; exchange of the per-rank lists by NVLink peer stores from the scan kernel + merge kernel waiting on arrival "
+                        "counters (orbm_knn_sharded), all inside the timed step" if world > 1 else ""),
+           "ms": ms, "ms_nccl_allgather_variant": ms_nccl if world > 1 else None,
+           "evaluations_per_s": eps, "planted_neighbours_found": ok,
            "roofline_int": {"bound": "popc", "popc_issued_per_evaluation": 4, "achieved_popc_per_s": 4 * eps,
                             "peak_popc_per_s": POPC_PEAK * world, "frac": 4 * eps / (POPC_PEAK * world),
                             "popc8_equivalent_frac": 8 * eps / (POPC_PEAK * world),
@@ -494,6 +521,8 @@ def knn_bench(args, torch, dist, rank, world, local):
                                "sample": f"{sub} x {NQ} of the same rows / queries, k={K}, oracle/cpp popcount scan "
                                          "(ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:2058-2074, in a strict-< k-NN loop)",
                                "extrapolated_full_search_s": NDB * NQ / (sub * NQ / dt)}
+    if xchg is not None:
+        xchg.close()
     D.close(); m.close()
     return out
 
@@ -509,6 +538,12 @@ def run_gpu(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference)")
     torch.cuda.set_device(local)
+    # host placement: this rank's threads and pinned staging buffers go to the NUMA node of its GPU (mam3slam_b200/numa.py);
+    # the original CPU mask comes back before the CPU baselines run.  BENCH_NUMA=0 switches it off (A/B).
+    from mam3slam_b200 import numa
+    cpu_mask0 = os.sched_getaffinity(0)
+    placement = (numa.bind_to_device_node(local) if os.environ.get("BENCH_NUMA", "1") != "0"
+                 else {"bound": False, "node": None, "cpus": 0, "reason": "BENCH_NUMA=0"})
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -667,10 +702,31 @@ def run_gpu(args):
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
 
-    tms = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    # ---- e2e ceiling: the same pinned 23.1 MB batches, host -> device copies ONLY, every rank at once ----
+    # What the end-to-end figure could reach if kernels and result copies were free: PCIe plus host-memory bandwidth shared by
+    # all ranks of the node.  Same streams and the same alternation over the input sets as the e2e leg.
+    land = [torch.empty((B, H, W), dtype=torch.uint8, device="cuda") for _ in range(epipes)]
+    host_sets = [host_t[s * B:(s + 1) * B] for s in range(nsets)]
+    def h2d_only(count):
+        for i in range(count):
+            with torch.cuda.stream(pipes[i % epipes]["ts"]):
+                land[i % epipes].copy_(host_sets[i % nsets], non_blocking=True)
+        torch.cuda.synchronize()
+    h2d_only(2 * epipes)
+    barrier()
+    t0 = time.perf_counter()
+    h2d_only(args.steps * bps)
+    h2d_s = time.perf_counter() - t0
+    del land
+    os.sched_setaffinity(0, cpu_mask0)
+
+    tms = torch.tensor([ms, e2e_s * 1e3, h2d_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms, e2e_ms = tms.tolist()
+    ms, e2e_ms, h2d_ms = tms.tolist()
+    bound = torch.tensor([1.0 if placement["bound"] else 0.0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(bound, op=dist.ReduceOp.SUM)
     total_frames = B * bps * args.steps * world
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
@@ -698,7 +754,13 @@ def run_gpu(args):
                                     "(tracking of batch i overlaps extraction of batch i+1)") if npipes > 1 else "serial, one stream",
                          "e2e": f"{epipes} host threads, one handle pair each, take alternating batches; every call is synchronous"},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
-                    "h2d_bytes_per_step": int(bps * B * W * H), "d2h_bytes_per_step": int(bps * B * (cap * 60 + 8 + stride * 4 + 4))},
+                    "h2d_bytes_per_step": int(bps * B * W * H), "d2h_bytes_per_step": int(bps * B * (cap * 60 + 8 + stride * 4 + 4)),
+                    "ceiling_frames_per_s": total_frames / (h2d_ms * 1e-3),
+                    "ceiling_h2d_gbs": total_frames * W * H / (h2d_ms * 1e-3) / 1e9,
+                    "ceiling_note": "the same pinned batches copied host -> device and nothing else, all ranks at once, max over ranks "
+                                    "(PCIe + host memory shared by the node's ranks); value / ceiling = how much of the link the "
+                                    "end-to-end path uses",
+                    "host_placement": {"ranks_bound_to_gpu_numa_node": int(bound.item()), "rank0": placement}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",

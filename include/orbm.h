@@ -204,6 +204,31 @@ int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq
 int orbm_knn_merge_device(orbm_handle h, const void* d_dist, const void* d_idx, size_t shard_stride_bytes, int nshards, int nq,
                           int k, uint16_t* d_out_dist, int32_t* d_out_idx, void* stream);
 
+/* ---- sharded k-NN over peer memory (map-sharded search of SURVEY.md 8e; the reference is one CPU process with one address
+ * space and has no counterpart) ------------------------------------------------------------------------------------------
+ * One process per GPU; rank r holds rows [row_offset, row_offset + n) of the database (orbm_db) and a replica of the queries.
+ * orbm_knn_sharded = local scan + all-gather + merge, with the exchange done BY the kernels: the scan kernel stores every
+ * finished query block of merged (distance, global row) keys straight into every rank's exchange buffer over NVLink peer
+ * stores and bumps that rank's arrival counter; a second kernel waits for all counters and merges.  No NCCL call, no host
+ * synchronisation.  The result equals the unsharded search bit for bit (same (distance, row) rule).
+ *
+ * Setup: every rank creates its buffer, the 64-byte CUDA IPC handles are exchanged by whatever the host has (the Python mirror
+ * uses torch.distributed.all_gather_object), every rank opens every other rank's handle.  orbm_xchg_open_local links two
+ * buffers of ONE process instead (several GPUs driven by one process, or two handles on one GPU in the tests).
+ * Collective semantics: every rank must call orbm_knn_sharded the same number of times with the same nq and k.  A rank that
+ * never arrives does not hang the GPU: the merge gives up after ORBM_XCHG_TIMEOUT_MS (default 4000), writes "no neighbour"
+ * (-1 / 65535) and raises orbm_xchg_status(). */
+typedef struct orbm_xchg_s* orbm_xchg;
+#define ORBM_XCHG_HANDLE_BYTES 64
+int orbm_xchg_create(orbm_handle h, int rank, int world, int max_nq, int max_k, orbm_xchg* out);
+int orbm_xchg_ipc_handle(orbm_xchg x, void* handle64);
+int orbm_xchg_open(orbm_xchg x, int peer_rank, const void* handle64);
+int orbm_xchg_open_local(orbm_xchg x, int peer_rank, orbm_xchg peer);
+int orbm_xchg_status(orbm_xchg x);            /* 0 = fine, 1 = a merge timed out waiting for a rank */
+void orbm_xchg_destroy(orbm_xchg x);
+int orbm_knn_sharded(orbm_handle h, orbm_xchg x, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist,
+                     int32_t* d_idx, void* stream);
+
 /* replaces the selection in MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:366-396) for a batch of map
  * points: descriptors of point p are rows [off[p], off[p+1]); best[p] = row (relative) with the least median distance */
 int orbm_distinctive_descriptors(orbm_handle h, const uint8_t* desc, const int* off, int npoints, int* best);

@@ -53,6 +53,9 @@ typedef struct orbx_keypoint {
 } orbx_keypoint;
 
 int orbx_device_count(void);
+/* PCI bus id of a device ("0000:1b:00.0"), for hosts that bind an agent's threads and pinned staging buffers to the NUMA
+ * node its GPU hangs off (mam3slam_b200/numa.py; the reference runs on the CPU and has no counterpart).  out: >= 16 bytes */
+int orbx_device_pci_bus_id(int device, char* out, int len);
 const char* orbx_strerror(int status);
 const char* orbx_last_error(orbx_handle h);
 

@@ -31,6 +31,8 @@ def lib():
     vp, i32, f32, u64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t
     ip = C.POINTER(C.c_int)
     L.orbx_device_count.restype = i32
+    L.orbx_device_pci_bus_id.restype = i32
+    L.orbx_device_pci_bus_id.argtypes = [i32, C.c_char_p, i32]
     L.orbx_strerror.restype = C.c_char_p
     L.orbx_strerror.argtypes = [i32]
     L.orbx_last_error.restype = C.c_char_p
@@ -120,6 +122,14 @@ def _bind_matcher(L):
     L.orbm_db_destroy.restype = None
     L.orbm_knn.argtypes = [vp, vp, vp, i32, i32, vp, vp]
     L.orbm_knn_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
+    L.orbm_xchg_create.argtypes = [vp, i32, i32, i32, i32, C.POINTER(vp)]
+    L.orbm_xchg_ipc_handle.argtypes = [vp, vp]
+    L.orbm_xchg_open.argtypes = [vp, i32, vp]
+    L.orbm_xchg_open_local.argtypes = [vp, i32, vp]
+    L.orbm_xchg_status.argtypes = [vp]
+    L.orbm_xchg_destroy.argtypes = [vp]
+    L.orbm_xchg_destroy.restype = None
+    L.orbm_knn_sharded.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp]
     L.orbm_knn_device_static.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
     L.orbm_debug_alloc_count.restype = C.c_longlong
     L.orbm_debug_alloc_count.argtypes = []
@@ -164,3 +174,10 @@ def check(status, handle=None, what=""):
 def device_count():
     """Number of CUDA devices the library sees (0 on a CPU-only host)."""
     return int(lib().orbx_device_count())
+
+
+def device_pci_bus_id(device):
+    """PCI bus id of a CUDA device, lower case ("0000:1b:00.0")."""
+    buf = C.create_string_buffer(32)
+    check(lib().orbx_device_pci_bus_id(int(device), buf, 32), None, "orbx_device_pci_bus_id")
+    return buf.value.decode().lower()

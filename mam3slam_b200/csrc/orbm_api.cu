@@ -55,6 +55,7 @@ struct orbm_matcher {
     void* pinned = nullptr; size_t pinnedBytes = 0;
     unsigned long long* dEvals = nullptr;
     unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
+    unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
     void* trackBuf = nullptr; size_t trackBytes = 0;
 };
 
@@ -65,6 +66,14 @@ namespace {
         cudaError_t e_ = (call);                                                                   \
         if (e_ != cudaSuccess) {                                                                   \
             M->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return ORBM_ERR_CUDA;                                                                  \
+        }                                                                                          \
+    } while (0)
+#define CKM_(MM, call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            (MM)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
             return ORBM_ERR_CUDA;                                                                  \
         }                                                                                          \
     } while (0)
@@ -214,6 +223,7 @@ void orbm_destroy(orbm_handle M) {
     if (M->pinned) cudaFreeHost(M->pinned);
     if (M->dEvals) cudaFree(M->dEvals);
     if (M->knnPart) cudaFree(M->knnPart);
+    if (M->knnCounter) cudaFree(M->knnCounter);
     if (M->trackBuf) cudaFree(M->trackBuf);
     cudaStreamDestroy(M->stream);
     delete M;
@@ -880,6 +890,58 @@ void orbm_db_destroy(orbm_handle M, orbm_db db) {
     delete db;
 }
 
+namespace {
+
+// chunking of a k-NN scan: about 4 resident CTAs per SM over all query blocks.  Chunks are NOT rounded to whole 128-row tiles
+// (the last tile of a chunk may be partial; rows are 32 bytes, so any row offset keeps the 16-byte alignment of the bulk copies):
+// rounding left e.g. 560 CTAs for 148 SMs on a 125 k-row shard - 3.8 per SM, the time of 4.
+struct KnnPlan { int qblocks, nchunks; long long rowsPerChunk; };
+KnnPlan knnPlan(const orbm_matcher* M, long long n, int nq, int qpt) {
+    KnnPlan P;
+    P.qblocks = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
+    const long long target = std::max<long long>(1, ((long long)M->smCount * 4) / P.qblocks);
+    long long rows = (n + target - 1) / target;
+    rows = std::max<long long>(kKnnTileRows, (rows + 3) & ~3LL);
+    rows = std::min<long long>(rows, 1LL << 22);
+    P.rowsPerChunk = rows;
+    P.nchunks = (int)std::max<long long>(1, (n + rows - 1) / rows);
+    return P;
+}
+
+int knnScratch(orbm_matcher* M, const KnnPlan& P, int nq, int k) {
+    const size_t need = (size_t)P.nchunks * nq * k * sizeof(unsigned long long);
+    if (need > M->knnPartBytes) {
+        if (M->knnPart) cudaFree(M->knnPart);
+        M->knnPart = nullptr; M->knnPartBytes = 0;
+        CKM(cMalloc((void**)&M->knnPart, need));
+        M->knnPartBytes = need;
+    }
+    if (P.qblocks > M->knnCounterCap) {
+        if (M->knnCounter) cudaFree(M->knnCounter);
+        M->knnCounter = nullptr; M->knnCounterCap = 0;
+        const int cap = std::max(P.qblocks, 256);
+        CKM(cMalloc((void**)&M->knnCounter, (size_t)cap * sizeof(unsigned int)));
+        CKM(cudaMemset(M->knnCounter, 0, (size_t)cap * sizeof(unsigned int)));
+        M->knnCounterCap = cap;
+    }
+    return ORBM_OK;
+}
+
+void launchKnn(orbm_matcher* M, const KnnPlan& P, int qpt, orbm_db db, const uint8_t* d_q, int nq, int k, const KnnFused& F, cudaStream_t st) {
+    const dim3 grid(P.qblocks, P.nchunks);
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(d_q);
+    if (qpt == 2) {
+        if (F.counter) k_knn<2, 4, true><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+        else k_knn<2, 4, false><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+    } else {
+        if (F.counter) k_knn<1, kKnnMaxK, true><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+        else k_knn<1, kKnnMaxK, false><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+    }
+    ++M->launches;
+}
+
+}  // namespace
+
 int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
     if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
     if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
@@ -888,28 +950,142 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     // two queries per thread when the list is short (registers) and there are enough queries to fill the blocks
     const char* qe = getenv("ORBM_KNN_QPT");
     const int qpt = (k <= 4 && nq >= 2 * kKnnThreads && qe && atoi(qe) == 2) ? 2 : 1;      // measured slower on B200; kept for experiments
-    const int qblocks = (nq + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
-    // chunks: about 4 resident CTAs per SM over all query blocks, each a multiple of the tile, at most 2^23 rows
-    long long target = std::max<long long>(1, ((long long)M->smCount * 4 + qblocks - 1) / qblocks);
-    long long rowsPerChunk = (db->n + target - 1) / std::max<long long>(target, 1);
-    rowsPerChunk = std::max<long long>(kKnnTileRows, (rowsPerChunk + kKnnTileRows - 1) / kKnnTileRows * kKnnTileRows);
-    rowsPerChunk = std::min<long long>(rowsPerChunk, 1LL << 22);
-    const int nchunks = (int)std::max<long long>(1, (db->n + rowsPerChunk - 1) / rowsPerChunk);
-    const size_t need = (size_t)nchunks * nq * k * sizeof(unsigned long long);
-    if (need > M->knnPartBytes) {
-        if (M->knnPart) cudaFree(M->knnPart);
-        M->knnPart = nullptr; M->knnPartBytes = 0;
-        CKM(cMalloc((void**)&M->knnPart, need));
-        M->knnPartBytes = need;
+    const KnnPlan P = knnPlan(M, db->n, nq, qpt);
+    int rc = knnScratch(M, P, nq, k);
+    if (rc) return rc;
+    KnnFused F;
+    memset(&F, 0, sizeof(F));
+    // ORBM_KNN_FUSED=1: the CTA that finishes a query block's last chunk merges the block's lists itself (one launch instead of
+    // two).  Off by default on one GPU: the epilogue costs the scan kernel 7 registers and measured ~2 % slower than scan +
+    // k_knn_merge (7 us); the sharded search always uses it (it is what pushes the lists to the peers).
+    static const bool fused = [] { const char* e = getenv("ORBM_KNN_FUSED"); return e && atoi(e) != 0; }();
+    if (fused) { F.counter = M->knnCounter; F.dist = d_dist; F.idx = d_idx; }
+    launchKnn(M, P, qpt, db, d_q, nq, k, F, st);
+    if (!fused) { k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, P.nchunks, nq, k, d_dist, d_idx); ++M->launches; }
+    M->lastEvals = (long long)nq * db->n;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+// ---- sharded k-NN over peer memory (no counterpart in the reference, which has no GPU and one address space) ----
+// Every rank scans its own shard of the database; the all-gather of the per-rank top-k lists and the final merge are part of
+// the kernels (KnnFused / k_knn_xchg_merge in orbm_kernels.cuh): k_knn stores a finished query block straight into every rank's
+// exchange buffer over NVLink and bumps that rank's arrival counter, k_knn_xchg_merge waits for the counters and merges.
+// Buffer of a rank: keys[2 parities][world][slotKeys] | flags[2][kXchgMaxRanks] | status.  Two parities: a rank can be at most
+// one call ahead of a peer (it needs the peer's arrival of call t to finish call t), so call t + 1 never overwrites what a
+// peer still merges from call t... and call t + 2 reuses the slot of call t only after every peer has started call t + 1.
+struct orbm_xchg_s {
+    orbm_matcher* M = nullptr;
+    int rank = 0, world = 1, maxNq = 0, maxK = 0;
+    size_t slotKeys = 0, flagsOff = 0, bytes = 0;
+    uint8_t* buf = nullptr;                       // this rank's buffer
+    uint8_t* peer[kXchgMaxRanks] = {};            // every rank's buffer as mapped here (peer[rank] == buf)
+    bool ipcOpened[kXchgMaxRanks] = {};
+    unsigned int expect[2] = {0, 0};              // arrivals every counter of a parity has seen once the current call is complete
+    unsigned long long calls = 0;
+};
+
+int orbm_xchg_create(orbm_handle M, int rank, int world, int max_nq, int max_k, orbm_xchg* out) {
+    if (!M || !out || world < 1 || world > kXchgMaxRanks || rank < 0 || rank >= world || max_nq < 1 || max_k < 1 || max_k > kKnnMaxK)
+        return ORBM_ERR_INVALID;
+    CKM(cudaSetDevice(M->device));
+    orbm_xchg_s* X = new orbm_xchg_s();
+    X->M = M; X->rank = rank; X->world = world; X->maxNq = max_nq; X->maxK = max_k;
+    X->slotKeys = (size_t)max_nq * max_k;
+    X->flagsOff = 2 * (size_t)world * X->slotKeys * sizeof(unsigned long long);
+    X->bytes = X->flagsOff + (2 * kXchgMaxRanks + 4) * sizeof(unsigned int);
+    if (cMalloc((void**)&X->buf, X->bytes) != cudaSuccess || cudaMemset(X->buf, 0, X->bytes) != cudaSuccess) {
+        M->err = cudaGetErrorString(cudaGetLastError());
+        delete X;
+        return ORBM_ERR_CUDA;
     }
-    if (qpt == 2)
-        k_knn<2, 4><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n, db->rowOffset,
-                                                                    (int)rowsPerChunk, k, M->knnPart);
-    else
-        k_knn<1, kKnnMaxK><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
-                                                                          db->rowOffset, (int)rowsPerChunk, k, M->knnPart);
-    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx);
-    M->launches += 2;
+    CKM(cudaDeviceSynchronize());
+    X->peer[rank] = X->buf;
+    *out = X;
+    return ORBM_OK;
+}
+
+int orbm_xchg_ipc_handle(orbm_xchg X, void* handle64) {
+    if (!X || !handle64) return ORBM_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == ORBM_XCHG_HANDLE_BYTES, "CUDA IPC handle size");
+    cudaIpcMemHandle_t h;
+    CKM_(X->M, cudaSetDevice(X->M->device));
+    CKM_(X->M, cudaIpcGetMemHandle(&h, X->buf));
+    memcpy(handle64, &h, sizeof(h));
+    return ORBM_OK;
+}
+
+int orbm_xchg_open(orbm_xchg X, int peer_rank, const void* handle64) {
+    if (!X || !handle64 || peer_rank < 0 || peer_rank >= X->world) return ORBM_ERR_INVALID;
+    if (peer_rank == X->rank) return ORBM_OK;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    void* p = nullptr;
+    CKM_(X->M, cudaSetDevice(X->M->device));
+    CKM_(X->M, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    X->peer[peer_rank] = static_cast<uint8_t*>(p);
+    X->ipcOpened[peer_rank] = true;
+    return ORBM_OK;
+}
+
+int orbm_xchg_open_local(orbm_xchg X, int peer_rank, orbm_xchg peer) {
+    if (!X || !peer || peer_rank < 0 || peer_rank >= X->world || peer->rank != peer_rank || peer->world != X->world ||
+        peer->slotKeys != X->slotKeys)
+        return ORBM_ERR_INVALID;
+    if (peer->M->device != X->M->device) {
+        CKM_(X->M, cudaSetDevice(X->M->device));
+        const cudaError_t e = cudaDeviceEnablePeerAccess(peer->M->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { X->M->err = cudaGetErrorString(e); return ORBM_ERR_CUDA; }
+        cudaGetLastError();
+    }
+    X->peer[peer_rank] = peer->buf;
+    return ORBM_OK;
+}
+
+int orbm_xchg_status(orbm_xchg X) {
+    if (!X) return ORBM_ERR_INVALID;
+    unsigned int v = 0;
+    CKM_(X->M, cudaSetDevice(X->M->device));
+    CKM_(X->M, cudaMemcpy(&v, X->buf + X->flagsOff + 2 * kXchgMaxRanks * sizeof(unsigned int), sizeof(v), cudaMemcpyDeviceToHost));
+    return (int)v;
+}
+
+void orbm_xchg_destroy(orbm_xchg X) {
+    if (!X) return;
+    cudaSetDevice(X->M->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < X->world; ++r) if (X->ipcOpened[r]) cudaIpcCloseMemHandle(X->peer[r]);
+    cudaFree(X->buf);
+    delete X;
+}
+
+int orbm_knn_sharded(orbm_handle M, orbm_xchg X, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
+    if (!M || !X || X->M != M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
+    if (nq > X->maxNq || k > X->maxK) { M->err = "orbm_knn_sharded: nq / k beyond the exchange buffer's capacity"; return ORBM_ERR_CAPACITY; }
+    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
+    for (int r = 0; r < X->world; ++r) if (!X->peer[r]) { M->err = "orbm_knn_sharded: a rank's exchange buffer has not been opened"; return ORBM_ERR_INVALID; }
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    const KnnPlan P = knnPlan(M, std::max<long long>(db->n, 1), nq, 1);
+    int rc = knnScratch(M, P, nq, k);
+    if (rc) return rc;
+    const int par = (int)(X->calls & 1);
+    KnnFused F;
+    memset(&F, 0, sizeof(F));
+    F.counter = M->knnCounter; F.world = X->world;
+    for (int r = 0; r < X->world; ++r) {
+        F.peerSlot[r] = reinterpret_cast<unsigned long long*>(X->peer[r]) + ((size_t)par * X->world + X->rank) * X->slotKeys;
+        F.peerFlag[r] = reinterpret_cast<unsigned int*>(X->peer[r] + X->flagsOff) + par * kXchgMaxRanks + X->rank;
+    }
+    launchKnn(M, P, 1, db, d_q, nq, k, F, st);
+    X->expect[par] += (unsigned int)P.qblocks;         // nq is the same on every rank (the queries are replicated), so is qblocks
+    static const unsigned long long timeoutNs = [] { const char* e = getenv("ORBM_XCHG_TIMEOUT_MS"); return (unsigned long long)(e ? atoll(e) : 4000) * 1000000ull; }();
+    const unsigned int* flags = reinterpret_cast<const unsigned int*>(X->buf + X->flagsOff) + par * kXchgMaxRanks;
+    unsigned int* status = reinterpret_cast<unsigned int*>(X->buf + X->flagsOff) + 2 * kXchgMaxRanks;
+    k_knn_xchg_merge<<<(nq + 7) / 8, 256, 0, st>>>(reinterpret_cast<const unsigned long long*>(X->buf) + (size_t)par * X->world * X->slotKeys,
+                                                   X->slotKeys, flags, X->expect[par], X->world, nq, k, d_dist, d_idx, status, timeoutNs);
+    ++M->launches;
+    ++X->calls;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());
     return ORBM_OK;
@@ -972,8 +1148,10 @@ int orbm_knn_device_static(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq
     }
     unsigned long long* part = nullptr;
     CKM(knnStaticAddress(M->device, &part));
-    k_knn<1, kKnnMaxK><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
-                                                                      db->rowOffset, (int)rowsPerChunk, k, part);
+    KnnFused none;                                              // no fused merge here: its done-counters would be one more buffer
+    memset(&none, 0, sizeof(none));
+    k_knn<1, kKnnMaxK, false><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
+                                                                             db->rowOffset, (int)rowsPerChunk, k, part, none);
     k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(part, nchunks, nq, k, d_dist, d_idx);
     M->launches += 2;
     M->lastEvals = (long long)nq * db->n;

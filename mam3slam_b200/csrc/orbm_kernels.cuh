@@ -1208,13 +1208,28 @@ __device__ __forceinline__ int hamming_csa(const uint32_t (&q)[8], const uint4 a
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// Optional fused epilogue of k_knn (kFused).  The CTA that finishes the LAST chunk of a query block (a done-counter per query
+// block) merges the per-chunk lists of its queries right away - no k_knn_merge launch - and writes either the final distances /
+// row ids (world == 0) or, for the sharded search, this rank's merged (distance, global row) keys straight into EVERY rank's
+// exchange buffer over NVLink peer stores, followed by one release-add on each rank's arrival flag (orbm_knn_sharded; the
+// receiving side is k_knn_xchg_merge).  That is the all-gather of the sharded search done by the kernel that produced the
+// data: no NCCL call, no extra launch, the transfer of one query block overlaps the scan of the others.
+constexpr int kXchgMaxRanks = 16;
+struct KnnFused {
+    unsigned int* counter;
+    uint16_t* dist; int32_t* idx;
+    int world;
+    unsigned long long* peerSlot[kXchgMaxRanks];      // rank r's buffer at [parity][this rank]
+    unsigned int* peerFlag[kXchgMaxRanks];            // rank r's arrival counter [parity][this rank]
+};
+
 // dist/idx partial lists: part[(chunk * nq + q) * k + t] = key (dist << 32 | global row)
 // kQ queries per thread (q, q + kKnnThreads, ...): one pair of 16-byte row loads serves kQ evaluations, and the kQ independent
 // carry-save trees give the scheduler instruction-level parallelism; kK = compile-time bound of k (list kept in registers).
-template <int kQ, int kK>
+template <int kQ, int kK, bool kFused>
 __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict__ qdesc, int nq, const uint32_t* __restrict__ db,
                                                      long long ndb, long long rowOffset, int rowsPerChunk, int k,
-                                                     unsigned long long* __restrict__ part) {
+                                                     unsigned long long* __restrict__ part, const KnnFused F) {
     __shared__ __align__(128) uint4 tile[2][kKnnTileRows * 2];
     __shared__ __align__(8) unsigned long long mbar[2];
     const int tid = threadIdx.x;
@@ -1317,6 +1332,108 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict_
                 }
             }
         }
+    }
+    if (!kFused) return;
+    // fused merge: last chunk of this query block done -> this CTA merges the block's lists (thread = query, keys ascending =
+    // (distance, global row): the strict-< rule of a single scan)
+    __shared__ int sLast;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) sLast = atomicAdd(&F.counter[blockIdx.x], 1u) == gridDim.y - 1;
+    __syncthreads();
+    if (!sLast) return;
+    if (tid == 0) F.counter[blockIdx.x] = 0;                    // re-armed for the next call on this stream
+    __threadfence();
+#pragma unroll 1
+    for (int j = 0; j < kQ; ++j) {
+        const int q = qBase + j * kKnnThreads;
+        if (q >= nq) continue;
+        unsigned long long top[kK];
+#pragma unroll
+        for (int u = 0; u < kK; ++u) top[u] = 0xffffffffffffffffull;
+        for (int c = 0; c < (int)gridDim.y; ++c) {
+            const unsigned long long* src = part + ((size_t)c * nq + q) * k;
+            for (int u = 0; u < k; ++u) {
+                unsigned long long carry = __ldcg(src + u);
+                if (carry == 0xffffffffffffffffull) break;      // a chunk's list is ascending: nothing but padding follows
+#pragma unroll
+                for (int v = 0; v < kK; ++v) {
+                    if (v < k) { const unsigned long long lo = top[v] < carry ? top[v] : carry, hi = top[v] < carry ? carry : top[v]; top[v] = lo; carry = hi; }
+                }
+            }
+        }
+        if (F.world == 0) {
+#pragma unroll
+            for (int u = 0; u < kK; ++u) {
+                if (u < k) {
+                    const bool none = top[u] == 0xffffffffffffffffull;
+                    F.dist[(size_t)q * k + u] = none ? (uint16_t)65535 : (uint16_t)(top[u] >> 32);
+                    F.idx[(size_t)q * k + u] = none ? -1 : (int32_t)(top[u] & 0xffffffffull);
+                }
+            }
+        } else {
+            for (int r = 0; r < F.world; ++r) {
+                unsigned long long* dst = F.peerSlot[r] + (size_t)q * k;
+#pragma unroll
+                for (int u = 0; u < kK; ++u) if (u < k) dst[u] = top[u];
+            }
+        }
+    }
+    if (F.world > 0) {
+        // every thread's peer stores are ordered before the arrival signal: fence (system scope), CTA barrier, one release-add per rank
+        __threadfence_system();
+        __syncthreads();
+        if (tid < F.world) asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(F.peerFlag[tid]), "r"(1u) : "memory");
+    }
+}
+
+// Receiving side of the sharded search: waits until every rank's arrival counter of this parity has reached `expected` (all
+// query blocks of all ranks have landed in THIS rank's exchange buffer), then merges the world lists of each query: one warp
+// per query, keys ascending.  A rank that never shows up must not hang the GPU: after timeoutNs the kernel gives up, raises
+// *status and writes "no neighbour".
+__global__ void __launch_bounds__(256) k_knn_xchg_merge(const unsigned long long* __restrict__ slots, size_t slotKeys,
+                                                        const unsigned int* __restrict__ flags, unsigned int expected, int world, int nq,
+                                                        int k, uint16_t* __restrict__ outDist, int32_t* __restrict__ outIdx,
+                                                        unsigned int* __restrict__ status, unsigned long long timeoutNs) {
+    __shared__ int sOk;
+    if (threadIdx.x == 0) {
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        int ok = 1;
+        for (int r = 0; r < world && ok; ++r) {
+            unsigned int v;
+            do {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+                if ((int)(v - expected) >= 0) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > timeoutNs) { ok = 0; atomicExch(status, 1u); }
+                else __nanosleep(200);
+            } while (ok);
+        }
+        sOk = ok;
+    }
+    __syncthreads();
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const int total = world * k;
+    unsigned long long prev = 0; bool first = true;
+    for (int t = 0; t < k; ++t) {
+        unsigned long long m = 0xffffffffffffffffull;
+        if (sOk) {
+            for (int e = lane; e < total; e += 32) {
+                const int c = e / k, u = e - c * k;
+                const unsigned long long key = __ldcg(slots + (size_t)c * slotKeys + (size_t)q * k + u);     // L2: where peer stores land
+                if ((first || key > prev) && key < m) m = key;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(0xffffffffu, m, o); m = x < m ? x : m; }
+        if (lane == 0) {
+            if (m == 0xffffffffffffffffull) { outDist[(size_t)q * k + t] = 65535; outIdx[(size_t)q * k + t] = -1; }
+            else { outDist[(size_t)q * k + t] = (uint16_t)(m >> 32); outIdx[(size_t)q * k + t] = (int32_t)(m & 0xffffffffull); }
+        }
+        if (m == 0xffffffffffffffffull) { for (int u = t + 1; u < k && lane == 0; ++u) { outDist[(size_t)q * k + u] = 65535; outIdx[(size_t)q * k + u] = -1; } break; }
+        prev = m; first = false;
     }
 }
 

@@ -651,6 +651,14 @@ int orbx_device_count(void) {
     return n;
 }
 
+int orbx_device_pci_bus_id(int device, char* out, int len) {
+    if (!out || len < 16) return ORBX_ERR_INVALID;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return ORBX_ERR_NO_DEVICE;
+    if (device < 0 || device >= n) return ORBX_ERR_INVALID;
+    return cudaDeviceGetPCIBusId(out, len, device) == cudaSuccess ? ORBX_OK : ORBX_ERR_CUDA;
+}
+
 const char* orbx_strerror(int s) {
     switch (s) {
         case ORBX_OK: return "ok";

@@ -108,6 +108,50 @@ class KnnDatabase:
             pass
 
 
+class KnnExchange:
+    """This rank's side of the sharded k-NN over peer memory (orbm_xchg, include/orbm.h): one buffer per rank, every rank
+    maps every other rank's buffer, and ORBmatcher.knn_sharded does scan + all-gather + merge inside its two kernels.
+
+    `connect(all_gather)` does the setup for one process per GPU: `all_gather(bytes) -> [bytes] * world` is whatever the host
+    has - with torch.distributed: `lambda b: (lambda out: (dist.all_gather_object(out, b), out)[1])([None] * world)`.
+    `link(peers)` is the single-process variant (a list of the KnnExchange objects of all ranks)."""
+    HANDLE_BYTES = 64
+
+    def __init__(self, matcher, rank, world, max_nq, max_k):
+        self._m, self.rank, self.world = matcher, int(rank), int(world)
+        self._x = C.c_void_p()
+        check_m(matcher._L.orbm_xchg_create(matcher._h, self.rank, self.world, int(max_nq), int(max_k), C.byref(self._x)),
+                matcher._h, "orbm_xchg_create")
+
+    def ipc_handle(self):
+        buf = C.create_string_buffer(self.HANDLE_BYTES)
+        check_m(self._m._L.orbm_xchg_ipc_handle(self._x, buf), self._m._h, "orbm_xchg_ipc_handle")
+        return buf.raw
+
+    def connect(self, all_gather):
+        handles = all_gather(self.ipc_handle())
+        assert len(handles) == self.world
+        for r, h in enumerate(handles):
+            if r != self.rank:
+                check_m(self._m._L.orbm_xchg_open(self._x, r, C.create_string_buffer(bytes(h), self.HANDLE_BYTES)), self._m._h,
+                        "orbm_xchg_open")
+        return self
+
+    def link(self, peers):
+        for r, p in enumerate(peers):
+            if r != self.rank:
+                check_m(self._m._L.orbm_xchg_open_local(self._x, r, p._x), self._m._h, "orbm_xchg_open_local")
+        return self
+
+    def status(self):
+        return int(self._m._L.orbm_xchg_status(self._x))
+
+    def close(self):
+        if getattr(self, "_x", None) and self._m._h:
+            self._m._L.orbm_xchg_destroy(self._x)
+            self._x = None
+
+
 class ORBVocabulary:
     """DBoW2 vocabulary tree resident in HBM (orbm_vocab) — the part of ORBVocabulary (include/ORBVocabulary.h;
     Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) that Frame::ComputeBoW / KeyFrame::ComputeBoW use.  The tree arrives as
@@ -397,6 +441,12 @@ class ORBmatcher:
         nothing (include/orbm.h).  No counterpart in the reference."""
         check_m(self._L.orbm_knn_device_static(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist),
                                                C.c_void_p(d_idx), C.c_void_p(stream or 0)), self._h, "orbm_knn_device_static")
+
+    def knn_sharded(self, xchg, db, d_q, nq, k, d_dist, d_idx, stream=None):
+        """orbm_knn_sharded: this rank's shard scan, the exchange of the per-rank lists over NVLink peer stores and the final
+        merge, all asynchronous on `stream`; every rank calls it with the same queries (include/orbm.h)."""
+        check_m(self._L.orbm_knn_sharded(self._h, xchg._x, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist),
+                                         C.c_void_p(d_idx), C.c_void_p(stream or 0)), self._h, "orbm_knn_sharded")
 
     def knn_merge_device(self, d_dist, d_idx, shard_stride_bytes, nshards, nq, k, d_out_dist, d_out_idx, stream=None):
         """Device-side merge of all-gathered per-shard top-k lists (include/orbm.h); pointers are device addresses."""

@@ -314,6 +314,85 @@ def test_knn_full_size_properties(M):
     Dp.close(); D.close()
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_knn_sharded_peer_exchange_equals_unsharded(M, world):
+    """orbm_knn_sharded (scan + exchange over peer stores + merge inside the kernels) with the ranks emulated on ONE GPU: one
+    matcher handle, exchange buffer and stream per rank, buffers linked with orbm_xchg_open_local.  Every rank's result must equal
+    the unsharded orbm_knn_device search bit for bit; several calls in a row with different queries exercise both buffer parities
+    and the re-armed done-counters."""
+    import torch
+    from mam3slam_b200.matcher import KnnDatabase, KnnExchange
+    ndb, k = 60000, 3
+    _, rows = sc.knn_data(ndb, 8, seed=91, planted=False)
+    rows[50000] = rows[100]                                   # equal distances across shards: the lower global row wins
+    rows_dev = torch.from_numpy(rows).cuda()
+    full = KnnDatabase(M, None, device_ptr=rows_dev.data_ptr(), n=ndb)
+    ms = [ORBmatcher(0.9, True) for _ in range(world)]
+    xs = [KnnExchange(ms[r], r, world, 700, 4) for r in range(world)]
+    for x in xs:
+        x.link(xs)
+    bounds = [ndb * r // world for r in range(world + 1)]
+    dbs = [KnnDatabase(ms[r], None, row_offset=bounds[r], device_ptr=rows_dev.data_ptr() + 32 * bounds[r], n=bounds[r + 1] - bounds[r])
+           for r in range(world)]
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    rng = np.random.default_rng(5)
+    # ranks emulated on ONE device: a rank's first call allocates its scratch, and cudaMalloc waits for the device - on which the
+    # previous rank's merge kernel would be waiting for this very rank.  Allocate up front (separate GPUs have no such coupling).
+    warm_q = torch.zeros((700, 32), dtype=torch.uint8, device="cuda")
+    wd = torch.empty((700, k), dtype=torch.int16, device="cuda"); wi = torch.empty((700, k), dtype=torch.int32, device="cuda")
+    for r in range(world):
+        ms[r].knn_device(dbs[r], warm_q.data_ptr(), 700, k, wd.data_ptr(), wi.data_ptr(), streams[r].cuda_stream)
+    torch.cuda.synchronize()
+    for call, nq in enumerate([600, 257, 600, 31, 700]):
+        q = rows[rng.integers(0, ndb, nq)].copy()
+        q[:, 5] ^= 0x21
+        q[0] = rows[100]                                      # distance 0 to rows 100 and 50000
+        q_dev = torch.from_numpy(q).cuda()
+        rd = torch.empty((nq, k), dtype=torch.int16, device="cuda"); ri = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+        M.knn_device(full, q_dev.data_ptr(), nq, k, rd.data_ptr(), ri.data_ptr(), torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        outs = []
+        for r in range(world):
+            od = torch.full((nq, k), -3, dtype=torch.int16, device="cuda"); oi = torch.full((nq, k), -3, dtype=torch.int32, device="cuda")
+            ms[r].knn_sharded(xs[r], dbs[r], q_dev.data_ptr(), nq, k, od.data_ptr(), oi.data_ptr(), streams[r].cuda_stream)
+            outs.append((od, oi))
+        torch.cuda.synchronize()
+        for r, (od, oi) in enumerate(outs):
+            assert xs[r].status() == 0
+            assert torch.equal(od, rd) and torch.equal(oi, ri), (call, r)
+        assert ri[0, 0].item() == 100 and ri[0, 1].item() == 50000 and rd[0, 1].item() == 0
+    od_o, oi_o = om.knn(q, rows, k)                          # and the last call against the CPU oracle
+    assert np.array_equal(rd.cpu().numpy().view(np.uint16), od_o) and np.array_equal(ri.cpu().numpy(), oi_o)
+    for r in range(world):
+        dbs[r].close(); xs[r].close(); ms[r].close()
+    full.close()
+
+
+def test_knn_sharded_missing_rank_times_out_instead_of_hanging():
+    """A rank whose peer never calls must give up (ORBM_XCHG_TIMEOUT_MS) and say so, not spin forever on the GPU."""
+    import subprocess, sys, os
+    prog = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+from mam3slam_b200 import ORBmatcher
+from mam3slam_b200.matcher import KnnDatabase, KnnExchange
+m0, m1 = ORBmatcher(0.9, True), ORBmatcher(0.9, True)
+x0, x1 = KnnExchange(m0, 0, 2, 64, 2), KnnExchange(m1, 1, 2, 64, 2)
+x0.link([x0, x1]); x1.link([x0, x1])
+rows = torch.randint(0, 256, (5000, 32), dtype=torch.uint8, device='cuda')
+q = rows[:40].clone()
+db = KnnDatabase(m0, None, device_ptr=rows.data_ptr(), n=2500)
+od = torch.zeros((40, 2), dtype=torch.int16, device='cuda'); oi = torch.zeros((40, 2), dtype=torch.int32, device='cuda')
+m0.knn_sharded(x0, db, q.data_ptr(), 40, 2, od.data_ptr(), oi.data_ptr())
+torch.cuda.synchronize()
+print(x0.status(), int((oi == -1).all()))
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", prog], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, ORBM_XCHG_TIMEOUT_MS="100"))
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert r.stdout.split()[-2:] == ["1", "1"]
+
+
 def test_knn_merge_device_equals_host_merge(M):
     """config 5 exchange step: per-shard lists laid out as one (ids | distances) buffer per rank, merged on the device."""
     import torch
