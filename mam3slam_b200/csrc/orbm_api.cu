@@ -927,16 +927,21 @@ int knnScratch(orbm_matcher* M, const KnnPlan& P, int nq, int k) {
     return ORBM_OK;
 }
 
-void launchKnn(orbm_matcher* M, const KnnPlan& P, int qpt, orbm_db db, const uint8_t* d_q, int nq, int k, const KnnFused& F, cudaStream_t st) {
+// kK = compile-time bound of k: the sorted insertion is unrolled kK deep, so a k = 2 search pays for 2 steps, not 16
+extern "C++" template <int kQ, int kK>
+void launchKnnK(orbm_matcher* M, const KnnPlan& P, orbm_db db, const uint8_t* d_q, int nq, int k, const KnnFused& F, cudaStream_t st) {
     const dim3 grid(P.qblocks, P.nchunks);
     const uint32_t* q = reinterpret_cast<const uint32_t*>(d_q);
-    if (qpt == 2) {
-        if (F.counter) k_knn<2, 4, true><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
-        else k_knn<2, 4, false><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
-    } else {
-        if (F.counter) k_knn<1, kKnnMaxK, true><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
-        else k_knn<1, kKnnMaxK, false><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
-    }
+    if (F.counter) k_knn<kQ, kK, true><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+    else k_knn<kQ, kK, false><<<grid, kKnnThreads, 0, st>>>(q, nq, db->rows, db->n, db->rowOffset, (int)P.rowsPerChunk, k, M->knnPart, F);
+}
+
+void launchKnn(orbm_matcher* M, const KnnPlan& P, int qpt, orbm_db db, const uint8_t* d_q, int nq, int k, const KnnFused& F, cudaStream_t st) {
+    if (qpt == 2) launchKnnK<2, 4>(M, P, db, d_q, nq, k, F, st);
+    else if (k <= 2) launchKnnK<1, 2>(M, P, db, d_q, nq, k, F, st);
+    else if (k <= 4) launchKnnK<1, 4>(M, P, db, d_q, nq, k, F, st);
+    else if (k <= 8) launchKnnK<1, 8>(M, P, db, d_q, nq, k, F, st);
+    else launchKnnK<1, kKnnMaxK>(M, P, db, d_q, nq, k, F, st);
     ++M->launches;
 }
 
@@ -1072,13 +1077,25 @@ int orbm_knn_sharded(orbm_handle M, orbm_xchg X, orbm_db db, const uint8_t* d_q,
     const int par = (int)(X->calls & 1);
     KnnFused F;
     memset(&F, 0, sizeof(F));
-    F.counter = M->knnCounter; F.world = X->world;
+    F.world = X->world;
     for (int r = 0; r < X->world; ++r) {
         F.peerSlot[r] = reinterpret_cast<unsigned long long*>(X->peer[r]) + ((size_t)par * X->world + X->rank) * X->slotKeys;
         F.peerFlag[r] = reinterpret_cast<unsigned int*>(X->peer[r] + X->flagsOff) + par * kXchgMaxRanks + X->rank;
     }
-    launchKnn(M, P, 1, db, d_q, nq, k, F, st);
-    X->expect[par] += (unsigned int)P.qblocks;         // nq is the same on every rank (the queries are replicated), so is qblocks
+    // ORBM_KNN_FUSED=1: the scan kernel's last CTA per query block merges and pushes (one launch less, but that CTA works alone
+    // at the end of the scan); default: plain scan, then k_knn_merge_push with a warp per query.  Every rank must use the same
+    // setting: the arrival counters count query blocks in one form and merge CTAs in the other.
+    static const bool fused = [] { const char* e = getenv("ORBM_KNN_FUSED"); return e && atoi(e) != 0; }();
+    if (fused) {
+        F.counter = M->knnCounter;
+        launchKnn(M, P, 1, db, d_q, nq, k, F, st);
+        X->expect[par] += (unsigned int)P.qblocks;     // nq is the same on every rank (the queries are replicated), so is qblocks
+    } else {
+        launchKnn(M, P, 1, db, d_q, nq, k, F, st);
+        k_knn_merge_push<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, P.nchunks, nq, k, F);
+        ++M->launches;
+        X->expect[par] += (unsigned int)((nq + 7) / 8);
+    }
     static const unsigned long long timeoutNs = [] { const char* e = getenv("ORBM_XCHG_TIMEOUT_MS"); return (unsigned long long)(e ? atoll(e) : 4000) * 1000000ull; }();
     const unsigned int* flags = reinterpret_cast<const unsigned int*>(X->buf + X->flagsOff) + par * kXchgMaxRanks;
     unsigned int* status = reinterpret_cast<unsigned int*>(X->buf + X->flagsOff) + 2 * kXchgMaxRanks;

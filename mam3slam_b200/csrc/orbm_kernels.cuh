@@ -1227,7 +1227,8 @@ struct KnnFused {
 // kQ queries per thread (q, q + kKnnThreads, ...): one pair of 16-byte row loads serves kQ evaluations, and the kQ independent
 // carry-save trees give the scheduler instruction-level parallelism; kK = compile-time bound of k (list kept in registers).
 template <int kQ, int kK, bool kFused>
-__global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict__ qdesc, int nq, const uint32_t* __restrict__ db,
+__global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fused: the merge epilogue must not cost the scan its 4 CTAs per SM
+    const uint32_t* __restrict__ qdesc, int nq, const uint32_t* __restrict__ db,
                                                      long long ndb, long long rowOffset, int rowsPerChunk, int k,
                                                      unsigned long long* __restrict__ part, const KnnFused F) {
     __shared__ __align__(128) uint4 tile[2][kKnnTileRows * 2];
@@ -1351,14 +1352,25 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict_
         unsigned long long top[kK];
 #pragma unroll
         for (int u = 0; u < kK; ++u) top[u] = 0xffffffffffffffffull;
-        for (int c = 0; c < (int)gridDim.y; ++c) {
-            const unsigned long long* src = part + ((size_t)c * nq + q) * k;
-            for (int u = 0; u < k; ++u) {
-                unsigned long long carry = __ldcg(src + u);
-                if (carry == 0xffffffffffffffffull) break;      // a chunk's list is ascending: nothing but padding follows
+        unsigned long long worst = 0xffffffffffffffffull;        // top[k - 1]
+        // eight independent loads in flight per round (a dependent load per key would cost ~150 L2 round trips per query)
+        const int nkeys = (int)gridDim.y * k;
+#pragma unroll 1
+        for (int e0 = 0; e0 < nkeys; e0 += 8) {
+            unsigned long long key[8];
 #pragma unroll
-                for (int v = 0; v < kK; ++v) {
-                    if (v < k) { const unsigned long long lo = top[v] < carry ? top[v] : carry, hi = top[v] < carry ? carry : top[v]; top[v] = lo; carry = hi; }
+            for (int i = 0; i < 8; ++i) {
+                const int e = e0 + i, c = e / k, u = e - c * k;
+                key[i] = e < nkeys ? __ldcg(part + ((size_t)c * nq + q) * k + u) : 0xffffffffffffffffull;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                unsigned long long carry = key[i];
+                if (carry < worst) {
+#pragma unroll
+                    for (int v = 0; v < kK; ++v) {
+                        if (v < k) { const unsigned long long lo = top[v] < carry ? top[v] : carry, hi = top[v] < carry ? carry : top[v]; top[v] = lo; carry = hi; worst = lo; }
+                    }
                 }
             }
         }
@@ -1385,6 +1397,37 @@ __global__ void __launch_bounds__(kKnnThreads) k_knn(const uint32_t* __restrict_
         __syncthreads();
         if (tid < F.world) asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(F.peerFlag[tid]), "r"(1u) : "memory");
     }
+}
+
+// Sending side of the sharded search, unfused form (the default): the per-chunk lists of one query are merged by one warp
+// (k_knn_merge's rule) and the merged keys go straight to EVERY rank's exchange buffer - lane r stores to rank r - followed by
+// one release-add per rank and CTA on the arrival counters.  250 CTAs work in parallel here, where the fused epilogue of
+// k_knn leaves the merge of a query block to ONE CTA at the very end of the scan (measured +60 us on a 125 k-row shard).
+__global__ void __launch_bounds__(256) k_knn_merge_push(const unsigned long long* __restrict__ part, int nchunks, int nq, int k, const KnnFused F) {
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q < nq) {
+        const int total = nchunks * k;
+        unsigned long long prev = 0; bool first = true;
+        for (int t = 0; t < k; ++t) {
+            unsigned long long m = 0xffffffffffffffffull;
+            for (int e = lane; e < total; e += 32) {
+                const int c = e / k, u = e - c * k;
+                const unsigned long long key = part[((size_t)c * nq + q) * k + u];
+                if ((first || key > prev) && key < m) m = key;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(0xffffffffu, m, o); m = x < m ? x : m; }
+            if (lane < F.world) F.peerSlot[lane][(size_t)q * k + t] = m;          // all-ones = no neighbour (the lists end there)
+            if (m == 0xffffffffffffffffull) {
+                for (int u = t + 1; u < k; ++u) if (lane < F.world) F.peerSlot[lane][(size_t)q * k + u] = m;
+                break;
+            }
+            prev = m; first = false;
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < F.world) asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(F.peerFlag[threadIdx.x]), "r"(1u) : "memory");
 }
 
 // Receiving side of the sharded search: waits until every rank's arrival counter of this parity has reached `expected` (all
