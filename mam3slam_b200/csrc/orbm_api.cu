@@ -55,6 +55,7 @@ struct orbm_matcher {
     void* pinned = nullptr; size_t pinnedBytes = 0;
     unsigned long long* dEvals = nullptr;
     unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
+    unsigned int* knnBound = nullptr; int knnBoundCap = 0;         // shared pruning bound per query (all ones at rest)
     unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
     void* trackBuf = nullptr; size_t trackBytes = 0;
 };
@@ -224,6 +225,7 @@ void orbm_destroy(orbm_handle M) {
     if (M->dEvals) cudaFree(M->dEvals);
     if (M->knnPart) cudaFree(M->knnPart);
     if (M->knnCounter) cudaFree(M->knnCounter);
+    if (M->knnBound) cudaFree(M->knnBound);
     if (M->trackBuf) cudaFree(M->trackBuf);
     cudaStreamDestroy(M->stream);
     delete M;
@@ -908,6 +910,14 @@ KnnPlan knnPlan(const orbm_matcher* M, long long n, int nq, int qpt) {
     return P;
 }
 
+// The chunks of a query block share a pruning bound (k_knn, KnnFused::bound) when a chunk is short: the list warm-up it saves
+// is a fixed ~20 us per chunk, 6 % of a 1700-row chunk (a 125 k-row shard: 354 -> 342 us) but nothing against the per-tile
+// read it costs on a 13 k-row chunk (1 M rows on one GPU: 2.56 -> 2.59 ms).  ORBM_KNN_BOUND=0 / 1 forces it off / on.
+bool knnShareBound(const KnnPlan& P) {
+    static const int mode = [] { const char* e = getenv("ORBM_KNN_BOUND"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
+    return mode < 0 ? P.rowsPerChunk <= 4096 : mode == 1;
+}
+
 int knnScratch(orbm_matcher* M, const KnnPlan& P, int nq, int k) {
     const size_t need = (size_t)P.nchunks * nq * k * sizeof(unsigned long long);
     if (need > M->knnPartBytes) {
@@ -915,6 +925,14 @@ int knnScratch(orbm_matcher* M, const KnnPlan& P, int nq, int k) {
         M->knnPart = nullptr; M->knnPartBytes = 0;
         CKM(cMalloc((void**)&M->knnPart, need));
         M->knnPartBytes = need;
+    }
+    if (nq > M->knnBoundCap) {
+        if (M->knnBound) cudaFree(M->knnBound);
+        M->knnBound = nullptr; M->knnBoundCap = 0;
+        const int cap = std::max(nq, 4096);
+        CKM(cMalloc((void**)&M->knnBound, (size_t)cap * sizeof(unsigned int)));
+        CKM(cudaMemset(M->knnBound, 0xff, (size_t)cap * sizeof(unsigned int)));
+        M->knnBoundCap = cap;
     }
     if (P.qblocks > M->knnCounterCap) {
         if (M->knnCounter) cudaFree(M->knnCounter);
@@ -965,8 +983,9 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     // k_knn_merge (7 us); the sharded search always uses it (it is what pushes the lists to the peers).
     static const bool fused = [] { const char* e = getenv("ORBM_KNN_FUSED"); return e && atoi(e) != 0; }();
     if (fused) { F.counter = M->knnCounter; F.dist = d_dist; F.idx = d_idx; }
+    if (knnShareBound(P)) F.bound = M->knnBound;
     launchKnn(M, P, qpt, db, d_q, nq, k, F, st);
-    if (!fused) { k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, P.nchunks, nq, k, d_dist, d_idx); ++M->launches; }
+    if (!fused) { k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, P.nchunks, nq, k, d_dist, d_idx, F.bound); ++M->launches; }
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());
     return ORBM_OK;
@@ -1078,6 +1097,7 @@ int orbm_knn_sharded(orbm_handle M, orbm_xchg X, orbm_db db, const uint8_t* d_q,
     KnnFused F;
     memset(&F, 0, sizeof(F));
     F.world = X->world;
+    if (knnShareBound(P)) F.bound = M->knnBound;
     for (int r = 0; r < X->world; ++r) {
         F.peerSlot[r] = reinterpret_cast<unsigned long long*>(X->peer[r]) + ((size_t)par * X->world + X->rank) * X->slotKeys;
         F.peerFlag[r] = reinterpret_cast<unsigned int*>(X->peer[r] + X->flagsOff) + par * kXchgMaxRanks + X->rank;
@@ -1169,7 +1189,7 @@ int orbm_knn_device_static(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq
     memset(&none, 0, sizeof(none));
     k_knn<1, kKnnMaxK, false><<<dim3(qblocks, nchunks), kKnnThreads, 0, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n,
                                                                              db->rowOffset, (int)rowsPerChunk, k, part, none);
-    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(part, nchunks, nq, k, d_dist, d_idx);
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(part, nchunks, nq, k, d_dist, d_idx, nullptr);
     M->launches += 2;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());

@@ -1216,6 +1216,7 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // data: no NCCL call, no extra launch, the transfer of one query block overlaps the scan of the others.
 constexpr int kXchgMaxRanks = 16;
 struct KnnFused {
+    unsigned int* bound;                              // per query: (smallest k-th best distance any chunk has published + 1) << 23, or all ones; NULL = off
     unsigned int* counter;
     uint16_t* dist; int32_t* idx;
     int world;
@@ -1241,6 +1242,10 @@ __global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fu
     uint32_t qd[kQ][8];
     uint32_t best[kQ][kK];       // keys dist << 23 | chunk-local row, ascending
     uint32_t worst[kQ];
+    // Chunks of one query block run side by side and each would warm its list up from scratch (~64 ln(rows / 64) warp-level
+    // insertions); they share a bound instead: a row farther than the k-th best distance ANY chunk has seen cannot be in the final
+    // top-k (equal distances stay: the lower row wins), so `worst` = min(own k-th best key, published bound).
+    uint32_t gb[kQ];
 #pragma unroll
     for (int j = 0; j < kQ; ++j) {
         const int qq = min(qBase + j * kKnnThreads, nq - 1);
@@ -1249,6 +1254,7 @@ __global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fu
 #pragma unroll
         for (int t = 0; t < kK; ++t) best[j][t] = 0xffffffffu;
         worst[j] = 0xffffffffu;
+        gb[j] = 0xffffffffu;
     }
 
     const int ntiles = (nrows + kKnnTileRows - 1) / kKnnTileRows;
@@ -1282,12 +1288,28 @@ __global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fu
         }
         const int rows = min(kKnnTileRows, nrows - t * kKnnTileRows);
         const uint32_t rowBase = (uint32_t)(t * kKnnTileRows);
+        if (F.bound) {      // once per tile: take the others' bound, publish mine if it is tighter
+#pragma unroll
+            for (int j = 0; j < kQ; ++j) {
+                const int qq = qBase + j * kKnnThreads;
+                if (qq < nq) {
+                    const uint32_t seen = __ldcg(F.bound + qq);
+                    uint32_t kth = 0xffffffffu;
+#pragma unroll
+                    for (int u = 0; u < kK; ++u) if (u == k - 1) kth = best[j][u];
+                    const uint32_t mine = kth == 0xffffffffu ? 0xffffffffu : ((kth >> 23) + 1u) << 23;
+                    if (mine < seen) atomicMin(F.bound + qq, mine);
+                    gb[j] = min(seen, mine);
+                    worst[j] = min(worst[j], gb[j]);
+                }
+            }
+        }
         auto offer = [&](int j, uint32_t key) {
             // sorted insertion into the k best: bubble the new key through, drop the largest
             uint32_t carry = key;
 #pragma unroll
             for (int u = 0; u < kK; ++u) {
-                if (u < k) { const uint32_t lo = min(best[j][u], carry), hi = max(best[j][u], carry); best[j][u] = lo; carry = hi; worst[j] = lo; }
+                if (u < k) { const uint32_t lo = min(best[j][u], carry), hi = max(best[j][u], carry); best[j][u] = lo; carry = hi; worst[j] = min(lo, gb[j]); }
             }
         };
         // four rows at a time: one comparison of the smallest of their keys against the current k-th best decides whether
@@ -1349,6 +1371,7 @@ __global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fu
     for (int j = 0; j < kQ; ++j) {
         const int q = qBase + j * kKnnThreads;
         if (q >= nq) continue;
+        if (F.bound) F.bound[q] = 0xffffffffu;
         unsigned long long top[kK];
 #pragma unroll
         for (int u = 0; u < kK; ++u) top[u] = 0xffffffffffffffffull;
@@ -1406,6 +1429,7 @@ __global__ void __launch_bounds__(kKnnThreads, kFused ? 4 : 5) k_knn(      // fu
 __global__ void __launch_bounds__(256) k_knn_merge_push(const unsigned long long* __restrict__ part, int nchunks, int nq, int k, const KnnFused F) {
     const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (q < nq) {
+        if (F.bound && lane == 0) F.bound[q] = 0xffffffffu;
         const int total = nchunks * k;
         unsigned long long prev = 0; bool first = true;
         for (int t = 0; t < k; ++t) {
@@ -1482,9 +1506,10 @@ __global__ void __launch_bounds__(256) k_knn_xchg_merge(const unsigned long long
 
 // merge the per-chunk lists of one query: k smallest (dist, row) keys.  One warp per query.
 __global__ void __launch_bounds__(256) k_knn_merge(const unsigned long long* __restrict__ part, int nchunks, int nq, int k,
-                                                   uint16_t* __restrict__ dist, int32_t* __restrict__ idx) {
+                                                   uint16_t* __restrict__ dist, int32_t* __restrict__ idx, unsigned int* __restrict__ bound) {
     const int q = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (q >= nq) return;
+    if (bound && lane == 0) bound[q] = 0xffffffffu;       // the scan's shared bound is back at rest for the next call
     const int total = nchunks * k;
     unsigned long long prev = 0; bool first = true;
     for (int t = 0; t < k; ++t) {
