@@ -207,6 +207,45 @@ def latency_bench(args, torch, local, frames):
             "note": "one frame in flight, synchronous calls, host buffers (pinned image)"}
 
 
+def agents_in_flight(local, frames, counts=(1, 4, 16)):
+    """How the reference feeds frames (src/Agent.cc:92-154: every agent's thread grabs ONE image, tracks it, grabs the next):
+    A agents on one GPU, each a host thread with its own extractor + matcher (mam3slam_b200.agents.AgentFrontEnd), one frame in
+    flight per agent, synchronous calls with host buffers.  Aggregate frames/s and the median per-frame latency an agent sees."""
+    import threading
+    from mam3slam_b200.agents import AgentFrontEnd
+    rows = []
+    nframes = 60
+    for A in counts:
+        agents = [AgentFrontEnd(a, local, NFEAT, SCALE, NLEVELS, INI_TH, MIN_TH) for a in range(A)]
+        lat = [[] for _ in range(A)]
+        go = threading.Barrier(A + 1)
+
+        def run(a):
+            ag = agents[a]
+            for i in range(6):
+                ag.GrabImageMonocular(frames[(a + i) % len(frames)], TH_TRACK)
+            go.wait()
+            for i in range(nframes):
+                t0 = time.perf_counter()
+                ag.GrabImageMonocular(frames[(a + i) % len(frames)], TH_TRACK)
+                lat[a].append(time.perf_counter() - t0)
+        th = [threading.Thread(target=run, args=(a,)) for a in range(A)]
+        for t in th:
+            t.start()
+        go.wait()
+        t0 = time.perf_counter()
+        for t in th:
+            t.join()
+        wall = time.perf_counter() - t0
+        for ag in agents:
+            ag.close()
+        rows.append({"agents": A, "frames_per_s": A * nframes / wall,
+                     "median_frame_latency_ms": float(np.median(np.concatenate(lat))) * 1e3})
+    return {"rows": rows, "note": "A agents x one frame in flight on ONE GPU, one host thread per agent (Python threads: the calls "
+                                  "release the GIL, the numpy marshalling between them does not), extraction + SearchByProjection "
+                                  "per frame, host buffers"}
+
+
 def search_latency_rows(local):
     """One row per ORBmatcher search member: per-call time through the product the way the C++ adapter calls it
     - an ORBmatcher CONSTRUCTED PER CALL, as the reference does (`ORBmatcher matcher(0.9,true);` inside every tracking /
@@ -731,6 +770,8 @@ def run_gpu(args):
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
     latency = latency_bench(args, torch, local, frames) if rank == 0 else None
+    if latency is not None:
+        latency["agents_one_frame_in_flight"] = agents_in_flight(local, frames)
     if latency is not None and not args.no_cpu:
         latency["search_members"] = search_latency_rows(local)
     sparse = sparse_bench(args, torch, local, rank) if rank == 0 and not args.no_sparse else None

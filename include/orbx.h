@@ -125,6 +125,10 @@ int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n
 /* standalone DistributeOctTree (src/ORBextractor.cc:555-779) on device: keys n x 3 ints (x, y, response) */
 int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,
                           int n_features, int* out, int cap, int* n_out);
+/* the same with the choice of form: use_pyramid = 1 tries the count-pyramid form first (*used_pyramid = 1 when it completed,
+ * 0 when a node deeper than the pyramid made the partitioning form take over); both forms must give the same keys */
+int orbx_debug_distribute2(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,
+                           int n_features, int use_pyramid, int* out, int cap, int* n_out, int* used_pyramid);
 
 /* bookkeeping for bench.py: kernels launched so far by this handle, and the handle's cudaStream_t */
 long long orbx_launch_count(orbx_handle h);

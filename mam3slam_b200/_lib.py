@@ -57,6 +57,7 @@ def lib():
     L.orbx_download_level_keypoints.argtypes = [vp, i32, i32, vp, i32, ip]
     L.orbx_debug_sort_nodes.argtypes = [vp, vp, vp, i32, vp, i32]
     L.orbx_debug_distribute.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, vp, i32, ip]
+    L.orbx_debug_distribute2.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, i32, ip, ip]
     L.orbx_launch_count.restype = C.c_longlong
     L.orbx_launch_count.argtypes = [vp]
     L.orbx_stream.restype = vp

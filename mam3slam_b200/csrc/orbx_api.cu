@@ -56,6 +56,7 @@ struct Extractor {
     bool fastPitchConst = false;
     bool pyrFast[kMaxLevels] = {};                  // level may use k_pyr_level_fast (4 pixels read <= 8 source bytes)
     size_t fastSmem = 0, treeSmem = 0;
+    int pyrRoots = 0;                // quadtree count pyramid: roots it is sized for (0 = off)
     // FAST cells in two launch groups: [0, fastNA) of dCellOrder = cells of at most fastRowsA tile rows (shared memory fastSmemA)
     int* dCellOrder = nullptr;
     int fastNA = 0, fastRowsA = 0, fastNA0 = 0;     // [0, fastNA0): the level-0 cells of group A
@@ -335,6 +336,14 @@ int configureShape(Extractor* E, int W, int H) {
         CK(cudaMemcpy(E->dCellOrder, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
     }
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
+    {   // count-pyramid form of the quadtree (orbx_kernels_tree.cuh): 12 bytes x 1365 cells per root on top of the list state
+        int roots = 0;
+        for (int l = 0; l < L; ++l) roots = std::max(roots, g.lv[l].nIni);
+        const char* pe = getenv("ORBX_TREE_PYRAMID");                     // A/B switch
+        const size_t withPyr = align16(E->treeSmem) + (size_t)roots * kPyrCellsPerRoot * 12;
+        E->pyrRoots = (roots <= kPyrMaxRoots && withPyr <= 100 * 1024 && !(pe && atoi(pe) == 0)) ? roots : 0;
+        if (E->pyrRoots) E->treeSmem = withPyr;
+    }
     // A quadtree CTA is 512 threads x 64 registers: two of them hold an SM's whole register file for ~100 us while issuing at
     // ~40 %, and no CTA of another handle's kernels can co-reside.  ORBX_TREE_CTAS=k caps the resident quadtree CTAs per SM at k
     // by padding the dynamic shared memory request (the occupancy limiter that needs no recompilation).
@@ -560,7 +569,7 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
     CK(launch_prio(k_octree, dim3(n, L), dim3(kTreeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
-                   E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb));
+                   E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb, E->pyrRoots));
     ++E->launches;
     mark();
     if (!side) launchBlur(st);
@@ -1110,6 +1119,11 @@ int orbx_debug_sort_nodes(orbx_handle h, const int* size, const int* ul_x, int n
 
 int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,
                           int n_features, int* out, int cap, int* n_out) {
+    return orbx_debug_distribute2(h, keys, n, min_x, max_x, min_y, max_y, n_features, 0, out, cap, n_out, nullptr);
+}
+
+int orbx_debug_distribute2(orbx_handle h, const int* keys, int n, int min_x, int max_x, int min_y, int max_y,
+                           int n_features, int use_pyramid, int* out, int cap, int* n_out, int* used_pyramid) {
     if (!h || n < 0 || !n_out || max_x <= min_x || max_y <= min_y || n_features < 1) return ORBX_ERR_INVALID;
     E_FROM(h);
     CK(cudaSetDevice(E->device));
@@ -1119,8 +1133,9 @@ int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int 
     const float hX = (float)treeW / nIni;
     const int P = std::max(n_features + 3, 4 * nIni) + 5;
     const int scanCap = std::max(P, 64) + 8;
-    const size_t smem = tree_smem_layout(P, scanCap, nullptr, nullptr);
+    const size_t smem = align16(tree_smem_layout(P, scanCap, nullptr, nullptr)) + (size_t)kPyrMaxRoots * kPyrCellsPerRoot * 12;
     if (smem > 200 * 1024) return ORBX_ERR_UNSUPPORTED;
+    if (use_pyramid && (treeW >= 4096 || treeH >= 4096)) use_pyramid = 0;
     CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
     std::vector<uint64_t> k(std::max(n, 1));
     for (int i = 0; i < n; ++i)
@@ -1129,16 +1144,19 @@ int orbx_debug_distribute(orbx_handle h, const int* keys, int n, int min_x, int 
     cudaError_t er = cudaMalloc((void**)&dA, k.size() * 8);
     if (er == cudaSuccess) er = cudaMalloc((void**)&dB, k.size() * 8);
     if (er == cudaSuccess) er = cudaMalloc((void**)&dOut, (size_t)P * 8);
-    if (er == cudaSuccess) er = cudaMalloc((void**)&dCnt, 4);
+    if (er == cudaSuccess) er = cudaMalloc((void**)&dCnt, 8);
     if (er == cudaSuccess) er = cudaMemcpy(dA, k.data(), k.size() * 8, cudaMemcpyHostToDevice);
     int cnt = 0;
     std::vector<uint64_t> res(P);
     if (er == cudaSuccess) {
-        k_debug_distribute<<<1, kTreeThreads, smem, E->stream>>>(dA, dB, n, n_features, nIni, hX, treeH, dOut, dCnt, P, scanCap);
+        k_debug_distribute<<<1, kTreeThreads, smem, E->stream>>>(dA, dB, n, n_features, nIni, hX, treeH, dOut, dCnt, P, scanCap, use_pyramid);
         ++E->launches;
         er = cudaStreamSynchronize(E->stream);
     }
-    if (er == cudaSuccess) er = cudaMemcpy(&cnt, dCnt, 4, cudaMemcpyDeviceToHost);
+    int cnt2[2] = {0, 0};
+    if (er == cudaSuccess) er = cudaMemcpy(cnt2, dCnt, 8, cudaMemcpyDeviceToHost);
+    cnt = cnt2[0];
+    if (used_pyramid) *used_pyramid = cnt2[1];
     if (er == cudaSuccess) er = cudaMemcpy(res.data(), dOut, (size_t)P * 8, cudaMemcpyDeviceToHost);
     cudaFree(dA); cudaFree(dB); cudaFree(dOut); cudaFree(dCnt);
     CK(er);

@@ -39,17 +39,25 @@ __host__ __device__ inline size_t tree_smem_layout(int P, int scanCap, TreeSmem*
 __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
                                                          const uint32_t* __restrict__ cand, const int* __restrict__ cellCount,
                                                          uint64_t* qtA, uint64_t* qtB, uint64_t* lvlKp, int* lvlCnt,
-                                                         int P, int scanCap, int frameBase) {
+                                                         int P, int scanCap, int frameBase, int pyrRoots) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int sW[33];
     TreeSmem S;
-    tree_smem_layout(P, scanCap, &S, smem);
+    const size_t treeBytes = tree_smem_layout(P, scanCap, &S, smem);
     const int l = blockIdx.y, frame = frameBase + blockIdx.x;      // level-major launch order: the heavy fine levels start first
     const LevelGeom& L = g->lv[l];
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
     const int cb = L.cellBegin, nc = L.cellEnd - L.cellBegin;
     const int* cc = cellCount + (size_t)frame * g->nCells + cb;
     TPROF_T0();
+    // count pyramid (orbx_kernels_tree.cuh): filled while the candidates are gathered, when the level's geometry fits its words
+    PyrView PV{nullptr, nullptr};
+    const bool pyr = pyrRoots > 0 && L.nIni <= pyrRoots && L.treeW < 4096 && L.treeH < 4096 && L.candCap < (1 << 20);
+    if (pyr) {
+        PV.best = reinterpret_cast<unsigned long long*>(smem + align16(treeBytes));
+        PV.cnt = reinterpret_cast<uint32_t*>(PV.best + (size_t)pyrRoots * kPyrCellsPerRoot);
+        for (int i = tid; i < L.nIni * kPyrCellsPerRoot; i += kTreeThreads) { PV.best[i] = 0; PV.cnt[i] = 0; }
+    }
     for (int i = tid; i < nc; i += kTreeThreads) S.scanA[i] = cc[i];
     __syncthreads();
     const int n = block_exscan(S.scanA, nc, sW);
@@ -63,24 +71,47 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
             const uint32_t e = cf[cell.outOffset + k];
             const uint32_t x = (e & 255u) + cell.relX, y = ((e >> 8) & 255u) + cell.relY, sc = e >> 16;
             bufA[off + k] = (uint64_t)x | ((uint64_t)y << 16) | ((uint64_t)sc << 32);
+            if (pyr) pyr_insert(PV, x, y, sc, (uint32_t)(off + k), L.hX, L.nIni, L.treeH);
         }
     }
     __syncthreads();
     TPROF(0);
     uint64_t* const buf[2] = {bufA, bufB};
-    distribute_tree(buf, n, L.quota, L.nIni, L.hX, L.treeH, S,
-                    lvlKp + (size_t)frame * g->kpCapFrame + L.kpOffset, lvlCnt + frame * g->nlevels + l);
+    uint64_t* out = lvlKp + (size_t)frame * g->kpCapFrame + L.kpOffset;
+    int* outCount = lvlCnt + frame * g->nlevels + l;
+    if (pyr) {
+        pyr_reduce(PV, L.nIni);
+        if (distribute_tree<true>(buf, n, L.quota, L.nIni, L.hX, L.treeH, S, out, outCount, PV)) return;
+        __syncthreads();                                           // a node deeper than the pyramid: the partitioning form takes over
+    }
+    distribute_tree<false>(buf, n, L.quota, L.nIni, L.hX, L.treeH, S, out, outCount);
 }
 
 // standalone tree for tests: keys (x | y<<16 | score<<32) already in bufA
+// usePyr: try the count-pyramid form first (outCount[1] = 1 when it completed, 0 when the partitioning form had to take over)
 __global__ void __launch_bounds__(kTreeThreads) k_debug_distribute(uint64_t* bufA, uint64_t* bufB, int n, int N, int nIni,
                                                                    float hX, int treeH, uint64_t* out, int* outCount,
-                                                                   int P, int scanCap) {
+                                                                   int P, int scanCap, int usePyr) {
     extern __shared__ __align__(16) uint8_t smem[];
     TreeSmem S;
-    tree_smem_layout(P, scanCap, &S, smem);
+    const size_t treeBytes = tree_smem_layout(P, scanCap, &S, smem);
     uint64_t* const buf[2] = {bufA, bufB};
-    distribute_tree(buf, n, N, nIni, hX, treeH, S, out, outCount);
+    if (threadIdx.x == 0) outCount[1] = 0;
+    if (usePyr && nIni <= kPyrMaxRoots && n < (1 << 20)) {
+        PyrView PV;
+        PV.best = reinterpret_cast<unsigned long long*>(smem + align16(treeBytes));
+        PV.cnt = reinterpret_cast<uint32_t*>(PV.best + (size_t)kPyrMaxRoots * kPyrCellsPerRoot);
+        for (int i = threadIdx.x; i < nIni * kPyrCellsPerRoot; i += kTreeThreads) { PV.best[i] = 0; PV.cnt[i] = 0; }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += kTreeThreads) {
+            const uint64_t k = bufA[i];
+            pyr_insert(PV, (uint32_t)(k & 0xffff), (uint32_t)((k >> 16) & 0xffff), (uint32_t)(k >> 32), (uint32_t)i, hX, nIni, treeH);
+        }
+        pyr_reduce(PV, nIni);
+        if (distribute_tree<true>(buf, n, N, nIni, hX, treeH, S, out, outCount, PV)) { if (threadIdx.x == 0) outCount[1] = 1; return; }
+        __syncthreads();
+    }
+    distribute_tree<false>(buf, n, N, nIni, hX, treeH, S, out, outCount);
 }
 
 // mode 0: single-thread std::sort emulation, 1: heap sort alone, 2: the warp version the quadtree uses (scratch: 3n+8 ints)

@@ -86,6 +86,78 @@ struct RootClass {
     }
 };
 
+// ---- count pyramid (second form of the tree, used when it fits) -------------------------------------------------------
+// DivideNode's split points depend on the node's rectangle only, never on its keys: the cells of depth d under a root are a
+// fixed (irregular, ceil-halved) 2^d x 2^d grid.  So instead of physically partitioning the keys pass after pass, every key
+// descends kPyrDepth levels ONCE (2 * kPyrDepth comparisons), bumps the count of its finest cell and offers itself as that
+// cell's best key; four-to-one sums / maxima give every coarser depth.  The list logic below (which nodes are split in which
+// order - the part of DistributeOctTree that decides the result) then runs on counts alone: child counts are four loads, the
+// kept key of a final node is one load.  A node the logic wants to split at depth kPyrDepth (clustered keys, or fewer keys
+// than the quota) aborts this form and the partitioning form runs instead: the keys themselves were never moved.
+constexpr int kPyrDepth = 5;
+constexpr int kPyrCellsPerRoot = (4 * 4 * 4 * 4 * 4 * 4 - 1) / 3;      // depths 0..5: 1365 cells
+constexpr int kPyrMaxRoots = 4;
+struct PyrView { uint32_t* cnt; unsigned long long* best; };
+__host__ __device__ inline int pyr_offset(int d) { return ((1 << (2 * d)) - 1) / 3; }
+// node address in pyramid form (kept in TreeSmem::beg): root << 28 | depth << 24 | cy << 12 | cx
+__device__ __forceinline__ uint32_t pyr_addr(int root, int d, int cx, int cy) { return ((uint32_t)root << 28) | ((uint32_t)d << 24) | ((uint32_t)cy << 12) | (uint32_t)cx; }
+__device__ __forceinline__ int pyr_cell(uint32_t a) {
+    const int root = (int)(a >> 28), d = (int)((a >> 24) & 15), cy = (int)((a >> 12) & 0xfff), cx = (int)(a & 0xfff);
+    return root * kPyrCellsPerRoot + pyr_offset(d) + (cy << d) + cx;
+}
+// best-key word: score << 44 | (0xfffff - position in vToDistributeKeys) << 24 | y << 12 | x.  The maximum is the highest
+// response, the FIRST such key in list order (:757-776), and carries its own coordinates.
+__device__ __forceinline__ unsigned long long pyr_best_word(uint32_t x, uint32_t y, uint32_t score, uint32_t pos) {
+    return ((unsigned long long)score << 44) | ((unsigned long long)(0xfffffu - pos) << 24) | ((unsigned long long)y << 12) | x;
+}
+__device__ __forceinline__ uint64_t pyr_best_key(unsigned long long w) {      // back to x | y << 16 | score << 32
+    return (uint64_t)(w & 0xfff) | ((uint64_t)((w >> 12) & 0xfff) << 16) | ((uint64_t)(w >> 44) << 32);
+}
+// one key into the pyramid's finest depth (any thread)
+__device__ __forceinline__ void pyr_insert(const PyrView& PV, uint32_t x, uint32_t y, uint32_t score, uint32_t pos, float hX, int nIni, int treeH) {
+    const int root = (int)__fdiv_rn((float)(int)x, hX);
+    if (root < 0 || root >= nIni) return;                              // RootClass: a key outside every root is in no node
+    int ax = (int)__fmul_rn(hX, (float)root), bx = (int)__fmul_rn(hX, (float)(root + 1)), ay = 0, by = treeH, cx = 0, cy = 0;
+#pragma unroll
+    for (int d = 0; d < kPyrDepth; ++d) {
+        const int mx = ax + ((bx - ax + 1) >> 1), my = ay + ((by - ay + 1) >> 1);      // split_of
+        if ((int)x < mx) { bx = mx; cx = 2 * cx; } else { ax = mx; cx = 2 * cx + 1; }
+        if ((int)y < my) { by = my; cy = 2 * cy; } else { ay = my; cy = 2 * cy + 1; }
+    }
+    const int cell = root * kPyrCellsPerRoot + pyr_offset(kPyrDepth) + (cy << kPyrDepth) + cx;
+    atomicAdd(PV.cnt + cell, 1u);
+    atomicMax(PV.best + cell, pyr_best_word(x, y, score, pos));
+}
+// coarser depths from the finest one (whole CTA; ends with a barrier)
+__device__ void pyr_reduce(const PyrView& PV, int nIni) {
+    for (int d = kPyrDepth - 1; d >= 0; --d) {
+        __syncthreads();
+        const int w = 1 << d, cells = w * w;
+        for (int i = threadIdx.x; i < nIni * cells; i += blockDim.x) {
+            const int root = i / cells, c = i - root * cells, cy = c >> d, cx = c & (w - 1);
+            const int child = root * kPyrCellsPerRoot + pyr_offset(d + 1) + ((2 * cy) << (d + 1)) + 2 * cx;
+            const int w2 = 2 * w;
+            PV.cnt[root * kPyrCellsPerRoot + pyr_offset(d) + c] = PV.cnt[child] + PV.cnt[child + 1] + PV.cnt[child + w2] + PV.cnt[child + w2 + 1];
+            const unsigned long long a = PV.best[child], b = PV.best[child + 1], e = PV.best[child + w2], f = PV.best[child + w2 + 1];
+            const unsigned long long m0 = a > b ? a : b, m1 = e > f ? e : f;
+            PV.best[root * kPyrCellsPerRoot + pyr_offset(d) + c] = m0 > m1 ? m0 : m1;
+        }
+    }
+    __syncthreads();
+}
+// child counts of the nodes proc[0..T) from the pyramid (threads firstThread.. of the CTA); a node at the finest depth raises *abort
+__device__ void pyr_children(TreeSmem& S, int cur, int T, const PyrView& PV, int firstThread, int* abort) {
+    for (int t = (int)threadIdx.x - firstThread; t >= 0 && t < T; t += kTreeThreads - firstThread) {
+        const int node = S.proc[t];
+        const uint32_t a = S.beg[cur][node];
+        const int root = (int)(a >> 28), d = (int)((a >> 24) & 15), cy = (int)((a >> 12) & 0xfff), cx = (int)(a & 0xfff);
+        if (d >= kPyrDepth) { *abort = 1; S.cc[node] = make_uint4(0, 0, 0, 0); continue; }
+        const int w2 = 2 << d;
+        const uint32_t* c = PV.cnt + root * kPyrCellsPerRoot + pyr_offset(d + 1) + (2 * cy) * w2 + 2 * cx;
+        S.cc[node] = make_uint4(c[0], c[1], c[w2], c[w2 + 1]);          // n1 (x<,y<), n2 (x>=,y<), n3 (x<,y>=), n4
+    }
+}
+
 // Stable 4-way partition of src[beg, beg+cnt) into dst starting at outBase, by one warp.  Returns class counts.
 // The loops are bound by the L2 round trip of their key loads, not by the ballots: keys are therefore fetched kPartU
 // blocks of 32 at a time (all loads of a group are issued before the first one is used), and a node of at most
@@ -246,6 +318,7 @@ __device__ void split_big_nodes(TreeSmem& S, int cur, int T, uint64_t* const (&b
 
 // Rebuild the list after the nodes proc[0..T) (in processing order) were split.  Returns new size; *mOut = number
 // of splittable children (the new pending list, in the reference's push_back order).
+template <bool kPyr>
 __device__ int apply_splits(TreeSmem& S, int cur, int listSize, int T, int* sWarp, int* mOut) {
     const int tid = threadIdx.x;
     const int nxt = cur ^ 1;
@@ -278,7 +351,8 @@ __device__ int apply_splits(TreeSmem& S, int cur, int listSize, int T, int* sWar
             if (cn[q] > 0) {
                 const int idx = neTot - 1 - (S.scanA[t] + rl);
                 S.rect[nxt][idx] = cr[q];
-                S.beg[nxt][idx] = b | childFlag;
+                if (kPyr) S.beg[nxt][idx] = pyr_addr((int)(bf >> 28), (int)((bf >> 24) & 15) + 1, 2 * (int)(bf & 0xfff) + (q & 1), 2 * (int)((bf >> 12) & 0xfff) + (q >> 1));
+                else S.beg[nxt][idx] = b | childFlag;
                 S.cnt[nxt][idx] = cn[q];
                 if (cn[q] > 1) {
                     ise::Elem e;
@@ -378,22 +452,31 @@ __device__ long long g_treeProf[16];
 
 // The whole DistributeOctTree for one level.  Keys are in buf[0][0..n) in the reference's vToDistributeKeys order.
 // Writes the kept keys (one per final node, list order) to out[0..*outCount).
-__device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIni, float hX, int treeH,
-                                TreeSmem& S, uint64_t* out, int* outCount) {
+// kPyr: the count-pyramid form (PV filled by pyr_insert / pyr_reduce; buf is not touched); returns false when a node at the
+// pyramid's finest depth would have to be split - nothing has been written then and the caller runs the partitioning form.
+template <bool kPyr>
+__device__ bool distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIni, float hX, int treeH,
+                                TreeSmem& S, uint64_t* out, int* outCount, const PyrView PV = PyrView{nullptr, nullptr}) {
     __shared__ int sWarp[33];
     __shared__ int sCnt[kTreeWarps + 1][4];
     __shared__ int sT;
+    __shared__ int sAbort;
     const int tid = threadIdx.x, wid = tid >> 5, lane = tid & 31;
-    if (n == 0) { if (tid == 0) *outCount = 0; return; }
+    if (n == 0) { if (tid == 0) *outCount = 0; return true; }
     TPROF_T0();
 
-    // roots: stable grouping of the keys by (int)(x / hX) into buf[1]
-    int outBase = 0;
-    for (int gb = 0; gb < nIni; gb += 4) {
-        RootClass rc; rc.hX = hX; rc.base = gb;
-        const uint4 c = cta_partition4(buf[0], buf[1], 0, n, outBase, rc, sCnt);
-        if (tid == 0) { S.scanB[gb] = c.x; S.scanB[gb + 1] = c.y; S.scanB[gb + 2] = c.z; S.scanB[gb + 3] = c.w; }
-        outBase += c.x + c.y + c.z + c.w;
+    if (kPyr) {
+        if (tid == 0) sAbort = 0;
+        if (tid < nIni) S.scanB[tid] = (int)PV.cnt[tid * kPyrCellsPerRoot];
+    } else {
+        // roots: stable grouping of the keys by (int)(x / hX) into buf[1]
+        int outBase = 0;
+        for (int gb = 0; gb < nIni; gb += 4) {
+            RootClass rc; rc.hX = hX; rc.base = gb;
+            const uint4 c = cta_partition4(buf[0], buf[1], 0, n, outBase, rc, sCnt);
+            if (tid == 0) { S.scanB[gb] = c.x; S.scanB[gb + 1] = c.y; S.scanB[gb + 2] = c.z; S.scanB[gb + 3] = c.w; }
+            outBase += c.x + c.y + c.z + c.w;
+        }
     }
     __syncthreads();
     int cur = 0;
@@ -404,7 +487,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
             if (c > 0) {
                 S.rect[0][sz] = make_ushort4((unsigned short)(int)__fmul_rn(hX, (float)i), 0,
                                              (unsigned short)(int)__fmul_rn(hX, (float)(i + 1)), (unsigned short)treeH);
-                S.beg[0][sz] = (uint32_t)b | 0x80000000u;
+                S.beg[0][sz] = kPyr ? pyr_addr(i, 0, 0, 0) : ((uint32_t)b | 0x80000000u);
                 S.cnt[0][sz] = c;
                 ++sz;
             }
@@ -427,13 +510,19 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
             if (S.cnt[cur][i] > 1) S.proc[S.scanA[i]] = (uint16_t)i;
         __syncthreads();
         TPROF(2);
-        split_big_nodes(S, cur, T, buf, sCnt);
-        TPROF(3);
-        split_nodes(S, cur, T, buf, sCnt, 0);
-        __syncthreads();
+        if (kPyr) {
+            pyr_children(S, cur, T, PV, 0, &sAbort);
+            __syncthreads();
+            if (sAbort) return false;
+        } else {
+            split_big_nodes(S, cur, T, buf, sCnt);
+            TPROF(3);
+            split_nodes(S, cur, T, buf, sCnt, 0);
+            __syncthreads();
+        }
         TPROF(4);
         int m;
-        listSize = apply_splits(S, cur, listSize, T, sWarp, &m);
+        listSize = apply_splits<kPyr>(S, cur, listSize, T, sWarp, &m);
         cur ^= 1;
         TPROF(5);
         if (listSize >= N || listSize == prevSize) {
@@ -446,9 +535,15 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
                 // std::sort emulation by warp 0 while the other warps pre-split every pending node
                 if (wid == 0) warp_sort_nodes(S.pend, m, reinterpret_cast<uint32_t*>(S.scanB), reinterpret_cast<uint32_t*>(S.scanB) + (S.scanCap >> 1),
                                               reinterpret_cast<uint32_t*>(S.scanA));
-                split_nodes(S, cur, m, buf, sCnt, 1);
-                __syncthreads();
-                split_big_nodes(S, cur, m, buf, sCnt);
+                if (kPyr) {
+                    pyr_children(S, cur, m, PV, 32, &sAbort);
+                    __syncthreads();
+                    if (sAbort) return false;
+                } else {
+                    split_nodes(S, cur, m, buf, sCnt, 1);
+                    __syncthreads();
+                    split_big_nodes(S, cur, m, buf, sCnt);
+                }
                 // processing order = sorted order from the back; stop as soon as the list reaches N
                 for (int t = tid; t < m; t += kTreeThreads) {
                     const int node = S.pend[m - 1 - t].id;
@@ -465,7 +560,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
                 __syncthreads();
                 const int T2 = sT;
                 __syncthreads();
-                listSize = apply_splits(S, cur, listSize, T2, sWarp, &m);
+                listSize = apply_splits<kPyr>(S, cur, listSize, T2, sWarp, &m);
                 cur ^= 1;
                 TPROF(7);
                 if (listSize >= N || listSize == prev2) finish = true;
@@ -474,6 +569,12 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
     }
 
     // keep the best response of every node; first maximum wins (:757-776)
+    if (kPyr) {
+        for (int i = tid; i < listSize; i += kTreeThreads) out[i] = pyr_best_key(PV.best[pyr_cell(S.beg[cur][i])]);
+        if (tid == 0) *outCount = listSize;
+        TPROF(8);
+        return true;
+    }
     for (int i = wid; i < listSize; i += kTreeWarps) {
         const uint32_t bf = S.beg[cur][i];
         const uint64_t* seg = buf[bf >> 31] + (bf & 0x7fffffffu);
@@ -495,6 +596,7 @@ __device__ void distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
     }
     if (tid == 0) *outCount = listSize;
     TPROF(8);
+    return true;
 }
 
 }  // namespace orbx

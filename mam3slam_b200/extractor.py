@@ -208,14 +208,21 @@ class ORBextractor:
               "orbx_debug_sort_nodes")
         return perm
 
-    def debug_distribute(self, keys, minX, maxX, minY, maxY, N):
+    def debug_distribute(self, keys, minX, maxX, minY, maxY, N, pyramid=None):
+        """Standalone DistributeOctTree.  pyramid = None: the partitioning form; True: the count-pyramid form first, returns
+        (keys, used_pyramid) - used_pyramid is False when a node deeper than the pyramid made the partitioning form take over."""
         keys = np.ascontiguousarray(keys, np.int32).reshape(-1, 3)
         cap = max(N + 64, 4 * 64)
         out = np.empty((cap, 3), np.int32)
         n = C.c_int(0)
-        check(self._L.orbx_debug_distribute(self._h, _p(keys), len(keys), minX, maxX, minY, maxY, N, _p(out), cap,
-                                            C.byref(n)), self._h, "orbx_debug_distribute")
-        return out[:n.value].copy()
+        if pyramid is None:
+            check(self._L.orbx_debug_distribute(self._h, _p(keys), len(keys), minX, maxX, minY, maxY, N, _p(out), cap,
+                                                C.byref(n)), self._h, "orbx_debug_distribute")
+            return out[:n.value].copy()
+        used = C.c_int(0)
+        check(self._L.orbx_debug_distribute2(self._h, _p(keys), len(keys), minX, maxX, minY, maxY, N, int(bool(pyramid)), _p(out), cap,
+                                             C.byref(n), C.byref(used)), self._h, "orbx_debug_distribute2")
+        return out[:n.value].copy(), bool(used.value)
 
     # ---- bookkeeping ----
     def launch_count(self):
