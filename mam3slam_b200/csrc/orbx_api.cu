@@ -336,11 +336,11 @@ int configureShape(Extractor* E, int W, int H) {
         CK(cudaMemcpy(E->dCellOrder, order.data(), order.size() * sizeof(int), cudaMemcpyHostToDevice));
     }
     if (E->treeSmem > 220 * 1024) { E->err = "nfeatures too large for on-chip quadtree state"; return ORBX_ERR_UNSUPPORTED; }
-    {   // count-pyramid form of the quadtree (orbx_kernels_tree.cuh): 12 bytes x 1365 cells per root on top of the list state
+    {   // count-pyramid form of the quadtree (orbx_kernels_tree.cuh): 8 bytes x 1365 cells per root on top of the list state
         int roots = 0;
         for (int l = 0; l < L; ++l) roots = std::max(roots, g.lv[l].nIni);
         const char* pe = getenv("ORBX_TREE_PYRAMID");                     // A/B switch
-        const size_t withPyr = align16(E->treeSmem) + (size_t)roots * kPyrCellsPerRoot * 12;
+        const size_t withPyr = align16(E->treeSmem) + (size_t)roots * kPyrCellsPerRoot * 8;
         E->pyrRoots = (roots <= kPyrMaxRoots && withPyr <= 100 * 1024 && !(pe && atoi(pe) == 0)) ? roots : 0;
         if (E->pyrRoots) E->treeSmem = withPyr;
     }
@@ -1133,9 +1133,8 @@ int orbx_debug_distribute2(orbx_handle h, const int* keys, int n, int min_x, int
     const float hX = (float)treeW / nIni;
     const int P = std::max(n_features + 3, 4 * nIni) + 5;
     const int scanCap = std::max(P, 64) + 8;
-    const size_t smem = align16(tree_smem_layout(P, scanCap, nullptr, nullptr)) + (size_t)kPyrMaxRoots * kPyrCellsPerRoot * 12;
+    const size_t smem = align16(tree_smem_layout(P, scanCap, nullptr, nullptr)) + (size_t)kPyrMaxRoots * kPyrCellsPerRoot * 8;
     if (smem > 200 * 1024) return ORBX_ERR_UNSUPPORTED;
-    if (use_pyramid && (treeW >= 4096 || treeH >= 4096)) use_pyramid = 0;
     CK(raise_dyn_smem((const void*)k_debug_distribute, E->device, 200 * 1024));
     std::vector<uint64_t> k(std::max(n, 1));
     for (int i = 0; i < n; ++i)

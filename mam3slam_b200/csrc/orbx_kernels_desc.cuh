@@ -52,10 +52,10 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
     TPROF_T0();
     // count pyramid (orbx_kernels_tree.cuh): filled while the candidates are gathered, when the level's geometry fits its words
     PyrView PV{nullptr, nullptr};
-    const bool pyr = pyrRoots > 0 && L.nIni <= pyrRoots && L.treeW < 4096 && L.treeH < 4096 && L.candCap < (1 << 20);
+    const bool pyr = pyrRoots > 0 && L.nIni <= pyrRoots && L.candCap < (1 << 20);
     if (pyr) {
-        PV.best = reinterpret_cast<unsigned long long*>(smem + align16(treeBytes));
-        PV.cnt = reinterpret_cast<uint32_t*>(PV.best + (size_t)pyrRoots * kPyrCellsPerRoot);
+        PV.best = reinterpret_cast<uint32_t*>(smem + align16(treeBytes));
+        PV.cnt = PV.best + (size_t)pyrRoots * kPyrCellsPerRoot;
         for (int i = tid; i < L.nIni * kPyrCellsPerRoot; i += kTreeThreads) { PV.best[i] = 0; PV.cnt[i] = 0; }
     }
     for (int i = tid; i < nc; i += kTreeThreads) S.scanA[i] = cc[i];
@@ -99,8 +99,8 @@ __global__ void __launch_bounds__(kTreeThreads) k_debug_distribute(uint64_t* buf
     if (threadIdx.x == 0) outCount[1] = 0;
     if (usePyr && nIni <= kPyrMaxRoots && n < (1 << 20)) {
         PyrView PV;
-        PV.best = reinterpret_cast<unsigned long long*>(smem + align16(treeBytes));
-        PV.cnt = reinterpret_cast<uint32_t*>(PV.best + (size_t)kPyrMaxRoots * kPyrCellsPerRoot);
+        PV.best = reinterpret_cast<uint32_t*>(smem + align16(treeBytes));
+        PV.cnt = PV.best + (size_t)kPyrMaxRoots * kPyrCellsPerRoot;
         for (int i = threadIdx.x; i < nIni * kPyrCellsPerRoot; i += kTreeThreads) { PV.best[i] = 0; PV.cnt[i] = 0; }
         __syncthreads();
         for (int i = threadIdx.x; i < n; i += kTreeThreads) {

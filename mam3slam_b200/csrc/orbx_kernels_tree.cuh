@@ -97,7 +97,7 @@ struct RootClass {
 constexpr int kPyrDepth = 5;
 constexpr int kPyrCellsPerRoot = (4 * 4 * 4 * 4 * 4 * 4 - 1) / 3;      // depths 0..5: 1365 cells
 constexpr int kPyrMaxRoots = 4;
-struct PyrView { uint32_t* cnt; unsigned long long* best; };
+struct PyrView { uint32_t* cnt; uint32_t* best; };
 __host__ __device__ inline int pyr_offset(int d) { return ((1 << (2 * d)) - 1) / 3; }
 // node address in pyramid form (kept in TreeSmem::beg): root << 28 | depth << 24 | cy << 12 | cx
 __device__ __forceinline__ uint32_t pyr_addr(int root, int d, int cx, int cy) { return ((uint32_t)root << 28) | ((uint32_t)d << 24) | ((uint32_t)cy << 12) | (uint32_t)cx; }
@@ -105,16 +105,14 @@ __device__ __forceinline__ int pyr_cell(uint32_t a) {
     const int root = (int)(a >> 28), d = (int)((a >> 24) & 15), cy = (int)((a >> 12) & 0xfff), cx = (int)(a & 0xfff);
     return root * kPyrCellsPerRoot + pyr_offset(d) + (cy << d) + cx;
 }
-// best-key word: score << 44 | (0xfffff - position in vToDistributeKeys) << 24 | y << 12 | x.  The maximum is the highest
-// response, the FIRST such key in list order (:757-776), and carries its own coordinates.
-__device__ __forceinline__ unsigned long long pyr_best_word(uint32_t x, uint32_t y, uint32_t score, uint32_t pos) {
-    return ((unsigned long long)score << 44) | ((unsigned long long)(0xfffffu - pos) << 24) | ((unsigned long long)y << 12) | x;
-}
-__device__ __forceinline__ uint64_t pyr_best_key(unsigned long long w) {      // back to x | y << 16 | score << 32
-    return (uint64_t)(w & 0xfff) | ((uint64_t)((w >> 12) & 0xfff) << 16) | ((uint64_t)(w >> 44) << 32);
-}
+// best-key word (32 bits, so that the shared-memory atomicMax is one native instruction): score << 20 | (0xfffff - position in
+// vToDistributeKeys).  The maximum is the highest response and, among equals, the FIRST key in list order (:757-776); the key
+// itself is read back from the gathered list by its position.
+__device__ __forceinline__ uint32_t pyr_best_word(uint32_t score, uint32_t pos) { return (score << 20) | (0xfffffu - pos); }
+__device__ __forceinline__ uint32_t pyr_best_pos(uint32_t w) { return 0xfffffu - (w & 0xfffffu); }
 // one key into the pyramid's finest depth (any thread)
 __device__ __forceinline__ void pyr_insert(const PyrView& PV, uint32_t x, uint32_t y, uint32_t score, uint32_t pos, float hX, int nIni, int treeH) {
+    score = min(score, 0xfffu);
     const int root = (int)__fdiv_rn((float)(int)x, hX);
     if (root < 0 || root >= nIni) return;                              // RootClass: a key outside every root is in no node
     int ax = (int)__fmul_rn(hX, (float)root), bx = (int)__fmul_rn(hX, (float)(root + 1)), ay = 0, by = treeH, cx = 0, cy = 0;
@@ -126,7 +124,7 @@ __device__ __forceinline__ void pyr_insert(const PyrView& PV, uint32_t x, uint32
     }
     const int cell = root * kPyrCellsPerRoot + pyr_offset(kPyrDepth) + (cy << kPyrDepth) + cx;
     atomicAdd(PV.cnt + cell, 1u);
-    atomicMax(PV.best + cell, pyr_best_word(x, y, score, pos));
+    atomicMax(PV.best + cell, pyr_best_word(score, pos));
 }
 // coarser depths from the finest one (whole CTA; ends with a barrier)
 __device__ void pyr_reduce(const PyrView& PV, int nIni) {
@@ -138,9 +136,7 @@ __device__ void pyr_reduce(const PyrView& PV, int nIni) {
             const int child = root * kPyrCellsPerRoot + pyr_offset(d + 1) + ((2 * cy) << (d + 1)) + 2 * cx;
             const int w2 = 2 * w;
             PV.cnt[root * kPyrCellsPerRoot + pyr_offset(d) + c] = PV.cnt[child] + PV.cnt[child + 1] + PV.cnt[child + w2] + PV.cnt[child + w2 + 1];
-            const unsigned long long a = PV.best[child], b = PV.best[child + 1], e = PV.best[child + w2], f = PV.best[child + w2 + 1];
-            const unsigned long long m0 = a > b ? a : b, m1 = e > f ? e : f;
-            PV.best[root * kPyrCellsPerRoot + pyr_offset(d) + c] = m0 > m1 ? m0 : m1;
+            PV.best[root * kPyrCellsPerRoot + pyr_offset(d) + c] = max(max(PV.best[child], PV.best[child + 1]), max(PV.best[child + w2], PV.best[child + w2 + 1]));
         }
     }
     __syncthreads();
@@ -570,7 +566,7 @@ __device__ bool distribute_tree(uint64_t* const (&buf)[2], int n, int N, int nIn
 
     // keep the best response of every node; first maximum wins (:757-776)
     if (kPyr) {
-        for (int i = tid; i < listSize; i += kTreeThreads) out[i] = pyr_best_key(PV.best[pyr_cell(S.beg[cur][i])]);
+        for (int i = tid; i < listSize; i += kTreeThreads) out[i] = buf[0][pyr_best_pos(PV.best[pyr_cell(S.beg[cur][i])])];
         if (tid == 0) *outCount = listSize;
         TPROF(8);
         return true;
