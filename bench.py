@@ -769,7 +769,7 @@ def run_gpu(args):
     total_frames = B * bps * args.steps * world
     hamming = None if args.no_knn else knn_bench(args, torch, dist, rank, world, local)
     kitti = None if args.no_kitti else kitti_bench(args, torch, dist, rank, world, local)
-    latency = latency_bench(args, torch, local, frames) if rank == 0 else None
+    latency = latency_bench(args, torch, local, frames) if rank == 0 and not args.no_latency else None
     if latency is not None:
         latency["agents_one_frame_in_flight"] = agents_in_flight(local, frames)
     if latency is not None and not args.no_cpu:
@@ -972,6 +972,7 @@ def main():
     ap.add_argument("--no-kitti", action="store_true", help="skip the KITTI-shaped leg (config 3)")
     ap.add_argument("--no-knn", action="store_true", help="skip the 1M x 2000 k-NN leg (config 5)")
     ap.add_argument("--no-sparse", action="store_true", help="skip the sparse-texture leg")
+    ap.add_argument("--no-latency", action="store_true", help="skip the one-frame-in-flight legs (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -4,7 +4,7 @@
 # (3) launch list (durations only) of the whole command.
 TAG=${1:-r2a}
 mkdir -p gpurun_out
-CMD="python bench.py --steps 2 --warmup 3 --batches-per-step 1 --no-cpu --no-kitti --no-sparse --pipes 1 --e2e-pipes 1"
+CMD="python bench.py --steps 2 --warmup 3 --batches-per-step 1 --no-cpu --no-kitti --no-sparse --no-latency --pipes 1 --e2e-pipes 1"
 $CMD > gpurun_out/${TAG}_plain.json 2> gpurun_out/${TAG}_plain.err || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain.err; exit 1; }
 # launches before the first timed batch: handle creation pass (14) + 8 graph-priming batches + 3 warm-up batches (18 each)
 SKIP=$((14 + 11 * 18))
