@@ -204,6 +204,12 @@ int orbm_knn_merge(const uint16_t* dist, const int32_t* idx, int nshards, int nq
 int orbm_knn_merge_device(orbm_handle h, const void* d_dist, const void* d_idx, size_t shard_stride_bytes, int nshards, int nq,
                           int k, uint16_t* d_out_dist, int32_t* d_out_idx, void* stream);
 
+/* The same search on the tensor cores (A/B beside orbm_knn_device, which stays the default; no counterpart in the reference):
+ * Hamming(q, r) = popc(q) + popc(r) - 2 <q, r>, the dot products computed exactly by tcgen05.mma kind::i8 on bits expanded to
+ * bytes on chip (mam3slam_b200/csrc/orbm_kernels_tc.cuh).  Same arguments, same result bit for bit. */
+int orbm_knn_device_tc(orbm_handle h, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx,
+                       void* stream);
+
 /* ---- sharded k-NN over peer memory (map-sharded search of SURVEY.md 8e; the reference is one CPU process with one address
  * space and has no counterpart) ------------------------------------------------------------------------------------------
  * One process per GPU; rank r holds rows [row_offset, row_offset + n) of the database (orbm_db) and a replica of the queries.

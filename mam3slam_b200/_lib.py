@@ -123,6 +123,7 @@ def _bind_matcher(L):
     L.orbm_db_destroy.restype = None
     L.orbm_knn.argtypes = [vp, vp, vp, i32, i32, vp, vp]
     L.orbm_knn_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
+    L.orbm_knn_device_tc.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
     L.orbm_xchg_create.argtypes = [vp, i32, i32, i32, i32, C.POINTER(vp)]
     L.orbm_xchg_ipc_handle.argtypes = [vp, vp]
     L.orbm_xchg_open.argtypes = [vp, i32, vp]

@@ -1,6 +1,7 @@
 // C ABI of the B200-native ORB matcher (include/orbm.h): handle / frame management, query marshalling, launches.
 // Host-side logic mirrors what each ORBmatcher method does before and after its Hamming loop (src/ORBmatcher.cc).
 #include "orbm_kernels.cuh"
+#include "orbm_kernels_tc.cuh"
 #include "orbx_internal.h"
 #include <algorithm>
 #include <atomic>
@@ -986,6 +987,46 @@ int orbm_knn_device(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k
     if (knnShareBound(P)) F.bound = M->knnBound;
     launchKnn(M, P, qpt, db, d_q, nq, k, F, st);
     if (!fused) { k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, P.nchunks, nq, k, d_dist, d_idx, F.bound); ++M->launches; }
+    M->lastEvals = (long long)nq * db->n;
+    CKM(cudaGetLastError());
+    return ORBM_OK;
+}
+
+// ---- k-NN on the tensor cores (A/B beside orbm_knn_device; orbm_kernels_tc.cuh) -----------------------------------------------
+namespace {
+extern "C++" template <int kK>
+void launchKnnTc(orbm_matcher* M, int qtiles, int nchunks, long long rowsPerChunk, orbm_db db, const uint8_t* d_q, int nq, int k, cudaStream_t st) {
+    k_knn_tc<kK><<<dim3(qtiles, nchunks), kTcThreads, kTcSmemBytes, st>>>(reinterpret_cast<const uint32_t*>(d_q), nq, db->rows, db->n, db->rowOffset,
+                                                                          (int)rowsPerChunk, k, M->knnPart,
+                                                                          getenv("ORBM_TC_STATS") ? reinterpret_cast<unsigned long long*>(strtoull(getenv("ORBM_TC_STATS"), nullptr, 10)) : nullptr);
+}
+}  // namespace
+
+int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
+    if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
+    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    // one CTA per SM (its two operand stages and the whole TMEM): query tiles of 128 x as many row chunks as fill the SMs
+    const int qtiles = (nq + kTcM - 1) / kTcM;
+    const long long want = std::max<long long>(1, M->smCount / qtiles);
+    long long rows = (db->n + want - 1) / want;
+    rows = std::max<long long>(kTcN, (rows + kTcN - 1) / kTcN * kTcN);
+    rows = std::min<long long>(rows, (1LL << 22));
+    const int nchunks = (int)std::max<long long>(1, (db->n + rows - 1) / rows);
+    KnnPlan P; P.qblocks = 1; P.nchunks = nchunks; P.rowsPerChunk = rows;
+    int rc = knnScratch(M, P, nq, k);
+    if (rc) return rc;
+    CKM(orbx::raise_dyn_smem((const void*)k_knn_tc<2>, M->device, kTcSmemBytes));
+    CKM(orbx::raise_dyn_smem((const void*)k_knn_tc<4>, M->device, kTcSmemBytes));
+    CKM(orbx::raise_dyn_smem((const void*)k_knn_tc<8>, M->device, kTcSmemBytes));
+    CKM(orbx::raise_dyn_smem((const void*)k_knn_tc<kKnnMaxK>, M->device, kTcSmemBytes));
+    if (k <= 2) launchKnnTc<2>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
+    else if (k <= 4) launchKnnTc<4>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
+    else if (k <= 8) launchKnnTc<8>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
+    else launchKnnTc<kKnnMaxK>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx, nullptr);
+    M->launches += 2;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());
     return ORBM_OK;

@@ -436,6 +436,12 @@ class ORBmatcher:
         check_m(self._L.orbm_knn_device(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist), C.c_void_p(d_idx),
                                         C.c_void_p(stream or 0)), self._h, "orbm_knn_device")
 
+    def knn_device_tc(self, db, d_q, nq, k, d_dist, d_idx, stream=None):
+        """orbm_knn_device_tc: the brute-force search with the dot products on the tensor cores (tcgen05.mma kind::i8); same
+        arguments and the same result as knn_device (include/orbm.h)."""
+        check_m(self._L.orbm_knn_device_tc(self._h, db._db, C.c_void_p(d_q), int(nq), int(k), C.c_void_p(d_dist), C.c_void_p(d_idx),
+                                           C.c_void_p(stream or 0)), self._h, "orbm_knn_device_tc")
+
     def knn_device_static(self, db, d_q, nq, k, d_dist, d_idx, stream=None):
         """orbm_knn_device_static: the same search with its scratch in a fixed-size static device array; the call allocates
         nothing (include/orbm.h).  No counterpart in the reference."""

@@ -393,6 +393,37 @@ print(x0.status(), int((oi == -1).all()))
     assert r.stdout.split()[-2:] == ["1", "1"]
 
 
+@pytest.mark.parametrize("ndb,nq,k", [(50000, 300, 2), (70001, 2000, 2), (1000, 17, 1), (129, 5, 16), (7, 3, 4), (300000, 257, 5),
+                                      (40000, 129, 8)])
+def test_knn_tensor_core_kernel_equals_popc_kernel(M, ndb, nq, k):
+    """orbm_knn_device_tc (tcgen05.mma kind::i8 on bits expanded to bytes, accumulator D' = 2<q,r> - popc(r) in TMEM) against
+    orbm_knn_device (LOP3 / POPC): same distances, same row ids, same tie rule - and both against the CPU oracle on the small
+    cases.  Shapes cover several query tiles, several row chunks, partial tiles and every list depth the kernel is compiled for."""
+    import torch
+    from mam3slam_b200.matcher import KnnDatabase
+    q, rows = sc.knn_data(ndb, nq, seed=7 + k)
+    rows[ndb // 2] = rows[0]                                  # equal distances: the lower row id must win
+    if ndb > 200:
+        rows[5] = 0; rows[6] = 255                            # popcount 0 and 256 rows
+        q[0] = 0; q[min(1, nq - 1)] = 255
+    rows_dev, q_dev = torch.from_numpy(rows).cuda(), torch.from_numpy(q).cuda()
+    D = KnnDatabase(M, None, row_offset=1000, device_ptr=rows_dev.data_ptr(), n=ndb)
+    st = torch.cuda.current_stream().cuda_stream
+    outs = []
+    for fn in (M.knn_device, M.knn_device_tc):
+        dd = torch.full((nq, k), -7, dtype=torch.int16, device="cuda")
+        di = torch.full((nq, k), -7, dtype=torch.int32, device="cuda")
+        fn(D, q_dev.data_ptr(), nq, k, dd.data_ptr(), di.data_ptr(), st)
+        torch.cuda.synchronize()
+        outs.append((dd.cpu().numpy().view(np.uint16), di.cpu().numpy()))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    if ndb <= 70001:
+        od, oi = om.knn(q, rows, k)
+        oi = np.where(oi >= 0, oi + 1000, oi)
+        assert np.array_equal(outs[1][0], od) and np.array_equal(outs[1][1], oi)
+    D.close()
+
+
 def test_knn_merge_device_equals_host_merge(M):
     """config 5 exchange step: per-shard lists laid out as one (ids | distances) buffer per rank, merged on the device."""
     import torch
