@@ -95,6 +95,7 @@ TH_TRACK = 15.0                          # TrackWithMotionModel's first window (
 BOUNDS = (0.0, 0.0, float(W), float(H))
 WORKLOAD = ("single-agent EuRoC-shaped 752x480 synthetic mono stream per GPU, 1000 kp, 8 levels @1.2, FAST 20/7: per frame "
             "ORBextractor::operator() + SearchByProjection(Cur, Last, th=15, mono)")
+I8_MAC_PEAK = 8192.0 * 148 * 1.965e9        # tcgen05.mma kind::i8, measured issue rate (tools/tc_rate.cu)
 POPC_PEAK = 4.635e12                     # measured on this pool's B200 (profiles/int_peaks_b200.txt): 16.5 popc/clk/SM
 
 
@@ -522,6 +523,16 @@ def knn_bench(args, torch, dist, rank, world, local):
 
     ms_nccl = timed(step_nccl)
     ms = timed(step_peer) if world > 1 else ms_nccl
+
+    # A/B beside the POPC kernel (never instead of it: north_star's design is the integer pipe): the same search with the dot
+    # products on the tensor cores, tcgen05.mma kind::i8 (orbm_knn_device_tc), on this rank's shard; results must be identical
+    td_dev = torch.empty((NQ, K), dtype=torch.int16, device="cuda")
+    ti_dev = torch.empty((NQ, K), dtype=torch.int32, device="cuda")
+    ms_tc = timed(lambda: m.knn_device_tc(D, q.data_ptr(), NQ, K, td_dev.data_ptr(), ti_dev.data_ptr(), st))
+    m.knn_device(D, q.data_ptr(), NQ, K, dd.data_ptr(), di.data_ptr(), st)
+    torch.cuda.synchronize()
+    if not (torch.equal(td_dev, dd) and torch.equal(ti_dev, di)):
+        raise SystemExit("bench.py: tensor-core k-NN differs from the POPC kernel")
     # correctness of the merged result on rank 0: the planted neighbour (distance 1) is found for every query
     if world > 1:
         md, mi = ORBmatcher.knn_merge(torch.stack(gath_d).cpu().numpy().view(np.uint16).reshape(world, NQ, K), torch.stack(gath_i).cpu().numpy())
@@ -539,6 +550,17 @@ def knn_bench(args, torch, dist, rank, world, local):
                         "counters (orbm_knn_sharded), all inside the timed step" if world > 1 else ""),
            "ms": ms, "ms_nccl_allgather_variant": ms_nccl if world > 1 else None,
            "evaluations_per_s": eps, "planted_neighbours_found": ok,
+           "tensor_core_variant": {
+               "ms_local_shard": ms_tc, "evaluations_per_s_per_gpu": float(hi - lo) * NQ / (ms_tc * 1e-3),
+               "identical_to_popc_kernel": True,
+               "what": "orbm_knn_device_tc on this rank's rows (scan + chunk merge, no exchange): Hamming = popc(q) + popc(r) - 2<q,r>, "
+                       "dot products by tcgen05.mma kind::i8 (M=128 queries, N=256 rows, K=288 = 256 bit-bytes + 32 popcount bytes) on "
+                       "bits expanded to bytes in shared memory, s32 accumulators in TMEM, top-k per TMEM lane",
+               "roofline_tensor": {"bound": "tensor", "unit": "TMAC/s", "achieved": float(hi - lo) * NQ * 288 / (ms_tc * 1e-3) / 1e12,
+                                   "peak": I8_MAC_PEAK / 1e12, "frac": float(hi - lo) * NQ * 288 / (ms_tc * 1e-3) / I8_MAC_PEAK,
+                                   "peak_source": "tools/tc_rate.cu on this pool: 128 cycles per 128x256x32 MMA = 8192 MAC/clk/SM x 148 SMs x 1.965 GHz",
+                                   "note": "tile time = MMA (1152 cycles) + accumulator read-out (128 KB at the 64 B/clk TMEM -> register rate): "
+                                           "the read-out, not the MMA, is the larger part (DESIGN.md 4)"}},
            "roofline_int": {"bound": "popc", "popc_issued_per_evaluation": 4, "achieved_popc_per_s": 4 * eps,
                             "peak_popc_per_s": POPC_PEAK * world, "frac": 4 * eps / (POPC_PEAK * world),
                             "popc8_equivalent_frac": 8 * eps / (POPC_PEAK * world),

@@ -1014,7 +1014,7 @@ int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, in
     rows = std::max<long long>(kTcN, (rows + kTcN - 1) / kTcN * kTcN);
     rows = std::min<long long>(rows, (1LL << 22));
     const int nchunks = (int)std::max<long long>(1, (db->n + rows - 1) / rows);
-    KnnPlan P; P.qblocks = 1; P.nchunks = nchunks; P.rowsPerChunk = rows;
+    KnnPlan P; P.qblocks = 1; P.nchunks = nchunks * kTcSlices; P.rowsPerChunk = rows;      // kTcSlices lists per (chunk, query)
     int rc = knnScratch(M, P, nq, k);
     if (rc) return rc;
     CKM(orbx::raise_dyn_smem((const void*)k_knn_tc<2>, M->device, kTcSmemBytes));
@@ -1025,7 +1025,7 @@ int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, in
     else if (k <= 4) launchKnnTc<4>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
     else if (k <= 8) launchKnnTc<8>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
     else launchKnnTc<kKnnMaxK>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
-    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks, nq, k, d_dist, d_idx, nullptr);
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks * kTcSlices, nq, k, d_dist, d_idx, nullptr);
     M->launches += 2;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());
