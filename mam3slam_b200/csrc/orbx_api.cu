@@ -74,6 +74,11 @@ struct Extractor {
     FsMaps pyrMaps{};                // m[l] = SOURCE level l-1 with the box of the resize to level l (m[1] per pass)
     PyrBox pyrBox[kMaxLevels] = {};  // boxW = 0: level l keeps k_pyr_level_fast / k_pyr_level
     bool pyrTma = true;              // ORBX_PYR_TMA=0 (A/B switch)
+    int smCount = 148;
+    bool pyrChainOk = false;         // all levels of a few frames in ONE launch (k_pyr_chain_tma); ORBX_PYR_CHAIN=0 switches it off
+    PyrChain pyrChain{};
+    size_t pyrChainSmem = 0;
+    unsigned int* dPyrArrive = nullptr;   // arrival counters [max_batch][kMaxLevels], zero at rest
     bool descTma = true;             // ORBX_DESC_TMA=0: k_orient_brief with global gathers (A/B switch)
     bool blurTma = true;             // ORBX_BLUR_TMA=0: the register-only k_blur7 (A/B switch; also the fallback when level 0 is not TMA-addressable)
     NmsTabs nmsTabs{};               // same-cell column / row masks of the non-max suppression
@@ -401,6 +406,8 @@ int configureShape(Extractor* E, int W, int H) {
     if ((rc = devAlloc(E, &E->dCand, (size_t)g.candCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dCellCount, (size_t)g.nCells * B))) return rc;
     if ((rc = devAlloc(E, &E->dCbits, (size_t)E->fsPlan.bitsPerFrame * B))) return rc;
+    if ((rc = devAlloc(E, &E->dPyrArrive, (size_t)B * kMaxLevels))) return rc;
+    CK(cudaMemset(E->dPyrArrive, 0, (size_t)B * kMaxLevels * sizeof(unsigned int)));
     memset(&E->fsMaps, 0, sizeof(E->fsMaps));
     memset(&E->scoreMaps, 0, sizeof(E->scoreMaps));
     memset(&E->blurMaps, 0, sizeof(E->blurMaps));
@@ -416,6 +423,23 @@ int configureShape(Extractor* E, int W, int H) {
                                                  g.lv[l - 1].planeBytes, E->pyrBox[l].boxH, E->pyrBox[l].boxW) ? 1 : 0;
         if (l > 0) E->oriMaps.tmaOk[l] = encodeLevelMap(&E->oriMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kOtBoxH, kOtBoxW) ? 1 : 0;
         if (l > 0) E->blurMaps.tmaOk[l] = encodeLevelMap(&E->blurMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kBtBoxH, kBtBoxW) ? 1 : 0;
+    }
+    cudaDeviceGetAttribute(&E->smCount, cudaDevAttrMultiProcessorCount, E->device);
+    {   // chained pyramid: usable when every level takes the TMA kernel
+        const char* ce = getenv("ORBX_PYR_CHAIN");
+        bool ok = E->pyrTma && L > 1 && !(ce && atoi(ce) == 0);
+        int tiles = 0; size_t smem = 0;
+        for (int l = 1; l < L && ok; ++l) {
+            if (!E->pyrFast[l] || E->pyrBox[l].boxW == 0 || (l > 1 && !E->pyrMaps.tmaOk[l])) { ok = false; break; }
+            E->pyrChain.tileBegin[l] = tiles;
+            E->pyrChain.tilesX[l] = (g.lv[l].w + 127) / 128;
+            E->pyrChain.box[l] = E->pyrBox[l];
+            tiles += E->pyrChain.tilesX[l] * ((g.lv[l].h + kPrTileH - 1) / kPrTileH);
+            smem = std::max(smem, (size_t)E->pyrBox[l].boxW * E->pyrBox[l].boxH);
+        }
+        E->pyrChain.tileBegin[L] = tiles;
+        E->pyrChainOk = ok && tiles > 0;
+        E->pyrChainSmem = smem;
     }
     {
         // same-cell masks of the 3x3 suppression.  The cells of a level form a regular grid (src/ORBextractor.cc:805-821: the
@@ -514,7 +538,20 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         ORBX_FAST_DISPATCH(E->aux[slot], 0, nA0, E->fastRowsA, E->fastSmemA);
         CK(cudaEventRecord(E->evF0[slot], E->aux[slot]));
     }
-    for (int l = 1; l < L; ++l) {
+    // few frames: the whole pyramid in one launch (tiles of a level wait on the arrival counter of the level below); all tiles must
+    // be resident at once - 4 CTAs per SM is a conservative bound for 256 threads x 40 registers x <= 16 KB
+    bool chained = false;
+    if (E->pyrChainOk && (long long)n * E->pyrChain.tileBegin[L] <= (long long)E->smCount * 4 &&
+        ((((uintptr_t)l0.base | (uintptr_t)l0.pitch | (uintptr_t)l0.frameBytes) & 3) == 0)) {
+        FsMaps cm = E->pyrMaps;
+        if (encodeLevelMap(&cm.m[1], l0.base, g.lv[0].w, g.lv[0].h, fb + n, (size_t)l0.pitch, l0stride, E->pyrBox[1].boxH, E->pyrBox[1].boxW)) {
+            k_pyr_chain_tma<<<dim3(E->pyrChain.tileBegin[L], n), 256, E->pyrChainSmem, st>>>(cm, E->dGeom, E->dTaps, E->pyrChain, fb,
+                                                                                             E->dPyrArrive + (size_t)fb * kMaxLevels);
+            ++E->launches;
+            chained = true;
+        }
+    }
+    for (int l = 1; l < L && !chained; ++l) {
         dim3 grid((g.lv[l].w + 127) / 128, (g.lv[l].h + 7) / 8, n), block(32, 8);
         const bool srcAligned = l > 1 || ((((uintptr_t)l0.base | (uintptr_t)l0.pitch | (uintptr_t)l0.frameBytes) & 3) == 0);
         bool ptma = E->pyrTma && E->pyrFast[l] && srcAligned && E->pyrBox[l].boxW > 0;

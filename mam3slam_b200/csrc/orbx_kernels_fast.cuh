@@ -644,14 +644,12 @@ __global__ void __launch_bounds__(kDtWarps * 32) k_orient_brief_tma(const __grid
 struct PyrBox { int boxW, boxH; };
 constexpr int kPrTileH = 64, kPrRowsPerWarp = 8;
 
-__global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ CUtensorMap srcMap, const DevGeom* __restrict__ g, int l,
-                                                       const ResizeTap* __restrict__ taps, PyrBox pb, int frameBase) {
-    extern __shared__ __align__(128) uint8_t ptile[];
-    __shared__ __align__(8) uint64_t mbar;
+// one 128 x 64 tile of level l (tile column bx, tile row by) of `frame`; srcMap = tensor map of level l-1; whole CTA (256 threads)
+__device__ __forceinline__ void pyr_level_tile(const CUtensorMap* srcMap, const DevGeom* __restrict__ g, int l, const ResizeTap* __restrict__ taps,
+                                               PyrBox pb, int frame, int bx, int by, uint8_t* ptile, uint64_t& mbar) {
     const LevelGeom& D = g->lv[l];
     const LevelGeom& S = g->lv[l - 1];
-    const int frame = frameBase + blockIdx.z;
-    const int X0 = blockIdx.x * 128, Y0 = blockIdx.y * kPrTileH;
+    const int X0 = bx * 128, Y0 = by * kPrTileH;
     // tile origin in the source level: first tap of the CTA's first column (16-byte aligned) / first row (clamped like the taps)
     const int gx = taps[D.tabX + X0].ofs & ~15;
     const int gy = min(max(taps[D.tabY + Y0].ofs, 0), S.h - 1);
@@ -662,7 +660,7 @@ __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ C
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(pb.boxW * pb.boxH) : "memory");
         asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                     :: "r"(smem_addr(ptile)), "l"(reinterpret_cast<uint64_t>(&srcMap)), "r"(bar), "r"(gx), "r"(gy), "r"(frame)
+                     :: "r"(smem_addr(ptile)), "l"(reinterpret_cast<uint64_t>(srcMap)), "r"(bar), "r"(gx), "r"(gy), "r"(frame)
                      : "memory");
     }
     __syncthreads();                                           // the barrier object is initialised before anyone polls it
@@ -728,6 +726,55 @@ __global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ C
         if (fullI) *reinterpret_cast<uint32_t*>(d) = packed;
         else for (int k = 0; k < 4 && k < wLeft; ++k) d[k] = (uint8_t)(packed >> (8 * k));
         d += pitch;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pyr_level_tma(const __grid_constant__ CUtensorMap srcMap, const DevGeom* __restrict__ g, int l,
+                                                       const ResizeTap* __restrict__ taps, PyrBox pb, int frameBase) {
+    extern __shared__ __align__(128) uint8_t ptile[];
+    __shared__ __align__(8) uint64_t mbar;
+    pyr_level_tile(&srcMap, g, l, taps, pb, frameBase + blockIdx.z, blockIdx.x, blockIdx.y, ptile, mbar);
+}
+
+// The whole pyramid of a FEW frames in ONE launch (single-frame calls: seven dependent launches cost ~7 us each for ~2 us of work).
+// CTA = one tile of one level; the tiles are numbered level by level, so every tile a CTA depends on has a lower block index and
+// the host launches this only when ALL tiles are co-resident (no CTA can wait for one that has not been scheduled).  A tile of
+// level l > 1 waits until the arrival counter of level l-1 of its frame has reached that level's tile count; the producers bump
+// it after their stores (fence + atomic), the consumer acquires it and crosses to the async proxy before its TMA load.  The last
+// tile of the last level puts the frame's counters back to zero for the next pass.
+struct PyrChain {
+    int tileBegin[kMaxLevels + 1];       // first tile index of level l (l = 1 .. nlevels-1), tileBegin[nlevels] = total
+    int tilesX[kMaxLevels];
+    PyrBox box[kMaxLevels];
+};
+__global__ void __launch_bounds__(256) k_pyr_chain_tma(const __grid_constant__ FsMaps maps, const DevGeom* __restrict__ g,
+                                                       const ResizeTap* __restrict__ taps, const PyrChain pc, int frameBase,
+                                                       unsigned int* __restrict__ arrive /* [frame][kMaxLevels] */) {
+    extern __shared__ __align__(128) uint8_t ptile[];
+    __shared__ __align__(8) uint64_t mbar;
+    const int L = g->nlevels;
+    int l = 1;
+    while (l + 1 < L && (int)blockIdx.x >= pc.tileBegin[l + 1]) ++l;
+    const int t = (int)blockIdx.x - pc.tileBegin[l];
+    const int by = t / pc.tilesX[l], bx = t - by * pc.tilesX[l];
+    const int frame = frameBase + blockIdx.y;
+    unsigned int* cnt = arrive + (size_t)blockIdx.y * kMaxLevels;
+    if (l > 1) {
+        if (threadIdx.x == 0) {
+            const unsigned int need = (unsigned int)(pc.tileBegin[l] - pc.tileBegin[l - 1]);
+            unsigned int v;
+            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt + l - 1) : "memory"); } while (v < need);
+            asm volatile("fence.proxy.async;" ::: "memory");          // the level below was written through the generic proxy; TMA reads through the async one
+        }
+        __syncthreads();
+    }
+    pyr_level_tile(&maps.m[l], g, l, taps, pc.box[l], frame, bx, by, ptile, mbar);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int done = atomicAdd(cnt + l, 1u) + 1u;
+        if (l == L - 1 && done == (unsigned int)(pc.tileBegin[L] - pc.tileBegin[L - 1]))
+            for (int i = 1; i < L; ++i) cnt[i] = 0;                    // every tile of this frame has read what it needed
     }
 }
 

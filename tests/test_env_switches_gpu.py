@@ -53,5 +53,7 @@ def test_schedule_switches_do_not_change_results():
                 {"ORBX_DESC_TMA": "0"}, {"ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_GEN": "1"},
                 # pyramid levels with direct global loads instead of TMA-staged source tiles; everything pre-TMA at once
                 {"ORBX_PYR_TMA": "0"},
+                # one launch per pyramid level even for few frames (the default chains all levels of <= ~4 frames into one launch)
+                {"ORBX_PYR_CHAIN": "0"}, {"ORBX_PYR_CHAIN": "0", "ORBX_GRAPHS": "0"},
                 {"ORBX_PYR_TMA": "0", "ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_TMA": "0", "ORBX_GRAPHS": "0"}):
         assert _digest(env) == base, env
