@@ -59,3 +59,38 @@ def test_agents_concurrent_equals_serial_and_oracle():
                                        lk["x"], lk["y"], lk["octave"], lk["angle"], ld, 15.0, 100, True)
             assert cnm == onm and np.array_equal(ckm, okm) and onm > 100
         last = (k, d)
+
+
+@pytest.mark.gpu
+def test_device_resident_tracking_on_every_device_of_one_process():
+    """One process driving several GPUs (agent i -> GPU i mod G): the opt-in shared-memory limits of the search kernels are set
+    per device, so the device-resident tracking step must work - and give the same matches - on every device, not only on the
+    one that happened to be current when the first handle was made.  Needs >= 2 GPUs (skipped on a one-GPU box)."""
+    import torch
+    from mam3slam_b200 import ORBextractor, ORBmatcher
+    from mam3slam_b200._lib import device_count
+    if device_count() < 2:
+        pytest.skip("one GPU")
+    B, W, H = 8, 752, 480
+    frames = np.stack(synth.stream(W, H, 3, B))
+    ref = None
+    for dev_id in range(min(device_count(), 4)):
+        with torch.cuda.device(dev_id):
+            dev = torch.from_numpy(frames).cuda()
+            ex = ORBextractor(1000, 1.2, 8, 20, 7, device=dev_id, max_batch=B)
+            mt = ORBmatcher(0.9, True, device=dev_id)
+            ts = torch.cuda.Stream()
+            ex.extract_device(dev.data_ptr(), W * H, B, W, H, W, (0, 1000), ts.cuda_stream)
+            dk, dd, dc, stride = ex.results_batch_device()
+            kpm = torch.empty((B, stride), dtype=torch.int32, device="cuda")
+            nmt = torch.empty(B, dtype=torch.int32, device="cuda")
+            mt.track_batch_device(B, dk, dd, dc, stride, (0., 0., float(W), float(H)), ex.GetScaleFactors(), 15.0, kpm.data_ptr(),
+                                  nmt.data_ptr(), stream=ts.cuda_stream)
+            ts.synchronize()
+            got = (nmt.cpu().numpy().copy(), kpm.cpu().numpy().copy())
+            mt.close(); ex.close()
+        if ref is None:
+            ref = got
+            assert got[0][1:].min() > 100
+        else:
+            assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]), f"device {dev_id}"

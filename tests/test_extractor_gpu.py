@@ -145,3 +145,40 @@ def test_device_sort_emulation_matches_std_sort(oracle_mod):
         ref = oracle_mod.sort_nodes(size, ulx)
         assert np.array_equal(ex.debug_sort_nodes(size, ulx, 0), ref)
         assert np.array_equal(ex.debug_sort_nodes(size, ulx, 2), ref)
+
+
+@pytest.mark.parametrize("graphs", ["1", "0"])
+def test_two_extractor_sizes_interleaved_on_one_device(graphs):
+    """The reference's mono flow keeps a 5x-features extractor (mpIniORBextractor, src/Tracking.cc:600-606) beside the tracking
+    one on the same GPU and goes back to it after tracking loss.  The opt-in shared-memory limits of the kernels are per function
+    and per device, not per handle: the small extractor must never lower what the big one needs (with graph replay and with
+    direct launches).  Each call must reproduce what a fresh extractor of the same size returns for the same frame."""
+    import hashlib, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    prog = r'''
+import hashlib, sys, numpy as np
+sys.path.insert(0, %r)
+from mam3slam_b200 import ORBextractor, synth
+frames = [synth.frame(752, 480, i) for i in range(3)]
+def digest(ex, f):
+    mono, k, d = ex(f)
+    return hashlib.sha256(np.int32(mono).tobytes() + k.tobytes() + d.tobytes()).hexdigest()
+ref = {}
+for n in (5000, 1000):
+    ex = ORBextractor(n, 1.2, 8, 20, 7)
+    ref[n] = [digest(ex, f) for f in frames]
+    ex.close()
+big, small = ORBextractor(5000, 1.2, 8, 20, 7), ORBextractor(1000, 1.2, 8, 20, 7)
+ok = True
+for rnd in range(2):
+    for i, f in enumerate(frames):
+        ok &= digest(big, f) == ref[5000][i]
+        ok &= digest(small, f) == ref[1000][i]
+small2 = ORBextractor(1000, 1.2, 8, 20, 7)          # a handle created AFTER the big one has run
+ok &= digest(small2, frames[1]) == ref[1000][1]
+ok &= digest(big, frames[2]) == ref[5000][2]
+print("OK" if ok else "MISMATCH")
+''' % root
+    r = subprocess.run([sys.executable, "-c", prog], capture_output=True, text=True, timeout=600, env=dict(os.environ, ORBX_GRAPHS=graphs))
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.strip().splitlines()[-1] == "OK"
