@@ -523,6 +523,7 @@ def knn_bench(args, torch, dist, rank, world, local):
 
     ms_nccl = timed(step_nccl)
     ms = timed(step_peer) if world > 1 else ms_nccl
+    sharded_knn_tc = os.environ.get("ORBM_KNN_TC") == "1"       # A/B: the shard scanned by the tensor-core kernel inside orbm_knn_sharded
 
     # A/B beside the POPC kernel (never instead of it: north_star's design is the integer pipe): the same search with the dot
     # products on the tensor cores, tcgen05.mma kind::i8 (orbm_knn_device_tc), on this rank's shard; results must be identical
@@ -549,6 +550,7 @@ def knn_bench(args, torch, dist, rank, world, local):
                        ("; exchange of the per-rank lists by NVLink peer stores from the scan kernel + merge kernel waiting on arrival "
                         "counters (orbm_knn_sharded), all inside the timed step" if world > 1 else ""),
            "ms": ms, "ms_nccl_allgather_variant": ms_nccl if world > 1 else None,
+           "sharded_scan_kernel": ("k_knn_tc (ORBM_KNN_TC=1)" if sharded_knn_tc else "k_knn (POPC)") if world > 1 else None,
            "evaluations_per_s": eps, "planted_neighbours_found": ok,
            "tensor_core_variant": {
                "ms_local_shard": ms_tc, "evaluations_per_s_per_gpu": float(hi - lo) * NQ / (ms_tc * 1e-3),

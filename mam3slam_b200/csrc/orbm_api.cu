@@ -1002,15 +1002,13 @@ void launchKnnTc(orbm_matcher* M, int qtiles, int nchunks, long long rowsPerChun
 }
 }  // namespace
 
-int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
-    if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
-    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
-    CKM(cudaSetDevice(M->device));
-    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+namespace {
+// the scan half of the tensor-core search: per-(chunk, slice) lists in M->knnPart, *nLists of them per query
+int knnTcScan(orbm_matcher* M, orbm_db db, const uint8_t* d_q, int nq, int k, cudaStream_t st, int* nLists) {
     // one CTA per SM (its two operand stages and the whole TMEM): query tiles of 128 x as many row chunks as fill the SMs
     const int qtiles = (nq + kTcM - 1) / kTcM;
     const long long want = std::max<long long>(1, M->smCount / qtiles);
-    long long rows = (db->n + want - 1) / want;
+    long long rows = (std::max<long long>(db->n, 1) + want - 1) / want;
     rows = std::max<long long>(kTcN, (rows + kTcN - 1) / kTcN * kTcN);
     rows = std::min<long long>(rows, (1LL << 22));
     const int nchunks = (int)std::max<long long>(1, (db->n + rows - 1) / rows);
@@ -1025,8 +1023,22 @@ int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, in
     else if (k <= 4) launchKnnTc<4>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
     else if (k <= 8) launchKnnTc<8>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
     else launchKnnTc<kKnnMaxK>(M, qtiles, nchunks, rows, db, d_q, nq, k, st);
-    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nchunks * kTcSlices, nq, k, d_dist, d_idx, nullptr);
-    M->launches += 2;
+    ++M->launches;
+    *nLists = nchunks * kTcSlices;
+    return ORBM_OK;
+}
+}  // namespace
+
+int orbm_knn_device_tc(orbm_handle M, orbm_db db, const uint8_t* d_q, int nq, int k, uint16_t* d_dist, int32_t* d_idx, void* stream) {
+    if (!M || !db || !d_q || nq <= 0 || k < 1 || k > kKnnMaxK || !d_dist || !d_idx) return ORBM_ERR_INVALID;
+    if (db->rowOffset + db->n > 0x7fffffffLL) { M->err = "global row ids beyond int32"; return ORBM_ERR_UNSUPPORTED; }
+    CKM(cudaSetDevice(M->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    int nLists = 0;
+    int rc = knnTcScan(M, db, d_q, nq, k, st, &nLists);
+    if (rc) return rc;
+    k_knn_merge<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nLists, nq, k, d_dist, d_idx, nullptr);
+    ++M->launches;
     M->lastEvals = (long long)nq * db->n;
     CKM(cudaGetLastError());
     return ORBM_OK;
@@ -1131,14 +1143,16 @@ int orbm_knn_sharded(orbm_handle M, orbm_xchg X, orbm_db db, const uint8_t* d_q,
     for (int r = 0; r < X->world; ++r) if (!X->peer[r]) { M->err = "orbm_knn_sharded: a rank's exchange buffer has not been opened"; return ORBM_ERR_INVALID; }
     CKM(cudaSetDevice(M->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : M->stream;
+    // ORBM_KNN_TC=1 (A/B, every rank alike): the shard is scanned by the tensor-core kernel (orbm_kernels_tc.cuh); the exchange is the same
+    static const bool tcScan = [] { const char* e = getenv("ORBM_KNN_TC"); return e && atoi(e) != 0; }();
     const KnnPlan P = knnPlan(M, std::max<long long>(db->n, 1), nq, 1);
-    int rc = knnScratch(M, P, nq, k);
+    int rc = tcScan ? ORBM_OK : knnScratch(M, P, nq, k);
     if (rc) return rc;
     const int par = (int)(X->calls & 1);
     KnnFused F;
     memset(&F, 0, sizeof(F));
     F.world = X->world;
-    if (knnShareBound(P)) F.bound = M->knnBound;
+    if (!tcScan && knnShareBound(P)) F.bound = M->knnBound;
     for (int r = 0; r < X->world; ++r) {
         F.peerSlot[r] = reinterpret_cast<unsigned long long*>(X->peer[r]) + ((size_t)par * X->world + X->rank) * X->slotKeys;
         F.peerFlag[r] = reinterpret_cast<unsigned int*>(X->peer[r] + X->flagsOff) + par * kXchgMaxRanks + X->rank;
@@ -1147,7 +1161,13 @@ int orbm_knn_sharded(orbm_handle M, orbm_xchg X, orbm_db db, const uint8_t* d_q,
     // at the end of the scan); default: plain scan, then k_knn_merge_push with a warp per query.  Every rank must use the same
     // setting: the arrival counters count query blocks in one form and merge CTAs in the other.
     static const bool fused = [] { const char* e = getenv("ORBM_KNN_FUSED"); return e && atoi(e) != 0; }();
-    if (fused) {
+    if (tcScan) {
+        int nLists = 0;
+        if ((rc = knnTcScan(M, db, d_q, nq, k, st, &nLists))) return rc;
+        k_knn_merge_push<<<(nq + 7) / 8, 256, 0, st>>>(M->knnPart, nLists, nq, k, F);
+        ++M->launches;
+        X->expect[par] += (unsigned int)((nq + 7) / 8);
+    } else if (fused) {
         F.counter = M->knnCounter;
         launchKnn(M, P, 1, db, d_q, nq, k, F, st);
         X->expect[par] += (unsigned int)P.qblocks;     // nq is the same on every rank (the queries are replicated), so is qblocks

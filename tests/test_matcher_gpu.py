@@ -424,6 +424,19 @@ def test_knn_tensor_core_kernel_equals_popc_kernel(M, ndb, nq, k):
     D.close()
 
 
+def test_knn_sharded_with_tensor_core_scan():
+    """ORBM_KNN_TC=1: orbm_knn_sharded scans the shard with the tensor-core kernel; the switch is read once per process, so the
+    emulated-ranks test above is re-run in a child interpreter with it set."""
+    import os, subprocess, sys
+    if os.environ.get("ORBM_KNN_TC") == "1":
+        pytest.skip("already inside the child run")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_matcher_gpu.py"), "-x", "-q", "-m", "gpu", "-k",
+                        "sharded_peer_exchange"], capture_output=True, text=True, timeout=900, cwd=root, env=dict(os.environ, ORBM_KNN_TC="1"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
+    assert "2 passed" in r.stdout
+
+
 def test_knn_merge_device_equals_host_merge(M):
     """config 5 exchange step: per-shard lists laid out as one (ids | distances) buffer per rank, merged on the device."""
     import torch
