@@ -211,6 +211,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_knn_tc(const uint32_t* __rest
             for (int c0 = slice * kTcSliceCols; c0 < (slice + 1) * kTcSliceCols; c0 += 32) {
                 uint32_t v[32];
                 tc_ld32(v, tm + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * kTcN + c0));
+                if (c0 + 32 >= (slice + 1) * kTcSliceCols) {       // my last load of this stage is in registers: the stage is free
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&dEmpty[s])) : "memory");
+                }
                 // one compare for 32 evaluations - almost never taken once the list has warmed up
                 int m32 = (int)v[0];
 #pragma unroll
@@ -234,8 +238,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_knn_tc(const uint32_t* __rest
                     }
                 }
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&dEmpty[s])) : "memory");
             if (doStats && tid == 0) { atomicAdd(stats + 4, (unsigned long long)(p1s - p0s)); atomicAdd(stats + 5, (unsigned long long)(clock64() - p1s)); atomicAdd(stats + 6, 1ull); }
         }
         if (q < nq) {
