@@ -157,7 +157,10 @@ struct SearchParams {
     unsigned int* ticket;        // CTAs-done counter for the fused rotation epilogue (zeroed by the host)
 };
 
-constexpr int kSearchThreads = 512, kSearchWarps = kSearchThreads / 32, kSlab = 192, kSlots = 64;
+#ifndef ORBM_SEARCH_THREADS
+#define ORBM_SEARCH_THREADS 256      /* 512 measured 2.8 % slower per 64-frame step: a 512 x 122-register CTA holds an SM's whole register file for the 107 us of the in-order commit; 128: 0.22 ms tracking, no gain */
+#endif
+constexpr int kSearchThreads = ORBM_SEARCH_THREADS, kSearchWarps = kSearchThreads / 32, kSlab = 192, kSlots = 64;
 
 // dynamic shared memory of a search CTA: slabs + match state (+ the staged target frame); host and device agree on this
 __host__ __device__ inline size_t search_smem_bytes(int n, int state, bool stage) {
