@@ -75,6 +75,7 @@ struct Extractor {
     PyrBox pyrBox[kMaxLevels] = {};  // boxW = 0: level l keeps k_pyr_level_fast / k_pyr_level
     bool pyrTma = true;              // ORBX_PYR_TMA=0 (A/B switch)
     int smCount = 148;
+    int treeThreadsSmall = 256, treeThreadsLarge = 128;   // ORBX_TREE_THREADS_SMALL / _LARGE (A/B switches; 128, 256 or 512)
     bool pyrChainOk = false;         // all levels of a few frames in ONE launch (k_pyr_chain_tma); ORBX_PYR_CHAIN=0 switches it off
     PyrChain pyrChain{};
     size_t pyrChainSmem = 0;
@@ -425,6 +426,11 @@ int configureShape(Extractor* E, int W, int H) {
         if (l > 0) E->blurMaps.tmaOk[l] = encodeLevelMap(&E->blurMaps.m[l], g.lvl[l], g.lv[l].w, g.lv[l].h, B, (size_t)g.lv[l].pitch, g.lv[l].planeBytes, kBtBoxH, kBtBoxW) ? 1 : 0;
     }
     cudaDeviceGetAttribute(&E->smCount, cudaDevAttrMultiProcessorCount, E->device);
+    for (int which = 0; which < 2; ++which)
+        if (const char* tt = getenv(which ? "ORBX_TREE_THREADS_LARGE" : "ORBX_TREE_THREADS_SMALL")) {
+            const int v = atoi(tt);
+            if (v == 128 || v == 256 || v == 512) (which ? E->treeThreadsLarge : E->treeThreadsSmall) = v;
+        }
     {   // chained pyramid: usable when every level takes the TMA kernel
         const char* ce = getenv("ORBX_PYR_CHAIN");
         bool ok = E->pyrTma && L > 1 && !(ce && atoi(ce) == 0);
@@ -605,7 +611,9 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         launchBlur(E->aux[slot]);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
-    CK(launch_prio(k_octree, dim3(n, L), dim3(kTreeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
+    // few CTAs in flight: wide CTAs (latency of one frame); a full batch: narrow ones (see orbx_kernels_tree.cuh)
+    const int treeThreads = n * L <= E->smCount ? E->treeThreadsSmall : E->treeThreadsLarge;
+    CK(launch_prio(k_octree, dim3(n, L), dim3(treeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
                    E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb, E->pyrRoots));
     ++E->launches;
     mark();
@@ -1185,7 +1193,7 @@ int orbx_debug_distribute2(orbx_handle h, const int* keys, int n, int min_x, int
     int cnt = 0;
     std::vector<uint64_t> res(P);
     if (er == cudaSuccess) {
-        k_debug_distribute<<<1, kTreeThreads, smem, E->stream>>>(dA, dB, n, n_features, nIni, hX, treeH, dOut, dCnt, P, scanCap, use_pyramid);
+        k_debug_distribute<<<1, E->treeThreadsSmall, smem, E->stream>>>(dA, dB, n, n_features, nIni, hX, treeH, dOut, dCnt, P, scanCap, use_pyramid);
         ++E->launches;
         er = cudaStreamSynchronize(E->stream);
     }

@@ -36,7 +36,7 @@ __host__ __device__ inline size_t tree_smem_layout(int P, int scanCap, TreeSmem*
 
 // One CTA per (level, frame): gather the level's FAST candidates in the reference's order (cells row-major,
 // raster inside a cell), cull with the quadtree, leave the kept keys in list order.
-__global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
+__global__ void __launch_bounds__(kTreeMaxThreads) k_octree(const DevGeom* __restrict__ g, const FastCell* __restrict__ cells,
                                                          const uint32_t* __restrict__ cand, const int* __restrict__ cellCount,
                                                          uint64_t* qtA, uint64_t* qtB, uint64_t* lvlKp, int* lvlCnt,
                                                          int P, int scanCap, int frameBase, int pyrRoots) {
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(kTreeThreads) k_octree(const DevGeom* __restri
 
 // standalone tree for tests: keys (x | y<<16 | score<<32) already in bufA
 // usePyr: try the count-pyramid form first (outCount[1] = 1 when it completed, 0 when the partitioning form had to take over)
-__global__ void __launch_bounds__(kTreeThreads) k_debug_distribute(uint64_t* bufA, uint64_t* bufB, int n, int N, int nIni,
+__global__ void __launch_bounds__(kTreeMaxThreads) k_debug_distribute(uint64_t* bufA, uint64_t* bufB, int n, int N, int nIni,
                                                                    float hX, int treeH, uint64_t* out, int* outCount,
                                                                    int P, int scanCap, int usePyr) {
     extern __shared__ __align__(16) uint8_t smem[];
