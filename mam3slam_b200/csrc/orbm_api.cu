@@ -1369,7 +1369,9 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     T.qwin = (float4*)(b + oWin); T.qlev = (int2*)(b + oLev); T.qangle = (float*)(b + oAng); T.occ = b + oOcc;
     T.qResult = (int*)(b + oRes); T.qDist = (int*)(b + oDist); T.qBin = (int*)(b + oBin);
     T.kpMatch = d_kp_match; T.nMatches = d_nmatches; T.evals = M->dEvals;
-    T.stageTgt = search_smem_bytes(frame_stride, 1, true) <= kSearchSmemMax ? 1 : 0;
+    // ORBM_TRACK_STAGE=0 (A/B): the target frame stays in L2 instead of shared memory - a slower kernel with a third of the footprint
+    static const bool stageOk = [] { const char* e = getenv("ORBM_TRACK_STAGE"); return !(e && e[0] == '0'); }();
+    T.stageTgt = (stageOk && search_smem_bytes(frame_stride, 1, true) <= kSearchSmemMax) ? 1 : 0;
     const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0);
     if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
     CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));

@@ -1,7 +1,5 @@
 #!/bin/bash
-for p in ${PIPES:-1 2 3}; do
-  echo "== pipes $p"
-  timeout 300 python bench.py --no-cpu --no-knn --steps 20 --pipes $p 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read()); print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms', round(d['ms_per_step'],4), 'launches', d['gpu_launches'])"
+for p in 2 3 4 5; do
+  python bench.py --steps 10 --warmup 3 --no-kitti --no-knn --no-sparse --no-cpu --no-latency --pipes $p --e2e-pipes $p > /tmp/ab.json 2>/dev/null
+  python -c "import json; d=json.load(open('/tmp/ab.json')); print('pipes $p', round(d['value']), round(d['e2e']['value']))"
 done
