@@ -75,7 +75,7 @@ struct Extractor {
     PyrBox pyrBox[kMaxLevels] = {};  // boxW = 0: level l keeps k_pyr_level_fast / k_pyr_level
     bool pyrTma = true;              // ORBX_PYR_TMA=0 (A/B switch)
     int smCount = 148;
-    int treeThreadsSmall = 256, treeThreadsLarge = 128;   // ORBX_TREE_THREADS_SMALL / _LARGE (A/B switches; 128, 256 or 512)
+    int treeThreadsSmall = 512, treeThreadsLarge = 128;   // ORBX_TREE_THREADS_SMALL / _LARGE (A/B switches; 128, 256 or 512)
     bool pyrChainOk = false;         // all levels of a few frames in ONE launch (k_pyr_chain_tma); ORBX_PYR_CHAIN=0 switches it off
     PyrChain pyrChain{};
     size_t pyrChainSmem = 0;

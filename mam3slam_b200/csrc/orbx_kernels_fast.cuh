@@ -763,7 +763,11 @@ __global__ void __launch_bounds__(256) k_pyr_chain_tma(const __grid_constant__ F
         if (threadIdx.x == 0) {
             const unsigned int need = (unsigned int)(pc.tileBegin[l] - pc.tileBegin[l - 1]);
             unsigned int v;
-            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt + l - 1) : "memory"); } while (v < need);
+            // bounded: the tiles below have lower block indices and are dispatched first, so this cannot wait for an unscheduled
+            // CTA; should that ever not hold (it would be a scheduler that dispatches out of order), give up after ~0.1 s instead of
+            // hanging the GPU
+            const long long t0 = clock64();
+            do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt + l - 1) : "memory"); } while (v < need && clock64() - t0 < 200000000LL);
             asm volatile("fence.proxy.async;" ::: "memory");          // the level below was written through the generic proxy; TMA reads through the async one
         }
         __syncthreads();

@@ -49,8 +49,8 @@ def test_schedule_switches_do_not_change_results():
                 {"ORBX_BLUR_TMA": "0"}, {"ORBX_BLUR_TMA": "0", "ORBX_OVERLAP": "0"}, {"ORBX_TREE_CTAS": "1"},
                 # quadtree in its partitioning form only (the default tries the count pyramid first)
                 {"ORBX_TREE_PYRAMID": "0"},
-                # quadtree CTA sizes (launch parameter: 256 threads for few frames, 128 for full batches by default)
-                {"ORBX_TREE_THREADS_SMALL": "512"}, {"ORBX_TREE_THREADS_SMALL": "128", "ORBX_TREE_PYRAMID": "0"},
+                # quadtree CTA sizes (launch parameter: 512 threads for few frames, 128 for full batches by default)
+                {"ORBX_TREE_THREADS_SMALL": "256"}, {"ORBX_TREE_THREADS_SMALL": "128", "ORBX_TREE_PYRAMID": "0"},
                 # orientation + BRIEF with global gathers instead of TMA-staged windows
                 {"ORBX_DESC_TMA": "0"}, {"ORBX_DESC_TMA": "0", "ORBX_BLUR_TMA": "0", "ORBX_FAST_GEN": "1"},
                 # pyramid levels with direct global loads instead of TMA-staged source tiles; everything pre-TMA at once
