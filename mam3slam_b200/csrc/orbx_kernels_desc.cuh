@@ -228,7 +228,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 //      tests live in registers as floats for the whole group (no per-keypoint table reads or int->float conversions);
 //      pattern points rotated in float with separately rounded products (no FMA), cvRound = round-half-even.
 #ifndef ORBX_DESC_GROUP
-#define ORBX_DESC_GROUP 4
+#define ORBX_DESC_GROUP 2      /* 4 -> 2 (with 2 warps per CTA in the TMA kernel): +1.4 % per 64-frame step, a third of the shared memory per CTA; 1 and 8 are slower */
 #endif
 constexpr int kDescWarps = 8, kDescGroup = ORBX_DESC_GROUP;
 __global__ void __launch_bounds__(kDescWarps * 32) k_orient_brief(const DevGeom* __restrict__ g, Level0 l0,

@@ -517,10 +517,13 @@ __global__ void __launch_bounds__(256) k_blur7_tma(const __grid_constant__ FsMap
 // The orientation window gets the same treatment (ncu: its 31 row loads with run-time pitch arithmetic were 44 % of the stall
 // samples and ~450 of the kernel's 884 warp-instructions per keypoint): a 48 x 31-byte tile of the UNBLURRED level (box start
 // floor16(x - 15)), read with one LDS per row at an immediate offset.
-constexpr int kDtWarps = 4;
+#ifndef ORBX_DT_WARPS
+#define ORBX_DT_WARPS 2
+#endif
+constexpr int kDtWarps = ORBX_DT_WARPS;
 constexpr int kDtBoxW = 64, kDtBoxH = 37, kDtTileBytes = kDtBoxW * kDtBoxH, kDtTileStride = 2432;
 constexpr int kOtBoxW = 48, kOtBoxH = 31, kOtTileBytes = kOtBoxW * kOtBoxH, kOtTileStride = 1536;
-constexpr int kDtSmemBytes = kDtWarps * kDescGroup * (kDtTileStride + kOtTileStride);      // 63,488 B: 3 CTAs per SM
+constexpr int kDtSmemBytes = kDtWarps * kDescGroup * (kDtTileStride + kOtTileStride);      // 15,872 B with 2 warps x 2 keypoints (63,488 B with 4 x 4 pinned most of an SM's shared memory)
 
 __global__ void __launch_bounds__(kDtWarps * 32) k_orient_brief_tma(const __grid_constant__ FsMaps bmaps, const __grid_constant__ FsMaps omaps,
                                                                      const DevGeom* __restrict__ g, const WorkItem* __restrict__ work,
