@@ -362,8 +362,8 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     P.qResult = S.dev<int>(oRes); P.qDist = S.dev<int>(oDist); P.qBin = S.dev<int>(oBin);
     P.evals = S.dev<unsigned long long>(oEv);
     // stateful searches run on one CTA: stage the target frame on chip; stateless ones spread over many CTAs instead
-    P.stageTgt = (P.state != 0 && search_smem_bytes(n, P.state, true) <= kSearchSmemMax && nq >= 64) ? 1 : 0;
-    const size_t smem = search_smem_bytes(n, P.state, P.stageTgt != 0);
+    P.stageTgt = (P.state != 0 && search_smem_bytes(n, P.state, true, P.source == 0) <= kSearchSmemMax && nq >= 64) ? 1 : 0;
+    const size_t smem = search_smem_bytes(n, P.state, P.stageTgt != 0, P.source == 0);
     if (smem > kSearchSmemMax) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
     // window searches walk one query per lane (32 per warp), BoW / triangulation runs one query per warp
     const int units = P.source == 0 ? (nq + 31) / 32 : nq;
@@ -1371,8 +1371,8 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     T.kpMatch = d_kp_match; T.nMatches = d_nmatches; T.evals = M->dEvals;
     // ORBM_TRACK_STAGE=0 (A/B): the target frame stays in L2 instead of shared memory - a slower kernel with a third of the footprint
     static const bool stageOk = [] { const char* e = getenv("ORBM_TRACK_STAGE"); return !(e && e[0] == '0'); }();
-    T.stageTgt = (stageOk && search_smem_bytes(frame_stride, 1, true) <= kSearchSmemMax) ? 1 : 0;
-    const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0);
+    T.stageTgt = (stageOk && search_smem_bytes(frame_stride, 1, true, true) <= kSearchSmemMax) ? 1 : 0;
+    const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0, true);
     if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
     CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));
     // the whole step is latency-bound (one CTA per frame pair): dispatched ahead of the queued CTAs of other handles' kernels

@@ -163,8 +163,11 @@ struct SearchParams {
 constexpr int kSearchThreads = ORBM_SEARCH_THREADS, kSearchWarps = kSearchThreads / 32, kSlab = 192, kSlots = 64;
 
 // dynamic shared memory of a search CTA: slabs + match state (+ the staged target frame); host and device agree on this
-__host__ __device__ inline size_t search_smem_bytes(int n, int state, bool stage) {
-    size_t b = (size_t)kSlots * kSlab * 4;
+// window: grid-window searches need only the 32-batch ring of Top4 lists (24 KB), run searches the 64 candidate slabs (48 KB)
+constexpr size_t kSearchRingBytes = 32 * 32 * (16 + 4 + 4);
+__host__ __device__ inline size_t search_slab_bytes(bool window) { return window ? kSearchRingBytes : (size_t)kSlots * kSlab * 4; }
+__host__ __device__ inline size_t search_smem_bytes(int n, int state, bool stage, bool window) {
+    size_t b = search_slab_bytes(window);
     if (state == 1) b += ((size_t)n + 15) & ~(size_t)15;
     if (state == 2) b += (((size_t)n * 2 + 15) & ~(size_t)15) + (((size_t)n * 4 + 15) & ~(size_t)15);
     if (stage) b = ((b + 15) & ~(size_t)15) + (size_t)n * 32 + (size_t)n * 16 + (size_t)(kGridCells + 1) * 4 + (size_t)n * 4 + 16;
@@ -549,7 +552,7 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
 #endif
     const int n = P.tgt.n;
     uint32_t* slabs = reinterpret_cast<uint32_t*>(dyn);
-    uint8_t* stateBase = dyn + (size_t)kSlots * kSlab * 4;
+    uint8_t* stateBase = dyn + search_slab_bytes(kWindow);
     uint8_t* occS = stateBase;                                        // state 1
     uint16_t* mdS = reinterpret_cast<uint16_t*>(stateBase);           // state 2
     int* m21S = reinterpret_cast<int*>(stateBase + (((size_t)n * 2 + 15) & ~(size_t)15));
@@ -558,7 +561,7 @@ __device__ __forceinline__ void search_cta(const SearchParams& P, uint8_t* dyn, 
     // runs at shared-memory latency instead of L2 latency.
     FrameDev T = P.tgt;
     if (P.stageTgt) {
-        const size_t so = search_smem_bytes(n, P.state, false);
+        const size_t so = search_smem_bytes(n, P.state, false, kWindow);
         uint4* sDesc = reinterpret_cast<uint4*>(dyn + ((so + 15) & ~(size_t)15));
         float4* sKp4 = reinterpret_cast<float4*>(sDesc + 2 * (size_t)n);
         int* sOff = reinterpret_cast<int*>(sKp4 + n);
