@@ -611,8 +611,10 @@ int launchPass(Extractor* E, Level0 l0, int n, int lap0, int lap1, cudaStream_t 
         launchBlur(E->aux[slot]);
         CK(cudaEventRecord(E->evJoin[slot], E->aux[slot]));
     }
-    // few CTAs in flight: wide CTAs (latency of one frame); a full batch: narrow ones (see orbx_kernels_tree.cuh)
-    const int treeThreads = n * L <= E->smCount ? E->treeThreadsSmall : E->treeThreadsLarge;
+    // few CTAs in flight: wide CTAs (latency of one frame); a full batch: narrow ones (see orbx_kernels_tree.cuh).  "Few" = all wide
+    // CTAs resident at once (two 512 x 64-register CTAs per SM): one frame, or the 32 KITTI frames of the bench (51 k frames/s with 256
+    // threads, 54 k with 512, 48 k with 128)
+    const int treeThreads = n * L <= 2 * E->smCount ? E->treeThreadsSmall : E->treeThreadsLarge;
     CK(launch_prio(k_octree, dim3(n, L), dim3(treeThreads), E->treeSmem, st, E->prio, E->dGeom, E->dCells, E->dCand, E->dCellCount,
                    E->dQtA, E->dQtB, E->dLvlKp, E->dLvlCnt, E->poolCap, E->scanCap, fb, E->pyrRoots));
     ++E->launches;
