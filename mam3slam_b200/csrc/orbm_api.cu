@@ -2,6 +2,7 @@
 // Host-side logic mirrors what each ORBmatcher method does before and after its Hamming loop (src/ORBmatcher.cc).
 #include "orbm_kernels.cuh"
 #include "orbm_kernels_tc.cuh"
+#include "orbm_kernels_rounds.cuh"
 #include "orbx_internal.h"
 #include <algorithm>
 #include <atomic>
@@ -58,7 +59,7 @@ struct orbm_matcher {
     unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
     unsigned int* knnBound = nullptr; int knnBoundCap = 0;         // shared pruning bound per query (all ones at rest)
     unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
-    void* trackBuf = nullptr; size_t trackBytes = 0;
+    void* trackBuf = nullptr; size_t trackBytes = 0; int trackFrames = 0, trackStride = 0;
 };
 
 namespace {
@@ -213,6 +214,8 @@ int orbm_create(int device, orbm_handle* out) {
     orbx::raise_dyn_smem((const void*)k_search<true>, device, 200 * 1024);
     orbx::raise_dyn_smem((const void*)k_search<false>, device, 200 * 1024);
     orbx::raise_dyn_smem((const void*)k_track_search, device, 200 * 1024);
+    orbx::raise_dyn_smem((const void*)k_search_rounds, device, kRoundsSmemMax);
+    orbx::raise_dyn_smem((const void*)k_track_rounds, device, kRoundsSmemMax);
     *out = M;
     return ORBM_OK;
 }
@@ -312,6 +315,7 @@ struct SearchIO {
     std::vector<int2> nodeQ;                // BoW: query range of every shared node (k_search_nodes), empty = single-CTA path
     const uint8_t* qdescDev = nullptr;      // BoW, node-parallel: the source frame's descriptors in HBM (rows gathered on the device)
     std::vector<int> result, dist;
+    void reserve(int nq) { qwin.reserve(nq); qlev.reserve(nq); qangle.reserve(nq); qsrc.reserve(nq); }
 };
 
 // uploads the compacted queries, runs k_search (+ k_rot_filter), downloads per-query results
@@ -322,16 +326,25 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     M->lastEvals = 0;
     if (nq == 0) return ORBM_OK;
     Stage S(M);
+    // layout: [uploaded: queries ... occupancy, counters] [downloaded with the last two: results] [device only: lists]
+    // so that one copy goes up and one contiguous copy (occupancy, counters, results) comes back
     const size_t oWin = S.take<float4>(nq), oLev = S.take<int2>(nq), oRun = S.take<int2>(nq), oDesc = S.take<uint32_t>((size_t)nq * 8);
     const size_t oAng = S.take<float>(nq), oBow = S.take<int>(std::max(io.nBow, 1)), oElig = S.take<uint8_t>(std::max(n, 1));
-    const size_t oOcc = S.take<uint8_t>(std::max(n, 1)), oQocc = S.take<uint8_t>(nq);
+    const size_t oQocc = S.take<uint8_t>(nq);
     const bool byNode = !io.nodeQ.empty() && io.qdescDev && P.source == 1 && P.state == 1;
     const int nNodes = (int)io.nodeQ.size();
     const size_t oNode = S.take<int2>(std::max(nNodes, 1)), oSrc = S.take<int>(byNode ? nq : 1), oTicket = S.take<unsigned int>(4);
+    const size_t oOcc = S.take<uint8_t>(std::max(n, 1)), oEv = S.take<unsigned long long>(16);
     const size_t inEnd = S.off;
-    const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq), oEv = S.take<unsigned long long>(16);
+    const size_t oRes = S.take<int>(nq), oDist = S.take<int>(nq), oBin = S.take<int>(nq);
     const size_t outEnd = S.off;
-    int rc = ensureScratch(M, outEnd);
+    // window searches under "best unblocked candidate <= th" against an occupancy state: claim rounds over many CTAs
+    // (orbm_kernels_rounds.cuh); ORBM_ROUNDS=0 keeps them on the single-CTA in-order resolver (A/B)
+    static const bool roundsOk = [] { const char* e = getenv("ORBM_ROUNDS"); return !(e && e[0] == '0'); }();
+    const bool byRounds = roundsOk && P.source == 0 && P.state == 1 && P.rule == RULE_BEST_LE && io.occ && nq <= kRoundsMaxQueries &&
+                          rounds_smem_bytes(n, nq) <= kRoundsSmemMax;
+    const size_t oLists = S.take<uint4>(byRounds ? nq : 1), oCnt = S.take<int>(byRounds ? nq : 1);
+    int rc = ensureScratch(M, S.off);
     if (rc) return rc;
     if (!io.qwin.empty()) memcpy(S.host<float4>(oWin), io.qwin.data(), (size_t)nq * sizeof(float4));
     if (!io.qlev.empty()) memcpy(S.host<int2>(oLev), io.qlev.data(), (size_t)nq * sizeof(int2));
@@ -342,6 +355,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
         memcpy(S.host<int>(oSrc), io.qsrc.data(), (size_t)nq * sizeof(int));
         *S.host<unsigned int>(oTicket) = 0;
     } else {
+        *S.host<unsigned int>(oTicket) = 0;
         uint8_t* hd = S.host<uint8_t>(oDesc);
         for (int q = 0; q < nq; ++q) memcpy(hd + 32 * (size_t)q, io.qdescSrc + 32 * (size_t)io.qsrc[q], 32);
     }
@@ -349,9 +363,8 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     if (io.elig && n) memcpy(S.host<uint8_t>(oElig), io.elig, n);
     if (io.occ && n) memcpy(S.host<uint8_t>(oOcc), io.occ, n);
     if (io.qocc) for (int q = 0; q < nq; ++q) S.host<uint8_t>(oQocc)[q] = io.qocc[io.qsrc[q]];
-    *S.host<unsigned long long>(oEv) = 0;
+    memset(S.host<unsigned long long>(oEv), 0, 128);
     CKM(cudaMemcpyAsync(M->scratch, M->pinned, inEnd, cudaMemcpyHostToDevice, M->stream));
-    CKM(cudaMemsetAsync(S.dev<unsigned long long>(oEv), 0, 128, M->stream));
     P.tgt = devView(T);
     P.nq = nq;
     P.qwin = S.dev<float4>(oWin); P.qlev = S.dev<int2>(oLev); P.qrun = S.dev<int2>(oRun);
@@ -364,11 +377,16 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     // stateful searches run on one CTA: stage the target frame on chip; stateless ones spread over many CTAs instead
     P.stageTgt = (P.state != 0 && search_smem_bytes(n, P.state, true, P.source == 0) <= kSearchSmemMax && nq >= 64) ? 1 : 0;
     const size_t smem = search_smem_bytes(n, P.state, P.stageTgt != 0, P.source == 0);
-    if (smem > kSearchSmemMax) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
+    if (!byRounds && smem > kSearchSmemMax) { M->err = "target frame too large for the on-chip match state"; return ORBM_ERR_UNSUPPORTED; }
     // window searches walk one query per lane (32 per warp), BoW / triangulation runs one query per warp
     const int units = P.source == 0 ? (nq + 31) / 32 : nq;
     const int grid = P.state != 0 ? 1 : std::max(1, std::min(units, M->smCount * 2));
-    if (byNode) {
+    if (byRounds) {
+        P.ticket = S.dev<unsigned int>(oTicket);
+        k_search_rounds<<<(nq + kRoundQueries - 1) / kRoundQueries, kRoundThreads, rounds_smem_bytes(n, nq), M->stream>>>(
+            P, S.dev<uint4>(oLists), S.dev<int>(oCnt));
+        ++M->launches;
+    } else if (byNode) {
         // BoW: a warp per shared node, rotation filter fused into the last CTA (orbm_kernels.cuh, k_search_nodes)
         P.nodeQ = S.dev<int2>(oNode); P.nNodes = nNodes; P.qsrc = S.dev<int>(oSrc);
         P.qdescBase = reinterpret_cast<const uint32_t*>(io.qdescDev); P.ticket = S.dev<unsigned int>(oTicket);
@@ -381,13 +399,19 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
         if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
     }
     CKM(cudaGetLastError());
-    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oRes, (uint8_t*)M->scratch + oRes, outEnd - oRes, cudaMemcpyDeviceToHost, M->stream));
-    if (io.occ && n) CKM(cudaMemcpyAsync(S.host<uint8_t>(oOcc), S.dev<uint8_t>(oOcc), n, cudaMemcpyDeviceToHost, M->stream));
+    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOcc, (uint8_t*)M->scratch + oOcc, outEnd - oOcc, cudaMemcpyDeviceToHost, M->stream));
     CKM(cudaStreamSynchronize(M->stream));
     memcpy(io.result.data(), S.host<int>(oRes), (size_t)nq * sizeof(int));
     memcpy(io.dist.data(), S.host<int>(oDist), (size_t)nq * sizeof(int));
     if (io.occ && n && P.state == 1) memcpy(io.occ, S.host<uint8_t>(oOcc), n);
     M->lastEvals = (long long)*S.host<unsigned long long>(oEv);
+#ifdef ORBM_STATS
+    if (byRounds) fprintf(stderr, "rounds: nq %d evals %llu rounds %llu incomplete %llu resolve cycles %llu walk cycles (max CTA) %llu; re-walks %llu in %llu rounds, %llu cycles\n", nq,
+                          S.host<unsigned long long>(oEv)[0], S.host<unsigned long long>(oEv)[1], S.host<unsigned long long>(oEv)[2],
+                          S.host<unsigned long long>(oEv)[3], S.host<unsigned long long>(oEv)[4], S.host<unsigned long long>(oEv)[5],
+                          S.host<unsigned long long>(oEv)[6], S.host<unsigned long long>(oEv)[7]);
+    if (byRounds) { fprintf(stderr, "  cycles in step 1 / 1r / 1b / 2:"); for (int i = 8; i < 12; ++i) fprintf(stderr, " %llu", S.host<unsigned long long>(oEv)[i]); fprintf(stderr, "\n"); }
+#endif
     return ORBM_OK;
 }
 
@@ -444,6 +468,7 @@ int orbm_search_local_map(orbm_handle M, orbm_frame f, uint8_t* occupied, const 
     if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
     const bool bFactor = th != 1.0;
     SearchIO io;
+    io.reserve(nq);
     for (int q = 0; q < nq; ++q) {
         if (!valid[q]) continue;
         const int l = level[q];
@@ -472,6 +497,7 @@ int orbm_search_frame(orbm_handle M, orbm_frame f, uint8_t* occupied, const floa
                       const uint8_t* q_occupies) {
     if (!M || !f || !occupied || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
     SearchIO io;
+    io.reserve(nq);
     for (int q = 0; q < nq; ++q) {
         if (!valid[q]) continue;
         const int o = octave[q];
@@ -506,6 +532,7 @@ int orbm_search_sim3(orbm_handle M, orbm_frame kf, uint8_t* matched, const float
                      float ratio_hamming, int* kp_match, int* nmatches) {
     if (!M || !kf || !matched || !scale_factors || nq < 0 || !kp_match || !nmatches) return ORBM_ERR_INVALID;
     SearchIO io;
+    io.reserve(nq);
     for (int q = 0; q < nq; ++q) {
         if (!valid[q]) continue;
         const int l = level[q];
@@ -1349,7 +1376,10 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     const size_t oKp4 = take(NS * 16), oCellOf = take(NS * 4), oCellIdx = take(NS * 4), oCellOff = take((size_t)nframes * (kGridCells + 1) * 4);
     const size_t oWin = take(NS * 16), oLev = take(NS * 8), oAng = take(NS * 4), oOcc = take(NS);
     const size_t oRes = take(NS * 4), oDist = take(NS * 4), oBin = take(NS * 4);
+    const size_t oLists = take(NS * 16), oListCnt = take(NS * 4), oTickets = take((size_t)nframes * 4);
+    bool fresh = false;
     if (off > M->trackBytes) {
+        fresh = true;
         if (M->trackBuf) { CKM(cudaStreamSynchronize(st)); cudaFree(M->trackBuf); }
         M->trackBuf = nullptr; M->trackBytes = 0;
         CKM(cMalloc(&M->trackBuf, off));
@@ -1369,17 +1399,34 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     T.qwin = (float4*)(b + oWin); T.qlev = (int2*)(b + oLev); T.qangle = (float*)(b + oAng); T.occ = b + oOcc;
     T.qResult = (int*)(b + oRes); T.qDist = (int*)(b + oDist); T.qBin = (int*)(b + oBin);
     T.kpMatch = d_kp_match; T.nMatches = d_nmatches; T.evals = M->dEvals;
+    T.lists = (uint4*)(b + oLists); T.listCounts = (int*)(b + oListCnt); T.tickets = (unsigned int*)(b + oTickets);
+    // the last CTA of a pair leaves its ticket at zero; a new or re-laid-out buffer starts from zero (the layout depends on
+    // nframes and frame_stride, so a different batch shape on the same handle re-zeroes as well)
+    if (fresh || M->trackFrames != nframes || M->trackStride != frame_stride) {
+        CKM(cudaMemsetAsync(T.tickets, 0, (size_t)nframes * 4, st));
+        M->trackFrames = nframes; M->trackStride = frame_stride;
+    }
+    // Off by default for the batch: measured on 64-frame steps the claim-rounds launch (2205 CTAs of 1024 threads) is a shorter
+    // stage by itself only with small CTAs and costs the overlapped step 10 % (109.7 k against 123.7 k frames/s): the in-order
+    // kernel's 63 small CTAs sit beside the other handles' kernels, this one does not.  ORBM_TRACK_ROUNDS=1 turns it on (A/B).
+    static const bool roundsOk = [] { const char* e = getenv("ORBM_TRACK_ROUNDS"); return e && e[0] == '1'; }();
+    const bool byRounds = roundsOk && frame_stride <= kRoundsMaxQueries && rounds_smem_bytes(frame_stride, frame_stride) <= kRoundsSmemMax;
     // ORBM_TRACK_STAGE=0 (A/B): the target frame stays in L2 instead of shared memory - a slower kernel with a third of the footprint
     static const bool stageOk = [] { const char* e = getenv("ORBM_TRACK_STAGE"); return !(e && e[0] == '0'); }();
     T.stageTgt = (stageOk && search_smem_bytes(frame_stride, 1, true, true) <= kSearchSmemMax) ? 1 : 0;
     const size_t smem = search_smem_bytes(frame_stride, 1, T.stageTgt != 0, true);
-    if (smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
+    if (!byRounds && smem > kSearchSmemMax) return ORBM_ERR_UNSUPPORTED;
     CKM(cudaMemsetAsync(M->dEvals, 0, 128, st));
     // the whole step is latency-bound (one CTA per frame pair): dispatched ahead of the queued CTAs of other handles' kernels
     CKM(orbx::launch_prio(k_track_prepare, dim3((frame_stride + 255) / 256, nframes), dim3(256), 0, st, M->prio, T));
     CKM(orbx::launch_prio(k_track_grid, dim3(nframes), dim3(kGridThreads), 0, st, M->prio, T));
     M->launches += 2;
-    if (nframes > 1) {
+    if (nframes > 1 && byRounds) {
+        // claim rounds: a warp per query over the whole GPU, the last CTA of a pair resolves, filters and scatters
+        CKM(orbx::launch_prio(k_track_rounds, dim3((frame_stride + kRoundQueries - 1) / kRoundQueries, nframes - 1), dim3(kRoundThreads),
+                              rounds_smem_bytes(frame_stride, frame_stride), st, M->prio, T));
+        M->launches += 1;
+    } else if (nframes > 1) {
         CKM(orbx::launch_prio(k_track_search, dim3(nframes - 1), dim3(kSearchThreads), smem, st, M->prio, T));
         CKM(orbx::launch_prio(k_track_finish, dim3(nframes - 1), dim3(256), 0, st, M->prio, T));
         M->launches += 2;

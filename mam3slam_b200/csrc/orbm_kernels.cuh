@@ -1066,6 +1066,7 @@ struct TrackBatch {
     int* qResult; int* qDist; int* qBin;
     int* kpMatch; int* nMatches /* nframes */;
     unsigned long long* evals;
+    uint4* lists; int* listCounts; unsigned int* tickets /* nframes, zero between passes */;   // claim rounds (orbm_kernels_rounds.cuh)
 };
 
 __global__ void k_track_prepare(const TrackBatch T) {
@@ -1093,10 +1094,9 @@ __global__ void __launch_bounds__(kGridThreads) k_track_grid(const TrackBatch T)
     grid_build_cta(n, T.cellOf + (size_t)f * T.stride, T.cellOff + (size_t)f * (kGridCells + 1), T.cellIdx + (size_t)f * T.stride);
 }
 
-__global__ void __launch_bounds__(kSearchThreads, 1) k_track_search(const TrackBatch T) {
-    extern __shared__ __align__(16) uint8_t dyn[];
-    const int cur = blockIdx.x + 1, last = blockIdx.x;
-    SearchParams P;
+// the search of frame pair (last = pair, cur = pair + 1) in the terms of the generic engine
+__device__ __forceinline__ void track_pair_params(const TrackBatch& T, int pair, SearchParams& P) {
+    const int cur = pair + 1, last = pair;
     P.tgt.n = min(T.counts[cur * T.countStride], T.stride);
     P.tgt.kp4 = T.kp4 + (size_t)cur * T.stride;
     P.tgt.desc = T.desc + (size_t)cur * T.stride * 8;
@@ -1118,6 +1118,13 @@ __global__ void __launch_bounds__(kSearchThreads, 1) k_track_search(const TrackB
     P.tri = 0; P.coarse = 0; P.ep0 = P.ep1 = 0.f; P.scale2 = nullptr; P.sigma2 = nullptr;
     P.qResult = T.qResult + (size_t)cur * T.stride; P.qDist = T.qDist + (size_t)cur * T.stride; P.qBin = T.qBin + (size_t)cur * T.stride;
     P.evals = T.evals;
+    P.nodeQ = nullptr; P.nNodes = 0; P.qsrc = nullptr; P.qdescBase = nullptr; P.ticket = nullptr;
+}
+
+__global__ void __launch_bounds__(kSearchThreads, 1) k_track_search(const TrackBatch T) {
+    extern __shared__ __align__(16) uint8_t dyn[];
+    SearchParams P;
+    track_pair_params(T, blockIdx.x, P);
     search_cta<true>(P, dyn, 0, 1);
 }
 

@@ -2,7 +2,8 @@
 import ctypes, sys, numpy as np, torch
 sys.path.insert(0, '.')
 from mam3slam_b200 import ORBextractor, ORBmatcher, _lib, synth
-B, W, H = 64, 752, 480
+import os
+B, W, H = int(os.environ.get('B', 64)), 752, 480
 frames = np.stack(synth.stream(W, H, 0, B))
 dev = torch.from_numpy(frames).cuda()
 ex = ORBextractor(1000, 1.2, 8, 20, 7, device=0, max_batch=B)
@@ -25,5 +26,5 @@ n = max(v[6], 1)
 print('evals', v[0], 'CTAs', v[6], 'matches', int(nmt.sum()))
 print('per CTA: prologue %.0f, main loop (tid 0) %.0f cycles' % (v[10]/n, v[9]/n))
 print('resolver per CTA: wait %.0f resolve %.0f cycles; iterations %.1f re-walks %.1f' % (v[1]/n, v[3]/n, v[4]/n, v[5]/n))
-print('producers per warp: wait %.0f work %.0f cycles' % (v[7]/n/15, v[8]/n/15))
+print('producers per warp: wait %.0f work %.0f cycles' % (v[7]/n/7, v[8]/n/7))
 print('resolver phases per CTA: pick %.0f conflict %.0f commit %.0f' % (v[11]/n, v[12]/n, v[13]/n))
