@@ -247,6 +247,31 @@ def agents_in_flight(local, frames, counts=(1, 4, 16)):
                                   "per frame, host buffers"}
 
 
+def agents_native(local, frames, counts=(1, 4, 8, 16), per_agent=300):
+    """The same loop from NATIVE host threads (tools/agents_native.cc, built by mam3slam_b200/csrc/Makefile): one std::thread per
+    agent, each with its own extractor + matcher handle, orbx_extract + orbm_frame_update + orbm_search_frame per frame over
+    the C ABI with host buffers - the reference's shape (one C++ Tracking thread per agent) without the interpreter in the
+    loop.  With and without the tracking search."""
+    import subprocess
+    import tempfile
+    exe = os.path.join(ROOT, "mam3slam_b200", "agents_native")
+    if not os.path.exists(exe):
+        return {"unavailable": "mam3slam_b200/agents_native not built (make -C mam3slam_b200/csrc)"}
+    out = {"note": "A agents x one frame in flight on ONE GPU, one native host thread per agent over the C ABI, host buffers "
+                   "(pageable image in, keypoints / descriptors / matches out), %d frames per agent" % per_agent}
+    with tempfile.NamedTemporaryFile(suffix=".u8") as f:
+        np.stack(frames[:16]).astype(np.uint8).tofile(f.name)
+        nfile = min(len(frames), 16)
+        for track, key in ((1, "extract_and_track"), (0, "extract_only")):
+            r = subprocess.run([exe, f.name, str(W), str(H), str(nfile), str(local), str(per_agent), ",".join(map(str, counts)), str(track)],
+                               capture_output=True, text=True, timeout=600)
+            if r.returncode != 0:
+                out[key] = {"error": r.stderr[-300:]}
+                continue
+            out[key] = json.loads(r.stdout.strip().splitlines()[-1])["rows"]
+    return out
+
+
 def search_latency_rows(local):
     """One row per ORBmatcher search member: per-call time through the product the way the C++ adapter calls it
     - an ORBmatcher CONSTRUCTED PER CALL, as the reference does (`ORBmatcher matcher(0.9,true);` inside every tracking /
@@ -796,6 +821,7 @@ def run_gpu(args):
     latency = latency_bench(args, torch, local, frames) if rank == 0 and not args.no_latency else None
     if latency is not None:
         latency["agents_one_frame_in_flight"] = agents_in_flight(local, frames)
+        latency["agents_one_frame_in_flight_native"] = agents_native(local, frames)
     if latency is not None and not args.no_cpu:
         latency["search_members"] = search_latency_rows(local)
     sparse = sparse_bench(args, torch, local, rank) if rank == 0 and not args.no_sparse else None

@@ -11,7 +11,7 @@ d=json.load(open('gpurun_out/${TAG}_bench.json'))
 print('value', round(d['value']), 'e2e', round(d['e2e']['value']), 'ms/step', round(d['ms_per_step'],3), 'launches', d['gpu_launches'])
 print(d['roofline'].get('stage_ms_per_batch'))
 print('knn', d['hamming']['knn']['ms'], d['hamming']['knn']['roofline_int']['frac'])
-L=d['latency']; print({k:v for k,v in L.items() if k not in ('search_members','agents_one_frame_in_flight')})
+L=d['latency']; print({k:v for k,v in L.items() if k not in ('search_members','agents_one_frame_in_flight','agents_one_frame_in_flight_native')}); print(json.dumps(L.get('agents_one_frame_in_flight_native'))[:1500])
 print(L['agents_one_frame_in_flight']['rows'])
 for r in L['search_members']['rows']: print(f"{r['member']:48s} gpu {r['gpu_call_ms']:.3f} ms  cpu {r['cpu_port_call_ms']:.3f} ms  x{r['ratio']:.1f}")
 print('cpu', d.get('cpu_baseline',{}).get('value'), 'cv2', (d.get('cpu_baseline_cv2') or {}).get('value'))
