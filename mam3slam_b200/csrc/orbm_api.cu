@@ -341,7 +341,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     // window searches under "best unblocked candidate <= th" against an occupancy state: claim rounds over many CTAs
     // (orbm_kernels_rounds.cuh); ORBM_ROUNDS=0 keeps them on the single-CTA in-order resolver (A/B)
     static const bool roundsOk = [] { const char* e = getenv("ORBM_ROUNDS"); return !(e && e[0] == '0'); }();
-    const bool byRounds = roundsOk && P.source == 0 && P.state == 1 && P.rule == RULE_BEST_LE && io.occ && nq <= kRoundsMaxQueries &&
+    const bool byRounds = roundsOk && P.source == 0 && P.state == 1 && rounds_rule(P.rule) && io.occ && nq <= kRoundsMaxQueries &&
                           rounds_smem_bytes(n, nq) <= kRoundsSmemMax;
     const size_t oLists = S.take<uint4>(byRounds ? nq : 1), oCnt = S.take<int>(byRounds ? nq : 1);
     int rc = ensureScratch(M, S.off);

@@ -26,10 +26,10 @@ namespace orbm {
 constexpr int kRoundThreads = 1024, kRoundQueries = kRoundThreads / 32;     // a warp per query; the resolving CTA wants a thread per query
 constexpr uint8_t kRfResolved = 1, kRfIncomplete = 2, kRfOccupies = 4, kRfAccepted = 8;
 
-// dynamic shared memory of the resolving CTA: owners u16 [n] | registrations u32 [n] | lists uint4 [nq] | picks u32 [nq] | flags [nq] | re-walk queue u16 [nq]
+// dynamic shared memory of the resolving CTA: owners u16 [n] | registrations u32 [n] | lists uint4 [nq] | best and second picks u32 [2 nq] | flags [nq] | re-walk queue u16 [nq]
 __host__ __device__ inline size_t rounds_smem_bytes(int n, int nq) {
     const size_t a = ((size_t)n * 2 + 15) & ~(size_t)15;
-    return a + (((size_t)n * 4 + 15) & ~(size_t)15) + (size_t)nq * 16 + (size_t)nq * 4 + (((size_t)nq + 15) & ~(size_t)15) + (size_t)nq * 2;
+    return a + (((size_t)n * 4 + 15) & ~(size_t)15) + (size_t)nq * 16 + (size_t)nq * 8 + (((size_t)nq + 15) & ~(size_t)15) + (size_t)nq * 2;
 }
 constexpr size_t kRoundsSmemMax = 200 * 1024;
 constexpr int kRoundsMaxQueries = 65000;       // query index + 1 and 0xffff - query index live in 16 bits
@@ -41,6 +41,17 @@ constexpr uint16_t kOwnerInitial = 0xffff;
 __device__ __forceinline__ bool owner_blocks(const uint16_t* owner, int idx, int q) {
     const unsigned o = owner[idx];
     return o != 0 && (o == kOwnerInitial || (int)o - 1 < q);
+}
+
+// Which rules the rounds cover, and which candidates can matter under them.  A candidate matters if it could be accepted as the
+// best (its distance passes the rule's threshold) or, under the best / second-best rule of SearchByProjection(Frame, local map
+// points) (src/ORBmatcher.cc:107-139), if it could reject a best as the runner-up: bestDist > nnratio * d2 with bestDist <= TH_HIGH
+// needs nnratio * d2 < TH_HIGH.  Both tests are monotone in the distance, so the kept candidates are exactly the closest ones
+// and the first two unblocked entries of a list are the best and the second best the reference would see.
+__host__ __device__ inline bool rounds_rule(int rule) { return rule == RULE_BEST_LE || rule == RULE_LOCAL_MAP; }
+__device__ __forceinline__ bool rounds_keepable(const SearchParams& P, int d) {
+    if (P.rule == RULE_BEST_LE) return (float)d <= P.thF;
+    return d <= ORBM_TH_HIGH || __fmul_rn(P.nnratio, (float)d) < (float)ORBM_TH_HIGH;
 }
 
 // The list of one query, by a whole warp: walk_candidates flattens the window's column runs over the lanes (reference
@@ -60,7 +71,7 @@ __device__ __forceinline__ void warp_list(const SearchParams& P, const FrameDev&
     uint32_t e0 = kNoEntry, e1 = kNoEntry, e2 = kNoEntry, e3 = kNoEntry;
     int count = 0, pos0 = 0;
     walk_candidates(P, T, q, qd, nEval, [&](bool ok, uint32_t entry) {
-        const bool keep = ok && (float)(entry >> 23) <= P.thF && !isBlocked((int)(entry & 0x7ffff));
+        const bool keep = ok && rounds_keepable(P, (int)(entry >> 23)) && !isBlocked((int)(entry & 0x7ffff));
         count += __popc(__ballot_sync(0xffffffffu, keep));
         if (keep) {
             const uint32_t key = ((entry >> 23) << 20) | (uint32_t)((pos0 + lane) & 0xfffff);
@@ -111,7 +122,9 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
     uint32_t* reg = reinterpret_cast<uint32_t*>(dyn + (((size_t)n * 2 + 15) & ~(size_t)15));
     uint4* L = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(reg) + (((size_t)n * 4 + 15) & ~(size_t)15));
     uint32_t* pick = reinterpret_cast<uint32_t*>(L + nq);
-    uint8_t* flag = reinterpret_cast<uint8_t*>(pick + nq);
+    uint32_t* pick2 = pick + nq;
+    uint8_t* flag = reinterpret_cast<uint8_t*>(pick2 + nq);
+    const int needed = rule_needs_second(P.rule) ? 2 : 1;
     uint16_t* queue = reinterpret_cast<uint16_t*>(flag + (((size_t)nq + 15) & ~(size_t)15));
     for (int i = tid; i < n; i += nthr) { owner[i] = P.occ[i] ? kOwnerInitial : (uint16_t)0; reg[i] = 0; }
     for (int q = tid; q < nq; q += nthr) {
@@ -133,7 +146,11 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
         // step 1: every unresolved query picks its first unblocked entry and registers on all its unblocked entries
         auto settle = [&](int q, uint8_t f, const uint4 l, bool b0, bool b1, bool b2, bool b3) {
             if (!(b0 || b1 || b2 || b3)) { flag[q] = f | kRfResolved; return; }      // nothing it could accept is left: no match, for good
-            pick[q] = b0 ? l.x : b1 ? l.y : b2 ? l.z : l.w;
+            // best and second best = the first two unblocked entries
+            const unsigned m = (unsigned)b0 | ((unsigned)b1 << 1) | ((unsigned)b2 << 2) | ((unsigned)b3 << 3);
+            const int ia = __ffs(m) - 1, ib = __ffs(m & (m - 1)) - 1;
+            pick[q] = ia == 0 ? l.x : ia == 1 ? l.y : ia == 2 ? l.z : l.w;
+            pick2[q] = ib == 1 ? l.y : ib == 2 ? l.z : ib == 3 ? l.w : kNoEntry;
             if (f & kRfOccupies) {
                 const unsigned v = tag | (0xffffu - (unsigned)q);
                 if (b0) atomicMax(&reg[l.x & 0x7ffff], v);
@@ -148,7 +165,7 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
             const uint4 l = L[q];
             const bool b0 = l.x != kNoEntry && !owner_blocks(owner, l.x & 0x7ffff, q), b1 = l.y != kNoEntry && !owner_blocks(owner, l.y & 0x7ffff, q);
             const bool b2 = l.z != kNoEntry && !owner_blocks(owner, l.z & 0x7ffff, q), b3 = l.w != kNoEntry && !owner_blocks(owner, l.w & 0x7ffff, q);
-            if (!(b0 || b1 || b2 || b3) && (f & kRfIncomplete)) { queue[atomicAdd(&sQueued, 1)] = (uint16_t)q; continue; }
+            if ((int)b0 + (int)b1 + (int)b2 + (int)b3 < needed && (f & kRfIncomplete)) { queue[atomicAdd(&sQueued, 1)] = (uint16_t)q; continue; }
             settle(q, f, l, b0, b1, b2, b3);
         }
         __syncthreads();
@@ -182,19 +199,20 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
 #ifdef ORBM_STATS
         c1b = clock64(); st1r += c1b - c1;
 #endif
-        // step 1b: an occupying query with more candidates than its list holds can only run out of entries if EVERY unblocked
-        // entry it has also sits on the list of an earlier unresolved occupying query; only then must the later queries wait
+        // step 1b: an occupying query with more candidates than its list holds can only run short of entries (one, or two under
+        // a best / second-best rule) if all but that many of its unblocked entries also sit on the list of an earlier unresolved
+        // occupying query; only then must the later queries wait
         for (int q = tid; q < nq; q += nthr) {
             const uint8_t f = flag[q];
             if ((f & (kRfResolved | kRfIncomplete | kRfOccupies)) != (kRfIncomplete | kRfOccupies)) continue;
             const uint4 l = L[q];
             const unsigned mine = tag | (0xffffu - (unsigned)q);
-            bool safe = false;                        // an unblocked entry nobody before q can take
-            if (l.x != kNoEntry && !owner_blocks(owner, l.x & 0x7ffff, q) && reg[l.x & 0x7ffff] == mine) safe = true;
-            if (l.y != kNoEntry && !owner_blocks(owner, l.y & 0x7ffff, q) && reg[l.y & 0x7ffff] == mine) safe = true;
-            if (l.z != kNoEntry && !owner_blocks(owner, l.z & 0x7ffff, q) && reg[l.z & 0x7ffff] == mine) safe = true;
-            if (l.w != kNoEntry && !owner_blocks(owner, l.w & 0x7ffff, q) && reg[l.w & 0x7ffff] == mine) safe = true;
-            if (!safe) atomicMax(&sBarrier, mine);
+            int safe = 0;                             // unblocked entries nobody before q can take
+            if (l.x != kNoEntry && !owner_blocks(owner, l.x & 0x7ffff, q) && reg[l.x & 0x7ffff] == mine) ++safe;
+            if (l.y != kNoEntry && !owner_blocks(owner, l.y & 0x7ffff, q) && reg[l.y & 0x7ffff] == mine) ++safe;
+            if (l.z != kNoEntry && !owner_blocks(owner, l.z & 0x7ffff, q) && reg[l.z & 0x7ffff] == mine) ++safe;
+            if (l.w != kNoEntry && !owner_blocks(owner, l.w & 0x7ffff, q) && reg[l.w & 0x7ffff] == mine) ++safe;
+            if (safe < needed) atomicMax(&sBarrier, mine);
         }
         __syncthreads();
 #ifdef ORBM_STATS
@@ -207,13 +225,18 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
         for (int q = tid; q < nq; q += nthr) {
             const uint8_t f = flag[q];
             if (f & kRfResolved) continue;
-            const uint32_t e = pick[q];
+            const uint32_t e = pick[q], e2 = needed == 2 ? pick2[q] : kNoEntry;
             const int K = (int)(e & 0x7ffff);
             const unsigned r = reg[K];
-            const int minQ = (r >> 16) == round ? (int)(0xffffu - (r & 0xffffu)) : INT_MAX;
+            int minQ = (r >> 16) == round ? (int)(0xffffu - (r & 0xffffu)) : INT_MAX;
+            if (e2 != kNoEntry) {                     // the runner-up must be as settled as the best
+                const unsigned r2 = reg[e2 & 0x7ffff];
+                if ((r2 >> 16) == round) minQ = min(minQ, (int)(0xffffu - (r2 & 0xffffu)));
+            }
             if (minQ >= q && q <= barQ) {
-                if (f & kRfOccupies) owner[K] = (uint16_t)(q + 1);
-                flag[q] = f | kRfResolved | kRfAccepted;
+                const bool acc = decide_query(P, e, e2);
+                if (acc && (f & kRfOccupies)) owner[K] = (uint16_t)(q + 1);
+                flag[q] = f | kRfResolved | (acc ? kRfAccepted : 0);
             } else ++open;
         }
         const int stillOpen = __syncthreads_count(open);
