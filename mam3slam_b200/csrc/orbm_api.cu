@@ -36,6 +36,10 @@ struct orbm_frame_s {
     float minX = 0, minY = 0, maxX = 0, maxY = 0, invW = 0, invH = 0;
     std::vector<orbx_keypoint> kpsHost;   // kept for the host-side marshalling of BoW / initialization searches
     bool haveHost = false;
+    // host uploads: keypoints and descriptors share one device block and go up in ONE copy from a page-locked staging buffer
+    // of the slot (two copies from the caller's pageable arrays cost ~8 us of host time each)
+    uint8_t* stage = nullptr; size_t descOff = 0;
+    cudaEvent_t staged = nullptr;         // the last upload has left the staging buffer
 };
 
 struct orbm_db_s {
@@ -103,7 +107,9 @@ struct Stage {
 };
 
 void freeFrameBuffers(orbm_frame_s* f) {
-    if (f->ownsInput) { cudaFree(f->kpsDev); cudaFree(f->descDev); }
+    if (f->ownsInput) cudaFree(f->kpsDev);         // one block: descDev points into it
+    if (f->stage) { cudaFreeHost(f->stage); f->stage = nullptr; }
+    if (f->staged) { cudaEventDestroy(f->staged); f->staged = nullptr; }
     cudaFree(f->kp4); cudaFree(f->cellOf); cudaFree(f->cellOff); cudaFree(f->cellIdx);
     f->kpsDev = nullptr; f->descDev = nullptr; f->kp4 = nullptr; f->cellOf = f->cellOff = f->cellIdx = nullptr;
     f->cap = 0; f->ownsInput = false;
@@ -119,8 +125,11 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
         freeFrameBuffers(f);
         const int cap = std::max(n, 1024);
         if (needOwn) {
-            CKM(cMalloc((void**)&f->kpsDev, (size_t)cap * sizeof(orbx_keypoint)));
-            CKM(cMalloc((void**)&f->descDev, (size_t)cap * 32));
+            f->descOff = ((size_t)cap * sizeof(orbx_keypoint) + 255) & ~(size_t)255;
+            CKM(cMalloc((void**)&f->kpsDev, f->descOff + (size_t)cap * 32));
+            f->descDev = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(f->kpsDev) + f->descOff);
+            CKM(cudaHostAlloc((void**)&f->stage, f->descOff + (size_t)cap * 32, cudaHostAllocDefault));
+            CKM(cudaEventCreateWithFlags(&f->staged, cudaEventDisableTiming));
         }
         CKM(cMalloc((void**)&f->kp4, (size_t)cap * sizeof(float4)));
         CKM(cMalloc((void**)&f->cellOf, (size_t)cap * sizeof(int)));
@@ -135,8 +144,16 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
     f->invH = static_cast<float>(kGridRows) / static_cast<float>(f->maxY - f->minY);
     if (needOwn) {
         if (n) {
-            CKM(cudaMemcpyAsync(f->kpsDev, v->kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, M->stream));
-            CKM(cudaMemcpyAsync(f->descDev, v->desc, (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
+            CKM(cudaEventSynchronize(f->staged));          // a previous upload of this slot still reading the staging buffer
+            memcpy(f->stage, v->kps, (size_t)n * sizeof(orbx_keypoint));
+            memcpy(f->stage + f->descOff, v->desc, (size_t)n * 32);
+            if ((size_t)n * 60 * 2 >= f->descOff + (size_t)n * 32) {        // the gap between the two arrays is small: one copy
+                CKM(cudaMemcpyAsync(f->kpsDev, f->stage, f->descOff + (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
+            } else {
+                CKM(cudaMemcpyAsync(f->kpsDev, f->stage, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, M->stream));
+                CKM(cudaMemcpyAsync(f->descDev, f->stage + f->descOff, (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
+            }
+            CKM(cudaEventRecord(f->staged, M->stream));
         }
         f->kpsHost.assign(v->kps, v->kps + n);
         f->haveHost = true;
@@ -145,12 +162,15 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
         f->descDev = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(v->desc));
         f->haveHost = false;
     }
-    if (n) {
-        k_grid_prepare<<<(n + 255) / 256, 256, 0, M->stream>>>(n, f->kpsDev, f->kp4, f->cellOf, f->minX, f->minY, f->invW, f->invH);
+    if (n <= 8 * kGridThreads) {
+        // cell of every keypoint + the CSR grid in one launch
+        k_frame_grid<<<1, kGridThreads, 0, M->stream>>>(n, f->kpsDev, f->kp4, f->cellOf, f->cellOff, f->cellIdx, f->minX, f->minY, f->invW, f->invH);
         ++M->launches;
+    } else {
+        k_grid_prepare<<<(n + 255) / 256, 256, 0, M->stream>>>(n, f->kpsDev, f->kp4, f->cellOf, f->minX, f->minY, f->invW, f->invH);
+        k_grid_build<<<1, kGridThreads, 0, M->stream>>>(n, f->cellOf, f->cellOff, f->cellIdx);
+        M->launches += 2;
     }
-    k_grid_build<<<1, kGridThreads, 0, M->stream>>>(n, f->cellOf, f->cellOff, f->cellIdx);
-    ++M->launches;
     CKM(cudaGetLastError());
     return ORBM_OK;
 }

@@ -56,7 +56,7 @@ __global__ void k_grid_prepare(int n, const orbx_keypoint* __restrict__ kps, flo
 // one CTA: histogram, exclusive scan over the 3072 cells, then a STABLE scatter (ascending keypoint index inside a cell,
 // the reference's push_back order).  n is a few thousand; the per-cell order is produced by letting each thread own a
 // contiguous range of cells and scan the keypoints of those cells in index order via a per-cell linked pass.
-constexpr int kGridThreads = 1024;
+constexpr int kGridThreads = 1024, kGridTmp = 4096;
 __device__ __forceinline__ void grid_build_cta(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
                                                int* __restrict__ cellIdx) {
     __shared__ int cnt[kGridCells];
@@ -88,9 +88,25 @@ __device__ __forceinline__ void grid_build_cta(int n, const int* __restrict__ ce
     for (int k = 0; k < per; ++k) { cnt[tid * per + k] = run; cellOff[tid * per + k] = run; run += v[k]; }
     if (tid == kGridThreads - 1) cellOff[kGridCells] = run;
     __syncthreads();
-    // stable scatter: warp w walks keypoints in index order in chunks of 32; within a chunk, a keypoint's rank inside its
-    // cell = number of lower lanes with the same cell (match_any); chunks are processed in order by ONE warp per pass
-    // over the array — n is small, so a single warp does the ordered pass while the others idle.
+    // stable scatter.  Usual case (n <= kGridTmp): every keypoint takes any free slot of its cell's segment (shared-memory
+    // atomic), then finds its place as the number of smaller indices in that segment - cells hold a handful of keypoints, so
+    // this is two short parallel passes instead of one warp walking all keypoints in order.
+    if (n <= kGridTmp) {
+        __shared__ int tmp[kGridTmp];
+        for (int i = tid; i < n; i += kGridThreads) { const int c = cellOf[i]; if (c >= 0) tmp[atomicAdd(&cnt[c], 1)] = i; }
+        __syncthreads();                              // cnt[c] is now the END of cell c's segment = the begin of cell c + 1
+        for (int i = tid; i < n; i += kGridThreads) {
+            const int c = cellOf[i];
+            if (c < 0) continue;
+            const int b = c ? cnt[c - 1] : 0, e = cnt[c];
+            int rank = 0;
+            for (int p = b; p < e; ++p) rank += tmp[p] < i;
+            cellIdx[b + rank] = i;
+        }
+        return;
+    }
+    // large frames: warp 0 walks keypoints in index order in chunks of 32; within a chunk, a keypoint's rank inside its
+    // cell = number of lower lanes with the same cell (match_any)
     if (wid == 0) {
         for (int base = 0; base < n; base += 32) {
             const int i = base + lane;
@@ -111,6 +127,21 @@ __device__ __forceinline__ void grid_build_cta(int n, const int* __restrict__ ce
 
 __global__ void __launch_bounds__(kGridThreads) k_grid_build(int n, const int* __restrict__ cellOf, int* __restrict__ cellOff,
                                                              int* __restrict__ cellIdx) {
+    grid_build_cta(n, cellOf, cellOff, cellIdx);
+}
+
+// k_grid_prepare + k_grid_build of one frame in one launch (one CTA: the frames of single searches hold a few thousand keypoints)
+__global__ void __launch_bounds__(kGridThreads) k_frame_grid(int n, const orbx_keypoint* __restrict__ kps, float4* __restrict__ kp4,
+                                                             int* __restrict__ cellOf, int* __restrict__ cellOff, int* __restrict__ cellIdx,
+                                                             float minX, float minY, float invW, float invH) {
+    for (int i = threadIdx.x; i < n; i += kGridThreads) {
+        const orbx_keypoint k = kps[i];
+        kp4[i] = make_float4(k.x, k.y, k.angle, __int_as_float(k.octave));
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(k.x, minX), invW));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(k.y, minY), invH));
+        cellOf[i] = (px < 0 || px >= kGridCols || py < 0 || py >= kGridRows) ? -1 : px * kGridRows + py;
+    }
+    __syncthreads();
     grid_build_cta(n, cellOf, cellOff, cellIdx);
 }
 
