@@ -102,6 +102,7 @@ struct Extractor {
     orbx_keypoint* hKp = nullptr;
     uint8_t* hDesc = nullptr;
     int* hCnt = nullptr;
+    size_t outBlockBytes = 0;          // dOutKp | dOutDesc | dOutCnt (and hKp | hDesc | hCnt) are one allocation of this size
     int lastFrames = 0;
     Level0 lastL0{};
 
@@ -155,9 +156,7 @@ void freeShape(Extractor* E) {
     for (void* p : E->allocs) cudaFree(p);
     E->allocs.clear();
     if (E->hImg) cudaFreeHost(E->hImg);
-    if (E->hKp) cudaFreeHost(E->hKp);
-    if (E->hDesc) cudaFreeHost(E->hDesc);
-    if (E->hCnt) cudaFreeHost(E->hCnt);
+    if (E->hKp) cudaFreeHost(E->hKp);           // one block: hDesc and hCnt point into it
     E->hImg = nullptr; E->hKp = nullptr; E->hDesc = nullptr; E->hCnt = nullptr;
     E->W = E->H = 0;
 }
@@ -477,9 +476,16 @@ int configureShape(Extractor* E, int W, int H) {
     if ((rc = devAlloc(E, &E->dQtB, g.qtCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dLvlKp, (size_t)g.kpCapFrame * B))) return rc;
     if ((rc = devAlloc(E, &E->dLvlCnt, (size_t)L * B))) return rc;
-    if ((rc = devAlloc(E, &E->dOutKp, (size_t)g.outCap * B))) return rc;
-    if ((rc = devAlloc(E, &E->dOutDesc, (size_t)g.outCap * B * 32))) return rc;
-    if ((rc = devAlloc(E, &E->dOutCnt, (size_t)2 * B))) return rc;
+    // keypoints | descriptors | {n, monoIndex} of all frames in ONE block (device and page-locked host): a single frame's
+    // results come back in one copy instead of three
+    const size_t outKpBytes = ((size_t)g.outCap * B * sizeof(orbx_keypoint) + 255) & ~(size_t)255;
+    const size_t outDsBytes = ((size_t)g.outCap * B * 32 + 255) & ~(size_t)255;
+    E->outBlockBytes = outKpBytes + outDsBytes + (size_t)2 * B * sizeof(int);
+    uint8_t* outBlock = nullptr;
+    if ((rc = devAlloc(E, &outBlock, E->outBlockBytes))) return rc;
+    E->dOutKp = reinterpret_cast<orbx_keypoint*>(outBlock);
+    E->dOutDesc = outBlock + outKpBytes;
+    E->dOutCnt = reinterpret_cast<int*>(outBlock + outKpBytes + outDsBytes);
     if ((rc = devAlloc(E, &E->dWork, (size_t)g.outCap * B))) return rc;
     if ((rc = devAlloc(E, &E->dGeom, 1))) return rc;
     if ((rc = devAlloc(E, &E->dCells, E->cells.size()))) return rc;
@@ -488,9 +494,11 @@ int configureShape(Extractor* E, int W, int H) {
     CK(cudaMemcpy(E->dCells, E->cells.data(), E->cells.size() * sizeof(FastCell), cudaMemcpyHostToDevice));
     if (!taps.empty()) CK(cudaMemcpy(E->dTaps, taps.data(), taps.size() * sizeof(ResizeTap), cudaMemcpyHostToDevice));
     CK(cudaMallocHost((void**)&E->hImg, g.lv[0].planeBytes * B));
-    CK(cudaMallocHost((void**)&E->hKp, (size_t)g.outCap * B * sizeof(orbx_keypoint)));
-    CK(cudaMallocHost((void**)&E->hDesc, (size_t)g.outCap * B * 32));
-    CK(cudaMallocHost((void**)&E->hCnt, (size_t)2 * B * sizeof(int)));
+    uint8_t* hostBlock = nullptr;
+    CK(cudaMallocHost((void**)&hostBlock, E->outBlockBytes));
+    E->hKp = reinterpret_cast<orbx_keypoint*>(hostBlock);
+    E->hDesc = hostBlock + outKpBytes;
+    E->hCnt = reinterpret_cast<int*>(hostBlock + outKpBytes + outDsBytes);
     E->W = W; E->H = H;
     E->lastFrames = 0;
     return ORBX_OK;
@@ -945,6 +953,11 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int 
             }
             Level0 l0{dchunk, slot, pitch0};
             if ((rc = runPass(E, l0, nc, lap0, lap1, st, c0))) return rc;
+            if (B == 1 && kps && desc && !kpPinned && !dsPinned) {
+                // one frame per pass (an agent's Tracking thread): the whole result block in one copy
+                CK(cudaMemcpyAsync(E->hKp, E->dOutKp, E->outBlockBytes, cudaMemcpyDeviceToHost, st));
+                continue;
+            }
             CK(cudaMemcpyAsync(E->hCnt + 2 * c0, E->dOutCnt + 2 * c0, (size_t)2 * nc * sizeof(int), cudaMemcpyDeviceToHost, st));
             if (kps) {
                 if (kpPinned)
@@ -962,7 +975,7 @@ int orbx_extract_batch(orbx_handle h, const uint8_t* const* imgs, int nimg, int 
             }
         }
         CK(cudaStreamSynchronize(E->stream));
-        CK(cudaStreamSynchronize(E->stream2));
+        if (n > C) CK(cudaStreamSynchronize(E->stream2));        // a second sub-batch ran there
         E->lastFrames = n;
         if ((rc = collectStageTimes(E))) return rc;
         for (int f = 0; f < n; ++f) {
