@@ -403,8 +403,11 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     const int grid = P.state != 0 ? 1 : std::max(1, std::min(units, M->smCount * 2));
     if (byRounds) {
         P.ticket = S.dev<unsigned int>(oTicket);
+        // the resolving CTA writes [occupancy, counters, results] straight into the page-locked mirror (UVA: the pinned buffer is
+        // addressable from the device), so the call is one copy up, one launch, one wait
+        const size_t outBytes = (outEnd - oOcc + 15) & ~(size_t)15;
         k_search_rounds<<<(nq + kRoundQueries - 1) / kRoundQueries, kRoundThreads, rounds_smem_bytes(n, nq), M->stream>>>(
-            P, S.dev<uint4>(oLists), S.dev<int>(oCnt));
+            P, S.dev<uint4>(oLists), S.dev<int>(oCnt), S.host<uint4>(oOcc), S.dev<uint4>(oOcc), (int)(outBytes / 16));
         ++M->launches;
     } else if (byNode) {
         // BoW: a warp per shared node, rotation filter fused into the last CTA (orbm_kernels.cuh, k_search_nodes)
@@ -419,7 +422,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
         if (P.checkOri) { k_rot_filter<<<1, 256, 0, M->stream>>>(nq, P.qBin, P.qResult); ++M->launches; }
     }
     CKM(cudaGetLastError());
-    CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOcc, (uint8_t*)M->scratch + oOcc, outEnd - oOcc, cudaMemcpyDeviceToHost, M->stream));
+    if (!byRounds) CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOcc, (uint8_t*)M->scratch + oOcc, outEnd - oOcc, cudaMemcpyDeviceToHost, M->stream));
     CKM(cudaStreamSynchronize(M->stream));
     memcpy(io.result.data(), S.host<int>(oRes), (size_t)nq * sizeof(int));
     memcpy(io.dist.data(), S.host<int>(oDist), (size_t)nq * sizeof(int));

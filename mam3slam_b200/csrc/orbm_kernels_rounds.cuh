@@ -264,7 +264,10 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
 
 // One search (orbm_search_frame / orbm_search_sim3): grid = ceil(nq / kRoundQueries) CTAs; the last one to finish resolves and
 // runs the rotation-consistency epilogue.
-__global__ void __launch_bounds__(kRoundThreads) k_search_rounds(const SearchParams P, uint4* lists, int* counts) {
+// mirrorDst / mirrorSrc / mirrorVec: the block (occupancy, counters, results) is written to the caller's page-locked host
+// mirror by this CTA at the end - no separate device-to-host copy on the latency path.
+__global__ void __launch_bounds__(kRoundThreads) k_search_rounds(const SearchParams P, uint4* lists, int* counts, uint4* mirrorDst,
+                                                                 const uint4* mirrorSrc, int mirrorVec) {
     extern __shared__ __align__(16) uint8_t dyn[];
     __shared__ int isLast;
     unsigned long long nEval = 0;
@@ -287,6 +290,10 @@ __global__ void __launch_bounds__(kRoundThreads) k_search_rounds(const SearchPar
     __threadfence();
     rounds_resolve_cta(P, dyn, lists, counts);
     if (P.checkOri) rot_filter_cta(P.nq, P.qBin, P.qResult, true);
+    if (mirrorDst) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < mirrorVec; i += blockDim.x) mirrorDst[i] = mirrorSrc[i];
+    }
 }
 
 // The tracking step of a batch (orbm_track_batch_device): grid = (ceil(stride / kRoundQueries), pairs); the last CTA of a pair
