@@ -64,6 +64,7 @@ struct orbm_matcher {
     unsigned int* knnBound = nullptr; int knnBoundCap = 0;         // shared pruning bound per query (all ones at rest)
     unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
     void* trackBuf = nullptr; size_t trackBytes = 0; int trackFrames = 0, trackStride = 0;
+    int lastRounds = 0, lastSerial = 0;          // claim rounds of the last search (0 = in-order kernel), 1 = finished in order
 };
 
 namespace {
@@ -428,9 +429,11 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     memcpy(io.dist.data(), S.host<int>(oDist), (size_t)nq * sizeof(int));
     if (io.occ && n && P.state == 1) memcpy(io.occ, S.host<uint8_t>(oOcc), n);
     M->lastEvals = (long long)*S.host<unsigned long long>(oEv);
+    M->lastRounds = byRounds ? (int)S.host<unsigned long long>(oEv)[1] : 0;
+    M->lastSerial = byRounds ? (int)S.host<unsigned long long>(oEv)[2] : 0;
 #ifdef ORBM_STATS
     if (byRounds) fprintf(stderr, "rounds: nq %d evals %llu rounds %llu incomplete %llu resolve cycles %llu walk cycles (max CTA) %llu; re-walks %llu in %llu rounds, %llu cycles\n", nq,
-                          S.host<unsigned long long>(oEv)[0], S.host<unsigned long long>(oEv)[1], S.host<unsigned long long>(oEv)[2],
+                          S.host<unsigned long long>(oEv)[0], S.host<unsigned long long>(oEv)[1], S.host<unsigned long long>(oEv)[12],
                           S.host<unsigned long long>(oEv)[3], S.host<unsigned long long>(oEv)[4], S.host<unsigned long long>(oEv)[5],
                           S.host<unsigned long long>(oEv)[6], S.host<unsigned long long>(oEv)[7]);
     if (byRounds) { fprintf(stderr, "  cycles in step 1 / 1r / 1b / 2:"); for (int i = 8; i < 12; ++i) fprintf(stderr, " %llu", S.host<unsigned long long>(oEv)[i]); fprintf(stderr, "\n"); }
@@ -1468,6 +1471,15 @@ extern "C" long long orbm_track_evaluations(orbm_handle M) {
     if (cudaDeviceSynchronize() != cudaSuccess) return -1;
     if (cudaMemcpy(&v, M->dEvals, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
     return (long long)v;
+}
+
+// developer aid, not part of include/orbm.h: how the last single search was resolved - claim rounds run (0 = the in-order
+// kernel) and whether it finished in query order on one warp (long chains of competing queries)
+extern "C" int orbm_debug_last_rounds(orbm_handle M, int* rounds, int* serial) {
+    if (!M) return ORBM_ERR_INVALID;
+    if (rounds) *rounds = M->lastRounds;
+    if (serial) *serial = M->lastSerial;
+    return ORBM_OK;
 }
 
 // developer aid, not part of include/orbm.h: the 16 counters of the last tracking step ([0] = evaluations; the rest are

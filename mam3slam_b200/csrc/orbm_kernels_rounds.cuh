@@ -133,6 +133,9 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
         flag[q] = (uint8_t)((c > 4 ? kRfIncomplete : 0) | ((!P.qocc || P.qocc[q]) ? kRfOccupies : 0));
     }
     if (tid == 0) { sBarrier = 0; sQueued = 0; }
+    bool serial = false;
+    unsigned roundsRun = 0;
+    int prevOpen = INT_MAX, slowRounds = 0;
     __syncthreads();
 #ifdef ORBM_STATS
     const long long rT0 = clock64();
@@ -140,6 +143,7 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
 #endif
     for (unsigned round = 1;; ++round) {
         const unsigned tag = round << 16;
+        roundsRun = round;
 #ifdef ORBM_STATS
         const long long rc0 = clock64();
 #endif
@@ -245,13 +249,74 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
 #endif
         if (!stillOpen) {
 #ifdef ORBM_STATS
-            if (tid == 0) { P.evals[1] = round; P.evals[3] = (unsigned long long)(clock64() - rT0); P.evals[8] = st1; P.evals[9] = st1r; P.evals[10] = st1b; P.evals[11] = st2; }
+            if (tid == 0) { P.evals[3] = (unsigned long long)(clock64() - rT0); P.evals[8] = st1; P.evals[9] = st1r; P.evals[10] = st1b; P.evals[11] = st2; }
 #endif
             break;
         }
+        // Long chains of queries that all compete for the same few keypoints settle a query or two per round: from there on the
+        // reference's own order is the faster way (below).  Progress = threads that have no open query left (exact with one
+        // query per thread, an under-estimate beyond 1024 queries; the value is the barrier's, so the decision is uniform).
+        // A single slow round is usually one query holding the later ones back (step 1b) with hundreds ready to go in the next
+        // round, so only a run of slow rounds counts.
+        slowRounds = (prevOpen - stillOpen < 4) ? slowRounds + 1 : 0;
+        if (round >= 8 && slowRounds >= 4) { serial = true; break; }
+        prevOpen = stillOpen;
     }
+    if (serial) {
+        // in-order finish by one warp (all lanes do the same scalar work; the lanes only share the window walks): every query
+        // before q is settled, so q's first unblocked entries are what the reference sees
+        // the open queries in ascending order (ballot ranks inside a warp, warp counts summed across the CTA)
+        __shared__ int sWarpOpen[32], sOpenBase;
+        if (tid == 0) sOpenBase = 0;
+        __syncthreads();
+        for (int q0 = 0; q0 < nq; q0 += nthr) {
+            const int q = q0 + tid;
+            const bool isOpen = q < nq && !(flag[q] & kRfResolved);
+            const unsigned bal = __ballot_sync(0xffffffffu, isOpen);
+            if ((tid & 31) == 0) sWarpOpen[tid >> 5] = __popc(bal);
+            __syncthreads();
+            int before = sOpenBase;
+            for (int w = 0; w < (tid >> 5); ++w) before += sWarpOpen[w];
+            if (isOpen) queue[before + __popc(bal & ((1u << (tid & 31)) - 1))] = (uint16_t)q;
+            __syncthreads();
+            if (tid == nthr - 1) sOpenBase = before + __popc(bal);
+            __syncthreads();
+        }
+        const int nOpen = sOpenBase;
+        if (tid < 32) {
+            for (int i = 0; i < nOpen; ++i) {
+                const int q = queue[i];
+                const uint8_t f = flag[q];
+                uint4 l = L[q];
+                bool b0 = l.x != kNoEntry && !owner_blocks(owner, l.x & 0x7ffff, q), b1 = l.y != kNoEntry && !owner_blocks(owner, l.y & 0x7ffff, q);
+                bool b2 = l.z != kNoEntry && !owner_blocks(owner, l.z & 0x7ffff, q), b3 = l.w != kNoEntry && !owner_blocks(owner, l.w & 0x7ffff, q);
+                if ((int)b0 + (int)b1 + (int)b2 + (int)b3 < needed && (f & kRfIncomplete)) {
+                    Top4 t; unsigned long long dummy = 0;
+                    warp_list(P, P.tgt, q, [&](int idx) { return owner_blocks(owner, idx, q); }, t, dummy);
+                    l = make_uint4(t.t0, t.t1, t.t2, t.t3);
+                    b0 = l.x != kNoEntry; b1 = l.y != kNoEntry; b2 = l.z != kNoEntry; b3 = l.w != kNoEntry;
+                }
+                uint8_t nf = f | kRfResolved;
+                if (b0 || b1 || b2 || b3) {
+                    const unsigned m = (unsigned)b0 | ((unsigned)b1 << 1) | ((unsigned)b2 << 2) | ((unsigned)b3 << 3);
+                    const int ia = __ffs(m) - 1, ib = __ffs(m & (m - 1)) - 1;
+                    const uint32_t e = ia == 0 ? l.x : ia == 1 ? l.y : ia == 2 ? l.z : l.w;
+                    const uint32_t e2 = needed == 2 ? (ib == 1 ? l.y : ib == 2 ? l.z : ib == 3 ? l.w : kNoEntry) : kNoEntry;
+                    if (decide_query(P, e, e2)) {
+                        if (f & kRfOccupies) owner[e & 0x7ffff] = (uint16_t)(q + 1);
+                        pick[q] = e;
+                        nf |= kRfAccepted;
+                    }
+                }
+                flag[q] = nf;
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) { P.evals[1] = roundsRun; P.evals[2] = serial ? 1ull : 0ull; }       // reporting (orbm_debug_last_rounds)
 #ifdef ORBM_STATS
-    { int inc = 0; for (int q = tid; q < nq; q += nthr) inc += __ldcg(counts + q) > 4; if (inc) atomicAdd(P.evals + 2, (unsigned long long)inc); }
+    { int inc = 0; for (int q = tid; q < nq; q += nthr) inc += __ldcg(counts + q) > 4; if (inc) atomicAdd(P.evals + 12, (unsigned long long)inc); }
 #endif
     // results in one pass (the rotation bin needs the accepted keypoint's angle from global memory: one round trip, not one per round)
     for (int q = tid; q < nq; q += nthr) {

@@ -1,5 +1,7 @@
 """GPU parity of every matcher entry point (through the C ABI) against the CPU oracle's literal restatements of the
 reference functions (oracle/cpp/orc_matcher.cc).  Bar: matches, assigned indices and distances bit-exact."""
+import os
+
 import numpy as np
 import pytest
 
@@ -585,3 +587,72 @@ def test_contention_many_queries_few_keypoints(M):
         assert nm == onm and np.array_equal(m12, om12) and np.array_equal(pm, opm), ori
     M.mbCheckOrientation = True
     F1.close(); F2.close()
+
+
+def _last_rounds(M):
+    import ctypes
+    r, s = ctypes.c_int(0), ctypes.c_int(0)
+    M._L.orbm_debug_last_rounds.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
+    assert M._L.orbm_debug_last_rounds(M._h, ctypes.byref(r), ctypes.byref(s)) == 0
+    return r.value, s.value
+
+
+def test_claim_rounds_long_chain_finishes_in_order(M):
+    """Hundreds of queries that all compete for the same sixty keypoints: the claim rounds settle one or two queries per round,
+    so the resolver hands over to the in-order finish (one warp, the reference's own order, windows walked again when a list
+    is used up).  Results equal the sequential oracle; a normal tracking pair stays in rounds."""
+    rng = np.random.default_rng(11)
+    bounds = (0.0, 0.0, 752.0, 480.0)
+    scale = (1.2 ** np.arange(8)).astype(np.float32)
+    n2, nq = 60, 700
+    k2 = np.zeros(n2, sc.KP)
+    k2["x"] = 400 + rng.random(n2).astype(np.float32) * 6
+    k2["y"] = 240 + rng.random(n2).astype(np.float32) * 6
+    k2["octave"] = 1
+    k2["angle"] = rng.random(n2).astype(np.float32) * 360
+    k2["size"] = 31; k2["response"] = 50; k2["class_id"] = -1
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    d2 = np.repeat(base[None], n2, 0)
+    for i in range(n2):
+        for b in rng.choice(256, 1 + i % 5, replace=False):
+            d2[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    qd = np.repeat(base[None], nq, 0)
+    for i in range(nq):
+        for b in rng.choice(256, i % 4, replace=False):
+            qd[i, b >> 3] ^= np.uint8(1 << (b & 7))
+    u = (400 + rng.random(nq) * 6).astype(np.float32)
+    v = (240 + rng.random(nq) * 6).astype(np.float32)
+    octave = np.ones(nq, np.int32)
+    angle = (rng.random(nq) * 360).astype(np.float32)
+    valid = np.ones(nq, np.uint8)
+    F = M.frame(k2, d2, bounds)
+    for ori in (False, True):
+        M.mbCheckOrientation = ori
+        for qocc in (None, (rng.random(nq) < 0.5).astype(np.uint8)):
+            occ = np.zeros(n2, np.uint8)
+            nm, km = M.SearchByProjection_Frame(F, occ, scale, valid, u, v, octave, angle, qd, 15.0, 100, q_occupies=qocc)
+            rounds, serial = _last_rounds(M)
+            onm, okm = om.search_frame(k2, d2, bounds, occ, scale, valid, u, v, octave, angle, qd, 15.0, 100, ori, q_occupies=qocc)
+            assert nm == onm and np.array_equal(km, okm), (ori, qocc is not None)
+            if os.environ.get("ORBM_ROUNDS", "1") != "0":
+                assert rounds >= 8 and serial == 1, (rounds, serial)
+    # the best / second-best rule on the same pile-up (M1)
+    vc = np.ones(nq, np.float32)
+    for ratio in (0.8, 0.95):
+        M.mfNNratio = ratio
+        occ = np.zeros(n2, np.uint8)
+        nm, km, occ_after = M.SearchByProjection_LocalMap(F, occ, scale, valid, u, v, octave, vc, qd, 3.0)
+        onm, okm, oocc = om.search_local_map(k2, d2, bounds, occ, scale, valid, u, v, octave, vc, qd, 3.0, ratio)
+        assert nm == onm and np.array_equal(km, okm) and np.array_equal(occ_after, oocc), ratio
+    M.mfNNratio = 0.9
+    M.mbCheckOrientation = True
+    F.close()
+    # ordinary tracking data: a handful of rounds, no hand-over
+    (k1, d1), (k2, d2), _, _ = sc.frame_pair(752, 480, 1000, 0)
+    F = M.frame(k2, d2, bounds)
+    nm, km = M.SearchByProjection_Frame(F, np.zeros(len(k2), np.uint8), scale, np.ones(len(k1), np.uint8), k1["x"], k1["y"],
+                                        k1["octave"], k1["angle"], d1, 15.0, 100)
+    rounds, serial = _last_rounds(M)
+    if os.environ.get("ORBM_ROUNDS", "1") != "0":
+        assert 1 <= rounds < 64 and serial == 0, (rounds, serial)
+    F.close()
