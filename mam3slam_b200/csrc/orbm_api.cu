@@ -63,7 +63,7 @@ struct orbm_matcher {
     unsigned long long* knnPart = nullptr; size_t knnPartBytes = 0;
     unsigned int* knnBound = nullptr; int knnBoundCap = 0;         // shared pruning bound per query (all ones at rest)
     unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
-    void* trackBuf = nullptr; size_t trackBytes = 0; int trackFrames = 0, trackStride = 0;
+    void* trackBuf = nullptr; size_t trackBytes = 0;
     int lastRounds = 0, lastSerial = 0;          // claim rounds of the last search (0 = in-order kernel), 1 = finished in order
 };
 
@@ -236,7 +236,7 @@ int orbm_create(int device, orbm_handle* out) {
     orbx::raise_dyn_smem((const void*)k_search<false>, device, 200 * 1024);
     orbx::raise_dyn_smem((const void*)k_track_search, device, 200 * 1024);
     orbx::raise_dyn_smem((const void*)k_search_rounds, device, kRoundsSmemMax);
-    orbx::raise_dyn_smem((const void*)k_track_rounds, device, kRoundsSmemMax);
+    orbx::raise_dyn_smem((const void*)k_track_resolve, device, kRoundsSmemMax);
     *out = M;
     return ORBM_OK;
 }
@@ -1402,10 +1402,8 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     const size_t oKp4 = take(NS * 16), oCellOf = take(NS * 4), oCellIdx = take(NS * 4), oCellOff = take((size_t)nframes * (kGridCells + 1) * 4);
     const size_t oWin = take(NS * 16), oLev = take(NS * 8), oAng = take(NS * 4), oOcc = take(NS);
     const size_t oRes = take(NS * 4), oDist = take(NS * 4), oBin = take(NS * 4);
-    const size_t oLists = take(NS * 16), oListCnt = take(NS * 4), oTickets = take((size_t)nframes * 4);
-    bool fresh = false;
+    const size_t oLists = take(NS * 16), oListCnt = take(NS * 4);
     if (off > M->trackBytes) {
-        fresh = true;
         if (M->trackBuf) { CKM(cudaStreamSynchronize(st)); cudaFree(M->trackBuf); }
         M->trackBuf = nullptr; M->trackBytes = 0;
         CKM(cMalloc(&M->trackBuf, off));
@@ -1425,16 +1423,11 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     T.qwin = (float4*)(b + oWin); T.qlev = (int2*)(b + oLev); T.qangle = (float*)(b + oAng); T.occ = b + oOcc;
     T.qResult = (int*)(b + oRes); T.qDist = (int*)(b + oDist); T.qBin = (int*)(b + oBin);
     T.kpMatch = d_kp_match; T.nMatches = d_nmatches; T.evals = M->dEvals;
-    T.lists = (uint4*)(b + oLists); T.listCounts = (int*)(b + oListCnt); T.tickets = (unsigned int*)(b + oTickets);
-    // the last CTA of a pair leaves its ticket at zero; a new or re-laid-out buffer starts from zero (the layout depends on
-    // nframes and frame_stride, so a different batch shape on the same handle re-zeroes as well)
-    if (fresh || M->trackFrames != nframes || M->trackStride != frame_stride) {
-        CKM(cudaMemsetAsync(T.tickets, 0, (size_t)nframes * 4, st));
-        M->trackFrames = nframes; M->trackStride = frame_stride;
-    }
-    // Off by default for the batch: measured on 64-frame steps the claim-rounds launch (2205 CTAs of 1024 threads) is a shorter
-    // stage by itself only with small CTAs and costs the overlapped step 10 % (109.7 k against 123.7 k frames/s): the in-order
-    // kernel's 63 small CTAs sit beside the other handles' kernels, this one does not.  ORBM_TRACK_ROUNDS=1 turns it on (A/B).
+    T.lists = (uint4*)(b + oLists); T.listCounts = (int*)(b + oListCnt);
+    // Off by default for the batch: measured on 64-frame steps the stage is shorter by itself (0.124 against 0.135 ms) but the
+    // overlapped step loses 8 % (113.8 k against 122.9 k frames/s): the 63 resolving CTAs of 1024 threads take a whole SM each
+    // where the in-order kernel's 63 CTAs of 256 threads leave room for the other handles' kernels.  ORBM_TRACK_ROUNDS=1 turns
+    // it on (A/B).
     static const bool roundsOk = [] { const char* e = getenv("ORBM_TRACK_ROUNDS"); return e && e[0] == '1'; }();
     const bool byRounds = roundsOk && frame_stride <= kRoundsMaxQueries && rounds_smem_bytes(frame_stride, frame_stride) <= kRoundsSmemMax;
     // ORBM_TRACK_STAGE=0 (A/B): the target frame stays in L2 instead of shared memory - a slower kernel with a third of the footprint
@@ -1448,10 +1441,11 @@ extern "C" int orbm_track_batch_device(orbm_handle M, int nframes, const orbx_ke
     CKM(orbx::launch_prio(k_track_grid, dim3(nframes), dim3(kGridThreads), 0, st, M->prio, T));
     M->launches += 2;
     if (nframes > 1 && byRounds) {
-        // claim rounds: a warp per query over the whole GPU, the last CTA of a pair resolves, filters and scatters
-        CKM(orbx::launch_prio(k_track_rounds, dim3((frame_stride + kRoundQueries - 1) / kRoundQueries, nframes - 1), dim3(kRoundThreads),
-                              rounds_smem_bytes(frame_stride, frame_stride), st, M->prio, T));
-        M->launches += 1;
+        // claim rounds: a warp per query over the whole GPU (small CTAs), then one CTA per pair resolves, filters and scatters
+        CKM(orbx::launch_prio(k_track_walk, dim3((frame_stride + 7) / 8, nframes - 1), dim3(256), 0, st, M->prio, T));
+        CKM(orbx::launch_prio(k_track_resolve, dim3(nframes - 1), dim3(kRoundThreads), rounds_smem_bytes(frame_stride, frame_stride), st,
+                              M->prio, T));
+        M->launches += 2;
     } else if (nframes > 1) {
         CKM(orbx::launch_prio(k_track_search, dim3(nframes - 1), dim3(kSearchThreads), smem, st, M->prio, T));
         CKM(orbx::launch_prio(k_track_finish, dim3(nframes - 1), dim3(256), 0, st, M->prio, T));

@@ -1097,7 +1097,7 @@ struct TrackBatch {
     int* qResult; int* qDist; int* qBin;
     int* kpMatch; int* nMatches /* nframes */;
     unsigned long long* evals;
-    uint4* lists; int* listCounts; unsigned int* tickets /* nframes, zero between passes */;   // claim rounds (orbm_kernels_rounds.cuh)
+    uint4* lists; int* listCounts;          // claim rounds (orbm_kernels_rounds.cuh): the short list of every query, [nframes x stride]
 };
 
 __global__ void k_track_prepare(const TrackBatch T) {

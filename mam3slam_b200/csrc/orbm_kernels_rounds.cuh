@@ -116,6 +116,7 @@ __device__ __forceinline__ void rounds_walk_cta(const SearchParams& P, int q0, u
 __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_t* dyn, const uint4* lists, const int* counts) {
     __shared__ unsigned int sBarrier;
     __shared__ int sQueued;
+    __shared__ int sSettled[2];          // queries settled in a round, by round parity
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int n = P.tgt.n, nq = P.nq;
     uint16_t* owner = reinterpret_cast<uint16_t*>(dyn);
@@ -132,10 +133,10 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
         const int c = __ldcg(counts + q);
         flag[q] = (uint8_t)((c > 4 ? kRfIncomplete : 0) | ((!P.qocc || P.qocc[q]) ? kRfOccupies : 0));
     }
-    if (tid == 0) { sBarrier = 0; sQueued = 0; }
+    if (tid == 0) { sBarrier = 0; sQueued = 0; sSettled[0] = sSettled[1] = 0; }
     bool serial = false;
     unsigned roundsRun = 0;
-    int prevOpen = INT_MAX, slowRounds = 0;
+    int slowRounds = 0;
     __syncthreads();
 #ifdef ORBM_STATS
     const long long rT0 = clock64();
@@ -173,6 +174,7 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
             settle(q, f, l, b0, b1, b2, b3);
         }
         __syncthreads();
+        if (tid == 0) sSettled[(round + 1) & 1] = 0;        // last read before this barrier (end of the previous round), next written in round + 1
 #ifdef ORBM_STATS
         c1 = clock64(); st1 += c1 - rc0;
 #endif
@@ -225,7 +227,7 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
         // step 2: a pick without an earlier registrant is final
         const unsigned bar = sBarrier;
         const int barQ = (bar >> 16) == round ? (int)(0xffffu - (bar & 0xffffu)) : INT_MAX;
-        int open = 0;
+        int open = 0, settled = 0;
         for (int q = tid; q < nq; q += nthr) {
             const uint8_t f = flag[q];
             if (f & kRfResolved) continue;
@@ -241,8 +243,10 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
                 const bool acc = decide_query(P, e, e2);
                 if (acc && (f & kRfOccupies)) owner[K] = (uint16_t)(q + 1);
                 flag[q] = f | kRfResolved | (acc ? kRfAccepted : 0);
+                ++settled;
             } else ++open;
         }
+        if (settled) atomicAdd(&sSettled[round & 1], settled);
         const int stillOpen = __syncthreads_count(open);
 #ifdef ORBM_STATS
         if (tid == 0) { st2 += clock64() - c2; }
@@ -254,13 +258,11 @@ __device__ __forceinline__ void rounds_resolve_cta(const SearchParams& P, uint8_
             break;
         }
         // Long chains of queries that all compete for the same few keypoints settle a query or two per round: from there on the
-        // reference's own order is the faster way (below).  Progress = threads that have no open query left (exact with one
-        // query per thread, an under-estimate beyond 1024 queries; the value is the barrier's, so the decision is uniform).
-        // A single slow round is usually one query holding the later ones back (step 1b) with hundreds ready to go in the next
-        // round, so only a run of slow rounds counts.
-        slowRounds = (prevOpen - stillOpen < 4) ? slowRounds + 1 : 0;
+        // reference's own order is the faster way (below).  The count is complete after the barrier and read by everyone before
+        // the next one, so the decision is uniform.  A single slow round is usually one query holding the later ones back
+        // (step 1b) with hundreds ready to go in the next round, so only a run of slow rounds counts.
+        slowRounds = (sSettled[round & 1] < 4) ? slowRounds + 1 : 0;
         if (round >= 8 && slowRounds >= 4) { serial = true; break; }
-        prevOpen = stillOpen;
     }
     if (serial) {
         // in-order finish by one warp (all lanes do the same scalar work; the lanes only share the window walks): every query
@@ -361,29 +363,28 @@ __global__ void __launch_bounds__(kRoundThreads) k_search_rounds(const SearchPar
     }
 }
 
-// The tracking step of a batch (orbm_track_batch_device): grid = (ceil(stride / kRoundQueries), pairs); the last CTA of a pair
-// resolves it, filters by rotation and scatters into the reference's output (what k_track_finish does for the in-order path).
-__global__ void __launch_bounds__(kRoundThreads) k_track_rounds(const TrackBatch T) {
-    extern __shared__ __align__(16) uint8_t dyn[];
-    __shared__ int isLast, cnt;
+// The tracking step of a batch (orbm_track_batch_device) in two launches: the walk over small CTAs (a warp per query of every
+// pair: grid = (ceil(stride / 8), pairs) x 256), then one resolving CTA per pair that also filters by rotation and scatters into
+// the reference's output (what k_track_finish does for the in-order path).
+__global__ void __launch_bounds__(256) k_track_walk(const TrackBatch T) {
     const int pair = blockIdx.y, cur = pair + 1;
     SearchParams P;
     track_pair_params(T, pair, P);
-    uint4* lists = T.lists + (size_t)cur * T.stride;
-    int* counts = T.listCounts + (size_t)cur * T.stride;
     unsigned long long nEval = 0;
-    rounds_walk_cta(P, blockIdx.x * kRoundQueries, lists, counts, nEval);
+    rounds_walk_cta(P, blockIdx.x * (blockDim.x >> 5), T.lists + (size_t)cur * T.stride, T.listCounts + (size_t)cur * T.stride, nEval);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) nEval += __shfl_xor_sync(0xffffffffu, nEval, o);
     if ((threadIdx.x & 31) == 0 && nEval) atomicAdd(P.evals, nEval);
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) isLast = atomicAdd(T.tickets + pair, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!isLast) return;
-    __threadfence();
-    if (threadIdx.x == 0) { T.tickets[pair] = 0; cnt = 0; }          // ready for the next pass
-    if (P.nq > 0) rounds_resolve_cta(P, dyn, lists, counts);
+}
+
+__global__ void __launch_bounds__(kRoundThreads) k_track_resolve(const TrackBatch T) {
+    extern __shared__ __align__(16) uint8_t dyn[];
+    __shared__ int cnt;
+    const int pair = blockIdx.x, cur = pair + 1;
+    SearchParams P;
+    track_pair_params(T, pair, P);
+    if (threadIdx.x == 0) cnt = 0;
+    if (P.nq > 0) rounds_resolve_cta(P, dyn, T.lists + (size_t)cur * T.stride, T.listCounts + (size_t)cur * T.stride);
     if (T.checkOri) rot_filter_cta(P.nq, P.qBin, P.qResult);
     __syncthreads();
     int mine = 0;
