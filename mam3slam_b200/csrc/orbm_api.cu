@@ -39,7 +39,8 @@ struct orbm_frame_s {
     // host uploads: keypoints and descriptors share one device block and go up in ONE copy from a page-locked staging buffer
     // of the slot (two copies from the caller's pageable arrays cost ~8 us of host time each)
     uint8_t* stage = nullptr; size_t descOff = 0;
-    cudaEvent_t staged = nullptr;         // the last upload has left the staging buffer
+    const void* uploadedBy = nullptr;     // handle whose stream carried the last upload from `stage`, and its syncEpoch then
+    unsigned long long uploadEpoch = 0;
 };
 
 struct orbm_db_s {
@@ -64,6 +65,7 @@ struct orbm_matcher {
     unsigned int* knnBound = nullptr; int knnBoundCap = 0;         // shared pruning bound per query (all ones at rest)
     unsigned int* knnCounter = nullptr; int knnCounterCap = 0;     // chunks-done counter per query block (fused merge), zero at rest
     void* trackBuf = nullptr; size_t trackBytes = 0;
+    unsigned long long syncEpoch = 1;          // completed waits on `stream` (syncStream)
     int lastRounds = 0, lastSerial = 0;          // claim rounds of the last search (0 = in-order kernel), 1 = finished in order
 };
 
@@ -98,6 +100,14 @@ int ensureScratch(orbm_matcher* M, size_t bytes) {
     return ORBM_OK;
 }
 
+// every wait on the handle's stream goes through here: frame slots use the count to know that their last upload has left the
+// page-locked staging buffer (a search always waits, so in steady state the next upload needs no CUDA call to be safe)
+static inline cudaError_t syncStream(orbm_matcher* M) {
+    const cudaError_t e = cudaStreamSynchronize(M->stream);
+    if (e == cudaSuccess) ++M->syncEpoch;
+    return e;
+}
+
 // bump allocator over the pinned staging buffer and its device twin (same offsets)
 struct Stage {
     orbm_matcher* M; size_t off = 0;
@@ -110,7 +120,6 @@ struct Stage {
 void freeFrameBuffers(orbm_frame_s* f) {
     if (f->ownsInput) cudaFree(f->kpsDev);         // one block: descDev points into it
     if (f->stage) { cudaFreeHost(f->stage); f->stage = nullptr; }
-    if (f->staged) { cudaEventDestroy(f->staged); f->staged = nullptr; }
     cudaFree(f->kp4); cudaFree(f->cellOf); cudaFree(f->cellOff); cudaFree(f->cellIdx);
     f->kpsDev = nullptr; f->descDev = nullptr; f->kp4 = nullptr; f->cellOf = f->cellOff = f->cellIdx = nullptr;
     f->cap = 0; f->ownsInput = false;
@@ -130,7 +139,6 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
             CKM(cMalloc((void**)&f->kpsDev, f->descOff + (size_t)cap * 32));
             f->descDev = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(f->kpsDev) + f->descOff);
             CKM(cudaHostAlloc((void**)&f->stage, f->descOff + (size_t)cap * 32, cudaHostAllocDefault));
-            CKM(cudaEventCreateWithFlags(&f->staged, cudaEventDisableTiming));
         }
         CKM(cMalloc((void**)&f->kp4, (size_t)cap * sizeof(float4)));
         CKM(cMalloc((void**)&f->cellOf, (size_t)cap * sizeof(int)));
@@ -145,7 +153,10 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
     f->invH = static_cast<float>(kGridRows) / static_cast<float>(f->maxY - f->minY);
     if (needOwn) {
         if (n) {
-            CKM(cudaEventSynchronize(f->staged));          // a previous upload of this slot still reading the staging buffer
+            // a previous upload of this slot may still be reading the staging buffer: not if its stream has been waited on since
+            // (every search does); otherwise wait now - on the same handle its stream, on another one the device (rare)
+            if (f->uploadedBy == M) { if (M->syncEpoch == f->uploadEpoch) CKM(syncStream(M)); }
+            else if (f->uploadedBy) CKM(cudaDeviceSynchronize());
             memcpy(f->stage, v->kps, (size_t)n * sizeof(orbx_keypoint));
             memcpy(f->stage + f->descOff, v->desc, (size_t)n * 32);
             if ((size_t)n * 60 * 2 >= f->descOff + (size_t)n * 32) {        // the gap between the two arrays is small: one copy
@@ -154,7 +165,7 @@ int setFrame(orbm_matcher* M, orbm_frame_s* f, const orbm_frame_view* v) {
                 CKM(cudaMemcpyAsync(f->kpsDev, f->stage, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, M->stream));
                 CKM(cudaMemcpyAsync(f->descDev, f->stage + f->descOff, (size_t)n * 32, cudaMemcpyHostToDevice, M->stream));
             }
-            CKM(cudaEventRecord(f->staged, M->stream));
+            f->uploadedBy = M; f->uploadEpoch = M->syncEpoch;
         }
         f->kpsHost.assign(v->kps, v->kps + n);
         f->haveHost = true;
@@ -181,7 +192,7 @@ int ensureHostKps(orbm_matcher* M, orbm_frame_s* f) {
     f->kpsHost.resize(f->n);
     if (f->n) {
         CKM(cudaMemcpyAsync(f->kpsHost.data(), f->kpsDev, (size_t)f->n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, M->stream));
-        CKM(cudaStreamSynchronize(M->stream));
+        CKM(syncStream(M));
     }
     f->haveHost = true;
     return ORBM_OK;
@@ -244,7 +255,7 @@ int orbm_create(int device, orbm_handle* out) {
 void orbm_destroy(orbm_handle M) {
     if (!M) return;
     cudaSetDevice(M->device);
-    cudaStreamSynchronize(M->stream);
+    syncStream(M);
     if (M->scratch) cudaFree(M->scratch);
     if (M->pinned) cudaFreeHost(M->pinned);
     if (M->dEvals) cudaFree(M->dEvals);
@@ -289,7 +300,7 @@ int orbm_frame_update(orbm_handle M, orbm_frame f, const orbm_frame_view* view) 
 void orbm_frame_destroy(orbm_handle M, orbm_frame f) {
     if (!M || !f) return;
     cudaSetDevice(M->device);
-    cudaStreamSynchronize(M->stream);
+    syncStream(M);
     freeFrameBuffers(f);
     delete f;
 }
@@ -298,7 +309,7 @@ int orbm_frame_grid(orbm_handle M, orbm_frame f, int* off, int* idx) {
     if (!M || !f || !off || !idx) return ORBM_ERR_INVALID;
     CKM(cudaSetDevice(M->device));
     CKM(cudaMemcpyAsync(off, f->cellOff, (size_t)(kGridCells + 1) * sizeof(int), cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     if (off[kGridCells]) CKM(cudaMemcpy(idx, f->cellIdx, (size_t)off[kGridCells] * sizeof(int), cudaMemcpyDeviceToHost));
     return ORBM_OK;
 }
@@ -424,7 +435,7 @@ int runSearch(orbm_matcher* M, const orbm_frame_s* T, SearchParams P, SearchIO& 
     }
     CKM(cudaGetLastError());
     if (!byRounds) CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOcc, (uint8_t*)M->scratch + oOcc, outEnd - oOcc, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     memcpy(io.result.data(), S.host<int>(oRes), (size_t)nq * sizeof(int));
     memcpy(io.dist.data(), S.host<int>(oDist), (size_t)nq * sizeof(int));
     if (io.occ && n && P.state == 1) memcpy(io.occ, S.host<uint8_t>(oOcc), n);
@@ -479,7 +490,7 @@ int orbm_features_in_area(orbm_handle M, orbm_frame f, float x, float y, float r
     ++M->launches;
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oOut, (uint8_t*)M->scratch + oOut, S.off - oOut, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     const int n = *S.host<int>(oN);
     *n_out = n;
     if (out) memcpy(out, S.host<int>(oOut), (size_t)std::min(n, cap) * sizeof(int));
@@ -671,7 +682,7 @@ int orbm_search_initialization(orbm_handle M, orbm_frame f1, orbm_frame f2, floa
     if (n1) {
         CKM(cudaSetDevice(M->device));
         CKM(cudaMemcpyAsync(d1.data(), f1->descDev, (size_t)n1 * 32, cudaMemcpyDeviceToHost, M->stream));
-        CKM(cudaStreamSynchronize(M->stream));
+        CKM(syncStream(M));
     }
     SearchIO io;
     for (int i1 = 0; i1 < n1; ++i1) {
@@ -759,7 +770,7 @@ int fetchDescHost(orbm_matcher* M, orbm_frame_s* f, std::vector<uint8_t>& out) {
     if (f->n) {
         CKM(cudaSetDevice(M->device));
         CKM(cudaMemcpyAsync(out.data(), f->descDev, (size_t)f->n * 32, cudaMemcpyDeviceToHost, M->stream));
-        CKM(cudaStreamSynchronize(M->stream));
+        CKM(syncStream(M));
     }
     return ORBM_OK;
 }
@@ -905,7 +916,7 @@ int orbm_triangulation_candidates(orbm_handle M, orbm_frame kf1, const orbm_feat
     ++M->launches;
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync((uint8_t*)M->pinned + oEv, (uint8_t*)M->scratch + oEv, S.off - oEv, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     M->lastEvals = (long long)*S.host<unsigned long long>(oEv);
     const int* hc = S.host<int>(oCnt); const int* hi = S.host<int>(oIdx); const int* hd = S.host<int>(oDist);
     int status = ORBM_OK;
@@ -941,7 +952,7 @@ int orbm_db_create(orbm_handle M, const uint8_t* rows, long long ndb, int rows_o
 void orbm_db_destroy(orbm_handle M, orbm_db db) {
     if (!M || !db) return;
     cudaSetDevice(M->device);
-    cudaStreamSynchronize(M->stream);
+    syncStream(M);
     if (db->owns) cudaFree(db->rows);
     delete db;
 }
@@ -1321,7 +1332,7 @@ int orbm_knn(orbm_handle M, orbm_db db, const uint8_t* q, int nq, int k, uint16_
     CKM(cudaMemcpyAsync(S.dev<uint8_t>(oQ), S.host<uint8_t>(oQ), (size_t)nq * 32, cudaMemcpyHostToDevice, M->stream));
     if ((rc = orbm_knn_device(M, db, S.dev<uint8_t>(oQ), nq, k, S.dev<uint16_t>(oD), S.dev<int32_t>(oI), nullptr))) return rc;
     CKM(cudaMemcpyAsync(S.host<uint8_t>(oD), S.dev<uint8_t>(oD), S.off - oD, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     memcpy(dist, S.host<uint16_t>(oD), (size_t)nq * k * sizeof(uint16_t));
     memcpy(idx, S.host<int32_t>(oI), (size_t)nq * k * sizeof(int32_t));
     return ORBM_OK;
@@ -1378,7 +1389,7 @@ int orbm_distinctive_descriptors(orbm_handle M, const uint8_t* desc, const int* 
     ++M->launches;
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync(S.host<int>(oB), S.dev<int>(oB), (size_t)npoints * sizeof(int), cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     memcpy(best, S.host<int>(oB), (size_t)npoints * sizeof(int));
     return ORBM_OK;
 }
@@ -1534,7 +1545,7 @@ int orbm_undistort_points(orbm_handle M, const float* xy, int n, const float* K4
     ++M->launches;
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync(S.host<float>(oOut), S.dev<float>(oOut), (size_t)n * 8, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     memcpy(out, S.host<float>(oOut), (size_t)n * 8);
     return ORBM_OK;
 }
@@ -1616,7 +1627,7 @@ int orbm_vocab_create(orbm_handle M, const orbm_vocab_view* v, orbm_vocab* out) 
 void orbm_vocab_destroy(orbm_handle M, orbm_vocab V) {
     if (!M || !V) return;
     cudaSetDevice(M->device);
-    cudaStreamSynchronize(M->stream);
+    syncStream(M);
     cudaFree(V->childOff); cudaFree(V->children); cudaFree(V->desc); cudaFree(V->wordId); cudaFree(V->weight);
     delete V;
 }
@@ -1655,7 +1666,7 @@ int orbm_bow_transform(orbm_handle M, orbm_vocab V, const uint8_t* desc, int n, 
     ++M->launches;
     CKM(cudaGetLastError());
     CKM(cudaMemcpyAsync(S.host<int>(oW), S.dev<int>(oW), (size_t)(oN - oW) + (size_t)n * 4, cudaMemcpyDeviceToHost, M->stream));
-    CKM(cudaStreamSynchronize(M->stream));
+    CKM(syncStream(M));
     const int* w = S.host<int>(oW);
     const int* nd = S.host<int>(oN);
     if (feat_word) memcpy(feat_word, w, (size_t)n * 4);
