@@ -1,23 +1,31 @@
-// Grid-window searches against an occupancy state under the rule "best unblocked candidate, accept if distance <= th"
+// Grid-window searches against an occupancy state under the rules "best unblocked candidate, accept if distance <= th"
 // (SearchByProjection(Cur, Last), src/ORBmatcher.cc:1676-1887; SearchByProjection(Frame, KeyFrame, found), :1889-2010;
-// the Sim3 projections, :427-646) resolved in CLAIM ROUNDS instead of one warp passing over the queries in order.
+// the Sim3 projections, :427-646) and "best / second best with the NN ratio" (SearchByProjection(Frame, local map points),
+// :43-213) resolved in CLAIM ROUNDS instead of one warp passing over the queries in order.
 //
-// The reference loop is sequential: query q takes the best keypoint of its window that no earlier query has taken, if its
-// distance is <= th.  Two facts make that parallel:
-//   (1) only candidates with distance <= th that are free at the start can ever be taken by q, so q's whole future is a
-//       short list (here: its first four such candidates in (distance, scan order), plus how many there were);
-//   (2) blocks only grow.  So q's current pick K (first unblocked entry of its list) is FINAL as soon as no earlier unresolved
-//       occupying query has K anywhere in its list: nobody who comes before q can take K any more, and everything better
-//       than K on q's list is already blocked for good.
-// Phase A (all CTAs): four lanes walk the window columns of one query (contiguous column chunks, merged in scan order) and
-//   write its list.  Phase B (the last CTA to finish): rounds over all unresolved queries in parallel - every occupying query
-//   registers min(q) on the keypoints of its unblocked entries (round-tagged atomicMax, no clearing), a query whose pick
-//   carries no smaller registrant commits; the lowest unresolved query always does, so the rounds end, and the number of
-//   rounds is the longest chain of queries that actually compete (a handful on tracking data) instead of nq / 32 batches.
-//   A query with more than four candidates on file (rare after the distance filter) may have to look beyond its list: while
-//   such an occupying query is unresolved no LATER query commits (it could still claim anything in its window), and when
-//   its four entries are all blocked it walks its window again against the current state.
-// Results are identical to the sequential loop (tests/test_matcher_gpu.py: contention cases against the oracle).
+// The reference loop is sequential: query q takes the best keypoint of its window that no earlier query has taken, if the rule
+// accepts it.  Two facts make that parallel:
+//   (1) only candidates below a distance bound that are free at the start can ever matter to q (rounds_keepable), so q's whole
+//       future is a short list: its first four such candidates in (distance, scan order), plus how many there were;
+//   (2) blocks only grow.  So q's current pick K (first unblocked entry of its list; under the ratio rule the first two) is
+//       FINAL as soon as no earlier unresolved occupying query has K anywhere in its list: nobody who comes before q can take K
+//       any more, and everything better than K on q's list is already blocked for good.
+// Phase A (all CTAs): a warp per query flattens the window's column runs over its lanes (walk_candidates, the reference's order)
+//   and pops the four best by min-reductions.  Phase B (one CTA, a thread per query): rounds over all unresolved queries in
+//   parallel - every occupying query registers min(q) on the keypoints of its unblocked entries (round-tagged atomicMax, no
+//   clearing), a query whose picks carry no smaller registrant commits; the lowest unresolved query always does, so the rounds
+//   end, and their number is the longest chain of queries that actually compete (14-26 on tracking data) instead of nq / 32
+//   batches in sequence.
+//   - A query with more than four candidates on file may have to look beyond its list.  It can only run short if all (but
+//     one, under the ratio rule) of its unblocked entries are also on the list of an earlier unresolved occupying query; only
+//     while that holds does it keep every LATER query from committing (step 1b), and when its entries are used up a warp
+//     rebuilds its list against the state as it is (step 1r).
+//   - A query that does not occupy what it matches (a map point without observations) holds nobody back, so later queries may
+//     commit before it is resolved: keypoints carry the index of the query that took them and block only later queries.
+//   - A run of rounds that settle almost nothing (hundreds of queries piled on a few dozen keypoints) hands the open queries,
+//     compacted in order, to one warp that finishes them in the reference's own order.
+// Results are identical to the sequential loop (tests/test_matcher_gpu.py: contention and pile-up cases against the oracle;
+// tests/test_env_switches_gpu.py: byte-identical to the in-order kernel).
 #pragma once
 #include "orbm_kernels.cuh"
 
@@ -55,7 +63,7 @@ __device__ __forceinline__ bool rounds_keepable(const SearchParams& P, int d) {
 }
 
 // The list of one query, by a whole warp: walk_candidates flattens the window's column runs over the lanes (reference
-// order), every lane keeps the candidates it saw that pass the tests, have distance <= thF and are not blocked, and the four
+// order), every lane keeps the candidates it saw that pass the tests, can matter under the rule and are not blocked, and the four
 // smallest (distance, scan position) of the warp are popped by min-reductions.  Every lane returns the same list.
 template <class Blocked>
 __device__ __forceinline__ void warp_list(const SearchParams& P, const FrameDev& T, int q, Blocked&& isBlocked, Top4& out,
