@@ -262,9 +262,11 @@ def agents_native(local, frames, counts=(1, 4, 8, 16), per_agent=300):
     with tempfile.NamedTemporaryFile(suffix=".u8") as f:
         np.stack(frames[:16]).astype(np.uint8).tofile(f.name)
         nfile = min(len(frames), 16)
-        for track, key in ((1, "extract_and_track"), (0, "extract_only")):
-            r = subprocess.run([exe, f.name, str(W), str(H), str(nfile), str(local), str(per_agent), ",".join(map(str, counts)), str(track)],
-                               capture_output=True, text=True, timeout=600)
+        # *_pinned_frames: the frame array page-locked once (orbx_pin_host, a registered camera ring buffer): frames go up in place
+        for track, pin, key in ((1, 0, "extract_and_track"), (0, 0, "extract_only"), (1, 1, "extract_and_track_pinned_frames"),
+                                (0, 1, "extract_only_pinned_frames")):
+            r = subprocess.run([exe, f.name, str(W), str(H), str(nfile), str(local), str(per_agent), ",".join(map(str, counts)), str(track),
+                                str(pin)], capture_output=True, text=True, timeout=600)
             if r.returncode != 0:
                 out[key] = {"error": r.stderr[-300:]}
                 continue

@@ -56,6 +56,12 @@ int orbx_device_count(void);
 /* PCI bus id of a device ("0000:1b:00.0"), for hosts that bind an agent's threads and pinned staging buffers to the NUMA
  * node its GPU hangs off (mam3slam_b200/numa.py; the reference runs on the CPU and has no counterpart).  out: >= 16 bytes */
 int orbx_device_pci_bus_id(int device, char* out, int len);
+/* Page-lock / release a host range the caller keeps frames or output arrays in (cudaHostRegister / cudaHostUnregister without
+ * CUDA headers on the caller's side).  orbx_extract / orbx_extract_batch use pinned pointers in place; pageable ones are copied
+ * through the handle's staging buffer first (a cv::Mat from cv::imread, src/Agent.cc:92-154, is pageable: the reference has no
+ * counterpart because it never leaves the host). */
+int orbx_pin_host(void* ptr, size_t bytes);
+int orbx_unpin_host(void* ptr);
 const char* orbx_strerror(int status);
 const char* orbx_last_error(orbx_handle h);
 

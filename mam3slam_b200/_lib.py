@@ -33,6 +33,10 @@ def lib():
     L.orbx_device_count.restype = i32
     L.orbx_device_pci_bus_id.restype = i32
     L.orbx_device_pci_bus_id.argtypes = [i32, C.c_char_p, i32]
+    L.orbx_pin_host.restype = i32
+    L.orbx_pin_host.argtypes = [C.c_void_p, C.c_size_t]
+    L.orbx_unpin_host.restype = i32
+    L.orbx_unpin_host.argtypes = [C.c_void_p]
     L.orbx_strerror.restype = C.c_char_p
     L.orbx_strerror.argtypes = [i32]
     L.orbx_last_error.restype = C.c_char_p

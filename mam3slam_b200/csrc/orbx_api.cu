@@ -723,6 +723,24 @@ int orbx_device_pci_bus_id(int device, char* out, int len) {
     return cudaDeviceGetPCIBusId(out, len, device) == cudaSuccess ? ORBX_OK : ORBX_ERR_CUDA;
 }
 
+// Page-lock a host range the caller keeps its frames (or its output arrays) in, e.g. the camera ring buffer: pinned pointers
+// are used in place by orbx_extract / orbx_extract_batch, pageable ones go through the handle's staging buffer (one host copy
+// of the frame per call).  Thin wrappers over cudaHostRegister / cudaHostUnregister so that a C or C++ host needs no CUDA headers.
+int orbx_pin_host(void* ptr, size_t bytes) {
+    if (!ptr || !bytes) return ORBX_ERR_INVALID;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return ORBX_ERR_NO_DEVICE;
+    const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) { cudaGetLastError(); return ORBX_ERR_CUDA; }
+    return ORBX_OK;
+}
+int orbx_unpin_host(void* ptr) {
+    if (!ptr) return ORBX_ERR_INVALID;
+    const cudaError_t e = cudaHostUnregister(ptr);
+    if (e != cudaSuccess) { cudaGetLastError(); return ORBX_ERR_CUDA; }
+    return ORBX_OK;
+}
+
 const char* orbx_strerror(int s) {
     switch (s) {
         case ORBX_OK: return "ok";

@@ -32,8 +32,9 @@ def test_agents_share_one_gpu_and_track(tmp_path):
     path = tmp_path / "frames.u8"
     frames.tofile(path)
 
-    def run(counts, track=1):
-        r = subprocess.run([_built(), str(path), "752", "480", "8", "0", "20", counts, str(track)], capture_output=True, text=True, timeout=300)
+    def run(counts, track=1, pin=0):
+        r = subprocess.run([_built(), str(path), "752", "480", "8", "0", "20", counts, str(track), str(pin)], capture_output=True, text=True,
+                           timeout=300)
         assert r.returncode == 0, r.stderr[-500:]
         return json.loads(r.stdout.strip().splitlines()[-1])["rows"]
 
@@ -45,3 +46,6 @@ def test_agents_share_one_gpu_and_track(tmp_path):
         assert r["gpu_launches"] > 0
     only = run("2", track=0)
     assert only[0]["matches_per_frame"] == 0 and only[0]["frames_per_s"] > 100
+    # frames page-locked once with orbx_pin_host (uploaded in place instead of through the staging buffer): same matches
+    pinned = run("1,3", pin=1)
+    assert [r["matches_per_frame"] for r in pinned] == [r["matches_per_frame"] for r in rows]

@@ -7,7 +7,8 @@
 // with HOST buffers in and out.  bench.py's Python leg measures the same loop under the GIL; this one shows what the
 // library and the GPU do when the host side is native, as it is in the reference.
 //
-// usage: agents_native <frames.u8> <width> <height> <nframes_in_file> <device> <frames_per_agent> <A1,A2,...> [track=1]
+// usage: agents_native <frames.u8> <width> <height> <nframes_in_file> <device> <frames_per_agent> <A1,A2,...> [track=1] [pin=0]
+// pin = 1 page-locks the frame array (orbx_pin_host: a camera ring buffer registered once), so frames are uploaded in place.
 // prints one JSON object.  Built by __graft_entry__.build() (g++, links libmam3slam_b200.so).
 #include "../include/orbx.h"
 #include "../include/orbm.h"
@@ -110,6 +111,7 @@ int main(int argc, char** argv) {
     if (argc < 8) { fprintf(stderr, "usage: %s frames.u8 w h nfile device frames_per_agent A1,A2,.. [track]\n", argv[0]); return 2; }
     const int w = atoi(argv[2]), h = atoi(argv[3]), nfile = atoi(argv[4]), device = atoi(argv[5]), per = atoi(argv[6]);
     const bool track = argc > 8 ? atoi(argv[8]) != 0 : true;
+    const bool pin = argc > 9 ? atoi(argv[9]) != 0 : false;
     std::vector<int> counts;
     for (char* t = strtok(argv[7], ","); t; t = strtok(nullptr, ",")) counts.push_back(atoi(t));
     std::vector<uint8_t> frames((size_t)w * h * nfile);
@@ -117,8 +119,9 @@ int main(int argc, char** argv) {
     if (!f || fread(frames.data(), 1, frames.size(), f) != frames.size()) { fprintf(stderr, "cannot read %s\n", argv[1]); return 3; }
     fclose(f);
     if (orbx_device_count() <= device) { fprintf(stderr, "no CUDA device %d\n", device); return 4; }
+    if (pin && orbx_pin_host(frames.data(), frames.size())) { fprintf(stderr, "orbx_pin_host failed\n"); return 4; }
 
-    printf("{\"track\": %d, \"frames_per_agent\": %d, \"rows\": [", track ? 1 : 0, per);
+    printf("{\"track\": %d, \"pinned_frames\": %d, \"frames_per_agent\": %d, \"rows\": [", track ? 1 : 0, pin ? 1 : 0, per);
     for (size_t ci = 0; ci < counts.size(); ++ci) {
         const int A = counts[ci];
         std::vector<Agent> agents(A);
@@ -173,5 +176,6 @@ int main(int argc, char** argv) {
         }
     }
     printf("]}\n");
+    if (pin) orbx_unpin_host(frames.data());
     return 0;
 }
