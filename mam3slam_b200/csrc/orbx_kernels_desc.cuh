@@ -64,14 +64,37 @@ __global__ void __launch_bounds__(kTreeMaxThreads) k_octree(const DevGeom* __res
     uint64_t* bufA = qtA + (size_t)frame * g->qtCapFrame + L.qtOffset;
     uint64_t* bufB = qtB + (size_t)frame * g->qtCapFrame + L.qtOffset;
     const uint32_t* cf = cand + (size_t)frame * g->candCapFrame;
-    for (int c = wid; c < nc; c += kTreeWarps) {
-        const FastCell cell = cells[cb + c];
-        const int cnt = cc[c], off = S.scanA[c];
-        for (int k = lane; k < cnt; k += 32) {
-            const uint32_t e = cf[cell.outOffset + k];
-            const uint32_t x = (e & 255u) + cell.relX, y = ((e >> 8) & 255u) + cell.relY, sc = e >> 16;
-            bufA[off + k] = (uint64_t)x | ((uint64_t)y << 16) | ((uint64_t)sc << 32);
-            if (pyr) pyr_insert(PV, x, y, sc, (uint32_t)(off + k), L.hX, L.nIni, L.treeH);
+    // A thread per candidate of the level (position i of the concatenated cell lists = its place in the key array; the cell is
+    // found by bisection in the offsets just scanned), four candidates per thread at a time with all their loads issued before
+    // anything is stored: a warp per cell walked 17 (512 threads) to 68 (128 threads) cells in sequence, each a chain of two
+    // L2 round trips that the shared-memory atomics of the insert kept from overlapping.
+    constexpr int kGatherBatch = 4;
+    for (int i0 = tid; i0 < n; i0 += kGatherBatch * kTreeThreads) {
+        uint32_t e[kGatherBatch];
+        int rx[kGatherBatch], ry[kGatherBatch];
+#pragma unroll
+        for (int j = 0; j < kGatherBatch; ++j) {
+            const int i = i0 + j * kTreeThreads;
+            e[j] = 0; rx[j] = 0; ry[j] = 0;
+            if (i < n) {
+                int lo = 0, hi = nc - 1;
+                while (lo < hi) {                                  // last cell whose offset is <= i (empty cells share the next one's)
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (S.scanA[mid] <= i) lo = mid; else hi = mid - 1;
+                }
+                const FastCell& cell = cells[cb + lo];
+                rx[j] = cell.relX; ry[j] = cell.relY;
+                e[j] = cf[cell.outOffset + (i - S.scanA[lo])];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kGatherBatch; ++j) {
+            const int i = i0 + j * kTreeThreads;
+            if (i < n) {
+                const uint32_t x = (e[j] & 255u) + rx[j], y = ((e[j] >> 8) & 255u) + ry[j], sc = e[j] >> 16;
+                bufA[i] = (uint64_t)x | ((uint64_t)y << 16) | ((uint64_t)sc << 32);
+                if (pyr) pyr_insert(PV, x, y, sc, (uint32_t)i, L.hX, L.nIni, L.treeH);
+            }
         }
     }
     __syncthreads();
