@@ -64,24 +64,35 @@ __global__ void __launch_bounds__(kTreeMaxThreads) k_octree(const DevGeom* __res
     uint64_t* bufA = qtA + (size_t)frame * g->qtCapFrame + L.qtOffset;
     uint64_t* bufB = qtB + (size_t)frame * g->qtCapFrame + L.qtOffset;
     const uint32_t* cf = cand + (size_t)frame * g->candCapFrame;
-    // A thread per candidate of the level (position i of the concatenated cell lists = its place in the key array; the cell is
-    // found by bisection in the offsets just scanned), four candidates per thread at a time with all their loads issued before
-    // anything is stored: a warp per cell walked 17 (512 threads) to 68 (128 threads) cells in sequence, each a chain of two
-    // L2 round trips that the shared-memory atomics of the insert kept from overlapping.
+    // A thread per candidate of the level (position i of the concatenated cell lists = its place in the key array).  A warp
+    // takes a contiguous stretch of positions, its lanes interleaved, so a lane's positions only grow: its cell is found by
+    // bisection in the offsets just scanned ONCE and then advanced (cells hold ~30 candidates: about one step per candidate).
+    // Four candidates per thread at a time with all their loads issued before anything is stored: a warp per cell walked 17
+    // (512 threads) to 68 (128 threads) cells in sequence, each a chain of two L2 round trips that the shared-memory atomics
+    // of the insert kept from overlapping.
+    if (tid == 0) S.scanA[nc] = n;                                 // sentinel (block_exscan left the exclusive offsets in scanA[0..nc))
+    __syncthreads();
     constexpr int kGatherBatch = 4;
-    for (int i0 = tid; i0 < n; i0 += kGatherBatch * kTreeThreads) {
+    const int perWarp = (((n + kTreeWarps - 1) / kTreeWarps) + 31) & ~31;
+    const int wBegin = wid * perWarp, wEnd = min(wBegin + perWarp, n);
+    int lo = 0;
+    if (wBegin + lane < wEnd) {
+        const int i = wBegin + lane;
+        int hi = nc - 1;
+        while (lo < hi) {                                          // last cell whose offset is <= i (empty cells share the next one's)
+            const int mid = (lo + hi + 1) >> 1;
+            if (S.scanA[mid] <= i) lo = mid; else hi = mid - 1;
+        }
+    }
+    for (int i0 = wBegin + lane; i0 < wEnd; i0 += kGatherBatch * 32) {
         uint32_t e[kGatherBatch];
         int rx[kGatherBatch], ry[kGatherBatch];
 #pragma unroll
         for (int j = 0; j < kGatherBatch; ++j) {
-            const int i = i0 + j * kTreeThreads;
+            const int i = i0 + j * 32;
             e[j] = 0; rx[j] = 0; ry[j] = 0;
-            if (i < n) {
-                int lo = 0, hi = nc - 1;
-                while (lo < hi) {                                  // last cell whose offset is <= i (empty cells share the next one's)
-                    const int mid = (lo + hi + 1) >> 1;
-                    if (S.scanA[mid] <= i) lo = mid; else hi = mid - 1;
-                }
+            if (i < wEnd) {
+                while (i >= S.scanA[lo + 1]) ++lo;
                 const FastCell& cell = cells[cb + lo];
                 rx[j] = cell.relX; ry[j] = cell.relY;
                 e[j] = cf[cell.outOffset + (i - S.scanA[lo])];
@@ -89,8 +100,8 @@ __global__ void __launch_bounds__(kTreeMaxThreads) k_octree(const DevGeom* __res
         }
 #pragma unroll
         for (int j = 0; j < kGatherBatch; ++j) {
-            const int i = i0 + j * kTreeThreads;
-            if (i < n) {
+            const int i = i0 + j * 32;
+            if (i < wEnd) {
                 const uint32_t x = (e[j] & 255u) + rx[j], y = ((e[j] >> 8) & 255u) + ry[j], sc = e[j] >> 16;
                 bufA[i] = (uint64_t)x | ((uint64_t)y << 16) | ((uint64_t)sc << 32);
                 if (pyr) pyr_insert(PV, x, y, sc, (uint32_t)i, L.hX, L.nIni, L.treeH);
